@@ -1,0 +1,383 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see cfo_types.hpp header).
+// Leaf arithmetic of the FVMCC path: perfect-gas Euler/Navier-Stokes variable sets,
+// Roe linearisation, Roe flux, Navier-Stokes diffusive flux with the DiamondVolume
+// derivative.  Every function follows the cited reference lines operation by
+// operation (same association order, no FMA: build with -ffp-contract=off).
+#pragma once
+#include "cfo_types.hpp"
+
+namespace cfo {
+
+struct PData {            // EulerTerm enum (plugins/NavierStokes/EulerTerm.hh:85-86)
+  double rho, p, H, E, A, T, V, v[3];
+};
+
+// Correctly-rounded x^1.5 and x^3 (see DESIGN.md "pow"): the reference calls glibc pow(),
+// which is correctly rounded in all but ~1e-4 of cases; oracle and product both use
+// the correctly rounded value so that they agree bit for bit.
+static inline double cr_pow15(double x) {
+  if (!(x > 0.0)) return (x == 0.0) ? 0.0 : std::numeric_limits<double>::quiet_NaN();
+  const double s0 = std::sqrt(x);
+  const __float128 X = x, S0 = s0;
+  const __float128 S = S0 + (X - S0*S0)/(2*S0);   // Newton step: |err| ~ 2^-105
+  return (double)(X*S);
+}
+static inline double cr_pow3(double x) {
+  const __float128 X = x;
+  return (double)(X*X*X);
+}
+
+// ---------------------------------------------------------------------------
+template <int D>
+struct Phys {
+  static constexpr int Q = D + 2;
+  static constexpr int TID = D + 1;
+
+  // Euler2DCons.cxx:441-465, Euler3DCons.cxx:538-562, Euler2DPuvt.cxx:78-108, Euler3DPvt.ci:76-116
+  static void computePhysicalData(const Config& c, const double* s, PData& d) {
+    if (c.updateVar == UV_CONS) {
+      const double rho = s[0];
+      const double ovRho = 1./rho;
+      double V2;
+      if (D == 2) {
+        const double u = s[1]*ovRho, v = s[2]*ovRho;
+        V2 = u*u + v*v;
+        d.v[0] = u; d.v[1] = v; d.v[2] = 0.;
+      } else {
+        const double u = s[1]*ovRho, v = s[2]*ovRho, w = s[3]*ovRho;
+        V2 = u*u + v*v + w*w;
+        d.v[0] = u; d.v[1] = v; d.v[2] = w;
+      }
+      const double gammaMinus1 = c.gamma - 1.;
+      d.rho = rho;
+      d.p = gammaMinus1*(s[TID] - 0.5*rho*V2);
+      const double pOvRho = d.p*ovRho;
+      d.E = s[TID]*ovRho;
+      d.H = d.E + pOvRho;
+      d.A = std::sqrt(c.gamma*pOvRho);
+      d.T = pOvRho/c.R;
+      d.V = std::sqrt(V2);
+    } else {
+      const double p = s[0] + c.pOffset;                 // EulerTerm.hh:199-202
+      const double T = s[TID];
+      const double rho = p/(c.R*T);                       // EulerTerm.hh:208-212
+      double V2;
+      if (D == 2) { V2 = s[1]*s[1] + s[2]*s[2]; d.v[0] = s[1]; d.v[1] = s[2]; d.v[2] = 0.; }
+      else { V2 = s[1]*s[1] + s[2]*s[2] + s[3]*s[3]; d.v[0] = s[1]; d.v[1] = s[2]; d.v[2] = s[3]; }
+      const double gammaDivGammaMinus1 = c.gamma/(c.gamma - 1.);
+      const double pOvRho = p/rho;
+      d.rho = rho;
+      d.p = s[0];
+      d.H = gammaDivGammaMinus1*pOvRho + 0.5*V2;
+      d.E = d.H - pOvRho;
+      d.A = std::sqrt(c.gamma*pOvRho);
+      d.T = T;
+      d.V = std::sqrt(V2);
+    }
+  }
+
+  // Euler2DCons.cxx / Euler3DCons.cxx:564-574 computeStateFromPhysicalData (Cons only; used by mirror BC)
+  static void stateFromPhysicalDataCons(const PData& d, double* s) {
+    const double rho = d.rho;
+    s[0] = rho;
+    for (int i = 0; i < D; ++i) s[1+i] = rho*d.v[i];
+    s[TID] = rho*d.H - d.p;
+  }
+
+  // Euler2DVarSet.cxx:83-117, Euler3DVarSet.cxx:78-105
+  static void convFlux(const PData& d, const double* n, double* f) {
+    double un;
+    if (D == 2) un = d.v[0]*n[0] + d.v[1]*n[1];
+    else        un = d.v[0]*n[0] + d.v[1]*n[1] + d.v[2]*n[2];
+    const double rhoVn = d.rho*un;
+    f[0] = rhoVn;
+    for (int i = 0; i < D; ++i) f[1+i] = d.p*n[i] + d.v[i]*rhoVn;
+    f[TID] = rhoVn*d.H;
+  }
+
+  // Euler2DVarSet.cxx:39-45, Euler3DVarSet.cxx:41-46
+  static double maxEigenValue(const PData& d, const double* n) {
+    double un;
+    if (D == 2) un = d.v[0]*n[0] + d.v[1]*n[1];
+    else        un = d.v[0]*n[0] + d.v[1]*n[1] + d.v[2]*n[2];
+    return un + d.A;
+  }
+
+  // update -> solution(Cons): identity or EulerPvtToCons.cxx:49-70
+  static void toCons(const Config& c, const double* s, double* r) {
+    if (c.updateVar == UV_CONS) { for (int i = 0; i < Q; ++i) r[i] = s[i]; return; }
+    const double p = s[0] + c.pOffset;
+    const double T = s[TID];
+    const double rho = p/(c.R*T);
+    r[0] = rho;
+    double V2 = 0.;
+    for (int i = 0; i < D; ++i) { const double u = s[1+i]; r[1+i] = rho*u; V2 += u*u; }
+    r[TID] = p/(c.gamma - 1.) + 0.5*rho*V2;
+  }
+
+  // Euler2DConsToRoe.cxx:41-52, Euler3DConsToRoe.cxx:41-58
+  static void consToRoe(const Config& c, const double* s, double* r) {
+    const double gamma = c.gamma;
+    const double gammaMinus1 = gamma - 1.;
+    if (D == 2) {
+      const double sqrho = std::sqrt(s[0]);
+      r[0] = sqrho;
+      r[1] = s[1]/sqrho;
+      r[2] = s[2]/sqrho;
+      const double sqrhoU2 = r[1]*r[1] + r[2]*r[2];
+      r[3] = (gamma*s[3] - 0.5*gammaMinus1*sqrhoU2)/sqrho;
+    } else {
+      const double rho = s[0], rhoU = s[1], rhoV = s[2], rhoW = s[3], rhoE = s[4];
+      r[0] = std::sqrt(rho);
+      r[1] = rhoU/r[0];
+      r[2] = rhoV/r[0];
+      r[3] = rhoW/r[0];
+      r[4] = (gamma*rhoE - 0.5*gammaMinus1*(rhoU*rhoU + rhoV*rhoV + rhoW*rhoW)/rho)/r[0];
+    }
+  }
+
+  // Euler2DLinearRoe.cxx:44-101, Euler3DLinearRoe.cxx:43-92.  Returns false if a2 < 0
+  // (the reference throws BadValueException there).
+  static bool linearize(const Config& c, const double* zL, const double* zR, PData& d) {
+    double sumZ[Q];
+    for (int i = 0; i < Q; ++i) { sumZ[i] = 0.; sumZ[i] += zL[i]; sumZ[i] += zR[i]; }
+    const double gamma = c.gamma;
+    if (D == 2) {
+      const double invNbStates = 1./2.;
+      double avZ[Q];
+      for (int i = 0; i < Q; ++i) avZ[i] = sumZ[i]*invNbStates;
+      const double ovAvZ0 = 1./avZ[0];
+      d.rho = avZ[0]*avZ[0];
+      d.v[0] = avZ[1]*ovAvZ0;
+      d.v[1] = avZ[2]*ovAvZ0;
+      d.v[2] = 0.;
+      const double speed2 = (d.v[0]*d.v[0] + d.v[1]*d.v[1]);
+      d.V = std::sqrt(speed2);
+      d.H = avZ[3]*ovAvZ0;
+      const double a2 = (gamma-1.)*(d.H - 0.5*speed2);
+      if (a2 < 0.0) return false;
+      d.A = std::sqrt(a2);
+      d.T = a2/(gamma*c.R);
+      const double RT = c.R*d.T;
+      d.p = d.rho*RT;
+      d.E = d.H - RT;
+    } else {
+      double avZ0 = sumZ[0]/2.;
+      d.rho = avZ0*avZ0;
+      d.v[0] = sumZ[1]/sumZ[0];
+      d.v[1] = sumZ[2]/sumZ[0];
+      d.v[2] = sumZ[3]/sumZ[0];
+      d.H = sumZ[4]/sumZ[0];
+      d.V = std::sqrt(d.v[0]*d.v[0] + d.v[1]*d.v[1] + d.v[2]*d.v[2]);
+      const double speed2 = d.V*d.V;
+      const double a2 = (gamma - 1.)*(d.H - 0.5*speed2);
+      if (a2 < 0.0) return false;
+      d.A = std::sqrt(a2);
+      d.T = a2/(gamma*c.R);
+      d.p = d.rho*c.R*d.T;
+      d.E = d.H - d.p/d.rho;
+    }
+    return true;
+  }
+
+  // Euler2DCons.cxx:156-228, Euler3DCons.cxx:150-239 (row-major Q x Q)
+  static void eigen(const Config& c, const PData& lin, const double* nrm, double* R, double* L, double* ev) {
+    const double gamma = c.gamma;
+    const double gammaMinus1 = gamma - 1.;
+    if (D == 2) {
+      const double nx = nrm[0], ny = nrm[1];
+      const double avRho = lin.rho, avU = lin.v[0], avV = lin.v[1], avH = lin.H, avA = lin.A;
+      const double ovAvA = 1./avA;
+      const double ovAvA2 = ovAvA*ovAvA;
+      const double um = avU*nx + avV*ny;
+      const double ra = 0.5*avRho*ovAvA;
+      const double coeffM2 = 0.5*gammaMinus1*(avU*avU + avV*avV)*ovAvA2;
+      const double ovAvRho = 1./avRho;
+      const double uDivA = gammaMinus1*avU*ovAvA;
+      const double vDivA = gammaMinus1*avV*ovAvA;
+      const double ovAvRhoA = ovAvRho*ovAvA;
+#define RE(i,j) R[(i)*4+(j)]
+#define LE(i,j) L[(i)*4+(j)]
+      RE(0,0) = 1.; RE(0,1) = 0.; RE(0,2) = ra; RE(0,3) = ra;
+      RE(1,0) = avU; RE(1,1) = avRho*ny; RE(1,2) = ra*(avU + avA*nx); RE(1,3) = ra*(avU - avA*nx);
+      RE(2,0) = avV; RE(2,1) = -avRho*nx; RE(2,2) = ra*(avV + avA*ny); RE(2,3) = ra*(avV - avA*ny);
+      RE(3,0) = 0.5*(avU*avU + avV*avV); RE(3,1) = avRho*(avU*ny - avV*nx);
+      RE(3,2) = ra*(avH + avA*um); RE(3,3) = ra*(avH - avA*um);
+      LE(0,0) = 1.- coeffM2; LE(0,1) = uDivA*ovAvA; LE(0,2) = vDivA*ovAvA; LE(0,3) = -gammaMinus1*ovAvA2;
+      LE(1,0) = ovAvRho*(avV*nx - avU*ny); LE(1,1) = ovAvRho*ny; LE(1,2) = -ovAvRho*nx; LE(1,3) = 0.0;
+      LE(2,0) = avA*ovAvRho*(coeffM2 - um*ovAvA); LE(2,1) = ovAvRho*(nx - uDivA);
+      LE(2,2) = ovAvRho*(ny - vDivA); LE(2,3) = gammaMinus1*ovAvRhoA;
+      LE(3,0) = avA*ovAvRho*(coeffM2 + um*ovAvA); LE(3,1) = -ovAvRho*(nx + uDivA);
+      LE(3,2) = -ovAvRho*(ny + vDivA); LE(3,3) = gammaMinus1*ovAvRhoA;
+#undef RE
+#undef LE
+      ev[0] = um; ev[1] = um; ev[2] = um + avA; ev[3] = um - avA;
+    } else {
+      const double nx = nrm[0], ny = nrm[1], nz = nrm[2];
+      const double avRho = lin.rho, avU = lin.v[0], avV = lin.v[1], avW = lin.v[2];
+      const double avH = lin.H, avA = lin.A;
+      const double avK = 0.5*lin.V*lin.V;
+      const double um = avU*nx + avV*ny + avW*nz;
+      const double ra = 0.5*avRho/avA;
+      const double avA2 = avA*avA;
+      const double invAvRho = 1./avRho;
+      const double k1 = gammaMinus1*avK/avA2;
+      const double k2 = 1.0 - k1;
+      const double k3 = -gammaMinus1/avA2;
+      const double uDivA = gammaMinus1*avU/avA;
+      const double vDivA = gammaMinus1*avV/avA;
+      const double wDivA = gammaMinus1*avW/avA;
+      const double uDivA2 = uDivA/avA;
+      const double vDivA2 = vDivA/avA;
+      const double wDivA2 = wDivA/avA;
+      const double rhoA = avRho*avA;
+#define RE(i,j) R[(i)*5+(j)]
+#define LE(i,j) L[(i)*5+(j)]
+      RE(0,0) = nx; RE(0,1) = ny; RE(0,2) = nz; RE(0,3) = ra; RE(0,4) = ra;
+      RE(1,0) = avU*nx; RE(1,1) = avU*ny - avRho*nz; RE(1,2) = avU*nz + avRho*ny;
+      RE(1,3) = ra*(avU + avA*nx); RE(1,4) = ra*(avU - avA*nx);
+      RE(2,0) = avV*nx + avRho*nz; RE(2,1) = avV*ny; RE(2,2) = avV*nz - avRho*nx;
+      RE(2,3) = ra*(avV + avA*ny); RE(2,4) = ra*(avV - avA*ny);
+      RE(3,0) = avW*nx - avRho*ny; RE(3,1) = avW*ny + avRho*nx; RE(3,2) = avW*nz;
+      RE(3,3) = ra*(avW + avA*nz); RE(3,4) = ra*(avW - avA*nz);
+      RE(4,0) = avK*nx + avRho*(avV*nz - avW*ny);
+      RE(4,1) = avK*ny + avRho*(avW*nx - avU*nz);
+      RE(4,2) = avK*nz + avRho*(avU*ny - avV*nx);
+      RE(4,3) = ra*(avH + avA*um); RE(4,4) = ra*(avH - avA*um);
+      LE(0,0) = nx*k2 - invAvRho*(avV*nz - avW*ny); LE(0,1) = uDivA2*nx;
+      LE(0,2) = vDivA2*nx + nz*invAvRho; LE(0,3) = wDivA2*nx - ny*invAvRho; LE(0,4) = k3*nx;
+      LE(1,0) = ny*k2 - invAvRho*(avW*nx - avU*nz); LE(1,1) = uDivA2*ny - nz*invAvRho;
+      LE(1,2) = vDivA2*ny; LE(1,3) = wDivA2*ny + nx*invAvRho; LE(1,4) = k3*ny;
+      LE(2,0) = nz*k2 - invAvRho*(avU*ny - avV*nx); LE(2,1) = uDivA2*nz + ny*invAvRho;
+      LE(2,2) = vDivA2*nz - nx*invAvRho; LE(2,3) = wDivA2*nz; LE(2,4) = k3*nz;
+      LE(3,0) = avA*invAvRho*(k1 - um/avA); LE(3,1) = invAvRho*(nx - uDivA);
+      LE(3,2) = invAvRho*(ny - vDivA); LE(3,3) = invAvRho*(nz - wDivA); LE(3,4) = gammaMinus1/rhoA;
+      LE(4,0) = avA*invAvRho*(k1 + um/avA); LE(4,1) = invAvRho*(-nx - uDivA);
+      LE(4,2) = invAvRho*(-ny - vDivA); LE(4,3) = invAvRho*(-nz - wDivA); LE(4,4) = gammaMinus1/rhoA;
+#undef RE
+#undef LE
+      ev[0] = um; ev[1] = um; ev[2] = um; ev[3] = um + avA; ev[4] = um - avA;
+    }
+  }
+
+  // RoeFlux.cxx:120-163: flux per unit area.  uL/uR are the reconstructed states in
+  // UPDATE variables, pL/pR their physical data.  Returns false on a2 < 0.
+  //   result = 0.5*(_sumFlux - k*(_rightEv*(_absEvalues*_leftEv))*(stateR - stateL))
+  // is evaluated lazily by MatExprT.hh:255-390 / ExprT.hh as
+  //   result_i = 0.5*(sumFlux_i - sum_k [ (k * sum_m R(i,m)*(|ev_m|*L(m,k))) * (sR_k - sL_k) ])
+  // (pinned against the reference headers by oracle/ref_mathtools.cpp).
+  static bool roeFlux(const Config& c, const double* uL, const double* uR,
+                      const PData& pL, const PData& pR, const double* n, double* result) {
+    double sL[Q], sR[Q], zL[Q], zR[Q];
+    toCons(c, uL, sL); toCons(c, uR, sR);
+    consToRoe(c, sL, zL); consToRoe(c, sR, zR);
+    PData lin;
+    if (!linearize(c, zL, zR, lin)) return false;
+    double Rm[Q*Q], Lm[Q*Q], ev[Q], aev[Q];
+    eigen(c, lin, n, Rm, Lm, ev);
+    for (int i = 0; i < Q; ++i) aev[i] = std::abs(ev[i]);     // RoeFlux.cxx:200-203
+    double sumFlux[Q], f2[Q];
+    convFlux(pL, n, sumFlux);
+    convFlux(pR, n, f2);
+    for (int i = 0; i < Q; ++i) sumFlux[i] += f2[i];
+    const double kred = c.diffRedCoeff;
+    for (int i = 0; i < Q; ++i) {
+      double res = 0.;
+      for (int k = 0; k < Q; ++k) {
+        double m = 0.;
+        for (int mm = 0; mm < Q; ++mm) m += Rm[i*Q+mm]*(aev[mm]*Lm[mm*Q+k]);
+        res += (kred*m)*(sR[k] - sL[k]);
+      }
+      result[i] = 0.5*(sumFlux[i] - res);
+    }
+    return true;
+  }
+
+  // ---- Navier-Stokes -------------------------------------------------------
+  // SimplerSutherlandDynViscosity.cxx:104-107, SutherlandDynViscosity.cxx:107-110
+  static double dynViscosityDim(const Config& c, double /*pdim*/, double Tdim) {
+    switch (c.viscLaw) {
+      case VISC_SIMPLER_SUTHERLAND: return c.viscRef*cr_pow15(Tdim)/(c.viscTRef + Tdim);
+      case VISC_SUTHERLAND: return c.viscRef*(c.viscTRef + c.viscSuthConst)/(Tdim + c.viscSuthConst)*cr_pow15(Tdim/c.viscTRef);
+      default: return c.fixedVisc;
+    }
+  }
+  // NavierStokes2DPuvt / NavierStokes3DPvt::getDynViscosity (NavierStokes3DPvt.cxx:103-109)
+  static double dynViscosity(const Config& c, const double* avState) {
+    const double Tdim = c.tempRef*avState[TID];
+    const double pdim = c.pRef*(avState[0] + c.pOffset);
+    return dynViscosityDim(c, pdim, Tdim)/c.muRef;
+  }
+  // NavierStokes3DPvt.hh:92-99
+  static double thermConductivity(const Config& c, double mu) {
+    if (c.isAdimensional) return mu;
+    return mu*c.cpOverPrandtl;
+  }
+  // NavierStokes3DPvt.cxx:113-117
+  static double nsDensity(const Config& c, const double* avState) {
+    const double p = avState[0] + c.pOffset;
+    return p/(c.R*avState[TID]);
+  }
+
+  // NavierStokesVarSet.cxx:70-129 + NavierStokes{2,3}DVarSet::getFlux (2D: NavierStokes2DVarSet.cxx:93-115,
+  // 3D: NavierStokes3DVarSet.cxx:25-45).  grad[v][ix]; returns flux per unit area in f[0..Q).
+  static void nsFluxUnit(const Config& c, const double* avState, const double (*grad)[3],
+                         const double* n, double mu, double lambda, double* f) {
+    const double twoThird = 2./3.;
+    double divTerm = 0.0;
+    if (D == 3) divTerm = grad[3][2];
+    const double* gradU = grad[1];
+    const double* gradV = grad[2];
+    const double twoThirdDivV = twoThird*(gradU[0] + gradV[1] + divTerm);
+    const double coeffTauMu = c.coeffTau*mu;
+    double tau[3][3];
+    tau[0][0] = coeffTauMu*(2.*gradU[0] - twoThirdDivV);
+    tau[0][1] = tau[1][0] = coeffTauMu*(gradU[1] + gradV[0]);
+    tau[1][1] = coeffTauMu*(2.*gradV[1] - twoThirdDivV);
+    if (D == 3) {
+      const double* gradW = grad[3];
+      tau[0][2] = tau[2][0] = coeffTauMu*(gradU[2] + gradW[0]);
+      tau[1][2] = tau[2][1] = coeffTauMu*(gradV[2] + gradW[1]);
+      tau[2][2] = coeffTauMu*(2.*gradW[2] - twoThirdDivV);
+    }
+    double ip = 0.;
+    for (int i = 0; i < D; ++i) ip += grad[TID][i]*n[i];
+    const double qFlux = -c.coeffQ*lambda*ip;
+    f[0] = 0.;
+    for (int i = 0; i < D; ++i) {
+      double r = 0.;
+      for (int k = 0; k < D; ++k) r += tau[i][k]*n[k];
+      f[1+i] = r;
+    }
+    if (D == 3) {
+      double r = 0.;
+      for (int i = 0; i < D; ++i) r += f[1+i]*avState[1+i];
+      f[TID] = r - qFlux;
+    } else {
+      f[TID] = (tau[0][0]*avState[1] + tau[0][1]*avState[2])*n[0] +
+               (tau[0][1]*avState[1] + tau[1][1]*avState[2])*n[1] - qFlux;
+    }
+  }
+};
+
+// MathFunctions.hh:167-179
+static inline void crossProd(const double* v1, const double* v2, double* r) {
+  r[0] =  v1[1]*v2[2] - v1[2]*v2[1];
+  r[1] = -v1[0]*v2[2] + v1[2]*v2[0];
+  r[2] =  v1[0]*v2[1] - v1[1]*v2[0];
+}
+// MathFunctions.hh:92-104
+template <int D> static inline double getDistance(const double* a, const double* b) {
+  double dist = 0.;
+  for (int i = 0; i < D; ++i) { const double diff = a[i] - b[i]; dist += diff*diff; }
+  return std::sqrt(dist);
+}
+// NormalsCalculator.hh:209-231
+static inline void faceTriagNormal(const double* ci, const double* cj, const double* ck, double* out) {
+  double v1[3], v2[3], v3[3];
+  for (int d = 0; d < 3; ++d) { v1[d] = cj[d] - ci[d]; v2[d] = ck[d] - cj[d]; }
+  crossProd(v1, v2, v3);
+  for (int d = 0; d < 3; ++d) out[d] = v3[d]*0.5;
+}
+
+} // namespace cfo

@@ -1,0 +1,689 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see cfo_types.hpp header).
+// The FVMCC ComputeRHS / ComputeRhsJacob command restated with the reference's
+// own loop structure: edge-wise LSQ accumulation, nodal extrapolation, a single
+// loop over faces in TRS order with first-touch limiter evaluation, scatter of
+// the flux into rhs, and per-face finite-difference Jacobian blocks added into
+// a BSR matrix in face order.
+#pragma once
+#include "cfo_physics.hpp"
+
+namespace cfo {
+
+struct Outputs {
+  double* rhs;          // [nCells*q]   (zeroed here, FVMCC_ComputeRHS.cxx:692)
+  double* updateCoeff;  // [nCells]     (accumulated, NOT zeroed: UpdateSol.cxx:192 does that)
+  double* uX;           // [nCells*q]
+  double* uY;
+  double* uZ;
+  double* limiter;      // [nCells*q]   in/out (historical limiter)
+  double* nstates;      // [nNodes*q]
+  // BSR Jacobian (may be null): pattern from FVMCCSparsity.cxx:47-106 (diag + face neighbours)
+  const int32_t* bsrRowPtr;
+  const int32_t* bsrColInd;
+  double* bsrVal;       // [nnzb*q*q], block row-major [ib][jb]  (BlockAccumulator.hh:289-296)
+  int32_t status;       // 0 ok, 1 = a2<0 in the Roe linearisation (BadValueException)
+};
+
+template <int D>
+class Solver {
+public:
+  static constexpr int Q = D + 2;
+  typedef Phys<D> P;
+
+  Solver(const Config& c, const MeshView& m, const BC* bcs) : cfg(c), mesh(m), bc(bcs) {}
+
+  // ---- boundary conditions (a16) -------------------------------------------
+  // FVMCC_BaseBC.ci:144-187 executeOnTrs -> setGhostState(face) for every boundary face.
+  void setGhostState(int f, const double* inner, double* ghost) const {
+    const BC& b = bc[mesh.faceBC[f]];
+    switch (b.type) {
+      case BC_SUPER_OUTLET:
+        for (int i = 0; i < Q; ++i) ghost[i] = inner[i];
+        break;
+      case BC_DIRICHLET:
+        for (int i = 0; i < Q; ++i) ghost[i] = b.mask[i] ? (2.*b.value[i] - inner[i]) : inner[i];
+        break;
+      case BC_MIRROR_VELOCITY: {       // MirrorVelocity.cxx:71-111 (velocity IDs = 1..D)
+        const double* nr = &mesh.normals[(size_t)f*D];
+        double vn = 0., area2 = 0.;
+        for (int i = 0; i < D; ++i) { const double nxComp = nr[i]; vn += nxComp*inner[1+i]; area2 += nxComp*nxComp; }
+        ghost[0] = inner[0];
+        for (int i = 0; i < D; ++i) ghost[1+i] = inner[1+i] - 2.0*vn*nr[i]/area2;
+        ghost[Q-1] = inner[Q-1];
+        break;
+      }
+      case BC_MIRROR_EULER_CONS: {     // MirrorEuler2D.cxx:56-94
+        const double* nr = &mesh.normals[(size_t)f*D];
+        double n[3] = {0,0,0};
+        double s2 = 0.;
+        if (D == 2) s2 = nr[0]*nr[0] + nr[1]*nr[1]; else s2 = nr[0]*nr[0] + nr[1]*nr[1] + nr[2]*nr[2];
+        const double invFaceLength = 1./std::sqrt(s2);
+        for (int i = 0; i < D; ++i) n[i] = nr[i]*invFaceLength;
+        PData di, dg;
+        P::computePhysicalData(cfg, inner, di);
+        double vn;
+        if (D == 2) vn = di.v[0]*n[0] + di.v[1]*n[1]; else vn = di.v[0]*n[0] + di.v[1]*n[1] + di.v[2]*n[2];
+        const double gamma = cfg.gamma;
+        const double gammaDivGammaMinus1 = gamma/(gamma - 1.0);
+        dg.rho = di.rho;
+        dg.v[2] = 0.;
+        for (int i = 0; i < D; ++i) dg.v[i] = di.v[i] - 2.0*vn*n[i];
+        dg.V = di.V;
+        dg.p = di.p;
+        dg.H = (gammaDivGammaMinus1*dg.p + 0.5*dg.rho*dg.V*dg.V)/dg.rho;
+        dg.A = std::sqrt(gamma*dg.p/dg.rho);
+        dg.T = di.T;
+        P::stateFromPhysicalDataCons(dg, ghost);
+        break;
+      }
+      default: throw std::runtime_error("unknown BC type");
+    }
+  }
+
+  void applyBC(double* U) const {
+    for (int f = mesh.nInner; f < mesh.nFaces; ++f) {
+      setGhostState(f, &U[(size_t)mesh.faceL[f]*Q], &U[(size_t)mesh.faceR[f]*Q]);
+    }
+  }
+
+  // ---- LSQ weights / normal matrix (a4): LeastSquareP1PolyRec{2,3}D::updateWeights
+  // (LeastSquareP1PolyRec2D.cxx:266-330, 3D.cxx:333-411)
+  void updateWeights() {
+    const int nc = mesh.nCells;
+    for (int k = 0; k < 6; ++k) l[k].assign(nc, 0.0);
+    weights.clear();
+    for (int iState = 0; iState < nc; ++iState) {
+      const double* xf = &mesh.centres[(size_t)iState*D];
+      for (int in = mesh.stencilPtr[iState]; in < mesh.stencilPtr[iState+1]; ++in) {
+        const int last = mesh.stencil[in];
+        const bool ghost = last >= nc;
+        if (ghost || last > iState) {
+          const double* xl = &mesh.centres[(size_t)last*D];
+          const double deltaR = getDistance<D>(xf, xl);
+          const double w = 1.0/deltaR;
+          weights.push_back(w);
+          double d[3] = {0,0,0};
+          for (int i = 0; i < D; ++i) d[i] = w*(xl[i] - xf[i]);
+          if (D == 2) {
+            l[0][iState] += d[0]*d[0]; l[1][iState] += d[0]*d[1]; l[3][iState] += d[1]*d[1];
+            if (!ghost) { l[0][last] += d[0]*d[0]; l[1][last] += d[0]*d[1]; l[3][last] += d[1]*d[1]; }
+          } else {
+            // l11 l12 l13 l22 l23 l33 -> l[0] l[1] l[2] l[3] l[4] l[5]
+            l[0][iState] += d[0]*d[0]; l[1][iState] += d[0]*d[1]; l[2][iState] += d[0]*d[2];
+            l[3][iState] += d[1]*d[1]; l[4][iState] += d[1]*d[2]; l[5][iState] += d[2]*d[2];
+            if (!ghost) {
+              l[0][last] += d[0]*d[0]; l[1][last] += d[0]*d[1]; l[2][last] += d[0]*d[2];
+              l[3][last] += d[1]*d[1]; l[4][last] += d[1]*d[2]; l[5][last] += d[2]*d[2];
+            }
+          }
+        }
+      }
+    }
+  }
+
+  // ---- LSQ gradients (a5): LeastSquareP1PolyRec2D.cxx:80-154, 3D.cxx:80-200
+  void computeGradients(const double* U, Outputs& o) {
+    const int nc = mesh.nCells;
+    std::vector<double> lf1(nc), lf2(nc), lf3(nc);
+    for (int iVar = 0; iVar < Q; ++iVar) {
+      std::fill(lf1.begin(), lf1.end(), 0.0);
+      std::fill(lf2.begin(), lf2.end(), 0.0);
+      std::fill(lf3.begin(), lf3.end(), 0.0);
+      size_t iEdge = 0;
+      for (int iState = 0; iState < nc; ++iState) {
+        const double* xf = &mesh.centres[(size_t)iState*D];
+        for (int in = mesh.stencilPtr[iState]; in < mesh.stencilPtr[iState+1]; ++in) {
+          const int last = mesh.stencil[in];
+          const bool ghost = last >= nc;
+          if (ghost || last > iState) {
+            const double* xl = &mesh.centres[(size_t)last*D];
+            const double w = weights[iEdge];
+            const double dx = w*(xl[0] - xf[0]);
+            const double dy = w*(xl[1] - xf[1]);
+            const double dz = (D == 3) ? w*(xl[2] - xf[2]) : 0.;
+            const double du = w*(U[(size_t)last*Q + iVar] - U[(size_t)iState*Q + iVar]);
+            lf1[iState] += dx*du; lf2[iState] += dy*du;
+            if (D == 3) lf3[iState] += dz*du;
+            if (!ghost) {
+              lf1[last] += dx*du; lf2[last] += dy*du;
+              if (D == 3) lf3[last] += dz*du;
+            }
+            ++iEdge;
+          }
+        }
+      }
+      for (int i = 0; i < nc; ++i) {
+        if (D == 2) {
+          const double l11 = l[0][i], l12 = l[1][i], l22 = l[3][i];
+          const double invDet = 1./(l11*l22 - l12*l12);
+          o.uX[(size_t)i*Q + iVar] = (l22*lf1[i] - l12*lf2[i])*invDet;
+          o.uY[(size_t)i*Q + iVar] = (l11*lf2[i] - l12*lf1[i])*invDet;
+        } else {
+          const double l11 = l[0][i], l12 = l[1][i], l13 = l[2][i], l22 = l[3][i], l23 = l[4][i], l33 = l[5][i];
+          const double det = l11*l22*l33 - l11*l23*l23 - l12*l12*l33 + l12*l13*l23 + l13*l12*l23 - l13*l13*l22;
+          const double linv11 = l22*l33 - l23*l23;
+          const double linv22 = l11*l33 - l13*l13;
+          const double linv33 = l11*l22 - l12*l12;
+          const double linv12 = -(l12*l33 - l13*l23);
+          const double linv13 = l12*l23 - l13*l22;
+          const double linv23 = -(l11*l23 - l13*l12);
+          if (!(std::abs(det) <= std::numeric_limits<double>::min())) {   // !MathChecks::isZero(det)
+            o.uX[(size_t)i*Q + iVar] = (linv11*lf1[i] + linv12*lf2[i] + linv13*lf3[i])/det;
+            o.uY[(size_t)i*Q + iVar] = (linv12*lf1[i] + linv22*lf2[i] + linv23*lf3[i])/det;
+            o.uZ[(size_t)i*Q + iVar] = (linv13*lf1[i] + linv23*lf2[i] + linv33*lf3[i])/det;
+          } else {
+            o.uX[(size_t)i*Q + iVar] = 0.0; o.uY[(size_t)i*Q + iVar] = 0.0; o.uZ[(size_t)i*Q + iVar] = 0.0;
+          }
+        }
+      }
+    }
+  }
+
+  // ---- nodal extrapolation (a6): DistanceBasedExtrapolator.ci:35-149
+  void extrapolateInAllNodes(const double* U, Outputs& o) const {
+    for (int n = 0; n < mesh.nNodes; ++n) {
+      double* ns = &o.nstates[(size_t)n*Q];
+      for (int i = 0; i < Q; ++i) ns[i] = 0.;
+      for (int k = mesh.nodeNbrPtr[n]; k < mesh.nodeNbrPtr[n+1]; ++k) {
+        const double w = mesh.nodeW[k];
+        const double* s = &U[(size_t)mesh.nodeNbr[k]*Q];
+        for (int i = 0; i < Q; ++i) ns[i] += s[i]*w;
+      }
+    }
+  }
+
+  // FVMCC_PolyRec.hh:114-123
+  void faceMidPoint(int f, double* xq) const {
+    const int b = mesh.faceNodePtr[f], e = mesh.faceNodePtr[f+1];
+    const int nb = e - b;
+    const double ov = 1./nb;
+    for (int d = 0; d < D; ++d) xq[d] = 0.0;
+    for (int k = b; k < e; ++k) {
+      const double* xn = &mesh.nodes[(size_t)mesh.faceNodes[k]*D];
+      for (int d = 0; d < D; ++d) xq[d] += xn[d]*ov;
+    }
+  }
+
+  // ---- limiter (a7): Venktn2D.cxx:111-260, Venktn3D.cxx:44-190 ("OLD IMPLEMENTATION" branch,
+  // isMFMHD = false), BarthJesp.cxx:60-155
+  void limitCell(int c, const double* U, const Outputs& o, double* lim) const {
+    const int fb = mesh.cellFacePtr[c], fe = mesh.cellFacePtr[c+1];
+    const int nbFaces = fe - fb;
+    const double* xc = &mesh.centres[(size_t)c*D];
+    double xq[6][3];
+    for (int k = 0; k < nbFaces; ++k) faceMidPoint(mesh.cellFaces[fb+k], xq[k]);
+    for (int iVar = 0; iVar < Q; ++iVar) {
+      const double u0 = U[(size_t)c*Q + iVar];
+      double min0 = u0, max0 = u0, avgDistance = 0.0;
+      if (cfg.useFullStencil) {
+        const int sb = mesh.stencilPtr[c], se = mesh.stencilPtr[c+1];
+        const int nbNeighbors = se - sb;
+        for (int is = sb; is < se; ++is) {
+          const int s = mesh.stencil[is];
+          if (s != c) {
+            min0 = std::min(min0, U[(size_t)s*Q + iVar]);
+            max0 = std::max(max0, U[(size_t)s*Q + iVar]);
+            avgDistance += getDistance<D>(xc, &mesh.centres[(size_t)s*D]);
+          }
+        }
+        avgDistance /= nbNeighbors;
+      } else {
+        for (int k = 0; k < nbFaces; ++k) {
+          const int f = mesh.cellFaces[fb+k];
+          const int nb = (mesh.faceL[f] == c) ? mesh.faceR[f] : mesh.faceL[f];
+          min0 = std::min(min0, U[(size_t)nb*Q + iVar]);
+          max0 = std::max(max0, U[(size_t)nb*Q + iVar]);
+          avgDistance += getDistance<D>(xc, &mesh.centres[(size_t)nb*D]);
+        }
+        avgDistance /= nbFaces;
+      }
+      const double deltaPlusMax = max0 - u0;
+      const double deltaPlusMin = min0 - u0;
+      double psi = 1.0;
+      double psimin = 1.1;
+      const double ux = o.uX[(size_t)c*Q + iVar], uy = o.uY[(size_t)c*Q + iVar];
+      const double uz = (D == 3) ? o.uZ[(size_t)c*Q + iVar] : 0.;
+      if (cfg.limiter == LIM_VENKTN) {
+        const double epsilon = cfg.coeffEps*cfg.magnitudeValues[iVar]*cfg.magnitudeValues[iVar]*
+          cr_pow3(avgDistance/cfg.length);
+        for (int k = 0; k < nbFaces; ++k) {
+          double deltaMin;
+          if (D == 2) deltaMin = ux*(xq[k][0] - xc[0]) + uy*(xq[k][1] - xc[1]);
+          else deltaMin = ux*(xq[k][0] - xc[0]) + uy*(xq[k][1] - xc[1]) + uz*(xq[k][2] - xc[2]);
+          if (deltaMin > 0.0) {
+            const double dPlusMax2 = deltaPlusMax*deltaPlusMax;
+            const double dPlusMaxMin = deltaPlusMax*deltaMin;
+            psi = (dPlusMax2 + 2.0*dPlusMaxMin + epsilon)/
+              (dPlusMax2 + dPlusMaxMin + 2.0*deltaMin*deltaMin + epsilon);
+          }
+          if (deltaMin < 0.0) {
+            const double y = deltaPlusMin/deltaMin;
+            psi = (y*y + 2*y)/(y*y + y + 2.);
+          }
+          psimin = std::min(psi, psimin);
+        }
+      } else { // LIM_BARTHJESP  BarthJesp.cxx:121-148
+        for (int k = 0; k < nbFaces; ++k) {
+          double deltaMin;
+          if (D == 2) deltaMin = ux*(xq[k][0] - xc[0]) + uy*(xq[k][1] - xc[1]);
+          else deltaMin = ux*(xq[k][0] - xc[0]) + uy*(xq[k][1] - xc[1]) + uz*(xq[k][2] - xc[2]);
+          if (deltaMin > 0.0) psi = std::min(1., deltaPlusMax/deltaMin);
+          if (deltaMin < 0.0) psi = std::min(1., deltaPlusMin/deltaMin);
+          psimin = std::min(psi, psimin);
+        }
+      }
+      lim[iVar] = psimin;
+    }
+  }
+
+  // FVMCC_PolyRec.cxx:120-167 computeFaceLimiter (first touch per cell through cellFlag)
+  void computeFaceLimiter(int f, const double* U, Outputs& o) {
+    if (cfg.limiter == LIM_NONE) return;
+    for (int iCell = 0; iCell < 2; ++iCell) {
+      const int c = (iCell == 0) ? mesh.faceL[f] : mesh.faceR[f];
+      if (c >= mesh.nCells) continue;   // ghost
+      if (cellFlag[c]) continue;
+      if (cfg.residual > cfg.limitRes && (cfg.limitIter > 0 && cfg.iter < cfg.limitIter)) {
+        for (int i = 0; i < Q; ++i) o.limiter[(size_t)c*Q + i] = 1.0;
+        limitCell(c, U, o, &o.limiter[(size_t)c*Q]);
+      } else if (!cfg.freezeLimiter) {
+        double tmp[Q];
+        limitCell(c, U, o, tmp);
+        for (int i = 0; i < Q; ++i)
+          o.limiter[(size_t)c*Q + i] = std::min(tmp[i], o.limiter[(size_t)c*Q + i]);
+      }
+    }
+  }
+
+  // ---- reconstruction (a8) -------------------------------------------------
+  struct FaceCtx {
+    int f, L, R; bool isB;
+    double xq[3];
+    double n[3];          // unit normal (FVMCC_ComputeRHS.cxx:518-534)
+    double area;
+    double vL[Q], vR[Q];  // extrapolated values
+    double bL[Q], bR[Q];  // backups
+    PData pL, pR;
+    // diffusive part
+    int nbCV;             // vertices in the control volume
+    const double* cvState[6];
+    double muBkp, lambdaBkp;
+    double pn1[5][3], pn2[5][3];  // pyramid normals (rows 1..4 used) / tetra normals
+    double n2d[4][2];
+    double volume;
+  };
+
+  double gradCoeff(int stateID, int iVar, const double* xq, const double* xs, const Outputs& o) const {
+    if (D == 2)
+      return cfg.gradientFactor*(o.uX[(size_t)stateID*Q+iVar]*(xq[0] - xs[0]) +
+                                 o.uY[(size_t)stateID*Q+iVar]*(xq[1] - xs[1]));
+    return cfg.gradientFactor*(o.uX[(size_t)stateID*Q+iVar]*(xq[0] - xs[0]) +
+                               o.uY[(size_t)stateID*Q+iVar]*(xq[1] - xs[1]) +
+                               o.uZ[(size_t)stateID*Q+iVar]*(xq[2] - xs[2]));
+  }
+
+  // LeastSquareP1PolyRec2D.cxx:158-217 / 3D.cxx:204-268 / ConstantPolyRec.cxx:43-47
+  void extrapolate(FaceCtx& x, const double* U, Outputs& o, bool withLimiter) {
+    faceMidPoint(x.f, x.xq);
+    const double* sL = &U[(size_t)x.L*Q];
+    const double* sR = &U[(size_t)x.R*Q];
+    if (cfg.polyRec == PR_CONSTANT) {
+      for (int i = 0; i < Q; ++i) { x.vL[i] = sL[i]; x.vR[i] = sR[i]; x.bL[i] = sL[i]; x.bR[i] = sR[i]; }
+      return;
+    }
+    if (withLimiter) computeFaceLimiter(x.f, U, o);
+    const int gradR = x.isB ? x.L : x.R;
+    const double* xL = &mesh.centres[(size_t)x.L*D];
+    const double* xR = &mesh.centres[(size_t)x.R*D];
+    const int32_t* zg = x.isB ? bc[mesh.faceBC[x.f]].zeroGrad : nullptr;
+    for (int iVar = 0; iVar < Q; ++iVar) {
+      const bool z = zg && zg[iVar];
+      const double gcS = (!z) ? gradCoeff(x.L, iVar, x.xq, xL, o) : 0.0;
+      const double gcN = (!z) ? gradCoeff(gradR, iVar, x.xq, xR, o) : 0.0;
+      const double lValue = (cfg.stopLimiting == 0) ? o.limiter[(size_t)x.L*Q + iVar] : 1.;
+      x.vL[iVar] = sL[iVar] + lValue*gcS;
+      const double rValue = (cfg.stopLimiting == 0) ? o.limiter[(size_t)gradR*Q + iVar] : 1.;
+      x.vR[iVar] = sR[iVar] + rValue*gcN;
+      x.bL[iVar] = x.vL[iVar]; x.bR[iVar] = x.vR[iVar];
+    }
+  }
+
+  // LeastSquareP1PolyRec2D.cxx:221-262 / 3D.cxx:272-318 / FVMCC_PolyRec.hh:149-157
+  void extrapolateVar(FaceCtx& x, const double* U, const Outputs& o, int iVar, int leftOrRight) {
+    for (int i = 0; i < Q; ++i) { x.vL[i] = x.bL[i]; x.vR[i] = x.bR[i]; }   // copyBackupValues
+    const int st = leftOrRight == 0 ? x.L : x.R;
+    double* v = leftOrRight == 0 ? x.vL : x.vR;
+    if (cfg.polyRec == PR_CONSTANT) { v[iVar] = U[(size_t)st*Q + iVar]; return; }
+    const int stateID = (leftOrRight == 0) ? x.L : (x.isB ? x.L : x.R);
+    const double* xs = &mesh.centres[(size_t)st*D];
+    const int32_t* zg = x.isB ? bc[mesh.faceBC[x.f]].zeroGrad : nullptr;
+    const bool z = zg && zg[iVar];
+    const double gc = (!z) ? gradCoeff(stateID, iVar, x.xq, xs, o) : 0.0;
+    const double lValue = (cfg.stopLimiting == 0) ? o.limiter[(size_t)stateID*Q + iVar] : 1.;
+    v[iVar] = U[(size_t)st*Q + iVar] + lValue*gc;
+  }
+
+  // ---- convective flux incl. face integration (FVMCC_FluxSplitter.hh:79-83) and, when
+  // !isPerturb, the update coefficient (RoeFlux.cxx:165-185)
+  bool convectiveFlux(FaceCtx& x, bool isPerturb, Outputs& o, double* flux) {
+    P::computePhysicalData(cfg, x.vL, x.pL);   // computeStatesData, FVMCC_ComputeRHS.hh:112-118
+    P::computePhysicalData(cfg, x.vR, x.pR);
+    for (int i = 0; i < Q; ++i) flux[i] = 0.;
+    if (!P::roeFlux(cfg, x.vL, x.vR, x.pL, x.pR, x.n, flux)) { o.status = 1; return false; }
+    if (!isPerturb) {
+      const double faceArea = x.area/1;       // polyRec->nbQPoints() == 1
+      double maxEV = P::maxEigenValue(x.pL, x.n);
+      o.updateCoeff[x.L] += std::max(maxEV, 0.)*faceArea;
+      if (!x.isB) {
+        double tn[3];
+        for (int i = 0; i < D; ++i) tn[i] = -1.0*x.n[i];
+        maxEV = P::maxEigenValue(x.pR, tn);
+        o.updateCoeff[x.R] += std::max(maxEV, 0.)*faceArea;
+      }
+    }
+    for (int i = 0; i < Q; ++i) flux[i] *= x.area;
+    return true;
+  }
+
+  // ---- diffusive flux (a14,a15): NSFlux.ci:59-156 with DiamondVolume{2,3}DDerivative
+  void diffusiveFlux(FaceCtx& x, const double* U, bool isPerturb, int iPerturbVar, Outputs& o, double* dflux) {
+    const int nb = mesh.faceNodePtr[x.f+1] - mesh.faceNodePtr[x.f];
+    const int32_t* fn = &mesh.faceNodes[mesh.faceNodePtr[x.f]];
+    const double* cL = &mesh.centres[(size_t)x.L*D];
+    const double* cR = &mesh.centres[(size_t)x.R*D];
+    if (!isPerturb) {
+      // computeControlVolume: DiamondVolume2DDerivative.cxx:91-137, 3D.cxx:386-411
+      if (D == 2) {
+        x.nbCV = 4;
+        x.cvState[0] = &o.nstates[(size_t)fn[0]*Q]; x.cvState[1] = &U[(size_t)x.L*Q];
+        x.cvState[2] = &o.nstates[(size_t)fn[1]*Q]; x.cvState[3] = &U[(size_t)x.R*Q];
+        const double* node0 = &mesh.nodes[(size_t)fn[0]*D]; const double* node1 = cL;
+        const double* node2 = &mesh.nodes[(size_t)fn[1]*D]; const double* node3 = cR;
+        x.n2d[0][0] = -node0[1] + node1[1]; x.n2d[0][1] = -node1[0] + node0[0];
+        x.n2d[1][0] = -node1[1] + node2[1]; x.n2d[1][1] = -node2[0] + node1[0];
+        x.n2d[2][0] = -node2[1] + node3[1]; x.n2d[2][1] = -node3[0] + node2[0];
+        x.n2d[3][0] = -node3[1] + node0[1]; x.n2d[3][1] = -node0[0] + node3[0];
+        const double det = (node2[0] - node0[0])*(node3[1] - node1[1]) - (node3[0] - node1[0])*(node2[1] - node0[1]);
+        if (det < 0.0) for (int k = 0; k < 4; ++k) { x.n2d[k][0] *= -1.; x.n2d[k][1] *= -1.; }
+        x.volume = 0.5*std::abs(det);
+      } else if (nb == 3) {
+        x.nbCV = 5;
+        for (int k = 0; k < 3; ++k) x.cvState[k] = &o.nstates[(size_t)fn[k]*Q];
+        x.cvState[3] = &U[(size_t)x.L*Q]; x.cvState[4] = &U[(size_t)x.R*Q];
+        x.volume = mesh.cvol[x.f];
+      } else {
+        x.nbCV = 6;
+        for (int k = 0; k < 4; ++k) x.cvState[k] = &o.nstates[(size_t)fn[k]*Q];
+        x.cvState[4] = &U[(size_t)x.L*Q]; x.cvState[5] = &U[(size_t)x.R*Q];
+        // compute2PyramidNormals: DiamondVolume3DDerivative.cxx:336-383
+        const double* c0 = &mesh.nodes[(size_t)fn[0]*3]; const double* c1 = &mesh.nodes[(size_t)fn[1]*3];
+        const double* c2 = &mesh.nodes[(size_t)fn[2]*3]; const double* c3 = &mesh.nodes[(size_t)fn[3]*3];
+        double factor = (!mesh.cvSign[x.f]) ? 1.0 : -1.0;
+        faceTriagNormal(c0, c1, cL, x.pn1[1]); faceTriagNormal(c1, c2, cL, x.pn1[2]);
+        faceTriagNormal(c2, c3, cL, x.pn1[3]); faceTriagNormal(c0, cL, c3, x.pn1[4]);
+        for (int r = 1; r < 5; ++r) for (int d = 0; d < 3; ++d) x.pn1[r][d] *= factor;
+        faceTriagNormal(c0, c1, cR, x.pn2[1]); faceTriagNormal(c1, c2, cR, x.pn2[2]);
+        faceTriagNormal(c2, c3, cR, x.pn2[3]); faceTriagNormal(c0, cR, c3, x.pn2[4]);
+        factor *= -1.;
+        for (int r = 1; r < 5; ++r) for (int d = 0; d < 3; ++d) x.pn2[r][d] *= factor;
+        x.volume = mesh.cvol[x.f];
+      }
+    }
+    // setGradientVars (NavierStokes3DPvt.cxx:52-63): values(i,j) = (*states[j])[i]
+    double values[Q][6];
+    for (int i = 0; i < Q; ++i) for (int j = 0; j < x.nbCV; ++j) values[i][j] = x.cvState[j][i];
+    double grad[Q][3];
+    double avState[Q];
+    if (D == 2) {
+      const double invVolume = 0.5/x.volume;
+      for (int i = 0; i < Q; ++i) {
+        const double v01 = values[i][0] + values[i][1];
+        const double v12 = values[i][1] + values[i][2];
+        const double v23 = values[i][2] + values[i][3];
+        const double v30 = values[i][3] + values[i][0];
+        for (int ix = 0; ix < 2; ++ix)
+          grad[i][ix] = invVolume*(x.n2d[0][ix]*v01 + x.n2d[1][ix]*v12 + x.n2d[2][ix]*v23 + x.n2d[3][ix]*v30);
+        grad[i][2] = 0.;
+      }
+      for (int i = 0; i < Q; ++i) avState[i] = 0.5*(x.cvState[0][i] + x.cvState[2][i]);
+    } else if (nb == 3) {
+      // compute2TetraGradient: DiamondVolume3DDerivative.cxx:190-263 (normals recomputed on every call)
+      const double* node0 = &mesh.nodes[(size_t)fn[0]*3]; const double* node1 = &mesh.nodes[(size_t)fn[1]*3];
+      const double* node2 = &mesh.nodes[(size_t)fn[2]*3]; const double* node3 = cL; const double* node4 = cR;
+      double factor = (!mesh.cvSign[x.f]) ? -0.5 : 0.5;
+      double v1[3], v2[3], v3[3], n031[3], n132[3], n023[3], n041[3], n142[3], n024[3];
+      auto nrm = [&](const double* a, const double* b, const double* c2_, const double* d, double fct, double* out) {
+        for (int k = 0; k < 3; ++k) { v1[k] = a[k] - b[k]; v2[k] = c2_[k] - d[k]; }
+        crossProd(v1, v2, v3);
+        for (int k = 0; k < 3; ++k) out[k] = fct*v3[k];
+      };
+      nrm(node3, node0, node1, node0, factor, n031);
+      nrm(node3, node1, node2, node1, factor, n132);
+      nrm(node2, node0, node3, node0, factor, n023);
+      factor *= -1;
+      nrm(node4, node0, node1, node0, factor, n041);
+      nrm(node4, node1, node2, node1, factor, n142);
+      nrm(node2, node0, node4, node0, factor, n024);
+      const double invVolume = (1./3.)/x.volume;
+      for (int i = 0; i < Q; ++i) {
+        const double v031 = values[i][0] + values[i][3] + values[i][1];
+        const double v132 = values[i][1] + values[i][3] + values[i][2];
+        const double v023 = values[i][0] + values[i][2] + values[i][3];
+        const double v041 = values[i][0] + values[i][4] + values[i][1];
+        const double v142 = values[i][1] + values[i][4] + values[i][2];
+        const double v024 = values[i][0] + values[i][2] + values[i][4];
+        for (int ix = 0; ix < 3; ++ix)
+          grad[i][ix] = invVolume*(n031[ix]*v031 + n132[ix]*v132 + n023[ix]*v023 +
+                                   n041[ix]*v041 + n142[ix]*v142 + n024[ix]*v024);
+      }
+      for (int i = 0; i < Q; ++i) avState[i] = (1./3.)*(x.cvState[0][i] + x.cvState[1][i] + x.cvState[2][i]);
+    } else {
+      // compute2PyramidGradient: DiamondVolume3DDerivative.cxx:267-298
+      const double invVolume = (1./3.)/x.volume;
+      for (int i = 0; i < Q; ++i) {
+        const double v014 = values[i][0] + values[i][1] + values[i][4];
+        const double v124 = values[i][1] + values[i][2] + values[i][4];
+        const double v234 = values[i][2] + values[i][3] + values[i][4];
+        const double v043 = values[i][0] + values[i][4] + values[i][3];
+        const double v015 = values[i][0] + values[i][1] + values[i][5];
+        const double v125 = values[i][1] + values[i][2] + values[i][5];
+        const double v235 = values[i][2] + values[i][3] + values[i][5];
+        const double v053 = values[i][0] + values[i][5] + values[i][3];
+        for (int ix = 0; ix < 3; ++ix)
+          grad[i][ix] = invVolume*(x.pn1[1][ix]*v014 + x.pn1[2][ix]*v124 + x.pn1[3][ix]*v234 + x.pn1[4][ix]*v043 +
+                                   x.pn2[1][ix]*v015 + x.pn2[2][ix]*v125 + x.pn2[3][ix]*v235 + x.pn2[4][ix]*v053);
+      }
+      for (int i = 0; i < Q; ++i)
+        avState[i] = 0.25*(x.cvState[0][i] + x.cvState[1][i] + x.cvState[2][i] + x.cvState[3][i]);
+    }
+    // setComposition (NavierStokes3DPvt.cxx:206-223, no chemistry library) +
+    // computeTransportProperties (NavierStokesVarSet.cxx:70-92)
+    bool useBackUp = false, setBackUp = false;
+    if (isPerturb && iPerturbVar != P::TID) useBackUp = true;
+    else if (!isPerturb) setBackUp = true;
+    double mu, lambda;
+    if (useBackUp || freezeCoeff) { mu = x.muBkp; lambda = x.lambdaBkp; }
+    else {
+      mu = P::dynViscosity(cfg, avState)*cfg.artDiffCoeff;
+      lambda = P::thermConductivity(cfg, mu);
+      if (setBackUp) { x.muBkp = mu; x.lambdaBkp = lambda; }
+    }
+    P::nsFluxUnit(cfg, avState, grad, x.n, mu, lambda, dflux);
+    for (int i = 0; i < Q; ++i) dflux[i] *= x.area;
+    if (!isPerturb) {
+      const double nu = mu/P::nsDensity(cfg, avState);
+      const double diffUpdateCoeff = nu*x.area*x.area/x.volume;
+      o.updateCoeff[x.L] += diffUpdateCoeff;
+      if (!x.isB) o.updateCoeff[x.R] += diffUpdateCoeff;
+    }
+  }
+
+  // NumericalJacobian.hh:131-140,224-228
+  double computeEps(int iVar, double value) const {
+    const double sgn = (value < 0.0) ? -1.0 : 1.0;
+    return cfg.fdTol*sgn*std::max(std::abs(value), std::abs(cfg.refValues[iVar]));
+  }
+
+  int findSlot(const Outputs& o, int row, int col) const {
+    for (int k = o.bsrRowPtr[row]; k < o.bsrRowPtr[row+1]; ++k) if (o.bsrColInd[k] == col) return k;
+    throw std::runtime_error("BSR slot not found");
+  }
+  // BlockAccumulator::addValues(i,j,jb,values) -> column jb of block (row,col): [ib][jb]
+  void addColumn(Outputs& o, int row, int col, int jb, const double* v) const {
+    double* blk = &o.bsrVal[(size_t)findSlot(o, row, col)*Q*Q];
+    for (int ib = 0; ib < Q; ++ib) blk[ib*Q + jb] += v[ib];
+  }
+
+  // ---- the command (a17, a18): FVMCC_ComputeRHS.cxx:139-325, FVMCC_ComputeRhsJacob.cxx:126-443
+  // U holds cell states followed by ghost states ([nCells+nGhosts][q]); ghost states must already
+  // be set (CellCenterFVM.cxx:464 applyBC before execute); U is perturbed and restored in place.
+  void execute(double* U, Outputs& o) {
+    const int nc = mesh.nCells;
+    o.status = 0;
+    // initializeComputationRHS (FVMCC_ComputeRHS.cxx:690-705 / FVMCC_ComputeRhsJacob.cxx:410-429)
+    std::fill(o.rhs, o.rhs + (size_t)nc*Q, 0.0);
+    cellFlag.assign(nc, 0);
+    const bool doJac = cfg.computeJacobian && o.bsrVal;
+    if (doJac) std::fill(o.bsrVal, o.bsrVal + (size_t)o.bsrRowPtr[nc]*Q*Q, 0.0);
+    if (cfg.polyRec == PR_LINEARLS) {
+      if (weights.empty()) updateWeights();
+      computeGradients(U, o);
+    }
+    extrapolateInAllNodes(U, o);
+
+    FaceCtx x;
+    double flux[Q], dFlux[Q], pertFlux[Q], fluxDiff[Q];
+    for (int f = 0; f < mesh.nFaces; ++f) {
+      x.f = f; x.L = mesh.faceL[f]; x.R = mesh.faceR[f]; x.isB = (x.R >= nc);
+      const bool upL = mesh.updatable[x.L];
+      const bool upR = (!x.isB) && mesh.updatable[x.R];
+      if (!(upL || upR)) continue;                     // FVMCC_ComputeRHS.cxx:212-213
+      // setFaceIntegratorData
+      const double invArea = 1./mesh.areas[f];
+      for (int i = 0; i < D; ++i) x.n[i] = mesh.normals[(size_t)f*D + i]*invArea;
+      x.area = mesh.areas[f];
+      extrapolate(x, U, o, true);
+      if (!convectiveFlux(x, false, o, flux)) return;
+      const bool hasDiff = (cfg.diffusive == DIFF_NS);
+      if (hasDiff) {
+        freezeCoeff = false;
+        diffusiveFlux(x, U, false, 0, o, dFlux);
+        for (int i = 0; i < Q; ++i) flux[i] -= dFlux[i];
+      }
+      // updateRHS (FVMCC_ComputeRHS.cxx:455-514), non axisymmetric: _rMid = _invr = 1
+      {
+        const double coeff = cfg.resFactor*1.0;
+        double rFlux[Q];
+        for (int i = 0; i < Q; ++i) rFlux[i] = coeff*flux[i];
+        for (int i = 0; i < Q; ++i) o.rhs[(size_t)x.L*Q + i] -= rFlux[i]*1.0;
+        if (!x.isB) for (int i = 0; i < Q; ++i) o.rhs[(size_t)x.R*Q + i] += rFlux[i]*1.0;
+        cellFlag[x.L] = 1; if (!x.isB) cellFlag[x.R] = 1;
+      }
+      if (!doJac) continue;
+      freezeCoeff = cfg.freezeDiffCoeff != 0;
+      if (!x.isB) {
+        // computeBothJacobTerms / computeJacobTerm (FVMCC_ComputeRhsJacob.cxx:126-236)
+        double upFactor[2];
+        if (upL && upR) { upFactor[0] = cfg.resFactor; upFactor[1] = -1.0; }
+        else {
+          const int idx = upL ? 0 : 1;
+          upFactor[idx] = std::pow(-1., (double)idx)*cfg.resFactor;
+        }
+        for (int iCell = 0; iCell < 2; ++iCell) {
+          const int st = (iCell == 0) ? x.L : x.R;
+          for (int iVar = 0; iVar < Q; ++iVar) {
+            double& val = U[(size_t)st*Q + iVar];
+            const double orig = val;
+            const double eps = computeEps(iVar, val);
+            val += eps;
+            // computeConvDiffFluxes (FVMCC_ComputeRhsJacob.cxx:321-343)
+            extrapolateVar(x, U, o, iVar, iCell);
+            if (!convectiveFlux(x, true, o, pertFlux)) { val = orig; return; }
+            if (hasDiff) {
+              diffusiveFlux(x, U, true, iVar, o, dFlux);
+              for (int i = 0; i < Q; ++i) pertFlux[i] -= dFlux[i];
+            }
+            const double invEps = 1./eps;
+            for (int i = 0; i < Q; ++i) fluxDiff[i] = (pertFlux[i] - flux[i])*invEps;
+            if (upL && upR) {
+              for (int i = 0; i < Q; ++i) fluxDiff[i] *= upFactor[0];
+              addColumn(o, x.L, st, iVar, fluxDiff);
+              for (int i = 0; i < Q; ++i) fluxDiff[i] *= upFactor[1];
+              addColumn(o, x.R, st, iVar, fluxDiff);
+            } else {
+              const int idx = upL ? 0 : 1;
+              for (int i = 0; i < Q; ++i) fluxDiff[i] *= upFactor[idx];
+              addColumn(o, idx == 0 ? x.L : x.R, st, iVar, fluxDiff);
+            }
+            val = orig;
+            (iCell == 0 ? x.vL : x.vR)[iVar] = (iCell == 0 ? x.bL : x.bR)[iVar];   // restoreValues
+          }
+        }
+      } else if (upL) {
+        // computeBoundaryJacobianTerm (FVMCC_ComputeRhsJacob.cxx:240-317)
+        double origGhost[Q];
+        for (int i = 0; i < Q; ++i) origGhost[i] = U[(size_t)x.R*Q + i];
+        for (int iVar = 0; iVar < Q; ++iVar) {
+          double& val = U[(size_t)x.L*Q + iVar];
+          const double orig = val;
+          const double eps = computeEps(iVar, val);
+          val += eps;
+          setGhostState(f, &U[(size_t)x.L*Q], &U[(size_t)x.R*Q]);
+          extrapolate(x, U, o, true);   // cellFlag[L] is already set: the limiter is not recomputed
+          if (!convectiveFlux(x, true, o, pertFlux)) { val = orig; return; }
+          if (hasDiff) {
+            diffusiveFlux(x, U, true, iVar, o, dFlux);
+            for (int i = 0; i < Q; ++i) pertFlux[i] -= dFlux[i];
+          }
+          const double invEps = 1./eps;
+          for (int i = 0; i < Q; ++i) fluxDiff[i] = (pertFlux[i] - flux[i])*invEps;
+          for (int i = 0; i < Q; ++i) fluxDiff[i] *= cfg.resFactor;
+          addColumn(o, x.L, x.L, iVar, fluxDiff);
+          val = orig;
+          for (int i = 0; i < Q; ++i) U[(size_t)x.R*Q + i] = origGhost[i];
+        }
+      }
+    }
+  }
+
+  // ---- pseudo-steady time term (a21): FVMCC_PseudoSteadyTimeRhs.cxx:106-262
+  // (steady: dt == 0 -> diag = updateCoeff/CFL; numerical transformation matrix)
+  void pseudoSteadyTimeRhs(double* U, const double* pastU, Outputs& o) const {
+    const bool doJac = cfg.computeJacobian && o.bsrVal;
+    for (int c = 0; c < mesh.nCells; ++c) {
+      const double diagValue = o.updateCoeff[c]/cfg.cfl;
+      if (!mesh.updatable[c]) continue;
+      double tempState[Q], tPast[Q], tPert[Q], fluxDiff[Q];
+      P::toCons(cfg, &U[(size_t)c*Q], tempState);
+      P::toCons(cfg, &pastU[(size_t)c*Q], tPast);
+      for (int iEq = 0; iEq < Q; ++iEq) {
+        const double dU = tempState[iEq] - tPast[iEq];
+        o.rhs[(size_t)c*Q + iEq] -= dU*diagValue*cfg.resFactor;
+      }
+      if (doJac) {
+        for (int iVar = 0; iVar < Q; ++iVar) {
+          double& val = U[(size_t)c*Q + iVar];
+          const double orig = val;
+          const double eps = computeEps(iVar, val);
+          val += eps;
+          P::toCons(cfg, &U[(size_t)c*Q], tPert);
+          const double invEps = 1./eps;
+          for (int i = 0; i < Q; ++i) fluxDiff[i] = (tPert[i] - tempState[i])*invEps;
+          for (int i = 0; i < Q; ++i) fluxDiff[i] *= diagValue*cfg.resFactor;
+          addColumn(o, c, c, iVar, fluxDiff);
+          val = orig;
+        }
+      }
+    }
+  }
+
+  const Config& cfg;
+  const MeshView& mesh;
+  const BC* bc;
+  std::vector<double> l[6];
+  std::vector<double> weights;
+  std::vector<uint8_t> cellFlag;
+  bool freezeCoeff = false;
+};
+
+} // namespace cfo

@@ -1,0 +1,117 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY.
+// CPU restatement of COOLFluiD's cell-centred finite-volume (FVMCC) ComputeRHS /
+// ComputeRhsJacob path.  Nothing under oracle/ is part of the shipped product:
+// only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+// legs may load it, and only as the checker / CPU baseline.
+//
+// Parity status: the arithmetic follows the reference file:line cited at each
+// function; the evaluation order of the lazy MathTools expression templates is
+// pinned against the reference's own headers through oracle/_ref (see
+// oracle/ref_mathtools.cpp); the end-to-end behaviour is pinned against the
+// reference's regression value `### Residual = -4.0017502` of
+// plugins/NavierStokes/testcases/Wedge/wedgeFVM.CFcase:14 (tests/test_wedge_pin.py).
+// Per-cell residual / Jacobian entries have no golden vectors in the reference
+//  and are pinned only through the above.
+//
+// All paths are relative to /root/reference.
+#pragma once
+#include <cstdint>
+#include <cmath>
+#include <vector>
+#include <array>
+#include <algorithm>
+#include <stdexcept>
+#include <string>
+#include <limits>
+
+namespace cfo {
+
+constexpr int MAXEQ = 9;
+constexpr int MAXDIM = 3;
+
+// ---- enums shared (by value) with the product's include/cfb200.h -------------
+enum UpdateVar { UV_CONS = 0, UV_PVT = 1 };            // Euler{2,3}DCons / Euler2DPuvt, Euler3DPvt
+enum FluxSplitter { FS_ROE = 0, FS_AUSMPLUS = 1, FS_AUSMPLUSUP = 2 };
+enum PolyRec { PR_CONSTANT = 0, PR_LINEARLS = 1 };
+enum Limiter { LIM_NONE = 0, LIM_VENKTN = 1, LIM_BARTHJESP = 2 };
+enum Diffusive { DIFF_NONE = 0, DIFF_NS = 1 };
+enum ViscLaw { VISC_SIMPLER_SUTHERLAND = 0, VISC_SUTHERLAND = 1, VISC_FIXED = 2 };
+enum BCType {
+  BC_SUPER_OUTLET = 0,     // FiniteVolume/SuperOutlet.cxx:38-47        ghost = inner
+  BC_DIRICHLET = 1,        // ghost[v] = 2*value[v] - inner[v] for v in mask, copy otherwise
+                           //   SuperInlet.cxx:156-209, SubInletEulerPvtVT.ci:52-77,
+                           //   SubOutletEulerPvt.ci:36-51, NoSlipWallAdiabaticNSPvt.cxx:109-128
+  BC_MIRROR_VELOCITY = 2,  // FiniteVolume/MirrorVelocity.cxx:71-111
+  BC_MIRROR_EULER_CONS = 3 // FiniteVolumeNavierStokes/MirrorEuler2D.cxx:56-94 (+3D analogue)
+};
+
+// One boundary condition (one per boundary TRS).
+struct BC {
+  int32_t type;
+  int32_t mask[MAXEQ];        // BC_DIRICHLET: which variables are imposed
+  double value[MAXEQ];        // BC_DIRICHLET: imposed (adimensional, update-variable) values
+  int32_t zeroGrad[MAXEQ];    // ZeroGradientFlags (FVMCC_ComputeRHS.cxx:186-188)
+};
+
+// Run configuration: everything the reference reads from the .CFcase + SubSystemStatus.
+struct Config {
+  int32_t dim;            // 2 | 3
+  int32_t nEqs;           // dim + 2
+  int32_t updateVar;      // UpdateVar
+  int32_t fluxSplitter;   // FluxSplitter
+  int32_t polyRec;        // PolyRec
+  int32_t limiter;        // Limiter
+  int32_t diffusive;      // Diffusive
+  int32_t viscLaw;        // ViscLaw
+  int32_t computeJacobian;// 0 | 1 (numerical, FVMCC_ComputeRhsJacob)
+  int32_t useFullStencil; // limiter option
+  int32_t freezeLimiter;  // PolyReconstructor.ci:66
+  int32_t stopLimiting;   // FVMCC_PolyRec.cxx:52
+  int32_t isAdimensional; // NavierStokesPhysicalModel.ci:137
+  int32_t freezeDiffCoeff;// FVMCC_ComputeRhsJacob option
+  int32_t iter;           // SubSystemStatus::getNbIter()
+  int32_t limitIter;      // PolyReconstructor.ci:57
+  double gamma;           // EulerTerm.cxx:48
+  double R;               // EulerTerm::getR()  (_RRef)
+  double pOffset;         // _p0Inf/m_refPhysicalData[P]  (EulerTerm.hh:199-202)
+  double refValues[MAXEQ];// PhysicalModel refValues -> NumericalJacobian (RoeFlux.cxx:113-115)
+  double fdTol;           // NumericalJacobian.cxx:31  (10e-7)
+  double resFactor;       // FVMCC_ComputeRHS.hh:98
+  double residual;        // SubSystemStatus::getResidual()
+  double limitRes;        // PolyReconstructor.ci:60
+  double gradientFactor;  // PolyReconstructor.ci:63
+  double coeffEps;        // Venktn2D.cxx:58
+  double length;          // Venktn2D.cxx:62 / refLength
+  double magnitudeValues[MAXEQ]; // Venktn2D.cxx:96-106
+  double diffRedCoeff;    // RoeFlux.cxx:62 DiffCoeff
+  // Navier-Stokes terms (NavierStokesPhysicalModel.ci:69-170, NSTerm)
+  double coeffTau, coeffQ, cpOverPrandtl, muRef /*refDataDiff[MU]*/, tempRef, pRef, artDiffCoeff;
+  double viscRef, viscTRef, viscSuthConst, fixedVisc;
+  double cfl;             // for the pseudo-steady time term
+};
+
+struct MeshView {
+  int32_t dim, nCells, nGhosts, nNodes, nFaces, nInner;
+  const double* nodes;      // [nNodes*dim]
+  const double* centres;    // [(nCells+nGhosts)*dim]: cell centres, then ghost centres
+  const int32_t* faceL;     // [nFaces]  faces are stored in the reference's LOOP order:
+  const int32_t* faceR;     //           InnerFaces first, then each boundary TRS; R = nCells+ghost for boundary faces
+  const int32_t* faceNodePtr; // [nFaces+1]
+  const int32_t* faceNodes;
+  const double* normals;    // [nFaces*dim]   area-weighted, outward from L
+  const double* areas;      // [nFaces]
+  const double* volumes;    // [nCells]
+  const int32_t* cellFacePtr; // [nCells+1]
+  const int32_t* cellFaces; // loop-order face index, in the cell's local face order
+  const int32_t* stencilPtr;  // [nCells+1]
+  const int32_t* stencil;   // state indices (cells, or nCells+ghost)
+  const int32_t* nodeNbrPtr;  // [nNodes+1]
+  const int32_t* nodeNbr;   // state indices
+  const double* nodeW;      // nodal extrapolation weights (DistanceBasedExtrapolator.ci:105-125)
+  const double* cvol;       // [nFaces] diamond control volumes (DiamondVolume*Derivative)
+  const uint8_t* cvSign;    // [nFaces] _changeNormalSign
+  const int32_t* faceBC;    // [nFaces] -1 inner, else index into the BC array
+  const uint8_t* updatable; // [nCells] isParUpdatable
+};
+
+} // namespace cfo
