@@ -1,0 +1,260 @@
+// cfb200 — host side of the engine: owns the device-resident mesh/state/Jacobian storage, builds the
+// gather tables once (cell->faces in loop order, LSQ edge order, BSR slots), and sequences the kernels
+// of one ComputeRHS (+Jacobian) evaluation.  Mirrors the command interface of the reference
+// (setup / execute / unsetup of FVMCC_ComputeRHS, plugins/FiniteVolume/FVMCC_ComputeRHS.hh:37-77).
+//
+// `BK` is the execution backend.  The product instantiates it ONLY with the CUDA backend
+// (cfb_capi.cu); tests/hostsim instantiates it with a host loop backend to check the kernel
+// functors against the oracle on machines without a GPU.  That host instantiation is test
+// infrastructure and is never linked into libcfb200.so.
+#pragma once
+#include <vector>
+#include <string>
+#include <cstring>
+#include <algorithm>
+#include <stdexcept>
+#include "cfb_kernels.cuh"
+
+namespace cfb {
+
+struct DeviceError : std::runtime_error {
+  int code;
+  DeviceError(int c, const std::string& what) : std::runtime_error(what), code(c) {}
+};
+
+template <class BK>
+class Engine {
+public:
+  Cfg cfg;
+  Dev d;
+  BK bk;
+  std::string err;
+  int nBC = 0;
+  int64_t nnzb = 0;
+  int nNonUpd = 0;
+  bool meshSet = false, statesSet = false;
+  int lastStatus = 0;
+  std::vector<void*> owned;
+  int* nonUpdCells = nullptr;
+  std::vector<int32_t> hRowPtr, hColInd;
+
+  explicit Engine(const Cfg& c, int device) : cfg(c), bk(device) { std::memset(&d, 0, sizeof(d)); }
+  ~Engine() { for (void* p : owned) bk.free(p); }
+
+  template <class T> T* dalloc(size_t n) {
+    T* p = (T*)bk.alloc(std::max<size_t>(n, 1)*sizeof(T));
+    owned.push_back(p);
+    return p;
+  }
+  template <class T> T* upload(const std::vector<T>& v) {
+    T* p = dalloc<T>(v.size());
+    if (!v.empty()) bk.h2d(p, v.data(), v.size()*sizeof(T));
+    return p;
+  }
+  template <class T> T* upload(const T* src, size_t n) {
+    T* p = dalloc<T>(n);
+    if (n) bk.h2d(p, src, n*sizeof(T));
+    return p;
+  }
+  static std::vector<double> toSoA(const double* a, size_t n, int k) {
+    std::vector<double> r(n*k);
+    for (size_t i = 0; i < n; ++i) for (int j = 0; j < k; ++j) r[(size_t)j*n + i] = a[i*k + j];
+    return r;
+  }
+
+  int q() const { return cfg.nEqs; }
+
+  // ---- setup: static data + gather tables --------------------------------------------------------
+  void setMesh(const cfb200_mesh& m, int nbc, const cfb200_bc* bcs) {
+    if (m.dim != cfg.dim) throw std::invalid_argument("mesh dimension differs from the configuration");
+    const int D = m.dim, nc = m.nCells, ng = m.nGhosts, nf = m.nFaces, nn = m.nNodes, ni = m.nInner;
+    const int ns = nc + ng;
+    const int Q = q();
+    d.dim = D; d.nCells = nc; d.nGhosts = ng; d.nStates = ns; d.nNodes = nn; d.nFaces = nf; d.nInner = ni;
+    nBC = nbc;
+    d.nodes = upload(toSoA(m.nodes, nn, D));
+    d.centres = upload(toSoA(m.centres, ns, D));
+    d.normals = upload(toSoA(m.normals, nf, D));
+    d.faceL = upload(m.faceL, nf); d.faceR = upload(m.faceR, nf);
+    d.faceNodePtr = upload(m.faceNodePtr, (size_t)nf + 1);
+    d.faceNodes = upload(m.faceNodes, (size_t)m.faceNodePtr[nf]);
+    d.areas = upload(m.areas, nf);
+    d.volumes = upload(m.volumes, nc);
+    d.cellFacePtr = upload(m.cellFacePtr, (size_t)nc + 1);
+    const size_t ncf = m.cellFacePtr[nc];
+    d.cellFaces = upload(m.cellFaces, ncf);
+    d.stencilPtr = upload(m.stencilPtr, (size_t)nc + 1);
+    d.stencil = upload(m.stencil, (size_t)m.stencilPtr[nc]);
+    d.nodeNbrPtr = upload(m.nodeNbrPtr, (size_t)nn + 1);
+    d.nodeNbr = upload(m.nodeNbr, (size_t)m.nodeNbrPtr[nn]);
+    d.nodeW = upload(m.nodeW, (size_t)m.nodeNbrPtr[nn]);
+    d.cvol = upload(m.cvol, nf);
+    d.cvSign = upload(m.cvSign, nf);
+    d.faceBC = upload(m.faceBC, nf);
+    d.updatable = upload(m.updatable, nc);
+    for (int f = ni; f < nf; ++f)
+      if (m.faceBC[f] < 0 || m.faceBC[f] >= nbc) throw std::invalid_argument("boundary face without a boundary condition");
+    d.bcs = upload(bcs, (size_t)nbc);
+
+    // cell -> faces sorted in loop order, R side flagged by bitwise not (gather order = reference face loop order)
+    {
+      std::vector<int32_t> sorted(ncf);
+      std::vector<uint8_t> active(nc, 0);
+      std::vector<int32_t> tmp;
+      for (int c = 0; c < nc; ++c) {
+        tmp.assign(m.cellFaces + m.cellFacePtr[c], m.cellFaces + m.cellFacePtr[c+1]);
+        std::sort(tmp.begin(), tmp.end());
+        for (size_t k = 0; k < tmp.size(); ++k) {
+          const int f = tmp[k];
+          const bool isR = (m.faceL[f] != c);
+          sorted[m.cellFacePtr[c] + k] = isR ? ~f : f;
+          const bool upL = m.updatable[m.faceL[f]];
+          const bool upR = f < ni && m.updatable[m.faceR[f]];
+          if (upL || upR) active[c] = 1;
+        }
+      }
+      d.cellFaceSorted = upload(sorted);
+      d.cellActive = upload(active);
+    }
+    // LSQ gather list: replay the reference's edge loop (LeastSquareP1PolyRec2D.cxx:100-134): cell i visits
+    // stencil entries that are ghosts or have a higher ID; the edge contributes to i and (if not ghost) to `last`.
+    {
+      std::vector<int32_t> cnt(nc + 1, 0);
+      for (int i = 0; i < nc; ++i)
+        for (int k = m.stencilPtr[i]; k < m.stencilPtr[i+1]; ++k) {
+          const int last = m.stencil[k];
+          if (last >= nc || last > i) { cnt[i+1]++; if (last < nc) cnt[last+1]++; }
+        }
+      for (int i = 0; i < nc; ++i) cnt[i+1] += cnt[i];
+      std::vector<int32_t> pos(cnt.begin(), cnt.end() - 1), nbr(cnt[nc]);
+      for (int i = 0; i < nc; ++i)
+        for (int k = m.stencilPtr[i]; k < m.stencilPtr[i+1]; ++k) {
+          const int last = m.stencil[k];
+          if (last >= nc || last > i) { nbr[pos[i]++] = last; if (last < nc) nbr[pos[last]++] = i; }
+        }
+      d.lsqPtr = upload(cnt);
+      d.lsqNbr = upload(nbr);
+    }
+    // BSR pattern (FVMCCSparsity.cxx:47-106: diagonal + one block per interior-face neighbour) and face slots
+    {
+      hRowPtr.assign(1, 0);
+      hColInd.clear();
+      hColInd.reserve(ncf + nc);
+      std::vector<int32_t> cols;
+      for (int c = 0; c < nc; ++c) {
+        cols.assign(1, c);
+        for (int k = m.cellFacePtr[c]; k < m.cellFacePtr[c+1]; ++k) {
+          const int f = m.cellFaces[k];
+          if (f < ni) cols.push_back(m.faceL[f] == c ? m.faceR[f] : m.faceL[f]);
+        }
+        std::sort(cols.begin(), cols.end());
+        hColInd.insert(hColInd.end(), cols.begin(), cols.end());
+        hRowPtr.push_back((int32_t)hColInd.size());
+      }
+      nnzb = (int64_t)hColInd.size();
+      auto slot = [&](int r, int cidx) {
+        const int32_t* b = &hColInd[hRowPtr[r]]; const int32_t* e = &hColInd[hRowPtr[r+1]];
+        const int32_t* it = std::lower_bound(b, e, cidx);
+        if (it == e || *it != cidx) throw std::runtime_error("BSR slot not found");
+        return (int32_t)(it - &hColInd[0]);
+      };
+      std::vector<int32_t> sLR(ni), sRL(ni), dg(nc);
+      for (int f = 0; f < ni; ++f) { sLR[f] = slot(m.faceL[f], m.faceR[f]); sRL[f] = slot(m.faceR[f], m.faceL[f]); }
+      for (int c = 0; c < nc; ++c) dg[c] = slot(c, c);
+      d.bsrRowPtr = upload(hRowPtr); d.bsrColInd = upload(hColInd);
+      d.slotLR = upload(sLR); d.slotRL = upload(sRL); d.diagSlot = upload(dg);
+      std::vector<int32_t> nu;
+      for (int c = 0; c < nc; ++c) if (!m.updatable[c]) nu.push_back(c);
+      nNonUpd = (int)nu.size();
+      nonUpdCells = upload(nu);
+    }
+    // fields
+    d.faceCentres = dalloc<double>((size_t)nf*D);
+    d.lsqL = dalloc<double>((size_t)6*nc);
+    d.U = dalloc<double>((size_t)Q*ns);
+    d.pastU = dalloc<double>((size_t)Q*nc);
+    d.uX = dalloc<double>((size_t)Q*nc); d.uY = dalloc<double>((size_t)Q*nc); d.uZ = dalloc<double>((size_t)Q*nc);
+    d.lim = dalloc<double>((size_t)Q*nc);
+    d.nstates = dalloc<double>((size_t)Q*nn);
+    d.faceFlux = dalloc<double>((size_t)Q*nf);
+    d.ucL = dalloc<double>(nf); d.ucR = dalloc<double>(nf); d.ucD = dalloc<double>(nf); d.faceMu = dalloc<double>(nf);
+    d.rhs = dalloc<double>((size_t)Q*nc);
+    d.updateCoeff = dalloc<double>(nc);
+    d.aos = dalloc<double>((size_t)Q*std::max(ns, nn));
+    d.partial = dalloc<double>((size_t)nc + 1024);
+    d.status = dalloc<int>(1);
+    d.bndBlocks = dalloc<double>((size_t)ng*Q*Q);
+    d.bsrVal = nullptr;       // allocated on the first Jacobian evaluation
+    bk.memset(d.uX, 0, sizeof(double)*Q*nc); bk.memset(d.uY, 0, sizeof(double)*Q*nc); bk.memset(d.uZ, 0, sizeof(double)*Q*nc);
+    bk.memset(d.updateCoeff, 0, sizeof(double)*nc);
+    bk.memset(d.U, 0, sizeof(double)*Q*ns);
+    bk.memset(d.nstates, 0, sizeof(double)*Q*nn);
+    bk.memset(d.rhs, 0, sizeof(double)*Q*nc);
+    bk.memset(d.faceMu, 0, sizeof(double)*nf);
+    {
+      std::vector<double> ones((size_t)Q*nc, 1.0);   // limiter socket starts at 1 (LeastSquareP1Setup.cxx:127-129)
+      bk.h2d(d.lim, ones.data(), ones.size()*sizeof(double));
+    }
+    bk.launch("faceCentres", FaceCentres{d}, nf, 256);
+    if (D == 2) bk.launch("lsqSetup", LsqSetup<2>{d}, nc, 256); else bk.launch("lsqSetup", LsqSetup<3>{d}, nc, 256);
+    bk.sync();
+    meshSet = true;
+  }
+
+  void ensureJacobian() {
+    if (!d.bsrVal) { d.bsrVal = dalloc<double>((size_t)nnzb*q()*q()); bk.memset(d.bsrVal, 0, sizeof(double)*nnzb*q()*q()); }
+  }
+
+  // ---- AoS <-> SoA transfers ---------------------------------------------------------------------
+  void putAoS(double* dstSoA, int ld, const double* hostAoS, int n, int k) {
+    bk.h2d(d.aos, hostAoS, (size_t)n*k*sizeof(double));
+    bk.launch("aosToSoa", AosToSoa{d.aos, dstSoA, n, k, ld}, n*k, 256);
+    bk.sync();
+  }
+  void getAoS(const double* srcSoA, int ld, double* hostAoS, int n, int k) {
+    bk.launch("soaToAos", SoaToAos{srcSoA, d.aos, n, k, ld}, n*k, 256);
+    bk.d2h(hostAoS, d.aos, (size_t)n*k*sizeof(double));
+  }
+
+  // ---- execute ------------------------------------------------------------------------------------
+  template <int D> void applyBC_() { if (d.nGhosts) bk.launch("applyBC", GhostFill<D>{d, cfg}, d.nGhosts, 128); }
+
+  template <int D> void computeRhs_(bool applyBC) {
+    const bool doJac = cfg.computeJacobian != 0;
+    if (doJac) ensureJacobian();
+    bk.resetTimings();
+    bk.memset(d.status, 0, sizeof(int));
+    if (applyBC) applyBC_<D>();
+    // initializeComputationRHS (FVMCC_ComputeRHS.cxx:690-705)
+    if (cfg.polyRec == CFB200_PR_LINEARLS) bk.launch("gradients", Gradients<D>{d}, d.nCells, 128);
+    bk.launch("nodalExtrapolate", NodalExtrapolate<D>{d}, d.nNodes, 256);
+    if (cfg.polyRec == CFB200_PR_LINEARLS && cfg.limiter != CFB200_LIM_NONE)
+      bk.launch("limiter", LimiterK<D>{d, cfg}, d.nCells, 128);
+    bk.launch("faceFlux", FaceFlux<D>{d, cfg}, d.nFaces, 128);
+    bk.launch("cellGather", CellGather<D>{d, cfg}, d.nCells, 256);
+    if (doJac) {
+      if (d.nInner) bk.launch("jacInner", JacInner<D>{d, cfg}, 2*d.nInner, 128);
+      if (d.nGhosts) bk.launch("jacBoundary", JacBoundary<D>{d, cfg}, d.nGhosts, 128);
+      bk.launch("diagGather", DiagGather<D>{d}, d.nCells*32, 256);
+      if (nNonUpd) bk.launch("zeroRows", ZeroRows<D>{d, nonUpdCells}, nNonUpd*32, 256);
+    }
+    int st = 0;
+    bk.d2h(&st, d.status, sizeof(int));   // synchronises
+    lastStatus = st;
+  }
+  void applyBC() { if (cfg.dim == 2) applyBC_<2>(); else applyBC_<3>(); bk.sync(); }
+  void computeRhs(bool applyBCFirst) { if (cfg.dim == 2) computeRhs_<2>(applyBCFirst); else computeRhs_<3>(applyBCFirst); }
+  void timeRhs() {
+    const int doJac = cfg.computeJacobian && d.bsrVal;
+    if (cfg.dim == 2) bk.launch("timeRhs", TimeRhs<2>{d, cfg, doJac}, d.nCells, 128);
+    else bk.launch("timeRhs", TimeRhs<3>{d, cfg, doJac}, d.nCells, 128);
+    bk.sync();
+  }
+  double updateSolFwdEuler(double cfl, int monitorVar) {
+    if (cfg.dim == 2) bk.launch("updateSol", UpdateSolFwdEuler<2>{d, cfl, monitorVar}, d.nCells, 256);
+    else bk.launch("updateSol", UpdateSolFwdEuler<3>{d, cfl, monitorVar}, d.nCells, 256);
+    return bk.sumOrdered(d.partial, d.nCells);
+  }
+};
+
+} // namespace cfb

@@ -1,0 +1,226 @@
+/* cfb200 — C ABI of the B200-native FVMCC ComputeRHS / ComputeRhsJacob engine.
+ *
+ * This header is the drop-in boundary: a thin COOLFluiD plugin
+ * (plugin/FiniteVolumeB200, a MethodCommand<CellCenterFVMData> registered with
+ * MethodCommandProvider exactly like plugins/FiniteVolumeCUDA/FVMCC_ComputeRHSCell.hh:31)
+ * copies socket data in, calls these entry points, and copies rhs / updateCoeff /
+ * the block Jacobian out.  Plain pointers and sizes only; no exceptions cross it
+ * (0 = success, non-zero = error code, text through cfb200_last_error).
+ *
+ * Every entry point cites the reference interface it replaces (paths relative to
+ * the COOLFluiD tree).  All reals are FP64 (CFreal = double, src/Common/COOLFluiD.hh:92-106),
+ * all indices 32-bit (CFuint without CF_HAVE_LONG).
+ *
+ * The library needs an NVIDIA B200 (sm_100a).  There is NO CPU fallback: every
+ * compute entry point returns CFB200_ERR_NO_DEVICE when no CUDA device is usable.
+ */
+#ifndef CFB200_H
+#define CFB200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CFB200_MAXEQ 9
+#define CFB200_ABI_VERSION 1
+
+/* ---- enums: values are shared with the .CFcase option strings through the plugin ---- */
+enum cfb200_update_var { CFB200_UV_CONS = 0 /* Euler2DCons, Euler3DCons */, CFB200_UV_PVT = 1 /* Euler2DPuvt, Euler3DPvt */ };
+enum cfb200_flux_splitter { CFB200_FS_ROE = 0 /* "Roe" plugins/FiniteVolume/RoeFlux.cxx */,
+                            CFB200_FS_AUSMPLUS = 1, CFB200_FS_AUSMPLUSUP = 2 /* reserved */ };
+enum cfb200_poly_rec { CFB200_PR_CONSTANT = 0 /* "Constant" ConstantPolyRec.cxx */,
+                       CFB200_PR_LINEARLS = 1 /* "LinearLS2D"/"LinearLS3D" LeastSquareP1PolyRec{2,3}D.cxx */ };
+enum cfb200_limiter { CFB200_LIM_NONE = 0, CFB200_LIM_VENKTN = 1 /* "Venktn2D"/"Venktn3D" */,
+                      CFB200_LIM_BARTHJESP = 2 /* "BarthJesp" */ };
+enum cfb200_diffusive { CFB200_DIFF_NONE = 0, CFB200_DIFF_NS = 1 /* "NavierStokes" NSFlux.ci + DiamondVolume{2,3}D */ };
+enum cfb200_visc_law { CFB200_VISC_SIMPLER_SUTHERLAND = 0, CFB200_VISC_SUTHERLAND = 1, CFB200_VISC_FIXED = 2 };
+enum cfb200_bc_type {
+  CFB200_BC_SUPER_OUTLET = 0,      /* FiniteVolume/SuperOutlet.cxx:38-47 */
+  CFB200_BC_DIRICHLET = 1,         /* ghost[v] = 2*value[v]-inner[v] where mask[v]: SuperInlet.cxx:156-209 (constant Def),
+                                      SubInletEulerPvtVT.ci:52-77, SubOutletEulerPvt.ci:36-51, NoSlipWallAdiabaticNSPvt.cxx:109-128 */
+  CFB200_BC_MIRROR_VELOCITY = 2,   /* FiniteVolume/MirrorVelocity.cxx:71-111 */
+  CFB200_BC_MIRROR_EULER_CONS = 3  /* FiniteVolumeNavierStokes/MirrorEuler2D.cxx:56-94, MirrorEuler3D */
+};
+
+enum cfb200_error {
+  CFB200_OK = 0,
+  CFB200_ERR_BAD_VALUE = 1,   /* a^2 < 0 in the Roe linearisation: the reference throws BadValueException (Euler2DLinearRoe.cxx:79-85) */
+  CFB200_ERR_INVALID_ARG = 2,
+  CFB200_ERR_NO_DEVICE = 3,   /* no usable CUDA device: the product has no CPU path */
+  CFB200_ERR_CUDA = 4,
+  CFB200_ERR_STATE = 5,       /* call order (mesh/states not set) */
+  CFB200_ERR_UNSUPPORTED = 6,
+  CFB200_ERR_NCCL = 7
+};
+
+/* One boundary condition per boundary TRS (FVMCC_BaseBC.ci:144-187 executeOnTrs -> setGhostState). */
+typedef struct cfb200_bc {
+  int32_t type;
+  int32_t mask[CFB200_MAXEQ];
+  double value[CFB200_MAXEQ];
+  int32_t zeroGrad[CFB200_MAXEQ];   /* ZeroGradientFlags, FVMCC_ComputeRHS.cxx:186-188 */
+} cfb200_bc;
+
+/* Everything ComputeRHS reads from the .CFcase and from SubSystemStatus (SURVEY.md §8b "Scalars crossing per call").
+ * The per-call scalars (iter, residual, resFactor, cfl, computeJacobian) may be changed between calls with
+ * cfb200_set_step. */
+typedef struct cfb200_config {
+  int32_t dim;              /* 2 | 3 */
+  int32_t nEqs;             /* dim + 2 */
+  int32_t updateVar, fluxSplitter, polyRec, limiter, diffusive, viscLaw;
+  int32_t computeJacobian;  /* doComputeJacobian() */
+  int32_t useFullStencil;   /* Venktn2D.cxx:60 */
+  int32_t freezeLimiter;    /* PolyReconstructor.ci:66 */
+  int32_t stopLimiting;     /* FVMCC_PolyRec.cxx:52 */
+  int32_t isAdimensional;   /* NavierStokesPhysicalModel.ci:137 */
+  int32_t freezeDiffCoeff;  /* FVMCC_ComputeRhsJacob option FreezeDiffCoeff */
+  int32_t iter;             /* SubSystemStatus::getNbIter() */
+  int32_t limitIter;        /* PolyReconstructor.ci:57 */
+  double gamma, R, pOffset; /* EulerTerm.cxx:46-50, EulerTerm.hh:199-212 */
+  double refValues[CFB200_MAXEQ]; /* PhysicalModel refValues -> NumericalJacobian (RoeFlux.cxx:113-115) */
+  double fdTol;             /* NumericalJacobian.cxx:31 */
+  double resFactor;         /* getMethodData().getResFactor() */
+  double residual;          /* SubSystemStatus::getResidual() */
+  double limitRes;          /* PolyReconstructor.ci:60 */
+  double gradientFactor;    /* PolyReconstructor.ci:63 */
+  double coeffEps, length;  /* Venktn2D.cxx:58,62 */
+  double magnitudeValues[CFB200_MAXEQ]; /* Venktn2D.cxx:96-106 */
+  double diffRedCoeff;      /* RoeFlux.cxx:62 */
+  double coeffTau, coeffQ, cpOverPrandtl, muRef, tempRef, pRef, artDiffCoeff; /* NSTerm / NavierStokesPhysicalModel.ci:69-170 */
+  double viscRef, viscTRef, viscSuthConst, fixedVisc;                          /* *SutherlandDynViscosity */
+  double cfl;
+} cfb200_config;
+
+/* Flat mesh data = the contents of the reference's sockets and connectivity tables (SURVEY.md §8b "Data ownership").
+ * Faces are in the reference's LOOP order: InnerFaces TRS, then each boundary TRS; faceR of a boundary face is
+ * nCells + ghost index.  State-indexed arrays hold the cells first, then the ghost states. */
+typedef struct cfb200_mesh {
+  int32_t dim, nCells, nGhosts, nNodes, nFaces, nInner;
+  const double* nodes;         /* [nNodes*dim]                     socket "nodes" */
+  const double* centres;       /* [(nCells+nGhosts)*dim]           State::getCoordinates() of states, gstates */
+  const int32_t* faceL;        /* [nFaces]                          face->getState(0)->getLocalID() */
+  const int32_t* faceR;        /* [nFaces] */
+  const int32_t* faceNodePtr;  /* [nFaces+1] */
+  const int32_t* faceNodes;
+  const double* normals;       /* [nFaces*dim]  socket "normals" (area weighted, outward from L) */
+  const double* areas;         /* [nFaces]      socket "faceAreas" */
+  const double* volumes;       /* [nCells]      socket "volumes" */
+  const int32_t* cellFacePtr;  /* [nCells+1]    connectivity "cellFaces" */
+  const int32_t* cellFaces;
+  const int32_t* stencilPtr;   /* [nCells+1]    socket "stencil" */
+  const int32_t* stencil;
+  const int32_t* nodeNbrPtr;   /* [nNodes+1]    NodalStatesExtrapolator neighbours */
+  const int32_t* nodeNbr;
+  const double* nodeW;         /*               DistanceBasedExtrapolator weights */
+  const double* cvol;          /* [nFaces]      DiamondVolume3DDerivative control volumes (3D) */
+  const uint8_t* cvSign;       /* [nFaces]      _changeNormalSign */
+  const int32_t* faceBC;       /* [nFaces]      -1 inner, else boundary-condition index */
+  const uint8_t* updatable;    /* [nCells]      State::isParUpdatable() */
+} cfb200_mesh;
+
+/* Device view of the block Jacobian (LSSMatrix replacement; BlockAccumulator.hh:289-296 sub-block layout [ib][jb]). */
+typedef struct cfb200_bsr {
+  int32_t nRows, nnzb, blockSize;
+  const int32_t* rowPtr;   /* device, [nRows+1] */
+  const int32_t* colInd;   /* device, [nnzb], ascending inside each row */
+  const double* val;       /* device, [nnzb*blockSize*blockSize], row-major blocks */
+} cfb200_bsr;
+
+typedef struct cfb200_handle cfb200_handle;
+
+int cfb200_abi_version(void);
+/* number of usable CUDA devices (0 without a GPU; never throws) */
+int cfb200_device_count(void);
+
+/* replaces: FVMCC_ComputeRHS constructor/configure/setup (plugins/FiniteVolume/FVMCC_ComputeRHS.cxx:46-128,329-440) */
+int cfb200_create(const cfb200_config* cfg, int device, cfb200_handle** out);
+/* replaces: FVMCC_ComputeRHS::unsetup */
+void cfb200_destroy(cfb200_handle* h);
+const char* cfb200_last_error(const cfb200_handle* h);
+
+/* replaces: the command's needsSockets()/setup() reads of nodes, normals, faceAreas, volumes, stencil, cellFaces
+ * (FVMCC_ComputeRHS.cxx:33-44,329-440; LeastSquareP1Setup.cxx:84-142).  Uploaded once; builds the device SoA,
+ * the gather tables (cell->faces in loop order, LSQ edge order, BSR slots) and the LSQ normal matrices. */
+int cfb200_set_mesh(cfb200_handle* h, const cfb200_mesh* mesh, int nBC, const cfb200_bc* bcs);
+/* per-call scalars: resFactor, iter, residual, cfl, computeJacobian, freezeLimiter ... (whole struct is re-read) */
+int cfb200_set_step(cfb200_handle* h, const cfb200_config* cfg);
+
+/* states socket: AoS [nCells][nEqs] as in socket_states.getGlobalArray()->ptr() (FVMCC_ComputeRHSCell.cu:743) */
+int cfb200_set_states(cfb200_handle* h, const double* U, int64_t nCells);
+int cfb200_get_states(cfb200_handle* h, double* U, int64_t nCells);
+/* pastStates socket (NewtonIterator::prepare) for the pseudo-time term */
+int cfb200_set_past_states(cfb200_handle* h, const double* U, int64_t nCells);
+int cfb200_backup_past_states(cfb200_handle* h);   /* device copy states -> pastStates */
+/* limiter / updateCoeff sockets are stateful across calls (historical limiter; updateCoeff is zeroed by the updater) */
+int cfb200_set_limiter(cfb200_handle* h, const double* limiter /* AoS [nCells][nEqs] */);
+int cfb200_set_update_coeff(cfb200_handle* h, const double* updateCoeff /* [nCells], NULL = zero */);
+
+/* replaces: CellCenterFVM::applyBC (CellCenterFVM.cxx:464) -> FVMCC_BaseBC::executeOnTrs (FVMCC_BaseBC.ci:144-187) */
+int cfb200_apply_bc(cfb200_handle* h);
+
+/* replaces: FVMCC_ComputeRHS::execute (FVMCC_ComputeRHS.cxx:139-325) and, when cfg.computeJacobian,
+ * FVMCC_ComputeRhsJacob (FVMCC_ComputeRhsJacob.cxx:126-443).  Runs applyBC first when applyBC != 0.
+ * Results stay on the device; rhs/updateCoeff are additionally copied to the host when the pointers are non-NULL
+ * (callers UpdateSol.cxx:83 / FVMCC_PseudoSteadyTimeRhs.cxx:106 read them right after). */
+int cfb200_compute_rhs(cfb200_handle* h, int applyBC, double* rhs /* [nCells*nEqs] or NULL */,
+                       double* updateCoeff /* [nCells] or NULL */);
+
+/* replaces: FVMCC_PseudoSteadyTimeRhs::execute (FVMCC_PseudoSteadyTimeRhs.cxx:106-262), steady branch */
+int cfb200_time_rhs(cfb200_handle* h, double* rhs /* or NULL */);
+
+/* replaces: ForwardEuler UpdateSol::execute + ComputeL2Norm (UpdateSol.cxx:83-193, ComputeL2Norm.cxx:81-143):
+ * U += CFL/updateCoeff * rhs on the device, updateCoeff = 0, returns log10 L2 norm of dU[monitorVar] */
+int cfb200_update_sol_fwd_euler(cfb200_handle* h, double cfl, int monitorVar, double* log10Residual);
+
+/* device-resident results */
+int cfb200_bsr_view(cfb200_handle* h, cfb200_bsr* out);
+int cfb200_bsr_pattern(cfb200_handle* h, int32_t* rowPtr /* [nCells+1] */, int32_t* colInd /* [nnzb] */);
+int64_t cfb200_bsr_nnzb(cfb200_handle* h);
+int cfb200_get_bsr_values(cfb200_handle* h, double* val /* [nnzb*q*q] */);
+/* scalar CSR view for Paralution (ParalutionMatrix.hh:144 SetDataPtrCSR): rows of a cell one after the other */
+int cfb200_export_csr(cfb200_handle* h, int32_t* rowOff, int32_t* col, double* val);
+/* named fields, reference (AoS, reference IDs) layout: "rhs","updateCoeff","uX","uY","uZ","limiter","nstates","gstates" */
+int cfb200_get_field(cfb200_handle* h, const char* name, double* out);
+const double* cfb200_device_ptr(cfb200_handle* h, const char* name);
+/* status of the last evaluation: 0 or CFB200_ERR_BAD_VALUE */
+int cfb200_status(cfb200_handle* h);
+
+/* per-kernel timing of the last compute call, in ms (CUDA events on the engine's stream; off by default):
+ * fills up to cap entries, returns the count */
+int cfb200_enable_timing(cfb200_handle* h, int on);
+int cfb200_last_timings(cfb200_handle* h, const char** names, float* ms, int cap);
+/* stream the engine launches on (cudaStream_t as void*) */
+void* cfb200_stream(cfb200_handle* h);
+
+/* ---- multi-GPU (one partition per GPU).  replaces: DataHandle<State*,GLOBAL>::synchronize()
+ * (src/Common/MPI/MPICommPattern.hh:1735-1782) for the states array ---------------------------------------- */
+int cfb200_nccl_unique_id(void* id128 /* 128 bytes out */);
+int cfb200_comm_init(cfb200_handle* h, int rank, int nRanks, const void* id128);
+/* sendPtr/recvPtr: CSR over ranks; sendCells: local cell ids to pack for each peer; recvCells: local (overlap) cell ids */
+int cfb200_set_halo(cfb200_handle* h, const int32_t* sendPtr, const int32_t* sendCells,
+                    const int32_t* recvPtr, const int32_t* recvCells);
+int cfb200_halo_exchange(cfb200_handle* h);
+int cfb200_allreduce_sum(cfb200_handle* h, double* v, int n);
+
+/* ---- host-side mesh-data construction (replaces FVMCC_MeshDataBuilder.cxx:91-499, ComputeFaceNormals*P1,
+ * FVMCCGeoDataComputer.ci:61-89, ComputeDummyStates.cxx, ComputeFaceVertexNeighborsPlusGhost.cxx,
+ * NodalStatesExtrapolator.ci:134-237, DistanceBasedExtrapolator.ci:60-125, DiamondVolume3DDerivative.cxx:413-563,
+ * FVMCCSparsity.cxx:47-106) for the stand-alone harness; under COOLFluiD the plugin reads the sockets instead. */
+typedef struct cfb200_meshdata cfb200_meshdata;
+cfb200_meshdata* cfb200_mesh_build(int dim, int nNodes, const double* nodes, int nCells, const int32_t* cellNodePtr,
+                                   const int32_t* cellNodes, const int32_t* cellShape /* 0 tri,1 quad,2 tet,3 hex */,
+                                   int nTRS, const int32_t* trsFacePtr, const int32_t* trsFaceCell,
+                                   const int32_t* trsFaceNodePtr, const int32_t* trsFaceNodes);
+/* sizes: nFaces, nInner, nGhosts, len(faceNodes), len(cellFaces), len(stencil), len(nodeNbr), nnzb */
+void cfb200_mesh_sizes(const cfb200_meshdata* m, int64_t* out8);
+int cfb200_mesh_get(const cfb200_meshdata* m, const char* name, void* dst);
+const void* cfb200_mesh_ptr(const cfb200_meshdata* m, const char* name);
+void cfb200_mesh_view(const cfb200_meshdata* m, cfb200_mesh* out);
+void cfb200_mesh_set_updatable(cfb200_meshdata* m, const uint8_t* updatable);
+void cfb200_mesh_free(cfb200_meshdata* m);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -33,7 +33,7 @@ class Outputs(C.Structure):
 
 def build(omp=False, ref=True):
     """Compile the oracle (and, when /root/reference exists, oracle/_ref) with the committed Makefile."""
-    targets = ["liboracle.so", "liboracle_omp.so"] + (["ref"] if ref else [])
+    targets = ["liboracle.so", "liboracle_fast.so"] + (["ref"] if ref else [])
     subprocess.check_call(["make", "-s", "-C", HERE] + targets)
 
 
@@ -41,7 +41,7 @@ _libs = {}
 
 
 def lib(omp=False):
-    name = "liboracle_omp.so" if omp else "liboracle.so"
+    name = "liboracle_fast.so" if omp else "liboracle.so"
     if name not in _libs:
         path = os.path.join(HERE, name)
         if not os.path.exists(path):

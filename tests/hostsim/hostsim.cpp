@@ -1,0 +1,36 @@
+// TEST INFRASTRUCTURE ONLY — never linked into libcfb200.so, never imported by coolfluid_b200.
+// Instantiates the product's kernel functors (coolfluid_b200/csrc/cfb_kernels.cuh) and engine sequencing
+// (cfb_engine.hpp) with a host-loop backend: "thread idx" becomes a for loop.  It exists so that the CPU
+// test tier (-m "not gpu", no GPU in the build container) can check the kernel LOGIC against the oracle
+// before any GPU time is spent.  The symbols are prefixed hostsim_ so they can never be mistaken for, or
+// shadow, the cfb200_ C ABI.
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <string>
+#include <vector>
+#include "../../coolfluid_b200/csrc/cfb_engine.hpp"
+
+namespace cfb {
+struct HostLoopBackend {
+  explicit HostLoopBackend(int) {}
+  void activate() {}
+  void* alloc(size_t bytes) { return std::calloc(1, bytes); }
+  void free(void* p) { std::free(p); }
+  void h2d(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
+  void d2h(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
+  void d2d(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
+  void memset(void* p, int v, size_t n) { std::memset(p, v, n); }
+  void sync() {}
+  void* streamPtr() { return nullptr; }
+  void enableTiming(bool) {}
+  void resetTimings() {}
+  int timings(const char**, float*, int) { return 0; }
+  template <class F> void launch(const char*, const F& f, int n, int) { for (int i = 0; i < n; ++i) f(i); }
+  double sumOrdered(double* x, int n) { double s = 0.; for (int i = 0; i < n; ++i) s += x[i]; return s; }
+};
+}
+
+typedef cfb::HostLoopBackend BackendT;
+#define CFB_FN(x) hostsim_##x
+#include "../../coolfluid_b200/csrc/cfb_capi.inc"
