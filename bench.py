@@ -1,0 +1,316 @@
+#!/usr/bin/env python
+"""bench.py — FP64 RHS+Jacobian cell-updates/s of the FVMCC ComputeRHS path on N B200s of one node.
+
+One "step" = one full ComputeRhsJacob evaluation of BASELINE.json configs[2] (3D Navier-Stokes, hexahedra, Roe +
+viscous flux, LSQ + Venkatakrishnan, finite-difference block Jacobian) on a synthetic jittered hex box: applyBC,
+LSQ gradients, nodal extrapolation, limiter, face fluxes, residual gather, interior + boundary FD Jacobian blocks,
+diagonal gather, pseudo-steady time term.  `value` = updatable cells / step time with everything
+resident in HBM; `e2e` = the same through the C ABI with HOST buffers (states H2D from pinned memory, rhs and
+updateCoeff D2H inside the timed region; the block Jacobian stays on the device for the linear solver, which is how
+the plugin hands it to PETSc-cusparse / Paralution).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--cells-per-gpu M] [--impl reference]
+
+N>1 is launched by torchrun (one rank per GPU); every rank owns one partition of the same size (weak scaling).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "fp64_rhs_jacobian_cell_updates_per_s"
+UNIT = "cells/s"
+# algorithmic bytes per cell-update, 3D NS hex, 2nd order, viscous: A_rhs 744 + A_jac 1400
+A_RHS, A_JAC = 744, 1400
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def flagship(n):
+    """configs[2]: jittered hex box n^3, Pvt variables, one inlet / outlet / no-slip wall / mirrors."""
+    import cases
+    from coolfluid_b200 import meshgen
+    em = meshgen.hex_box(n, n, n)
+    return em, cases.ns3d_cfg(), cases.bcs_ns3d()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu):
+        self.gpu = gpu
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=3)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); smax.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_baseline(sample_n, evals, threads):
+    """The oracle (CPU restatement of the reference path, `kind: port`) on `threads` host threads, one independent
+    partition of sample_n^3 hex cells per thread (the MPI path runs one rank per core on its own partition)."""
+    import cases
+    from oracle import binding as ob
+    em, cfg, bcs = flagship(sample_n)
+    fm = ob.build_mesh(em)
+    q = 5
+    U0 = cases.init_state(fm, q, True)
+    ob.lib(True)
+    outs = [ob.alloc_outputs(cfg, fm, True) for _ in range(threads)]
+    Us = [U0.copy() for _ in range(threads)]
+    past = np.concatenate([U0[:fm.nCells*q]*(1 + 1e-3), np.zeros(fm.nGhosts*q)])
+
+    def work(i):
+        for _ in range(evals):
+            outs[i].updateCoeff[:] = 0.0
+            ob.compute(cfg, fm, bcs, Us[i], jacobian=True, omp=True, out=outs[i])
+            ob.time_rhs(cfg, fm, bcs, Us[i], past, outs[i], omp=True)
+    th = [threading.Thread(target=work, args=(i,)) for i in range(threads)]
+    t0 = time.perf_counter()
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    dt = time.perf_counter() - t0
+    cells = fm.nCells*threads*evals
+    return cells/dt, dt, fm.nCells
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    n = args.cpu_sample
+    vals = []
+    for _ in range(args.warmup):
+        cpu_baseline(n, 1, threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        v, dt, nc = cpu_baseline(n, 1, threads)
+        vals.append(v)
+    total = time.perf_counter() - t0
+    v = statistics.median(vals)
+    sample = "%d independent partitions of %d^3 hex cells (one per host thread), 1 evaluation per step" % (threads, n)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3*total/max(args.steps, 1), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "3D Navier-Stokes hex box, Roe + viscous (DiamondVolume3D), LSQ + Venktn3D, FD Jacobian, "
+                               "pseudo-steady time term; CPU sample %s" % sample},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "the reference itself (Boost/MPI/PETSc) cannot be built on this image; this is the oracle port "
+                "(-O3, no FP contraction), one instance per host thread"}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="cfb200")
+    ap.add_argument("--n", type=int, default=220, help="hex box edge per GPU (220^3 = 10.6 M cells, configs[2])")
+    ap.add_argument("--cpu-sample", type=int, default=36, help="edge of the per-thread hex box of the CPU baseline")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch
+    import cases
+    from coolfluid_b200 import lib as cl
+    L = cl.load()
+    if L.device_count() < 1:
+        raise SystemExit("bench.py needs a CUDA device: cfb200 has no CPU path")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_
+        dist = dist_
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    q = 5
+    t0 = time.perf_counter()
+    em, cfg, bcs = flagship(args.n)
+    fm = cl.build_mesh(em, L)
+    t_mesh = time.perf_counter() - t0
+    U0 = cases.init_state(fm, q, True)[:fm.nCells*q]
+    eng = cl.Engine(cfg, local_rank, lib=L)
+    t0 = time.perf_counter()
+    eng.set_mesh(fm, bcs)
+    t_setup = time.perf_counter() - t0
+    nc = fm.nCells
+    # pinned host buffers of the reference-facing call (states in, rhs / updateCoeff out)
+    hU = torch.empty(nc*q, dtype=torch.float64, pin_memory=True)
+    hU.numpy()[:] = U0
+    hR = torch.empty(nc*q, dtype=torch.float64, pin_memory=True)
+    hC = torch.empty(nc, dtype=torch.float64, pin_memory=True)
+    eng.set_states(hU.numpy())
+    eng.set_past_states(hU.numpy()*(1 + 1e-3))
+    stream = torch.cuda.ExternalStream(eng.stream(), device=torch.device("cuda", local_rank))
+
+    def step_resident():
+        eng.set_update_coeff(None)           # the updater zeroes updateCoeff between evaluations (UpdateSol.cxx:192)
+        eng.compute_rhs(apply_bc=True, download=False)
+        eng.time_rhs(download=False)
+
+    def step_e2e():
+        eng.set_states(hU.numpy())
+        eng.set_update_coeff(None)
+        eng.compute_rhs(apply_bc=True, download=True, out_rhs=hR.numpy(), out_uc=hC.numpy())
+        eng.time_rhs(download=False)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for _ in range(steps):
+            fn()
+        b.record(stream)
+        barrier()
+        ms = a.elapsed_time(b)
+        if dist is not None:
+            t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    for _ in range(args.warmup):
+        step_resident()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    eng.enable_timing(True)
+    kern = {}
+    launches = [0]
+
+    def step_resident_timed():
+        step_resident()
+        tl = eng.last_timings()
+        launches[0] += len(tl) + 1          # + the time-term kernel is in the list; +1 = updateCoeff memset excluded
+        for name, ms in tl:
+            kern.setdefault(name, []).append(ms)
+    ms_total = timed(step_resident_timed, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    eng.enable_timing(False)
+    ms_step = ms_total/args.steps
+    total_cells = nc*world
+    value = total_cells/(ms_step*1e-3)
+
+    for _ in range(max(1, args.warmup//2)):
+        step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)/args.steps
+    e2e_value = total_cells/(ms_e2e*1e-3)
+
+    status = eng.L.status(eng.h)
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        kavg = {k: sum(v)/len(v) for k, v in kern.items()}
+        top = max(kavg, key=kavg.get)
+        # algorithmic bytes of the dominant kernel per launch (DESIGN.md "kernels"): the interior-face FD Jacobian
+        # writes two q x q blocks per interior face and reads both cell states, gradients, limiters, the face flux,
+        # normal, area and the 4 nodal states: see DESIGN.md for the per-face count
+        per_launch = {"jacInner": fm.nInner*(2*25*8 + 2*5*8 + 2*(3*5*8 + 5*8) + 5*8 + 3*8 + 8 + 8 + 8),
+                      "faceFlux": fm.nFaces*(2*5*8 + 5*8 + 4*8 + 3*8 + 8 + 8)}
+        algo = per_launch.get(top, nc*(A_RHS + A_JAC))
+        achieved = algo/(kavg[top]*1e-3)/1e9
+        out = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": "configs[2]: 3D Navier-Stokes, %d^3 = %d jittered hex cells per GPU, Pvt variables, Roe + "
+                                   "viscous (DiamondVolume3D) flux, LinearLS3D + Venktn3D, finite-difference block "
+                                   "Jacobian (NumJacob) into device BSR, pseudo-steady time term" % (args.n, nc),
+                       "cells_per_gpu": nc, "faces_per_gpu": int(fm.nFaces), "bsr_blocks_per_gpu": int(eng.nnzb),
+                       "l2": "inputs (%.1f GB BSR + %.2f GB states/gradients) far larger than the 126 MB L2; no flush needed"
+                             % (eng.nnzb*200/1e9, nc*5*8*6/1e9),
+                       "partitioning": "one partition per GPU, no data-path collective inside ComputeRHS",
+                       "mesh_build_s": round(t_mesh, 2), "device_setup_s": round(t_setup, 2)},
+            "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e,
+                    "h2d_bytes_per_step": int(nc*q*8*world), "d2h_bytes_per_step": int((nc*q*8 + nc*8)*world)},
+            "gpu_launches": int(launches[0]),
+            "kernels_ms": {k: round(v, 4) for k, v in sorted(kavg.items(), key=lambda kv: -kv[1])},
+            "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved/peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": int(algo), "avg_launch_ms": kavg[top]},
+            "step_roofline": {"bytes_per_cell": A_RHS + A_JAC, "achieved_gbs": (A_RHS + A_JAC)*value/world/1e9,
+                              "frac_of_hbm_peak": (A_RHS + A_JAC)*value/world/1e9/peak},
+            "clocks": clocks, "status": int(status),
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            v, dt, ncs = cpu_baseline(args.cpu_sample, 1, threads)
+            out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                                   "sample": "%d independent partitions of %d^3 hex cells (one oracle instance per host "
+                                             "thread), 1 evaluation, %.1f s" % (threads, args.cpu_sample, dt)}
+        print(json.dumps(out))
+    eng.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

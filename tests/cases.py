@@ -1,0 +1,174 @@
+"""Shared parity cases: (mesh, configuration, boundary conditions, seeded state) used by the CPU checks of the
+kernel logic (tests/hostsim) and by the GPU parity tests through the C ABI."""
+import numpy as np
+from coolfluid_b200 import meshgen, config as B
+
+
+def relerr(a, b):
+    s = np.abs(b).max()
+    return float(np.abs(a - b).max()/(s if s > 0 else 1.0))
+
+
+def init_state(fm, q, pvt, seed=67890):
+    """Smooth field + seeded noise, physically admissible (SURVEY.md §8d synthetic inputs)."""
+    d = fm.dim
+    x = fm.centres.reshape(-1, d)[:fm.nCells]
+    rng = np.random.RandomState(seed)
+    n = fm.nCells
+    U = np.zeros((n + fm.nGhosts, q))
+    s = 1.0 + 0.05*np.sin(2*np.pi*x[:, 0])*np.cos(2*np.pi*x[:, 1]) + 0.01*rng.standard_normal(n)
+    if pvt:
+        U[:n, 0] = s
+        U[:n, 1] = 0.4 + 0.05*np.cos(2*np.pi*x[:, 1])
+        U[:n, 2] = 0.03*np.sin(2*np.pi*x[:, 0])
+        if d == 3:
+            U[:n, 3] = 0.02*np.sin(2*np.pi*x[:, 2])
+        U[:n, q-1] = 1.0 + 0.05*np.cos(2*np.pi*x[:, 0]) + 0.01*rng.standard_normal(n)
+    else:
+        rho = s
+        u = 0.8 + 0.1*np.cos(2*np.pi*x[:, 1])
+        v = 0.05*np.sin(2*np.pi*x[:, 0])
+        p = 1.0 + 0.05*np.cos(2*np.pi*x[:, 0])
+        U[:n, 0] = rho; U[:n, 1] = rho*u; U[:n, 2] = rho*v
+        ke = 0.5*rho*(u*u + v*v)
+        if d == 3:
+            w = 0.02*np.sin(2*np.pi*x[:, 2])
+            U[:n, 3] = rho*w
+            ke = ke + 0.5*rho*w*w
+        U[:n, q-1] = p/0.4 + ke
+    return U.reshape(-1).copy()
+
+
+def ns_kwargs():
+    kw = B.ns_reference_values()
+    for k in ("ref_speed", "rho_ref", "u_inf"):
+        kw.pop(k)
+    return kw
+
+
+def bcs_ns3d():
+    """one no-slip wall, one inlet, one outlet, mirrors (+ one supersonic outlet)."""
+    wall = B.make_bc(B.BC_DIRICHLET, mask=[0, 1, 1, 1, 0], value=[0, 0, 0, 0, 0])
+    inlet = B.make_bc(B.BC_DIRICHLET, mask=[0, 1, 1, 1, 1], value=[0, 0.4, 0, 0, 1.0])
+    outlet = B.make_bc(B.BC_DIRICHLET, mask=[1, 0, 0, 0, 0], value=[1.0, 0, 0, 0, 0])
+    mirror = B.make_bc(B.BC_MIRROR_VELOCITY, zero_grad=[1, 0, 0, 0, 1])
+    return [inlet, outlet, wall, mirror, mirror, B.make_bc(B.BC_SUPER_OUTLET)]
+
+
+def bcs_ns2d():
+    wall = B.make_bc(B.BC_DIRICHLET, mask=[0, 1, 1, 0], value=[0, 0, 0, 0])
+    inlet = B.make_bc(B.BC_DIRICHLET, mask=[0, 1, 1, 1], value=[0, 0.4, 0, 1.0])
+    outlet = B.make_bc(B.BC_DIRICHLET, mask=[1, 0, 0, 0], value=[1.0, 0, 0, 0])
+    return [inlet, outlet, wall, B.make_bc(B.BC_MIRROR_VELOCITY)]
+
+
+def bcs_euler2d():
+    mir = B.make_bc(B.BC_MIRROR_EULER_CONS)
+    inl = B.make_bc(B.BC_DIRICHLET, mask=[1, 1, 1, 1], value=[1.0, 0.8, 0.0, 2.82])
+    return [inl, B.make_bc(B.BC_SUPER_OUTLET), mir, mir]
+
+
+def bcs_euler3d():
+    mir = B.make_bc(B.BC_MIRROR_EULER_CONS)
+    return [B.make_bc(B.BC_SUPER_OUTLET)]*2 + [mir]*4
+
+
+def ns3d_cfg(**over):
+    kw = dict(update_var=B.UV_PVT, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, diffusive=B.DIFF_NS, jacobian=True)
+    kw.update(ns_kwargs())
+    kw.update(over)
+    return B.make_config(3, **kw)
+
+
+def ns2d_cfg(**over):
+    kw = dict(update_var=B.UV_PVT, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, diffusive=B.DIFF_NS, jacobian=True)
+    kw.update(ns_kwargs())
+    kw.update(over)
+    return B.make_config(2, **kw)
+
+
+# name -> (mesh factory, config factory, bcs factory, primitive update variables?)
+CASES = {
+    # BASELINE config 3: 3D Navier-Stokes, Roe + viscous, LSQ + Venkatakrishnan, implicit (FD Jacobian)
+    "ns3d_hex": (lambda: meshgen.hex_box(7, 6, 5), ns3d_cfg, bcs_ns3d, True),
+    "ns3d_tet": (lambda: meshgen.tet_box(4, 3, 3), ns3d_cfg, bcs_ns3d, True),
+    "ns3d_hex_barth_fullstencil": (lambda: meshgen.hex_box(6, 5, 4),
+                                   lambda: ns3d_cfg(limiter=B.LIM_BARTHJESP, use_full_stencil=True), bcs_ns3d, True),
+    "ns3d_hex_resfactor": (lambda: meshgen.hex_box(5, 5, 4), lambda: ns3d_cfg(res_factor=0.5, gradient_factor=0.7),
+                           bcs_ns3d, True),
+    # BASELINE config 1: 2D Euler, first-order Roe
+    "euler2d_1st_quad": (lambda: meshgen.quad_channel(12, 9), lambda: B.make_config(2, jacobian=True), bcs_euler2d, False),
+    "euler2d_1st_tri": (lambda: meshgen.quad_channel(12, 9, triangles=True), lambda: B.make_config(2, jacobian=True),
+                        bcs_euler2d, False),
+    # BASELINE config 2: 2D Euler, LSQ + Venkatakrishnan, implicit
+    "euler2d_2nd_quad": (lambda: meshgen.quad_channel(12, 9),
+                         lambda: B.make_config(2, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, jacobian=True),
+                         bcs_euler2d, False),
+    "euler2d_2nd_tri_fullstencil": (lambda: meshgen.quad_channel(12, 9, triangles=True),
+                                    lambda: B.make_config(2, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, jacobian=True,
+                                                          use_full_stencil=True), bcs_euler2d, False),
+    "ns2d_quad": (lambda: meshgen.quad_channel(10, 8), ns2d_cfg, bcs_ns2d, True),
+    "ns2d_tri_nolimiter": (lambda: meshgen.quad_channel(10, 8, triangles=True), lambda: ns2d_cfg(limiter=B.LIM_NONE),
+                           bcs_ns2d, True),
+    "euler3d_cons_tet": (lambda: meshgen.tet_box(3, 3, 3),
+                         lambda: B.make_config(3, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, jacobian=True),
+                         bcs_euler3d, False),
+    # single cell / single row edge cases
+    "ns3d_single_cell": (lambda: meshgen.hex_box(1, 1, 1, jitter=0.0), ns3d_cfg, bcs_ns3d, True),
+    "euler2d_single_row": (lambda: meshgen.quad_channel(5, 1), lambda: B.make_config(2, poly_rec=B.PR_LINEARLS,
+                           limiter=B.LIM_BARTHJESP, jacobian=True), bcs_euler2d, False),
+}
+
+FIELDS = ("uX", "uY", "uZ", "limiter", "nstates")
+
+
+def run_case(name, oracle, make_engine, updatable=None, limiter_init=None, cfg_mut=None):
+    """Runs the oracle and an engine on one case; returns {quantity: (engine array, oracle array)}."""
+    mesh_f, cfg_f, bcs_f, pvt = CASES[name]
+    em = mesh_f()
+    fm = oracle.build_mesh(em)
+    cfg = cfg_f()
+    if cfg_mut:
+        cfg_mut(cfg)
+    bcs = bcs_f()
+    q = cfg.nEqs
+    if updatable is not None:
+        fm.updatable = np.ascontiguousarray(updatable(fm), dtype=np.uint8)
+    U = init_state(fm, q, pvt)
+    jac = bool(cfg.computeJacobian)
+    uc0 = 0.1*np.arange(fm.nCells, dtype=np.float64)/max(fm.nCells, 1)      # updateCoeff accumulates onto its input
+    r = oracle.compute(cfg, fm, bcs, U.copy(), jacobian=jac, limiter_init=limiter_init, update_coeff_init=uc0)
+    assert r.status == 0
+    e = make_engine(cfg)
+    out = {}
+    try:
+        e.set_mesh(fm, bcs)
+        e.set_states(U[:fm.nCells*q])
+        e.set_update_coeff(uc0)
+        if limiter_init is not None:
+            e.set_limiter(limiter_init)
+        rhs, uc = e.compute_rhs()
+        out["rhs"] = (rhs, r.rhs.copy())
+        out["updateCoeff"] = (uc, r.updateCoeff.copy())
+        for f in FIELDS:
+            if f == "uZ" and fm.dim == 2:
+                continue
+            out[f] = (e.field(f), getattr(r, f).copy())
+        out["gstates"] = (e.field("gstates"), None)
+        if jac:
+            out["jacobian"] = (e.bsr_values(), r.bsrVal.copy())
+            rp, ci = e.bsr_pattern()
+            out["bsrRowPtr"] = (rp, fm.bsrRowPtr)
+            out["bsrColInd"] = (ci, fm.bsrColInd)
+            # pseudo-steady time term on top (FVMCC_PseudoSteadyTimeRhs)
+            past = U[:fm.nCells*q]*(1 + 1e-3)
+            Uo = U.copy()
+            oracle.apply_bc(cfg, fm, bcs, Uo)
+            oracle.time_rhs(cfg, fm, bcs, Uo, np.concatenate([past, np.zeros(fm.nGhosts*q)]), r)
+            e.set_past_states(past)
+            out["time_rhs"] = (e.time_rhs(), r.rhs.copy())
+            out["time_jacobian"] = (e.bsr_values(), r.bsrVal.copy())
+        out["_fm"] = fm
+    finally:
+        e.close()
+    return out

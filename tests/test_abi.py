@@ -1,0 +1,59 @@
+"""The C-ABI shared library loads and exports every symbol include/cfb200.h declares; without a GPU the
+compute entry points fail loudly (no CPU fallback in the product)."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+from conftest import ROOT, has_gpu
+from coolfluid_b200 import lib as cl, config as B
+
+
+def test_header_symbols_exported(product_lib):
+    hdr = open(os.path.join(ROOT, "include", "cfb200.h")).read()
+    declared = sorted(set(re.findall(r"\b(cfb200_[a-z0-9_]+)\s*\(", hdr)))
+    assert len(declared) >= 40
+    dll = product_lib._cdll
+    missing = [s for s in declared if not hasattr(dll, s)]
+    assert missing == []
+    assert sorted("cfb200_" + s for s in cl.ABI_SYMBOLS) == declared
+    assert dll.cfb200_abi_version() == 1
+
+
+def test_struct_layouts_match_the_oracle(oracle):
+    """cfb200_config / cfb200_bc / cfb200_mesh are shared by value with the oracle's structs."""
+    L = oracle.lib()
+    assert L.cfo_sizeof_config() == C.sizeof(B.ConfigStruct)
+    assert L.cfo_sizeof_bc() == C.sizeof(B.BCStruct)
+    assert L.cfo_sizeof_meshview() == C.sizeof(cl.MeshStruct)
+
+
+def test_product_does_not_link_the_oracle():
+    out = os.popen("ldd %s" % cl.LIB_PATH).read()
+    assert "oracle" not in out and "hostsim" not in out
+    src = os.path.join(ROOT, "coolfluid_b200")
+    for dp, _dn, fns in os.walk(src):
+        for fn in fns:
+            if fn.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".inc", ".h")):
+                text = open(os.path.join(dp, fn)).read()
+                assert "import oracle" not in text and "from oracle" not in text and "liboracle" not in text, fn
+
+
+@pytest.mark.skipif(has_gpu(), reason="a GPU is present")
+def test_no_device_fails_loudly(product_lib):
+    cfg = B.make_config(2)
+    with pytest.raises(cl.Cfb200Error) as ei:
+        cl.Engine(cfg, 0, lib=product_lib)
+    assert ei.value.code == 3      # CFB200_ERR_NO_DEVICE
+    assert product_lib.device_count() == 0
+
+
+def test_invalid_arguments(product_lib):
+    h = C.c_void_p()
+    cfg = B.make_config(2)
+    cfg.nEqs = 7
+    assert product_lib.create(C.byref(cfg), 0, C.byref(h)) == 2
+    cfg = B.make_config(2, flux=B.FS_AUSMPLUS)
+    assert product_lib.create(C.byref(cfg), 0, C.byref(h)) == 6
+    assert product_lib.compute_rhs(None, 1, None, None) == 2

@@ -1,0 +1,83 @@
+"""CPU tier: the product's kernel functors + engine sequencing, compiled for the host by tests/hostsim (TEST ONLY),
+against the oracle.  This checks the kernel LOGIC (gather orders, slots, signs, operation order) without a GPU;
+the same cases run on the B200 through the C ABI in test_gpu_parity.py.  Bar: bit-exact (the FD Jacobian
+amplifies flux rounding by ~1e6, so the 1e-12 target of BASELINE.json is only robust if fluxes agree bit for bit)."""
+import numpy as np
+import pytest
+
+import cases
+from coolfluid_b200 import lib as cl
+
+
+def _engine_factory(hostsim_lib):
+    return lambda cfg: cl.Engine(cfg, 0, lib=hostsim_lib)
+
+
+def _check(out):
+    for k, ab in out.items():
+        if k.startswith("_") or ab[1] is None:
+            continue
+        a, b = ab
+        assert a.shape == b.shape, k
+        assert np.array_equal(a, b), "%s differs: rel err %.3e" % (k, cases.relerr(a, b))
+    assert np.abs(out["rhs"][1]).max() > 0.0
+
+
+@pytest.mark.parametrize("name", sorted(cases.CASES))
+def test_kernel_logic_bit_exact(name, oracle, hostsim_lib):
+    _check(cases.run_case(name, oracle, _engine_factory(hostsim_lib)))
+
+
+def test_partition_overlap_rows(oracle, hostsim_lib):
+    """Non-updatable (overlap) cells: faces with no updatable side are skipped, rows of non-updatable cells stay
+    zero, one-sided faces fill only the updatable row (FVMCC_ComputeRhsJacob.cxx:108-119,184-236)."""
+    def upd(fm):
+        x = fm.centres.reshape(-1, fm.dim)[:fm.nCells, 0]
+        return (x < 0.6).astype(np.uint8)
+    for name in ("ns3d_hex", "euler2d_2nd_tri_fullstencil"):
+        out = cases.run_case(name, oracle, _engine_factory(hostsim_lib), updatable=upd)
+        _check(out)
+        fm = out["_fm"]
+        jac = out["jacobian"][0].reshape(len(fm.bsrColInd), -1)
+        for c in np.nonzero(fm.updatable == 0)[0]:
+            assert not jac[fm.bsrRowPtr[c]:fm.bsrRowPtr[c+1]].any()
+
+
+def test_historical_and_frozen_limiter(oracle, hostsim_lib):
+    """FVMCC_PolyRec.cxx:131-165: residual <= limitRes -> limiter = min(new, stored); freezeLimiter keeps it."""
+    rng = np.random.RandomState(3)
+    for freeze in (0, 1):
+        def mut(cfg):
+            cfg.residual = -3.0
+            cfg.freezeLimiter = freeze
+        mesh_f = cases.CASES["ns3d_hex"][0]
+        n = mesh_f().n_cells*5
+        lim0 = 0.3 + 0.7*rng.random_sample(n)
+        out = cases.run_case("ns3d_hex", oracle, _engine_factory(hostsim_lib), limiter_init=lim0, cfg_mut=mut)
+        _check(out)
+        if freeze:
+            assert np.array_equal(out["limiter"][0], lim0)
+        else:
+            assert (out["limiter"][0] <= lim0).all() and (out["limiter"][0] < lim0).any()
+
+
+def test_stop_limiting(oracle, hostsim_lib):
+    def mut(cfg):
+        cfg.stopLimiting = 1
+    _check(cases.run_case("euler2d_2nd_quad", oracle, _engine_factory(hostsim_lib), cfg_mut=mut))
+
+
+def test_bad_value_is_reported(oracle, hostsim_lib):
+    """a^2 < 0 in the Roe linearisation -> CFB200_ERR_BAD_VALUE (BadValueException in the reference)."""
+    from coolfluid_b200 import meshgen, config as B
+    fm = oracle.build_mesh(meshgen.quad_channel(4, 4))
+    cfg = B.make_config(2)
+    U = cases.init_state(fm, 4, False)
+    U[4*5 + 3] = -50.0          # negative total energy in cell 5
+    e = cl.Engine(cfg, 0, lib=hostsim_lib)
+    e.set_mesh(fm, cases.bcs_euler2d())
+    e.set_states(U[:fm.nCells*4])
+    with pytest.raises(cl.Cfb200Error) as ei:
+        e.compute_rhs()
+    assert ei.value.code == 1
+    e.close()
