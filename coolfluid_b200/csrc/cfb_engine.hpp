@@ -230,11 +230,15 @@ public:
     bk.launch("nodalExtrapolate", NodalExtrapolate<D>{d}, d.nNodes, 256);
     if (cfg.polyRec == CFB200_PR_LINEARLS && cfg.limiter != CFB200_LIM_NONE)
       bk.launch("limiter", LimiterK<D>{d, cfg}, d.nCells, 128);
-    bk.launch("faceFlux", FaceFlux<D>{d, cfg}, d.nFaces, 128);
+    if (doJac) {
+      bk.launch("innerFaceJac", InnerFaceK<D, true>{d, cfg}, d.nInner, 128);
+      bk.launch("boundaryFaceJac", BoundaryFaceK<D, true>{d, cfg}, d.nGhosts, 128);
+    } else {
+      bk.launch("innerFace", InnerFaceK<D, false>{d, cfg}, d.nInner, 128);
+      bk.launch("boundaryFace", BoundaryFaceK<D, false>{d, cfg}, d.nGhosts, 128);
+    }
     bk.launch("cellGather", CellGather<D>{d, cfg}, d.nCells, 256);
     if (doJac) {
-      if (d.nInner) bk.launch("jacInner", JacInner<D>{d, cfg}, 2*d.nInner, 128);
-      if (d.nGhosts) bk.launch("jacBoundary", JacBoundary<D>{d, cfg}, d.nGhosts, 128);
       bk.launch("diagGather", DiagGather<D>{d}, d.nCells*32, 256);
       if (nNonUpd) bk.launch("zeroRows", ZeroRows<D>{d, nonUpdCells}, nNonUpd*32, 256);
     }

@@ -1,0 +1,418 @@
+// cfb200 — face kernels: reconstruction, Roe + Navier-Stokes face flux, update coefficients and the
+// finite-difference block Jacobian, one thread per face (included by cfb_kernels.cuh).
+//
+// Register discipline: every small array is indexed with compile-time constants only (loops over
+// variables are unrolled, the perturbed variable is handled with select chains, the perturbed side is a
+// template parameter), so nothing is demoted to local memory; the loop over the perturbed variable itself
+// stays rolled to keep the code size of ~1 flux evaluation per side.
+#pragma once
+// (included from inside namespace cfb in cfb_kernels.cuh)
+
+template <int N> CFB_HD double pick(const double* a, int i) {
+  double r = a[0];
+#pragma unroll
+  for (int k = 1; k < N; ++k) if (i == k) r = a[k];
+  return r;
+}
+
+// Per-face working set shared by the flux and the Jacobian part.
+template <int D>
+struct FaceWork {
+  static constexpr int Q = D + 2;
+  static constexpr int NMAX = (D == 2) ? 2 : 4;
+  typedef Phys<D> P;
+  int f, L, R, nbN; bool isB;
+  double n[3], area;
+  double gL[Q], gR[Q];      // limiter * gradientFactor * grad . (xq - x): the frozen reconstruction increments
+  // diamond control volume (DiamondVolume{2,3}DDerivative)
+  double cvn[8][3];         // 2D: 4 edge normals; 3D quad: 2x4 pyramid normals; 3D tri: 6 tetra normals
+  double volume, mu, lambda;
+  double val[Q][6];         // control-volume states per variable: face nodes in [0..3], L cell in [4], R state in [5]
+  double avState[Q];
+  double grad[Q][3];
+
+  // a8: LeastSquareP1PolyRec2D.cxx:158-217, 3D.cxx:204-268.  Boundary faces use the INNER cell's gradient
+  // and limiter for the ghost side (reference behaviour).  Also loads the unit normal (FVMCC_ComputeRHS.cxx:518-534).
+  CFB_HD void load(const Dev& d, const Cfg& c, int face, bool withDiamond) {
+    f = face; L = d.faceL[f]; R = d.faceR[f]; isB = (R >= d.nCells);
+    area = d.areas[f];
+    const double invArea = 1./area;
+    double xq[3] = {0., 0., 0.}, xL[3] = {0., 0., 0.}, xR[3] = {0., 0., 0.};
+    n[2] = 0.;
+#pragma unroll
+    for (int k = 0; k < D; ++k) {
+      n[k] = d.normals[(size_t)k*d.nFaces + f]*invArea;
+      xL[k] = d.centres[(size_t)k*d.nStates + L];
+      xR[k] = d.centres[(size_t)k*d.nStates + R];
+    }
+    if (c.polyRec == CFB200_PR_CONSTANT) {
+#pragma unroll
+      for (int v = 0; v < Q; ++v) { gL[v] = 0.; gR[v] = 0.; }
+    } else {
+#pragma unroll
+      for (int k = 0; k < D; ++k) xq[k] = d.faceCentres[(size_t)k*d.nFaces + f];
+      const int gradR = isB ? L : R;
+      const int32_t* zg = isB ? d.bcs[d.faceBC[f]].zeroGrad : nullptr;
+      const bool stop = (c.stopLimiting != 0);
+#pragma unroll
+      for (int v = 0; v < Q; ++v) {
+        const bool z = zg && zg[v];
+        double gcS = 0.0, gcN = 0.0;
+        if (!z) {
+          const size_t iL = (size_t)v*d.nCells + L, iR = (size_t)v*d.nCells + gradR;
+          if (D == 2) {
+            gcS = c.gradientFactor*(d.uX[iL]*(xq[0] - xL[0]) + d.uY[iL]*(xq[1] - xL[1]));
+            gcN = c.gradientFactor*(d.uX[iR]*(xq[0] - xR[0]) + d.uY[iR]*(xq[1] - xR[1]));
+          } else {
+            gcS = c.gradientFactor*(d.uX[iL]*(xq[0] - xL[0]) + d.uY[iL]*(xq[1] - xL[1]) + d.uZ[iL]*(xq[2] - xL[2]));
+            gcN = c.gradientFactor*(d.uX[iR]*(xq[0] - xR[0]) + d.uY[iR]*(xq[1] - xR[1]) + d.uZ[iR]*(xq[2] - xR[2]));
+          }
+        }
+        const double lValue = stop ? 1. : d.lim[(size_t)v*d.nCells + L];
+        const double rValue = stop ? 1. : d.lim[(size_t)v*d.nCells + gradR];
+        gL[v] = lValue*gcS;
+        gR[v] = rValue*gcN;
+      }
+    }
+    if (withDiamond) loadDiamond(d, xL, xR);
+  }
+
+  CFB_HD void reconstruct(const Cfg& c, const double* sL, const double* sR, double* vL, double* vR) const {
+    if (c.polyRec == CFB200_PR_CONSTANT) {
+#pragma unroll
+      for (int v = 0; v < Q; ++v) { vL[v] = sL[v]; vR[v] = sR[v]; }
+    } else {
+#pragma unroll
+      for (int v = 0; v < Q; ++v) { vL[v] = sL[v] + gL[v]; vR[v] = sR[v] + gR[v]; }
+    }
+  }
+
+  static CFB_HD void tetN(const double* a, const double* b, const double* c2, const double* dd, double fct, double* out) {
+    double v1[3], v2[3], v3[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { v1[k] = a[k] - b[k]; v2[k] = c2[k] - dd[k]; }
+    cross3(v1, v2, v3);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) out[k] = fct*v3[k];
+  }
+
+  // a15: control volume of the face, DiamondVolume2DDerivative.cxx:91-137, DiamondVolume3DDerivative.cxx:336-411,
+  // and the nodal part of the control-volume states.
+  CFB_HD void loadDiamond(const Dev& d, const double* xL, const double* xR) {
+    const int b = d.faceNodePtr[f];
+    nbN = d.faceNodePtr[f+1] - b;
+    double xn[NMAX][3];
+#pragma unroll
+    for (int j = 0; j < NMAX; ++j) {
+      const int node = d.faceNodes[b + ((j < nbN) ? j : nbN - 1)];
+      xn[j][2] = 0.;
+#pragma unroll
+      for (int k = 0; k < D; ++k) xn[j][k] = d.nodes[(size_t)k*d.nNodes + node];
+#pragma unroll
+      for (int v = 0; v < Q; ++v) val[v][j] = d.nstates[(size_t)v*d.nNodes + node];
+    }
+    if constexpr (D == 2) {
+      const double* node0 = xn[0]; const double* node1 = xL; const double* node2 = xn[1]; const double* node3 = xR;
+      cvn[0][0] = -node0[1] + node1[1]; cvn[0][1] = -node1[0] + node0[0];
+      cvn[1][0] = -node1[1] + node2[1]; cvn[1][1] = -node2[0] + node1[0];
+      cvn[2][0] = -node2[1] + node3[1]; cvn[2][1] = -node3[0] + node2[0];
+      cvn[3][0] = -node3[1] + node0[1]; cvn[3][1] = -node0[0] + node3[0];
+      const double det = (node2[0] - node0[0])*(node3[1] - node1[1]) - (node3[0] - node1[0])*(node2[1] - node0[1]);
+      if (det < 0.0) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { cvn[k][0] *= -1.; cvn[k][1] *= -1.; }
+      }
+      volume = 0.5*fabs(det);
+#pragma unroll
+      for (int v = 0; v < Q; ++v) avState[v] = 0.5*(val[v][0] + val[v][1]);
+    } else if constexpr (D == 3) { if (nbN == 3) {
+      // compute2TetraGradient normals, DiamondVolume3DDerivative.cxx:190-263
+      double factor = (!d.cvSign[f]) ? -0.5 : 0.5;
+      tetN(xL, xn[0], xn[1], xn[0], factor, cvn[0]);     // n031
+      tetN(xL, xn[1], xn[2], xn[1], factor, cvn[1]);     // n132
+      tetN(xn[2], xn[0], xL, xn[0], factor, cvn[2]);     // n023
+      factor *= -1;
+      tetN(xR, xn[0], xn[1], xn[0], factor, cvn[3]);     // n041
+      tetN(xR, xn[1], xn[2], xn[1], factor, cvn[4]);     // n142
+      tetN(xn[2], xn[0], xR, xn[0], factor, cvn[5]);     // n024
+      volume = d.cvol[f];
+#pragma unroll
+      for (int v = 0; v < Q; ++v) avState[v] = (1./3.)*(val[v][0] + val[v][1] + val[v][2]);
+    } else {
+      // compute2PyramidNormals, DiamondVolume3DDerivative.cxx:336-383
+      double factor = (!d.cvSign[f]) ? 1.0 : -1.0;
+      triNormal(xn[0], xn[1], xL, factor, cvn[0]); triNormal(xn[1], xn[2], xL, factor, cvn[1]);
+      triNormal(xn[2], xn[3], xL, factor, cvn[2]); triNormal(xn[0], xL, xn[3], factor, cvn[3]);
+      factor *= -1.;
+      triNormal(xn[0], xn[1], xR, factor, cvn[4]); triNormal(xn[1], xn[2], xR, factor, cvn[5]);
+      triNormal(xn[2], xn[3], xR, factor, cvn[6]); triNormal(xn[0], xR, xn[3], factor, cvn[7]);
+      volume = d.cvol[f];
+#pragma unroll
+      for (int v = 0; v < Q; ++v) avState[v] = 0.25*(val[v][0] + val[v][1] + val[v][2] + val[v][3]);
+    } }
+  }
+
+  // Green-Gauss gradient of one variable over the diamond from its 6 control-volume values a[] (nodes 0..3, L, R):
+  // DiamondVolume2DDerivative.cxx:139-176, DiamondVolume3DDerivative.cxx:190-298
+  CFB_HD void gradRow(const double* a, double* g) const {
+    if constexpr (D == 2) {
+      const double invVolume = 0.5/volume;
+      const double v01 = a[0] + a[4], v12 = a[4] + a[1], v23 = a[1] + a[5], v30 = a[5] + a[0];
+#pragma unroll
+      for (int ix = 0; ix < 2; ++ix)
+        g[ix] = invVolume*(cvn[0][ix]*v01 + cvn[1][ix]*v12 + cvn[2][ix]*v23 + cvn[3][ix]*v30);
+      g[2] = 0.;
+    } else if constexpr (D == 3) { if (nbN == 3) {
+      const double invVolume = (1./3.)/volume;
+      const double v031 = a[0] + a[4] + a[1], v132 = a[1] + a[4] + a[2], v023 = a[0] + a[2] + a[4];
+      const double v041 = a[0] + a[5] + a[1], v142 = a[1] + a[5] + a[2], v024 = a[0] + a[2] + a[5];
+#pragma unroll
+      for (int ix = 0; ix < 3; ++ix)
+        g[ix] = invVolume*(cvn[0][ix]*v031 + cvn[1][ix]*v132 + cvn[2][ix]*v023 +
+                           cvn[3][ix]*v041 + cvn[4][ix]*v142 + cvn[5][ix]*v024);
+    } else {
+      const double invVolume = (1./3.)/volume;
+      const double v014 = a[0] + a[1] + a[4], v124 = a[1] + a[2] + a[4], v234 = a[2] + a[3] + a[4], v043 = a[0] + a[4] + a[3];
+      const double v015 = a[0] + a[1] + a[5], v125 = a[1] + a[2] + a[5], v235 = a[2] + a[3] + a[5], v053 = a[0] + a[5] + a[3];
+#pragma unroll
+      for (int ix = 0; ix < 3; ++ix)
+        g[ix] = invVolume*(cvn[0][ix]*v014 + cvn[1][ix]*v124 + cvn[2][ix]*v234 + cvn[3][ix]*v043 +
+                           cvn[4][ix]*v015 + cvn[5][ix]*v125 + cvn[6][ix]*v235 + cvn[7][ix]*v053);
+    } }
+  }
+  CFB_HD void setCellStates(const double* sL, const double* sR) {
+#pragma unroll
+    for (int v = 0; v < Q; ++v) { val[v][4] = sL[v]; val[v][5] = sR[v]; }
+  }
+  CFB_HD void allGrads() {
+#pragma unroll
+    for (int v = 0; v < Q; ++v) gradRow(val[v], grad[v]);
+  }
+  // a14: NSFlux.ci:59-156.  mu/lambda depend on the NODAL average state only, which the perturbation loop never
+  // touches (and which FreezeDiffCoeff would freeze anyway), so they are evaluated once per face.
+  CFB_HD void transport(const Cfg& c) {
+    mu = P::dynViscosity(c, avState)*c.artDiffCoeff;
+    lambda = P::thermConductivity(c, mu);
+  }
+  CFB_HD void diffFlux(const Cfg& c, const double (*g)[3], double* dflux) const {
+    P::nsFlux(c, avState, g, n, mu, lambda, dflux);
+#pragma unroll
+    for (int v = 0; v < Q; ++v) dflux[v] *= area;
+  }
+
+  // Base (unperturbed) evaluation: a11/a14/a17.  Returns the face-integrated flux (convective - diffusive) and the
+  // update coefficients (RoeFlux.cxx:165-185, NSFlux.ci:127-152).
+  CFB_HD void baseFlux(const Dev& d, const Cfg& c, const double* sL, const double* sR, const typename P::Side& a,
+                       const typename P::Side& b, bool hasDiff, double* flux, double& ucL, double& ucR, double& ucD) {
+    if (!P::roe(c, a, b, n, flux)) {
+      *d.status = CFB200_ERR_BAD_VALUE;
+#pragma unroll
+      for (int v = 0; v < Q; ++v) flux[v] = 0.;
+    }
+    const double faceArea = area/1;                     // one quadrature point per face
+    ucL = dmax(P::maxEigenValue(a.pd, n), 0.)*faceArea;
+    double tn[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) tn[k] = -1.0*n[k];
+    ucR = dmax(P::maxEigenValue(b.pd, tn), 0.)*faceArea;
+#pragma unroll
+    for (int v = 0; v < Q; ++v) flux[v] *= area;        // FVMCC_FluxSplitter.hh:79-83
+    ucD = 0.;
+    if (hasDiff) {
+      setCellStates(sL, sR);
+      allGrads();
+      transport(c);
+      double dflux[Q];
+      diffFlux(c, grad, dflux);
+#pragma unroll
+      for (int v = 0; v < Q; ++v) flux[v] -= dflux[v];  // FVMCC_ComputeRHS.cxx:260-276
+      const double nu = mu/P::density(c, avState);
+      ucD = nu*area*area/volume;
+    }
+  }
+
+  // a18: FVMCC_ComputeRhsJacob.cxx:126-236,321-365.  Perturbs the q variables of the SIDE cell in turn, re-evaluates
+  // the convective + diffusive flux with frozen gradient/limiter (LeastSquareP1PolyRec2D.cxx:221-262), and writes
+  // column iVar of   blk = sgn * resFactor * dF/dU_SIDE   (row-major q x q, BlockAccumulator.hh:289-296).
+  template <int SIDE>
+  CFB_HD void perturbSide(const Dev& d, const Cfg& c, const double* sP, const double* vBase,
+                          const typename P::Side& fixed, const double* flux, bool hasDiff, bool negate, double* blk) const {
+    const double rf = c.resFactor;
+#pragma unroll 1
+    for (int iVar = 0; iVar < Q; ++iVar) {
+      const double orig = pick<Q>(sP, iVar);
+      const double eps = fdEps(c, iVar, orig);
+      const double pv = orig + eps;
+      const double pvr = (c.polyRec == CFB200_PR_CONSTANT) ? pv : pv + pick<Q>(SIDE == 0 ? gL : gR, iVar);
+      double vp[Q];
+#pragma unroll
+      for (int v = 0; v < Q; ++v) vp[v] = (v == iVar) ? pvr : vBase[v];
+      typename P::Side pert;
+      P::side(c, vp, n, pert);
+      double pf[Q];
+      const bool ok = (SIDE == 0) ? P::roe(c, pert, fixed, n, pf) : P::roe(c, fixed, pert, n, pf);
+      if (!ok) {
+        *d.status = CFB200_ERR_BAD_VALUE;
+#pragma unroll
+        for (int v = 0; v < Q; ++v) pf[v] = 0.;
+      }
+#pragma unroll
+      for (int v = 0; v < Q; ++v) pf[v] *= area;
+      if (hasDiff) {
+        double a[6], gr[3];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+          double r = val[0][j];
+#pragma unroll
+          for (int v = 1; v < Q; ++v) if (iVar == v) r = val[v][j];
+          a[j] = r;
+        }
+        a[4 + SIDE] = pv;                        // the control volume holds the CELL state, not the reconstructed one
+        gradRow(a, gr);
+        double g2[Q][3];
+#pragma unroll
+        for (int v = 0; v < Q; ++v)
+#pragma unroll
+          for (int k = 0; k < 3; ++k) g2[v][k] = (v == iVar) ? gr[k] : grad[v][k];
+        double dflux[Q];
+        diffFlux(c, g2, dflux);
+#pragma unroll
+        for (int v = 0; v < Q; ++v) pf[v] -= dflux[v];
+      }
+      const double invEps = 1./eps;
+#pragma unroll
+      for (int v = 0; v < Q; ++v) {
+        double fd = (pf[v] - flux[v])*invEps;
+        fd *= rf;                                // what row L receives (upFactor[0])
+        blk[v*Q + iVar] = negate ? fd*(-1.0) : fd;   // row R receives upFactor[1] = -1 times that
+      }
+    }
+  }
+};
+
+// ------------------------------------------------------------------------------------------------
+// Interior faces: flux + update coefficients into face-owned slots and, when JAC, the two off-diagonal blocks
+//   block(R,L) = -resFactor * dF/dU_L        block(L,R) = +resFactor * dF/dU_R
+// straight into the BSR array (each has exactly one writer).  The diagonal contributions are the negatives of
+// these and are gathered by DiagGather.  One-sided updatable faces (partition overlap) use the same values
+// (FVMCC_ComputeRhsJacob.cxx:184-236: row idx receives (-1)^idx * resFactor * dF/dU); the blocks that land in
+// non-updatable rows are staging for DiagGather and are zeroed afterwards by ZeroRows.
+template <int D, bool JAC>
+struct InnerFaceK {   // idx over interior faces
+  Dev d; Cfg c;
+  CFB_HD void operator()(int f) const {
+    constexpr int Q = D + 2;
+    typedef Phys<D> P;
+    const bool hasDiff = (c.diffusive == CFB200_DIFF_NS);
+    const int L = d.faceL[f], R = d.faceR[f];
+    if (!(d.updatable[L] || d.updatable[R])) {             // FVMCC_ComputeRHS.cxx:212-213
+#pragma unroll
+      for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = 0.;
+      d.ucL[f] = 0.; d.ucR[f] = 0.; d.ucD[f] = 0.;
+      if (JAC) {
+        double* b0 = &d.bsrVal[(size_t)d.slotRL[f]*Q*Q]; double* b1 = &d.bsrVal[(size_t)d.slotLR[f]*Q*Q];
+        for (int k = 0; k < Q*Q; ++k) { b0[k] = 0.; b1[k] = 0.; }
+      }
+      return;
+    }
+    FaceWork<D> w;
+    w.load(d, c, f, hasDiff);
+    double sL[Q], sR[Q], vL[Q], vR[Q], flux[Q];
+#pragma unroll
+    for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + L]; sR[v] = d.U[(size_t)v*d.nStates + R]; }
+    w.reconstruct(c, sL, sR, vL, vR);
+    typename P::Side a, b;
+    P::side(c, vL, w.n, a);
+    P::side(c, vR, w.n, b);
+    double ucL, ucR, ucD;
+    w.baseFlux(d, c, sL, sR, a, b, hasDiff, flux, ucL, ucR, ucD);
+    d.ucL[f] = ucL; d.ucR[f] = ucR; d.ucD[f] = ucD;
+#pragma unroll
+    for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = flux[v];
+    if (JAC) {
+      w.template perturbSide<0>(d, c, sL, vL, b, flux, hasDiff, true, &d.bsrVal[(size_t)d.slotRL[f]*Q*Q]);
+      w.template perturbSide<1>(d, c, sR, vR, a, flux, hasDiff, false, &d.bsrVal[(size_t)d.slotLR[f]*Q*Q]);
+    }
+  }
+};
+
+// Boundary faces: flux as above (the ghost is the R state) and, when JAC, FVMCC_ComputeRhsJacob.cxx:240-317: the inner
+// state is perturbed, the ghost state is rebuilt by the boundary condition, both sides are re-extrapolated, and
+// resFactor * dF/dU_L goes to the boundary block of the face (added to the diagonal by DiagGather).
+template <int D, bool JAC>
+struct BoundaryFaceK {   // idx over boundary faces
+  Dev d; Cfg c;
+  CFB_HD void operator()(int g) const {
+    constexpr int Q = D + 2;
+    typedef Phys<D> P;
+    const bool hasDiff = (c.diffusive == CFB200_DIFF_NS);
+    const int f = d.nInner + g;
+    const int L = d.faceL[f], R = d.faceR[f];
+    double* blk = &d.bndBlocks[(size_t)g*Q*Q];
+    if (!d.updatable[L]) {
+#pragma unroll
+      for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = 0.;
+      d.ucL[f] = 0.; d.ucR[f] = 0.; d.ucD[f] = 0.;
+      if (JAC) for (int k = 0; k < Q*Q; ++k) blk[k] = 0.;
+      return;
+    }
+    FaceWork<D> w;
+    w.load(d, c, f, hasDiff);
+    double sL[Q], sR[Q], vL[Q], vR[Q], flux[Q];
+#pragma unroll
+    for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + L]; sR[v] = d.U[(size_t)v*d.nStates + R]; }
+    w.reconstruct(c, sL, sR, vL, vR);
+    {
+      typename P::Side a, b;
+      P::side(c, vL, w.n, a);
+      P::side(c, vR, w.n, b);
+      double ucL, ucR, ucD;
+      w.baseFlux(d, c, sL, sR, a, b, hasDiff, flux, ucL, ucR, ucD);
+      d.ucL[f] = ucL; d.ucR[f] = ucR; d.ucD[f] = ucD;
+    }
+#pragma unroll
+    for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = flux[v];
+    if (!JAC) return;
+    double nr[D];
+#pragma unroll
+    for (int k = 0; k < D; ++k) nr[k] = d.normals[(size_t)k*d.nFaces + f];
+    const BCond& bc = d.bcs[d.faceBC[f]];
+    const double rf = c.resFactor;
+#pragma unroll 1
+    for (int iVar = 0; iVar < Q; ++iVar) {
+      const double orig = pick<Q>(sL, iVar);
+      const double eps = fdEps(c, iVar, orig);
+      double sLp[Q], sRp[Q];
+#pragma unroll
+      for (int v = 0; v < Q; ++v) sLp[v] = (v == iVar) ? orig + eps : sL[v];
+      ghostState<D>(c, bc, nr, sLp, sRp);
+      w.reconstruct(c, sLp, sRp, vL, vR);
+      typename P::Side a, b;
+      P::side(c, vL, w.n, a);
+      P::side(c, vR, w.n, b);
+      double pf[Q];
+      if (!P::roe(c, a, b, w.n, pf)) {
+        *d.status = CFB200_ERR_BAD_VALUE;
+#pragma unroll
+        for (int v = 0; v < Q; ++v) pf[v] = 0.;
+      }
+#pragma unroll
+      for (int v = 0; v < Q; ++v) pf[v] *= w.area;
+      if (hasDiff) {
+        w.setCellStates(sLp, sRp);
+        w.allGrads();
+        double dflux[Q];
+        w.diffFlux(c, w.grad, dflux);
+#pragma unroll
+        for (int v = 0; v < Q; ++v) pf[v] -= dflux[v];
+      }
+      const double invEps = 1./eps;
+#pragma unroll
+      for (int v = 0; v < Q; ++v) {
+        double fd = (pf[v] - flux[v])*invEps;
+        fd *= rf;
+        blk[v*Q + iVar] = fd;
+      }
+    }
+  }
+};

@@ -336,221 +336,7 @@ struct LimiterK {   // idx over cells
   }
 };
 
-// ------------------------------------------------------------------------------------------------
-// Per-face working set shared by the flux kernel and the finite-difference Jacobian kernels.
-template <int D>
-struct FaceWork {
-  static constexpr int Q = D + 2;
-  typedef Phys<D> P;
-  int f, L, R, nbN; bool isB;
-  double n[3], area, xq[3], xL[3], xR[3];
-  double gL[Q], gR[Q];      // limiter * gradientFactor * grad . (xq - x): the frozen reconstruction increments
-  // diamond control volume (DiamondVolume{2,3}DDerivative)
-  double cvn[8][3];         // 2D: 4 edge normals; 3D quad: 2x4 pyramid normals; 3D tri: 6 tetra normals
-  double volume, mu, lambda;
-  double val[Q][6];         // values(i,j) = state j of the control volume, variable i
-  double avState[Q];
-  double grad[Q][3];
-
-  CFB_HD void loadGeom(const Dev& d, int face) {
-    f = face; L = d.faceL[f]; R = d.faceR[f]; isB = (R >= d.nCells);
-    area = d.areas[f];
-    const double invArea = 1./area;                     // FVMCC_ComputeRHS.cxx:518-534
-    for (int k = 0; k < D; ++k) {
-      n[k] = d.normals[(size_t)k*d.nFaces + f]*invArea;
-      xq[k] = d.faceCentres[(size_t)k*d.nFaces + f];
-      xL[k] = d.centres[(size_t)k*d.nStates + L];
-      xR[k] = d.centres[(size_t)k*d.nStates + R];
-    }
-    if (D == 2) { n[2] = 0.; xq[2] = 0.; xL[2] = 0.; xR[2] = 0.; }
-  }
-
-  // a8: LeastSquareP1PolyRec2D.cxx:158-217, 3D.cxx:204-268.  Boundary faces use the INNER cell's gradient
-  // and limiter for the ghost side (reference behaviour).
-  CFB_HD void loadReconstruction(const Dev& d, const Cfg& c) {
-    if (c.polyRec == CFB200_PR_CONSTANT) { for (int v = 0; v < Q; ++v) { gL[v] = 0.; gR[v] = 0.; } return; }
-    const int gradR = isB ? L : R;
-    const int32_t* zg = isB ? d.bcs[d.faceBC[f]].zeroGrad : nullptr;
-    for (int v = 0; v < Q; ++v) {
-      const bool z = zg && zg[v];
-      double gcS = 0.0, gcN = 0.0;
-      if (!z) {
-        const size_t iL = (size_t)v*d.nCells + L, iR = (size_t)v*d.nCells + gradR;
-        if (D == 2) {
-          gcS = c.gradientFactor*(d.uX[iL]*(xq[0] - xL[0]) + d.uY[iL]*(xq[1] - xL[1]));
-          gcN = c.gradientFactor*(d.uX[iR]*(xq[0] - xR[0]) + d.uY[iR]*(xq[1] - xR[1]));
-        } else {
-          gcS = c.gradientFactor*(d.uX[iL]*(xq[0] - xL[0]) + d.uY[iL]*(xq[1] - xL[1]) + d.uZ[iL]*(xq[2] - xL[2]));
-          gcN = c.gradientFactor*(d.uX[iR]*(xq[0] - xR[0]) + d.uY[iR]*(xq[1] - xR[1]) + d.uZ[iR]*(xq[2] - xR[2]));
-        }
-      }
-      const double lValue = (c.stopLimiting == 0) ? d.lim[(size_t)v*d.nCells + L] : 1.;
-      const double rValue = (c.stopLimiting == 0) ? d.lim[(size_t)v*d.nCells + gradR] : 1.;
-      gL[v] = lValue*gcS;
-      gR[v] = rValue*gcN;
-    }
-  }
-  CFB_HD void reconstruct(const Cfg& c, const double* sL, const double* sR, double* vL, double* vR) const {
-    if (c.polyRec == CFB200_PR_CONSTANT) { for (int v = 0; v < Q; ++v) { vL[v] = sL[v]; vR[v] = sR[v]; } return; }
-    for (int v = 0; v < Q; ++v) { vL[v] = sL[v] + gL[v]; vR[v] = sR[v] + gR[v]; }
-  }
-
-  // a15: control volume of the face, DiamondVolume2DDerivative.cxx:91-137, DiamondVolume3DDerivative.cxx:336-411,
-  // and the nodal part of the control-volume states.
-  CFB_HD void loadDiamond(const Dev& d) {
-    const int b = d.faceNodePtr[f];
-    nbN = d.faceNodePtr[f+1] - b;
-    int fn[4];
-    double xn[4][3];
-    for (int j = 0; j < nbN; ++j) {
-      fn[j] = d.faceNodes[b + j];
-      for (int k = 0; k < D; ++k) xn[j][k] = d.nodes[(size_t)k*d.nNodes + fn[j]];
-    }
-    if (D == 2) {
-      const double* node0 = xn[0]; const double* node1 = xL; const double* node2 = xn[1]; const double* node3 = xR;
-      cvn[0][0] = -node0[1] + node1[1]; cvn[0][1] = -node1[0] + node0[0];
-      cvn[1][0] = -node1[1] + node2[1]; cvn[1][1] = -node2[0] + node1[0];
-      cvn[2][0] = -node2[1] + node3[1]; cvn[2][1] = -node3[0] + node2[0];
-      cvn[3][0] = -node3[1] + node0[1]; cvn[3][1] = -node0[0] + node3[0];
-      const double det = (node2[0] - node0[0])*(node3[1] - node1[1]) - (node3[0] - node1[0])*(node2[1] - node0[1]);
-      if (det < 0.0) for (int k = 0; k < 4; ++k) { cvn[k][0] *= -1.; cvn[k][1] *= -1.; }
-      volume = 0.5*fabs(det);
-      // control-volume order: node0, L, node1, R
-      for (int v = 0; v < Q; ++v) {
-        val[v][0] = d.nstates[(size_t)v*d.nNodes + fn[0]];
-        val[v][2] = d.nstates[(size_t)v*d.nNodes + fn[1]];
-        avState[v] = 0.5*(val[v][0] + val[v][2]);
-      }
-    } else if (nbN == 3) {
-      // compute2TetraGradient normals, DiamondVolume3DDerivative.cxx:190-263
-      double factor = (!d.cvSign[f]) ? -0.5 : 0.5;
-      tetN(xL, xn[0], xn[1], xn[0], factor, cvn[0]);     // n031
-      tetN(xL, xn[1], xn[2], xn[1], factor, cvn[1]);     // n132
-      tetN(xn[2], xn[0], xL, xn[0], factor, cvn[2]);     // n023
-      factor *= -1;
-      tetN(xR, xn[0], xn[1], xn[0], factor, cvn[3]);     // n041
-      tetN(xR, xn[1], xn[2], xn[1], factor, cvn[4]);     // n142
-      tetN(xn[2], xn[0], xR, xn[0], factor, cvn[5]);     // n024
-      volume = d.cvol[f];
-      for (int v = 0; v < Q; ++v) {
-        for (int j = 0; j < 3; ++j) val[v][j] = d.nstates[(size_t)v*d.nNodes + fn[j]];
-        avState[v] = (1./3.)*(val[v][0] + val[v][1] + val[v][2]);
-      }
-    } else {
-      // compute2PyramidNormals, DiamondVolume3DDerivative.cxx:336-383
-      double factor = (!d.cvSign[f]) ? 1.0 : -1.0;
-      triNormal(xn[0], xn[1], xL, factor, cvn[0]); triNormal(xn[1], xn[2], xL, factor, cvn[1]);
-      triNormal(xn[2], xn[3], xL, factor, cvn[2]); triNormal(xn[0], xL, xn[3], factor, cvn[3]);
-      factor *= -1.;
-      triNormal(xn[0], xn[1], xR, factor, cvn[4]); triNormal(xn[1], xn[2], xR, factor, cvn[5]);
-      triNormal(xn[2], xn[3], xR, factor, cvn[6]); triNormal(xn[0], xR, xn[3], factor, cvn[7]);
-      volume = d.cvol[f];
-      for (int v = 0; v < Q; ++v) {
-        for (int j = 0; j < 4; ++j) val[v][j] = d.nstates[(size_t)v*d.nNodes + fn[j]];
-        avState[v] = 0.25*(val[v][0] + val[v][1] + val[v][2] + val[v][3]);
-      }
-    }
-  }
-  static CFB_HD void tetN(const double* a, const double* b, const double* c2, const double* dd, double fct, double* out) {
-    double v1[3], v2[3], v3[3];
-    for (int k = 0; k < 3; ++k) { v1[k] = a[k] - b[k]; v2[k] = c2[k] - dd[k]; }
-    cross3(v1, v2, v3);
-    for (int k = 0; k < 3; ++k) out[k] = fct*v3[k];
-  }
-  // positions of the L / R cell states in the control volume
-  CFB_HD int slotL() const { return (D == 2) ? 1 : nbN; }
-  CFB_HD int slotR() const { return (D == 2) ? 3 : nbN + 1; }
-
-  // Green-Gauss gradient of variable v over the diamond: DiamondVolume2DDerivative.cxx:139-176,
-  // DiamondVolume3DDerivative.cxx:190-298
-  CFB_HD void diamondGrad(int v) {
-    const double* a = val[v];
-    if (D == 2) {
-      const double invVolume = 0.5/volume;
-      const double v01 = a[0] + a[1], v12 = a[1] + a[2], v23 = a[2] + a[3], v30 = a[3] + a[0];
-      for (int ix = 0; ix < 2; ++ix)
-        grad[v][ix] = invVolume*(cvn[0][ix]*v01 + cvn[1][ix]*v12 + cvn[2][ix]*v23 + cvn[3][ix]*v30);
-      grad[v][2] = 0.;
-    } else if (nbN == 3) {
-      const double invVolume = (1./3.)/volume;
-      const double v031 = a[0] + a[3] + a[1], v132 = a[1] + a[3] + a[2], v023 = a[0] + a[2] + a[3];
-      const double v041 = a[0] + a[4] + a[1], v142 = a[1] + a[4] + a[2], v024 = a[0] + a[2] + a[4];
-      for (int ix = 0; ix < 3; ++ix)
-        grad[v][ix] = invVolume*(cvn[0][ix]*v031 + cvn[1][ix]*v132 + cvn[2][ix]*v023 +
-                                 cvn[3][ix]*v041 + cvn[4][ix]*v142 + cvn[5][ix]*v024);
-    } else {
-      const double invVolume = (1./3.)/volume;
-      const double v014 = a[0] + a[1] + a[4], v124 = a[1] + a[2] + a[4], v234 = a[2] + a[3] + a[4], v043 = a[0] + a[4] + a[3];
-      const double v015 = a[0] + a[1] + a[5], v125 = a[1] + a[2] + a[5], v235 = a[2] + a[3] + a[5], v053 = a[0] + a[5] + a[3];
-      for (int ix = 0; ix < 3; ++ix)
-        grad[v][ix] = invVolume*(cvn[0][ix]*v014 + cvn[1][ix]*v124 + cvn[2][ix]*v234 + cvn[3][ix]*v043 +
-                                 cvn[4][ix]*v015 + cvn[5][ix]*v125 + cvn[6][ix]*v235 + cvn[7][ix]*v053);
-    }
-  }
-
-  // a14: NSFlux.ci:59-156: flux integrated over the face.  mu/lambda depend on the NODAL average state only,
-  // which the perturbation loop never touches, so they are evaluated once per face.
-  CFB_HD void transport(const Cfg& c) {
-    mu = P::dynViscosity(c, avState)*c.artDiffCoeff;
-    lambda = P::thermConductivity(c, mu);
-  }
-  CFB_HD void diffFlux(const Cfg& c, double* dflux) const {
-    P::nsFlux(c, avState, grad, n, mu, lambda, dflux);
-    for (int v = 0; v < Q; ++v) dflux[v] *= area;
-  }
-};
-
-// ------------------------------------------------------------------------------------------------
-// a11/a14/a17: one thread per face: reconstruct, Roe flux, Navier-Stokes flux, update coefficients.
-// Writes face-owned slots only (no scatter).
-template <int D>
-struct FaceFlux {   // idx over faces
-  Dev d; Cfg c;
-  CFB_HD void operator()(int f) const {
-    constexpr int Q = D + 2;
-    typedef Phys<D> P;
-    FaceWork<D> w;
-    w.loadGeom(d, f);
-    const bool upL = d.updatable[w.L];
-    const bool upR = (!w.isB) && d.updatable[w.R];
-    if (!(upL || upR)) {                                   // FVMCC_ComputeRHS.cxx:212-213
-      for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = 0.;
-      d.ucL[f] = 0.; d.ucR[f] = 0.; d.ucD[f] = 0.;
-      return;
-    }
-    double sL[Q], sR[Q], vL[Q], vR[Q];
-    for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + w.L]; sR[v] = d.U[(size_t)v*d.nStates + w.R]; }
-    w.loadReconstruction(d, c);
-    w.reconstruct(c, sL, sR, vL, vR);
-    typename P::Side a, b;
-    P::side(c, vL, w.n, a);
-    P::side(c, vR, w.n, b);
-    double flux[Q];
-    if (!P::roe(c, a, b, w.n, flux)) { *d.status = CFB200_ERR_BAD_VALUE; for (int v = 0; v < Q; ++v) flux[v] = 0.; }
-    // RoeFlux.cxx:165-185 update coefficients (one quadrature point per face)
-    const double faceArea = w.area/1;
-    d.ucL[f] = dmax(P::maxEigenValue(a.pd, w.n), 0.)*faceArea;
-    double tn[3];
-    for (int k = 0; k < 3; ++k) tn[k] = -1.0*w.n[k];
-    d.ucR[f] = dmax(P::maxEigenValue(b.pd, tn), 0.)*faceArea;
-    for (int v = 0; v < Q; ++v) flux[v] *= w.area;         // FVMCC_FluxSplitter.hh:79-83
-    double ucD = 0.;
-    if (c.diffusive == CFB200_DIFF_NS) {
-      w.loadDiamond(d);
-      for (int v = 0; v < Q; ++v) { w.val[v][w.slotL()] = sL[v]; w.val[v][w.slotR()] = sR[v]; }
-      for (int v = 0; v < Q; ++v) w.diamondGrad(v);
-      w.transport(c);
-      double dflux[Q];
-      w.diffFlux(c, dflux);
-      for (int v = 0; v < Q; ++v) flux[v] -= dflux[v];     // FVMCC_ComputeRHS.cxx:260-276
-      const double nu = w.mu/P::density(c, w.avState);     // NSFlux.ci:127-152
-      ucD = nu*w.area*w.area/w.volume;
-      d.faceMu[f] = w.mu;
-    }
-    d.ucD[f] = ucD;
-    for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = flux[v];
-  }
-};
+#include "cfb_face.cuh"
 
 // a17: FVMCC_ComputeRHS::updateRHS (FVMCC_ComputeRHS.cxx:455-514) as a gather: for each cell, its faces in
 // ascending loop order; rhs starts from 0, updateCoeff accumulates onto the incoming value
@@ -581,138 +367,6 @@ struct CellGather {   // idx over cells
     }
     for (int v = 0; v < Q; ++v) d.rhs[(size_t)cell*Q + v] = r[v];
     d.updateCoeff[cell] = uc;
-  }
-};
-
-// ------------------------------------------------------------------------------------------------
-// a18: finite-difference block Jacobian of an interior face, FVMCC_ComputeRhsJacob.cxx:126-236,321-365.
-// One thread per (face, side): perturbs the q variables of that side's cell in turn, re-evaluates the
-// convective + diffusive flux with frozen gradient/limiter, and writes the q x q block
-//   side L: block(R,L) = -resFactor * dF/dU_L      side R: block(L,R) = +resFactor * dF/dU_R
-// (the diagonal contributions are the negatives of these and are gathered by DiagGather).
-template <int D>
-struct JacInner {   // idx over 2*nInner
-  Dev d; Cfg c;
-  CFB_HD void operator()(int idx) const {
-    constexpr int Q = D + 2;
-    typedef Phys<D> P;
-    const int f = idx >> 1, side = idx & 1;
-    FaceWork<D> w;
-    w.loadGeom(d, f);
-    double* blk = &d.bsrVal[(size_t)(side == 0 ? d.slotRL[f] : d.slotLR[f])*Q*Q];
-    const bool upL = d.updatable[w.L], upR = d.updatable[w.R];
-    if (!(upL || upR)) { for (int k = 0; k < Q*Q; ++k) blk[k] = 0.; return; }
-    double sL[Q], sR[Q], vL[Q], vR[Q], flux[Q];
-    for (int v = 0; v < Q; ++v) {
-      sL[v] = d.U[(size_t)v*d.nStates + w.L]; sR[v] = d.U[(size_t)v*d.nStates + w.R];
-      flux[v] = d.faceFlux[(size_t)v*d.nFaces + f];
-    }
-    w.loadReconstruction(d, c);
-    w.reconstruct(c, sL, sR, vL, vR);
-    const bool hasDiff = (c.diffusive == CFB200_DIFF_NS);
-    if (hasDiff) {
-      w.loadDiamond(d);
-      for (int v = 0; v < Q; ++v) { w.val[v][w.slotL()] = sL[v]; w.val[v][w.slotR()] = sR[v]; }
-      for (int v = 0; v < Q; ++v) w.diamondGrad(v);
-      w.mu = d.faceMu[f];
-      w.lambda = P::thermConductivity(c, w.mu);
-    }
-    typename P::Side fixed, pert;
-    P::side(c, side == 0 ? vR : vL, w.n, fixed);
-    double* vP = side == 0 ? vL : vR;
-    const double* sP = side == 0 ? sL : sR;
-    const double* gP = side == 0 ? w.gL : w.gR;
-    const int slot = side == 0 ? w.slotL() : w.slotR();
-    // both updatable: rows L and R get +rf and -rf; one side only: row idx gets (-1)^idx * rf
-    // (FVMCC_ComputeRhsJacob.cxx:184-236).  Stored block = what row "other" receives.
-    const double rf = c.resFactor;
-    for (int iVar = 0; iVar < Q; ++iVar) {
-      const double orig = sP[iVar];
-      const double eps = fdEps(c, iVar, orig);
-      const double pv = orig + eps;
-      const double keep = vP[iVar];
-      vP[iVar] = (c.polyRec == CFB200_PR_CONSTANT) ? pv : pv + gP[iVar];   // LeastSquareP1PolyRec2D.cxx:221-262
-      P::side(c, vP, w.n, pert);
-      double pf[Q];
-      bool ok = (side == 0) ? P::roe(c, pert, fixed, w.n, pf) : P::roe(c, fixed, pert, w.n, pf);
-      if (!ok) { *d.status = CFB200_ERR_BAD_VALUE; for (int v = 0; v < Q; ++v) pf[v] = 0.; }
-      for (int v = 0; v < Q; ++v) pf[v] *= w.area;
-      if (hasDiff) {
-        const double keepVal = w.val[iVar][slot];
-        double keepGrad[3];
-        for (int k = 0; k < 3; ++k) keepGrad[k] = w.grad[iVar][k];
-        w.val[iVar][slot] = pv;
-        w.diamondGrad(iVar);
-        double dflux[Q];
-        w.diffFlux(c, dflux);
-        for (int v = 0; v < Q; ++v) pf[v] -= dflux[v];
-        w.val[iVar][slot] = keepVal;
-        for (int k = 0; k < 3; ++k) w.grad[iVar][k] = keepGrad[k];
-      }
-      const double invEps = 1./eps;
-      for (int v = 0; v < Q; ++v) {
-        double fd = (pf[v] - flux[v])*invEps;
-        fd *= rf;                              // what row L receives
-        blk[v*Q + iVar] = (side == 0) ? fd*(-1.0) : fd;
-      }
-      vP[iVar] = keep;
-    }
-  }
-};
-
-// Boundary faces: FVMCC_ComputeRhsJacob.cxx:240-317.  The inner state is perturbed, the ghost state is rebuilt
-// by the boundary condition, both sides are re-extrapolated, and resFactor * dF/dU_L goes to the diagonal block.
-template <int D>
-struct JacBoundary {   // idx over boundary faces
-  Dev d; Cfg c;
-  CFB_HD void operator()(int g) const {
-    constexpr int Q = D + 2;
-    typedef Phys<D> P;
-    const int f = d.nInner + g;
-    FaceWork<D> w;
-    w.loadGeom(d, f);
-    double* blk = &d.bndBlocks[(size_t)g*Q*Q];
-    if (!d.updatable[w.L]) { for (int k = 0; k < Q*Q; ++k) blk[k] = 0.; return; }
-    double sL[Q], sR[Q], vL[Q], vR[Q], flux[Q], nr[D];
-    for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + w.L]; flux[v] = d.faceFlux[(size_t)v*d.nFaces + f]; }
-    for (int k = 0; k < D; ++k) nr[k] = d.normals[(size_t)k*d.nFaces + f];
-    const BCond& bc = d.bcs[d.faceBC[f]];
-    const bool hasDiff = (c.diffusive == CFB200_DIFF_NS);
-    if (hasDiff) {
-      w.loadDiamond(d);
-      w.mu = d.faceMu[f];
-      w.lambda = P::thermConductivity(c, w.mu);
-    }
-    // the reconstruction increments use the inner cell's gradient for both sides and do not depend on the states
-    w.loadReconstruction(d, c);
-    const double rf = c.resFactor;
-    for (int iVar = 0; iVar < Q; ++iVar) {
-      const double orig = sL[iVar];
-      const double eps = fdEps(c, iVar, orig);
-      sL[iVar] = orig + eps;
-      ghostState<D>(c, bc, nr, sL, sR);
-      w.reconstruct(c, sL, sR, vL, vR);
-      typename P::Side a, b;
-      P::side(c, vL, w.n, a);
-      P::side(c, vR, w.n, b);
-      double pf[Q];
-      if (!P::roe(c, a, b, w.n, pf)) { *d.status = CFB200_ERR_BAD_VALUE; for (int v = 0; v < Q; ++v) pf[v] = 0.; }
-      for (int v = 0; v < Q; ++v) pf[v] *= w.area;
-      if (hasDiff) {
-        for (int v = 0; v < Q; ++v) { w.val[v][w.slotL()] = sL[v]; w.val[v][w.slotR()] = sR[v]; }
-        for (int v = 0; v < Q; ++v) w.diamondGrad(v);
-        double dflux[Q];
-        w.diffFlux(c, dflux);
-        for (int v = 0; v < Q; ++v) pf[v] -= dflux[v];
-      }
-      const double invEps = 1./eps;
-      for (int v = 0; v < Q; ++v) {
-        double fd = (pf[v] - flux[v])*invEps;
-        fd *= rf;
-        blk[v*Q + iVar] = fd;
-      }
-      sL[iVar] = orig;
-    }
   }
 };
 
@@ -793,7 +447,7 @@ struct TimeRhs {   // idx over cells
 };
 
 // ------------------------------------------------------------------------------------------------
-// §8f-1: ForwardEuler UpdateSol.cxx:83-193 on the device: dt = CFL/updateCoeff, rhs *= dt (in place), U += rhs,
+// §8f-1: ForwardEuler UpdateSol.cxx:83-193 on the device: dt = CFL/updateCoeff, U += rhs*dt (rhs itself is left unscaled),
 // updateCoeff = 0; per-cell squared dU[monitorVar] goes to `partial` for the ordered norm reduction.
 template <int D>
 struct UpdateSolFwdEuler {   // idx over cells
@@ -808,12 +462,10 @@ struct UpdateSolFwdEuler {   // idx over cells
       const bool isZero = fabs(uc) <= 2.2250738585072014e-308;
       const double dt = isZero ? 0. : cfl/uc;
       for (int v = 0; v < Q; ++v) {
-        double r = d.rhs[(size_t)cell*Q + v];
-        r *= dt;
-        d.rhs[(size_t)cell*Q + v] = r;
-        d.U[(size_t)v*d.nStates + cell] += r;
+        double rhsState = d.rhs[(size_t)cell*Q + v];     // a copy: the rhs socket itself is NOT scaled (UpdateSol.cxx:176-177)
+        d.U[(size_t)v*d.nStates + cell] += rhsState *= dt;
       }
-      const double t = d.rhs[(size_t)cell*Q + monitorVar];
+      const double t = d.rhs[(size_t)cell*Q + monitorVar]; // ComputeL2Norm.cxx:111-125 on the rhs socket
       sq = t*t;
     }
     d.updateCoeff[cell] = 0.0;
