@@ -3,6 +3,7 @@
 // execution path in this library: without a usable CUDA device cfb200_create returns CFB200_ERR_NO_DEVICE.
 #include <cuda_runtime.h>
 #include <cstdio>
+#include <cstdlib>
 #include <cmath>
 #include <string>
 #include <vector>
@@ -13,8 +14,8 @@ namespace cfb {
 #define CFB_CUDA(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
   throw DeviceError(CFB200_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
 
-template <class F, int BS>
-__global__ void __launch_bounds__(BS) k_run(const F f, const int n) {
+template <class F, int BS, int MINB>
+__global__ void __launch_bounds__(BS, MINB) k_run(const F f, const int n) {
   const int i = blockIdx.x*BS + threadIdx.x;
   if (i < n) f(i);
 }
@@ -94,8 +95,12 @@ struct CudaBackend {
       ev = &evs[nEv++]; ev->name = name;
       CFB_CUDA(cudaEventRecord(ev->a, stream));
     }
-    if (bs == 128) k_run<F, 128><<<(n + 127)/128, 128, 0, stream>>>(f, n);
-    else k_run<F, 256><<<(n + 255)/256, 256, 0, stream>>>(f, n);
+    // bs encodes the launch shape: 256 -> 256 threads; 128 -> 128 threads, >= 2 blocks/SM (<= 255 registers);
+    // 1283 / 1284 -> 128 threads with >= 3 / 4 resident blocks per SM (<= 168 / 128 registers)
+    if (bs == 1283) k_run<F, 128, 3><<<(n + 127)/128, 128, 0, stream>>>(f, n);
+    else if (bs == 1284) k_run<F, 128, 4><<<(n + 127)/128, 128, 0, stream>>>(f, n);
+    else if (bs == 128) k_run<F, 128, 2><<<(n + 127)/128, 128, 0, stream>>>(f, n);
+    else k_run<F, 256, 1><<<(n + 255)/256, 256, 0, stream>>>(f, n);
     CFB_CUDA(cudaGetLastError());
     if (ev) CFB_CUDA(cudaEventRecord(ev->b, stream));
   }

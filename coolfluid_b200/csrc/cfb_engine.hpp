@@ -34,6 +34,7 @@ public:
   int nNonUpd = 0;
   bool meshSet = false, statesSet = false;
   int lastStatus = 0;
+  int faceShape = 128;     // launch shape of the interior-face Jacobian kernel (see CudaBackend::launch)
   std::vector<void*> owned;
   int* nonUpdCells = nullptr;
   std::vector<int32_t> hRowPtr, hColInd;
@@ -231,7 +232,7 @@ public:
     if (cfg.polyRec == CFB200_PR_LINEARLS && cfg.limiter != CFB200_LIM_NONE)
       bk.launch("limiter", LimiterK<D>{d, cfg}, d.nCells, 128);
     if (doJac) {
-      bk.launch("innerFaceJac", InnerFaceK<D, true>{d, cfg}, d.nInner, 128);
+      bk.launch("innerFaceJac", InnerFaceK<D, true>{d, cfg}, d.nInner, faceShape);
       bk.launch("boundaryFaceJac", BoundaryFaceK<D, true>{d, cfg}, d.nGhosts, 128);
     } else {
       bk.launch("innerFace", InnerFaceK<D, false>{d, cfg}, d.nInner, 128);

@@ -33,7 +33,7 @@ struct FaceWork {
 
   // a8: LeastSquareP1PolyRec2D.cxx:158-217, 3D.cxx:204-268.  Boundary faces use the INNER cell's gradient
   // and limiter for the ghost side (reference behaviour).  Also loads the unit normal (FVMCC_ComputeRHS.cxx:518-534).
-  CFB_HD void load(const Dev& d, const Cfg& c, int face, bool withDiamond) {
+  CFB_HD void load(const Dev& d, const Cfg& c, int face) {
     f = face; L = d.faceL[f]; R = d.faceR[f]; isB = (R >= d.nCells);
     area = d.areas[f];
     const double invArea = 1./area;
@@ -74,7 +74,6 @@ struct FaceWork {
         gR[v] = rValue*gcN;
       }
     }
-    if (withDiamond) loadDiamond(d, xL, xR);
   }
 
   CFB_HD void reconstruct(const Cfg& c, const double* sL, const double* sR, double* vL, double* vR) const {
@@ -98,7 +97,10 @@ struct FaceWork {
 
   // a15: control volume of the face, DiamondVolume2DDerivative.cxx:91-137, DiamondVolume3DDerivative.cxx:336-411,
   // and the nodal part of the control-volume states.
-  CFB_HD void loadDiamond(const Dev& d, const double* xL, const double* xR) {
+  CFB_HD void loadDiamond(const Dev& d) {
+    double xL[3] = {0., 0., 0.}, xR[3] = {0., 0., 0.};
+#pragma unroll
+    for (int k = 0; k < D; ++k) { xL[k] = d.centres[(size_t)k*d.nStates + L]; xR[k] = d.centres[(size_t)k*d.nStates + R]; }
     const int b = d.faceNodePtr[f];
     nbN = d.faceNodePtr[f+1] - b;
     double xn[NMAX][3];
@@ -219,6 +221,7 @@ struct FaceWork {
     for (int v = 0; v < Q; ++v) flux[v] *= area;        // FVMCC_FluxSplitter.hh:79-83
     ucD = 0.;
     if (hasDiff) {
+      loadDiamond(d);          // only now: the diamond working set must not be live across the Roe evaluation
       setCellStates(sL, sR);
       allGrads();
       transport(c);
@@ -231,12 +234,149 @@ struct FaceWork {
     }
   }
 
-  // a18: FVMCC_ComputeRhsJacob.cxx:126-236,321-365.  Perturbs the q variables of the SIDE cell in turn, re-evaluates
-  // the convective + diffusive flux with frozen gradient/limiter (LeastSquareP1PolyRec2D.cxx:221-262), and writes
-  // column iVar of   blk = sgn * resFactor * dF/dU_SIDE   (row-major q x q, BlockAccumulator.hh:289-296).
+  // ---- interior faces: ONE rolled loop body serves the base evaluation and all 2q perturbations (code size) -------
+  // Diffusive part first: base diffusive flux + ucD, then (JAC) the 2q perturbed diffusive fluxes staged into the
+  // two output blocks (column iVar of blkRL for side L, of blkLR for side R).
+  CFB_HD void innerDiffusive(const Dev& d, const Cfg& c, const double* sL, const double* sR, bool jac,
+                             double* dfluxBase, double& ucD, double* blkRL, double* blkLR) {
+    loadDiamond(d);
+    setCellStates(sL, sR);
+    allGrads();
+    transport(c);
+    diffFlux(c, grad, dfluxBase);
+    const double nu = mu/P::density(c, avState);      // NSFlux.ci:127-152
+    ucD = nu*area*area/volume;
+    if (!jac) return;
+#pragma unroll 1
+    for (int it = 0; it < 2*Q; ++it) {
+      const int side = (it >= Q) ? 1 : 0;
+      const int iVar = it - side*Q;
+      double orig = sL[0];
+#pragma unroll
+      for (int v = 0; v < Q; ++v) { if (side == 0 && iVar == v) orig = sL[v]; if (side == 1 && iVar == v) orig = sR[v]; }
+      const double pv = orig + fdEps(c, iVar, orig);
+      double a[6], gr[3];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        double r = val[0][j];
+#pragma unroll
+        for (int v = 1; v < Q; ++v) if (iVar == v) r = val[v][j];
+        a[j] = r;
+      }
+      if (side == 0) a[4] = pv; else a[5] = pv;  // the control volume holds the CELL state, not the reconstructed one
+      gradRow(a, gr);
+      double g2[Q][3];
+#pragma unroll
+      for (int v = 0; v < Q; ++v)
+#pragma unroll
+        for (int k = 0; k < 3; ++k) g2[v][k] = (v == iVar) ? gr[k] : grad[v][k];
+      double dflux[Q];
+      diffFlux(c, g2, dflux);
+      double* blk = side ? blkLR : blkRL;
+#pragma unroll
+      for (int v = 0; v < Q; ++v) blk[v*Q + iVar] = dflux[v];
+    }
+  }
+
+  // Convective part: it = -1 is the base evaluation (-> flux, faceFlux), it = 0..2q-1 perturbs variable it%q of side
+  // it/q (FVMCC_ComputeRhsJacob.cxx:126-236,321-365; frozen gradient/limiter, LeastSquareP1PolyRec2D.cxx:221-262):
+  //   pf = F_c*area - staged F_d ;  column <- sgn * resFactor * (pf - flux)/eps  (row-major q x q, BlockAccumulator.hh:289-296)
+  CFB_HD void innerConvective(const Dev& d, const Cfg& c, const double* sL, const double* sR, const double* vL,
+                              const double* vR, bool hasDiff, const double* dfluxBase, bool jac,
+                              double* flux, double* blkRL, double* blkLR) const {
+    const double rf = c.resFactor;
+    typename P::SideLite fixed;
+    const int last = jac ? 2*Q : 0;
+#pragma unroll 1
+    for (int it = -1; it < last; ++it) {
+      const int side = (it >= Q) ? 1 : 0;
+      const int iVar = it - side*Q;                // -1 for the base evaluation
+      if (it == -1 || it == Q) {
+        double vF[Q];
+#pragma unroll
+        for (int v = 0; v < Q; ++v) vF[v] = side ? vL[v] : vR[v];
+        P::sideLite(c, vF, n, fixed);              // the unperturbed other side
+      }
+      double orig = 0., gp = 0.;
+#pragma unroll
+      for (int v = 0; v < Q; ++v) {
+        if (side == 0 && iVar == v) { orig = sL[v]; gp = gL[v]; }
+        if (side == 1 && iVar == v) { orig = sR[v]; gp = gR[v]; }
+      }
+      const double eps = (iVar >= 0) ? fdEps(c, iVar, orig) : 1.0;
+      const double pv = orig + eps;
+      const double pvr = (c.polyRec == CFB200_PR_CONSTANT) ? pv : pv + gp;
+      double vp[Q];
+#pragma unroll
+      for (int v = 0; v < Q; ++v) { const double base = side ? vR[v] : vL[v]; vp[v] = (v == iVar) ? pvr : base; }
+      typename P::SideLite pert;
+      P::sideLite(c, vp, n, pert);
+      double pf[Q];
+      if (!P::roeOriented(c, pert, fixed, side == 0, n, pf)) {
+        *d.status = CFB200_ERR_BAD_VALUE;
+#pragma unroll
+        for (int v = 0; v < Q; ++v) pf[v] = 0.;
+      }
+      if (iVar < 0) {
+#pragma unroll
+        for (int v = 0; v < Q; ++v) {
+          pf[v] *= area;                            // FVMCC_FluxSplitter.hh:79-83
+          if (hasDiff) pf[v] -= dfluxBase[v];       // FVMCC_ComputeRHS.cxx:260-276
+          flux[v] = pf[v];
+          d.faceFlux[(size_t)v*d.nFaces + f] = pf[v];
+        }
+      } else {
+        double* blk = side ? blkLR : blkRL;
+        const double invEps = 1./eps;
+#pragma unroll
+        for (int v = 0; v < Q; ++v) {
+          pf[v] *= area;
+          if (hasDiff) pf[v] -= blk[v*Q + iVar];
+          double fd = (pf[v] - flux[v])*invEps;
+          fd *= rf;                                 // what row L receives (upFactor[0])
+          blk[v*Q + iVar] = side ? fd : fd*(-1.0);  // block(R,L) is what row R receives: upFactor[1] = -1 times that
+        }
+      }
+    }
+  }
+
+  // a18 (boundary-kernel helpers, kept per side): FVMCC_ComputeRhsJacob.cxx:126-236,321-365.
+  // Done in two passes over the perturbed variables so that the diamond-volume working set (24 normals, 30 control
+  // volume values, 15 gradients) and the Roe working set are never live in registers at the same time:
+  //   diffPass : column iVar of blk <- perturbed diffusive flux (staging, same thread reads it back)
+  //   convPass : perturbed convective flux, pf = F_c*area - staged F_d, then
+  //              blk column <- sgn * resFactor * (pf - flux)/eps   (row-major q x q, BlockAccumulator.hh:289-296)
   template <int SIDE>
-  CFB_HD void perturbSide(const Dev& d, const Cfg& c, const double* sP, const double* vBase,
-                          const typename P::Side& fixed, const double* flux, bool hasDiff, bool negate, double* blk) const {
+  CFB_HD void diffPass(const Cfg& c, const double* sP, double* blk) const {
+#pragma unroll 1
+    for (int iVar = 0; iVar < Q; ++iVar) {
+      const double orig = pick<Q>(sP, iVar);
+      const double pv = orig + fdEps(c, iVar, orig);
+      double a[6], gr[3];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        double r = val[0][j];
+#pragma unroll
+        for (int v = 1; v < Q; ++v) if (iVar == v) r = val[v][j];
+        a[j] = r;
+      }
+      a[4 + SIDE] = pv;                        // the control volume holds the CELL state, not the reconstructed one
+      gradRow(a, gr);
+      double g2[Q][3];
+#pragma unroll
+      for (int v = 0; v < Q; ++v)
+#pragma unroll
+        for (int k = 0; k < 3; ++k) g2[v][k] = (v == iVar) ? gr[k] : grad[v][k];
+      double dflux[Q];
+      diffFlux(c, g2, dflux);
+#pragma unroll
+      for (int v = 0; v < Q; ++v) blk[v*Q + iVar] = dflux[v];
+    }
+  }
+
+  template <int SIDE>
+  CFB_HD void convPass(const Dev& d, const Cfg& c, const double* sP, const double* vBase,
+                       const typename P::Side& fixed, const double* flux, bool hasDiff, bool negate, double* blk) const {
     const double rf = c.resFactor;
 #pragma unroll 1
     for (int iVar = 0; iVar < Q; ++iVar) {
@@ -256,32 +396,11 @@ struct FaceWork {
 #pragma unroll
         for (int v = 0; v < Q; ++v) pf[v] = 0.;
       }
-#pragma unroll
-      for (int v = 0; v < Q; ++v) pf[v] *= area;
-      if (hasDiff) {
-        double a[6], gr[3];
-#pragma unroll
-        for (int j = 0; j < 6; ++j) {
-          double r = val[0][j];
-#pragma unroll
-          for (int v = 1; v < Q; ++v) if (iVar == v) r = val[v][j];
-          a[j] = r;
-        }
-        a[4 + SIDE] = pv;                        // the control volume holds the CELL state, not the reconstructed one
-        gradRow(a, gr);
-        double g2[Q][3];
-#pragma unroll
-        for (int v = 0; v < Q; ++v)
-#pragma unroll
-          for (int k = 0; k < 3; ++k) g2[v][k] = (v == iVar) ? gr[k] : grad[v][k];
-        double dflux[Q];
-        diffFlux(c, g2, dflux);
-#pragma unroll
-        for (int v = 0; v < Q; ++v) pf[v] -= dflux[v];
-      }
       const double invEps = 1./eps;
 #pragma unroll
       for (int v = 0; v < Q; ++v) {
+        pf[v] *= area;
+        if (hasDiff) pf[v] -= blk[v*Q + iVar];
         double fd = (pf[v] - flux[v])*invEps;
         fd *= rf;                                // what row L receives (upFactor[0])
         blk[v*Q + iVar] = negate ? fd*(-1.0) : fd;   // row R receives upFactor[1] = -1 times that
@@ -316,23 +435,31 @@ struct InnerFaceK {   // idx over interior faces
       return;
     }
     FaceWork<D> w;
-    w.load(d, c, f, hasDiff);
+    w.load(d, c, f);
     double sL[Q], sR[Q], vL[Q], vR[Q], flux[Q];
 #pragma unroll
     for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + L]; sR[v] = d.U[(size_t)v*d.nStates + R]; }
     w.reconstruct(c, sL, sR, vL, vR);
-    typename P::Side a, b;
-    P::side(c, vL, w.n, a);
-    P::side(c, vR, w.n, b);
-    double ucL, ucR, ucD;
-    w.baseFlux(d, c, sL, sR, a, b, hasDiff, flux, ucL, ucR, ucD);
-    d.ucL[f] = ucL; d.ucR[f] = ucR; d.ucD[f] = ucD;
+    double* blkRL = JAC ? &d.bsrVal[(size_t)d.slotRL[f]*Q*Q] : nullptr;
+    double* blkLR = JAC ? &d.bsrVal[(size_t)d.slotLR[f]*Q*Q] : nullptr;
+    {
+      // update coefficients, RoeFlux.cxx:165-185 (one quadrature point per face)
+      PData pL, pR;
+      P::physicalData(c, vL, pL);
+      P::physicalData(c, vR, pR);
+      const double faceArea = w.area/1;
+      d.ucL[f] = dmax(P::maxEigenValue(pL, w.n), 0.)*faceArea;
+      double tn[3];
 #pragma unroll
-    for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = flux[v];
-    if (JAC) {
-      w.template perturbSide<0>(d, c, sL, vL, b, flux, hasDiff, true, &d.bsrVal[(size_t)d.slotRL[f]*Q*Q]);
-      w.template perturbSide<1>(d, c, sR, vR, a, flux, hasDiff, false, &d.bsrVal[(size_t)d.slotLR[f]*Q*Q]);
+      for (int k = 0; k < 3; ++k) tn[k] = -1.0*w.n[k];
+      d.ucR[f] = dmax(P::maxEigenValue(pR, tn), 0.)*faceArea;
     }
+    double dfluxBase[Q], ucD = 0.;
+#pragma unroll
+    for (int v = 0; v < Q; ++v) dfluxBase[v] = 0.;
+    if (hasDiff) w.innerDiffusive(d, c, sL, sR, JAC, dfluxBase, ucD, blkRL, blkLR);
+    d.ucD[f] = ucD;
+    w.innerConvective(d, c, sL, sR, vL, vR, hasDiff, dfluxBase, JAC, flux, blkRL, blkLR);
   }
 };
 
@@ -357,7 +484,7 @@ struct BoundaryFaceK {   // idx over boundary faces
       return;
     }
     FaceWork<D> w;
-    w.load(d, c, f, hasDiff);
+    w.load(d, c, f);
     double sL[Q], sR[Q], vL[Q], vR[Q], flux[Q];
 #pragma unroll
     for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + L]; sR[v] = d.U[(size_t)v*d.nStates + R]; }
