@@ -158,3 +158,25 @@ def test_large_size_properties(product_lib):
     scale = np.abs(jac).max()
     assert np.abs(colsum[interior]).max() <= 1e-12*scale
     e.close()
+
+
+def test_cuda_matches_committed_golden_vectors(product_lib):
+    """The CUDA path against tests/golden/cases.npz (vectors generated by tests/golden/make_golden.py): no oracle
+    run involved on the GPU box."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cases.npz"))
+    for name in sorted(cases.CASES):
+        mesh_f, cfg_f, bcs_f, pvt = cases.CASES[name]
+        fm = cl.build_mesh(mesh_f(), product_lib)
+        c = cfg_f()
+        U = cases.init_state(fm, c.nEqs, pvt)
+        uc0 = 0.1*np.arange(fm.nCells, dtype=np.float64)/max(fm.nCells, 1)
+        e = cl.Engine(c, 0, lib=product_lib)
+        e.set_mesh(fm, bcs_f())
+        e.set_states(U[:fm.nCells*c.nEqs])
+        e.set_update_coeff(uc0)
+        rhs, uc = e.compute_rhs()
+        got = {"rhs": rhs, "updateCoeff": uc, "limiter": e.field("limiter"), "jacobian": e.bsr_values()}
+        e.close()
+        for k, a in got.items():
+            assert cases.relerr(a, g[name + "/" + k]) <= TOL, (name, k)
