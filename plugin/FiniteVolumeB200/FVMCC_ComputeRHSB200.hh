@@ -1,0 +1,51 @@
+// FVMCC_ComputeRHSB200 — drop-in ComputeRHS command: selects the B200 engine from a .CFcase with
+//   Simulator.Modules.Libs = ... libFiniteVolume libFiniteVolumeNavierStokes libFiniteVolumeB200
+//   Simulator.SubSystem.CellCenterFVM.ComputeRHS = B200Rhs          (explicit)   | B200RhsJacob (implicit)
+//   Simulator.SubSystem.CellCenterFVM.B200RhsJacob.Device = 0        (default: rank % deviceCount)
+// It derives from FVMCC_ComputeRHS (as plugins/FiniteVolumeCUDA/FVMCC_ComputeRHSCell.hh:31 does) to inherit the
+// sockets and the configured strategies, copies socket data to libcfb200 once in setup(), and in execute() sends
+// the states, runs the device evaluation and leaves rhs / updateCoeff valid on the host (callers read them right
+// away: UpdateSol.cxx:83, FVMCC_PseudoSteadyTimeRhs.cxx:106).  The block Jacobian is inserted in the LSS matrix.
+#ifndef COOLFluiD_Numerics_FiniteVolume_FVMCC_ComputeRHSB200_hh
+#define COOLFluiD_Numerics_FiniteVolume_FVMCC_ComputeRHSB200_hh
+
+#include "FiniteVolume/FVMCC_ComputeRHS.hh"
+#include "Framework/BlockAccumulator.hh"
+#include "cfb200.h"
+
+namespace COOLFluiD { namespace Numerics { namespace FiniteVolume {
+
+class FVMCC_ComputeRHSB200 : public FVMCC_ComputeRHS {
+public:
+  explicit FVMCC_ComputeRHSB200(const std::string& name);
+  virtual ~FVMCC_ComputeRHSB200();
+  static void defineConfigOptions(Config::OptionList& options);
+  virtual void configure(Config::ConfigArgs& args);
+  virtual void setup();
+  virtual void unsetup();
+  virtual void execute();
+
+protected:
+  /// true for the "B200RhsJacob" provider
+  virtual bool withJacobian() const { return false; }
+  void fillConfig(cfb200_config& c);
+  void uploadMesh();
+  void insertJacobian();
+  void check(int rc, const char* what);
+
+  cfb200_handle* m_h;
+  CFint m_device;          ///< option Device (-1: rank % device count, as CudaDeviceManager.cu:58)
+  bool m_hostJacobian;     ///< option HostJacobian: copy the BSR back and MatSetValuesBlocked (CPU PETSc); else device view
+  std::vector<CFreal> m_gstates, m_bsr;
+  std::vector<CFint> m_rowPtr, m_colInd;
+};
+
+class FVMCC_ComputeRhsJacobB200 : public FVMCC_ComputeRHSB200 {
+public:
+  explicit FVMCC_ComputeRhsJacobB200(const std::string& name) : FVMCC_ComputeRHSB200(name) {}
+protected:
+  virtual bool withJacobian() const { return true; }
+};
+
+} } }
+#endif
