@@ -20,6 +20,29 @@ __global__ void __launch_bounds__(BS, MINB) k_run(const F f, const int n) {
   if (i < n) f(i);
 }
 
+// One item per thread with a per-thread staging area in shared memory (entry k of thread t at sm[k*(BS+1) + t]: conflict
+// free for the thread's own accesses AND for the warp's transposed read-out below).  After the item is evaluated the warp
+// writes its 32 x 2 finished blocks to their BSR slots, F::BLK contiguous doubles at a time (coalesced), instead of 8-byte
+// scattered stores.  No block-wide barrier: warps stay independent.
+template <class F, int BS, int MINB>
+__global__ void __launch_bounds__(BS, MINB) k_staged(const F f, const int n) {
+  extern __shared__ double sm[];
+  constexpr int STRIDE = BS + 1;
+  const int t = threadIdx.x, lane = t & 31, warpBase = t & ~31;
+  const int i = blockIdx.x*BS + t;
+  int s0 = -1, s1 = -1;
+  if (i < n) { f.run(i, sm + t, STRIDE); f.slots(i, s0, s1); }
+  __syncwarp();
+  double* out = f.out();
+  for (int e = lane; e < 32*F::NOUT; e += 32) {
+    const int lf = e/F::NOUT, k = e - lf*F::NOUT;
+    const int sel = k/F::BLK, kk = k - sel*F::BLK;
+    const int a0 = __shfl_sync(0xffffffffu, s0, lf), a1 = __shfl_sync(0xffffffffu, s1, lf);
+    const int slot = sel ? a1 : a0;
+    if (slot >= 0) out[(size_t)slot*F::BLK + kk] = sm[k*STRIDE + warpBase + lf];
+  }
+}
+
 // fixed-shape block sum (run-to-run deterministic): each block reduces 1024 consecutive entries
 __global__ void __launch_bounds__(256) k_block_sum(const double* __restrict__ x, double* __restrict__ out, int n) {
   __shared__ double s[256];
@@ -105,6 +128,28 @@ struct CudaBackend {
     if (ev) CFB_CUDA(cudaEventRecord(ev->b, stream));
   }
 
+  // 128-thread blocks with F::STAGE doubles of shared-memory staging per thread; minBlocks = resident blocks per SM
+  template <class F> void launchStaged(const char* name, const F& f, int n, int minBlocks) {
+    if (n <= 0) return;
+    Ev* ev = nullptr;
+    if (timing) {
+      if (nEv == evs.size()) { Ev e; e.name = name; CFB_CUDA(cudaEventCreate(&e.a)); CFB_CUDA(cudaEventCreate(&e.b)); evs.push_back(e); }
+      ev = &evs[nEv++]; ev->name = name;
+      CFB_CUDA(cudaEventRecord(ev->a, stream));
+    }
+    constexpr int BS = 128;
+    const size_t smem = (size_t)F::STAGE*(BS + 1)*sizeof(double);
+    auto go = [&](auto kern) {
+      CFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      kern<<<(n + BS - 1)/BS, BS, smem, stream>>>(f, n);
+    };
+    if (minBlocks <= 2) go(k_staged<F, BS, 2>);
+    else if (minBlocks == 3) go(k_staged<F, BS, 3>);
+    else go(k_staged<F, BS, 4>);
+    CFB_CUDA(cudaGetLastError());
+    if (ev) CFB_CUDA(cudaEventRecord(ev->b, stream));
+  }
+
   // sum of x[0..n) with a fixed reduction shape; x must have >= ceil(n/1024) doubles of scratch after position n
   double sumOrdered(double* x, int n) {
     if (n <= 0) return 0.;
@@ -140,7 +185,61 @@ typedef cfb::CudaBackend BackendT;
 #define CFB_FN(x) cfb200_##x
 #include "cfb_capi.inc"
 
+// ---- self test of the branch-free divide / square root (cfb_math.cuh) against the compiler's IEEE `/` and sqrt() ----
+namespace cfb {
+__device__ __forceinline__ unsigned long long splitmix(unsigned long long x) {
+  x += 0x9e3779b97f4a7c15ull; x = (x ^ (x >> 30))*0xbf58476d1ce4e5b9ull; x = (x ^ (x >> 27))*0x94d049bb133111ebull; return x ^ (x >> 31);
+}
+// operand with a random 52-bit significand, random sign and an exponent uniform in [-span, span]
+__device__ __forceinline__ double randOperand(unsigned long long h, int span) {
+  const unsigned long long mant = h & 0x000fffffffffffffull;
+  const int e = (int)((h >> 52) % (unsigned)(2*span + 1)) - span;
+  const unsigned long long sign = (h >> 63) << 63;
+  return __longlong_as_double((long long)(sign | ((unsigned long long)(1023 + e) << 52) | mant));
+}
+__global__ void k_selftest_divsqrt(unsigned long long seed, long long n, int span, unsigned long long* bad) {
+  const long long i = (long long)blockIdx.x*blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const unsigned long long h0 = splitmix(seed + 3ull*i), h1 = splitmix(seed + 3ull*i + 1), h2 = splitmix(seed + 3ull*i + 2);
+  double a = randOperand(h0, span), b = randOperand(h1, span);
+  if ((h2 & 1023) == 0) a = 0.0;
+  if ((h2 & 1023) == 1) a = -0.0;
+  if ((h2 & 1023) == 2) a = b;                       // exact quotients
+  if ((h2 & 1023) == 3) b = (double)(1 + (h2 >> 40) % 1000);
+  unsigned long long nbad = 0;
+  const Recip r = recipOf(b);
+  const double q0 = a/b, q1 = divBy(a, r);
+  if (__double_as_longlong(q0) != __double_as_longlong(q1)) ++nbad;
+  const double c = a*1.0000001 + b;                  // a second numerator for the shared reciprocal
+  const double q2 = c/b, q3 = divBy(c, r);
+  if (__double_as_longlong(q2) != __double_as_longlong(q3)) ++nbad;
+  const double o0 = 1.0/b, o1 = ddiv(1.0, b);
+  if (__double_as_longlong(o0) != __double_as_longlong(o1)) ++nbad;
+  const double x = fabs(a);
+  const double s0 = sqrt(x), s1 = dsqrt(x);
+  if (__double_as_longlong(s0) != __double_as_longlong(s1)) ++nbad;
+  if (nbad) atomicAdd(bad, nbad);
+}
+}
+
 extern "C" {
+
+int cfb200_selftest_divsqrt(int device, int64_t n, uint64_t seed, int exponentSpan, int64_t* mismatches) {
+  if (!mismatches || n <= 0 || exponentSpan < 0 || exponentSpan > 480) return CFB200_ERR_INVALID_ARG;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) { cudaGetLastError(); return CFB200_ERR_NO_DEVICE; }
+  if (cudaSetDevice(device) != cudaSuccess) return CFB200_ERR_INVALID_ARG;
+  unsigned long long* d = nullptr;
+  if (cudaMalloc((void**)&d, 8) != cudaSuccess) return CFB200_ERR_CUDA;
+  cudaMemset(d, 0, 8);
+  cfb::k_selftest_divsqrt<<<(unsigned)((n + 255)/256), 256>>>(seed, n, exponentSpan, d);
+  unsigned long long h = 0;
+  const cudaError_t e = cudaMemcpy(&h, d, 8, cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  if (e != cudaSuccess) return CFB200_ERR_CUDA;
+  *mismatches = (int64_t)h;
+  return CFB200_OK;
+}
 
 int cfb200_abi_version(void) { return CFB200_ABI_VERSION; }
 

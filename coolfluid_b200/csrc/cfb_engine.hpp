@@ -34,8 +34,8 @@ public:
   int nNonUpd = 0;
   bool meshSet = false, statesSet = false;
   int lastStatus = 0;
-  int faceShape = 1283;    // launch shape of the interior-face Jacobian kernel (see CudaBackend::launch):
-                           // 128 threads, 3 blocks/SM (168 registers) measured fastest on B200 (profiles/)
+  int faceShape = 2;       // resident 128-thread blocks per SM the interior-face Jacobian kernel is compiled for
+                           // (CudaBackend::launchStaged): 2 -> 255 registers, no spills: measured fastest on B200 (profiles/)
   std::vector<void*> owned;
   int* nonUpdCells = nullptr;
   std::vector<int32_t> hRowPtr, hColInd;
@@ -233,7 +233,7 @@ public:
     if (cfg.polyRec == CFB200_PR_LINEARLS && cfg.limiter != CFB200_LIM_NONE)
       bk.launch("limiter", LimiterK<D>{d, cfg}, d.nCells, 128);
     if (doJac) {
-      bk.launch("innerFaceJac", InnerFaceK<D, true>{d, cfg}, d.nInner, faceShape);
+      bk.launchStaged("innerFaceJac", InnerFaceK<D, true>{d, cfg}, d.nInner, faceShape);
       bk.launch("boundaryFaceJac", BoundaryFaceK<D, true>{d, cfg}, d.nGhosts, 128);
     } else {
       bk.launch("innerFace", InnerFaceK<D, false>{d, cfg}, d.nInner, 128);

@@ -36,7 +36,7 @@ struct FaceWork {
   CFB_HD void load(const Dev& d, const Cfg& c, int face) {
     f = face; L = d.faceL[f]; R = d.faceR[f]; isB = (R >= d.nCells);
     area = d.areas[f];
-    const double invArea = 1./area;
+    const double invArea = ddiv(1., area);
     double xq[3] = {0., 0., 0.}, xL[3] = {0., 0., 0.}, xR[3] = {0., 0., 0.};
     n[2] = 0.;
 #pragma unroll
@@ -158,14 +158,14 @@ struct FaceWork {
   // DiamondVolume2DDerivative.cxx:139-176, DiamondVolume3DDerivative.cxx:190-298
   CFB_HD void gradRow(const double* a, double* g) const {
     if constexpr (D == 2) {
-      const double invVolume = 0.5/volume;
+      const double invVolume = ddiv(0.5, volume);
       const double v01 = a[0] + a[4], v12 = a[4] + a[1], v23 = a[1] + a[5], v30 = a[5] + a[0];
 #pragma unroll
       for (int ix = 0; ix < 2; ++ix)
         g[ix] = invVolume*(cvn[0][ix]*v01 + cvn[1][ix]*v12 + cvn[2][ix]*v23 + cvn[3][ix]*v30);
       g[2] = 0.;
     } else if constexpr (D == 3) { if (nbN == 3) {
-      const double invVolume = (1./3.)/volume;
+      const double invVolume = ddiv(1./3., volume);
       const double v031 = a[0] + a[4] + a[1], v132 = a[1] + a[4] + a[2], v023 = a[0] + a[2] + a[4];
       const double v041 = a[0] + a[5] + a[1], v142 = a[1] + a[5] + a[2], v024 = a[0] + a[2] + a[5];
 #pragma unroll
@@ -173,7 +173,7 @@ struct FaceWork {
         g[ix] = invVolume*(cvn[0][ix]*v031 + cvn[1][ix]*v132 + cvn[2][ix]*v023 +
                            cvn[3][ix]*v041 + cvn[4][ix]*v142 + cvn[5][ix]*v024);
     } else {
-      const double invVolume = (1./3.)/volume;
+      const double invVolume = ddiv(1./3., volume);
       const double v014 = a[0] + a[1] + a[4], v124 = a[1] + a[2] + a[4], v234 = a[2] + a[3] + a[4], v043 = a[0] + a[4] + a[3];
       const double v015 = a[0] + a[1] + a[5], v125 = a[1] + a[2] + a[5], v235 = a[2] + a[3] + a[5], v053 = a[0] + a[5] + a[3];
 #pragma unroll
@@ -229,8 +229,8 @@ struct FaceWork {
       diffFlux(c, grad, dflux);
 #pragma unroll
       for (int v = 0; v < Q; ++v) flux[v] -= dflux[v];  // FVMCC_ComputeRHS.cxx:260-276
-      const double nu = mu/P::density(c, avState);
-      ucD = nu*area*area/volume;
+      const double nu = ddiv(mu, P::density(c, avState));
+      ucD = ddiv(nu*area*area, volume);
     }
   }
 
@@ -238,14 +238,14 @@ struct FaceWork {
   // Diffusive part first: base diffusive flux + ucD, then (JAC) the 2q perturbed diffusive fluxes staged into the
   // two output blocks (column iVar of blkRL for side L, of blkLR for side R).
   CFB_HD void innerDiffusive(const Dev& d, const Cfg& c, const double* sL, const double* sR, bool jac,
-                             double* dfluxBase, double& ucD, double* blkRL, double* blkLR) {
+                             double* dfluxBase, double& ucD, double* stg, int stride) {
     loadDiamond(d);
     setCellStates(sL, sR);
     allGrads();
     transport(c);
     diffFlux(c, grad, dfluxBase);
-    const double nu = mu/P::density(c, avState);      // NSFlux.ci:127-152
-    ucD = nu*area*area/volume;
+    const double nu = ddiv(mu, P::density(c, avState));      // NSFlux.ci:127-152
+    ucD = ddiv(nu*area*area, volume);
     if (!jac) return;
 #pragma unroll 1
     for (int it = 0; it < 2*Q; ++it) {
@@ -272,9 +272,9 @@ struct FaceWork {
         for (int k = 0; k < 3; ++k) g2[v][k] = (v == iVar) ? gr[k] : grad[v][k];
       double dflux[Q];
       diffFlux(c, g2, dflux);
-      double* blk = side ? blkLR : blkRL;
+      double* blk = stg + (size_t)(side*Q*Q + iVar)*stride;
 #pragma unroll
-      for (int v = 0; v < Q; ++v) blk[v*Q + iVar] = dflux[v];
+      for (int v = 0; v < Q; ++v) blk[(size_t)v*Q*stride] = dflux[v];
     }
   }
 
@@ -283,9 +283,14 @@ struct FaceWork {
   //   pf = F_c*area - staged F_d ;  column <- sgn * resFactor * (pf - flux)/eps  (row-major q x q, BlockAccumulator.hh:289-296)
   CFB_HD void innerConvective(const Dev& d, const Cfg& c, const double* sL, const double* sR, const double* vL,
                               const double* vR, bool hasDiff, const double* dfluxBase, bool jac,
-                              double* flux, double* blkRL, double* blkLR) const {
+                              double* stg, int stride) const {
     const double rf = c.resFactor;
-    typename P::SideLite fixed;
+    // loop-carried state parked in the staging area (shared memory) instead of registers: the unperturbed other side
+    // (s z f) and the base flux; without a staging area (RHS-only kernel: one evaluation) they live in locals
+    double local[4*Q];
+    double* fx = jac ? stg + (size_t)2*Q*Q*stride : local;
+    const int fs = jac ? stride : 1;
+    double* fluxS = fx + (size_t)3*Q*fs;
     const int last = jac ? 2*Q : 0;
 #pragma unroll 1
     for (int it = -1; it < last; ++it) {
@@ -295,7 +300,10 @@ struct FaceWork {
         double vF[Q];
 #pragma unroll
         for (int v = 0; v < Q; ++v) vF[v] = side ? vL[v] : vR[v];
+        typename P::SideLite fixed;
         P::sideLite(c, vF, n, fixed);              // the unperturbed other side
+#pragma unroll
+        for (int v = 0; v < Q; ++v) { fx[(size_t)v*fs] = fixed.s[v]; fx[(size_t)(Q + v)*fs] = fixed.z[v]; fx[(size_t)(2*Q + v)*fs] = fixed.f[v]; }
       }
       double orig = 0., gp = 0.;
 #pragma unroll
@@ -312,7 +320,7 @@ struct FaceWork {
       typename P::SideLite pert;
       P::sideLite(c, vp, n, pert);
       double pf[Q];
-      if (!P::roeOriented(c, pert, fixed, side == 0, n, pf)) {
+      if (!P::roeOriented(c, pert, fx, fs, side == 0, n, pf)) {
         *d.status = CFB200_ERR_BAD_VALUE;
 #pragma unroll
         for (int v = 0; v < Q; ++v) pf[v] = 0.;
@@ -322,19 +330,19 @@ struct FaceWork {
         for (int v = 0; v < Q; ++v) {
           pf[v] *= area;                            // FVMCC_FluxSplitter.hh:79-83
           if (hasDiff) pf[v] -= dfluxBase[v];       // FVMCC_ComputeRHS.cxx:260-276
-          flux[v] = pf[v];
+          fluxS[(size_t)v*fs] = pf[v];
           d.faceFlux[(size_t)v*d.nFaces + f] = pf[v];
         }
       } else {
-        double* blk = side ? blkLR : blkRL;
-        const double invEps = 1./eps;
+        double* blk = stg + (size_t)(side*Q*Q + iVar)*stride;   // column iVar of block(R,L) (side 0) / block(L,R) (side 1)
+        const double invEps = ddiv(1., eps);
 #pragma unroll
         for (int v = 0; v < Q; ++v) {
           pf[v] *= area;
-          if (hasDiff) pf[v] -= blk[v*Q + iVar];
-          double fd = (pf[v] - flux[v])*invEps;
+          if (hasDiff) pf[v] -= blk[(size_t)v*Q*stride];
+          double fd = (pf[v] - fluxS[(size_t)v*fs])*invEps;
           fd *= rf;                                 // what row L receives (upFactor[0])
-          blk[v*Q + iVar] = side ? fd : fd*(-1.0);  // block(R,L) is what row R receives: upFactor[1] = -1 times that
+          blk[(size_t)v*Q*stride] = side ? fd : fd*(-1.0);  // block(R,L) is what row R receives: upFactor[1] = -1 times that
         }
       }
     }
@@ -396,7 +404,7 @@ struct FaceWork {
 #pragma unroll
         for (int v = 0; v < Q; ++v) pf[v] = 0.;
       }
-      const double invEps = 1./eps;
+      const double invEps = ddiv(1., eps);
 #pragma unroll
       for (int v = 0; v < Q; ++v) {
         pf[v] *= area;
@@ -412,15 +420,22 @@ struct FaceWork {
 // ------------------------------------------------------------------------------------------------
 // Interior faces: flux + update coefficients into face-owned slots and, when JAC, the two off-diagonal blocks
 //   block(R,L) = -resFactor * dF/dU_L        block(L,R) = +resFactor * dF/dU_R
-// straight into the BSR array (each has exactly one writer).  The diagonal contributions are the negatives of
+// assembled in the thread's shared-memory staging area (which also parks the perturbed diffusive fluxes between the
+// two passes) and then written by the warp, in whole rows, straight into the BSR array (each has exactly one writer).  The diagonal contributions are the negatives of
 // these and are gathered by DiagGather.  One-sided updatable faces (partition overlap) use the same values
 // (FVMCC_ComputeRhsJacob.cxx:184-236: row idx receives (-1)^idx * resFactor * dF/dU); the blocks that land in
 // non-updatable rows are staging for DiagGather and are zeroed afterwards by ZeroRows.
 template <int D, bool JAC>
 struct InnerFaceK {   // idx over interior faces
+  static constexpr int Q = D + 2;
+  static constexpr int BLK = Q*Q;
+  static constexpr int NOUT = 2*Q*Q;    // per-thread staging (shared memory, entry k at stg[k*stride]): block(R,L) | block(L,R)
+  static constexpr int STAGE = NOUT + 4*Q;   // ... | fixed side s z f | base flux (loop-carried state of the FD loop)
   Dev d; Cfg c;
-  CFB_HD void operator()(int f) const {
-    constexpr int Q = D + 2;
+  CFB_HD void operator()(int f) const { run(f, nullptr, 0); }
+  CFB_HD double* out() const { return d.bsrVal; }
+  CFB_HD void slots(int f, int& s0, int& s1) const { s0 = d.slotRL[f]; s1 = d.slotLR[f]; }
+  CFB_HD void run(int f, double* stg, int stride) const {
     typedef Phys<D> P;
     const bool hasDiff = (c.diffusive == CFB200_DIFF_NS);
     const int L = d.faceL[f], R = d.faceR[f];
@@ -428,20 +443,15 @@ struct InnerFaceK {   // idx over interior faces
 #pragma unroll
       for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = 0.;
       d.ucL[f] = 0.; d.ucR[f] = 0.; d.ucD[f] = 0.;
-      if (JAC) {
-        double* b0 = &d.bsrVal[(size_t)d.slotRL[f]*Q*Q]; double* b1 = &d.bsrVal[(size_t)d.slotLR[f]*Q*Q];
-        for (int k = 0; k < Q*Q; ++k) { b0[k] = 0.; b1[k] = 0.; }
-      }
+      if (JAC) for (int k = 0; k < NOUT; ++k) stg[(size_t)k*stride] = 0.;
       return;
     }
     FaceWork<D> w;
     w.load(d, c, f);
-    double sL[Q], sR[Q], vL[Q], vR[Q], flux[Q];
+    double sL[Q], sR[Q], vL[Q], vR[Q];
 #pragma unroll
     for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + L]; sR[v] = d.U[(size_t)v*d.nStates + R]; }
     w.reconstruct(c, sL, sR, vL, vR);
-    double* blkRL = JAC ? &d.bsrVal[(size_t)d.slotRL[f]*Q*Q] : nullptr;
-    double* blkLR = JAC ? &d.bsrVal[(size_t)d.slotLR[f]*Q*Q] : nullptr;
     {
       // update coefficients, RoeFlux.cxx:165-185 (one quadrature point per face)
       PData pL, pR;
@@ -457,9 +467,9 @@ struct InnerFaceK {   // idx over interior faces
     double dfluxBase[Q], ucD = 0.;
 #pragma unroll
     for (int v = 0; v < Q; ++v) dfluxBase[v] = 0.;
-    if (hasDiff) w.innerDiffusive(d, c, sL, sR, JAC, dfluxBase, ucD, blkRL, blkLR);
+    if (hasDiff) w.innerDiffusive(d, c, sL, sR, JAC, dfluxBase, ucD, stg, stride);
     d.ucD[f] = ucD;
-    w.innerConvective(d, c, sL, sR, vL, vR, hasDiff, dfluxBase, JAC, flux, blkRL, blkLR);
+    w.innerConvective(d, c, sL, sR, vL, vR, hasDiff, dfluxBase, JAC, stg, stride);
   }
 };
 
@@ -533,7 +543,7 @@ struct BoundaryFaceK {   // idx over boundary faces
 #pragma unroll
         for (int v = 0; v < Q; ++v) pf[v] -= dflux[v];
       }
-      const double invEps = 1./eps;
+      const double invEps = ddiv(1., eps);
 #pragma unroll
       for (int v = 0; v < Q; ++v) {
         double fd = (pf[v] - flux[v])*invEps;

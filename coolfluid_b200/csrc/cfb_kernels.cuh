@@ -156,7 +156,7 @@ CFB_HD double edgeWeight(const Dev& d, int c, int nb, double* dx) {
     dist += diff*diff;
     dx[k] = xn - xc;
   }
-  const double w = 1.0/sqrt(dist);
+  const double w = ddiv(1.0, dsqrt(dist));
   for (int k = 0; k < D; ++k) dx[k] = w*dx[k];
   return w;
 }
@@ -199,7 +199,7 @@ struct Gradients {   // idx over cells
     }
     if (D == 2) {
       const double l11 = d.lsqL[c], l12 = d.lsqL[(size_t)d.nCells + c], l22 = d.lsqL[(size_t)3*d.nCells + c];
-      const double invDet = 1./(l11*l22 - l12*l12);
+      const double invDet = ddiv(1., l11*l22 - l12*l12);
       for (int v = 0; v < Q; ++v) {
         d.uX[(size_t)v*d.nCells + c] = (l22*lf[0][v] - l12*lf[1][v])*invDet;
         d.uY[(size_t)v*d.nCells + c] = (l11*lf[1][v] - l12*lf[0][v])*invDet;
@@ -216,12 +216,13 @@ struct Gradients {   // idx over cells
       const double linv13 = l12*l23 - l13*l22;
       const double linv23 = -(l11*l23 - l13*l12);
       const bool ok = !(fabs(det) <= 2.2250738585072014e-308);   // !MathChecks::isZero(det)
+      const Recip rdet = recipOf(ok ? det : 1.0);
       for (int v = 0; v < Q; ++v) {
         double gx = 0.0, gy = 0.0, gz = 0.0;
         if (ok) {
-          gx = (linv11*lf[0][v] + linv12*lf[1][v] + linv13*lf[2][v])/det;
-          gy = (linv12*lf[0][v] + linv22*lf[1][v] + linv23*lf[2][v])/det;
-          gz = (linv13*lf[0][v] + linv23*lf[1][v] + linv33*lf[2][v])/det;
+          gx = divBy(linv11*lf[0][v] + linv12*lf[1][v] + linv13*lf[2][v], rdet);
+          gy = divBy(linv12*lf[0][v] + linv22*lf[1][v] + linv23*lf[2][v], rdet);
+          gz = divBy(linv13*lf[0][v] + linv23*lf[1][v] + linv33*lf[2][v], rdet);
         }
         d.uX[(size_t)v*n + c] = gx; d.uY[(size_t)v*n + c] = gy; d.uZ[(size_t)v*n + c] = gz;
       }
@@ -280,7 +281,7 @@ struct LimiterK {   // idx over cells
             min0 = dmin(min0, us); max0 = dmax(max0, us);
             double dist = 0.;
             for (int k = 0; k < D; ++k) { const double diff = xc[k] - d.centres[(size_t)k*d.nStates + s]; dist += diff*diff; }
-            avgDistance += sqrt(dist);
+            avgDistance += dsqrt(dist);
           }
         }
         avgDistance /= (se - sb);
@@ -293,7 +294,7 @@ struct LimiterK {   // idx over cells
           min0 = dmin(min0, us); max0 = dmax(max0, us);
           double dist = 0.;
           for (int k = 0; k < D; ++k) { const double diff = xc[k] - d.centres[(size_t)k*d.nStates + s]; dist += diff*diff; }
-          avgDistance += sqrt(dist);
+          avgDistance += dsqrt(dist);
         }
         avgDistance /= nbFaces;
       }
@@ -419,7 +420,7 @@ struct TimeRhs {   // idx over cells
     constexpr int Q = D + 2;
     typedef Phys<D> P;
     if (!d.updatable[cell]) return;
-    const double diagValue = d.updateCoeff[cell]/c.cfl;
+    const double diagValue = ddiv(d.updateCoeff[cell], c.cfl);
     double u[Q], up[Q], tempState[Q], tPast[Q], tPert[Q];
     for (int v = 0; v < Q; ++v) { u[v] = d.U[(size_t)v*d.nStates + cell]; up[v] = d.pastU[(size_t)v*d.nCells + cell]; }
     P::toCons(c, u, tempState);
@@ -435,7 +436,7 @@ struct TimeRhs {   // idx over cells
       const double eps = fdEps(c, iVar, orig);
       u[iVar] = orig + eps;
       P::toCons(c, u, tPert);
-      const double invEps = 1./eps;
+      const double invEps = ddiv(1., eps);
       for (int v = 0; v < Q; ++v) {
         double fd = (tPert[v] - tempState[v])*invEps;
         fd *= diagValue*c.resFactor;

@@ -50,6 +50,7 @@ ABI_SYMBOLS = [
     "export_csr", "get_field", "device_ptr", "status", "enable_timing", "last_timings", "stream",
     "nccl_unique_id", "comm_init", "set_halo", "halo_exchange", "allreduce_sum",
     "mesh_build", "mesh_sizes", "mesh_get", "mesh_ptr", "mesh_view", "mesh_set_updatable", "mesh_free",
+    "selftest_divsqrt",
 ]
 # symbols the engine part needs (a test-only host build of the kernel functors exports just these)
 ENGINE_SYMBOLS = ABI_SYMBOLS[2:28]
@@ -75,6 +76,8 @@ def load(path=None, prefix="cfb200_"):
         except AttributeError:
             if prefix == "cfb200_" or name in ENGINE_SYMBOLS:
                 raise
+    if hasattr(ns, "selftest_divsqrt"):
+        ns.selftest_divsqrt.argtypes = [C.c_int, C.c_int64, C.c_uint64, C.c_int, C.POINTER(C.c_int64)]
     H = C.c_void_p
     ns.create.argtypes = [C.POINTER(ConfigStruct), C.c_int, C.POINTER(H)]
     ns.destroy.argtypes = [H]; ns.destroy.restype = None

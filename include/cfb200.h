@@ -133,6 +133,11 @@ int cfb200_abi_version(void);
 /* number of usable CUDA devices (0 without a GPU; never throws) */
 int cfb200_device_count(void);
 
+/* diagnostic: compares the kernels' branch-free FP64 divide / square root (csrc/cfb_math.cuh) with the compiler's IEEE
+ * `/` and sqrt() on n pseudo-random operand pairs with binary exponents in [-exponentSpan, exponentSpan] (<= 480),
+ * zeros and exact quotients included; *mismatches must come back 0 */
+int cfb200_selftest_divsqrt(int device, int64_t n, uint64_t seed, int exponentSpan, int64_t* mismatches);
+
 /* replaces: FVMCC_ComputeRHS constructor/configure/setup (plugins/FiniteVolume/FVMCC_ComputeRHS.cxx:46-128,329-440) */
 int cfb200_create(const cfb200_config* cfg, int device, cfb200_handle** out);
 /* replaces: FVMCC_ComputeRHS::unsetup */

@@ -27,6 +27,17 @@ struct HostLoopBackend {
   void resetTimings() {}
   int timings(const char**, float*, int) { return 0; }
   template <class F> void launch(const char*, const F& f, int n, int) { for (int i = 0; i < n; ++i) f(i); }
+  template <class F> void launchStaged(const char*, const F& f, int n, int) {
+    double stg[F::STAGE];
+    for (int i = 0; i < n; ++i) {
+      int s0 = -1, s1 = -1;
+      f.run(i, stg, 1); f.slots(i, s0, s1);
+      for (int k = 0; k < F::NOUT; ++k) {                   // the warp's block write-out
+        const int slot = (k/F::BLK) ? s1 : s0;
+        if (slot >= 0) f.out()[(size_t)slot*F::BLK + k%F::BLK] = stg[k];
+      }
+    }
+  }
   double sumOrdered(double* x, int n) { double s = 0.; for (int i = 0; i < n; ++i) s += x[i]; return s; }
 };
 }

@@ -180,3 +180,15 @@ def test_cuda_matches_committed_golden_vectors(product_lib):
         e.close()
         for k, a in got.items():
             assert cases.relerr(a, g[name + "/" + k]) <= TOL, (name, k)
+
+
+def test_div_sqrt_bitexact(product_lib):
+    """The kernels' branch-free FP64 divide / square root (csrc/cfb_math.cuh) against the compiler's IEEE `/` and
+    sqrt() on the device: 2^28 operand pairs per exponent span, zeros, exact quotients and shared reciprocals included.
+    Bar: zero mismatching bit patterns."""
+    import ctypes as C
+    for span, seed in ((4, 1), (60, 2), (300, 3), (480, 4)):
+        bad = C.c_int64(-1)
+        rc = product_lib.selftest_divsqrt(0, 1 << 28, seed, span, C.byref(bad))
+        assert rc == 0
+        assert bad.value == 0, "span 2^+-%d: %d mismatches" % (span, bad.value)
