@@ -165,6 +165,18 @@ public:
       for (int c = 0; c < nc; ++c) dg[c] = slot(c, c);
       d.bsrRowPtr = upload(hRowPtr); d.bsrColInd = upload(hColInd);
       d.slotLR = upload(sLR); d.slotRL = upload(sRL); d.diagSlot = upload(dg);
+      // diagonal gather sources, in the cell's face-loop order: inner face, cell == L: block(R,cell); cell == R:
+      // block(L,cell); boundary face g: ~g
+      std::vector<int32_t> dsrc(ncf);
+      for (int c = 0; c < nc; ++c) {
+        std::vector<int32_t> fs(m.cellFaces + m.cellFacePtr[c], m.cellFaces + m.cellFacePtr[c+1]);
+        std::sort(fs.begin(), fs.end());
+        for (size_t k = 0; k < fs.size(); ++k) {
+          const int f = fs[k];
+          dsrc[m.cellFacePtr[c] + k] = (f >= ni) ? ~(f - ni) : ((m.faceL[f] == c) ? sRL[f] : sLR[f]);
+        }
+      }
+      d.diagSrc = upload(dsrc);
       std::vector<int32_t> nu;
       for (int c = 0; c < nc; ++c) if (!m.updatable[c]) nu.push_back(c);
       nNonUpd = (int)nu.size();

@@ -41,6 +41,7 @@ struct Dev {
   const int* slotLR;          // [nInner] block (L,R)
   const int* slotRL;          // [nInner] block (R,L)
   const int* diagSlot;        // [nCells]
+  const int* diagSrc;         // CSR like cellFaceSorted: source block of each face's diagonal contribution (see DiagGather)
   double* bsrVal;             // [nnzb][q][q]
   double* bndBlocks;          // [nGhosts][q][q]  boundary-face contribution to the diagonal of the inner cell
   // ---- fields ----
@@ -265,13 +266,42 @@ struct LimiterK {   // idx over cells
     double xc[3] = {0., 0., 0.};
     for (int k = 0; k < D; ++k) xc[k] = d.centres[(size_t)k*d.nStates + cell];
     double dxq[6][3];       // face quadrature point - cell centre
-    for (int j = 0; j < nbFaces; ++j) {
+#pragma unroll
+    for (int j = 0; j < 6; ++j) if (j < nbFaces) {     // fully unrolled + predicated: dxq / nbrFace stay in registers
       const int f = d.cellFaces[fb + j];
       for (int k = 0; k < D; ++k) dxq[j][k] = d.faceCentres[(size_t)k*d.nFaces + f] - xc[k];
     }
+    // neighbour list and average distance: the reference recomputes them inside its loop over the variables
+    // (Venktn2D.cxx:150-185); they depend on the geometry only, so they are formed once here, by the same operations
+    double avgDistance = 0.0;
+    int nbrFace[6] = {0, 0, 0, 0, 0, 0};
+    if (c.useFullStencil) {
+      const int sb = d.stencilPtr[cell], se = d.stencilPtr[cell+1];
+      for (int is = sb; is < se; ++is) {
+        const int s = d.stencil[is];
+        if (s != cell) {
+          double dist = 0.;
+          for (int k = 0; k < D; ++k) { const double diff = xc[k] - d.centres[(size_t)k*d.nStates + s]; dist += diff*diff; }
+          avgDistance += dsqrt(dist);
+        }
+      }
+      avgDistance /= (se - sb);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 6; ++j) if (j < nbFaces) {
+        const int f = d.cellFaces[fb + j];
+        const int fl = d.faceL[f];
+        const int s = (fl == cell) ? d.faceR[f] : fl;
+        nbrFace[j] = s;
+        double dist = 0.;
+        for (int k = 0; k < D; ++k) { const double diff = xc[k] - d.centres[(size_t)k*d.nStates + s]; dist += diff*diff; }
+        avgDistance += dsqrt(dist);
+      }
+      avgDistance /= nbFaces;
+    }
     for (int v = 0; v < Q; ++v) {
       const double u0 = d.U[(size_t)v*d.nStates + cell];
-      double min0 = u0, max0 = u0, avgDistance = 0.0;
+      double min0 = u0, max0 = u0;
       if (c.useFullStencil) {
         const int sb = d.stencilPtr[cell], se = d.stencilPtr[cell+1];
         for (int is = sb; is < se; ++is) {
@@ -279,24 +309,14 @@ struct LimiterK {   // idx over cells
           if (s != cell) {
             const double us = d.U[(size_t)v*d.nStates + s];
             min0 = dmin(min0, us); max0 = dmax(max0, us);
-            double dist = 0.;
-            for (int k = 0; k < D; ++k) { const double diff = xc[k] - d.centres[(size_t)k*d.nStates + s]; dist += diff*diff; }
-            avgDistance += dsqrt(dist);
           }
         }
-        avgDistance /= (se - sb);
       } else {
-        for (int j = 0; j < nbFaces; ++j) {
-          const int f = d.cellFaces[fb + j];
-          const int fl = d.faceL[f];
-          const int s = (fl == cell) ? d.faceR[f] : fl;
-          const double us = d.U[(size_t)v*d.nStates + s];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) if (j < nbFaces) {
+          const double us = d.U[(size_t)v*d.nStates + nbrFace[j]];
           min0 = dmin(min0, us); max0 = dmax(max0, us);
-          double dist = 0.;
-          for (int k = 0; k < D; ++k) { const double diff = xc[k] - d.centres[(size_t)k*d.nStates + s]; dist += diff*diff; }
-          avgDistance += dsqrt(dist);
         }
-        avgDistance /= nbFaces;
       }
       const double deltaPlusMax = max0 - u0;
       const double deltaPlusMin = min0 - u0;
@@ -306,7 +326,8 @@ struct LimiterK {   // idx over cells
       const double uz = (D == 3) ? d.uZ[(size_t)v*d.nCells + cell] : 0.;
       if (c.limiter == CFB200_LIM_VENKTN) {
         const double epsilon = c.coeffEps*c.magnitudeValues[v]*c.magnitudeValues[v]*pow3(avgDistance/c.length);
-        for (int j = 0; j < nbFaces; ++j) {
+#pragma unroll
+        for (int j = 0; j < 6; ++j) if (j < nbFaces) {
           double deltaMin;
           if (D == 2) deltaMin = ux*dxq[j][0] + uy*dxq[j][1];
           else deltaMin = ux*dxq[j][0] + uy*dxq[j][1] + uz*dxq[j][2];
@@ -322,7 +343,8 @@ struct LimiterK {   // idx over cells
           psimin = dmin(psi, psimin);
         }
       } else {
-        for (int j = 0; j < nbFaces; ++j) {
+#pragma unroll
+        for (int j = 0; j < 6; ++j) if (j < nbFaces) {
           double deltaMin;
           if (D == 2) deltaMin = ux*dxq[j][0] + uy*dxq[j][1];
           else deltaMin = ux*dxq[j][0] + uy*dxq[j][1] + uz*dxq[j][2];
@@ -383,16 +405,24 @@ struct DiagGather {   // idx over nCells*32 (one warp-sized group per cell, Q*Q 
     if (e >= Q*Q) return;
     double acc = 0.;
     if (d.updatable[cell]) {
-      for (int j = d.cellFacePtr[cell]; j < d.cellFacePtr[cell+1]; ++j) {
-        const int s = d.cellFaceSorted[j];
-        const bool isR = s < 0;
-        const int f = isR ? ~s : s;
-        if (f < d.nInner) {
-          const int slot = isR ? d.slotLR[f] : d.slotRL[f];
-          acc -= d.bsrVal[(size_t)slot*Q*Q + e];
-        } else {
-          acc += d.bndBlocks[(size_t)(f - d.nInner)*Q*Q + e];
+      // diagSrc[j] (built once on the host, aligned with cellFaceSorted): the BSR slot of the block this face
+      // contributes with a minus sign, or ~g for boundary face g (plus sign).  Batches of 6 faces: all source
+      // blocks of a batch are requested before the first is consumed (memory-level parallelism), then added in
+      // face-loop order.
+      const int jb = d.cellFacePtr[cell], je = d.cellFacePtr[cell+1];
+      for (int j0 = jb; j0 < je; j0 += 6) {
+        double x[6];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+          x[k] = 0.;
+          if (j0 + k < je) {
+            const int s = d.diagSrc[j0 + k];
+            x[k] = (s >= 0) ? d.bsrVal[(size_t)s*Q*Q + e] : d.bndBlocks[(size_t)(~s)*Q*Q + e];
+          }
         }
+#pragma unroll
+        for (int k = 0; k < 6; ++k)
+          if (j0 + k < je) { if (d.diagSrc[j0 + k] >= 0) acc -= x[k]; else acc += x[k]; }
       }
     }
     d.bsrVal[(size_t)d.diagSlot[cell]*Q*Q + e] = acc;
