@@ -325,21 +325,21 @@ struct LimiterK {   // idx over cells
       const double ux = d.uX[(size_t)v*d.nCells + cell], uy = d.uY[(size_t)v*d.nCells + cell];
       const double uz = (D == 3) ? d.uZ[(size_t)v*d.nCells + cell] : 0.;
       if (c.limiter == CFB200_LIM_VENKTN) {
-        const double epsilon = c.coeffEps*c.magnitudeValues[v]*c.magnitudeValues[v]*pow3(avgDistance/c.length);
+        const double epsilon = c.coeffEps*c.magnitudeValues[v]*c.magnitudeValues[v]*pow3(ddiv(avgDistance, c.length));
 #pragma unroll
         for (int j = 0; j < 6; ++j) if (j < nbFaces) {
           double deltaMin;
           if (D == 2) deltaMin = ux*dxq[j][0] + uy*dxq[j][1];
           else deltaMin = ux*dxq[j][0] + uy*dxq[j][1] + uz*dxq[j][2];
-          if (deltaMin > 0.0) {
-            const double dPlusMax2 = deltaPlusMax*deltaPlusMax;
-            const double dPlusMaxMin = deltaPlusMax*deltaMin;
-            psi = (dPlusMax2 + 2.0*dPlusMaxMin + epsilon)/(dPlusMax2 + dPlusMaxMin + 2.0*deltaMin*deltaMin + epsilon);
-          }
-          if (deltaMin < 0.0) {
-            const double y = deltaPlusMin/deltaMin;
-            psi = (y*y + 2*y)/(y*y + y + 2.);
-          }
+          // both candidates are formed without branching (the divisions of the six faces overlap), then selected:
+          // same values as the reference's two if-blocks (Venktn2D.cxx:226-243), psi is kept when deltaMin == 0
+          const double dPlusMax2 = deltaPlusMax*deltaPlusMax;
+          const double dPlusMaxMin = deltaPlusMax*deltaMin;
+          const double psiP = ddiv(dPlusMax2 + 2.0*dPlusMaxMin + epsilon, dPlusMax2 + dPlusMaxMin + 2.0*deltaMin*deltaMin + epsilon);
+          const double y = ddiv(deltaPlusMin, deltaMin);
+          const double psiM = ddiv(y*y + 2*y, y*y + y + 2.);
+          if (deltaMin > 0.0) psi = psiP;
+          if (deltaMin < 0.0) psi = psiM;
           psimin = dmin(psi, psimin);
         }
       } else {
@@ -348,8 +348,10 @@ struct LimiterK {   // idx over cells
           double deltaMin;
           if (D == 2) deltaMin = ux*dxq[j][0] + uy*dxq[j][1];
           else deltaMin = ux*dxq[j][0] + uy*dxq[j][1] + uz*dxq[j][2];
-          if (deltaMin > 0.0) psi = dmin(1., deltaPlusMax/deltaMin);
-          if (deltaMin < 0.0) psi = dmin(1., deltaPlusMin/deltaMin);
+          const Recip rd = recipOf(deltaMin);
+          const double qMax = divBy(deltaPlusMax, rd), qMin = divBy(deltaPlusMin, rd);
+          if (deltaMin > 0.0) psi = dmin(1., qMax);
+          if (deltaMin < 0.0) psi = dmin(1., qMin);
           psimin = dmin(psi, psimin);
         }
       }
