@@ -12,7 +12,7 @@
 namespace cfb {
 
 #define CFB_CUDA(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
-  throw DeviceError(CFB200_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+  throw cfb::DeviceError(CFB200_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
 
 template <class F, int BS, int MINB>
 __global__ void __launch_bounds__(BS, MINB) k_run(const F f, const int n) {
@@ -184,6 +184,139 @@ struct CudaBackend {
 typedef cfb::CudaBackend BackendT;
 #define CFB_FN(x) cfb200_##x
 #include "cfb_capi.inc"
+#include "cfb_halo.cuh"
+
+// ---- multi-GPU entry points (include/cfb200.h) -----------------------------------------------------------------
+namespace {
+cfb::Halo* haloOf(cfb200_handle* h, bool create) {
+  if (!h->ext && create) {
+    h->ext = new cfb::Halo();
+    h->extFree = [](void* p) { delete static_cast<cfb::Halo*>(p); };
+  }
+  return static_cast<cfb::Halo*>(h->ext);
+}
+void haloBegin(cfb::Engine<BackendT>& e, cfb::Halo& H) {
+  if (!H.comm || !H.haveLists) throw std::runtime_error("comm_init / set_halo have not been called");
+  if (e.haloPending) throw std::runtime_error("a halo exchange is already in flight");
+  cfb::NcclApi& N = cfb::NcclApi::get();
+  const int q = e.q();
+  const int nSend = H.sendPtr[H.nRanks], nRecv = H.recvPtr[H.nRanks];
+  if (nSend) e.bk.launch("haloPack", cfb::HaloPack{e.d.U, e.d.nStates, q, H.dSend, H.sbuf}, nSend*q, 256);
+  CFB_CUDA(cudaEventRecord(H.packed, e.bk.stream));
+  CFB_CUDA(cudaStreamWaitEvent(H.cs, H.packed, 0));
+  CFB_NCCL(N.GroupStart());
+  for (int p = 0; p < H.nRanks; ++p) {
+    const int ns = H.sendPtr[p+1] - H.sendPtr[p], nr = H.recvPtr[p+1] - H.recvPtr[p];
+    if (ns) CFB_NCCL(N.Send(H.sbuf + (size_t)H.sendPtr[p]*q, (size_t)ns*q, ncclDouble, p, H.comm, H.cs));
+    if (nr) CFB_NCCL(N.Recv(H.rbuf + (size_t)H.recvPtr[p]*q, (size_t)nr*q, ncclDouble, p, H.comm, H.cs));
+  }
+  CFB_NCCL(N.GroupEnd());
+  if (nRecv) {
+    const int n = nRecv*q;
+    cfb::k_run<cfb::HaloUnpack, 256, 1><<<(n + 255)/256, 256, 0, H.cs>>>(cfb::HaloUnpack{e.d.U, e.d.nStates, q, H.dRecv, H.rbuf}, n);
+    CFB_CUDA(cudaGetLastError());
+  }
+  CFB_CUDA(cudaEventRecord(H.done, H.cs));
+  e.haloPending = true;
+  cudaEvent_t done = H.done;
+  cudaStream_t s = e.bk.stream;
+  e.haloWait = [done, s]() { CFB_CUDA(cudaStreamWaitEvent(s, done, 0)); };
+}
+}
+
+extern "C" {
+
+int cfb200_nccl_unique_id(void* id128) {
+  if (!id128) return CFB200_ERR_INVALID_ARG;
+  try {
+    ncclUniqueId id;
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    if (cfb::NcclApi::get().GetUniqueId(&id) != ncclSuccess) return CFB200_ERR_NCCL;
+    std::memcpy(id128, &id, 128);
+    return CFB200_OK;
+  } catch (const cfb::DeviceError& e) { return e.code; }
+}
+
+int cfb200_comm_init(cfb200_handle* h, int rank, int nRanks, const void* id128) {
+  if (!id128 || nRanks < 1 || rank < 0 || rank >= nRanks) return CFB200_ERR_INVALID_ARG;
+  return guarded(h, [&](cfb::Engine<BackendT>& e) {
+    cfb::Halo* H = haloOf(h, true);
+    if (H->comm) throw std::runtime_error("communicator already initialised");
+    ncclUniqueId id;
+    std::memcpy(&id, id128, 128);
+    H->rank = rank; H->nRanks = nRanks; H->dev = e.bk.dev;
+    CFB_NCCL(cfb::NcclApi::get().CommInitRank(&H->comm, nRanks, id, rank));
+    CFB_CUDA(cudaStreamCreateWithFlags(&H->cs, cudaStreamNonBlocking));
+    CFB_CUDA(cudaEventCreateWithFlags(&H->packed, cudaEventDisableTiming));
+    CFB_CUDA(cudaEventCreateWithFlags(&H->done, cudaEventDisableTiming));
+    CFB_CUDA(cudaMalloc((void**)&H->red, sizeof(double)*64));
+    return CFB200_OK;
+  });
+}
+
+int cfb200_set_halo(cfb200_handle* h, const int32_t* sendPtr, const int32_t* sendCells, const int32_t* recvPtr,
+                    const int32_t* recvCells, int32_t nIndependent) {
+  if (!sendPtr || !recvPtr) return CFB200_ERR_INVALID_ARG;
+  return guarded(h, [&](cfb::Engine<BackendT>& e) {
+    CFB_NEED_MESH(e);
+    cfb::Halo* H = haloOf(h, false);
+    if (!H || !H->comm) throw std::runtime_error("comm_init has not been called");
+    const int n = H->nRanks, q = e.q();
+    H->sendPtr.assign(sendPtr, sendPtr + n + 1); H->recvPtr.assign(recvPtr, recvPtr + n + 1);
+    const int ns = H->sendPtr[n], nr = H->recvPtr[n];
+    if ((ns && !sendCells) || (nr && !recvCells)) throw std::invalid_argument("set_halo: null cell list");
+    for (int i = 0; i < ns; ++i) if (sendCells[i] < 0 || sendCells[i] >= e.d.nCells) throw std::invalid_argument("set_halo: send cell out of range");
+    for (int i = 0; i < nr; ++i) if (recvCells[i] < 0 || recvCells[i] >= e.d.nCells) throw std::invalid_argument("set_halo: receive cell out of range");
+    if (nIndependent < 0 || nIndependent > e.d.nCells) throw std::invalid_argument("set_halo: nIndependent out of range");
+    cudaFree(H->dSend); cudaFree(H->dRecv); cudaFree(H->sbuf); cudaFree(H->rbuf);
+    H->dSend = H->dRecv = nullptr; H->sbuf = H->rbuf = nullptr;
+    CFB_CUDA(cudaMalloc((void**)&H->dSend, sizeof(int)*std::max(ns, 1)));
+    CFB_CUDA(cudaMalloc((void**)&H->dRecv, sizeof(int)*std::max(nr, 1)));
+    CFB_CUDA(cudaMalloc((void**)&H->sbuf, sizeof(double)*std::max(ns, 1)*q));
+    CFB_CUDA(cudaMalloc((void**)&H->rbuf, sizeof(double)*std::max(nr, 1)*q));
+    if (ns) CFB_CUDA(cudaMemcpy(H->dSend, sendCells, sizeof(int)*ns, cudaMemcpyHostToDevice));
+    if (nr) CFB_CUDA(cudaMemcpy(H->dRecv, recvCells, sizeof(int)*nr, cudaMemcpyHostToDevice));
+    H->haveLists = true;
+    e.nIndep = nIndependent;
+    return CFB200_OK;
+  });
+}
+
+int cfb200_halo_begin(cfb200_handle* h) {
+  return guarded(h, [&](cfb::Engine<BackendT>& e) {
+    cfb::Halo* H = haloOf(h, false);
+    if (!H) throw std::runtime_error("comm_init has not been called");
+    haloBegin(e, *H);
+    return CFB200_OK;
+  });
+}
+
+int cfb200_halo_exchange(cfb200_handle* h) {
+  return guarded(h, [&](cfb::Engine<BackendT>& e) {
+    cfb::Halo* H = haloOf(h, false);
+    if (!H) throw std::runtime_error("comm_init has not been called");
+    haloBegin(e, *H);
+    e.haloWait();
+    e.haloPending = false;
+    e.bk.sync();
+    return CFB200_OK;
+  });
+}
+
+int cfb200_allreduce_sum(cfb200_handle* h, double* v, int n) {
+  if (!v || n < 1 || n > 64) return CFB200_ERR_INVALID_ARG;
+  return guarded(h, [&](cfb::Engine<BackendT>& e) {
+    cfb::Halo* H = haloOf(h, false);
+    if (!H || !H->comm) throw std::runtime_error("comm_init has not been called");
+    CFB_CUDA(cudaMemcpyAsync(H->red, v, sizeof(double)*n, cudaMemcpyHostToDevice, e.bk.stream));
+    CFB_NCCL(cfb::NcclApi::get().AllReduce(H->red, H->red, (size_t)n, ncclDouble, ncclSum, H->comm, e.bk.stream));
+    CFB_CUDA(cudaMemcpyAsync(v, H->red, sizeof(double)*n, cudaMemcpyDeviceToHost, e.bk.stream));
+    e.bk.sync();
+    return CFB200_OK;
+  });
+}
+
+} // extern "C"
 
 // ---- self test of the branch-free divide / square root (cfb_math.cuh) against the compiler's IEEE `/` and sqrt() ----
 namespace cfb {

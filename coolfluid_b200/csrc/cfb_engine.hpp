@@ -13,6 +13,7 @@
 #include <cstring>
 #include <algorithm>
 #include <stdexcept>
+#include <functional>
 #include "cfb_kernels.cuh"
 
 namespace cfb {
@@ -36,6 +37,11 @@ public:
   int lastStatus = 0;
   int faceShape = 2;       // resident 128-thread blocks per SM the interior-face Jacobian kernel is compiled for
                            // (CudaBackend::launchStaged): 2 -> 255 registers, no spills: measured fastest on B200 (profiles/)
+  // multi-GPU (cfb_halo.cuh): a state halo exchange may be in flight when computeRhs is called; the first nIndep
+  // cells have no received cell in their reconstruction stencil, so their gradients overlap with the exchange
+  int nIndep = 0;
+  bool haloPending = false;
+  std::function<void()> haloWait;
   std::vector<void*> owned;
   int* nonUpdCells = nullptr;
   std::vector<int32_t> hRowPtr, hColInd;
@@ -238,9 +244,20 @@ public:
     if (doJac) ensureJacobian();
     bk.resetTimings();
     bk.memset(d.status, 0, sizeof(int));
+    int g0 = 0;
+    if (haloPending) {
+      // overlap with the halo exchange: ghosts + gradients of the cells that do not see a received state
+      if (applyBC) applyBC_<D>();
+      if (cfg.polyRec == CFB200_PR_LINEARLS && nIndep > 0) {
+        g0 = std::min(nIndep, d.nCells);
+        bk.launch("gradientsInterior", Gradients<D>{d, 0}, g0, 128);
+      }
+      haloWait();                          // the engine's stream now waits for the unpacked overlap states
+      haloPending = false;
+    }
     if (applyBC) applyBC_<D>();
     // initializeComputationRHS (FVMCC_ComputeRHS.cxx:690-705)
-    if (cfg.polyRec == CFB200_PR_LINEARLS) bk.launch("gradients", Gradients<D>{d}, d.nCells, 128);
+    if (cfg.polyRec == CFB200_PR_LINEARLS) bk.launch("gradients", Gradients<D>{d, g0}, d.nCells - g0, 128);
     bk.launch("nodalExtrapolate", NodalExtrapolate<D>{d}, d.nNodes, 256);
     if (cfg.polyRec == CFB200_PR_LINEARLS && cfg.limiter != CFB200_LIM_NONE)
       bk.launch("limiter", LimiterK<D>{d, cfg}, d.nCells, 128);

@@ -181,10 +181,11 @@ struct LsqSetup {   // LeastSquareP1PolyRec{2,3}D::updateWeights; idx over cells
 };
 
 template <int D>
-struct Gradients {   // idx over cells
-  Dev d;
-  CFB_HD void operator()(int c) const {
+struct Gradients {   // idx over the cells [c0, c0 + n)
+  Dev d; int c0;
+  CFB_HD void operator()(int idx) const {
     constexpr int Q = D + 2;
+    const int c = c0 + idx;
     double lf[3][Q];
     double u0[Q];
     for (int v = 0; v < Q; ++v) { lf[0][v] = lf[1][v] = lf[2][v] = 0.; u0[v] = d.U[(size_t)v*d.nStates + c]; }

@@ -48,7 +48,7 @@ ABI_SYMBOLS = [
     "get_states", "set_past_states", "backup_past_states", "set_limiter", "set_update_coeff", "apply_bc",
     "compute_rhs", "time_rhs", "update_sol_fwd_euler", "bsr_view", "bsr_pattern", "bsr_nnzb", "get_bsr_values",
     "export_csr", "get_field", "device_ptr", "status", "enable_timing", "last_timings", "stream",
-    "nccl_unique_id", "comm_init", "set_halo", "halo_exchange", "allreduce_sum",
+    "nccl_unique_id", "comm_init", "set_halo", "halo_begin", "halo_exchange", "allreduce_sum",
     "mesh_build", "mesh_sizes", "mesh_get", "mesh_ptr", "mesh_view", "mesh_set_updatable", "mesh_free",
     "selftest_divsqrt",
 ]
@@ -116,7 +116,8 @@ def load(path=None, prefix="cfb200_"):
         ns.mesh_free.argtypes = [C.c_void_p]; ns.mesh_free.restype = None
         ns.nccl_unique_id.argtypes = [C.c_void_p]
         ns.comm_init.argtypes = [H, C.c_int, C.c_int, C.c_void_p]
-        ns.set_halo.argtypes = [H, P_I, P_I, P_I, P_I]
+        ns.set_halo.argtypes = [H, P_I, P_I, P_I, P_I, C.c_int32]
+        ns.halo_begin.argtypes = [H]
         ns.halo_exchange.argtypes = [H]
         ns.allreduce_sum.argtypes = [H, P_D, C.c_int]
     _libs[key] = ns
@@ -307,3 +308,34 @@ class Engine:
 
     def stream(self):
         return self.L.stream(self.h)
+
+    # ---- multi-GPU (one partition per GPU) ----
+    def comm_init(self, rank, nranks, unique_id: bytes):
+        buf = C.create_string_buffer(unique_id, 128)
+        self._chk(self.L.comm_init(self.h, rank, nranks, buf), "comm_init")
+
+    def set_halo(self, part):
+        """part: coolfluid_b200.partition.Partition of this rank"""
+        sp, sc, rp, rc = part.halo_csr()
+        self._halo_keep = (sp, sc, rp, rc)
+        self._chk(self.L.set_halo(self.h, _pi(sp), _pi(sc), _pi(rp), _pi(rc), int(part.n_interior)), "set_halo")
+
+    def halo_begin(self):
+        self._chk(self.L.halo_begin(self.h), "halo_begin")
+
+    def halo_exchange(self):
+        self._chk(self.L.halo_exchange(self.h), "halo_exchange")
+
+    def allreduce_sum(self, values):
+        v = np.ascontiguousarray(values, dtype=np.float64).copy()
+        self._chk(self.L.allreduce_sum(self.h, _pd(v), len(v)), "allreduce_sum")
+        return v
+
+
+def nccl_unique_id(lib=None) -> bytes:
+    L = lib or load()
+    buf = C.create_string_buffer(128)
+    rc = L.nccl_unique_id(buf)
+    if rc:
+        raise Cfb200Error(rc, "nccl_unique_id")
+    return buf.raw

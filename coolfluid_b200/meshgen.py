@@ -49,6 +49,9 @@ def _pack_trs(faces_per_trs):
     cells, nptr, nodes = [], [0], []
     for c, n in faces_per_trs:
         c = np.asarray(c, dtype=np.int64)
+        if len(c) == 0:                 # an empty TRS keeps its index (boundary conditions are matched by TRS index)
+            cells.append(c); nodes.append(np.zeros(0, dtype=np.int64)); ptr.append(ptr[-1])
+            continue
         n = np.asarray(n, dtype=np.int64).reshape(len(c), -1)
         cells.append(c)
         k = n.shape[1]

@@ -200,12 +200,20 @@ void* cfb200_stream(cfb200_handle* h);
 
 /* ---- multi-GPU (one partition per GPU).  replaces: DataHandle<State*,GLOBAL>::synchronize()
  * (src/Common/MPI/MPICommPattern.hh:1735-1782) for the states array ---------------------------------------- */
-int cfb200_nccl_unique_id(void* id128 /* 128 bytes out */);
+int cfb200_nccl_unique_id(void* id128 /* 128 bytes out: ncclUniqueId made on one rank, handed to all by the host code */);
 int cfb200_comm_init(cfb200_handle* h, int rank, int nRanks, const void* id128);
-/* sendPtr/recvPtr: CSR over ranks; sendCells: local cell ids to pack for each peer; recvCells: local (overlap) cell ids */
+/* sendPtr/recvPtr: CSR over ranks [nRanks+1]; sendCells: local ids of the updatable cells to pack for each peer;
+ * recvCells: local ids of the overlap cells each peer fills.  Both sides list the cells of a pair in the same
+ * (global id) order.  nIndependent: the first nIndependent local cells have no received cell in their reconstruction
+ * stencil (their gradients are computed while an exchange is in flight); 0 = no overlap of compute and exchange */
 int cfb200_set_halo(cfb200_handle* h, const int32_t* sendPtr, const int32_t* sendCells,
-                    const int32_t* recvPtr, const int32_t* recvCells);
+                    const int32_t* recvPtr, const int32_t* recvCells, int32_t nIndependent);
+/* starts the exchange (pack kernel, NCCL send/recv group and unpack kernel on a communication stream) and returns;
+ * the next cfb200_compute_rhs overlaps it with the work that does not depend on received states */
+int cfb200_halo_begin(cfb200_handle* h);
+/* begin + wait: the overlap states are in place when it returns */
 int cfb200_halo_exchange(cfb200_handle* h);
+/* sum over ranks of n <= 64 host doubles (residual norms; replaces the MPI_Allreduce of ComputeL2Norm.cxx:127-137) */
 int cfb200_allreduce_sum(cfb200_handle* h, double* v, int n);
 
 /* ---- host-side mesh-data construction (replaces FVMCC_MeshDataBuilder.cxx:91-499, ComputeFaceNormals*P1,
