@@ -37,6 +37,9 @@ class ConfigStruct(C.Structure):
         ("muRef", C.c_double), ("tempRef", C.c_double), ("pRef", C.c_double), ("artDiffCoeff", C.c_double),
         ("viscRef", C.c_double), ("viscTRef", C.c_double), ("viscSuthConst", C.c_double),
         ("fixedVisc", C.c_double), ("cfl", C.c_double),
+        ("choiceA12", C.c_int32), ("reservedI", C.c_int32),
+        ("ausmBeta", C.c_double), ("ausmAlpha", C.c_double),
+        ("ausmKu", C.c_double), ("ausmKp", C.c_double), ("ausmSigma", C.c_double), ("machInf", C.c_double),
     ]
 
 
@@ -111,6 +114,14 @@ def make_config(dim, update_var=UV_CONS, flux=FS_ROE, poly_rec=PR_CONSTANT, limi
     c.viscSuthConst = kw.get("visc_suth_const", 120.0)
     c.fixedVisc = kw.get("fixed_visc", 1.0)
     c.cfl = cfl
+    # AUSM family defaults: AUSMFlux.ci:55, AUSMPlusFlux.ci:17-23, AUSMPlusUpFlux.ci:20-33
+    c.choiceA12 = int(kw.get("choice_a12", 1))
+    c.ausmBeta = kw.get("ausm_beta", 1.0/8.0)
+    c.ausmAlpha = kw.get("ausm_alpha", 3.0/16.0)
+    c.ausmKu = kw.get("coeff_ku", 0.75)
+    c.ausmKp = kw.get("coeff_kp", 0.25)
+    c.ausmSigma = kw.get("sigma", 1.0)
+    c.machInf = kw.get("mach_inf", 0.0)
     return c
 
 

@@ -18,6 +18,14 @@
 
 namespace cfb {
 
+// Roe; AUSM+ and AUSM+up with the perfect-gas interface sound speeds (choiceA12 4/5 are the TCNEQ variants).
+inline bool splitterSupported(const cfb200_config& c) {
+  if (c.fluxSplitter == CFB200_FS_ROE) return true;
+  if (c.fluxSplitter == CFB200_FS_AUSMPLUS || c.fluxSplitter == CFB200_FS_AUSMPLUSUP)
+    return c.choiceA12 >= 1 && c.choiceA12 <= 3 && (c.fluxSplitter == CFB200_FS_AUSMPLUS || c.machInf > 0.);
+  return false;
+}
+
 struct DeviceError : std::runtime_error {
   int code;
   DeviceError(int c, const std::string& what) : std::runtime_error(what), code(c) {}
@@ -262,10 +270,12 @@ public:
     if (cfg.polyRec == CFB200_PR_LINEARLS && cfg.limiter != CFB200_LIM_NONE)
       bk.launch("limiter", LimiterK<D>{d, cfg}, d.nCells, 128);
     if (doJac) {
-      bk.launchStaged("innerFaceJac", InnerFaceK<D, true>{d, cfg}, d.nInner, faceShape);
+      if (cfg.fluxSplitter == CFB200_FS_ROE) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 0>{d, cfg}, d.nInner, faceShape);
+      else bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 1>{d, cfg}, d.nInner, faceShape);
       bk.launch("boundaryFaceJac", BoundaryFaceK<D, true>{d, cfg}, d.nGhosts, 128);
     } else {
-      bk.launch("innerFace", InnerFaceK<D, false>{d, cfg}, d.nInner, 128);
+      if (cfg.fluxSplitter == CFB200_FS_ROE) bk.launch("innerFace", InnerFaceK<D, false, 0>{d, cfg}, d.nInner, 128);
+      else bk.launch("innerFace", InnerFaceK<D, false, 1>{d, cfg}, d.nInner, 128);
       bk.launch("boundaryFace", BoundaryFaceK<D, false>{d, cfg}, d.nGhosts, 128);
     }
     bk.launch("cellGather", CellGather<D>{d, cfg}, d.nCells, 256);

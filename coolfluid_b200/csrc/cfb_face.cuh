@@ -206,7 +206,7 @@ struct FaceWork {
   // update coefficients (RoeFlux.cxx:165-185, NSFlux.ci:127-152).
   CFB_HD void baseFlux(const Dev& d, const Cfg& c, const double* sL, const double* sR, const typename P::Side& a,
                        const typename P::Side& b, bool hasDiff, double* flux, double& ucL, double& ucR, double& ucD) {
-    if (!P::roe(c, a, b, n, flux)) {
+    if (!P::numFlux(c, a, b, n, flux)) {
       *d.status = CFB200_ERR_BAD_VALUE;
 #pragma unroll
       for (int v = 0; v < Q; ++v) flux[v] = 0.;
@@ -281,6 +281,8 @@ struct FaceWork {
   // Convective part: it = -1 is the base evaluation (-> flux, faceFlux), it = 0..2q-1 perturbs variable it%q of side
   // it/q (FVMCC_ComputeRhsJacob.cxx:126-236,321-365; frozen gradient/limiter, LeastSquareP1PolyRec2D.cxx:221-262):
   //   pf = F_c*area - staged F_d ;  column <- sgn * resFactor * (pf - flux)/eps  (row-major q x q, BlockAccumulator.hh:289-296)
+  // FS = 0: Roe (fixed side parked as s | z | f);  FS = 1: AUSM family (fixed side parked as rho p H a v[3])
+  template <int FS>
   CFB_HD void innerConvective(const Dev& d, const Cfg& c, const double* sL, const double* sR, const double* vL,
                               const double* vR, bool hasDiff, const double* dfluxBase, bool jac,
                               double* stg, int stride) const {
@@ -300,10 +302,18 @@ struct FaceWork {
         double vF[Q];
 #pragma unroll
         for (int v = 0; v < Q; ++v) vF[v] = side ? vL[v] : vR[v];
-        typename P::SideLite fixed;
-        P::sideLite(c, vF, n, fixed);              // the unperturbed other side
+        if constexpr (FS == 0) {
+          typename P::SideLite fixed;
+          P::sideLite(c, vF, n, fixed);              // the unperturbed other side
 #pragma unroll
-        for (int v = 0; v < Q; ++v) { fx[(size_t)v*fs] = fixed.s[v]; fx[(size_t)(Q + v)*fs] = fixed.z[v]; fx[(size_t)(2*Q + v)*fs] = fixed.f[v]; }
+          for (int v = 0; v < Q; ++v) { fx[(size_t)v*fs] = fixed.s[v]; fx[(size_t)(Q + v)*fs] = fixed.z[v]; fx[(size_t)(2*Q + v)*fs] = fixed.f[v]; }
+        } else {
+          typename P::ASide fixed;
+          P::aside(c, vF, fixed);
+          fx[0] = fixed.rho; fx[(size_t)fs] = fixed.p; fx[(size_t)2*fs] = fixed.H; fx[(size_t)3*fs] = fixed.A;
+#pragma unroll
+          for (int k = 0; k < 3; ++k) fx[(size_t)(4 + k)*fs] = fixed.v[k];
+        }
       }
       double orig = 0., gp = 0.;
 #pragma unroll
@@ -317,13 +327,26 @@ struct FaceWork {
       double vp[Q];
 #pragma unroll
       for (int v = 0; v < Q; ++v) { const double base = side ? vR[v] : vL[v]; vp[v] = (v == iVar) ? pvr : base; }
-      typename P::SideLite pert;
-      P::sideLite(c, vp, n, pert);
       double pf[Q];
-      if (!P::roeOriented(c, pert, fx, fs, side == 0, n, pf)) {
-        *d.status = CFB200_ERR_BAD_VALUE;
+      if constexpr (FS == 0) {
+        typename P::SideLite pert;
+        P::sideLite(c, vp, n, pert);
+        if (!P::roeOriented(c, pert, fx, fs, side == 0, n, pf)) {
+          *d.status = CFB200_ERR_BAD_VALUE;
 #pragma unroll
-        for (int v = 0; v < Q; ++v) pf[v] = 0.;
+          for (int v = 0; v < Q; ++v) pf[v] = 0.;
+        }
+      } else {
+        typename P::ASide pert, l, r;
+        P::aside(c, vp, pert);
+        const bool pl = (side == 0);
+        { const double x = fx[0];              l.rho = pl ? pert.rho : x; r.rho = pl ? x : pert.rho; }
+        { const double x = fx[(size_t)fs];     l.p = pl ? pert.p : x;     r.p = pl ? x : pert.p; }
+        { const double x = fx[(size_t)2*fs];   l.H = pl ? pert.H : x;     r.H = pl ? x : pert.H; }
+        { const double x = fx[(size_t)3*fs];   l.A = pl ? pert.A : x;     r.A = pl ? x : pert.A; }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { const double x = fx[(size_t)(4 + k)*fs]; l.v[k] = pl ? pert.v[k] : x; r.v[k] = pl ? x : pert.v[k]; }
+        P::ausm(c, l, r, n, pf);
       }
       if (iVar < 0) {
 #pragma unroll
@@ -398,7 +421,7 @@ struct FaceWork {
       typename P::Side pert;
       P::side(c, vp, n, pert);
       double pf[Q];
-      const bool ok = (SIDE == 0) ? P::roe(c, pert, fixed, n, pf) : P::roe(c, fixed, pert, n, pf);
+      const bool ok = (SIDE == 0) ? P::numFlux(c, pert, fixed, n, pf) : P::numFlux(c, fixed, pert, n, pf);
       if (!ok) {
         *d.status = CFB200_ERR_BAD_VALUE;
 #pragma unroll
@@ -425,8 +448,8 @@ struct FaceWork {
 // these and are gathered by DiagGather.  One-sided updatable faces (partition overlap) use the same values
 // (FVMCC_ComputeRhsJacob.cxx:184-236: row idx receives (-1)^idx * resFactor * dF/dU); the blocks that land in
 // non-updatable rows are staging for DiagGather and are zeroed afterwards by ZeroRows.
-template <int D, bool JAC>
-struct InnerFaceK {   // idx over interior faces
+template <int D, bool JAC, int FS = 0>
+struct InnerFaceK {   // idx over interior faces; FS = 0 Roe, 1 AUSM+ / AUSM+up
   static constexpr int Q = D + 2;
   static constexpr int BLK = Q*Q;
   static constexpr int NOUT = 2*Q*Q;    // per-thread staging (shared memory, entry k at stg[k*stride]): block(R,L) | block(L,R)
@@ -469,7 +492,7 @@ struct InnerFaceK {   // idx over interior faces
     for (int v = 0; v < Q; ++v) dfluxBase[v] = 0.;
     if (hasDiff) w.innerDiffusive(d, c, sL, sR, JAC, dfluxBase, ucD, stg, stride);
     d.ucD[f] = ucD;
-    w.innerConvective(d, c, sL, sR, vL, vR, hasDiff, dfluxBase, JAC, stg, stride);
+    w.template innerConvective<FS>(d, c, sL, sR, vL, vR, hasDiff, dfluxBase, JAC, stg, stride);
   }
 };
 
@@ -528,7 +551,7 @@ struct BoundaryFaceK {   // idx over boundary faces
       P::side(c, vL, w.n, a);
       P::side(c, vR, w.n, b);
       double pf[Q];
-      if (!P::roe(c, a, b, w.n, pf)) {
+      if (!P::numFlux(c, a, b, w.n, pf)) {
         *d.status = CFB200_ERR_BAD_VALUE;
 #pragma unroll
         for (int v = 0; v < Q; ++v) pf[v] = 0.;

@@ -293,6 +293,80 @@ struct Phys {
     return true;
   }
 
+  // ---- AUSM family ---------------------------------------------------------
+  // AUSMFlux.hh:147-174 (pow(x,2.) is folded to x*x by the compiler)
+  static double mach1Plus(double m) { return 0.5*(m + std::abs(m)); }
+  static double mach1Min(double m) { return 0.5*(m - std::abs(m)); }
+  static double mach2Plus(double m) { return 0.25*((m + 1.0)*(m + 1.0)); }
+  static double mach2Min(double m) { return -0.25*((m - 1.0)*(m - 1.0)); }
+
+  // AUSMFlux.ci:547-581 computeInterfaceSoundSpeed -> computeSoundSpeed1/2/3 (:585-646)
+  static double ausmSoundSpeed(const Config& c, const PData& L, const PData& R, double unL, double unR) {
+    switch (c.choiceA12) {
+      case 2: return 0.5*(L.A + R.A);
+      case 3: return std::sqrt(L.A*R.A);
+      default: {
+        const double gammaL = c.gamma, gammaMinus1L = gammaL - 1.0;
+        const double gammaR = c.gamma, gammaMinus1R = gammaR - 1.0;
+        const double aCritL = std::sqrt((2.0*gammaMinus1L/(gammaL + 1.0))*L.H);
+        const double aCritR = std::sqrt((2.0*gammaMinus1R/(gammaR + 1.0))*R.H);
+        const double acL = (aCritL*aCritL)/std::max(aCritL, unL);
+        const double acR = (aCritR*aCritR)/std::max(aCritR, -unR);
+        return std::min(acL, acR);
+      }
+    }
+  }
+
+  // AUSMFlux.ci:123-222 compute (single Euler set, no mesh speed, no incompressible correction:
+  // AUSMFlux.hh:97 switches it off) with computeMassFlux / computePressureFlux of
+  // AUSMPlusFlux.ci:47-105 (FS_AUSMPLUS) or AUSMPlusUpFlux.ci:50-135 (FS_AUSMPLUSUP), and
+  // computeMassFluxImpl AUSMFlux.ci:497-543.  Flux per unit area.
+  static bool ausmFlux(const Config& c, const PData& L, const PData& R, const double* n, double* result) {
+    double unL = 0.0, unR = 0.0;
+    for (int i = 0; i < D; ++i) { unL += L.v[i]*n[i]; unR += R.v[i]*n[i]; }
+    const double a12 = ausmSoundSpeed(c, L, R, unL, unR);
+    const double mL = unL/a12, mR = unR/a12;
+    const double rhoL = L.rho, rhoR = R.rho, pL = L.p, pR = R.p;
+    double mflux12, p12;
+    if (c.fluxSplitter == FS_AUSMPLUS) {
+      const double beta = c.ausmBeta, alpha = c.ausmAlpha;
+      const double sqL = (mL*mL - 1.0)*(mL*mL - 1.0), sqR = (mR*mR - 1.0)*(mR*mR - 1.0);
+      const double M4Plus = (std::abs(mL) >= 1.0) ? mach1Plus(mL) : mach2Plus(mL) + beta*sqL;
+      const double M4Minus = (std::abs(mR) >= 1.0) ? mach1Min(mR) : mach2Min(mR) - beta*sqR;
+      const double m12 = M4Plus + M4Minus;
+      mflux12 = (m12 > 0.0) ? a12*m12*rhoL : a12*m12*rhoR;
+      const double P5Plus = (std::abs(mL) >= 1.0) ? 0.5*(1 + ((mL < 0.0) ? -1.0 : 1.0)) :
+        mach2Plus(mL)*(2.0 - mL) + alpha*mL*sqL;
+      const double P5Minus = (std::abs(mR) >= 1.0) ? 0.5*(1 - ((mR < 0.0) ? -1.0 : 1.0)) :
+        -mach2Min(mR)*(2.0 + mR) - alpha*mR*sqR;
+      p12 = P5Plus*pL + P5Minus*pR;
+    } else {
+      const double beta = c.ausmBeta;
+      const double mBarSq = (unL*unL + unR*unR)/(2.0*a12*a12);
+      const double mInf = c.machInf;
+      const double mZero = std::sqrt(std::min(1.0, std::max(mBarSq, mInf*mInf)));
+      const double fa = mZero*(2.0 - mZero);
+      const double M4Plus = (std::abs(mL) >= 1.0) ? mach1Plus(mL) : mach2Plus(mL)*(1.0 - 16.*beta*mach2Min(mL));
+      const double M4Minus = (std::abs(mR) >= 1.0) ? mach1Min(mR) : mach2Min(mR)*(1.0 + 16.*beta*mach2Plus(mR));
+      const double rhoa2 = 0.5*(rhoL + rhoR)*a12*a12;
+      const double mP = (-c.ausmKp/fa)*std::max(1.0 - c.ausmSigma*mBarSq, 0.0)*(pR - pL)/rhoa2;
+      const double m12 = M4Plus + M4Minus + mP;
+      mflux12 = (m12 > 0.0) ? a12*m12*rhoL : a12*m12*rhoR;
+      const double alpha = (3.0/16.0)*(-4.0 + 5.0*fa*fa);
+      const double P5Plus = (std::abs(mL) >= 1.0) ? mach1Plus(mL)/mL :
+        mach2Plus(mL)*((2.0 - mL) - 16.*alpha*mL*mach2Min(mL));
+      const double P5Minus = (std::abs(mR) >= 1.0) ? mach1Min(mR)/mR :
+        mach2Min(mR)*((-2.0 - mR) + 16.*alpha*mR*mach2Plus(mR));
+      const double pU = -c.ausmKu*P5Plus*P5Minus*(rhoL + rhoR)*fa*a12*(unR - unL);
+      p12 = P5Plus*pL + P5Minus*pR + pU;
+    }
+    const PData& up = (mflux12 > 0.0) ? L : R;
+    result[0] = mflux12;
+    for (int i = 0; i < D; ++i) result[1+i] = mflux12*up.v[i] + p12*n[i];
+    result[TID] = mflux12*up.H;
+    return true;
+  }
+
   // ---- Navier-Stokes -------------------------------------------------------
   // SimplerSutherlandDynViscosity.cxx:104-107, SutherlandDynViscosity.cxx:107-110
   static double dynViscosityDim(const Config& c, double /*pdim*/, double Tdim) {

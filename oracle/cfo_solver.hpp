@@ -369,7 +369,11 @@ public:
     P::computePhysicalData(cfg, x.vL, x.pL);   // computeStatesData, FVMCC_ComputeRHS.hh:112-118
     P::computePhysicalData(cfg, x.vR, x.pR);
     for (int i = 0; i < Q; ++i) flux[i] = 0.;
-    if (!P::roeFlux(cfg, x.vL, x.vR, x.pL, x.pR, x.n, flux)) { o.status = 1; return false; }
+    if (cfg.fluxSplitter == FS_ROE) {
+      if (!P::roeFlux(cfg, x.vL, x.vR, x.pL, x.pR, x.n, flux)) { o.status = 1; return false; }
+    } else {
+      P::ausmFlux(cfg, x.pL, x.pR, x.n, flux);      // update coefficient: AUSMFlux.ci:410-440, same form as Roe's
+    }
     if (!isPerturb) {
       const double faceArea = x.area/1;       // polyRec->nbQPoints() == 1
       double maxEV = P::maxEigenValue(x.pL, x.n);

@@ -88,6 +88,11 @@ struct Config {
   double coeffTau, coeffQ, cpOverPrandtl, muRef /*refDataDiff[MU]*/, tempRef, pRef, artDiffCoeff;
   double viscRef, viscTRef, viscSuthConst, fixedVisc;
   double cfl;             // for the pseudo-steady time term
+  // AUSM family (FiniteVolumeNavierStokes/AUSMFlux.ci:55, AUSMPlusFlux.ci:17-23, AUSMPlusUpFlux.ci:20-33)
+  int32_t choiceA12;      // interface sound speed: 1 Liou critical, 2 arithmetic mean, 3 geometric mean
+  int32_t reservedI;
+  double ausmBeta, ausmAlpha;                 // AUSM+ : 1/8, 3/16
+  double ausmKu, ausmKp, ausmSigma, machInf;  // AUSM+up : 0.75, 0.25, 1.0, (required > 0)
 };
 
 struct MeshView {

@@ -113,6 +113,21 @@ CASES = {
     "euler3d_cons_tet": (lambda: meshgen.tet_box(3, 3, 3),
                          lambda: B.make_config(3, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, jacobian=True),
                          bcs_euler3d, False),
+    # a12: AUSM+ (2D Euler, cons, 1st order; 3D NS Pvt 2nd order) and AUSM+up (jets2DFVMImplAUSMAnalytic-like options,
+    # numerical Jacobian), all three perfect-gas interface sound speeds
+    "euler2d_ausmplus_1st": (lambda: meshgen.quad_channel(12, 9),
+                             lambda: B.make_config(2, flux=B.FS_AUSMPLUS, jacobian=True), bcs_euler2d, False),
+    "euler2d_ausmplusup_2nd_tri": (lambda: meshgen.quad_channel(12, 9, triangles=True),
+                                   lambda: B.make_config(2, flux=B.FS_AUSMPLUSUP, poly_rec=B.PR_LINEARLS,
+                                                         limiter=B.LIM_VENKTN, jacobian=True, mach_inf=2.0, choice_a12=1),
+                                   bcs_euler2d, False),
+    "ns3d_hex_ausmplusup": (lambda: meshgen.hex_box(6, 5, 4), lambda: ns3d_cfg(flux=B.FS_AUSMPLUSUP, mach_inf=0.35),
+                            bcs_ns3d, True),
+    "ns3d_tet_ausmplus_a2": (lambda: meshgen.tet_box(3, 3, 3), lambda: ns3d_cfg(flux=B.FS_AUSMPLUS, choice_a12=2),
+                             bcs_ns3d, True),
+    "euler3d_ausmplusup_a3": (lambda: meshgen.tet_box(3, 3, 3),
+                              lambda: B.make_config(3, flux=B.FS_AUSMPLUSUP, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN,
+                                                    jacobian=True, mach_inf=0.8, choice_a12=3), bcs_euler3d, False),
     # single cell / single row edge cases
     "ns3d_single_cell": (lambda: meshgen.hex_box(1, 1, 1, jitter=0.0), ns3d_cfg, bcs_ns3d, True),
     "euler2d_single_row": (lambda: meshgen.quad_channel(5, 1), lambda: B.make_config(2, poly_rec=B.PR_LINEARLS,

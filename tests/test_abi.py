@@ -54,6 +54,8 @@ def test_invalid_arguments(product_lib):
     cfg = B.make_config(2)
     cfg.nEqs = 7
     assert product_lib.create(C.byref(cfg), 0, C.byref(h)) == 2
-    cfg = B.make_config(2, flux=B.FS_AUSMPLUS)
+    cfg = B.make_config(2, flux=B.FS_AUSMPLUS, choice_a12=5)      # TCNEQ interface sound speed: unsupported
+    assert product_lib.create(C.byref(cfg), 0, C.byref(h)) == 6
+    cfg = B.make_config(2, flux=B.FS_AUSMPLUSUP)                  # AUSM+up needs machInf > 0 (AUSMPlusUpFlux.ci:55-57)
     assert product_lib.create(C.byref(cfg), 0, C.byref(h)) == 6
     assert product_lib.compute_rhs(None, 1, None, None) == 2
