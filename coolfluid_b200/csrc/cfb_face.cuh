@@ -36,12 +36,10 @@ struct FaceWork {
   CFB_HD void load(const Dev& d, const Cfg& c, int face) {
     f = face; L = d.faceL[f]; R = d.faceR[f]; isB = (R >= d.nCells);
     area = d.areas[f];
-    const double invArea = ddiv(1., area);
-    double xq[3] = {0., 0., 0.}, xL[3] = {0., 0., 0.}, xR[3] = {0., 0., 0.};
-    n[2] = 0.;
+    double xq[3] = {0., 0., 0.}, xL[3] = {0., 0., 0.}, xR[3] = {0., 0., 0.}, nr[3] = {0., 0., 0.};
 #pragma unroll
     for (int k = 0; k < D; ++k) {
-      n[k] = d.normals[(size_t)k*d.nFaces + f]*invArea;
+      nr[k] = d.normals[(size_t)k*d.nFaces + f];
       xL[k] = d.centres[(size_t)k*d.nStates + L];
       xR[k] = d.centres[(size_t)k*d.nStates + R];
     }
@@ -54,26 +52,38 @@ struct FaceWork {
       const int gradR = isB ? L : R;
       const int32_t* zg = isB ? d.bcs[d.faceBC[f]].zeroGrad : nullptr;
       const bool stop = (c.stopLimiting != 0);
+      // every gather of the face is issued before the first use (one memory round trip instead of one per variable:
+      // with ~8 resident warps per SM the latency of a dependent chain of gathers is not hidden by other warps)
+      double gxL[Q], gyL[Q], gzL[Q], gxR[Q], gyR[Q], gzR[Q], lmL[Q], lmR[Q];
+#pragma unroll
+      for (int v = 0; v < Q; ++v) {
+        const size_t iL = (size_t)v*d.nCells + L, iR = (size_t)v*d.nCells + gradR;
+        gxL[v] = d.uX[iL]; gyL[v] = d.uY[iL]; gxR[v] = d.uX[iR]; gyR[v] = d.uY[iR];
+        if (D == 3) { gzL[v] = d.uZ[iL]; gzR[v] = d.uZ[iR]; } else { gzL[v] = 0.; gzR[v] = 0.; }
+        lmL[v] = stop ? 1. : d.lim[iL];
+        lmR[v] = stop ? 1. : d.lim[iR];
+      }
 #pragma unroll
       for (int v = 0; v < Q; ++v) {
         const bool z = zg && zg[v];
         double gcS = 0.0, gcN = 0.0;
         if (!z) {
-          const size_t iL = (size_t)v*d.nCells + L, iR = (size_t)v*d.nCells + gradR;
           if (D == 2) {
-            gcS = c.gradientFactor*(d.uX[iL]*(xq[0] - xL[0]) + d.uY[iL]*(xq[1] - xL[1]));
-            gcN = c.gradientFactor*(d.uX[iR]*(xq[0] - xR[0]) + d.uY[iR]*(xq[1] - xR[1]));
+            gcS = c.gradientFactor*(gxL[v]*(xq[0] - xL[0]) + gyL[v]*(xq[1] - xL[1]));
+            gcN = c.gradientFactor*(gxR[v]*(xq[0] - xR[0]) + gyR[v]*(xq[1] - xR[1]));
           } else {
-            gcS = c.gradientFactor*(d.uX[iL]*(xq[0] - xL[0]) + d.uY[iL]*(xq[1] - xL[1]) + d.uZ[iL]*(xq[2] - xL[2]));
-            gcN = c.gradientFactor*(d.uX[iR]*(xq[0] - xR[0]) + d.uY[iR]*(xq[1] - xR[1]) + d.uZ[iR]*(xq[2] - xR[2]));
+            gcS = c.gradientFactor*(gxL[v]*(xq[0] - xL[0]) + gyL[v]*(xq[1] - xL[1]) + gzL[v]*(xq[2] - xL[2]));
+            gcN = c.gradientFactor*(gxR[v]*(xq[0] - xR[0]) + gyR[v]*(xq[1] - xR[1]) + gzR[v]*(xq[2] - xR[2]));
           }
         }
-        const double lValue = stop ? 1. : d.lim[(size_t)v*d.nCells + L];
-        const double rValue = stop ? 1. : d.lim[(size_t)v*d.nCells + gradR];
-        gL[v] = lValue*gcS;
-        gR[v] = rValue*gcN;
+        gL[v] = lmL[v]*gcS;
+        gR[v] = lmR[v]*gcN;
       }
     }
+    const double invArea = ddiv(1., area);
+    n[2] = 0.;
+#pragma unroll
+    for (int k = 0; k < D; ++k) n[k] = nr[k]*invArea;
   }
 
   CFB_HD void reconstruct(const Cfg& c, const double* sL, const double* sR, double* vL, double* vR) const {
@@ -97,22 +107,32 @@ struct FaceWork {
 
   // a15: control volume of the face, DiamondVolume2DDerivative.cxx:91-137, DiamondVolume3DDerivative.cxx:336-411,
   // and the nodal part of the control-volume states.
-  CFB_HD void loadDiamond(const Dev& d) {
-    double xL[3] = {0., 0., 0.}, xR[3] = {0., 0., 0.};
+  // Raw loads of the diamond (face nodes: coordinates + nodal states; the two cell centres).  Separate from the
+  // arithmetic so that the interior-face kernel can issue them together with the other gathers of its prologue.
+  struct DiamondRaw { double xL[3], xR[3], xn[NMAX][3]; };
+  CFB_HD void fetchDiamond(const Dev& d, DiamondRaw& w) {
 #pragma unroll
-    for (int k = 0; k < D; ++k) { xL[k] = d.centres[(size_t)k*d.nStates + L]; xR[k] = d.centres[(size_t)k*d.nStates + R]; }
+    for (int k = 0; k < 3; ++k) { w.xL[k] = 0.; w.xR[k] = 0.; }
+#pragma unroll
+    for (int k = 0; k < D; ++k) { w.xL[k] = d.centres[(size_t)k*d.nStates + L]; w.xR[k] = d.centres[(size_t)k*d.nStates + R]; }
     const int b = d.faceNodePtr[f];
     nbN = d.faceNodePtr[f+1] - b;
-    double xn[NMAX][3];
+    int node[NMAX];
+#pragma unroll
+    for (int j = 0; j < NMAX; ++j) node[j] = d.faceNodes[b + ((j < nbN) ? j : nbN - 1)];
 #pragma unroll
     for (int j = 0; j < NMAX; ++j) {
-      const int node = d.faceNodes[b + ((j < nbN) ? j : nbN - 1)];
-      xn[j][2] = 0.;
+      w.xn[j][2] = 0.;
 #pragma unroll
-      for (int k = 0; k < D; ++k) xn[j][k] = d.nodes[(size_t)k*d.nNodes + node];
+      for (int k = 0; k < D; ++k) w.xn[j][k] = d.nodes[(size_t)k*d.nNodes + node[j]];
 #pragma unroll
-      for (int v = 0; v < Q; ++v) val[v][j] = d.nstates[(size_t)v*d.nNodes + node];
+      for (int v = 0; v < Q; ++v) val[v][j] = d.nstates[(size_t)v*d.nNodes + node[j]];
     }
+  }
+  CFB_HD void loadDiamond(const Dev& d) { DiamondRaw w; fetchDiamond(d, w); buildDiamond(d, w); }
+  CFB_HD void buildDiamond(const Dev& d, const DiamondRaw& w) {
+    const double* xL = w.xL; const double* xR = w.xR;
+    const double (*xn)[3] = w.xn;
     if constexpr (D == 2) {
       const double* node0 = xn[0]; const double* node1 = xL; const double* node2 = xn[1]; const double* node3 = xR;
       cvn[0][0] = -node0[1] + node1[1]; cvn[0][1] = -node1[0] + node0[0];
@@ -238,8 +258,8 @@ struct FaceWork {
   // Diffusive part first: base diffusive flux + ucD, then (JAC) the 2q perturbed diffusive fluxes staged into the
   // two output blocks (column iVar of blkRL for side L, of blkLR for side R).
   CFB_HD void innerDiffusive(const Dev& d, const Cfg& c, const double* sL, const double* sR, bool jac,
-                             double* dfluxBase, double& ucD, double* stg, int stride) {
-    loadDiamond(d);
+                             const DiamondRaw& raw, double* dfluxBase, double& ucD, double* stg, int stride) {
+    buildDiamond(d, raw);
     setCellStates(sL, sR);
     allGrads();
     transport(c);
@@ -469,11 +489,16 @@ struct InnerFaceK {   // idx over interior faces; FS = 0 Roe, 1 AUSM+ / AUSM+up
       if (JAC) for (int k = 0; k < NOUT; ++k) stg[(size_t)k*stride] = 0.;
       return;
     }
+    // prologue: every gather of the face (states, diamond nodes, gradients, limiters) is issued before the first
+    // arithmetic that depends on one of them
     FaceWork<D> w;
-    w.load(d, c, f);
+    w.f = f; w.L = L; w.R = R;
     double sL[Q], sR[Q], vL[Q], vR[Q];
 #pragma unroll
     for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + L]; sR[v] = d.U[(size_t)v*d.nStates + R]; }
+    typename FaceWork<D>::DiamondRaw raw;
+    if (hasDiff) w.fetchDiamond(d, raw);                   // consumed by innerDiffusive
+    w.load(d, c, f);
     w.reconstruct(c, sL, sR, vL, vR);
     {
       // update coefficients, RoeFlux.cxx:165-185 (one quadrature point per face)
@@ -490,7 +515,7 @@ struct InnerFaceK {   // idx over interior faces; FS = 0 Roe, 1 AUSM+ / AUSM+up
     double dfluxBase[Q], ucD = 0.;
 #pragma unroll
     for (int v = 0; v < Q; ++v) dfluxBase[v] = 0.;
-    if (hasDiff) w.innerDiffusive(d, c, sL, sR, JAC, dfluxBase, ucD, stg, stride);
+    if (hasDiff) w.innerDiffusive(d, c, sL, sR, JAC, raw, dfluxBase, ucD, stg, stride);
     d.ucD[f] = ucD;
     w.template innerConvective<FS>(d, c, sL, sR, vL, vR, hasDiff, dfluxBase, JAC, stg, stride);
   }
