@@ -34,6 +34,25 @@ UNIT = "cells/s"
 A_RHS, A_JAC = 744, 1400
 
 
+# Compulsory bytes of the interior-face Jacobian kernel per face: per-face arrays once (normal 24, area 8,
+# face centre 24, L/R ids 8, node ptr 8, node ids 16, diamond volume 8, two BSR slots 8 = 104), per-cell arrays once per
+# cell = 1/3 per face (state 40, gradients 120, limiter 40, centre 24 -> 75), per-node arrays once per node = 1/3 per face
+# (coordinates 24, nodal state 40 -> 21), writes: two 5x5 blocks 400, face flux 40, three update coefficients 24.
+INNER_FACE_JAC_BYTES = 104 + 75 + 21 + 400 + 40 + 24
+
+
+def measured_traffic(kernel, items):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch from the committed `ncu --set full` capture
+    (profiles/traffic.json: bytes per item measured at the capture's size), scaled to this launch's item count."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(p):
+        return None, None
+    t = json.load(open(p)).get(kernel)
+    if not t:
+        return None, None
+    return int(t["bytes_per_item"]*items), t["source"]
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -164,6 +183,7 @@ def main():
     ap.add_argument("--impl", default="cfb200")
     ap.add_argument("--n", "--edge", dest="n", type=int, default=220, help="hex box edge per GPU (220^3 = 10.6 M cells, configs[2])")
     ap.add_argument("--cpu-sample", type=int, default=36, help="edge of the per-thread hex box of the CPU baseline")
+    ap.add_argument("--cpu-evals", type=int, default=24, help="evaluations per thread of the cpu_baseline leg (~10-20 s)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -275,10 +295,10 @@ def main():
         # algorithmic bytes of the dominant kernel per launch (DESIGN.md "kernels"): the interior-face FD Jacobian
         # writes two q x q blocks per interior face and reads both cell states, gradients, limiters, the face flux,
         # normal, area and the 4 nodal states: see DESIGN.md for the per-face count
-        per_launch = {"innerFacePert": fm.nInner*(2*25*8 + 2*5*8 + 2*(3*5*8 + 5*8) + 5*8 + 3*8 + 8 + 8 + 8),
-                      "innerFaceBase": fm.nInner*(2*5*8 + 2*(3*5*8 + 5*8) + 5*8 + 4*5*8 + 3*8 + 8 + 8 + 8)}
+        per_launch = {"innerFaceJac": fm.nInner*INNER_FACE_JAC_BYTES}
         algo = per_launch.get(top, nc*(A_RHS + A_JAC))
         achieved = algo/(kavg[top]*1e-3)/1e9
+        traffic, traffic_src = measured_traffic(top, fm.nInner if top == "innerFaceJac" else nc)
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
@@ -296,7 +316,8 @@ def main():
             "gpu_launches": int(launches[0]),
             "kernels_ms": {k: round(v, 4) for k, v in sorted(kavg.items(), key=lambda kv: -kv[1])},
             "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved/peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved/peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": int(algo), "avg_launch_ms": kavg[top]},
             "step_roofline": {"bytes_per_cell": A_RHS + A_JAC, "achieved_gbs": (A_RHS + A_JAC)*value/world/1e9,
                               "frac_of_hbm_peak": (A_RHS + A_JAC)*value/world/1e9/peak},
@@ -304,10 +325,11 @@ def main():
         }
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
-            v, dt, ncs = cpu_baseline(args.cpu_sample, 1, threads)
+            v, dt, ncs = cpu_baseline(args.cpu_sample, args.cpu_evals, threads)
             out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                                    "sample": "%d independent partitions of %d^3 hex cells (one oracle instance per host "
-                                             "thread), 1 evaluation, %.1f s" % (threads, args.cpu_sample, dt)}
+                                             "thread), %d evaluations each, %.1f s" % (threads, args.cpu_sample,
+                                                                                       args.cpu_evals, dt)}
         print(json.dumps(out))
     eng.close()
     if dist is not None:

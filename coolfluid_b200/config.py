@@ -13,7 +13,7 @@ MAXEQ = 9
 
 # enums (must match include/cfb200.h and oracle/cfo_types.hpp)
 UV_CONS, UV_PVT = 0, 1
-FS_ROE, FS_AUSMPLUS, FS_AUSMPLUSUP = 0, 1, 2
+FS_ROE, FS_AUSMPLUS, FS_AUSMPLUSUP, FS_LAXFRIED, FS_HLL = 0, 1, 2, 3, 4
 PR_CONSTANT, PR_LINEARLS = 0, 1
 LIM_NONE, LIM_VENKTN, LIM_BARTHJESP = 0, 1, 2
 DIFF_NONE, DIFF_NS = 0, 1
@@ -37,7 +37,7 @@ class ConfigStruct(C.Structure):
         ("muRef", C.c_double), ("tempRef", C.c_double), ("pRef", C.c_double), ("artDiffCoeff", C.c_double),
         ("viscRef", C.c_double), ("viscTRef", C.c_double), ("viscSuthConst", C.c_double),
         ("fixedVisc", C.c_double), ("cfl", C.c_double),
-        ("choiceA12", C.c_int32), ("reservedI", C.c_int32),
+        ("choiceA12", C.c_int32), ("hllUseAlpha", C.c_int32),
         ("ausmBeta", C.c_double), ("ausmAlpha", C.c_double),
         ("ausmKu", C.c_double), ("ausmKp", C.c_double), ("ausmSigma", C.c_double), ("machInf", C.c_double),
     ]
@@ -116,6 +116,7 @@ def make_config(dim, update_var=UV_CONS, flux=FS_ROE, poly_rec=PR_CONSTANT, limi
     c.cfl = cfl
     # AUSM family defaults: AUSMFlux.ci:55, AUSMPlusFlux.ci:17-23, AUSMPlusUpFlux.ci:20-33
     c.choiceA12 = int(kw.get("choice_a12", 1))
+    c.hllUseAlpha = int(kw.get("hll_use_alpha", 0))
     c.ausmBeta = kw.get("ausm_beta", 1.0/8.0)
     c.ausmAlpha = kw.get("ausm_alpha", 3.0/16.0)
     c.ausmKu = kw.get("coeff_ku", 0.75)

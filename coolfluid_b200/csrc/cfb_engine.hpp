@@ -23,7 +23,13 @@ inline bool splitterSupported(const cfb200_config& c) {
   if (c.fluxSplitter == CFB200_FS_ROE) return true;
   if (c.fluxSplitter == CFB200_FS_AUSMPLUS || c.fluxSplitter == CFB200_FS_AUSMPLUSUP)
     return c.choiceA12 >= 1 && c.choiceA12 <= 3 && (c.fluxSplitter == CFB200_FS_AUSMPLUS || c.machInf > 0.);
+  if (c.fluxSplitter == CFB200_FS_LAXFRIED || c.fluxSplitter == CFB200_FS_HLL) return true;
   return false;
+}
+// kernel family of the splitter: 0 Roe, 1 AUSM+ / AUSM+up, 2 Lax-Friedrichs / HLL
+inline int splitterFamily(const cfb200_config& c) {
+  if (c.fluxSplitter == CFB200_FS_ROE) return 0;
+  return (c.fluxSplitter == CFB200_FS_LAXFRIED || c.fluxSplitter == CFB200_FS_HLL) ? 2 : 1;
 }
 
 struct DeviceError : std::runtime_error {
@@ -270,12 +276,16 @@ public:
     if (cfg.polyRec == CFB200_PR_LINEARLS && cfg.limiter != CFB200_LIM_NONE)
       bk.launch("limiter", LimiterK<D>{d, cfg}, d.nCells, 128);
     if (doJac) {
-      if (cfg.fluxSplitter == CFB200_FS_ROE) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 0>{d, cfg}, d.nInner, faceShape);
-      else bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 1>{d, cfg}, d.nInner, faceShape);
+      const int fam = splitterFamily(cfg);
+      if (fam == 0) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 0>{d, cfg}, d.nInner, faceShape);
+      else if (fam == 1) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 1>{d, cfg}, d.nInner, faceShape);
+      else bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 2>{d, cfg}, d.nInner, faceShape);
       bk.launch("boundaryFaceJac", BoundaryFaceK<D, true>{d, cfg}, d.nGhosts, 128);
     } else {
-      if (cfg.fluxSplitter == CFB200_FS_ROE) bk.launch("innerFace", InnerFaceK<D, false, 0>{d, cfg}, d.nInner, 128);
-      else bk.launch("innerFace", InnerFaceK<D, false, 1>{d, cfg}, d.nInner, 128);
+      const int fam = splitterFamily(cfg);
+      if (fam == 0) bk.launch("innerFace", InnerFaceK<D, false, 0>{d, cfg}, d.nInner, 128);
+      else if (fam == 1) bk.launch("innerFace", InnerFaceK<D, false, 1>{d, cfg}, d.nInner, 128);
+      else bk.launch("innerFace", InnerFaceK<D, false, 2>{d, cfg}, d.nInner, 128);
       bk.launch("boundaryFace", BoundaryFaceK<D, false>{d, cfg}, d.nGhosts, 128);
     }
     bk.launch("cellGather", CellGather<D>{d, cfg}, d.nCells, 256);

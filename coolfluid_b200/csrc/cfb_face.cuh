@@ -301,7 +301,8 @@ struct FaceWork {
   // Convective part: it = -1 is the base evaluation (-> flux, faceFlux), it = 0..2q-1 perturbs variable it%q of side
   // it/q (FVMCC_ComputeRhsJacob.cxx:126-236,321-365; frozen gradient/limiter, LeastSquareP1PolyRec2D.cxx:221-262):
   //   pf = F_c*area - staged F_d ;  column <- sgn * resFactor * (pf - flux)/eps  (row-major q x q, BlockAccumulator.hh:289-296)
-  // FS = 0: Roe (fixed side parked as s | z | f);  FS = 1: AUSM family (fixed side parked as rho p H a v[3])
+  // FS = 0: Roe (fixed side parked as s | z | f);  FS = 1: AUSM family (fixed side parked as rho p H a v[3]);
+  // FS = 2: Lax-Friedrichs / HLL (fixed side parked as f | s | un a)
   template <int FS>
   CFB_HD void innerConvective(const Dev& d, const Cfg& c, const double* sL, const double* sR, const double* vL,
                               const double* vR, bool hasDiff, const double* dfluxBase, bool jac,
@@ -327,6 +328,12 @@ struct FaceWork {
           P::sideLite(c, vF, n, fixed);              // the unperturbed other side
 #pragma unroll
           for (int v = 0; v < Q; ++v) { fx[(size_t)v*fs] = fixed.s[v]; fx[(size_t)(Q + v)*fs] = fixed.z[v]; fx[(size_t)(2*Q + v)*fs] = fixed.f[v]; }
+        } else if constexpr (FS == 2) {
+          typename P::CSide fixed;
+          P::cside(c, vF, n, fixed);
+#pragma unroll
+          for (int v = 0; v < Q; ++v) { fx[(size_t)v*fs] = fixed.f[v]; fx[(size_t)(Q + v)*fs] = fixed.s[v]; }
+          fx[(size_t)(2*Q)*fs] = fixed.un; fx[(size_t)(2*Q + 1)*fs] = fixed.A;
         } else {
           typename P::ASide fixed;
           P::aside(c, vF, fixed);
@@ -356,6 +363,19 @@ struct FaceWork {
 #pragma unroll
           for (int v = 0; v < Q; ++v) pf[v] = 0.;
         }
+      } else if constexpr (FS == 2) {
+        typename P::CSide pert, l, r;
+        P::cside(c, vp, n, pert);
+        const bool pl = (side == 0);
+#pragma unroll
+        for (int v = 0; v < Q; ++v) {
+          const double xf = fx[(size_t)v*fs], xs = fx[(size_t)(Q + v)*fs];
+          l.f[v] = pl ? pert.f[v] : xf; r.f[v] = pl ? xf : pert.f[v];
+          l.s[v] = pl ? pert.s[v] : xs; r.s[v] = pl ? xs : pert.s[v];
+        }
+        { const double x = fx[(size_t)(2*Q)*fs];     l.un = pl ? pert.un : x; r.un = pl ? x : pert.un; }
+        { const double x = fx[(size_t)(2*Q + 1)*fs]; l.A = pl ? pert.A : x;   r.A = pl ? x : pert.A; }
+        P::centred(c, l, r, pf);
       } else {
         typename P::ASide pert, l, r;
         P::aside(c, vp, pert);
@@ -469,7 +489,7 @@ struct FaceWork {
 // (FVMCC_ComputeRhsJacob.cxx:184-236: row idx receives (-1)^idx * resFactor * dF/dU); the blocks that land in
 // non-updatable rows are staging for DiagGather and are zeroed afterwards by ZeroRows.
 template <int D, bool JAC, int FS = 0>
-struct InnerFaceK {   // idx over interior faces; FS = 0 Roe, 1 AUSM+ / AUSM+up
+struct InnerFaceK {   // idx over interior faces; FS = 0 Roe, 1 AUSM+ / AUSM+up, 2 LaxFried / HLL
   static constexpr int Q = D + 2;
   static constexpr int BLK = Q*Q;
   static constexpr int NOUT = 2*Q*Q;    // per-thread staging (shared memory, entry k at stg[k*stride]): block(R,L) | block(L,R)

@@ -29,7 +29,9 @@ extern "C" {
 enum cfb200_update_var { CFB200_UV_CONS = 0 /* Euler2DCons, Euler3DCons */, CFB200_UV_PVT = 1 /* Euler2DPuvt, Euler3DPvt */ };
 enum cfb200_flux_splitter { CFB200_FS_ROE = 0 /* "Roe" plugins/FiniteVolume/RoeFlux.cxx */,
                             CFB200_FS_AUSMPLUS = 1 /* "AUSMPlus2D/3D" FiniteVolumeNavierStokes/AUSMPlusFlux.ci */,
-                            CFB200_FS_AUSMPLUSUP = 2 /* "AUSMPlusUp2D/3D" AUSMPlusUpFlux.ci:50-135 */ };
+                            CFB200_FS_AUSMPLUSUP = 2 /* "AUSMPlusUp2D/3D" AUSMPlusUpFlux.ci:50-135 */,
+                            CFB200_FS_LAXFRIED = 3 /* "LaxFried" plugins/FiniteVolume/LaxFriedFlux.cxx:79-190 */,
+                            CFB200_FS_HLL = 4 /* "HLL" plugins/FiniteVolume/HLLFlux.cxx:73-150 */ };
 enum cfb200_poly_rec { CFB200_PR_CONSTANT = 0 /* "Constant" ConstantPolyRec.cxx */,
                        CFB200_PR_LINEARLS = 1 /* "LinearLS2D"/"LinearLS3D" LeastSquareP1PolyRec{2,3}D.cxx */ };
 enum cfb200_limiter { CFB200_LIM_NONE = 0, CFB200_LIM_VENKTN = 1 /* "Venktn2D"/"Venktn3D" */,
@@ -93,7 +95,8 @@ typedef struct cfb200_config {
   double cfl;
   /* AUSM family: AUSMFlux.ci:55 choiceA12 (1 Liou critical speed, 2 arithmetic, 3 geometric mean of a_L,a_R);
    * AUSMPlusFlux.ci:17-23 beta, alpha; AUSMPlusUpFlux.ci:20-33 coeffKu, coeffKp, sigma, machInf */
-  int32_t choiceA12, reservedI;
+  int32_t choiceA12;
+  int32_t hllUseAlpha;      /* HLLFlux.cxx:48 UseAlpha */
   double ausmBeta, ausmAlpha;
   double ausmKu, ausmKp, ausmSigma, machInf;
 } cfb200_config;

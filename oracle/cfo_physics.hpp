@@ -367,6 +367,52 @@ struct Phys {
     return true;
   }
 
+  // ---- Lax-Friedrichs and HLL (a13), Euler variable sets ---------------------
+  // Euler2DVarSet.cxx:47-66 / Euler3DVarSet.cxx:64-84 computeEigenValues
+  static void eigenValues(const PData& d, const double* n, double* ev) {
+    double un;
+    if (D == 2) un = d.v[0]*n[0] + d.v[1]*n[1];
+    else        un = d.v[0]*n[0] + d.v[1]*n[1] + d.v[2]*n[2];
+    for (int i = 0; i < D; ++i) ev[i] = un;
+    ev[D] = un + d.A;
+    ev[D+1] = un - d.A;
+  }
+  // LaxFriedFlux.cxx:79-118 and HLLFlux.cxx:73-133, flux per unit area; uL/uR are the reconstructed UPDATE states
+  static bool centredFlux(const Config& c, const double* uL, const double* uR, const PData& pL, const PData& pR,
+                          const double* n, double* result) {
+    double fL[Q], fR[Q], evL[Q], evR[Q], sL[Q], sR[Q];
+    convFlux(pR, n, fR); convFlux(pL, n, fL);
+    eigenValues(pR, n, evR); eigenValues(pL, n, evL);
+    toCons(c, uL, sL); toCons(c, uR, sR);
+    if (c.fluxSplitter == FS_LAXFRIED) {
+      double aR = 0.0, aL = 0.0;
+      for (int i = 0; i < Q; ++i) { aR = std::max(aR, std::abs(evR[i])); aL = std::max(aL, std::abs(evL[i])); }
+      const double a = std::max(aR, aL);
+      const double aDiff = a*c.diffRedCoeff;
+      for (int i = 0; i < Q; ++i) {
+        const double sumFlux = fR[i] + fL[i];
+        result[i] = 0.5*(sumFlux - aDiff*(sR[i] - sL[i]));
+      }
+    } else {
+      double aR = 0.0, aL = 0.0;
+      for (int i = 0; i < Q; ++i) { aR = std::max(aR, evR[i]); aL = std::max(aL, evL[i]); }
+      const double amax = std::max(0.0, std::max(aR, aL));
+      aR = 0.0; aL = 0.0;
+      for (int i = 0; i < Q; ++i) { aR = std::min(aR, evR[i]); aL = std::min(aL, evL[i]); }
+      const double amin = std::min(0.0, std::min(aR, aL));
+      const double c1 = (amax + amin)/(amax - amin);
+      double c2;
+      if (!c.hllUseAlpha) c2 = amax*amin/(amax - amin);
+      else {
+        const double alpha = std::max(std::abs(amin), std::abs(amax))/(amax - amin);
+        c2 = alpha*2.0*amax*amin/(amax - amin);
+      }
+      for (int i = 0; i < Q; ++i)
+        result[i] = 0.5*(fL[i] + fR[i] - c1*(fR[i] - fL[i]) + c2*(sR[i] - sL[i]));
+    }
+    return true;
+  }
+
   // ---- Navier-Stokes -------------------------------------------------------
   // SimplerSutherlandDynViscosity.cxx:104-107, SutherlandDynViscosity.cxx:107-110
   static double dynViscosityDim(const Config& c, double /*pdim*/, double Tdim) {

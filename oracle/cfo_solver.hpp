@@ -371,6 +371,9 @@ public:
     for (int i = 0; i < Q; ++i) flux[i] = 0.;
     if (cfg.fluxSplitter == FS_ROE) {
       if (!P::roeFlux(cfg, x.vL, x.vR, x.pL, x.pR, x.n, flux)) { o.status = 1; return false; }
+    } else if (cfg.fluxSplitter == FS_LAXFRIED || cfg.fluxSplitter == FS_HLL) {
+      // update coefficient (LaxFriedFlux.cxx:120-188, HLLFlux.cxx:135-150): _leftEv.max() == un + a, as Roe's
+      P::centredFlux(cfg, x.vL, x.vR, x.pL, x.pR, x.n, flux);
     } else {
       P::ausmFlux(cfg, x.pL, x.pR, x.n, flux);      // update coefficient: AUSMFlux.ci:410-440, same form as Roe's
     }

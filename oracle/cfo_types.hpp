@@ -31,7 +31,7 @@ constexpr int MAXDIM = 3;
 
 // ---- enums shared (by value) with the product's include/cfb200.h -------------
 enum UpdateVar { UV_CONS = 0, UV_PVT = 1 };            // Euler{2,3}DCons / Euler2DPuvt, Euler3DPvt
-enum FluxSplitter { FS_ROE = 0, FS_AUSMPLUS = 1, FS_AUSMPLUSUP = 2 };
+enum FluxSplitter { FS_ROE = 0, FS_AUSMPLUS = 1, FS_AUSMPLUSUP = 2, FS_LAXFRIED = 3, FS_HLL = 4 };
 enum PolyRec { PR_CONSTANT = 0, PR_LINEARLS = 1 };
 enum Limiter { LIM_NONE = 0, LIM_VENKTN = 1, LIM_BARTHJESP = 2 };
 enum Diffusive { DIFF_NONE = 0, DIFF_NS = 1 };
@@ -90,7 +90,7 @@ struct Config {
   double cfl;             // for the pseudo-steady time term
   // AUSM family (FiniteVolumeNavierStokes/AUSMFlux.ci:55, AUSMPlusFlux.ci:17-23, AUSMPlusUpFlux.ci:20-33)
   int32_t choiceA12;      // interface sound speed: 1 Liou critical, 2 arithmetic mean, 3 geometric mean
-  int32_t reservedI;
+  int32_t hllUseAlpha;    // HLLFlux.cxx:48 UseAlpha
   double ausmBeta, ausmAlpha;                 // AUSM+ : 1/8, 3/16
   double ausmKu, ausmKp, ausmSigma, machInf;  // AUSM+up : 0.75, 0.25, 1.0, (required > 0)
 };

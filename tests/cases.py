@@ -128,6 +128,16 @@ CASES = {
     "euler3d_ausmplusup_a3": (lambda: meshgen.tet_box(3, 3, 3),
                               lambda: B.make_config(3, flux=B.FS_AUSMPLUSUP, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN,
                                                     jacobian=True, mach_inf=0.8, choice_a12=3), bcs_euler3d, False),
+    # a13 (Euler part): Lax-Friedrichs and HLL
+    "euler2d_laxfried_1st": (lambda: meshgen.quad_channel(12, 9),
+                             lambda: B.make_config(2, flux=B.FS_LAXFRIED, jacobian=True), bcs_euler2d, False),
+    "euler3d_hll_2nd_tet": (lambda: meshgen.tet_box(3, 3, 3),
+                            lambda: B.make_config(3, flux=B.FS_HLL, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN,
+                                                  jacobian=True), bcs_euler3d, False),
+    "ns3d_hex_hll_alpha": (lambda: meshgen.hex_box(5, 4, 4), lambda: ns3d_cfg(flux=B.FS_HLL, hll_use_alpha=1),
+                           bcs_ns3d, True),
+    "ns2d_quad_laxfried": (lambda: meshgen.quad_channel(10, 8), lambda: ns2d_cfg(flux=B.FS_LAXFRIED, diff_red_coeff=0.8),
+                           bcs_ns2d, True),
     # single cell / single row edge cases
     "ns3d_single_cell": (lambda: meshgen.hex_box(1, 1, 1, jitter=0.0), ns3d_cfg, bcs_ns3d, True),
     "euler2d_single_row": (lambda: meshgen.quad_channel(5, 1), lambda: B.make_config(2, poly_rec=B.PR_LINEARLS,
