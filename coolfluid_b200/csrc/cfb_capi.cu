@@ -137,15 +137,21 @@ struct CudaBackend {
       ev = &evs[nEv++]; ev->name = name;
       CFB_CUDA(cudaEventRecord(ev->a, stream));
     }
-    constexpr int BS = 128;
-    const size_t smem = (size_t)F::STAGE*(BS + 1)*sizeof(double);
-    auto go = [&](auto kern) {
+    auto go = [&](auto kern, int BS) {
+      const size_t smem = (size_t)F::STAGE*(BS + 1)*sizeof(double);
       CFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      // without this the driver sizes the shared-memory carve-out for ONE block and the intended number of resident
+      // blocks does not fit
+      CFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
       kern<<<(n + BS - 1)/BS, BS, smem, stream>>>(f, n);
     };
-    if (minBlocks <= 2) go(k_staged<F, BS, 2>);
-    else if (minBlocks == 3) go(k_staged<F, BS, 3>);
-    else go(k_staged<F, BS, 4>);
+    // launch shape = resident 128-thread blocks per SM = warps per scheduler (each scheduler owns 16384 registers, so the
+    // only register budgets that change occupancy are 255 / 168 / 128 per thread; measured on B200: 2 is fastest)
+    switch (minBlocks) {
+      case 3: go(k_staged<F, 128, 3>, 128); break;      // 12 warps, 168 registers
+      case 4: go(k_staged<F, 128, 4>, 128); break;      // 16 warps, 128 registers
+      default: go(k_staged<F, 128, 2>, 128); break;     //  8 warps, 255 registers
+    }
     CFB_CUDA(cudaGetLastError());
     if (ev) CFB_CUDA(cudaEventRecord(ev->b, stream));
   }
