@@ -12,6 +12,7 @@ import math
 MAXEQ = 9
 
 # enums (must match include/cfb200.h and oracle/cfo_types.hpp)
+PM_EULER, PM_MHD3D_PROJECTION = 0, 1
 UV_CONS, UV_PVT = 0, 1
 FS_ROE, FS_AUSMPLUS, FS_AUSMPLUSUP, FS_LAXFRIED, FS_HLL = 0, 1, 2, 3, 4
 PR_CONSTANT, PR_LINEARLS = 0, 1
@@ -40,6 +41,7 @@ class ConfigStruct(C.Structure):
         ("choiceA12", C.c_int32), ("hllUseAlpha", C.c_int32),
         ("ausmBeta", C.c_double), ("ausmAlpha", C.c_double),
         ("ausmKu", C.c_double), ("ausmKp", C.c_double), ("ausmSigma", C.c_double), ("machInf", C.c_double),
+        ("physicalModel", C.c_int32), ("reserved2", C.c_int32), ("refSpeed", C.c_double),
     ]
 
 
@@ -77,7 +79,9 @@ def make_config(dim, update_var=UV_CONS, flux=FS_ROE, poly_rec=PR_CONSTANT, limi
     """Defaults follow the reference: gamma/RDim EulerTerm.cxx:46-50, tol NumericalJacobian.cxx:31,
     limitRes/gradientFactor/limitIter PolyReconstructor.ci:57-67, coeffEps Venktn2D.cxx:58."""
     c = ConfigStruct()
-    q = dim + 2
+    c.physicalModel = int(kw.get("physical_model", PM_EULER))
+    q = 9 if c.physicalModel == PM_MHD3D_PROJECTION else dim + 2
+    c.refSpeed = kw.get("ref_speed", 1.0)
     c.dim, c.nEqs = dim, q
     c.updateVar, c.fluxSplitter, c.polyRec, c.limiter, c.diffusive = update_var, flux, poly_rec, limiter, diffusive
     c.viscLaw = kw.get("visc_law", VISC_SIMPLER_SUTHERLAND)

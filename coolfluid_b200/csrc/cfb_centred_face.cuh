@@ -1,0 +1,195 @@
+// cfb200 — face kernels of the centred splitters (Lax-Friedrichs, HLL) for physics policies that provide
+//   PH::CSide / PH::cside() / PH::centred() / PH::maxEigenValue()   (MhdPhys: cfb_mhd.cuh)
+// One thread per face, no diffusive flux.  Same contract as InnerFaceK / BoundaryFaceK (cfb_face.cuh): flux and update
+// coefficients into face-owned slots; with JAC the finite-difference blocks block(R,L) = -resFactor dF/dU_L and
+// block(L,R) = +resFactor dF/dU_R straight into the BSR array (one writer each), boundary blocks into bndBlocks.
+// (included from inside namespace cfb in cfb_kernels.cuh)
+#pragma once
+
+// a8: frozen reconstruction increments limiter * gradientFactor * grad . (xq - x) of both sides and the unit normal
+// (LeastSquareP1PolyRec3D.cxx:204-268, FVMCC_ComputeRHS.cxx:518-534); boundary faces use the inner cell's gradient
+// and limiter for the ghost side.
+template <int D, int Q>
+CFB_HD void faceRecon(const Dev& d, const Cfg& c, int f, int L, int R, double* n, double& area, double* gL, double* gR) {
+  const bool isB = (R >= d.nCells);
+  area = d.areas[f];
+  double xq[3] = {0., 0., 0.}, xL[3] = {0., 0., 0.}, xR[3] = {0., 0., 0.}, nr[3] = {0., 0., 0.};
+#pragma unroll
+  for (int k = 0; k < D; ++k) {
+    nr[k] = d.normals[(size_t)k*d.nFaces + f];
+    xL[k] = d.centres[(size_t)k*d.nStates + L];
+    xR[k] = d.centres[(size_t)k*d.nStates + R];
+  }
+  if (c.polyRec == CFB200_PR_CONSTANT) {
+#pragma unroll
+    for (int v = 0; v < Q; ++v) { gL[v] = 0.; gR[v] = 0.; }
+  } else {
+#pragma unroll
+    for (int k = 0; k < D; ++k) xq[k] = d.faceCentres[(size_t)k*d.nFaces + f];
+    const int gradR = isB ? L : R;
+    const int32_t* zg = isB ? d.bcs[d.faceBC[f]].zeroGrad : nullptr;
+    const bool stop = (c.stopLimiting != 0);
+#pragma unroll
+    for (int v = 0; v < Q; ++v) {
+      const size_t iL = (size_t)v*d.nCells + L, iR = (size_t)v*d.nCells + gradR;
+      const bool z = zg && zg[v];
+      double gcS = 0.0, gcN = 0.0;
+      if (!z) {
+        if (D == 2) {
+          gcS = c.gradientFactor*(d.uX[iL]*(xq[0] - xL[0]) + d.uY[iL]*(xq[1] - xL[1]));
+          gcN = c.gradientFactor*(d.uX[iR]*(xq[0] - xR[0]) + d.uY[iR]*(xq[1] - xR[1]));
+        } else {
+          gcS = c.gradientFactor*(d.uX[iL]*(xq[0] - xL[0]) + d.uY[iL]*(xq[1] - xL[1]) + d.uZ[iL]*(xq[2] - xL[2]));
+          gcN = c.gradientFactor*(d.uX[iR]*(xq[0] - xR[0]) + d.uY[iR]*(xq[1] - xR[1]) + d.uZ[iR]*(xq[2] - xR[2]));
+        }
+      }
+      gL[v] = (stop ? 1. : d.lim[iL])*gcS;
+      gR[v] = (stop ? 1. : d.lim[iR])*gcN;
+    }
+  }
+  const double invArea = ddiv(1., area);
+  n[2] = 0.;
+#pragma unroll
+  for (int k = 0; k < D; ++k) n[k] = nr[k]*invArea;
+}
+
+template <class PH, bool JAC>
+struct CentredInnerFaceK {   // idx over interior faces
+  static constexpr int D = PH::DIM, Q = PH::Q;
+  Dev d; Cfg c;
+  CFB_HD void operator()(int f) const {
+    const int L = d.faceL[f], R = d.faceR[f];
+    double* blkRL = JAC ? &d.bsrVal[(size_t)d.slotRL[f]*Q*Q] : nullptr;
+    double* blkLR = JAC ? &d.bsrVal[(size_t)d.slotLR[f]*Q*Q] : nullptr;
+    if (!(d.updatable[L] || d.updatable[R])) {             // FVMCC_ComputeRHS.cxx:212-213
+      for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = 0.;
+      d.ucL[f] = 0.; d.ucR[f] = 0.; d.ucD[f] = 0.;
+      if (JAC) for (int k = 0; k < Q*Q; ++k) { blkRL[k] = 0.; blkLR[k] = 0.; }
+      return;
+    }
+    double n[3], area, gL[Q], gR[Q], sL[Q], sR[Q], vL[Q], vR[Q];
+#pragma unroll
+    for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + L]; sR[v] = d.U[(size_t)v*d.nStates + R]; }
+    faceRecon<D, Q>(d, c, f, L, R, n, area, gL, gR);
+    const bool lin = (c.polyRec != CFB200_PR_CONSTANT);
+#pragma unroll
+    for (int v = 0; v < Q; ++v) { vL[v] = lin ? sL[v] + gL[v] : sL[v]; vR[v] = lin ? sR[v] + gR[v] : sR[v]; }
+    typename PH::CSide a, b;
+    PH::cside(c, vL, n, a);
+    PH::cside(c, vR, n, b);
+    double flux[Q];
+    PH::centred(c, a, b, flux);
+    {
+      // update coefficients: LaxFriedFlux.cxx:120-188 / HLLFlux.cxx:135-150 (left: _leftEv.max(); right: getMaxEigenValue
+      // with the reversed normal)
+      const double faceArea = area/1;
+      d.ucL[f] = dmax(a.evVecMax, 0.)*faceArea;
+      double tn[3];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) tn[k] = -1.0*n[k];
+      typename PH::Data pR;
+      PH::physicalData(c, vR, pR);
+      d.ucR[f] = dmax(PH::maxEigenValue(c, pR, tn), 0.)*faceArea;
+      d.ucD[f] = 0.;
+    }
+#pragma unroll
+    for (int v = 0; v < Q; ++v) { flux[v] *= area; d.faceFlux[(size_t)v*d.nFaces + f] = flux[v]; }
+    if (!JAC) return;
+    // FVMCC_ComputeRhsJacob.cxx:126-236,321-365 with the frozen gradient / limiter (LeastSquareP1PolyRec3D.cxx:272-318)
+    const double rf = c.resFactor;
+#pragma unroll 1
+    for (int it = 0; it < 2*Q; ++it) {
+      const int side = (it >= Q) ? 1 : 0;
+      const int iVar = it - side*Q;
+      double orig = 0., gp = 0.;
+#pragma unroll
+      for (int v = 0; v < Q; ++v) {
+        if (side == 0 && iVar == v) { orig = sL[v]; gp = gL[v]; }
+        if (side == 1 && iVar == v) { orig = sR[v]; gp = gR[v]; }
+      }
+      const double eps = fdEps(c, iVar, orig);
+      const double pv = orig + eps;
+      const double pvr = (c.polyRec == CFB200_PR_CONSTANT) ? pv : pv + gp;
+      double vp[Q];
+#pragma unroll
+      for (int v = 0; v < Q; ++v) { const double base = side ? vR[v] : vL[v]; vp[v] = (v == iVar) ? pvr : base; }
+      typename PH::CSide pert;
+      PH::cside(c, vp, n, pert);
+      double pf[Q];
+      if (side == 0) PH::centred(c, pert, b, pf); else PH::centred(c, a, pert, pf);
+      const double invEps = ddiv(1., eps);
+      double* blk = side ? blkLR : blkRL;        // column iVar of block(R,L) (perturbed L) / block(L,R) (perturbed R)
+#pragma unroll
+      for (int v = 0; v < Q; ++v) {
+        double fd = (pf[v]*area - flux[v])*invEps;
+        fd *= rf;                                 // what row L receives (upFactor[0])
+        blk[v*Q + iVar] = side ? fd : fd*(-1.0);  // row R receives upFactor[1] = -1 times that
+      }
+    }
+  }
+};
+
+template <class PH, bool JAC>
+struct CentredBoundaryFaceK {   // idx over boundary faces
+  static constexpr int D = PH::DIM, Q = PH::Q;
+  Dev d; Cfg c;
+  CFB_HD void operator()(int g) const {
+    const int f = d.nInner + g;
+    const int L = d.faceL[f], R = d.faceR[f];
+    double* blk = &d.bndBlocks[(size_t)g*Q*Q];
+    if (!d.updatable[L]) {
+      for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = 0.;
+      d.ucL[f] = 0.; d.ucR[f] = 0.; d.ucD[f] = 0.;
+      if (JAC) for (int k = 0; k < Q*Q; ++k) blk[k] = 0.;
+      return;
+    }
+    double n[3], area, gL[Q], gR[Q], sL[Q], sR[Q], vL[Q], vR[Q];
+#pragma unroll
+    for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + L]; sR[v] = d.U[(size_t)v*d.nStates + R]; }
+    faceRecon<D, Q>(d, c, f, L, R, n, area, gL, gR);
+    const bool lin = (c.polyRec != CFB200_PR_CONSTANT);
+#pragma unroll
+    for (int v = 0; v < Q; ++v) { vL[v] = lin ? sL[v] + gL[v] : sL[v]; vR[v] = lin ? sR[v] + gR[v] : sR[v]; }
+    double flux[Q];
+    {
+      typename PH::CSide a, b;
+      PH::cside(c, vL, n, a);
+      PH::cside(c, vR, n, b);
+      PH::centred(c, a, b, flux);
+      d.ucL[f] = dmax(a.evVecMax, 0.)*(area/1);
+      d.ucR[f] = 0.; d.ucD[f] = 0.;               // the ghost side has no cell (FVMCC_ComputeRHS.cxx:455-514)
+    }
+#pragma unroll
+    for (int v = 0; v < Q; ++v) { flux[v] *= area; d.faceFlux[(size_t)v*d.nFaces + f] = flux[v]; }
+    if (!JAC) return;
+    // FVMCC_ComputeRhsJacob.cxx:240-317: perturb the inner state, rebuild the ghost state, re-extrapolate both sides
+    double nr[D];
+#pragma unroll
+    for (int k = 0; k < D; ++k) nr[k] = d.normals[(size_t)k*d.nFaces + f];
+    const BCond& bc = d.bcs[d.faceBC[f]];
+    const double rf = c.resFactor;
+#pragma unroll 1
+    for (int iVar = 0; iVar < Q; ++iVar) {
+      const double orig = pick<Q>(sL, iVar);
+      const double eps = fdEps(c, iVar, orig);
+      double sLp[Q], sRp[Q];
+#pragma unroll
+      for (int v = 0; v < Q; ++v) sLp[v] = (v == iVar) ? orig + eps : sL[v];
+      ghostState<D, PH>(c, bc, nr, sLp, sRp);
+#pragma unroll
+      for (int v = 0; v < Q; ++v) { vL[v] = lin ? sLp[v] + gL[v] : sLp[v]; vR[v] = lin ? sRp[v] + gR[v] : sRp[v]; }
+      typename PH::CSide a, b;
+      PH::cside(c, vL, n, a);
+      PH::cside(c, vR, n, b);
+      double pf[Q];
+      PH::centred(c, a, b, pf);
+      const double invEps = ddiv(1., eps);
+#pragma unroll
+      for (int v = 0; v < Q; ++v) {
+        double fd = (pf[v]*area - flux[v])*invEps;
+        fd *= rf;
+        blk[v*Q + iVar] = fd;
+      }
+    }
+  }
+};

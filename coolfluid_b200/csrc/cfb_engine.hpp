@@ -20,6 +20,9 @@ namespace cfb {
 
 // Roe; AUSM+ and AUSM+up with the perfect-gas interface sound speeds (choiceA12 4/5 are the TCNEQ variants).
 inline bool splitterSupported(const cfb200_config& c) {
+  if (c.physicalModel == CFB200_PM_MHD3D_PROJECTION)      // MHD: centred splitters, conservative variables, inviscid
+    return (c.fluxSplitter == CFB200_FS_LAXFRIED || c.fluxSplitter == CFB200_FS_HLL) && c.updateVar == CFB200_UV_CONS &&
+           c.diffusive == CFB200_DIFF_NONE;
   if (c.fluxSplitter == CFB200_FS_ROE) return true;
   if (c.fluxSplitter == CFB200_FS_AUSMPLUS || c.fluxSplitter == CFB200_FS_AUSMPLUSUP)
     return c.choiceA12 >= 1 && c.choiceA12 <= 3 && (c.fluxSplitter == CFB200_FS_AUSMPLUS || c.machInf > 0.);
@@ -251,9 +254,9 @@ public:
   }
 
   // ---- execute ------------------------------------------------------------------------------------
-  template <int D> void applyBC_() { if (d.nGhosts) bk.launch("applyBC", GhostFill<D>{d, cfg}, d.nGhosts, 128); }
+  template <int D, class PH> void applyBC_() { if (d.nGhosts) bk.launch("applyBC", GhostFill<D, PH>{d, cfg}, d.nGhosts, 128); }
 
-  template <int D> void computeRhs_(bool applyBC) {
+  template <int D, class PH> void computeRhs_(bool applyBC) {
     const bool doJac = cfg.computeJacobian != 0;
     if (doJac) ensureJacobian();
     bk.resetTimings();
@@ -261,52 +264,70 @@ public:
     int g0 = 0;
     if (haloPending) {
       // overlap with the halo exchange: ghosts + gradients of the cells that do not see a received state
-      if (applyBC) applyBC_<D>();
+      if (applyBC) applyBC_<D, PH>();
       if (cfg.polyRec == CFB200_PR_LINEARLS && nIndep > 0) {
         g0 = std::min(nIndep, d.nCells);
-        bk.launch("gradientsInterior", Gradients<D>{d, 0}, g0, 128);
+        bk.launch("gradientsInterior", Gradients<D, PH>{d, 0}, g0, 128);
       }
       haloWait();                          // the engine's stream now waits for the unpacked overlap states
       haloPending = false;
     }
-    if (applyBC) applyBC_<D>();
+    if (applyBC) applyBC_<D, PH>();
     // initializeComputationRHS (FVMCC_ComputeRHS.cxx:690-705)
-    if (cfg.polyRec == CFB200_PR_LINEARLS) bk.launch("gradients", Gradients<D>{d, g0}, d.nCells - g0, 128);
-    bk.launch("nodalExtrapolate", NodalExtrapolate<D>{d}, d.nNodes, 256);
+    if (cfg.polyRec == CFB200_PR_LINEARLS) bk.launch("gradients", Gradients<D, PH>{d, g0}, d.nCells - g0, 128);
+    bk.launch("nodalExtrapolate", NodalExtrapolate<D, PH>{d}, d.nNodes, 256);
     if (cfg.polyRec == CFB200_PR_LINEARLS && cfg.limiter != CFB200_LIM_NONE)
-      bk.launch("limiter", LimiterK<D>{d, cfg}, d.nCells, 128);
-    if (doJac) {
-      const int fam = splitterFamily(cfg);
-      if (fam == 0) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 0>{d, cfg}, d.nInner, faceShape);
-      else if (fam == 1) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 1>{d, cfg}, d.nInner, faceShape);
-      else bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 2>{d, cfg}, d.nInner, faceShape);
-      bk.launch("boundaryFaceJac", BoundaryFaceK<D, true>{d, cfg}, d.nGhosts, 128);
+      bk.launch("limiter", LimiterK<D, PH>{d, cfg}, d.nCells, 128);
+    if constexpr (PH::CENTRED_ONLY) {
+      if (doJac) {
+        bk.launch("innerFaceJac", CentredInnerFaceK<PH, true>{d, cfg}, d.nInner, 128);
+        bk.launch("boundaryFaceJac", CentredBoundaryFaceK<PH, true>{d, cfg}, d.nGhosts, 128);
+      } else {
+        bk.launch("innerFace", CentredInnerFaceK<PH, false>{d, cfg}, d.nInner, 128);
+        bk.launch("boundaryFace", CentredBoundaryFaceK<PH, false>{d, cfg}, d.nGhosts, 128);
+      }
     } else {
       const int fam = splitterFamily(cfg);
-      if (fam == 0) bk.launch("innerFace", InnerFaceK<D, false, 0>{d, cfg}, d.nInner, 128);
-      else if (fam == 1) bk.launch("innerFace", InnerFaceK<D, false, 1>{d, cfg}, d.nInner, 128);
-      else bk.launch("innerFace", InnerFaceK<D, false, 2>{d, cfg}, d.nInner, 128);
-      bk.launch("boundaryFace", BoundaryFaceK<D, false>{d, cfg}, d.nGhosts, 128);
+      if (doJac) {
+        if (fam == 0) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 0>{d, cfg}, d.nInner, faceShape);
+        else if (fam == 1) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 1>{d, cfg}, d.nInner, faceShape);
+        else bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 2>{d, cfg}, d.nInner, faceShape);
+        bk.launch("boundaryFaceJac", BoundaryFaceK<D, true>{d, cfg}, d.nGhosts, 128);
+      } else {
+        if (fam == 0) bk.launch("innerFace", InnerFaceK<D, false, 0>{d, cfg}, d.nInner, 128);
+        else if (fam == 1) bk.launch("innerFace", InnerFaceK<D, false, 1>{d, cfg}, d.nInner, 128);
+        else bk.launch("innerFace", InnerFaceK<D, false, 2>{d, cfg}, d.nInner, 128);
+        bk.launch("boundaryFace", BoundaryFaceK<D, false>{d, cfg}, d.nGhosts, 128);
+      }
     }
-    bk.launch("cellGather", CellGather<D>{d, cfg}, d.nCells, 256);
+    bk.launch("cellGather", CellGather<D, PH>{d, cfg}, d.nCells, 256);
     if (doJac) {
-      bk.launch("diagGather", DiagGather<D>{d}, d.nCells*32, 256);
-      if (nNonUpd) bk.launch("zeroRows", ZeroRows<D>{d, nonUpdCells}, nNonUpd*32, 256);
+      bk.launch("diagGather", DiagGather<D, PH>{d}, d.nCells*DiagGather<D, PH>::GS, 256);
+      if (nNonUpd) bk.launch("zeroRows", ZeroRows<D, PH>{d, nonUpdCells}, nNonUpd*ZeroRows<D, PH>::GS, 256);
     }
     int st = 0;
     bk.d2h(&st, d.status, sizeof(int));   // synchronises
     lastStatus = st;
   }
-  void applyBC() { if (cfg.dim == 2) applyBC_<2>(); else applyBC_<3>(); bk.sync(); }
-  void computeRhs(bool applyBCFirst) { if (cfg.dim == 2) computeRhs_<2>(applyBCFirst); else computeRhs_<3>(applyBCFirst); }
+  bool isMhd() const { return cfg.physicalModel == CFB200_PM_MHD3D_PROJECTION; }
+  void applyBC() {
+    if (isMhd()) applyBC_<3, MhdPhys>(); else if (cfg.dim == 2) applyBC_<2, Phys<2> >(); else applyBC_<3, Phys<3> >();
+    bk.sync();
+  }
+  void computeRhs(bool applyBCFirst) {
+    if (isMhd()) computeRhs_<3, MhdPhys>(applyBCFirst);
+    else if (cfg.dim == 2) computeRhs_<2, Phys<2> >(applyBCFirst); else computeRhs_<3, Phys<3> >(applyBCFirst);
+  }
   void timeRhs() {
     const int doJac = cfg.computeJacobian && d.bsrVal;
-    if (cfg.dim == 2) bk.launch("timeRhs", TimeRhs<2>{d, cfg, doJac}, d.nCells, 128);
+    if (isMhd()) bk.launch("timeRhs", TimeRhs<3, MhdPhys>{d, cfg, doJac}, d.nCells, 128);
+    else if (cfg.dim == 2) bk.launch("timeRhs", TimeRhs<2>{d, cfg, doJac}, d.nCells, 128);
     else bk.launch("timeRhs", TimeRhs<3>{d, cfg, doJac}, d.nCells, 128);
     bk.sync();
   }
   double updateSolFwdEuler(double cfl, int monitorVar) {
-    if (cfg.dim == 2) bk.launch("updateSol", UpdateSolFwdEuler<2>{d, cfl, monitorVar}, d.nCells, 256);
+    if (isMhd()) bk.launch("updateSol", UpdateSolFwdEuler<3, MhdPhys>{d, cfl, monitorVar}, d.nCells, 256);
+    else if (cfg.dim == 2) bk.launch("updateSol", UpdateSolFwdEuler<2>{d, cfl, monitorVar}, d.nCells, 256);
     else bk.launch("updateSol", UpdateSolFwdEuler<3>{d, cfl, monitorVar}, d.nCells, 256);
     return bk.sumOrdered(d.partial, d.nCells);
   }

@@ -83,11 +83,11 @@ struct FaceCentres {   // idx over faces
 
 // ------------------------------------------------------------------------------------------------
 // a16: boundary conditions, FVMCC_BaseBC.ci:144-187 executeOnTrs -> setGhostState(face)
-template <int D>
+template <int D, class PH = Phys<D> >
 CFB_HD void ghostState(const Cfg& c, const BCond& b, const double* nr /*area-weighted normal*/,
                        const double* inner, double* ghost) {
-  constexpr int Q = D + 2;
-  typedef Phys<D> P;
+  constexpr int Q = PH::Q;
+  typedef PH P;
   switch (b.type) {
     case CFB200_BC_SUPER_OUTLET:
       for (int i = 0; i < Q; ++i) ghost[i] = inner[i];
@@ -103,42 +103,23 @@ CFB_HD void ghostState(const Cfg& c, const BCond& b, const double* nr /*area-wei
       ghost[Q-1] = inner[Q-1];
       break;
     }
-    default: {                            // CFB200_BC_MIRROR_EULER_CONS, MirrorEuler2D.cxx:56-94
-      double n[3] = {0., 0., 0.};
-      double s2;
-      if (D == 2) s2 = nr[0]*nr[0] + nr[1]*nr[1]; else s2 = nr[0]*nr[0] + nr[1]*nr[1] + nr[2]*nr[2];
-      const double invFaceLength = 1./sqrt(s2);
-      for (int i = 0; i < D; ++i) n[i] = nr[i]*invFaceLength;
-      PData di, dg;
-      P::physicalData(c, inner, di);
-      const double vn = P::vn(di, n);
-      const double gamma = c.gamma;
-      const double gammaDivGammaMinus1 = gamma/(gamma - 1.0);
-      dg.rho = di.rho;
-      dg.v[2] = 0.;
-      for (int i = 0; i < D; ++i) dg.v[i] = di.v[i] - 2.0*vn*n[i];
-      dg.V = di.V;
-      dg.p = di.p;
-      dg.H = (gammaDivGammaMinus1*dg.p + 0.5*dg.rho*dg.V*dg.V)/dg.rho;
-      dg.A = sqrt(gamma*dg.p/dg.rho);
-      dg.T = di.T;
-      P::consFromPhysicalData(dg, ghost);
+    default:                              // CFB200_BC_MIRROR_EULER_CONS: MirrorEuler2D.cxx:56-94 / MirrorMHD3DProjection.cxx:56-96
+      P::mirrorGhost(c, nr, inner, ghost);
       break;
-    }
   }
 }
 
-template <int D>
+template <int D, class PH = Phys<D> >
 struct GhostFill {   // idx over boundary faces
   Dev d; Cfg c;
   CFB_HD void operator()(int g) const {
-    constexpr int Q = D + 2;
+    constexpr int Q = PH::Q;
     const int f = d.nInner + g;
     const int L = d.faceL[f];
     double inner[Q], ghost[Q], nr[D];
     for (int v = 0; v < Q; ++v) inner[v] = d.U[(size_t)v*d.nStates + L];
     for (int k = 0; k < D; ++k) nr[k] = d.normals[(size_t)k*d.nFaces + f];
-    ghostState<D>(c, d.bcs[d.faceBC[f]], nr, inner, ghost);
+    ghostState<D, PH>(c, d.bcs[d.faceBC[f]], nr, inner, ghost);
     for (int v = 0; v < Q; ++v) d.U[(size_t)v*d.nStates + d.nCells + g] = ghost[v];
   }
 };
@@ -148,7 +129,7 @@ struct GhostFill {   // idx over boundary faces
 // its lower-ID cell (LeastSquareP1PolyRec2D.cxx:100-134, 3D.cxx:104-160).  `lsqNbr` lists, per cell, the
 // other end of every edge that touches it in exactly that global edge order, so the per-cell gather below
 // forms the same sums term by term ((-dx)*(-du) == dx*du exactly, so the edge orientation is irrelevant).
-template <int D>
+template <int D, class PH = Phys<D> >
 CFB_HD double edgeWeight(const Dev& d, int c, int nb, double* dx) {
   double dist = 0.;
   for (int k = 0; k < D; ++k) {
@@ -162,7 +143,7 @@ CFB_HD double edgeWeight(const Dev& d, int c, int nb, double* dx) {
   return w;
 }
 
-template <int D>
+template <int D, class PH = Phys<D> >
 struct LsqSetup {   // LeastSquareP1PolyRec{2,3}D::updateWeights; idx over cells
   Dev d;
   CFB_HD void operator()(int c) const {
@@ -180,11 +161,11 @@ struct LsqSetup {   // LeastSquareP1PolyRec{2,3}D::updateWeights; idx over cells
   }
 };
 
-template <int D>
+template <int D, class PH = Phys<D> >
 struct Gradients {   // idx over the cells [c0, c0 + n)
   Dev d; int c0;
   CFB_HD void operator()(int idx) const {
-    constexpr int Q = D + 2;
+    constexpr int Q = PH::Q;
     const int c = c0 + idx;
     double lf[3][Q];
     double u0[Q];
@@ -234,11 +215,11 @@ struct Gradients {   // idx over the cells [c0, c0 + n)
 
 // ------------------------------------------------------------------------------------------------
 // a6: nodal states, DistanceBasedExtrapolator.ci:105-149; idx over nodes
-template <int D>
+template <int D, class PH = Phys<D> >
 struct NodalExtrapolate {
   Dev d;
   CFB_HD void operator()(int n) const {
-    constexpr int Q = D + 2;
+    constexpr int Q = PH::Q;
     double ns[Q];
     for (int v = 0; v < Q; ++v) ns[v] = 0.;
     for (int k = d.nodeNbrPtr[n]; k < d.nodeNbrPtr[n+1]; ++k) {
@@ -254,11 +235,11 @@ struct NodalExtrapolate {
 // a7: Venkatakrishnan / Barth-Jespersen limiter, evaluated eagerly per cell (the reference evaluates it at
 // the first face that touches the cell, FVMCC_PolyRec.cxx:120-167; all its inputs are frozen before the face
 // loop, so the value is the same).  Venktn2D.cxx:111-260, Venktn3D.cxx:44-190, BarthJesp.cxx:60-155.
-template <int D>
+template <int D, class PH = Phys<D> >
 struct LimiterK {   // idx over cells
   Dev d; Cfg c;
   CFB_HD void operator()(int cell) const {
-    constexpr int Q = D + 2;
+    constexpr int Q = PH::Q;
     if (!d.cellActive[cell]) return;
     const bool fresh = (c.residual > c.limitRes) && (c.limitIter > 0 && c.iter < c.limitIter);
     if (!fresh && c.freezeLimiter) return;
@@ -363,15 +344,16 @@ struct LimiterK {   // idx over cells
 };
 
 #include "cfb_face.cuh"
+#include "cfb_centred_face.cuh"
 
 // a17: FVMCC_ComputeRHS::updateRHS (FVMCC_ComputeRHS.cxx:455-514) as a gather: for each cell, its faces in
 // ascending loop order; rhs starts from 0, updateCoeff accumulates onto the incoming value
 // (it is zeroed by the updater, UpdateSol.cxx:192).
-template <int D>
+template <int D, class PH = Phys<D> >
 struct CellGather {   // idx over cells
   Dev d; Cfg c;
   CFB_HD void operator()(int cell) const {
-    constexpr int Q = D + 2;
+    constexpr int Q = PH::Q;
     double r[Q];
     for (int v = 0; v < Q; ++v) r[v] = 0.;
     double uc = d.updateCoeff[cell];
@@ -399,12 +381,13 @@ struct CellGather {   // idx over cells
 // Diagonal blocks: one thread per (cell, block entry).  diag(c) = sum over the cell's faces in loop order of
 //   inner face, c == L:  -block(R,c)      inner face, c == R:  -block(L,c)      boundary face: +bnd block
 // Rows of non-updatable cells are staging only and are zeroed by ZeroRows afterwards.
-template <int D>
-struct DiagGather {   // idx over nCells*32 (one warp-sized group per cell, Q*Q <= 25 lanes active)
+template <int D, class PH = Phys<D> >
+struct DiagGather {   // idx over nCells*GS (one group of GS threads per cell, Q*Q of them active: 32 | 96 for q = 9)
+  static constexpr int GS = (PH::Q*PH::Q <= 32) ? 32 : 96;
   Dev d;
   CFB_HD void operator()(int idx) const {
-    constexpr int Q = D + 2;
-    const int cell = idx >> 5, e = idx & 31;
+    constexpr int Q = PH::Q;
+    const int cell = idx/GS, e = idx - cell*GS;
     if (e >= Q*Q) return;
     double acc = 0.;
     if (d.updatable[cell]) {
@@ -432,12 +415,13 @@ struct DiagGather {   // idx over nCells*32 (one warp-sized group per cell, Q*Q 
   }
 };
 
-template <int D>
-struct ZeroRows {   // idx over (non-updatable cell list) * 32
+template <int D, class PH = Phys<D> >
+struct ZeroRows {   // idx over (non-updatable cell list) * GS
+  static constexpr int GS = (PH::Q*PH::Q <= 32) ? 32 : 96;
   Dev d; const int* cells;
   CFB_HD void operator()(int idx) const {
-    constexpr int Q = D + 2;
-    const int cell = cells[idx >> 5], e = idx & 31;
+    constexpr int Q = PH::Q;
+    const int cell = cells[idx/GS], e = idx - (idx/GS)*GS;
     if (e >= Q*Q) return;
     for (int k = d.bsrRowPtr[cell]; k < d.bsrRowPtr[cell+1]; ++k) d.bsrVal[(size_t)k*Q*Q + e] = 0.;
   }
@@ -446,12 +430,12 @@ struct ZeroRows {   // idx over (non-updatable cell list) * 32
 // ------------------------------------------------------------------------------------------------
 // a21: FVMCC_PseudoSteadyTimeRhs.cxx:106-262, steady branch (dt == 0): diag = updateCoeff/CFL,
 // rhs -= (U - U_past) * diag * resFactor in SOLUTION variables, diagonal block += diag * dU/dP (numerical)
-template <int D>
+template <int D, class PH = Phys<D> >
 struct TimeRhs {   // idx over cells
   Dev d; Cfg c; int doJac;
   CFB_HD void operator()(int cell) const {
-    constexpr int Q = D + 2;
-    typedef Phys<D> P;
+    constexpr int Q = PH::Q;
+    typedef PH P;
     if (!d.updatable[cell]) return;
     const double diagValue = ddiv(d.updateCoeff[cell], c.cfl);
     double u[Q], up[Q], tempState[Q], tPast[Q], tPert[Q];
@@ -483,11 +467,11 @@ struct TimeRhs {   // idx over cells
 // ------------------------------------------------------------------------------------------------
 // §8f-1: ForwardEuler UpdateSol.cxx:83-193 on the device: dt = CFL/updateCoeff, U += rhs*dt (rhs itself is left unscaled),
 // updateCoeff = 0; per-cell squared dU[monitorVar] goes to `partial` for the ordered norm reduction.
-template <int D>
+template <int D, class PH = Phys<D> >
 struct UpdateSolFwdEuler {   // idx over cells
   Dev d; double cfl; int monitorVar;
   CFB_HD void operator()(int cell) const {
-    constexpr int Q = D + 2;
+    constexpr int Q = PH::Q;
     double sq = 0.;
     if (!d.updatable[cell]) {
       for (int v = 0; v < Q; ++v) d.rhs[(size_t)cell*Q + v] = 0.;

@@ -1,0 +1,148 @@
+// cfb200 — MHD3DProjection (a13): the ideal-MHD + hyperbolic divergence cleaning model of plugins/MHD in conservative
+// variables (rho, rho u, rho v, rho w, Bx, By, Bz, rho E, phi; q = 9) and the face kernels of the centred splitters
+// (Lax-Friedrichs, HLL) for it.  Included by cfb_kernels.cuh inside namespace cfb.
+//   MHD3DProjectionCons.cxx:540-574   computePhysicalData          :1132-1148 computeStateFromPhysicalData
+//   MHD3DProjectionVarSet.cxx:42-78   computeFlux   :398-436 getMaxEigenValue   :499-548 computeEigenValues
+//   FiniteVolumeMHD/MirrorMHD3DProjection.cxx:56-96
+// No background potential field (potentialBType unset, B0 = 0).
+#pragma once
+
+struct MhdData { double rho, p, A, V, B, phi, v[3], b[3]; };
+
+struct MhdPhys {
+  static constexpr int DIM = 3;
+  static constexpr int Q = 9;
+  static constexpr int TID = 7;
+  static constexpr bool CENTRED_ONLY = true;    // only the centred splitters (cfb_centred_face.cuh), no diffusive flux
+  typedef MhdData Data;
+
+  static CFB_HD void physicalData(const Cfg& c, const double* s, MhdData& d) {
+    const double rho = s[0];
+    const Recip rr = recipOf(rho);
+    const double u = divBy(s[1], rr), v = divBy(s[2], rr), w = divBy(s[3], rr);
+    const double Bx = s[4], By = s[5], Bz = s[6];
+    const double V2 = u*u + v*v + w*w;
+    const double B2 = Bx*Bx + By*By + Bz*Bz;
+    d.v[0] = u; d.v[1] = v; d.v[2] = w;
+    d.b[0] = Bx; d.b[1] = By; d.b[2] = Bz;
+    d.B = dsqrt(B2);
+    d.rho = rho;
+    d.V = dsqrt(V2);
+    d.p = (c.gamma - 1.)*(s[7] - 0.5*(rho*V2 + B2));
+    d.phi = s[8];
+    d.A = dsqrt(divBy(c.gamma*d.p, rr));
+  }
+  static CFB_HD void stateFromPhysicalData(const Cfg& c, const MhdData& d, double* s) {
+    const double rho = d.rho;
+    s[0] = rho;
+    s[1] = rho*d.v[0]; s[2] = rho*d.v[1]; s[3] = rho*d.v[2];
+    s[4] = d.b[0]; s[5] = d.b[1]; s[6] = d.b[2];
+    s[7] = ddiv(d.p, c.gamma - 1.0) + 0.5*(rho*d.V*d.V + d.B*d.B);
+    s[8] = d.phi;
+  }
+  static CFB_HD void mirrorGhost(const Cfg& c, const double* nr, const double* inner, double* ghost) {
+    double nx = nr[0], ny = nr[1], nz = nr[2];
+    const double invFaceLength = ddiv(1., dsqrt(nx*nx + ny*ny + nz*nz));
+    nx *= invFaceLength; ny *= invFaceLength; nz *= invFaceLength;
+    MhdData di, dg;
+    physicalData(c, inner, di);
+    const double vn = di.v[0]*nx + di.v[1]*ny + di.v[2]*nz;
+    const double bn = di.b[0]*nx + di.b[1]*ny + di.b[2]*nz;
+    dg.rho = di.rho;
+    dg.v[0] = di.v[0] - 2.0*vn*nx; dg.v[1] = di.v[1] - 2.0*vn*ny; dg.v[2] = di.v[2] - 2.0*vn*nz;
+    dg.b[0] = di.b[0] - 2.0*bn*nx; dg.b[1] = di.b[1] - 2.0*bn*ny; dg.b[2] = di.b[2] - 2.0*bn*nz;
+    dg.V = di.V; dg.A = di.A; dg.p = di.p; dg.B = di.B; dg.phi = di.phi;
+    stateFromPhysicalData(c, dg, ghost);
+  }
+  static CFB_HD void physFlux(const Cfg& c, const MhdData& d, const double* n, double* f) {
+    const double nx = n[0], ny = n[1], nz = n[2];
+    const double rho = d.rho, u = d.v[0], v = d.v[1], w = d.v[2], Bx = d.b[0], By = d.b[1], Bz = d.b[2];
+    const double Vn = u*nx + v*ny + w*nz;
+    const double Bn = Bx*nx + By*ny + Bz*nz;
+    const double B2 = Bx*Bx + By*By + Bz*Bz;
+    const double VdotB = u*Bx + v*By + w*Bz;
+    const double P = d.p + 0.5*B2;
+    const double E = ddiv(d.p, c.gamma - 1.0) + 0.5*(rho*(u*u + v*v + w*w) + B2);
+    const double mn = Vn*rho;
+    f[0] = mn;
+    f[1] = mn*u - Bn*Bx + P*nx;
+    f[2] = mn*v - Bn*By + P*ny;
+    f[3] = mn*w - Bn*Bz + P*nz;
+    f[4] = (v*Bx - By*u)*ny + (w*Bx - Bz*u)*nz + d.phi*nx;
+    f[5] = (u*By - Bx*v)*nx + (w*By - Bz*v)*nz + d.phi*ny;
+    f[6] = (u*Bz - Bx*w)*nx + (v*Bz - By*w)*ny + d.phi*nz;
+    f[7] = Vn*(E + P) - Bn*VdotB;
+    f[8] = (c.refSpeed*c.refSpeed)*Bn;
+  }
+  // The wave speeds the eigenvalue vector is made of (computeEigenValues): Vn, cf, cs, ca.
+  struct Waves { double Vn, cf, cs, ca; };
+  static CFB_HD void waves(const Cfg& c, const MhdData& d, const double* n, Waves& w) {
+    const double Bx = d.b[0] + 0.0, By = d.b[1] + 0.0, Bz = d.b[2] + 0.0;      // B1 + B0 with B0 = 0
+    const Recip rr = recipOf(d.rho);
+    const double invRho = divBy(1., rr);
+    const double sqB = Bx*Bx + By*By + Bz*Bz;
+    w.Vn = d.v[0]*n[0] + d.v[1]*n[1] + d.v[2]*n[2];
+    const double Bn = Bx*n[0] + By*n[1] + Bz*n[2];
+    const double sqrbar = dsqrt(d.rho);
+    const double astar2 = (c.gamma*d.p + sqB)*invRho;
+    const double astarb = dsqrt(astar2*astar2 - 4.0*c.gamma*d.p*Bn*Bn*invRho*invRho);
+    w.cf = dsqrt(0.5*(astar2 + astarb));
+    w.cs = dsqrt(0.5*(astar2 - astarb));
+    w.ca = ddiv(fabs(Bn), sqrbar);
+  }
+  static CFB_HD void eigenValues(const Cfg& c, const Waves& w, double* ev) {
+    ev[0] = w.Vn - w.cf; ev[1] = w.Vn - w.ca; ev[2] = w.Vn - w.cs; ev[3] = w.Vn;
+    ev[4] = c.refSpeed; ev[5] = -c.refSpeed;
+    ev[6] = w.Vn + w.cs; ev[7] = w.Vn + w.ca; ev[8] = w.Vn + w.cf;
+  }
+  static CFB_HD double maxEigenValue(const Cfg& c, const MhdData& d, const double* n) {
+    Waves w;
+    waves(c, d, n, w);
+    return dmax(c.refSpeed, (w.Vn + w.cf));
+  }
+  static CFB_HD void toCons(const Cfg&, const double* s, double* r) {
+#pragma unroll
+    for (int i = 0; i < Q; ++i) r[i] = s[i];
+  }
+
+  // What the centred splitters read of one side: flux, solution state and the three folds over the eigenvalue vector
+  // that LaxFriedFlux.cxx:96-102 / HLLFlux.cxx:93-107 form (each starting from 0.0), plus RealVector::max() of it
+  // (ArrayT.hh:61-66) for the left update coefficient.
+  struct CSide { double f[Q], s[Q], evMax0, evMin0, evAbs0, evVecMax; };
+  static CFB_HD void cside(const Cfg& c, const double* u, const double* n, CSide& o) {
+    MhdData pd;
+    physicalData(c, u, pd);
+    physFlux(c, pd, n, o.f);
+#pragma unroll
+    for (int i = 0; i < Q; ++i) o.s[i] = u[i];
+    Waves w;
+    waves(c, pd, n, w);
+    double ev[Q];
+    eigenValues(c, w, ev);
+    double a = 0.0, b = 0.0, m = 0.0, vm = ev[0];
+#pragma unroll
+    for (int i = 0; i < Q; ++i) {
+      a = dmax(a, ev[i]); b = dmin(b, ev[i]); m = dmax(m, fabs(ev[i]));
+      if (i > 0) vm = dmax(vm, ev[i]);
+    }
+    o.evMax0 = a; o.evMin0 = b; o.evAbs0 = m; o.evVecMax = vm;
+  }
+  // LaxFriedFlux.cxx:79-118:  0.5*(fR + fL - a*k*(sR - sL));  HLLFlux.cxx:73-133
+  static CFB_HD void centred(const Cfg& c, const CSide& l, const CSide& r, double* result) {
+    if (c.fluxSplitter == CFB200_FS_LAXFRIED) {
+      const double aDiff = dmax(r.evAbs0, l.evAbs0)*c.diffRedCoeff;
+#pragma unroll
+      for (int i = 0; i < Q; ++i) result[i] = 0.5*((r.f[i] + l.f[i]) - aDiff*(r.s[i] - l.s[i]));
+    } else {
+      const double amax = dmax(0.0, dmax(r.evMax0, l.evMax0)), amin = dmin(0.0, dmin(r.evMin0, l.evMin0));
+      const Recip rd = recipOf(amax - amin);
+      const double c1 = divBy(amax + amin, rd);
+      double c2;
+      if (!c.hllUseAlpha) c2 = divBy(amax*amin, rd);
+      else c2 = divBy(((divBy(dmax(fabs(amin), fabs(amax)), rd)*2.0)*amax)*amin, rd);
+#pragma unroll
+      for (int i = 0; i < Q; ++i)
+        result[i] = 0.5*(((l.f[i] + r.f[i]) - c1*(r.f[i] - l.f[i])) + c2*(r.s[i] - l.s[i]));
+    }
+  }
+};

@@ -26,6 +26,7 @@ extern "C" {
 #define CFB200_ABI_VERSION 1
 
 /* ---- enums: values are shared with the .CFcase option strings through the plugin ---- */
+enum cfb200_physical_model { CFB200_PM_EULER = 0, CFB200_PM_MHD3D_PROJECTION = 1 };
 enum cfb200_update_var { CFB200_UV_CONS = 0 /* Euler2DCons, Euler3DCons */, CFB200_UV_PVT = 1 /* Euler2DPuvt, Euler3DPvt */ };
 enum cfb200_flux_splitter { CFB200_FS_ROE = 0 /* "Roe" plugins/FiniteVolume/RoeFlux.cxx */,
                             CFB200_FS_AUSMPLUS = 1 /* "AUSMPlus2D/3D" FiniteVolumeNavierStokes/AUSMPlusFlux.ci */,
@@ -99,6 +100,10 @@ typedef struct cfb200_config {
   int32_t hllUseAlpha;      /* HLLFlux.cxx:48 UseAlpha */
   double ausmBeta, ausmAlpha;
   double ausmKu, ausmKp, ausmSigma, machInf;
+  /* physical model: CFB200_PM_EULER (Euler / Navier-Stokes, nEqs = dim + 2) or CFB200_PM_MHD3D_PROJECTION
+   * (plugins/MHD/MHD3DProjectionCons.cxx, dim 3, nEqs 9: rho, rho u, rho v, rho w, Bx, By, Bz, rho E, phi) */
+  int32_t physicalModel, reserved2;
+  double refSpeed;          /* MHD3DProjection.ConvTerm.refSpeed */
 } cfb200_config;
 
 /* Flat mesh data = the contents of the reference's sockets and connectivity tables (SURVEY.md §8b "Data ownership").

@@ -56,7 +56,8 @@ void cfo_mesh_free(void* h) { delete (MeshData*)h; }
 
 int cfo_apply_bc(const Config* c, const MeshView* m, const BC* bcs, double* U) {
   try {
-    if (c->dim == 2) Solver<2>(*c, *m, bcs).applyBC(U); else Solver<3>(*c, *m, bcs).applyBC(U);
+    if (c->physicalModel == PM_MHD3D_PROJECTION) Solver<3, MhdPhys>(*c, *m, bcs).applyBC(U);
+    else if (c->dim == 2) Solver<2>(*c, *m, bcs).applyBC(U); else Solver<3>(*c, *m, bcs).applyBC(U);
   } catch (const std::exception&) { return 2; }
   return 0;
 }
@@ -66,7 +67,12 @@ int cfo_compute(const Config* c, const MeshView* m, const BC* bcs, double* U, Cf
   Outputs o{co->rhs, co->updateCoeff, co->uX, co->uY, co->uZ, co->limiter, co->nstates,
             co->bsrRowPtr, co->bsrColInd, co->bsrVal, 0};
   try {
-    if (c->dim == 2) { Solver<2> s(*c, *m, bcs); s.execute(U, o); }
+    if (c->physicalModel == PM_MHD3D_PROJECTION) {
+      if (c->dim != 3 || c->nEqs != 9 || !(c->fluxSplitter == FS_LAXFRIED || c->fluxSplitter == FS_HLL) ||
+          c->diffusive != DIFF_NONE) { co->status = 2; return 2; }
+      Solver<3, MhdPhys> s(*c, *m, bcs); s.execute(U, o);
+    }
+    else if (c->dim == 2) { Solver<2> s(*c, *m, bcs); s.execute(U, o); }
     else { Solver<3> s(*c, *m, bcs); s.execute(U, o); }
   } catch (const std::exception&) { co->status = 2; return 2; }
   co->status = o.status;
@@ -77,7 +83,8 @@ int cfo_time_rhs(const Config* c, const MeshView* m, const BC* bcs, double* U, c
   Outputs o{co->rhs, co->updateCoeff, co->uX, co->uY, co->uZ, co->limiter, co->nstates,
             co->bsrRowPtr, co->bsrColInd, co->bsrVal, 0};
   try {
-    if (c->dim == 2) Solver<2>(*c, *m, bcs).pseudoSteadyTimeRhs(U, pastU, o);
+    if (c->physicalModel == PM_MHD3D_PROJECTION) Solver<3, MhdPhys>(*c, *m, bcs).pseudoSteadyTimeRhs(U, pastU, o);
+    else if (c->dim == 2) Solver<2>(*c, *m, bcs).pseudoSteadyTimeRhs(U, pastU, o);
     else Solver<3>(*c, *m, bcs).pseudoSteadyTimeRhs(U, pastU, o);
   } catch (const std::exception&) { return 2; }
   return 0;

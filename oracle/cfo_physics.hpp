@@ -32,6 +32,7 @@ template <int D>
 struct Phys {
   static constexpr int Q = D + 2;
   static constexpr int TID = D + 1;
+  typedef PData Data;
 
   // Euler2DCons.cxx:441-465, Euler3DCons.cxx:538-562, Euler2DPuvt.cxx:78-108, Euler3DPvt.ci:76-116
   static void computePhysicalData(const Config& c, const double* s, PData& d) {
@@ -84,6 +85,30 @@ struct Phys {
     s[TID] = rho*d.H - d.p;
   }
 
+  // MirrorEuler2D.cxx:56-94 (+ 3D analogue): nr is the area-weighted face normal
+  static void mirrorGhost(const Config& cfg, const double* nr, const double* inner, double* ghost) {
+    double n[3] = {0,0,0};
+    double s2 = 0.;
+    if (D == 2) s2 = nr[0]*nr[0] + nr[1]*nr[1]; else s2 = nr[0]*nr[0] + nr[1]*nr[1] + nr[2]*nr[2];
+    const double invFaceLength = 1./std::sqrt(s2);
+    for (int i = 0; i < D; ++i) n[i] = nr[i]*invFaceLength;
+    PData di, dg;
+    computePhysicalData(cfg, inner, di);
+    double vn;
+    if (D == 2) vn = di.v[0]*n[0] + di.v[1]*n[1]; else vn = di.v[0]*n[0] + di.v[1]*n[1] + di.v[2]*n[2];
+    const double gamma = cfg.gamma;
+    const double gammaDivGammaMinus1 = gamma/(gamma - 1.0);
+    dg.rho = di.rho;
+    dg.v[2] = 0.;
+    for (int i = 0; i < D; ++i) dg.v[i] = di.v[i] - 2.0*vn*n[i];
+    dg.V = di.V;
+    dg.p = di.p;
+    dg.H = (gammaDivGammaMinus1*dg.p + 0.5*dg.rho*dg.V*dg.V)/dg.rho;
+    dg.A = std::sqrt(gamma*dg.p/dg.rho);
+    dg.T = di.T;
+    stateFromPhysicalDataCons(dg, ghost);
+  }
+
   // Euler2DVarSet.cxx:83-117, Euler3DVarSet.cxx:78-105
   static void convFlux(const PData& d, const double* n, double* f) {
     double un;
@@ -101,6 +126,16 @@ struct Phys {
     if (D == 2) un = d.v[0]*n[0] + d.v[1]*n[1];
     else        un = d.v[0]*n[0] + d.v[1]*n[1] + d.v[2]*n[2];
     return un + d.A;
+  }
+
+  static double maxEigenValue(const Config&, const PData& d, const double* n) { return maxEigenValue(d, n); }
+  // RealVector::max() of computeEigenValues (ArrayT.hh:61-66)
+  static double evMaxOfVector(const Config&, const PData& d, const double* n) {
+    double ev[Q];
+    eigenValues(d, n, ev);
+    double emax = ev[0];
+    for (int i = 1; i < Q; ++i) emax = std::max(emax, ev[i]);
+    return emax;
   }
 
   // update -> solution(Cons): identity or EulerPvtToCons.cxx:49-70
@@ -499,5 +534,170 @@ static inline void faceTriagNormal(const double* ci, const double* cj, const dou
   crossProd(v1, v2, v3);
   for (int d = 0; d < 3; ++d) out[d] = v3[d]*0.5;
 }
+
+} // namespace cfo
+
+namespace cfo {
+
+// ---------------------------------------------------------------------------
+// MHD3DProjection in conservative variables (a13): rho, rho u, rho v, rho w, Bx, By, Bz, rho E, phi.
+// plugins/MHD/MHD3DProjectionCons.cxx:540-574 (computePhysicalData), :1132-1148 (computeStateFromPhysicalData),
+// plugins/MHD/MHD3DProjectionVarSet.cxx:42-78 (computeFlux), :398-436 (getMaxEigenValue), :499-548 (computeEigenValues);
+// no background potential field (potentialBType unset: B0 = 0).  Only the centred splitters (LaxFried, HLL) apply.
+struct MhdData { double rho, p, A, V, B, phi, v[3], b[3]; };
+
+struct MhdPhys {
+  static constexpr int D = 3;
+  static constexpr int Q = 9;
+  static constexpr int TID = 7;
+  typedef MhdData Data;
+
+  static void computePhysicalData(const Config& c, const double* s, MhdData& d) {
+    const double rho = s[0];
+    const double u = s[1]/rho, v = s[2]/rho, w = s[3]/rho;
+    const double Bx = s[4], By = s[5], Bz = s[6];
+    const double V2 = u*u + v*v + w*w;
+    const double B2 = Bx*Bx + By*By + Bz*Bz;
+    d.v[0] = u; d.v[1] = v; d.v[2] = w;
+    d.b[0] = Bx; d.b[1] = By; d.b[2] = Bz;
+    d.B = std::sqrt(B2);
+    d.rho = rho;
+    d.V = std::sqrt(V2);
+    d.p = (c.gamma - 1.)*(s[7] - 0.5*(rho*V2 + B2));
+    d.phi = s[8];
+    d.A = std::sqrt(c.gamma*d.p/rho);
+  }
+  static void stateFromPhysicalData(const Config& c, const MhdData& d, double* s) {
+    const double rho = d.rho;
+    s[0] = rho;
+    s[1] = rho*d.v[0]; s[2] = rho*d.v[1]; s[3] = rho*d.v[2];
+    s[4] = d.b[0]; s[5] = d.b[1]; s[6] = d.b[2];
+    const double B = d.B;
+    s[7] = d.p/(c.gamma - 1.0) + 0.5*(rho*d.V*d.V + B*B);
+    s[8] = d.phi;
+  }
+  // FiniteVolumeMHD/MirrorMHD3DProjection.cxx:56-96
+  static void mirrorGhost(const Config& c, const double* nr, const double* inner, double* ghost) {
+    double nx = nr[0], ny = nr[1], nz = nr[2];
+    const double invFaceLength = 1./std::sqrt(nx*nx + ny*ny + nz*nz);
+    nx *= invFaceLength; ny *= invFaceLength; nz *= invFaceLength;
+    MhdData di, dg;
+    computePhysicalData(c, inner, di);
+    const double vn = di.v[0]*nx + di.v[1]*ny + di.v[2]*nz;
+    const double bn = di.b[0]*nx + di.b[1]*ny + di.b[2]*nz;
+    dg.rho = di.rho;
+    dg.v[0] = di.v[0] - 2.0*vn*nx; dg.v[1] = di.v[1] - 2.0*vn*ny; dg.v[2] = di.v[2] - 2.0*vn*nz;
+    dg.b[0] = di.b[0] - 2.0*bn*nx; dg.b[1] = di.b[1] - 2.0*bn*ny; dg.b[2] = di.b[2] - 2.0*bn*nz;
+    dg.V = di.V; dg.A = di.A; dg.p = di.p; dg.B = di.B; dg.phi = di.phi;
+    stateFromPhysicalData(c, dg, ghost);
+  }
+  static void convFlux(const Config& c, const MhdData& d, const double* n, double* f) {
+    const double nx = n[0], ny = n[1], nz = n[2];
+    const double rho = d.rho, u = d.v[0], v = d.v[1], w = d.v[2], Bx = d.b[0], By = d.b[1], Bz = d.b[2];
+    const double Vn = u*nx + v*ny + w*nz;
+    const double Bn = Bx*nx + By*ny + Bz*nz;
+    const double B2 = Bx*Bx + By*By + Bz*Bz;
+    const double VdotB = u*Bx + v*By + w*Bz;
+    const double p = d.p, phi = d.phi;
+    const double P = p + 0.5*B2;
+    const double E = p/(c.gamma - 1.0) + 0.5*(rho*(u*u + v*v + w*w) + B2);
+    const double refSpeedSq = c.refSpeed*c.refSpeed;
+    f[0] = Vn*rho;
+    f[1] = Vn*rho*u - Bn*Bx + P*nx;
+    f[2] = Vn*rho*v - Bn*By + P*ny;
+    f[3] = Vn*rho*w - Bn*Bz + P*nz;
+    f[4] = (v*Bx - By*u)*ny + (w*Bx - Bz*u)*nz + phi*nx;
+    f[5] = (u*By - Bx*v)*nx + (w*By - Bz*v)*nz + phi*ny;
+    f[6] = (u*Bz - Bx*w)*nx + (v*Bz - By*w)*ny + phi*nz;
+    f[7] = Vn*(E + P) - Bn*VdotB;
+    f[8] = refSpeedSq*Bn;
+  }
+  static void eigenValues(const Config& c, const MhdData& d, const double* n, double* ev) {
+    const double Bx = d.b[0] + 0.0, By = d.b[1] + 0.0, Bz = d.b[2] + 0.0;    // B1 + B0, B0 = 0
+    const double invRho = 1./d.rho;
+    const double sqB = Bx*Bx + By*By + Bz*Bz;
+    const double p = d.p;
+    const double Vn = d.v[0]*n[0] + d.v[1]*n[1] + d.v[2]*n[2];
+    const double Bn = Bx*n[0] + By*n[1] + Bz*n[2];
+    const double sqrbar = std::sqrt(d.rho);
+    const double astar2 = (c.gamma*p + sqB)*invRho;
+    const double astarb = std::sqrt(astar2*astar2 - 4.0*c.gamma*p*Bn*Bn*invRho*invRho);
+    const double cf2 = 0.5*(astar2 + astarb);
+    const double cs2 = 0.5*(astar2 - astarb);
+    const double ca = std::abs(Bn)/sqrbar;
+    const double cf = std::sqrt(cf2);
+    const double cs = std::sqrt(cs2);
+    ev[0] = Vn - cf; ev[1] = Vn - ca; ev[2] = Vn - cs; ev[3] = Vn;
+    ev[4] = c.refSpeed; ev[5] = -c.refSpeed;
+    ev[6] = Vn + cs; ev[7] = Vn + ca; ev[8] = Vn + cf;
+  }
+  // MHD3DProjectionVarSet.cxx:398-436 (what the RIGHT side of the update coefficient uses; the left side uses
+  // _leftEv.max(): LaxFriedFlux.cxx:131, HLLFlux.cxx:141)
+  static double maxEigenValue(const Config& c, const MhdData& d, const double* n) {
+    const double Bx = d.b[0] + 0.0, By = d.b[1] + 0.0, Bz = d.b[2] + 0.0;
+    const double invRho = 1./d.rho;
+    const double sqB = Bx*Bx + By*By + Bz*Bz;
+    const double p = d.p;
+    const double Vn = d.v[0]*n[0] + d.v[1]*n[1] + d.v[2]*n[2];
+    const double Bn = Bx*n[0] + By*n[1] + Bz*n[2];
+    const double astar2 = (c.gamma*p + sqB)*invRho;
+    const double astarb = std::sqrt(astar2*astar2 - 4.0*c.gamma*p*Bn*Bn*invRho*invRho);
+    const double cf2 = 0.5*(astar2 + astarb);
+    const double cf = std::sqrt(cf2);
+    return std::max(c.refSpeed, (Vn + cf));
+  }
+  static double evMaxOfVector(const Config& c, const MhdData& d, const double* n) {
+    double ev[Q];
+    eigenValues(c, d, n, ev);
+    double emax = ev[0];
+    for (int i = 1; i < Q; ++i) emax = std::max(emax, ev[i]);
+    return emax;
+  }
+  static void toCons(const Config&, const double* s, double* r) { for (int i = 0; i < Q; ++i) r[i] = s[i]; }
+
+  // LaxFriedFlux.cxx:79-118 and HLLFlux.cxx:73-133 on the MHD variable set (update = solution = Cons)
+  static bool centredFlux(const Config& c, const double* uL, const double* uR, const MhdData& pL, const MhdData& pR,
+                          const double* n, double* result) {
+    double fL[Q], fR[Q], evL[Q], evR[Q];
+    convFlux(c, pR, n, fR); convFlux(c, pL, n, fL);
+    eigenValues(c, pR, n, evR); eigenValues(c, pL, n, evL);
+    if (c.fluxSplitter == FS_LAXFRIED) {
+      double aR = 0.0, aL = 0.0;
+      for (int i = 0; i < Q; ++i) { aR = std::max(aR, std::abs(evR[i])); aL = std::max(aL, std::abs(evL[i])); }
+      const double a = std::max(aR, aL);
+      const double aDiff = a*c.diffRedCoeff;
+      for (int i = 0; i < Q; ++i) {
+        const double sumFlux = fR[i] + fL[i];
+        result[i] = 0.5*(sumFlux - aDiff*(uR[i] - uL[i]));
+      }
+    } else {
+      double aR = 0.0, aL = 0.0;
+      for (int i = 0; i < Q; ++i) { aR = std::max(aR, evR[i]); aL = std::max(aL, evL[i]); }
+      const double amax = std::max(0.0, std::max(aR, aL));
+      aR = 0.0; aL = 0.0;
+      for (int i = 0; i < Q; ++i) { aR = std::min(aR, evR[i]); aL = std::min(aL, evL[i]); }
+      const double amin = std::min(0.0, std::min(aR, aL));
+      const double c1 = (amax + amin)/(amax - amin);
+      double c2;
+      if (!c.hllUseAlpha) c2 = amax*amin/(amax - amin);
+      else {
+        const double alpha = std::max(std::abs(amin), std::abs(amax))/(amax - amin);
+        c2 = alpha*2.0*amax*amin/(amax - amin);
+      }
+      for (int i = 0; i < Q; ++i)
+        result[i] = 0.5*(fL[i] + fR[i] - c1*(fR[i] - fL[i]) + c2*(uR[i] - uL[i]));
+    }
+    return true;
+  }
+  // not available for this model (the configuration is rejected before the solver runs)
+  static bool roeFlux(const Config&, const double*, const double*, const MhdData&, const MhdData&, const double*, double*) { return false; }
+  static bool ausmFlux(const Config&, const MhdData&, const MhdData&, const double*, double*) { return false; }
+  static double dynViscosity(const Config&, const double*) { return 0.; }
+  static double thermConductivity(const Config&, double) { return 0.; }
+  static double nsDensity(const Config&, const double*) { return 1.; }
+  static void nsFluxUnit(const Config&, const double*, const double (*)[3], const double*, double, double, double* f) {
+    for (int i = 0; i < Q; ++i) f[i] = 0.;
+  }
+};
 
 } // namespace cfo

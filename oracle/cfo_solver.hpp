@@ -24,11 +24,12 @@ struct Outputs {
   int32_t status;       // 0 ok, 1 = a2<0 in the Roe linearisation (BadValueException)
 };
 
-template <int D>
+template <int D, class PHYS = Phys<D> >
 class Solver {
 public:
-  static constexpr int Q = D + 2;
-  typedef Phys<D> P;
+  typedef PHYS P;                       // Phys<D>: Euler / Navier-Stokes (Q = D + 2);  MhdPhys: MHD3DProjection (Q = 9)
+  static constexpr int Q = P::Q;
+  typedef typename P::Data PData;
 
   Solver(const Config& c, const MeshView& m, const BC* bcs) : cfg(c), mesh(m), bc(bcs) {}
 
@@ -52,30 +53,9 @@ public:
         ghost[Q-1] = inner[Q-1];
         break;
       }
-      case BC_MIRROR_EULER_CONS: {     // MirrorEuler2D.cxx:56-94
-        const double* nr = &mesh.normals[(size_t)f*D];
-        double n[3] = {0,0,0};
-        double s2 = 0.;
-        if (D == 2) s2 = nr[0]*nr[0] + nr[1]*nr[1]; else s2 = nr[0]*nr[0] + nr[1]*nr[1] + nr[2]*nr[2];
-        const double invFaceLength = 1./std::sqrt(s2);
-        for (int i = 0; i < D; ++i) n[i] = nr[i]*invFaceLength;
-        PData di, dg;
-        P::computePhysicalData(cfg, inner, di);
-        double vn;
-        if (D == 2) vn = di.v[0]*n[0] + di.v[1]*n[1]; else vn = di.v[0]*n[0] + di.v[1]*n[1] + di.v[2]*n[2];
-        const double gamma = cfg.gamma;
-        const double gammaDivGammaMinus1 = gamma/(gamma - 1.0);
-        dg.rho = di.rho;
-        dg.v[2] = 0.;
-        for (int i = 0; i < D; ++i) dg.v[i] = di.v[i] - 2.0*vn*n[i];
-        dg.V = di.V;
-        dg.p = di.p;
-        dg.H = (gammaDivGammaMinus1*dg.p + 0.5*dg.rho*dg.V*dg.V)/dg.rho;
-        dg.A = std::sqrt(gamma*dg.p/dg.rho);
-        dg.T = di.T;
-        P::stateFromPhysicalDataCons(dg, ghost);
+      case BC_MIRROR_EULER_CONS:       // MirrorEuler2D.cxx:56-94 / MirrorMHD3DProjection.cxx:56-96
+        P::mirrorGhost(cfg, &mesh.normals[(size_t)f*D], inner, ghost);
         break;
-      }
       default: throw std::runtime_error("unknown BC type");
     }
   }
@@ -379,12 +359,15 @@ public:
     }
     if (!isPerturb) {
       const double faceArea = x.area/1;       // polyRec->nbQPoints() == 1
-      double maxEV = P::maxEigenValue(x.pL, x.n);
+      // left side: getMaxEigenValue (Roe, AUSM) or _leftEv.max() (LaxFriedFlux.cxx:131, HLLFlux.cxx:141); right side:
+      // getMaxEigenValue with the reversed normal in all splitters
+      const bool centred = (cfg.fluxSplitter == FS_LAXFRIED || cfg.fluxSplitter == FS_HLL);
+      double maxEV = centred ? P::evMaxOfVector(cfg, x.pL, x.n) : P::maxEigenValue(cfg, x.pL, x.n);
       o.updateCoeff[x.L] += std::max(maxEV, 0.)*faceArea;
       if (!x.isB) {
         double tn[3];
         for (int i = 0; i < D; ++i) tn[i] = -1.0*x.n[i];
-        maxEV = P::maxEigenValue(x.pR, tn);
+        maxEV = P::maxEigenValue(cfg, x.pR, tn);
         o.updateCoeff[x.R] += std::max(maxEV, 0.)*faceArea;
       }
     }

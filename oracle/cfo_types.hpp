@@ -30,6 +30,7 @@ constexpr int MAXEQ = 9;
 constexpr int MAXDIM = 3;
 
 // ---- enums shared (by value) with the product's include/cfb200.h -------------
+enum PhysicalModel { PM_EULER = 0, PM_MHD3D_PROJECTION = 1 };
 enum UpdateVar { UV_CONS = 0, UV_PVT = 1 };            // Euler{2,3}DCons / Euler2DPuvt, Euler3DPvt
 enum FluxSplitter { FS_ROE = 0, FS_AUSMPLUS = 1, FS_AUSMPLUSUP = 2, FS_LAXFRIED = 3, FS_HLL = 4 };
 enum PolyRec { PR_CONSTANT = 0, PR_LINEARLS = 1 };
@@ -93,6 +94,10 @@ struct Config {
   int32_t hllUseAlpha;    // HLLFlux.cxx:48 UseAlpha
   double ausmBeta, ausmAlpha;                 // AUSM+ : 1/8, 3/16
   double ausmKu, ausmKp, ausmSigma, machInf;  // AUSM+up : 0.75, 0.25, 1.0, (required > 0)
+  // physical model: 0 = Euler / Navier-Stokes (nEqs = dim + 2), 1 = MHD3DProjection (dim 3, nEqs 9, Cons variables)
+  int32_t physicalModel;
+  int32_t reserved2;
+  double refSpeed;        // MHDProjectionTerm refSpeed (hyperbolic divergence cleaning speed)
 };
 
 struct MeshView {

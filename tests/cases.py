@@ -17,7 +17,18 @@ def init_state(fm, q, pvt, seed=67890):
     n = fm.nCells
     U = np.zeros((n + fm.nGhosts, q))
     s = 1.0 + 0.05*np.sin(2*np.pi*x[:, 0])*np.cos(2*np.pi*x[:, 1]) + 0.01*rng.standard_normal(n)
-    if pvt:
+    if pvt == "mhd":
+        # rho, rho V, B (dipole-like smooth field + uniform part), rho E, phi
+        rho = s
+        u = 0.8 + 0.1*np.cos(2*np.pi*x[:, 1]); v = 0.05*np.sin(2*np.pi*x[:, 0]); w = 0.02*np.sin(2*np.pi*x[:, 2])
+        r2 = ((x - np.array([0.5, 0.5, -0.6]))**2).sum(axis=1)
+        bx = 0.3 + 0.05*(x[:, 0] - 0.5)/r2**1.5; by = 0.1 + 0.05*(x[:, 1] - 0.5)/r2**1.5; bz = 0.05 + 0.05*(x[:, 2] + 0.6)/r2**1.5
+        p = 1.0 + 0.05*np.cos(2*np.pi*x[:, 0])
+        U[:n, 0] = rho; U[:n, 1] = rho*u; U[:n, 2] = rho*v; U[:n, 3] = rho*w
+        U[:n, 4] = bx; U[:n, 5] = by; U[:n, 6] = bz
+        U[:n, 7] = p/0.05 + 0.5*rho*(u*u + v*v + w*w) + 0.5*(bx*bx + by*by + bz*bz)
+        U[:n, 8] = 0.01*np.sin(2*np.pi*x[:, 0])*np.sin(2*np.pi*x[:, 1])
+    elif pvt:
         U[:n, 0] = s
         U[:n, 1] = 0.4 + 0.05*np.cos(2*np.pi*x[:, 1])
         U[:n, 2] = 0.03*np.sin(2*np.pi*x[:, 0])
@@ -71,6 +82,21 @@ def bcs_euler2d():
 def bcs_euler3d():
     mir = B.make_bc(B.BC_MIRROR_EULER_CONS)
     return [B.make_bc(B.BC_SUPER_OUTLET)]*2 + [mir]*4
+
+
+def bcs_mhd3d():
+    """SuperInlet (constant Def) / SuperOutlet / MirrorMHD3DProjection."""
+    inl = B.make_bc(B.BC_DIRICHLET, mask=[1]*9, value=[1.0, 0.8, 0.0, 0.0, 0.3, 0.1, 0.05, 2.5, 0.0])
+    mir = B.make_bc(B.BC_MIRROR_EULER_CONS)      # dispatched by the physical model: MirrorMHD3DProjection
+    return [inl, B.make_bc(B.BC_SUPER_OUTLET), mir, mir, mir, mir]
+
+
+def mhd3d_cfg(**over):
+    """BASELINE config 4: MHD3DProjection, q = 9, gamma 1.05, refSpeed 1."""
+    kw = dict(physical_model=B.PM_MHD3D_PROJECTION, flux=B.FS_HLL, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN,
+              jacobian=True, gamma=1.05, ref_speed=1.0)
+    kw.update(over)
+    return B.make_config(3, **kw)
 
 
 def ns3d_cfg(**over):
@@ -138,6 +164,14 @@ CASES = {
                            bcs_ns3d, True),
     "ns2d_quad_laxfried": (lambda: meshgen.quad_channel(10, 8), lambda: ns2d_cfg(flux=B.FS_LAXFRIED, diff_red_coeff=0.8),
                            bcs_ns2d, True),
+    # BASELINE config 4: 3D ideal MHD with hyperbolic divergence cleaning (q = 9), HLL / Lax-Friedrichs
+    "mhd3d_hex_hll": (lambda: meshgen.hex_box(5, 4, 4), mhd3d_cfg, bcs_mhd3d, "mhd"),
+    "mhd3d_tet_laxfried_1st": (lambda: meshgen.tet_box(3, 3, 2),
+                               lambda: mhd3d_cfg(flux=B.FS_LAXFRIED, poly_rec=B.PR_CONSTANT, limiter=B.LIM_NONE),
+                               bcs_mhd3d, "mhd"),
+    "mhd3d_hex_laxfried_barth": (lambda: meshgen.hex_box(4, 4, 3),
+                                 lambda: mhd3d_cfg(flux=B.FS_LAXFRIED, limiter=B.LIM_BARTHJESP, res_factor=0.5),
+                                 bcs_mhd3d, "mhd"),
     # single cell / single row edge cases
     "ns3d_single_cell": (lambda: meshgen.hex_box(1, 1, 1, jitter=0.0), ns3d_cfg, bcs_ns3d, True),
     "euler2d_single_row": (lambda: meshgen.quad_channel(5, 1), lambda: B.make_config(2, poly_rec=B.PR_LINEARLS,
