@@ -378,6 +378,31 @@ struct CellGather {   // idx over cells
   }
 };
 
+// a22: FVMCC_ComputeRHSMHD<BASE>::computeInterConvDiff (FiniteVolumeMHD/FVMCC_ComputeRHSMHD.ci:160-203): the cell divergence of B
+// from the last component (the phi equation) of the face fluxes of the last evaluation,
+//   divB[L] += F[q-1]/(refSpeed^2 V_L),  divB[R] -= F[q-1]/(refSpeed^2 V_R),
+// gathered per cell in face-loop order like the residual.
+template <int D, class PH = Phys<D> >
+struct DivBGather {   // idx over cells
+  Dev d; Cfg c; double* out;
+  CFB_HD void operator()(int cell) const {
+    constexpr int Q = PH::Q;
+    const double den = (c.refSpeed*c.refSpeed)*d.volumes[cell];
+    const Recip rd = recipOf(den);
+    double acc = 0.;
+    for (int j = d.cellFacePtr[cell]; j < d.cellFacePtr[cell+1]; ++j) {
+      const int e = d.cellFaceSorted[j];
+      const bool isR = e < 0;
+      const int f = isR ? ~e : e;
+      const bool skip = !(d.updatable[d.faceL[f]] || (f < d.nInner && d.updatable[d.faceR[f]]));
+      if (skip) continue;
+      const double t = divBy(d.faceFlux[(size_t)(Q-1)*d.nFaces + f], rd);
+      if (isR) acc -= t; else acc += t;
+    }
+    out[cell] = acc;
+  }
+};
+
 // Diagonal blocks: one thread per (cell, block entry).  diag(c) = sum over the cell's faces in loop order of
 //   inner face, c == L:  -block(R,c)      inner face, c == R:  -block(L,c)      boundary face: +bnd block
 // Rows of non-updatable cells are staging only and are zeroed by ZeroRows afterwards.

@@ -292,7 +292,7 @@ class Engine:
         n = {"rhs": fm.nCells*q, "updateCoeff": fm.nCells, "uX": fm.nCells*q, "uY": fm.nCells*q, "uZ": fm.nCells*q,
              "limiter": fm.nCells*q, "nstates": fm.nNodes*q, "states": (fm.nCells + fm.nGhosts)*q,
              "gstates": fm.nGhosts*q, "faceFlux": fm.nFaces*q, "faceCentres": fm.nFaces*fm.dim,
-             "bndBlocks": fm.nGhosts*q*q}[name]
+             "bndBlocks": fm.nGhosts*q*q, "divB": fm.nCells}[name]
         a = np.empty(n)
         self._chk(self.L.get_field(self.h, name.encode(), _pd(a)), "get_field " + name)
         return a

@@ -199,7 +199,9 @@ int64_t cfb200_bsr_nnzb(cfb200_handle* h);
 int cfb200_get_bsr_values(cfb200_handle* h, double* val /* [nnzb*q*q] */);
 /* scalar CSR view for Paralution (ParalutionMatrix.hh:144 SetDataPtrCSR): rows of a cell one after the other */
 int cfb200_export_csr(cfb200_handle* h, int32_t* rowOff, int32_t* col, double* val);
-/* named fields, reference (AoS, reference IDs) layout: "rhs","updateCoeff","uX","uY","uZ","limiter","nstates","gstates" */
+/* named fields, reference (AoS, reference IDs) layout: "rhs","updateCoeff","uX","uY","uZ","limiter","nstates","gstates";
+ * "divB" [nCells] (MHD3DProjection only): the divergence diagnostic of FVMCC_ComputeRHSMHD.ci:160-203, formed from the
+ * face fluxes of the last evaluation */
 int cfb200_get_field(cfb200_handle* h, const char* name, double* out);
 const double* cfb200_device_ptr(cfb200_handle* h, const char* name);
 /* status of the last evaluation: 0 or CFB200_ERR_BAD_VALUE */

@@ -28,7 +28,7 @@ class MeshView(C.Structure):
 
 class Outputs(C.Structure):
     _fields_ = [("rhs", P_D), ("updateCoeff", P_D), ("uX", P_D), ("uY", P_D), ("uZ", P_D), ("limiter", P_D),
-                ("nstates", P_D), ("bsrRowPtr", P_I), ("bsrColInd", P_I), ("bsrVal", P_D), ("status", C.c_int32)]
+                ("nstates", P_D), ("bsrRowPtr", P_I), ("bsrColInd", P_I), ("bsrVal", P_D), ("status", C.c_int32), ("divB", P_D)]
 
 
 def build(omp=False, ref=True):
@@ -158,6 +158,8 @@ def alloc_outputs(cfg, fm, jacobian, limiter_init=None):
     o.limiter, o.nstates = pd(r.limiter), pd(r.nstates)
     o.bsrRowPtr, o.bsrColInd = pi(fm.bsrRowPtr), pi(fm.bsrColInd)
     o.bsrVal = pd(r.bsrVal) if jacobian else None
+    r.divB = np.zeros(fm.nCells) if cfg.nEqs == 9 else None
+    o.divB = pd(r.divB) if r.divB is not None else None
     r._o = o
     return r
 

@@ -19,7 +19,7 @@ extern "C" {
 
 struct CfoOutputs {
   double* rhs; double* updateCoeff; double* uX; double* uY; double* uZ; double* limiter; double* nstates;
-  const int32_t* bsrRowPtr; const int32_t* bsrColInd; double* bsrVal; int32_t status;
+  const int32_t* bsrRowPtr; const int32_t* bsrColInd; double* bsrVal; int32_t status; double* divB;
 };
 
 void* cfo_mesh_build(int dim, int nNodes, const double* nodes, int nCells, const int32_t* cellNodePtr,
@@ -65,7 +65,7 @@ int cfo_apply_bc(const Config* c, const MeshView* m, const BC* bcs, double* U) {
 // One ComputeRHS (+Jacobian) evaluation.  Ghost states in U must have been set (cfo_apply_bc).
 int cfo_compute(const Config* c, const MeshView* m, const BC* bcs, double* U, CfoOutputs* co) {
   Outputs o{co->rhs, co->updateCoeff, co->uX, co->uY, co->uZ, co->limiter, co->nstates,
-            co->bsrRowPtr, co->bsrColInd, co->bsrVal, 0};
+            co->bsrRowPtr, co->bsrColInd, co->bsrVal, 0, co->divB};
   try {
     if (c->physicalModel == PM_MHD3D_PROJECTION) {
       if (c->dim != 3 || c->nEqs != 9 || !(c->fluxSplitter == FS_LAXFRIED || c->fluxSplitter == FS_HLL) ||
@@ -81,7 +81,7 @@ int cfo_compute(const Config* c, const MeshView* m, const BC* bcs, double* U, Cf
 
 int cfo_time_rhs(const Config* c, const MeshView* m, const BC* bcs, double* U, const double* pastU, CfoOutputs* co) {
   Outputs o{co->rhs, co->updateCoeff, co->uX, co->uY, co->uZ, co->limiter, co->nstates,
-            co->bsrRowPtr, co->bsrColInd, co->bsrVal, 0};
+            co->bsrRowPtr, co->bsrColInd, co->bsrVal, 0, co->divB};
   try {
     if (c->physicalModel == PM_MHD3D_PROJECTION) Solver<3, MhdPhys>(*c, *m, bcs).pseudoSteadyTimeRhs(U, pastU, o);
     else if (c->dim == 2) Solver<2>(*c, *m, bcs).pseudoSteadyTimeRhs(U, pastU, o);

@@ -22,6 +22,7 @@ struct Outputs {
   const int32_t* bsrColInd;
   double* bsrVal;       // [nnzb*q*q], block row-major [ib][jb]  (BlockAccumulator.hh:289-296)
   int32_t status;       // 0 ok, 1 = a2<0 in the Roe linearisation (BadValueException)
+  double* divB;         // [nCells] or null: FVMCC_ComputeRHSMHD.ci:160-203 diagnostic (zeroed here, MHD only)
 };
 
 template <int D, class PHYS = Phys<D> >
@@ -541,6 +542,7 @@ public:
     }
     extrapolateInAllNodes(U, o);
 
+    if (o.divB) for (int i = 0; i < nc; ++i) o.divB[i] = 0.;
     FaceCtx x;
     double flux[Q], dFlux[Q], pertFlux[Q], fluxDiff[Q];
     for (int f = 0; f < mesh.nFaces; ++f) {
@@ -559,6 +561,12 @@ public:
         freezeCoeff = false;
         diffusiveFlux(x, U, false, 0, o, dFlux);
         for (int i = 0; i < Q; ++i) flux[i] -= dFlux[i];
+      }
+      if (o.divB && P::Q == 9) {
+        // a22: FVMCC_ComputeRHSMHD<BASE>::computeInterConvDiff (FiniteVolumeMHD/FVMCC_ComputeRHSMHD.ci:160-203)
+        const double refSpeedSq = cfg.refSpeed*cfg.refSpeed;
+        o.divB[x.L] += flux[Q-1]/(refSpeedSq*mesh.volumes[x.L]);
+        if (!x.isB) o.divB[x.R] -= flux[Q-1]/(refSpeedSq*mesh.volumes[x.R]);
       }
       // updateRHS (FVMCC_ComputeRHS.cxx:455-514), non axisymmetric: _rMid = _invr = 1
       {

@@ -55,11 +55,28 @@ void FVMCC_ComputeRHSB200::fillConfig(cfb200_config& c)
   const CFuint nbEqs = PhysicalModelStack::getActive()->getNbEq();
   std::memset(&c, 0, sizeof(c));
   c.dim = dim; c.nEqs = nbEqs;
-  SafePtr<Physics::NavierStokes::EulerTerm> eulerTerm = PhysicalModelStack::getActive()->getImplementor()->
-    getConvectiveTerm().d_castTo<Physics::NavierStokes::EulerTerm>();
-  c.gamma = eulerTerm->getGamma(); c.R = eulerTerm->getR();
+  const std::string model = PhysicalModelStack::getActive()->getImplementor()->getConvectiveName();
+  if (model.find("MHD3DProjection") == 0) {
+    // plugins/MHD: MHD3DProjection.ConvTerm.gamma / refSpeed (e.g. Dipole3D/dipole3DFVMMHDProjImpl.CFcase)
+    SafePtr<Physics::MHD::MHDProjectionTerm> mhdTerm = PhysicalModelStack::getActive()->getImplementor()->
+      getConvectiveTerm().d_castTo<Physics::MHD::MHDProjectionTerm>();
+    c.physicalModel = CFB200_PM_MHD3D_PROJECTION;
+    c.gamma = mhdTerm->getGamma(); c.refSpeed = mhdTerm->getRefSpeed(); c.R = 1.0;
+  } else {
+    SafePtr<Physics::NavierStokes::EulerTerm> eulerTerm = PhysicalModelStack::getActive()->getImplementor()->
+      getConvectiveTerm().d_castTo<Physics::NavierStokes::EulerTerm>();
+    c.physicalModel = CFB200_PM_EULER;
+    c.gamma = eulerTerm->getGamma(); c.R = eulerTerm->getR();
+  }
   c.updateVar = (getMethodData().getUpdateVarStr() == "Cons") ? CFB200_UV_CONS : CFB200_UV_PVT;
-  c.fluxSplitter = CFB200_FS_ROE;
+  // CellCenterFVM.Data.FluxSplitter = Roe | AUSMPlus{2,3}D | AUSMPlusUp{2,3}D | LaxFried | HLL
+  const std::string fs = getMethodData().getFluxSplitter()->getName();
+  c.fluxSplitter = (fs.find("AUSMPlusUp") == 0) ? CFB200_FS_AUSMPLUSUP : (fs.find("AUSMPlus") == 0) ? CFB200_FS_AUSMPLUS :
+                   (fs == "LaxFried") ? CFB200_FS_LAXFRIED : (fs == "HLL") ? CFB200_FS_HLL : CFB200_FS_ROE;
+  // AUSMFlux.ci:55, AUSMPlusFlux.ci:17-23, AUSMPlusUpFlux.ci:20-33 defaults; the configured values are read from the
+  // splitter's option map (choiceA12, beta, alpha, coeffKu, coeffKp, sigma, machInf), HLLFlux.cxx:48 UseAlpha
+  c.choiceA12 = 1; c.ausmBeta = 1./8.; c.ausmAlpha = 3./16.; c.ausmKu = 0.75; c.ausmKp = 0.25; c.ausmSigma = 1.0;
+  c.machInf = 0.0; c.hllUseAlpha = 0;
   c.polyRec = (getMethodData().getPolyReconstructor()->getName() == "Constant") ? CFB200_PR_CONSTANT : CFB200_PR_LINEARLS;
   const std::string lim = getMethodData().getLimiter()->getName();
   c.limiter = (lim.find("Venktn") == 0) ? CFB200_LIM_VENKTN : (lim == "BarthJesp" ? CFB200_LIM_BARTHJESP : CFB200_LIM_NONE);

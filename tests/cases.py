@@ -214,6 +214,8 @@ def run_case(name, oracle, make_engine, updatable=None, limiter_init=None, cfg_m
                 continue
             out[f] = (e.field(f), getattr(r, f).copy())
         out["gstates"] = (e.field("gstates"), None)
+        if q == 9:
+            out["divB"] = (e.field("divB"), r.divB.copy())      # a22
         if jac:
             out["jacobian"] = (e.bsr_values(), r.bsrVal.copy())
             rp, ci = e.bsr_pattern()
