@@ -61,12 +61,26 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def flagship(n):
-    """configs[2]: jittered hex box n^3, Pvt variables, one inlet / outlet / no-slip wall / mirrors."""
+def flagship(n, workload="ns3d"):
+    """configs[2]: jittered hex box n^3, Pvt variables, one inlet / outlet / no-slip wall / mirrors;
+    `mhd3d` = configs[3]: the same box with MHD3DProjection (q = 9), HLL, LSQ + Venkatakrishnan."""
     import cases
     from coolfluid_b200 import meshgen
     em = meshgen.hex_box(n, n, n)
+    if workload == "mhd3d":
+        return em, cases.mhd3d_cfg(), cases.bcs_mhd3d()
     return em, cases.ns3d_cfg(), cases.bcs_ns3d()
+
+
+WORKLOADS = {
+    # name: (description, pvt flag of cases.init_state, A_rhs, A_jac)   [SURVEY.md §8d algorithmic bytes per cell-update]
+    "ns3d": ("configs[2]: 3D Navier-Stokes, %d^3 = %d jittered hex cells per GPU, Pvt variables, Roe + viscous "
+             "(DiamondVolume3D) flux, LinearLS3D + Venktn3D, finite-difference block Jacobian (NumJacob) into device "
+             "BSR, pseudo-steady time term", True, 744, 1400),
+    "mhd3d": ("configs[3]: 3D ideal MHD (MHD3DProjection, q = 9), %d^3 = %d jittered hex cells per GPU, Cons variables, "
+              "HLL flux, LinearLS3D + Venktn3D, finite-difference 9x9 block Jacobian into device BSR, pseudo-steady "
+              "time term", "mhd", 960, 4536),
+}
 
 
 class ClockSampler:
@@ -182,6 +196,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cfb200")
     ap.add_argument("--n", "--edge", dest="n", type=int, default=220, help="hex box edge per GPU (220^3 = 10.6 M cells, configs[2])")
+    ap.add_argument("--workload", default="ns3d", choices=sorted(WORKLOADS), help="ns3d = configs[2] (the metric), mhd3d = configs[3]")
     ap.add_argument("--cpu-sample", type=int, default=36, help="edge of the per-thread hex box of the CPU baseline")
     ap.add_argument("--cpu-evals", type=int, default=24, help="evaluations per thread of the cpu_baseline leg (~10-20 s)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -206,12 +221,13 @@ def main():
         dist = dist_
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    q = 5
+    wl_desc, wl_pvt, a_rhs, a_jac = WORKLOADS[args.workload]
     t0 = time.perf_counter()
-    em, cfg, bcs = flagship(args.n)
+    em, cfg, bcs = flagship(args.n, args.workload)
+    q = cfg.nEqs
     fm = cl.build_mesh(em, L)
     t_mesh = time.perf_counter() - t0
-    U0 = cases.init_state(fm, q, True)[:fm.nCells*q]
+    U0 = cases.init_state(fm, q, wl_pvt)[:fm.nCells*q]
     eng = cl.Engine(cfg, local_rank, lib=L)
     t0 = time.perf_counter()
     eng.set_mesh(fm, bcs)
@@ -295,20 +311,19 @@ def main():
         # algorithmic bytes of the dominant kernel per launch (DESIGN.md "kernels"): the interior-face FD Jacobian
         # writes two q x q blocks per interior face and reads both cell states, gradients, limiters, the face flux,
         # normal, area and the 4 nodal states: see DESIGN.md for the per-face count
-        per_launch = {"innerFaceJac": fm.nInner*INNER_FACE_JAC_BYTES}
-        algo = per_launch.get(top, nc*(A_RHS + A_JAC))
+        per_launch = {"innerFaceJac": fm.nInner*INNER_FACE_JAC_BYTES} if args.workload == "ns3d" else {}
+        algo = per_launch.get(top, nc*(a_rhs + a_jac))
         achieved = algo/(kavg[top]*1e-3)/1e9
-        traffic, traffic_src = measured_traffic(top, fm.nInner if top == "innerFaceJac" else nc)
+        traffic, traffic_src = (measured_traffic(top, fm.nInner if top == "innerFaceJac" else nc)
+                                if args.workload == "ns3d" else (None, None))
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": "configs[2]: 3D Navier-Stokes, %d^3 = %d jittered hex cells per GPU, Pvt variables, Roe + "
-                                   "viscous (DiamondVolume3D) flux, LinearLS3D + Venktn3D, finite-difference block "
-                                   "Jacobian (NumJacob) into device BSR, pseudo-steady time term" % (args.n, nc),
+            "config": {"workload": wl_desc % (args.n, nc),
                        "cells_per_gpu": nc, "faces_per_gpu": int(fm.nFaces), "bsr_blocks_per_gpu": int(eng.nnzb),
                        "l2": "inputs (%.1f GB BSR + %.2f GB states/gradients) far larger than the 126 MB L2; no flush needed"
-                             % (eng.nnzb*200/1e9, nc*5*8*6/1e9),
+                             % (eng.nnzb*q*q*8/1e9, nc*q*8*6/1e9),
                        "partitioning": "one partition per GPU, no data-path collective inside ComputeRHS",
                        "mesh_build_s": round(t_mesh, 2), "device_setup_s": round(t_setup, 2)},
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e,
@@ -319,11 +334,11 @@ def main():
                          "frac": achieved/peak, "traffic": traffic, "traffic_source": traffic_src,
                          "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": int(algo), "avg_launch_ms": kavg[top]},
-            "step_roofline": {"bytes_per_cell": A_RHS + A_JAC, "achieved_gbs": (A_RHS + A_JAC)*value/world/1e9,
-                              "frac_of_hbm_peak": (A_RHS + A_JAC)*value/world/1e9/peak},
+            "step_roofline": {"bytes_per_cell": a_rhs + a_jac, "achieved_gbs": (a_rhs + a_jac)*value/world/1e9,
+                              "frac_of_hbm_peak": (a_rhs + a_jac)*value/world/1e9/peak},
             "clocks": clocks, "status": int(status),
         }
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and not args.no_cpu_baseline and args.workload == "ns3d":
             threads = os.cpu_count() or 1
             v, dt, ncs = cpu_baseline(args.cpu_sample, args.cpu_evals, threads)
             out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",

@@ -13,3 +13,5 @@ timeout 1200 ncu --set full --clock-control none --import-source on --kernel-nam
 echo "ncu full rc=$?"
 tail -3 gpurun_out/pytest_gpu.log gpurun_out/smoke.log gpurun_out/bench_n128.log
 tail -2 gpurun_out/bench_n220.log | cut -c1-1500
+timeout 600 python bench.py --workload mhd3d --n 96 --steps 5 --warmup 3 > gpurun_out/bench_mhd_n96.log 2>&1; echo "mhd rc=$?"
+tail -1 gpurun_out/bench_mhd_n96.log | cut -c1-900
