@@ -83,6 +83,39 @@ WORKLOADS = {
 }
 
 
+def slab_partition(n, rank, world, workload):
+    """N > 1: rank r owns a slab of n^3 cells of an n x n x (n*world) box cut along z and carries the two overlap
+    layers of each interior side (LSQ needs 2: LeastSquareP1Setup.cxx:60-63).  The slab is generated locally; its cells
+    are renumbered [own cells that see no overlap cell | own cells next to the overlap | overlap cells] so that the
+    gradients of the first group overlap the state halo exchange; the halo lists pair this slab's two outermost own
+    layers with the neighbour's overlap layers (same (i, j, k) order on both sides).  Returns (ElementMesh, Partition)."""
+    from coolfluid_b200 import meshgen, partition
+    lo = 2 if rank > 0 else 0
+    hi = 2 if rank < world - 1 else 0
+    K = n + lo + hi
+    em = meshgen.hex_box(n, n, K, lengths=(1.0, 1.0, K/float(n)), seed=12345 + rank)
+    nl = n*n
+    k_of = np.arange(em.n_cells)//nl
+    own = (k_of >= lo) & (k_of < lo + n)
+    near = own & (((k_of == lo) & (lo > 0)) | ((k_of == lo + n - 1) & (hi > 0)))
+    group = np.where(own & ~near, 0, np.where(near, 1, 2))
+    perm = np.argsort(group, kind="stable").astype(np.int64)        # new -> old
+    inv = np.empty_like(perm); inv[perm] = np.arange(em.n_cells)    # old -> new
+    em.cell_nodes = np.ascontiguousarray(em.cell_nodes.reshape(-1, 8)[perm].reshape(-1))
+    em.trs_face_cell = np.ascontiguousarray(inv[em.trs_face_cell]).astype(em.trs_face_cell.dtype)
+    p = partition.Partition()
+    p.rank, p.nranks, p.em = rank, world, em
+    p.updatable = (group[perm] < 2).astype(np.uint8)
+    p.n_interior = int((group == 0).sum())
+    p.n_updatable = int(own.sum())
+    layer = lambda k0: inv[np.arange(k0*nl, (k0 + 2)*nl)].astype(np.int32)
+    if lo:
+        p.send[rank - 1] = layer(lo); p.recv[rank - 1] = layer(0)
+    if hi:
+        p.send[rank + 1] = layer(lo + n - 2); p.recv[rank + 1] = layer(lo + n)
+    return em, p
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
@@ -223,9 +256,14 @@ def main():
 
     wl_desc, wl_pvt, a_rhs, a_jac = WORKLOADS[args.workload]
     t0 = time.perf_counter()
-    em, cfg, bcs = flagship(args.n, args.workload)
+    em, cfg, bcs = flagship(args.n if world == 1 else 2, args.workload)
     q = cfg.nEqs
+    part = None
+    if world > 1:
+        em, part = slab_partition(args.n, rank, world, args.workload)
     fm = cl.build_mesh(em, L)
+    if part is not None:
+        fm.updatable = np.ascontiguousarray(part.updatable)
     t_mesh = time.perf_counter() - t0
     U0 = cases.init_state(fm, q, wl_pvt)[:fm.nCells*q]
     eng = cl.Engine(cfg, local_rank, lib=L)
@@ -233,6 +271,15 @@ def main():
     eng.set_mesh(fm, bcs)
     t_setup = time.perf_counter() - t0
     nc = fm.nCells
+    n_upd = nc if part is None else part.n_updatable
+    if part is not None:
+        # NCCL communicator of the engine (cfb200_comm_init) + halo lists; the unique id travels over torch.distributed
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(cl.nccl_unique_id(L)), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        eng.comm_init(rank, world, bytes(idt.cpu().numpy().tobytes()))
+        eng.set_halo(part)
     # pinned host buffers of the reference-facing call (states in, rhs / updateCoeff out)
     hU = torch.empty(nc*q, dtype=torch.float64, pin_memory=True)
     hU.numpy()[:] = U0
@@ -244,12 +291,16 @@ def main():
 
     def step_resident():
         eng.set_update_coeff(None)           # the updater zeroes updateCoeff between evaluations (UpdateSol.cxx:192)
+        if part is not None:
+            eng.halo_begin()                 # state halo over NCCL; compute_rhs overlaps it with the interior gradients
         eng.compute_rhs(apply_bc=True, download=False)
         eng.time_rhs(download=False)
 
     def step_e2e():
         eng.set_states(hU.numpy())
         eng.set_update_coeff(None)
+        if part is not None:
+            eng.halo_begin()
         eng.compute_rhs(apply_bc=True, download=True, out_rhs=hR.numpy(), out_uc=hC.numpy())
         eng.time_rhs(download=False)
 
@@ -295,7 +346,7 @@ def main():
     clocks = sampler.stop() if rank == 0 else None
     eng.enable_timing(False)
     ms_step = ms_total/args.steps
-    total_cells = nc*world
+    total_cells = n_upd*world            # updatable cells only (overlap cells are recomputed copies)
     value = total_cells/(ms_step*1e-3)
 
     for _ in range(max(1, args.warmup//2)):
@@ -324,7 +375,10 @@ def main():
                        "cells_per_gpu": nc, "faces_per_gpu": int(fm.nFaces), "bsr_blocks_per_gpu": int(eng.nnzb),
                        "l2": "inputs (%.1f GB BSR + %.2f GB states/gradients) far larger than the 126 MB L2; no flush needed"
                              % (eng.nnzb*q*q*8/1e9, nc*q*8*6/1e9),
-                       "partitioning": "one partition per GPU, no data-path collective inside ComputeRHS",
+                       "partitioning": ("single partition" if part is None else
+                                        "slab per GPU (%d updatable + %d overlap cells on rank 0), state halo exchange over "
+                                        "NCCL every step (%d cells x %d doubles per neighbour), overlapped with the "
+                                        "interior gradients" % (n_upd, nc - n_upd, 2*args.n*args.n, q)),
                        "mesh_build_s": round(t_mesh, 2), "device_setup_s": round(t_setup, 2)},
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": int(nc*q*8*world), "d2h_bytes_per_step": int((nc*q*8 + nc*8)*world)},
