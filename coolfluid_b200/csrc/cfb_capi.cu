@@ -32,14 +32,22 @@ __global__ void __launch_bounds__(BS, MINB) k_staged(const F f, const int n) {
   const int i = blockIdx.x*BS + t;
   int s0 = -1, s1 = -1;
   if (i < n) { f.run(i, sm + t, STRIDE); f.slots(i, s0, s1); }
+  // the two destination slots of every face of the warp go to the (now free) loop-state rows of the staging area
+  sm[(F::NOUT + 0)*STRIDE + t] = __hiloint2double(0, s0);
+  sm[(F::NOUT + 1)*STRIDE + t] = __hiloint2double(0, s1);
   __syncwarp();
   double* out = f.out();
-  for (int e = lane; e < 32*F::NOUT; e += 32) {
-    const int lf = e/F::NOUT, k = e - lf*F::NOUT;
-    const int sel = k/F::BLK, kk = k - sel*F::BLK;
-    const int a0 = __shfl_sync(0xffffffffu, s0, lf), a1 = __shfl_sync(0xffffffffu, s1, lf);
-    const int slot = sel ? a1 : a0;
+  // entry e = lane + 32*it of the warp's 32 x NOUT finished values: face lf = e / NOUT, k = e % NOUT, kept incrementally
+  static_assert(F::NOUT >= 32 && F::STAGE >= F::NOUT + 2, "staging layout");
+  int k = lane, lf = 0;
+#pragma unroll 2
+  for (int it = 0; it < F::NOUT; ++it) {
+    const int sel = (k >= F::BLK) ? 1 : 0;
+    const int kk = k - sel*F::BLK;
+    const int slot = __double2loint(sm[(F::NOUT + sel)*STRIDE + warpBase + lf]);
     if (slot >= 0) out[(size_t)slot*F::BLK + kk] = sm[k*STRIDE + warpBase + lf];
+    k += 32;
+    if (k >= F::NOUT) { k -= F::NOUT; ++lf; }
   }
 }
 
