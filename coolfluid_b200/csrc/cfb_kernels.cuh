@@ -313,15 +313,18 @@ struct LimiterK {   // idx over cells
           double deltaMin;
           if (D == 2) deltaMin = ux*dxq[j][0] + uy*dxq[j][1];
           else deltaMin = ux*dxq[j][0] + uy*dxq[j][1] + uz*dxq[j][2];
-          // both candidates are formed without branching (the divisions of the six faces overlap), then selected:
-          // same values as the reference's two if-blocks (Venktn2D.cxx:226-243), psi is kept when deltaMin == 0
+          // no branches (the divisions of the six faces overlap): numerator and denominator of the candidate that
+          // applies are selected first, then divided once: same values as the reference's two if-blocks
+          // (Venktn2D.cxx:226-243); psi is kept when deltaMin == 0
           const double dPlusMax2 = deltaPlusMax*deltaPlusMax;
           const double dPlusMaxMin = deltaPlusMax*deltaMin;
-          const double psiP = ddiv(dPlusMax2 + 2.0*dPlusMaxMin + epsilon, dPlusMax2 + dPlusMaxMin + 2.0*deltaMin*deltaMin + epsilon);
+          const double numP = dPlusMax2 + 2.0*dPlusMaxMin + epsilon;
+          const double denP = dPlusMax2 + dPlusMaxMin + 2.0*deltaMin*deltaMin + epsilon;
           const double y = ddiv(deltaPlusMin, deltaMin);
-          const double psiM = ddiv(y*y + 2*y, y*y + y + 2.);
-          if (deltaMin > 0.0) psi = psiP;
-          if (deltaMin < 0.0) psi = psiM;
+          const double numM = y*y + 2*y, denM = y*y + y + 2.;
+          const bool pos = deltaMin > 0.0;
+          const double cand = ddiv(pos ? numP : numM, pos ? denP : denM);
+          if (deltaMin > 0.0 || deltaMin < 0.0) psi = cand;
           psimin = dmin(psi, psimin);
         }
       } else {
