@@ -41,7 +41,7 @@ class ConfigStruct(C.Structure):
         ("choiceA12", C.c_int32), ("hllUseAlpha", C.c_int32),
         ("ausmBeta", C.c_double), ("ausmAlpha", C.c_double),
         ("ausmKu", C.c_double), ("ausmKp", C.c_double), ("ausmSigma", C.c_double), ("machInf", C.c_double),
-        ("physicalModel", C.c_int32), ("reserved2", C.c_int32), ("refSpeed", C.c_double),
+        ("physicalModel", C.c_int32), ("entropyFixID", C.c_int32), ("refSpeed", C.c_double),
     ]
 
 
@@ -82,6 +82,7 @@ def make_config(dim, update_var=UV_CONS, flux=FS_ROE, poly_rec=PR_CONSTANT, limi
     c.physicalModel = int(kw.get("physical_model", PM_EULER))
     q = 9 if c.physicalModel == PM_MHD3D_PROJECTION else dim + 2
     c.refSpeed = kw.get("ref_speed", 1.0)
+    c.entropyFixID = int(kw.get("entropy_fix_id", 0))
     c.dim, c.nEqs = dim, q
     c.updateVar, c.fluxSplitter, c.polyRec, c.limiter, c.diffusive = update_var, flux, poly_rec, limiter, diffusive
     c.viscLaw = kw.get("visc_law", VISC_SIMPLER_SUTHERLAND)

@@ -23,15 +23,15 @@ inline bool splitterSupported(const cfb200_config& c) {
   if (c.physicalModel == CFB200_PM_MHD3D_PROJECTION)      // MHD: centred splitters, conservative variables, inviscid
     return (c.fluxSplitter == CFB200_FS_LAXFRIED || c.fluxSplitter == CFB200_FS_HLL) && c.updateVar == CFB200_UV_CONS &&
            c.diffusive == CFB200_DIFF_NONE;
-  if (c.fluxSplitter == CFB200_FS_ROE) return true;
+  if (c.fluxSplitter == CFB200_FS_ROE) return c.entropyFixID >= 0 && c.entropyFixID <= 2;
   if (c.fluxSplitter == CFB200_FS_AUSMPLUS || c.fluxSplitter == CFB200_FS_AUSMPLUSUP)
     return c.choiceA12 >= 1 && c.choiceA12 <= 3 && (c.fluxSplitter == CFB200_FS_AUSMPLUS || c.machInf > 0.);
   if (c.fluxSplitter == CFB200_FS_LAXFRIED || c.fluxSplitter == CFB200_FS_HLL) return true;
   return false;
 }
-// kernel family of the splitter: 0 Roe, 1 AUSM+ / AUSM+up, 2 Lax-Friedrichs / HLL
+// kernel family of the splitter: 0 Roe, 1 AUSM+ / AUSM+up, 2 Lax-Friedrichs / HLL, 3 Roe with the entropy fix
 inline int splitterFamily(const cfb200_config& c) {
-  if (c.fluxSplitter == CFB200_FS_ROE) return 0;
+  if (c.fluxSplitter == CFB200_FS_ROE) return (c.entropyFixID != 0) ? 3 : 0;
   return (c.fluxSplitter == CFB200_FS_LAXFRIED || c.fluxSplitter == CFB200_FS_HLL) ? 2 : 1;
 }
 
@@ -291,12 +291,14 @@ public:
       if (doJac) {
         if (fam == 0) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 0>{d, cfg}, d.nInner, faceShape);
         else if (fam == 1) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 1>{d, cfg}, d.nInner, faceShape);
-        else bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 2>{d, cfg}, d.nInner, faceShape);
+        else if (fam == 2) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 2>{d, cfg}, d.nInner, faceShape);
+        else bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 3>{d, cfg}, d.nInner, faceShape);
         bk.launch("boundaryFaceJac", BoundaryFaceK<D, true>{d, cfg}, d.nGhosts, 128);
       } else {
         if (fam == 0) bk.launch("innerFace", InnerFaceK<D, false, 0>{d, cfg}, d.nInner, 128);
         else if (fam == 1) bk.launch("innerFace", InnerFaceK<D, false, 1>{d, cfg}, d.nInner, 128);
-        else bk.launch("innerFace", InnerFaceK<D, false, 2>{d, cfg}, d.nInner, 128);
+        else if (fam == 2) bk.launch("innerFace", InnerFaceK<D, false, 2>{d, cfg}, d.nInner, 128);
+        else bk.launch("innerFace", InnerFaceK<D, false, 3>{d, cfg}, d.nInner, 128);
         bk.launch("boundaryFace", BoundaryFaceK<D, false>{d, cfg}, d.nGhosts, 128);
       }
     }

@@ -302,7 +302,7 @@ struct FaceWork {
   // it/q (FVMCC_ComputeRhsJacob.cxx:126-236,321-365; frozen gradient/limiter, LeastSquareP1PolyRec2D.cxx:221-262):
   //   pf = F_c*area - staged F_d ;  column <- sgn * resFactor * (pf - flux)/eps  (row-major q x q, BlockAccumulator.hh:289-296)
   // FS = 0: Roe (fixed side parked as s | z | f);  FS = 1: AUSM family (fixed side parked as rho p H a v[3]);
-  // FS = 2: Lax-Friedrichs / HLL (fixed side parked as f | s | un a)
+  // FS = 2: Lax-Friedrichs / HLL (fixed side parked as f | s | un a);  FS = 3: Roe with the entropy fix (s | z | f | un a)
   template <int FS>
   CFB_HD void innerConvective(const Dev& d, const Cfg& c, const double* sL, const double* sR, const double* vL,
                               const double* vR, bool hasDiff, const double* dfluxBase, bool jac,
@@ -310,10 +310,11 @@ struct FaceWork {
     const double rf = c.resFactor;
     // loop-carried state parked in the staging area (shared memory) instead of registers: the unperturbed other side
     // (s z f) and the base flux; without a staging area (RHS-only kernel: one evaluation) they live in locals
-    double local[4*Q];
+    constexpr int NFX = (FS == 3) ? 3*Q + 2 : 3*Q;       // doubles of the parked fixed side
+    double local[NFX + Q];
     double* fx = jac ? stg + (size_t)2*Q*Q*stride : local;
     const int fs = jac ? stride : 1;
-    double* fluxS = fx + (size_t)3*Q*fs;
+    double* fluxS = fx + (size_t)NFX*fs;
     const int last = jac ? 2*Q : 0;
 #pragma unroll 1
     for (int it = -1; it < last; ++it) {
@@ -323,11 +324,12 @@ struct FaceWork {
         double vF[Q];
 #pragma unroll
         for (int v = 0; v < Q; ++v) vF[v] = side ? vL[v] : vR[v];
-        if constexpr (FS == 0) {
+        if constexpr (FS == 0 || FS == 3) {
           typename P::SideLite fixed;
           P::sideLite(c, vF, n, fixed);              // the unperturbed other side
 #pragma unroll
           for (int v = 0; v < Q; ++v) { fx[(size_t)v*fs] = fixed.s[v]; fx[(size_t)(Q + v)*fs] = fixed.z[v]; fx[(size_t)(2*Q + v)*fs] = fixed.f[v]; }
+          if constexpr (FS == 3) { fx[(size_t)(3*Q)*fs] = fixed.un; fx[(size_t)(3*Q + 1)*fs] = fixed.A; }
         } else if constexpr (FS == 2) {
           typename P::CSide fixed;
           P::cside(c, vF, n, fixed);
@@ -355,10 +357,10 @@ struct FaceWork {
 #pragma unroll
       for (int v = 0; v < Q; ++v) { const double base = side ? vR[v] : vL[v]; vp[v] = (v == iVar) ? pvr : base; }
       double pf[Q];
-      if constexpr (FS == 0) {
+      if constexpr (FS == 0 || FS == 3) {
         typename P::SideLite pert;
         P::sideLite(c, vp, n, pert);
-        if (!P::roeOriented(c, pert, fx, fs, side == 0, n, pf)) {
+        if (!P::template roeOriented<FS == 3>(c, pert, fx, fs, side == 0, n, pf)) {
           *d.status = CFB200_ERR_BAD_VALUE;
 #pragma unroll
           for (int v = 0; v < Q; ++v) pf[v] = 0.;
@@ -493,7 +495,7 @@ struct InnerFaceK {   // idx over interior faces; FS = 0 Roe, 1 AUSM+ / AUSM+up,
   static constexpr int Q = D + 2;
   static constexpr int BLK = Q*Q;
   static constexpr int NOUT = 2*Q*Q;    // per-thread staging (shared memory, entry k at stg[k*stride]): block(R,L) | block(L,R)
-  static constexpr int STAGE = NOUT + 4*Q;   // ... | fixed side s z f | base flux (loop-carried state of the FD loop)
+  static constexpr int STAGE = NOUT + 4*Q + ((FS == 3) ? 2 : 0);   // ... | fixed side s z f (un a) | base flux (loop-carried state of the FD loop)
   Dev d; Cfg c;
   CFB_HD void operator()(int f) const { run(f, nullptr, 0); }
   CFB_HD double* out() const { return d.bsrVal; }

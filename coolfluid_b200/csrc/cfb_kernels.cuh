@@ -410,8 +410,8 @@ struct DivBGather {   // idx over cells
 //   inner face, c == L:  -block(R,c)      inner face, c == R:  -block(L,c)      boundary face: +bnd block
 // Rows of non-updatable cells are staging only and are zeroed by ZeroRows afterwards.
 template <int D, class PH = Phys<D> >
-struct DiagGather {   // idx over nCells*GS (one group of GS threads per cell, Q*Q of them active: 32 | 96 for q = 9)
-  static constexpr int GS = (PH::Q*PH::Q <= 32) ? 32 : 96;
+struct DiagGather {   // idx over nCells*GS: one thread per (cell, block entry), no idle lanes
+  static constexpr int GS = PH::Q*PH::Q;
   Dev d;
   CFB_HD void operator()(int idx) const {
     constexpr int Q = PH::Q;
@@ -445,7 +445,7 @@ struct DiagGather {   // idx over nCells*GS (one group of GS threads per cell, Q
 
 template <int D, class PH = Phys<D> >
 struct ZeroRows {   // idx over (non-updatable cell list) * GS
-  static constexpr int GS = (PH::Q*PH::Q <= 32) ? 32 : 96;
+  static constexpr int GS = PH::Q*PH::Q;
   Dev d; const int* cells;
   CFB_HD void operator()(int idx) const {
     constexpr int Q = PH::Q;

@@ -102,7 +102,8 @@ typedef struct cfb200_config {
   double ausmKu, ausmKp, ausmSigma, machInf;
   /* physical model: CFB200_PM_EULER (Euler / Navier-Stokes, nEqs = dim + 2) or CFB200_PM_MHD3D_PROJECTION
    * (plugins/MHD/MHD3DProjectionCons.cxx, dim 3, nEqs 9: rho, rho u, rho v, rho w, Bx, By, Bz, rho E, phi) */
-  int32_t physicalModel, reserved2;
+  int32_t physicalModel;
+  int32_t entropyFixID;     /* 0: "Roe" (RoeFlux.cxx); 1 | 2: "RoeEntropyFix" entropyFixID (RoeEntropyFixFlux.cxx:35,57-90) */
   double refSpeed;          /* MHD3DProjection.ConvTerm.refSpeed */
 } cfb200_config;
 

@@ -311,6 +311,24 @@ struct Phys {
     double Rm[Q*Q], Lm[Q*Q], ev[Q], aev[Q];
     eigen(c, lin, n, Rm, Lm, ev);
     for (int i = 0; i < Q; ++i) aev[i] = std::abs(ev[i]);     // RoeFlux.cxx:200-203
+    if (c.entropyFixID != 0) {
+      // RoeEntropyFixFlux::setAbsEigenValues (RoeEntropyFixFlux.cxx:57-90) + computeLambdaCorr (RoeEntropyFixFlux.hh:49-56)
+      double evL[Q], evR[Q];
+      eigenValues(pL, n, evL);
+      eigenValues(pR, n, evR);
+      double lambdaCorr = 0.0;
+      for (int i = 0; i < Q; ++i) lambdaCorr = std::max(lambdaCorr, std::abs(evR[i] - evL[i]));
+      lambdaCorr *= 0.5;
+      if (c.entropyFixID == 1) {
+        for (int i = 0; i < Q; ++i) aev[i] = std::max(std::abs(ev[i]), lambdaCorr);
+      } else if (c.entropyFixID == 2) {
+        const double twoLambdaCorr = 2.0*lambdaCorr;
+        for (int i = 0; i < Q; ++i) {
+          const double absLambda = std::abs(ev[i]);
+          aev[i] = (!(std::abs(ev[i]) < twoLambdaCorr)) ? absLambda : (absLambda*absLambda/(4.0*lambdaCorr) + lambdaCorr);
+        }
+      }
+    }
     double sumFlux[Q], f2[Q];
     convFlux(pL, n, sumFlux);
     convFlux(pR, n, f2);

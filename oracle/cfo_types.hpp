@@ -96,7 +96,7 @@ struct Config {
   double ausmKu, ausmKp, ausmSigma, machInf;  // AUSM+up : 0.75, 0.25, 1.0, (required > 0)
   // physical model: 0 = Euler / Navier-Stokes (nEqs = dim + 2), 1 = MHD3DProjection (dim 3, nEqs 9, Cons variables)
   int32_t physicalModel;
-  int32_t reserved2;
+  int32_t entropyFixID;   // RoeEntropyFixFlux.cxx:35 (0 = plain RoeFlux, 1 | 2 = "RoeEntropyFix")
   double refSpeed;        // MHDProjectionTerm refSpeed (hyperbolic divergence cleaning speed)
 };
 

@@ -154,6 +154,11 @@ CASES = {
     "euler3d_ausmplusup_a3": (lambda: meshgen.tet_box(3, 3, 3),
                               lambda: B.make_config(3, flux=B.FS_AUSMPLUSUP, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN,
                                                     jacobian=True, mach_inf=0.8, choice_a12=3), bcs_euler3d, False),
+    # "RoeEntropyFix" (RoeEntropyFixFlux.cxx), both correction types
+    "euler2d_roe_efix1": (lambda: meshgen.quad_channel(12, 9, triangles=True),
+                          lambda: B.make_config(2, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, jacobian=True,
+                                                entropy_fix_id=1), bcs_euler2d, False),
+    "ns3d_hex_roe_efix2": (lambda: meshgen.hex_box(5, 4, 4), lambda: ns3d_cfg(entropy_fix_id=2), bcs_ns3d, True),
     # a13 (Euler part): Lax-Friedrichs and HLL
     "euler2d_laxfried_1st": (lambda: meshgen.quad_channel(12, 9),
                              lambda: B.make_config(2, flux=B.FS_LAXFRIED, jacobian=True), bcs_euler2d, False),
