@@ -41,7 +41,7 @@ class ConfigStruct(C.Structure):
         ("choiceA12", C.c_int32), ("hllUseAlpha", C.c_int32),
         ("ausmBeta", C.c_double), ("ausmAlpha", C.c_double),
         ("ausmKu", C.c_double), ("ausmKp", C.c_double), ("ausmSigma", C.c_double), ("machInf", C.c_double),
-        ("physicalModel", C.c_int32), ("entropyFixID", C.c_int32), ("refSpeed", C.c_double),
+        ("physicalModel", C.c_int32), ("entropyFixID", C.c_int32), ("refSpeed", C.c_double), ("coeffSigmoid", C.c_double),
     ]
 
 
@@ -86,7 +86,8 @@ def make_config(dim, update_var=UV_CONS, flux=FS_ROE, poly_rec=PR_CONSTANT, limi
     c.dim, c.nEqs = dim, q
     c.updateVar, c.fluxSplitter, c.polyRec, c.limiter, c.diffusive = update_var, flux, poly_rec, limiter, diffusive
     c.viscLaw = kw.get("visc_law", VISC_SIMPLER_SUTHERLAND)
-    c.computeJacobian = 1 if jacobian else 0
+    c.computeJacobian = (2 if jacobian == "analytic" else 1) if jacobian else 0
+    c.coeffSigmoid = kw.get("coeff_sigmoid", 1e-8)
     c.useFullStencil = 1 if use_full_stencil else 0
     c.freezeLimiter = int(kw.get("freeze_limiter", 0))
     c.stopLimiting = int(kw.get("stop_limiting", 0))

@@ -73,7 +73,8 @@ typedef struct cfb200_config {
   int32_t dim;              /* 2 | 3 */
   int32_t nEqs;             /* dim + 2 */
   int32_t updateVar, fluxSplitter, polyRec, limiter, diffusive, viscLaw;
-  int32_t computeJacobian;  /* doComputeJacobian() */
+  int32_t computeJacobian;  /* 0: ComputeRHS only; 1: doComputeJacobian() with "NumJacob" (finite differences); 2: "NumJacobAnalytic"
+                             * (FVMCC_ComputeRhsJacobAnalytic.cxx: analytic AUSM+up convective blocks on interior faces, Cons) */
   int32_t useFullStencil;   /* Venktn2D.cxx:60 */
   int32_t freezeLimiter;    /* PolyReconstructor.ci:66 */
   int32_t stopLimiting;     /* FVMCC_PolyRec.cxx:52 */
@@ -105,6 +106,7 @@ typedef struct cfb200_config {
   int32_t physicalModel;
   int32_t entropyFixID;     /* 0: "Roe" (RoeFlux.cxx); 1 | 2: "RoeEntropyFix" entropyFixID (RoeEntropyFixFlux.cxx:35,57-90) */
   double refSpeed;          /* MHD3DProjection.ConvTerm.refSpeed */
+  double coeffSigmoid;      /* AUSMFlux.ci:64 coeffSigmoid (default 1e-8), analytic Jacobian only */
 } cfb200_config;
 
 /* Flat mesh data = the contents of the reference's sockets and connectivity tables (SURVEY.md §8b "Data ownership").

@@ -72,6 +72,8 @@ int cfo_compute(const Config* c, const MeshView* m, const BC* bcs, double* U, Cf
           c->diffusive != DIFF_NONE) { co->status = 2; return 2; }
       Solver<3, MhdPhys> s(*c, *m, bcs); s.execute(U, o);
     }
+    else if (c->computeJacobian == 2 && !(c->fluxSplitter == FS_AUSMPLUSUP && c->updateVar == UV_CONS &&
+                                          c->diffusive == DIFF_NONE)) { co->status = 2; return 2; }
     else if (c->dim == 2) { Solver<2> s(*c, *m, bcs); s.execute(U, o); }
     else { Solver<3> s(*c, *m, bcs); s.execute(U, o); }
   } catch (const std::exception&) { co->status = 2; return 2; }
@@ -87,6 +89,22 @@ int cfo_time_rhs(const Config* c, const MeshView* m, const BC* bcs, double* U, c
     else if (c->dim == 2) Solver<2>(*c, *m, bcs).pseudoSteadyTimeRhs(U, pastU, o);
     else Solver<3>(*c, *m, bcs).pseudoSteadyTimeRhs(U, pastU, o);
   } catch (const std::exception&) { return 2; }
+  return 0;
+}
+
+// Test hook: analytic AUSM+up flux Jacobian (Cons) of one face from the two CONSERVATIVE face states.
+int cfo_ausm_jacob_cons(const Config* c, const double* uL, const double* uR, const double* n, int side, double* J) {
+  if (c->dim == 2) { Phys<2>::Data a, b; Phys<2>::computePhysicalData(*c, uL, a); Phys<2>::computePhysicalData(*c, uR, b);
+                     Phys<2>::ausmPlusUpJacobCons(*c, a, b, n, side, J); }
+  else { Phys<3>::Data a, b; Phys<3>::computePhysicalData(*c, uL, a); Phys<3>::computePhysicalData(*c, uR, b);
+         Phys<3>::ausmPlusUpJacobCons(*c, a, b, n, side, J); }
+  return 0;
+}
+int cfo_ausm_flux(const Config* c, const double* uL, const double* uR, const double* n, double* F) {
+  if (c->dim == 2) { Phys<2>::Data a, b; Phys<2>::computePhysicalData(*c, uL, a); Phys<2>::computePhysicalData(*c, uR, b);
+                     Phys<2>::ausmFlux(*c, a, b, n, F); }
+  else { Phys<3>::Data a, b; Phys<3>::computePhysicalData(*c, uL, a); Phys<3>::computePhysicalData(*c, uR, b);
+         Phys<3>::ausmFlux(*c, a, b, n, F); }
   return 0;
 }
 

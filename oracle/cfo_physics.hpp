@@ -420,6 +420,205 @@ struct Phys {
     return true;
   }
 
+  // ---- a19: analytic Jacobian of the AUSM+up flux in conservative variables ----------------------------
+  // MathFunctions.hh:58-61
+  static double sigmoidF(double x, double y, double K) { return 0.5*(1.0 - (1.0 + K)*(x - y)/(-std::abs(x - y) - K)); }
+
+  // AUSMPlusUpFlux<UPDATEVAR>::ComputedFluxdCons (AUSMPlusUpFlux.ci:675-1203) with
+  // AUSMFlux::computeSoundSpeedForJacobian (AUSMFlux.ci:795-822).  side 0 = LEFT, 1 = RIGHT;
+  // J is row-major Q x Q: J[i*Q + j] = d F_i / d U_j (per unit area).  The columns follow the reference one by
+  // one, including the terms it leaves out where a derivative vanishes and its row-(w, rho w) quirk.
+  static void ausmPlusUpJacobCons(const Config& c, const PData& L, const PData& R, const double* n, int side, double* J) {
+    const bool LEFT = (side == 0);
+    const double rhoL = L.rho, rhoR = R.rho, HL = L.H, HR = R.H, EL = L.E, ER = R.E;
+    const double gammaL = c.gamma, gammaR = c.gamma, pL = L.p, pR = R.p;
+    const double UL = L.v[0], UR = R.v[0], VL = L.v[1], VR = R.v[1], WL = L.v[2], WR = R.v[2];
+    const double beta = c.ausmBeta, Ksig = c.coeffSigmoid, sigma = c.ausmSigma;
+    double qnL = 0.0, qnR = 0.0;
+    for (int i = 0; i < D; ++i) { qnL += L.v[i]*n[i]; qnR += R.v[i]*n[i]; }
+    // computeSoundSpeedForJacobian
+    const double aCritL = std::sqrt(2.0*(gammaL - 1.0)/(gammaL + 1.0)*HL);
+    const double aCritR = std::sqrt(2.0*(gammaR - 1.0)/(gammaR + 1.0)*HR);
+    const double aCritLsig = sigmoidF(aCritL, qnL, Ksig);
+    const double OneaCritLsig = (1.0 - aCritLsig);
+    const double aCritRsig = sigmoidF(aCritR, -qnR, Ksig);
+    const double OneaCritRsig = -(1.0 - aCritRsig);
+    const double asigL = aCritLsig*aCritL + (1.0 - aCritLsig)*qnL;
+    const double asigR = aCritRsig*aCritR - (1.0 - aCritRsig)*qnR;
+    const double ahatL = aCritL*aCritL/std::max(aCritL, qnL);
+    const double ahatR = aCritR*aCritR/std::max(aCritR, -qnR);
+    const double a12 = (1.0 - sigmoidF(ahatL, ahatR, Ksig))*aCritL*aCritL/asigL + sigmoidF(ahatL, ahatR, Ksig)*aCritR*aCritR/asigR;
+
+    const double rho12 = 0.5*(rhoL + rhoR);
+    const double ML = qnL/a12, MR = qnR/a12;
+    const double mInf = c.machInf;
+    const double MBarSq = 0.5*(ML*ML + MR*MR);
+    const double MinfSq = mInf*mInf;
+    const double sigMbarsqMinfsq = sigmoidF(MBarSq, MinfSq, Ksig);
+    const double sig2 = sigMbarsqMinfsq*MBarSq + (1.0 - sigMbarsqMinfsq)*MinfSq;
+    const double MZeroSig = sigmoidF(1.0, sig2, Ksig);
+    const double mZero = std::sqrt((1 - MZeroSig)*1.0 + MZeroSig*sig2);
+    const double fa = mZero*(2.0 - mZero);
+    const double sigmaMBarSq = 1.0 - sigma*MBarSq;
+    const double mPSig = sigmoidF(sigmaMBarSq, 0.0, Ksig);
+    const double dMpCon = -(c.ausmKp)*mPSig;
+    const double M4Plus = (std::abs(ML) >= 1.0) ? mach1Plus(ML) : mach2Plus(ML)*(1.0 - 16.*beta*mach2Min(ML));
+    const double M4Minus = (std::abs(MR) >= 1.0) ? mach1Min(MR) : mach2Min(MR)*(1.0 + 16.*beta*mach2Plus(MR));
+    const double mP = -(c.ausmKp)*mPSig*(pR - pL)/(rho12*a12*a12);
+    const double M12 = M4Plus + M4Minus + mP;
+    const double sigrho = sigmoidF(M12, 0.0, Ksig);
+    const double Onesigrho = (1.0 - sigrho);
+    const double rhostar = sigrho*rhoL + Onesigrho*rhoR;
+    const double mdot12 = M12*a12*rhostar;
+    const double sigm = sigmoidF(mdot12, 0.0, Ksig);
+    const double Onesigm = (1.0 - sigm);
+    const double alpha = (3.0/16.0)*(-4.0 + 5.0*fa*fa);
+    const double P5Plus = (std::abs(ML) >= 1.0) ? mach1Plus(ML)/ML : mach2Plus(ML)*((2.0 - ML) - 16.*alpha*ML*mach2Min(ML));
+    const double P5Minus = (std::abs(MR) >= 1.0) ? mach1Min(MR)/MR : mach2Min(MR)*((-2.0 - MR) + 16.*alpha*MR*mach2Plus(MR));
+    // global constants
+    const double rhoa2 = rho12*a12*a12;
+    const double prho2a2 = (pR - pL)/(rho12*rho12*a12*a12);
+    const double prhoa3 = -2.0*(pR - pL)/(rho12*a12*a12*a12);
+    const double daCritLconst = std::sqrt((gammaL - 1.0)/(2.0*(gammaL + 1.0)*HL));
+    const double daCritRconst = std::sqrt((gammaR - 1.0)/(2.0*(gammaR + 1.0)*HR));
+    const double dahatCon1L = 2.0*aCritL/asigL, dahatCon1R = 2.0*aCritR/asigR;
+    const double dahatCon2L = -aCritL*aCritL/(asigL*asigL), dahatCon2R = -aCritR*aCritR/(asigR*asigR);
+    const double dahatSig = sigmoidF(ahatL, ahatR, Ksig);
+    const double OnedahatSig = (1.0 - dahatSig);
+    const double dMCon = 1.0/a12;
+    const double dMConL = -qnL/(a12*a12), dMConR = -qnR/(a12*a12);
+    const double dmZeroCon = 0.5/mZero*sigMbarsqMinfsq*MZeroSig;
+    const double dfaCon = 2.0*(1.0 - mZero);
+    const double dM4Lsign = (ML < 0.0) ? -1.0 : 1.0, dM4Rsign = (MR < 0.0) ? -1.0 : 1.0;
+    const double OnedM4Lsign = 0.5*(1. + dM4Lsign), OnedM4Rsign = 0.5*(1. - dM4Rsign);
+    const double dM4Lsuper = (0.5*(ML + 1.) + 4.*beta*ML*(ML*ML - 1.));
+    const double dM4Rsuper = -(0.5*(MR - 1.) + 4.*beta*MR*(MR*MR - 1.));
+    const double a12rhostar = a12*rhostar, M12a12 = M12*a12, M12rhostar = M12*rhostar;
+    const double dalphaCon = 15.0/8.0*fa;
+    const double dP5Lconst1 = 0.5*(10.0*alpha*ML*ML*ML*ML - (1.5 + 12.0*alpha)*ML*ML + 1.5 + 2.0*alpha);
+    const double dP5Rconst1 = -0.5*(10.0*alpha*MR*MR*MR*MR - (1.5 + 12.0*alpha)*MR*MR + 1.5 + 2.0*alpha);
+    const double dP5Lconst2 = ML*(ML*ML - 1)*(ML*ML - 1);
+    const double dP5Rconst2 = -MR*(MR*MR - 1)*(MR*MR - 1);
+    const double pudP5Plus = P5Minus*rho12*fa*a12*(qnR - qnL);
+    const double pudP5Minus = P5Plus*rho12*fa*a12*(qnR - qnL);
+    const double pudrho12 = P5Plus*P5Minus*fa*a12*(qnR - qnL);
+    const double pudfa = P5Plus*P5Minus*rho12*a12*(qnR - qnL);
+    const double puda12 = P5Plus*P5Minus*rho12*fa*(qnR - qnL);
+    const double pudqn = P5Plus*P5Minus*rho12*fa;
+    const double dpuCon = 0.5*c.ausmKu;
+    const double Usig = sigm*UL + Onesigm*UR, Vsig = sigm*VL + Onesigm*VR, Wsig = sigm*WL + Onesigm*WR;
+    const double Hsig = sigm*HL + Onesigm*HR;
+    const bool supL = std::abs(ML) >= 1.0, supR = std::abs(MR) >= 1.0;
+    for (int k = 0; k < Q*Q; ++k) J[k] = 0.;
+
+    // One column: the chain shared by all of them; `kind` says which optional terms the reference writes.
+    //   kind 0: rho (drho12, drhostar, qn in asig and pu)   1: momentum (qn in asig and pu)   2: rhoE (no qn terms)
+    struct Col { double dmdot, dp12; };
+    auto column = [&](int kind, double dqnL, double dqnR, double dhL, double dhR, double dpL, double dpR,
+                      double drhoLd, double drhoRd) -> Col {
+      const double daCritLd = daCritLconst*dhL, daCritRd = daCritRconst*dhR;
+      const double dasigLd = (kind == 2) ? aCritLsig*daCritLd : aCritLsig*daCritLd + OneaCritLsig*dqnL;
+      const double dasigRd = (kind == 2) ? aCritRsig*daCritRd : aCritRsig*daCritRd + OneaCritRsig*dqnR;
+      const double dahatLd = (dahatCon1L*daCritLd + dahatCon2L*dasigLd);
+      const double dahatRd = (dahatCon1R*daCritRd + dahatCon2R*dasigRd);
+      const double da12d = OnedahatSig*dahatLd + dahatSig*dahatRd;
+      const double dMLd = (kind == 2) ? dMConL*da12d : dMCon*dqnL + dMConL*da12d;
+      const double dMRd = (kind == 2) ? dMConR*da12d : dMCon*dqnR + dMConR*da12d;
+      const double dMBarSqd = ML*dMLd + MR*dMRd;
+      const double dmZerod = dmZeroCon*dMBarSqd;
+      const double dfad = dfaCon*dmZerod;
+      const double dM4Plusd = supL ? OnedM4Lsign*dMLd : dM4Lsuper*dMLd;
+      const double dM4Minusd = supR ? OnedM4Rsign*dMRd : dM4Rsuper*dMRd;
+      const double dMpddp = (dpR - dpL)/rhoa2;
+      const double dMpdda = prhoa3*da12d;
+      double dMpd, dmdotd;
+      const double drho12d = 0.5*(drhoLd + drhoRd);
+      if (kind == 0) {
+        const double dMpddrho = prho2a2*drho12d;
+        dMpd = dMpCon*(dMpddp + dMpddrho + dMpdda);
+      } else dMpd = dMpCon*(dMpddp + dMpdda);
+      const double dM12d = dM4Plusd + dM4Minusd + dMpd;
+      if (kind == 0) {
+        const double drhostard = sigrho*drhoLd + Onesigrho*drhoRd;
+        dmdotd = dM12d*a12rhostar + M12rhostar*da12d + M12a12*drhostard;
+      } else dmdotd = dM12d*a12rhostar + M12rhostar*da12d;
+      const double dalphad = dalphaCon*dfad;
+      const double dP5Plusd = supL ? 0. : dP5Lconst1*dMLd + dP5Lconst2*dalphad;
+      const double dP5Minusd = supR ? 0. : dP5Rconst1*dMRd + dP5Rconst2*dalphad;
+      const double t1 = pudP5Plus*dP5Plusd, t2 = pudP5Minus*dP5Minusd, tfa = pudfa*dfad, tda = puda12*da12d;
+      double dpud;
+      if (kind == 0) {
+        const double trho = pudrho12*drho12d;
+        const double tqn = pudqn*da12d*(dqnR - dqnL);
+        dpud = dpuCon*(t1 + t2 + trho + tfa + tda + tqn);
+      } else if (kind == 1) {
+        const double tqn = pudqn*da12d*(dqnR - dqnL);
+        dpud = dpuCon*(t1 + t2 + tfa + tda + tqn);
+      } else dpud = dpuCon*(t1 + t2 + tfa + tda);
+      Col o;
+      o.dmdot = dmdotd;
+      o.dp12 = dP5Plusd*pL + P5Plus*dpL + dP5Minusd*pR + P5Minus*dpR + dpud;
+      return o;
+    };
+
+    // dFdrho
+    {
+      const double dqnLd = LEFT ? -qnL/rhoL : 0., dqnRd = LEFT ? 0. : -qnR/rhoR;
+      double VLsq, VRsq;
+      if (D == 3) { VLsq = UL*UL + VL*VL + WL*WL; VRsq = UR*UR + VR*VR + WR*WR; }
+      else { VLsq = UL*UL + VL*VL; VRsq = UR*UR + VR*VR; }
+      const double dhL = LEFT ? -gammaL*EL/rhoL + (gammaL - 1.)*VLsq/rhoL : 0.;
+      const double dhR = LEFT ? 0. : -gammaR*ER/rhoR + (gammaR - 1.)*VRsq/rhoR;
+      const double dpL = LEFT ? 0.5*(gammaL - 1.)*VLsq : 0., dpR = LEFT ? 0. : 0.5*(gammaR - 1.)*VRsq;
+      const double duL = LEFT ? -UL/rhoL : 0., duR = LEFT ? 0. : -UR/rhoR;
+      const double dvL = LEFT ? -VL/rhoL : 0., dvR = LEFT ? 0. : -VR/rhoR;
+      double dwL = 0., dwR = 0.;
+      if (D == 3) { dwL = LEFT ? -WL/rhoL : 0.; dwR = LEFT ? 0. : -WR/rhoR; }
+      const Col k = column(0, dqnLd, dqnRd, dhL, dhR, dpL, dpR, LEFT ? 1. : 0., LEFT ? 0. : 1.);
+      J[0*Q + 0] = k.dmdot;
+      J[1*Q + 0] = k.dmdot*Usig + mdot12*(sigm*duL + Onesigm*duR) + k.dp12*n[0];
+      J[2*Q + 0] = k.dmdot*Vsig + mdot12*(sigm*dvL + Onesigm*dvR) + k.dp12*n[1];
+      if (D == 3) J[3*Q + 0] = k.dmdot*Wsig + mdot12*(sigm*dwL + Onesigm*dwR) + k.dp12*n[2];
+      J[(Q-1)*Q + 0] = k.dmdot*Hsig + mdot12*(sigm*dhL + Onesigm*dhR);
+    }
+    // dFdrhoU, dFdrhoV, dFdrhoW
+    double dmdotV = 0.;
+    for (int m = 0; m < D; ++m) {
+      const double vLm = L.v[m], vRm = R.v[m];
+      const double dqnLd = LEFT ? n[m]/rhoL : 0., dqnRd = LEFT ? 0. : n[m]/rhoR;
+      const double dhL = LEFT ? -(gammaL - 1.)*vLm/rhoL : 0., dhR = LEFT ? 0 : -(gammaR - 1.)*vRm/rhoR;
+      const double dpL = LEFT ? -(gammaL - 1.)*vLm : 0., dpR = LEFT ? 0. : -(gammaR - 1.)*vRm;
+      const double dvelL = LEFT ? 1/rhoL : 0., dvelR = LEFT ? 0. : 1/rhoR;
+      const Col k = column(1, dqnLd, dqnRd, dhL, dhR, dpL, dpR, 0., 0.);
+      if (m == 1) dmdotV = k.dmdot;
+      const int col = 1 + m;
+      const double vs[3] = {Usig, Vsig, Wsig};
+      J[0*Q + col] = k.dmdot;
+      for (int r = 0; r < D; ++r) {
+        if (r == m) {
+          // the reference's (3,3) entry multiplies Wsigmoid by the rho V column's dmdot12 (AUSMPlusUpFlux.ci:1141)
+          const double dm = (m == 2) ? dmdotV : k.dmdot;
+          J[(1+r)*Q + col] = dm*vs[r] + mdot12*(sigm*dvelL + Onesigm*dvelR) + k.dp12*n[r];
+        } else {
+          J[(1+r)*Q + col] = k.dmdot*vs[r] + k.dp12*n[r];
+        }
+      }
+      J[(Q-1)*Q + col] = k.dmdot*Hsig + mdot12*(sigm*dhL + Onesigm*dhR);
+    }
+    // dFdrhoE
+    {
+      const double dhL = LEFT ? gammaL/rhoL : 0., dhR = LEFT ? 0. : gammaR/rhoR;
+      const double dpL = LEFT ? gammaL - 1. : 0., dpR = LEFT ? 0. : gammaR - 1.;
+      const Col k = column(2, 0., 0., dhL, dhR, dpL, dpR, 0., 0.);
+      const int col = Q - 1;
+      J[0*Q + col] = k.dmdot;
+      J[1*Q + col] = k.dmdot*Usig + k.dp12*n[0];
+      J[2*Q + col] = k.dmdot*Vsig + k.dp12*n[1];
+      if (D == 3) J[3*Q + col] = k.dmdot*Wsig + k.dp12*n[2];
+      J[(Q-1)*Q + col] = k.dmdot*Hsig + mdot12*(sigm*dhL + Onesigm*dhR);
+    }
+  }
+
   // ---- Lax-Friedrichs and HLL (a13), Euler variable sets ---------------------
   // Euler2DVarSet.cxx:47-66 / Euler3DVarSet.cxx:64-84 computeEigenValues
   static void eigenValues(const PData& d, const double* n, double* ev) {
@@ -710,6 +909,7 @@ struct MhdPhys {
   // not available for this model (the configuration is rejected before the solver runs)
   static bool roeFlux(const Config&, const double*, const double*, const MhdData&, const MhdData&, const double*, double*) { return false; }
   static bool ausmFlux(const Config&, const MhdData&, const MhdData&, const double*, double*) { return false; }
+  static void ausmPlusUpJacobCons(const Config&, const MhdData&, const MhdData&, const double*, int, double*) {}
   static double dynViscosity(const Config&, const double*) { return 0.; }
   static double thermConductivity(const Config&, double) { return 0.; }
   static double nsDensity(const Config&, const double*) { return 1.; }

@@ -579,6 +579,33 @@ public:
       }
       if (!doJac) continue;
       freezeCoeff = cfg.freezeDiffCoeff != 0;
+      if (!x.isB && cfg.computeJacobian == 2) {
+        // a19: FVMCC_ComputeRhsJacobAnalytic.cxx:68-246 (non axisymmetric, no diffusive term, no source term) with the
+        // flux Jacobians integrated over the face by FVMCC_FluxSplitter::integrateFluxAndJacob (FVMCC_FluxSplitter.hh:88-96)
+        double JL[Q*Q], JR[Q*Q], colv[Q];
+        P::ausmPlusUpJacobCons(cfg, x.pL, x.pR, x.n, 0, JL);
+        P::ausmPlusUpJacobCons(cfg, x.pL, x.pR, x.n, 1, JR);
+        for (int k = 0; k < Q*Q; ++k) { JL[k] *= x.area; JR[k] *= x.area; }
+        auto addBlock = [&](int rowCell, int colCell, const double* Jm) {
+          for (int j = 0; j < Q; ++j) {
+            for (int i = 0; i < Q; ++i) colv[i] = Jm[i*Q + j];
+            addColumn(o, rowCell, colCell, j, colv);
+          }
+        };
+        if (upL && upR) {                       // noaxiBothJacobTerms
+          for (int k = 0; k < Q*Q; ++k) { JL[k] *= cfg.resFactor; JR[k] *= cfg.resFactor; }
+          addBlock(x.L, x.L, JL); addBlock(x.L, x.R, JR);
+          for (int k = 0; k < Q*Q; ++k) { JL[k] *= -1.; JR[k] *= -1.; }
+          addBlock(x.R, x.L, JL); addBlock(x.R, x.R, JR);
+        } else {                                // computeJacobTerm(idx) -> noaxiJacobTerm
+          const int idx = upL ? 0 : 1;
+          const double factor = std::pow(-1., (double)idx)*cfg.resFactor;
+          for (int k = 0; k < Q*Q; ++k) { JL[k] *= factor; JR[k] *= factor; }
+          const int rowCell = idx == 0 ? x.L : x.R;
+          addBlock(rowCell, x.L, JL); addBlock(rowCell, x.R, JR);
+        }
+        continue;
+      }
       if (!x.isB) {
         // computeBothJacobTerms / computeJacobTerm (FVMCC_ComputeRhsJacob.cxx:126-236)
         double upFactor[2];

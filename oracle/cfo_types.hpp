@@ -64,7 +64,7 @@ struct Config {
   int32_t limiter;        // Limiter
   int32_t diffusive;      // Diffusive
   int32_t viscLaw;        // ViscLaw
-  int32_t computeJacobian;// 0 | 1 (numerical, FVMCC_ComputeRhsJacob)
+  int32_t computeJacobian;// 0 | 1 (numerical, FVMCC_ComputeRhsJacob) | 2 ("NumJacobAnalytic": FVMCC_ComputeRhsJacobAnalytic)
   int32_t useFullStencil; // limiter option
   int32_t freezeLimiter;  // PolyReconstructor.ci:66
   int32_t stopLimiting;   // FVMCC_PolyRec.cxx:52
@@ -98,6 +98,7 @@ struct Config {
   int32_t physicalModel;
   int32_t entropyFixID;   // RoeEntropyFixFlux.cxx:35 (0 = plain RoeFlux, 1 | 2 = "RoeEntropyFix")
   double refSpeed;        // MHDProjectionTerm refSpeed (hyperbolic divergence cleaning speed)
+  double coeffSigmoid;    // AUSMFlux.ci:64 coeffSigmoid (1e-8): blending of the sigmoid switches of the analytic Jacobian
 };
 
 struct MeshView {
