@@ -20,6 +20,10 @@ namespace cfb {
 
 // Roe; AUSM+ and AUSM+up with the perfect-gas interface sound speeds (choiceA12 4/5 are the TCNEQ variants).
 inline bool splitterSupported(const cfb200_config& c) {
+  // "NumJacobAnalytic": the analytic flux Jacobian exists for AUSM+up in conservative variables, inviscid (a19)
+  if (c.computeJacobian == 2 && !(c.physicalModel == CFB200_PM_EULER && c.fluxSplitter == CFB200_FS_AUSMPLUSUP &&
+                                  c.updateVar == CFB200_UV_CONS && c.diffusive == CFB200_DIFF_NONE && c.machInf > 0.))
+    return false;
   if (c.physicalModel == CFB200_PM_MHD3D_PROJECTION)      // MHD: centred splitters, conservative variables, inviscid
     return (c.fluxSplitter == CFB200_FS_LAXFRIED || c.fluxSplitter == CFB200_FS_HLL) && c.updateVar == CFB200_UV_CONS &&
            c.diffusive == CFB200_DIFF_NONE;
@@ -288,7 +292,10 @@ public:
       }
     } else {
       const int fam = splitterFamily(cfg);
-      if (doJac) {
+      if (doJac && cfg.computeJacobian == 2) {
+        bk.launch("innerFaceJacAnalytic", AnalyticInnerFaceK<D>{d, cfg}, d.nInner, 128);
+        bk.launch("boundaryFaceJac", BoundaryFaceK<D, true>{d, cfg}, d.nGhosts, 128);
+      } else if (doJac) {
         if (fam == 0) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 0>{d, cfg}, d.nInner, faceShape);
         else if (fam == 1) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 1>{d, cfg}, d.nInner, faceShape);
         else if (fam == 2) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 2>{d, cfg}, d.nInner, faceShape);

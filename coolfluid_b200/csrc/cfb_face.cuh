@@ -543,6 +543,67 @@ struct InnerFaceK {   // idx over interior faces; FS = 0 Roe, 1 AUSM+ / AUSM+up,
   }
 };
 
+// a19: "NumJacobAnalytic" (FVMCC_ComputeRhsJacobAnalytic.cxx:68-246) for AUSM+up in conservative variables, no
+// diffusive term: flux + update coefficients as InnerFaceK, and the two off-diagonal blocks from the analytic flux
+// Jacobians of the face states, integrated over the face (FVMCC_FluxSplitter.hh:88-96):
+//   block(R,L) = -(resFactor * area * dF/dU_L)       block(L,R) = resFactor * area * dF/dU_R
+// (the diagonal contributions are their negatives, gathered by DiagGather like the finite-difference ones; the same values
+// serve the one-sided updatable faces).  Boundary faces keep the finite-difference term (FVMCC_FluxSplitter.cxx:117-124).
+template <int D>
+struct AnalyticInnerFaceK {   // idx over interior faces
+  static constexpr int Q = D + 2;
+  Dev d; Cfg c;
+  CFB_HD void operator()(int f) const {
+    typedef Phys<D> P;
+    const int L = d.faceL[f], R = d.faceR[f];
+    double* blkRL = &d.bsrVal[(size_t)d.slotRL[f]*Q*Q];
+    double* blkLR = &d.bsrVal[(size_t)d.slotLR[f]*Q*Q];
+    if (!(d.updatable[L] || d.updatable[R])) {
+#pragma unroll
+      for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = 0.;
+      d.ucL[f] = 0.; d.ucR[f] = 0.; d.ucD[f] = 0.;
+      for (int k = 0; k < Q*Q; ++k) { blkRL[k] = 0.; blkLR[k] = 0.; }
+      return;
+    }
+    FaceWork<D> w;
+    w.f = f; w.L = L; w.R = R;
+    double sL[Q], sR[Q], vL[Q], vR[Q];
+#pragma unroll
+    for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + L]; sR[v] = d.U[(size_t)v*d.nStates + R]; }
+    w.load(d, c, f);
+    w.reconstruct(c, sL, sR, vL, vR);
+    {
+      PData pL, pR;
+      P::physicalData(c, vL, pL);
+      P::physicalData(c, vR, pR);
+      const double faceArea = w.area/1;
+      d.ucL[f] = dmax(P::maxEigenValue(pL, w.n), 0.)*faceArea;         // AUSMFlux.ci:410-440
+      double tn[3];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) tn[k] = -1.0*w.n[k];
+      d.ucR[f] = dmax(P::maxEigenValue(pR, tn), 0.)*faceArea;
+      d.ucD[f] = 0.;
+      typename P::ASide a, b;
+      P::aside(pL, a); P::aside(pR, b);
+      double flux[Q];
+      P::ausm(c, a, b, w.n, flux);
+#pragma unroll
+      for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = flux[v]*w.area;
+    }
+    typename P::JSide jl, jr;
+    P::jside(c, vL, jl);
+    P::jside(c, vR, jr);
+    const double rf = c.resFactor;
+    double J[Q*Q];
+    P::ausmUpJacobCons(c, jl, jr, w.n, 0, J);
+#pragma unroll
+    for (int k = 0; k < Q*Q; ++k) blkRL[k] = ((J[k]*w.area)*rf)*(-1.);
+    P::ausmUpJacobCons(c, jl, jr, w.n, 1, J);
+#pragma unroll
+    for (int k = 0; k < Q*Q; ++k) blkLR[k] = (J[k]*w.area)*rf;
+  }
+};
+
 // Boundary faces: flux as above (the ghost is the R state) and, when JAC, FVMCC_ComputeRhsJacob.cxx:240-317: the inner
 // state is perturbed, the ghost state is rebuilt by the boundary condition, both sides are re-extrapolated, and
 // resFactor * dF/dU_L goes to the boundary block of the face (added to the diagonal by DiagGather).

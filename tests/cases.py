@@ -154,6 +154,15 @@ CASES = {
     "euler3d_ausmplusup_a3": (lambda: meshgen.tet_box(3, 3, 3),
                               lambda: B.make_config(3, flux=B.FS_AUSMPLUSUP, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN,
                                                     jacobian=True, mach_inf=0.8, choice_a12=3), bcs_euler3d, False),
+    # a19 / BASELINE config 2: AUSM+up with the ANALYTIC Jacobian (NumJacobAnalytic), conservative variables
+    "euler2d_ausmplusup_analytic": (lambda: meshgen.quad_channel(12, 9, triangles=True),
+                                    lambda: B.make_config(2, flux=B.FS_AUSMPLUSUP, poly_rec=B.PR_LINEARLS,
+                                                          limiter=B.LIM_VENKTN, jacobian="analytic", mach_inf=2.0),
+                                    bcs_euler2d, False),
+    "euler3d_ausmplusup_analytic": (lambda: meshgen.hex_box(5, 4, 4),
+                                    lambda: B.make_config(3, flux=B.FS_AUSMPLUSUP, poly_rec=B.PR_LINEARLS,
+                                                          limiter=B.LIM_VENKTN, jacobian="analytic", mach_inf=0.8,
+                                                          res_factor=0.5), bcs_euler3d, False),
     # "RoeEntropyFix" (RoeEntropyFixFlux.cxx), both correction types
     "euler2d_roe_efix1": (lambda: meshgen.quad_channel(12, 9, triangles=True),
                           lambda: B.make_config(2, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, jacobian=True,
