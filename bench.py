@@ -66,9 +66,15 @@ def flagship(n, workload="ns3d"):
     `mhd3d` = configs[3]: the same box with MHD3DProjection (q = 9), HLL, LSQ + Venkatakrishnan."""
     import cases
     from coolfluid_b200 import meshgen
-    em = meshgen.hex_box(n, n, n)
+    em = meshgen.hex_box(n, n, n) if not workload.startswith("euler2d") else None
     if workload == "mhd3d":
         return em, cases.mhd3d_cfg(), cases.bcs_mhd3d()
+    if workload.startswith("euler2d"):
+        from coolfluid_b200 import config as B
+        em = meshgen.quad_channel(n, n)
+        jac = "analytic" if workload == "euler2d_analytic" else True
+        return em, B.make_config(2, flux=B.FS_AUSMPLUSUP, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, jacobian=jac,
+                                 mach_inf=2.0, choice_a12=1), cases.bcs_euler2d()
     return em, cases.ns3d_cfg(), cases.bcs_ns3d()
 
 
@@ -77,6 +83,11 @@ WORKLOADS = {
     "ns3d": ("configs[2]: 3D Navier-Stokes, %d^3 = %d jittered hex cells per GPU, Pvt variables, Roe + viscous "
              "(DiamondVolume3D) flux, LinearLS3D + Venktn3D, finite-difference block Jacobian (NumJacob) into device "
              "BSR, pseudo-steady time term", True, 744, 1400),
+    "euler2d_analytic": ("configs[1]: 2D Euler, %d^2 = %d quadrilaterals per GPU, Cons variables, AUSM+up (machInf 2, choiceA12 1), "
+                         "LinearLS2D + Venktn2D, ANALYTIC flux Jacobian (NumJacobAnalytic) into device BSR, pseudo-steady time "
+                         "term", False, 368, 640),
+    "euler2d_numjac": ("configs[1] with the finite-difference Jacobian instead: 2D Euler, %d^2 = %d quadrilaterals per GPU, "
+                       "AUSM+up, LinearLS2D + Venktn2D, NumJacob, pseudo-steady time term", False, 368, 640),
     "mhd3d": ("configs[3]: 3D ideal MHD (MHD3DProjection, q = 9), %d^3 = %d jittered hex cells per GPU, Cons variables, "
               "HLL flux, LinearLS3D + Venktn3D, finite-difference 9x9 block Jacobian into device BSR, pseudo-steady "
               "time term", "mhd", 960, 4536),
@@ -229,7 +240,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cfb200")
     ap.add_argument("--n", "--edge", dest="n", type=int, default=220, help="hex box edge per GPU (220^3 = 10.6 M cells, configs[2])")
-    ap.add_argument("--workload", default="ns3d", choices=sorted(WORKLOADS), help="ns3d = configs[2] (the metric), mhd3d = configs[3]")
+    ap.add_argument("--workload", default="ns3d", choices=sorted(WORKLOADS), help="ns3d = configs[2] (the metric), euler2d_* = configs[1], mhd3d = configs[3]")
     ap.add_argument("--cpu-sample", type=int, default=36, help="edge of the per-thread hex box of the CPU baseline")
     ap.add_argument("--cpu-evals", type=int, default=24, help="evaluations per thread of the cpu_baseline leg (~10-20 s)")
     ap.add_argument("--no-cpu-baseline", action="store_true")

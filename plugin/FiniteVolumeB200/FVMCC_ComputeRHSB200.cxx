@@ -20,6 +20,8 @@ MethodCommandProvider<FVMCC_ComputeRHSB200, CellCenterFVMData, FiniteVolumeB200M
 fvmcc_computeRHSB200Provider("B200Rhs");
 MethodCommandProvider<FVMCC_ComputeRhsJacobB200, CellCenterFVMData, FiniteVolumeB200Module>
 fvmcc_computeRhsJacobB200Provider("B200RhsJacob");
+MethodCommandProvider<FVMCC_ComputeRhsJacobAnalyticB200, CellCenterFVMData, FiniteVolumeB200Module>
+fvmcc_computeRhsJacobAnalyticB200Provider("B200RhsJacobAnalytic");
 
 void FVMCC_ComputeRHSB200::defineConfigOptions(Config::OptionList& options)
 {
@@ -116,7 +118,7 @@ void FVMCC_ComputeRHSB200::execute()
   DataHandle<CFreal> updateCoeff = socket_updateCoeff.getDataHandle();
   cfb200_config c; fillConfig(c);
   c.resFactor = getResFactor();
-  c.computeJacobian = withJacobian() && getMethodData().doComputeJacobian();
+  c.computeJacobian = getMethodData().doComputeJacobian() ? withJacobian() : 0;
   c.iter = SubSystemStatusStack::getActive()->getNbIter();
   c.residual = SubSystemStatusStack::getActive()->getResidual();
   check(cfb200_set_step(m_h, &c), "cfb200_set_step");

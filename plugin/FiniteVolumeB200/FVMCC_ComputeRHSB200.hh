@@ -1,6 +1,6 @@
 // FVMCC_ComputeRHSB200 — drop-in ComputeRHS command: selects the B200 engine from a .CFcase with
 //   Simulator.Modules.Libs = ... libFiniteVolume libFiniteVolumeNavierStokes libFiniteVolumeB200
-//   Simulator.SubSystem.CellCenterFVM.ComputeRHS = B200Rhs          (explicit)   | B200RhsJacob (implicit)
+//   Simulator.SubSystem.CellCenterFVM.ComputeRHS = B200Rhs          (explicit)   | B200RhsJacob (implicit, NumJacob) | B200RhsJacobAnalytic (implicit, NumJacobAnalytic)
 //   Simulator.SubSystem.CellCenterFVM.B200RhsJacob.Device = 0        (default: rank % deviceCount)
 // It derives from FVMCC_ComputeRHS (as plugins/FiniteVolumeCUDA/FVMCC_ComputeRHSCell.hh:31 does) to inherit the
 // sockets and the configured strategies, copies socket data to libcfb200 once in setup(), and in execute() sends
@@ -26,8 +26,8 @@ public:
   virtual void execute();
 
 protected:
-  /// true for the "B200RhsJacob" provider
-  virtual bool withJacobian() const { return false; }
+  /// 0 for "B200Rhs", 1 for "B200RhsJacob" (= NumJacob), 2 for "B200RhsJacobAnalytic" (= NumJacobAnalytic)
+  virtual int withJacobian() const { return 0; }
   void fillConfig(cfb200_config& c);
   void uploadMesh();
   void insertJacobian();
@@ -44,7 +44,15 @@ class FVMCC_ComputeRhsJacobB200 : public FVMCC_ComputeRHSB200 {
 public:
   explicit FVMCC_ComputeRhsJacobB200(const std::string& name) : FVMCC_ComputeRHSB200(name) {}
 protected:
-  virtual bool withJacobian() const { return true; }
+  virtual int withJacobian() const { return 1; }
+};
+
+/// drop-in for FVMCC_ComputeRhsJacobAnalytic ("NumJacobAnalytic", FVMCC_ComputeRhsJacobAnalytic.cxx:32-35)
+class FVMCC_ComputeRhsJacobAnalyticB200 : public FVMCC_ComputeRHSB200 {
+public:
+  explicit FVMCC_ComputeRhsJacobAnalyticB200(const std::string& name) : FVMCC_ComputeRHSB200(name) {}
+protected:
+  virtual int withJacobian() const { return 2; }
 };
 
 } } }
