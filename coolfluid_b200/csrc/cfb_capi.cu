@@ -51,6 +51,32 @@ __global__ void __launch_bounds__(BS, MINB) k_staged(const F f, const int n) {
   }
 }
 
+// Two-phase variant for functors that stage ONE block per phase (f.run(i, phase, ...), f.slot(i, phase)): q = 9 blocks.
+template <class F, int BS, int MINB>
+__global__ void __launch_bounds__(BS, MINB) k_staged2(const F f, const int n) {
+  extern __shared__ double sm[];
+  constexpr int STRIDE = BS + 1;
+  static_assert(F::BLK >= 32 && F::STAGE >= F::BLK + 1, "staging layout");
+  const int t = threadIdx.x, lane = t & 31, warpBase = t & ~31;
+  const int i = blockIdx.x*BS + t;
+  double* out = f.out();
+  for (int phase = 0; phase < 2; ++phase) {
+    int s = -1;
+    if (i < n) { f.run(i, phase, sm + t, STRIDE); s = f.slot(i, phase); }
+    sm[F::BLK*STRIDE + t] = __hiloint2double(0, s);
+    __syncwarp();
+    int k = lane, lf = 0;
+#pragma unroll 2
+    for (int it = 0; it < F::BLK; ++it) {
+      const int slot = __double2loint(sm[F::BLK*STRIDE + warpBase + lf]);
+      if (slot >= 0) out[(size_t)slot*F::BLK + k] = sm[k*STRIDE + warpBase + lf];
+      k += 32;
+      if (k >= F::BLK) { k -= F::BLK; ++lf; }
+    }
+    __syncwarp();
+  }
+}
+
 // fixed-shape block sum (run-to-run deterministic): each block reduces 1024 consecutive entries
 __global__ void __launch_bounds__(256) k_block_sum(const double* __restrict__ x, double* __restrict__ out, int n) {
   __shared__ double s[256];
@@ -160,6 +186,24 @@ struct CudaBackend {
       case 4: go(k_staged<F, 128, 4>, 128); break;      // 16 warps, 128 registers
       default: go(k_staged<F, 128, 2>, 128); break;     //  8 warps, 255 registers
     }
+    CFB_CUDA(cudaGetLastError());
+    if (ev) CFB_CUDA(cudaEventRecord(ev->b, stream));
+  }
+
+  template <class F> void launchStaged2(const char* name, const F& f, int n) {
+    if (n <= 0) return;
+    Ev* ev = nullptr;
+    if (timing) {
+      if (nEv == evs.size()) { Ev e; e.name = name; CFB_CUDA(cudaEventCreate(&e.a)); CFB_CUDA(cudaEventCreate(&e.b)); evs.push_back(e); }
+      ev = &evs[nEv++]; ev->name = name;
+      CFB_CUDA(cudaEventRecord(ev->a, stream));
+    }
+    constexpr int BS = 128;
+    const size_t smem = (size_t)F::STAGE*(BS + 1)*sizeof(double);
+    auto kern = k_staged2<F, BS, 2>;
+    CFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    kern<<<(n + BS - 1)/BS, BS, smem, stream>>>(f, n);
     CFB_CUDA(cudaGetLastError());
     if (ev) CFB_CUDA(cudaEventRecord(ev->b, stream));
   }

@@ -56,15 +56,24 @@ CFB_HD void faceRecon(const Dev& d, const Cfg& c, int f, int L, int R, double* n
 template <class PH, bool JAC>
 struct CentredInnerFaceK {   // idx over interior faces
   static constexpr int D = PH::DIM, Q = PH::Q;
+  // JAC: launched in two phases through k_staged2 (cfb_capi.cu): phase 0 evaluates the face and perturbs the L state ->
+  // block(R,L); phase 1 re-evaluates the two unperturbed sides and perturbs the R state -> block(L,R).  One q x q block is
+  // staged in shared memory per thread and written out by the warp in whole rows (a 9 x 9 block is 648 B: staging both at
+  // once would leave one resident block per SM).
+  static constexpr int BLK = Q*Q;
+  static constexpr int STAGE = BLK + 1;
   Dev d; Cfg c;
-  CFB_HD void operator()(int f) const {
+  CFB_HD double* out() const { return d.bsrVal; }
+  CFB_HD int slot(int f, int phase) const { return phase ? d.slotLR[f] : d.slotRL[f]; }
+  CFB_HD void operator()(int f) const { run(f, 0, nullptr, 0); }        // RHS only
+  CFB_HD void run(int f, int phase, double* stg, int stride) const {
     const int L = d.faceL[f], R = d.faceR[f];
-    double* blkRL = JAC ? &d.bsrVal[(size_t)d.slotRL[f]*Q*Q] : nullptr;
-    double* blkLR = JAC ? &d.bsrVal[(size_t)d.slotLR[f]*Q*Q] : nullptr;
     if (!(d.updatable[L] || d.updatable[R])) {             // FVMCC_ComputeRHS.cxx:212-213
-      for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = 0.;
-      d.ucL[f] = 0.; d.ucR[f] = 0.; d.ucD[f] = 0.;
-      if (JAC) for (int k = 0; k < Q*Q; ++k) { blkRL[k] = 0.; blkLR[k] = 0.; }
+      if (phase == 0) {
+        for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = 0.;
+        d.ucL[f] = 0.; d.ucR[f] = 0.; d.ucD[f] = 0.;
+      }
+      if (JAC) for (int k = 0; k < BLK; ++k) stg[(size_t)k*stride] = 0.;
       return;
     }
     double n[3], area, gL[Q], gR[Q], sL[Q], sR[Q], vL[Q], vR[Q];
@@ -79,7 +88,9 @@ struct CentredInnerFaceK {   // idx over interior faces
     PH::cside(c, vR, n, b);
     double flux[Q];
     PH::centred(c, a, b, flux);
-    {
+#pragma unroll
+    for (int v = 0; v < Q; ++v) flux[v] *= area;
+    if (phase == 0) {
       // update coefficients: LaxFriedFlux.cxx:120-188 / HLLFlux.cxx:135-150 (left: _leftEv.max(); right: getMaxEigenValue
       // with the reversed normal)
       const double faceArea = area/1;
@@ -91,16 +102,15 @@ struct CentredInnerFaceK {   // idx over interior faces
       PH::physicalData(c, vR, pR);
       d.ucR[f] = dmax(PH::maxEigenValue(c, pR, tn), 0.)*faceArea;
       d.ucD[f] = 0.;
-    }
 #pragma unroll
-    for (int v = 0; v < Q; ++v) { flux[v] *= area; d.faceFlux[(size_t)v*d.nFaces + f] = flux[v]; }
+      for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = flux[v];
+    }
     if (!JAC) return;
     // FVMCC_ComputeRhsJacob.cxx:126-236,321-365 with the frozen gradient / limiter (LeastSquareP1PolyRec3D.cxx:272-318)
     const double rf = c.resFactor;
+    const int side = phase;
 #pragma unroll 1
-    for (int it = 0; it < 2*Q; ++it) {
-      const int side = (it >= Q) ? 1 : 0;
-      const int iVar = it - side*Q;
+    for (int iVar = 0; iVar < Q; ++iVar) {
       double orig = 0., gp = 0.;
 #pragma unroll
       for (int v = 0; v < Q; ++v) {
@@ -109,7 +119,7 @@ struct CentredInnerFaceK {   // idx over interior faces
       }
       const double eps = fdEps(c, iVar, orig);
       const double pv = orig + eps;
-      const double pvr = (c.polyRec == CFB200_PR_CONSTANT) ? pv : pv + gp;
+      const double pvr = lin ? pv + gp : pv;
       double vp[Q];
 #pragma unroll
       for (int v = 0; v < Q; ++v) { const double base = side ? vR[v] : vL[v]; vp[v] = (v == iVar) ? pvr : base; }
@@ -118,12 +128,11 @@ struct CentredInnerFaceK {   // idx over interior faces
       double pf[Q];
       if (side == 0) PH::centred(c, pert, b, pf); else PH::centred(c, a, pert, pf);
       const double invEps = ddiv(1., eps);
-      double* blk = side ? blkLR : blkRL;        // column iVar of block(R,L) (perturbed L) / block(L,R) (perturbed R)
 #pragma unroll
       for (int v = 0; v < Q; ++v) {
         double fd = (pf[v]*area - flux[v])*invEps;
-        fd *= rf;                                 // what row L receives (upFactor[0])
-        blk[v*Q + iVar] = side ? fd : fd*(-1.0);  // row R receives upFactor[1] = -1 times that
+        fd *= rf;                                                    // what row L receives (upFactor[0])
+        stg[(size_t)(v*Q + iVar)*stride] = side ? fd : fd*(-1.0);    // row R receives upFactor[1] = -1 times that
       }
     }
   }

@@ -284,7 +284,7 @@ public:
       bk.launch("limiter", LimiterK<D, PH>{d, cfg}, d.nCells, 128);
     if constexpr (PH::CENTRED_ONLY) {
       if (doJac) {
-        bk.launch("innerFaceJac", CentredInnerFaceK<PH, true>{d, cfg}, d.nInner, 128);
+        bk.launchStaged2("innerFaceJac", CentredInnerFaceK<PH, true>{d, cfg}, d.nInner);
         bk.launch("boundaryFaceJac", CentredBoundaryFaceK<PH, true>{d, cfg}, d.nGhosts, 128);
       } else {
         bk.launch("innerFace", CentredInnerFaceK<PH, false>{d, cfg}, d.nInner, 128);
@@ -293,7 +293,7 @@ public:
     } else {
       const int fam = splitterFamily(cfg);
       if (doJac && cfg.computeJacobian == 2) {
-        bk.launch("innerFaceJacAnalytic", AnalyticInnerFaceK<D>{d, cfg}, d.nInner, 128);
+        bk.launchStaged("innerFaceJacAnalytic", AnalyticInnerFaceK<D>{d, cfg}, d.nInner, faceShape);
         bk.launch("boundaryFaceJac", BoundaryFaceK<D, true>{d, cfg}, d.nGhosts, 128);
       } else if (doJac) {
         if (fam == 0) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 0>{d, cfg}, d.nInner, faceShape);

@@ -550,19 +550,22 @@ struct InnerFaceK {   // idx over interior faces; FS = 0 Roe, 1 AUSM+ / AUSM+up,
 // (the diagonal contributions are their negatives, gathered by DiagGather like the finite-difference ones; the same values
 // serve the one-sided updatable faces).  Boundary faces keep the finite-difference term (FVMCC_FluxSplitter.cxx:117-124).
 template <int D>
-struct AnalyticInnerFaceK {   // idx over interior faces
+struct AnalyticInnerFaceK {   // idx over interior faces; staged like InnerFaceK (the warp writes whole blocks)
   static constexpr int Q = D + 2;
+  static constexpr int BLK = Q*Q;
+  static constexpr int NOUT = 2*Q*Q;
+  static constexpr int STAGE = NOUT + 2;
   Dev d; Cfg c;
-  CFB_HD void operator()(int f) const {
+  CFB_HD double* out() const { return d.bsrVal; }
+  CFB_HD void slots(int f, int& s0, int& s1) const { s0 = d.slotRL[f]; s1 = d.slotLR[f]; }
+  CFB_HD void run(int f, double* stg, int stride) const {
     typedef Phys<D> P;
     const int L = d.faceL[f], R = d.faceR[f];
-    double* blkRL = &d.bsrVal[(size_t)d.slotRL[f]*Q*Q];
-    double* blkLR = &d.bsrVal[(size_t)d.slotLR[f]*Q*Q];
     if (!(d.updatable[L] || d.updatable[R])) {
 #pragma unroll
       for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = 0.;
       d.ucL[f] = 0.; d.ucR[f] = 0.; d.ucD[f] = 0.;
-      for (int k = 0; k < Q*Q; ++k) { blkRL[k] = 0.; blkLR[k] = 0.; }
+      for (int k = 0; k < NOUT; ++k) stg[(size_t)k*stride] = 0.;
       return;
     }
     FaceWork<D> w;
@@ -597,10 +600,10 @@ struct AnalyticInnerFaceK {   // idx over interior faces
     double J[Q*Q];
     P::ausmUpJacobCons(c, jl, jr, w.n, 0, J);
 #pragma unroll
-    for (int k = 0; k < Q*Q; ++k) blkRL[k] = ((J[k]*w.area)*rf)*(-1.);
+    for (int k = 0; k < Q*Q; ++k) stg[(size_t)k*stride] = ((J[k]*w.area)*rf)*(-1.);
     P::ausmUpJacobCons(c, jl, jr, w.n, 1, J);
 #pragma unroll
-    for (int k = 0; k < Q*Q; ++k) blkLR[k] = (J[k]*w.area)*rf;
+    for (int k = 0; k < Q*Q; ++k) stg[(size_t)(Q*Q + k)*stride] = (J[k]*w.area)*rf;
   }
 };
 

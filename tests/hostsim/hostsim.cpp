@@ -38,6 +38,15 @@ struct HostLoopBackend {
       }
     }
   }
+  template <class F> void launchStaged2(const char*, const F& f, int n) {
+    double stg[F::STAGE];
+    for (int i = 0; i < n; ++i)
+      for (int phase = 0; phase < 2; ++phase) {
+        f.run(i, phase, stg, 1);
+        const int slot = f.slot(i, phase);
+        if (slot >= 0) for (int k = 0; k < F::BLK; ++k) f.out()[(size_t)slot*F::BLK + k] = stg[k];
+      }
+  }
   double sumOrdered(double* x, int n) { double s = 0.; for (int i = 0; i < n; ++i) s += x[i]; return s; }
 };
 }
