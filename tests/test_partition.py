@@ -97,3 +97,38 @@ def test_partition_matches_single_domain(name, nparts, oracle, hostsim_lib):
                 s = np.abs(jac_g[gk]).max()
                 # FD entries amplify the 1e-16 summation-order differences of gradients / nodal states by 1/eps ~ 1e6
                 assert np.abs(jl[k] - jac_g[gk]).max() <= 1e-8*s + 1e-300, (c, k)
+
+
+def test_bench_slab_partition_is_consistent(product_lib):
+    """bench.py --gpus N: every rank's send list pairs, cell for cell (same (i, j, k) order), with the neighbour's
+    overlap list; the leading n_interior cells see no overlap cell; own cells are updatable, overlap cells are not."""
+    import bench
+    from coolfluid_b200 import lib as cl
+    n, world = 5, 3
+    parts = []
+    for r in range(world):
+        em, p = bench.slab_partition(n, r, world, "ns3d")
+        fm = cl.build_mesh(em, product_lib)
+        x = fm.centres.reshape(-1, 3)[:fm.nCells]
+        lo = 2 if r > 0 else 0
+        parts.append((p, x, lo))
+        assert p.n_updatable == n**3 and int(p.updatable.sum()) == n**3
+        assert p.updatable[:p.n_updatable].all() and not p.updatable[p.n_updatable:].any()
+        # interior cells: no stencil entry is an overlap cell
+        sp, st = fm.stencilPtr, fm.stencil
+        for c in range(p.n_interior):
+            nb = st[sp[c]:sp[c+1]]
+            nb = nb[nb < fm.nCells]
+            assert p.updatable[nb].all()
+    h = 1.0/n
+    for r in range(world):
+        p, x, lo = parts[r]
+        for peer, ids in p.send.items():
+            q, xq, loq = parts[peer]
+            rid = q.recv[r]
+            assert len(ids) == len(rid) == 2*n*n
+            # same cell of the global box: x, y match to the jitter, z matches after removing each slab's own offset
+            zs = x[ids, 2] - lo*h + r*n*h
+            zr = xq[rid, 2] - loq*h + peer*n*h
+            assert np.abs(zs - zr).max() < 0.5*h
+            assert np.abs(x[ids, :2] - xq[rid, :2]).max() < 0.5*h
