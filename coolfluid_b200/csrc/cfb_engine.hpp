@@ -311,6 +311,8 @@ public:
     }
     bk.launch("cellGather", CellGather<D, PH>{d, cfg}, d.nCells, 256);
     if (doJac) {
+      if ((long long)d.nCells*DiagGather<D, PH>::GS > 2147483647LL)
+        throw std::runtime_error("mesh too large for one device: nCells * q*q exceeds the 32-bit launch index");
       bk.launch("diagGather", DiagGather<D, PH>{d}, d.nCells*DiagGather<D, PH>::GS, 256);
       if (nNonUpd) bk.launch("zeroRows", ZeroRows<D, PH>{d, nonUpdCells}, nNonUpd*ZeroRows<D, PH>::GS, 256);
     }

@@ -157,6 +157,38 @@ def test_large_size_properties(product_lib):
     interior[fm.faceL[fm.nInner:]] = False
     scale = np.abs(jac).max()
     assert np.abs(colsum[interior]).max() <= 1e-12*scale
+    # (i) a second evaluation of the same state is bit-identical (no atomics, fixed gather order)
+    rhs2, uc2 = e.compute_rhs()
+    assert np.array_equal(rhs, rhs2) and np.array_equal(uc, uc2)
+    assert np.array_equal(jac, e.bsr_values().reshape(-1, 25))
+    e.close()
+
+
+def test_full_size_freestream_and_determinism(product_lib):
+    """BASELINE config 3 at its full size (220^3 = 10.6 M hexahedra): a uniform state is preserved by every cell
+    without a boundary face (closed control volumes, zero gradients: the residual is rounding noise of the flux sums),
+    and two evaluations of a non-uniform state give bit-identical residuals."""
+    n = 220
+    fm = cl.build_mesh(meshgen.hex_box(n, n, n), product_lib)
+    cfg = cases.ns3d_cfg()
+    e = cl.Engine(cfg, 0, lib=product_lib)
+    e.set_mesh(fm, cases.bcs_ns3d())
+    U = np.empty((fm.nCells, 5))
+    U[:] = [1.0, 0.4, 0.03, 0.02, 1.0]                    # p u v w T in the units of cases.ns3d_cfg()
+    e.set_states(U.reshape(-1))
+    rhs, uc = e.compute_rhs()
+    # two cell layers next to the boundary see the ghost states through their gradients
+    x = fm.centres.reshape(-1, 3)[:fm.nCells]
+    interior = ((x > 2.0/n) & (x < 1.0 - 2.0/n)).all(axis=1)
+    assert interior.sum() == (n - 4)**3
+    flux_scale = 3.5*1.0*0.4*(1.0/n)**2                   # ~ rho u H * face area
+    assert np.abs(rhs.reshape(fm.nCells, 5)[interior]).max() <= 1e-11*flux_scale
+    assert (uc > 0).all()
+    U2 = cases.init_state(fm, 5, True)
+    e.set_states(U2[:fm.nCells*5])
+    a, ua = e.compute_rhs()
+    b, ub = e.compute_rhs()
+    assert np.isfinite(a).all() and np.array_equal(a, b) and np.array_equal(ua, ub)
     e.close()
 
 
