@@ -75,6 +75,8 @@ def flagship(n, workload="ns3d"):
         jac = "analytic" if workload == "euler2d_analytic" else True
         return em, B.make_config(2, flux=B.FS_AUSMPLUSUP, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, jacobian=jac,
                                  mach_inf=2.0, choice_a12=1), cases.bcs_euler2d()
+    if workload == "ns3d_corrected":
+        return em, cases.ns3d_cfg(derivative="corrected"), cases.bcs_ns3d()
     return em, cases.ns3d_cfg(), cases.bcs_ns3d()
 
 
@@ -83,6 +85,9 @@ WORKLOADS = {
     "ns3d": ("configs[2]: 3D Navier-Stokes, %d^3 = %d jittered hex cells per GPU, Pvt variables, Roe + viscous "
              "(DiamondVolume3D) flux, LinearLS3D + Venktn3D, finite-difference block Jacobian (NumJacob) into device "
              "BSR, pseudo-steady time term", True, 744, 1400),
+    "ns3d_corrected": ("configs[2] with DerivativeStrategy = Corrected3D instead of DiamondVolume3D: 3D Navier-Stokes, "
+                       "%d^3 = %d jittered hex cells per GPU, Pvt variables, Roe + viscous flux, LinearLS3D + Venktn3D, "
+                       "NumJacob into device BSR, pseudo-steady time term", True, 744, 1400),
     "euler2d_analytic": ("configs[1]: 2D Euler, %d^2 = %d quadrilaterals per GPU, Cons variables, AUSM+up (machInf 2, choiceA12 1), "
                          "LinearLS2D + Venktn2D, ANALYTIC flux Jacobian (NumJacobAnalytic) into device BSR, pseudo-steady time "
                          "term", False, 368, 640),

@@ -24,6 +24,10 @@ inline bool splitterSupported(const cfb200_config& c) {
   if (c.computeJacobian == 2 && !(c.physicalModel == CFB200_PM_EULER && c.fluxSplitter == CFB200_FS_AUSMPLUSUP &&
                                   c.updateVar == CFB200_UV_CONS && c.diffusive == CFB200_DIFF_NONE && c.machInf > 0.))
     return false;
+  // Corrected2D/3D reads the cell gradients (uX uY uZ sockets), which only the linear reconstruction computes
+  if (c.diffusive == CFB200_DIFF_NS && c.derivativeStrategy != CFB200_DV_DIAMOND &&
+      !(c.derivativeStrategy == CFB200_DV_CORRECTED && c.polyRec != CFB200_PR_CONSTANT))
+    return false;
   if (c.physicalModel == CFB200_PM_MHD3D_PROJECTION)      // MHD: centred splitters, conservative variables, inviscid
     return (c.fluxSplitter == CFB200_FS_LAXFRIED || c.fluxSplitter == CFB200_FS_HLL) && c.updateVar == CFB200_UV_CONS &&
            c.diffusive == CFB200_DIFF_NONE;
@@ -119,6 +123,31 @@ public:
     d.nodeW = upload(m.nodeW, (size_t)m.nodeNbrPtr[nn]);
     d.cvol = upload(m.cvol, nf);
     d.cvSign = upload(m.cvSign, nf);
+    d.bndStPtr = nullptr; d.bndSt = nullptr;
+    if (cfg.derivativeStrategy == CFB200_DV_CORRECTED && cfg.diffusive == CFB200_DIFF_NS) {
+      // gradient stencil of each boundary face (CorrectedDerivative2D.cxx:376-414): the left cell, then, in the order of
+      // the left cell's reconstruction stencil, the ghosts other than the face's own and the cells touching a face node
+      std::vector<int32_t> sp(1, 0), st;
+      for (int g = 0; g < ng; ++g) {
+        const int f = ni + g, L = m.faceL[f], R = m.faceR[f];
+        const int32_t* fnB = m.faceNodes + m.faceNodePtr[f];
+        const int32_t* fnE = m.faceNodes + m.faceNodePtr[f+1];
+        st.push_back(L);
+        for (int k = m.stencilPtr[L]; k < m.stencilPtr[L+1]; ++k) {
+          const int s = m.stencil[k];
+          bool member = (s >= nc) ? (s != R) : false;
+          if (s < nc)
+            for (const int32_t* pn = fnB; pn != fnE && !member; ++pn) {
+              const int32_t* nb = m.nodeNbr + m.nodeNbrPtr[*pn];
+              const int32_t* ne = m.nodeNbr + m.nodeNbrPtr[*pn + 1];
+              member = std::find(nb, ne, s) != ne;
+            }
+          if (member) st.push_back(s);
+        }
+        sp.push_back((int32_t)st.size());
+      }
+      d.bndStPtr = upload(sp); d.bndSt = upload(st);
+    }
     d.faceBC = upload(m.faceBC, nf);
     d.updatable = upload(m.updatable, nc);
     for (int f = ni; f < nf; ++f)
@@ -260,6 +289,28 @@ public:
   // ---- execute ------------------------------------------------------------------------------------
   template <int D, class PH> void applyBC_() { if (d.nGhosts) bk.launch("applyBC", GhostFill<D, PH>{d, cfg}, d.nGhosts, 128); }
 
+  // the face kernels of the Euler / Navier-Stokes families; DV = derivative computer of the diffusive flux
+  template <int D, int DV>
+  void faceKernels_(bool doJac, int faceShape) {
+    const int fam = splitterFamily(cfg);
+    if (doJac && cfg.computeJacobian == 2) {
+      bk.launchStaged("innerFaceJacAnalytic", AnalyticInnerFaceK<D>{d, cfg}, d.nInner, faceShape);
+      bk.launch("boundaryFaceJac", BoundaryFaceK<D, true, 0>{d, cfg}, d.nGhosts, 128);
+    } else if (doJac) {
+      if (fam == 0) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 0, DV>{d, cfg}, d.nInner, faceShape);
+      else if (fam == 1) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 1, DV>{d, cfg}, d.nInner, faceShape);
+      else if (fam == 2) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 2, DV>{d, cfg}, d.nInner, faceShape);
+      else bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 3, DV>{d, cfg}, d.nInner, faceShape);
+      bk.launch("boundaryFaceJac", BoundaryFaceK<D, true, DV>{d, cfg}, d.nGhosts, 128);
+    } else {
+      if (fam == 0) bk.launch("innerFace", InnerFaceK<D, false, 0, DV>{d, cfg}, d.nInner, 128);
+      else if (fam == 1) bk.launch("innerFace", InnerFaceK<D, false, 1, DV>{d, cfg}, d.nInner, 128);
+      else if (fam == 2) bk.launch("innerFace", InnerFaceK<D, false, 2, DV>{d, cfg}, d.nInner, 128);
+      else bk.launch("innerFace", InnerFaceK<D, false, 3, DV>{d, cfg}, d.nInner, 128);
+      bk.launch("boundaryFace", BoundaryFaceK<D, false, DV>{d, cfg}, d.nGhosts, 128);
+    }
+  }
+
   template <int D, class PH> void computeRhs_(bool applyBC) {
     const bool doJac = cfg.computeJacobian != 0;
     if (doJac) ensureJacobian();
@@ -291,23 +342,8 @@ public:
         bk.launch("boundaryFace", CentredBoundaryFaceK<PH, false>{d, cfg}, d.nGhosts, 128);
       }
     } else {
-      const int fam = splitterFamily(cfg);
-      if (doJac && cfg.computeJacobian == 2) {
-        bk.launchStaged("innerFaceJacAnalytic", AnalyticInnerFaceK<D>{d, cfg}, d.nInner, faceShape);
-        bk.launch("boundaryFaceJac", BoundaryFaceK<D, true>{d, cfg}, d.nGhosts, 128);
-      } else if (doJac) {
-        if (fam == 0) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 0>{d, cfg}, d.nInner, faceShape);
-        else if (fam == 1) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 1>{d, cfg}, d.nInner, faceShape);
-        else if (fam == 2) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 2>{d, cfg}, d.nInner, faceShape);
-        else bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 3>{d, cfg}, d.nInner, faceShape);
-        bk.launch("boundaryFaceJac", BoundaryFaceK<D, true>{d, cfg}, d.nGhosts, 128);
-      } else {
-        if (fam == 0) bk.launch("innerFace", InnerFaceK<D, false, 0>{d, cfg}, d.nInner, 128);
-        else if (fam == 1) bk.launch("innerFace", InnerFaceK<D, false, 1>{d, cfg}, d.nInner, 128);
-        else if (fam == 2) bk.launch("innerFace", InnerFaceK<D, false, 2>{d, cfg}, d.nInner, 128);
-        else bk.launch("innerFace", InnerFaceK<D, false, 3>{d, cfg}, d.nInner, 128);
-        bk.launch("boundaryFace", BoundaryFaceK<D, false>{d, cfg}, d.nGhosts, 128);
-      }
+      if (cfg.derivativeStrategy == CFB200_DV_CORRECTED && cfg.diffusive == CFB200_DIFF_NS) faceKernels_<D, 1>(doJac, faceShape);
+      else faceKernels_<D, 0>(doJac, faceShape);
     }
     bk.launch("cellGather", CellGather<D, PH>{d, cfg}, d.nCells, 256);
     if (doJac) {
@@ -341,6 +377,18 @@ public:
     else if (cfg.dim == 2) bk.launch("updateSol", UpdateSolFwdEuler<2>{d, cfl, monitorVar}, d.nCells, 256);
     else bk.launch("updateSol", UpdateSolFwdEuler<3>{d, cfl, monitorVar}, d.nCells, 256);
     return bk.sumOrdered(d.partial, d.nCells);
+  }
+  template <int D, class PH> double updateSolNewton_(const double* alpha, int monitorVar) {
+    UpdateSolNewton<D, PH> k;
+    k.d = d; k.monitorVar = monitorVar;
+    for (int v = 0; v < PH::Q; ++v) k.alpha[v] = alpha ? alpha[v] : 1.;
+    bk.launch("updateSolNewton", k, d.nCells, 256);
+    return bk.sumOrdered(d.partial, d.nCells);
+  }
+  double updateSolNewton(const double* alpha, int monitorVar) {
+    if (isMhd()) return updateSolNewton_<3, MhdPhys>(alpha, monitorVar);
+    if (cfg.dim == 2) return updateSolNewton_<2, Phys<2> >(alpha, monitorVar);
+    return updateSolNewton_<3, Phys<3> >(alpha, monitorVar);
   }
 };
 

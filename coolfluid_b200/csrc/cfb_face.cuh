@@ -482,6 +482,8 @@ struct FaceWork {
   }
 };
 
+#include "cfb_corrected.cuh"
+
 // ------------------------------------------------------------------------------------------------
 // Interior faces: flux + update coefficients into face-owned slots and, when JAC, the two off-diagonal blocks
 //   block(R,L) = -resFactor * dF/dU_L        block(L,R) = +resFactor * dF/dU_R
@@ -490,8 +492,8 @@ struct FaceWork {
 // these and are gathered by DiagGather.  One-sided updatable faces (partition overlap) use the same values
 // (FVMCC_ComputeRhsJacob.cxx:184-236: row idx receives (-1)^idx * resFactor * dF/dU); the blocks that land in
 // non-updatable rows are staging for DiagGather and are zeroed afterwards by ZeroRows.
-template <int D, bool JAC, int FS = 0>
-struct InnerFaceK {   // idx over interior faces; FS = 0 Roe, 1 AUSM+ / AUSM+up, 2 LaxFried / HLL
+template <int D, bool JAC, int FS = 0, int DV = 0>
+struct InnerFaceK {   // idx over interior faces; FS = 0 Roe, 1 AUSM+ / AUSM+up, 2 LaxFried / HLL; DV = 0 DiamondVolume, 1 Corrected
   static constexpr int Q = D + 2;
   static constexpr int BLK = Q*Q;
   static constexpr int NOUT = 2*Q*Q;    // per-thread staging (shared memory, entry k at stg[k*stride]): block(R,L) | block(L,R)
@@ -519,7 +521,7 @@ struct InnerFaceK {   // idx over interior faces; FS = 0 Roe, 1 AUSM+ / AUSM+up,
 #pragma unroll
     for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + L]; sR[v] = d.U[(size_t)v*d.nStates + R]; }
     typename FaceWork<D>::DiamondRaw raw;
-    if (hasDiff) w.fetchDiamond(d, raw);                   // consumed by innerDiffusive
+    if (DV == 0 && hasDiff) w.fetchDiamond(d, raw);        // consumed by innerDiffusive
     w.load(d, c, f);
     w.reconstruct(c, sL, sR, vL, vR);
     {
@@ -537,7 +539,15 @@ struct InnerFaceK {   // idx over interior faces; FS = 0 Roe, 1 AUSM+ / AUSM+up,
     double dfluxBase[Q], ucD = 0.;
 #pragma unroll
     for (int v = 0; v < Q; ++v) dfluxBase[v] = 0.;
-    if (hasDiff) w.innerDiffusive(d, c, sL, sR, JAC, raw, dfluxBase, ucD, stg, stride);
+    if (hasDiff) {
+      if constexpr (DV == 1) {
+        CorrectedWork<D> cw;
+        cw.setup(d, c, f, L, R, false, w.n, w.area);
+        cw.innerDiffusive(d, c, R, sL, sR, JAC, dfluxBase, ucD, stg, stride);
+      } else {
+        w.innerDiffusive(d, c, sL, sR, JAC, raw, dfluxBase, ucD, stg, stride);
+      }
+    }
     d.ucD[f] = ucD;
     w.template innerConvective<FS>(d, c, sL, sR, vL, vR, hasDiff, dfluxBase, JAC, stg, stride);
   }
@@ -610,8 +620,8 @@ struct AnalyticInnerFaceK {   // idx over interior faces; staged like InnerFaceK
 // Boundary faces: flux as above (the ghost is the R state) and, when JAC, FVMCC_ComputeRhsJacob.cxx:240-317: the inner
 // state is perturbed, the ghost state is rebuilt by the boundary condition, both sides are re-extrapolated, and
 // resFactor * dF/dU_L goes to the boundary block of the face (added to the diagonal by DiagGather).
-template <int D, bool JAC>
-struct BoundaryFaceK {   // idx over boundary faces
+template <int D, bool JAC, int DV = 0>
+struct BoundaryFaceK {   // idx over boundary faces; DV = 0 DiamondVolume, 1 Corrected
   Dev d; Cfg c;
   CFB_HD void operator()(int g) const {
     constexpr int Q = D + 2;
@@ -638,8 +648,18 @@ struct BoundaryFaceK {   // idx over boundary faces
       P::side(c, vL, w.n, a);
       P::side(c, vR, w.n, b);
       double ucL, ucR, ucD;
-      w.baseFlux(d, c, sL, sR, a, b, hasDiff, flux, ucL, ucR, ucD);
+      w.baseFlux(d, c, sL, sR, a, b, hasDiff && DV == 0, flux, ucL, ucR, ucD);
       d.ucL[f] = ucL; d.ucR[f] = ucR; d.ucD[f] = ucD;
+    }
+    CorrectedWork<D> cw;
+    if (DV == 1 && hasDiff) {
+      cw.setup(d, c, f, L, R, true, w.n, w.area);
+      cw.boundaryGrads(d, g, sL, sR);
+      double dflux[Q];
+      cw.diffFlux(c, cw.grad, dflux);
+#pragma unroll
+      for (int v = 0; v < Q; ++v) flux[v] -= dflux[v];    // FVMCC_ComputeRHS.cxx:260-276
+      d.ucD[f] = cw.diffUpdateCoeff(c);
     }
 #pragma unroll
     for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = flux[v];
@@ -669,7 +689,13 @@ struct BoundaryFaceK {   // idx over boundary faces
       }
 #pragma unroll
       for (int v = 0; v < Q; ++v) pf[v] *= w.area;
-      if (hasDiff) {
+      if (DV == 1 && hasDiff) {
+        cw.boundaryGrads(d, g, sLp, sRp);
+        double dflux[Q];
+        cw.diffFlux(c, cw.grad, dflux);
+#pragma unroll
+        for (int v = 0; v < Q; ++v) pf[v] -= dflux[v];
+      } else if (hasDiff) {
         w.setCellStates(sLp, sRp);
         w.allGrads();
         double dflux[Q];

@@ -32,6 +32,7 @@ struct Dev {
   const int* lsqPtr; const int* lsqNbr;            // per-cell neighbour list in the reference's edge order
   const int* nodeNbrPtr; const int* nodeNbr; const double* nodeW;
   const double* cvol; const uint8_t* cvSign; const int* faceBC;
+  const int* bndStPtr; const int* bndSt;           // Corrected2D/3D: gradient stencil of each boundary face (CSR over ghosts)
   const uint8_t* updatable;
   const uint8_t* cellActive;  // cell touches at least one face with an updatable side
   const BCond* bcs;
@@ -513,6 +514,30 @@ struct UpdateSolFwdEuler {   // idx over cells
       }
       const double t = d.rhs[(size_t)cell*Q + monitorVar]; // ComputeL2Norm.cxx:111-125 on the rhs socket
       sq = t*t;
+    }
+    d.updateCoeff[cell] = 0.0;
+    d.partial[cell] = sq;
+  }
+};
+
+// §8f-1: NewtonMethod StdUpdateSol.cxx:110-141,256 on the device: the solution increment dU of the linear solve sits in
+// the rhs socket; U += alpha[iEq]*dU for the updatable states, dU = 0 for the others, updateCoeff = 0; per-cell squared
+// dU[monitorVar] goes to `partial` for the ordered norm reduction (ComputeL2Norm.cxx:111-125 on the rhs socket).
+template <int D, class PH = Phys<D> >
+struct UpdateSolNewton {   // idx over cells
+  Dev d; double alpha[PH::Q]; int monitorVar;
+  CFB_HD void operator()(int cell) const {
+    constexpr int Q = PH::Q;
+    double sq = 0.;
+    if (!d.updatable[cell]) {
+      for (int v = 0; v < Q; ++v) d.rhs[(size_t)cell*Q + v] = 0.;
+    } else {
+#pragma unroll
+      for (int v = 0; v < Q; ++v) {
+        const double dU = d.rhs[(size_t)cell*Q + v];
+        d.U[(size_t)v*d.nStates + cell] += alpha[v]*dU;
+        if (v == monitorVar) sq = dU*dU;
+      }
     }
     d.updateCoeff[cell] = 0.0;
     d.partial[cell] = sq;

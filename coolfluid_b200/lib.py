@@ -46,14 +46,15 @@ class BsrStruct(C.Structure):    # cfb200_bsr
 ABI_SYMBOLS = [
     "abi_version", "device_count", "create", "destroy", "last_error", "set_mesh", "set_step", "set_states",
     "get_states", "set_past_states", "backup_past_states", "set_limiter", "set_update_coeff", "apply_bc",
-    "compute_rhs", "time_rhs", "update_sol_fwd_euler", "bsr_view", "bsr_pattern", "bsr_nnzb", "get_bsr_values",
+    "compute_rhs", "time_rhs", "update_sol_fwd_euler", "update_sol_newton", "bsr_view", "bsr_pattern", "bsr_nnzb",
+    "get_bsr_values",
     "export_csr", "get_field", "device_ptr", "status", "enable_timing", "last_timings", "stream",
     "nccl_unique_id", "comm_init", "set_halo", "halo_begin", "halo_exchange", "allreduce_sum",
     "mesh_build", "mesh_sizes", "mesh_get", "mesh_ptr", "mesh_view", "mesh_set_updatable", "mesh_free",
     "selftest_divsqrt",
 ]
 # symbols the engine part needs (a test-only host build of the kernel functors exports just these)
-ENGINE_SYMBOLS = ABI_SYMBOLS[2:28]
+ENGINE_SYMBOLS = ABI_SYMBOLS[2:29]
 
 _libs = {}
 
@@ -93,6 +94,7 @@ def load(path=None, prefix="cfb200_"):
     ns.compute_rhs.argtypes = [H, C.c_int, P_D, P_D]
     ns.time_rhs.argtypes = [H, P_D]
     ns.update_sol_fwd_euler.argtypes = [H, C.c_double, C.c_int, P_D]
+    ns.update_sol_newton.argtypes = [H, P_D, P_D, C.c_int, P_D]
     ns.bsr_view.argtypes = [H, C.POINTER(BsrStruct)]
     ns.bsr_pattern.argtypes = [H, P_I, P_I]
     ns.bsr_nnzb.argtypes = [H]; ns.bsr_nnzb.restype = C.c_int64
@@ -261,6 +263,14 @@ class Engine:
     def update_sol_fwd_euler(self, cfl, monitor_var=0):
         r = C.c_double()
         self._chk(self.L.update_sol_fwd_euler(self.h, cfl, monitor_var, C.byref(r)), "update_sol")
+        return r.value
+
+    def update_sol_newton(self, dU=None, alpha=None, monitor_var=0):
+        """StdUpdateSol on the device: U += alpha*dU (dU = None: the increment already in the device rhs buffer)."""
+        r = C.c_double()
+        pdu = None if dU is None else _pd(np.ascontiguousarray(dU, dtype=np.float64))
+        pal = None if alpha is None else _pd(np.ascontiguousarray(alpha, dtype=np.float64))
+        self._chk(self.L.update_sol_newton(self.h, pdu, pal, monitor_var, C.byref(r)), "update_sol_newton")
         return r.value
 
     def bsr_pattern(self):

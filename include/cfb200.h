@@ -66,6 +66,10 @@ typedef struct cfb200_bc {
   int32_t zeroGrad[CFB200_MAXEQ];   /* ZeroGradientFlags, FVMCC_ComputeRHS.cxx:186-188 */
 } cfb200_bc;
 
+/* DerivativeComputer of the diffusive flux: DiamondVolume2D/3D (DiamondVolume{2,3}DDerivative.cxx, the default) or
+ * Corrected2D/3D (CorrectedDerivative2D.cxx:91-430, CorrectedDerivative3D.cxx:54-176) */
+enum cfb200_derivative { CFB200_DV_DIAMOND = 0, CFB200_DV_CORRECTED = 1 };
+
 /* Everything ComputeRHS reads from the .CFcase and from SubSystemStatus (SURVEY.md §8b "Scalars crossing per call").
  * The per-call scalars (iter, residual, resFactor, cfl, computeJacobian) may be changed between calls with
  * cfb200_set_step. */
@@ -107,6 +111,8 @@ typedef struct cfb200_config {
   int32_t entropyFixID;     /* 0: "Roe" (RoeFlux.cxx); 1 | 2: "RoeEntropyFix" entropyFixID (RoeEntropyFixFlux.cxx:35,57-90) */
   double refSpeed;          /* MHD3DProjection.ConvTerm.refSpeed */
   double coeffSigmoid;      /* AUSMFlux.ci:64 coeffSigmoid (default 1e-8), analytic Jacobian only */
+  int32_t derivativeStrategy; /* cfb200_derivative: CellCenterFVM.Data.DerivativeStrategy (CellCenterFVMData.cxx:298) */
+  int32_t reserved0;
 } cfb200_config;
 
 /* Flat mesh data = the contents of the reference's sockets and connectivity tables (SURVEY.md §8b "Data ownership").
@@ -194,6 +200,14 @@ int cfb200_time_rhs(cfb200_handle* h, double* rhs /* or NULL */);
 /* replaces: ForwardEuler UpdateSol::execute + ComputeL2Norm (UpdateSol.cxx:83-193, ComputeL2Norm.cxx:81-143):
  * U += CFL/updateCoeff * rhs on the device, updateCoeff = 0, returns log10 L2 norm of dU[monitorVar] */
 int cfb200_update_sol_fwd_euler(cfb200_handle* h, double cfl, int monitorVar, double* log10Residual);
+
+/* replaces: NewtonMethod StdUpdateSol::execute + ComputeL2Norm (StdUpdateSol.cxx:110-141,256; NewtonIterator.cxx step):
+ * U += alpha[iEq] * dU for the updatable states, dU = 0 for the others, updateCoeff = 0; returns log10 L2 norm of
+ * dU[monitorVar].  dU [nCells*q] is the solution of the linear system in the rhs socket layout; NULL = the increment is
+ * already in the device rhs buffer (a device-side solver wrote it through cfb200_bsr_view's rhs pointer).
+ * alpha [q] = StdUpdateSol.Relaxation, NULL = 1. */
+int cfb200_update_sol_newton(cfb200_handle* h, const double* dU, const double* alpha, int monitorVar,
+                             double* log10Residual);
 
 /* device-resident results */
 int cfb200_bsr_view(cfb200_handle* h, cfb200_bsr* out);

@@ -292,6 +292,9 @@ public:
     double pn1[5][3], pn2[5][3];  // pyramid normals (rows 1..4 used) / tetra normals
     double n2d[4][2];
     double volume;
+    // Corrected{2,3}D derivative (CorrectedDerivative2D.hh:150-190)
+    double dr, eRLdotNN[3], oEminusNN[3][3];
+    int nCorr, corrStencil[128];   // _stencil of a boundary face (state indices)
   };
 
   double gradCoeff(int stateID, int iVar, const double* xq, const double* xs, const Outputs& o) const {
@@ -377,7 +380,143 @@ public:
   }
 
   // ---- diffusive flux (a14,a15): NSFlux.ci:59-156 with DiamondVolume{2,3}DDerivative
+  // ---- a15, second DerivativeComputer: CorrectedDerivative2D.cxx:91-430 / CorrectedDerivative3D.cxx:54-220 inside
+  // NSFlux.ci:59-156.  The face gradient is the mean of the two cell gradients (the least-squares uX/uY/uZ of the
+  // update variables, frozen during the perturbations) with its normal part replaced by the two-point difference:
+  //   grad = (vR - vL)/|xR - xL| * (e.n) n + (I - n n) 0.5 (gradL + gradR)
+  // On a boundary face gradR is a local least-squares gradient at the ghost centre over the left cell, the other ghosts
+  // of the left cell's stencil and those stencil cells that share a node with the face.
+  void diffusiveFluxCorrected(FaceCtx& x, const double* U, bool isPerturb, int iPerturbVar, Outputs& o, double* dflux) {
+    const int nb = mesh.faceNodePtr[x.f+1] - mesh.faceNodePtr[x.f];
+    const int32_t* fn = &mesh.faceNodes[mesh.faceNodePtr[x.f]];
+    const double* cL = &mesh.centres[(size_t)x.L*D];
+    const double* cR = &mesh.centres[(size_t)x.R*D];
+    if (!isPerturb) {
+      // computeControlVolume, CorrectedDerivative2D.cxx:262-331 (+ setControlVolumeStates :352-430)
+      if (x.isB) {
+        x.nCorr = 0;
+        x.corrStencil[x.nCorr++] = x.L;
+        for (int in = mesh.stencilPtr[x.L]; in < mesh.stencilPtr[x.L+1]; ++in) {
+          const int last = mesh.stencil[in];
+          bool take = false;
+          if (last >= mesh.nCells) take = (last != x.R);
+          else {
+            for (int j = 0; j < nb && !take; ++j)        // cell->containNode(face->getNode(iNode))
+              for (int k = mesh.nodeNbrPtr[fn[j]]; k < mesh.nodeNbrPtr[fn[j]+1]; ++k)
+                if (mesh.nodeNbr[k] == last) { take = true; break; }
+          }
+          if (take) {
+            if (x.nCorr >= 128) throw std::runtime_error("Corrected derivative: boundary stencil larger than 128");
+            x.corrStencil[x.nCorr++] = last;
+          }
+        }
+      }
+      x.dr = getDistance<D>(cL, cR);
+      double eRL[3] = {0., 0., 0.};
+      for (int k = 0; k < D; ++k) eRL[k] = (cR[k] - cL[k])/x.dr;
+      double eDotN = 0.0;
+      for (int k = 0; k < D; ++k) eDotN += eRL[k]*x.n[k];
+      for (int k = 0; k < D; ++k) x.eRLdotNN[k] = eDotN*x.n[k];
+      // computeOEminusNN, CorrectedDerivative2D.cxx:498-504, 3D.cxx:190-211
+      for (int a = 0; a < D; ++a)
+        for (int b = 0; b < D; ++b)
+          x.oEminusNN[a][b] = (a == b) ? 1.0 - x.n[a]*x.n[a] : -(x.n[std::min(a, b)]*x.n[std::max(a, b)]);
+      x.volume = x.isB ? mesh.volumes[x.L] : 0.5*(mesh.volumes[x.L] + mesh.volumes[x.R]);
+    }
+    // setGradientVars: values(i,j) = (*states[j])[i]; states = L, R, face nodes, boundary stencil
+    const double* sL = &U[(size_t)x.L*Q];
+    const double* sR = &U[(size_t)x.R*Q];
+    double grad[Q][3];
+    double uR[Q][3];
+    if (x.isB) {
+      // computeBoundaryGradients, CorrectedDerivative2D.cxx:155-257, 3D.cxx:88-176
+      double l11 = 0.0, l12 = 0.0, l13 = 0.0, l22 = 0.0, l23 = 0.0, l33 = 0.0;
+      double lf1[Q], lf2[Q], lf3[Q];
+      for (int i = 0; i < Q; ++i) { lf1[i] = 0.0; lf2[i] = 0.0; lf3[i] = 0.0; }
+      for (int in = 0; in < x.nCorr; ++in) {
+        const double* nodeLast = &mesh.centres[(size_t)x.corrStencil[in]*D];
+        const double deltaR = getDistance<D>(cR, nodeLast);
+        const double weight = 1.0/deltaR;
+        const double dx = weight*(nodeLast[0] - cR[0]);
+        const double dy = weight*(nodeLast[1] - cR[1]);
+        const double dz = (D == 3) ? weight*(nodeLast[D-1] - cR[D-1]) : 0.0;
+        l11 += dx*dx; l12 += dx*dy; l22 += dy*dy;
+        if (D == 3) { l13 += dx*dz; l23 += dy*dz; l33 += dz*dz; }
+        const double* sv = &U[(size_t)x.corrStencil[in]*Q];
+        for (int i = 0; i < Q; ++i) {
+          const double du = weight*(sv[i] - sR[i]);
+          lf1[i] += dx*du; lf2[i] += dy*du;
+          if (D == 3) lf3[i] += dz*du;
+        }
+      }
+      if (D == 2) {
+        const double invDet = 1./(l11*l22 - l12*l12);
+        for (int i = 0; i < Q; ++i) {
+          uR[i][0] = (l22*lf1[i] - l12*lf2[i])*invDet;
+          uR[i][1] = (l11*lf2[i] - l12*lf1[i])*invDet;
+          uR[i][2] = 0.;
+        }
+      } else {
+        const double det = (l11*l22*l33 - l11*l23*l23 - l12*l12*l33 + l12*l13*l23 + l13*l12*l23 - l13*l13*l22);
+        const double invDet = 1./det;
+        const double linv11 = l22*l33 - l23*l23, linv22 = l11*l33 - l13*l13, linv33 = l11*l22 - l12*l12;
+        const double linv12 = -(l12*l33 - l13*l23), linv13 = l12*l23 - l13*l22, linv23 = -(l11*l23 - l13*l12);
+        for (int i = 0; i < Q; ++i) {
+          uR[i][0] = (linv11*lf1[i] + linv12*lf2[i] + linv13*lf3[i])*invDet;
+          uR[i][1] = (linv12*lf1[i] + linv22*lf2[i] + linv23*lf3[i])*invDet;
+          uR[i][2] = (linv13*lf1[i] + linv23*lf2[i] + linv33*lf3[i])*invDet;
+        }
+      }
+    } else {
+      for (int i = 0; i < Q; ++i) {
+        uR[i][0] = o.uX[(size_t)x.R*Q + i]; uR[i][1] = o.uY[(size_t)x.R*Q + i];
+        uR[i][2] = (D == 3) ? o.uZ[(size_t)x.R*Q + i] : 0.;
+      }
+    }
+    for (int i = 0; i < Q; ++i) {
+      const double dv = (sR[i] - sL[i])/x.dr;
+      double gradLR[3];
+      gradLR[0] = 0.5*(o.uX[(size_t)x.L*Q + i] + uR[i][0]);
+      gradLR[1] = 0.5*(o.uY[(size_t)x.L*Q + i] + uR[i][1]);
+      gradLR[2] = (D == 3) ? 0.5*(o.uZ[(size_t)x.L*Q + i] + uR[i][2]) : 0.;
+      // correctGradient (CorrectedDerivative2D.hh:127-130): grad*_eRLdotNN + _oEminusNN*gradLR, the matrix-vector
+      // product accumulating from 0 (MatExprT.hh:356-363)
+      for (int a = 0; a < D; ++a) {
+        double res = 0.0;
+        for (int k = 0; k < D; ++k) res += x.oEminusNN[a][k]*gradLR[k];
+        grad[i][a] = dv*x.eRLdotNN[a] + res;
+      }
+      if (D == 2) grad[i][2] = 0.;
+    }
+    // computeAverageValues, CorrectedDerivative2D.cxx:335-349: mean of the nodal states of the face
+    double avState[Q];
+    const double invNbNodes = 1./static_cast<double>(nb);
+    for (int i = 0; i < Q; ++i) {
+      avState[i] = 0.0;
+      for (int j = 0; j < nb; ++j) avState[i] += invNbNodes*o.nstates[(size_t)fn[j]*Q + i];
+    }
+    bool useBackUp = false, setBackUp = false;
+    if (isPerturb && iPerturbVar != P::TID) useBackUp = true;
+    else if (!isPerturb) setBackUp = true;
+    double mu, lambda;
+    if (useBackUp || freezeCoeff) { mu = x.muBkp; lambda = x.lambdaBkp; }
+    else {
+      mu = P::dynViscosity(cfg, avState)*cfg.artDiffCoeff;
+      lambda = P::thermConductivity(cfg, mu);
+      if (setBackUp) { x.muBkp = mu; x.lambdaBkp = lambda; }
+    }
+    P::nsFluxUnit(cfg, avState, grad, x.n, mu, lambda, dflux);
+    for (int i = 0; i < Q; ++i) dflux[i] *= x.area;
+    if (!isPerturb) {
+      const double nu = mu/P::nsDensity(cfg, avState);
+      const double diffUpdateCoeff = nu*x.area*x.area/x.volume;
+      o.updateCoeff[x.L] += diffUpdateCoeff;
+      if (!x.isB) o.updateCoeff[x.R] += diffUpdateCoeff;
+    }
+  }
+
   void diffusiveFlux(FaceCtx& x, const double* U, bool isPerturb, int iPerturbVar, Outputs& o, double* dflux) {
+    if (cfg.derivativeStrategy == 1) { diffusiveFluxCorrected(x, U, isPerturb, iPerturbVar, o, dflux); return; }
     const int nb = mesh.faceNodePtr[x.f+1] - mesh.faceNodePtr[x.f];
     const int32_t* fn = &mesh.faceNodes[mesh.faceNodePtr[x.f]];
     const double* cL = &mesh.centres[(size_t)x.L*D];

@@ -83,6 +83,13 @@ void FVMCC_ComputeRHSB200::fillConfig(cfb200_config& c)
   const std::string lim = getMethodData().getLimiter()->getName();
   c.limiter = (lim.find("Venktn") == 0) ? CFB200_LIM_VENKTN : (lim == "BarthJesp" ? CFB200_LIM_BARTHJESP : CFB200_LIM_NONE);
   c.diffusive = getMethodData().getDiffusiveFluxComputer()->isNull() ? CFB200_DIFF_NONE : CFB200_DIFF_NS;
+  // CellCenterFVM.Data.DerivativeStrategy: DiamondVolume2D/3D (CellCenterFVMData.cxx:298 default) or Corrected2D/3D
+  const std::string deriv = getMethodData().getDerivativeComputer()->getName();
+  if (deriv == "Corrected2D" || deriv == "Corrected3D") c.derivativeStrategy = CFB200_DV_CORRECTED;
+  else if (deriv == "DiamondVolume2D" || deriv == "DiamondVolume3D" || c.diffusive == CFB200_DIFF_NONE)
+    c.derivativeStrategy = CFB200_DV_DIAMOND;
+  else c.derivativeStrategy = -1;      // CorrectedGG*, StateDiff, ...: cfb200_create answers CFB200_ERR_UNSUPPORTED
+  c.reserved0 = 0;
   const RealVector& refValues = PhysicalModelStack::getActive()->getImplementor()->getRefStateValues();
   for (CFuint i = 0; i < nbEqs; ++i) { c.refValues[i] = refValues[i]; c.magnitudeValues[i] = refValues[i]; }
   c.fdTol = 10e-7;                     // NumericalJacobian.cxx:31

@@ -186,6 +186,17 @@ CASES = {
     "mhd3d_hex_laxfried_barth": (lambda: meshgen.hex_box(4, 4, 3),
                                  lambda: mhd3d_cfg(flux=B.FS_LAXFRIED, limiter=B.LIM_BARTHJESP, res_factor=0.5),
                                  bcs_mhd3d, "mhd"),
+    # a15: the Corrected2D / Corrected3D derivative computer (what most reference test cases select) on every face type
+    "ns3d_hex_corrected": (lambda: meshgen.hex_box(6, 5, 4), lambda: ns3d_cfg(derivative="corrected"), bcs_ns3d, True),
+    "ns3d_tet_corrected_ausmplusup": (lambda: meshgen.tet_box(3, 3, 3),
+                                      lambda: ns3d_cfg(derivative="corrected", flux=B.FS_AUSMPLUSUP, mach_inf=0.35),
+                                      bcs_ns3d, True),
+    "ns2d_quad_corrected": (lambda: meshgen.quad_channel(10, 8), lambda: ns2d_cfg(derivative="corrected"), bcs_ns2d, True),
+    "ns2d_tri_corrected_fullstencil": (lambda: meshgen.quad_channel(10, 8, triangles=True),
+                                       lambda: ns2d_cfg(derivative="corrected", use_full_stencil=True, res_factor=0.5),
+                                       bcs_ns2d, True),
+    "ns3d_single_cell_corrected": (lambda: meshgen.hex_box(1, 1, 1, jitter=0.0), lambda: ns3d_cfg(derivative="corrected"),
+                                   bcs_ns3d, True),
     # single cell / single row edge cases
     "ns3d_single_cell": (lambda: meshgen.hex_box(1, 1, 1, jitter=0.0), ns3d_cfg, bcs_ns3d, True),
     "euler2d_single_row": (lambda: meshgen.quad_channel(5, 1), lambda: B.make_config(2, poly_rec=B.PR_LINEARLS,
@@ -247,3 +258,41 @@ def run_case(name, oracle, make_engine, updatable=None, limiter_init=None, cfg_m
     finally:
         e.close()
     return out
+
+
+def check_newton_update(engine_factory, build_mesh):
+    """StdUpdateSol (NewtonMethod/StdUpdateSol.cxx:110-141,256) through cfb200_update_sol_newton against numpy:
+    U += alpha*dU on the updatable states only, dU zeroed elsewhere, updateCoeff zeroed, log10 L2 norm of dU[monitorVar]
+    (ComputeL2Norm.cxx:111-143).  One multiplication and one addition per entry: bit-exact."""
+    from coolfluid_b200 import lib as cl
+    fm = build_mesh(meshgen.hex_box(6, 5, 4))
+    x = fm.centres.reshape(-1, 3)[:fm.nCells, 0]
+    fm.updatable = np.ascontiguousarray((x < 0.7).astype(np.uint8))
+    e = engine_factory(ns3d_cfg())
+    e.set_mesh(fm, bcs_ns3d())
+    U = init_state(fm, 5, True)[:fm.nCells*5]
+    e.set_states(U)
+    rng = np.random.RandomState(7)
+    dU = 1e-3*rng.standard_normal(fm.nCells*5)
+    alpha = np.array([1.0, 0.9, 0.8, 0.7, 0.5])
+    e.set_update_coeff(np.ones(fm.nCells))
+    res = e.update_sol_newton(dU, alpha, 4)
+    upd = fm.updatable.astype(bool)
+    ref = U.reshape(-1, 5).copy()
+    ref[upd] += alpha*dU.reshape(-1, 5)[upd]
+    assert np.array_equal(e.get_states().reshape(-1, 5), ref)
+    d4 = np.where(upd, dU.reshape(-1, 5)[:, 4], 0.0)
+    assert abs(res - np.log10(np.sqrt((d4*d4).sum()))) <= 1e-12
+    out = np.empty(fm.nCells)
+    e._chk(e.L.get_field(e.h, b"updateCoeff", out.ctypes.data_as(cl.P_D)), "get_field")
+    assert not out.any()
+    rhs = np.empty(fm.nCells*5)
+    e._chk(e.L.get_field(e.h, b"rhs", rhs.ctypes.data_as(cl.P_D)), "get_field")
+    assert np.array_equal(rhs.reshape(-1, 5), np.where(upd[:, None], dU.reshape(-1, 5), 0.0))
+    # the increment already on the device, unit relaxation
+    before = e.get_states()
+    e.update_sol_newton(None, None, 0)
+    after = before.reshape(-1, 5).copy()
+    after[upd] += dU.reshape(-1, 5)[upd]
+    assert np.array_equal(e.get_states().reshape(-1, 5), after)
+    e.close()

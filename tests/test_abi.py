@@ -58,4 +58,9 @@ def test_invalid_arguments(product_lib):
     assert product_lib.create(C.byref(cfg), 0, C.byref(h)) == 6
     cfg = B.make_config(2, flux=B.FS_AUSMPLUSUP)                  # AUSM+up needs machInf > 0 (AUSMPlusUpFlux.ci:55-57)
     assert product_lib.create(C.byref(cfg), 0, C.byref(h)) == 6
+    cfg = B.make_config(2, diffusive=B.DIFF_NS, update_var=B.UV_PVT, derivative="corrected")   # needs the LSQ gradients
+    assert product_lib.create(C.byref(cfg), 0, C.byref(h)) == 6
+    cfg = B.make_config(2, diffusive=B.DIFF_NS, update_var=B.UV_PVT, poly_rec=B.PR_LINEARLS)
+    cfg.derivativeStrategy = 3                                    # CorrectedGG / StateDiff: not implemented
+    assert product_lib.create(C.byref(cfg), 0, C.byref(h)) == 6
     assert product_lib.compute_rhs(None, 1, None, None) == 2

@@ -134,6 +134,10 @@ def test_forward_euler_history(oracle, product_lib):
     assert np.abs(np.array(hist) - ref.history).max() <= 1e-10
 
 
+def test_newton_update(product_lib):
+    cases.check_newton_update(_factory(product_lib), lambda em: cl.build_mesh(em, product_lib))
+
+
 def test_large_size_properties(product_lib):
     """At a size the oracle does not finish quickly: size-independent properties.  (i) determinism; (ii) block-row
     sums: every flux is added to L and subtracted from R, so over a mesh whose cells are all updatable the column

@@ -81,3 +81,8 @@ def test_bad_value_is_reported(oracle, hostsim_lib):
         e.compute_rhs()
     assert ei.value.code == 1
     e.close()
+
+
+def test_newton_update(hostsim_lib):
+    from oracle import binding as ob
+    cases.check_newton_update(_engine_factory(hostsim_lib), ob.build_mesh)
