@@ -104,6 +104,9 @@ CFB_HD void ghostState(const Cfg& c, const BCond& b, const double* nr /*area-wei
       ghost[Q-1] = inner[Q-1];
       break;
     }
+    case CFB200_BC_FARFIELD_EULER:        // FarFieldEuler2D.cxx:127-300, FarFieldEuler3D.cxx:62-196
+      P::farFieldGhost(c, nr, b.value, inner, ghost);
+      break;
     default:                              // CFB200_BC_MIRROR_EULER_CONS: MirrorEuler2D.cxx:56-94 / MirrorMHD3DProjection.cxx:56-96
       P::mirrorGhost(c, nr, inner, ghost);
       break;

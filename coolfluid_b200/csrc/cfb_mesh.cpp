@@ -562,6 +562,27 @@ void cfb200_mesh_set_updatable(cfb200_meshdata* M, const uint8_t* updatable) {
   std::memcpy(M->updatable.data(), updatable, M->updatable.size());
 }
 
+// Diamond control volumes of the faces of a flat mesh (DiamondVolume3DDerivative.cxx:413-563): what a caller that fills
+// cfb200_mesh from the reference's sockets cannot read there (they are private to the DerivativeComputer).
+void cfb200_mesh_diamond_volumes(const cfb200_mesh* m, double* cvol, uint8_t* cvSign) {
+  for (int f = 0; f < m->nFaces; ++f) { cvol[f] = 0.0; cvSign[f] = 0; }
+  if (m->dim != 3) return;
+  for (int f = 0; f < m->nFaces; ++f) {
+    const int nb = m->faceNodePtr[f+1] - m->faceNodePtr[f];
+    const int32_t* fn = &m->faceNodes[m->faceNodePtr[f]];
+    const double* cL = &m->centres[(size_t)m->faceL[f]*3];
+    const double* cR = &m->centres[(size_t)m->faceR[f]*3];
+    const double* x0 = &m->nodes[(size_t)fn[0]*3]; const double* x1 = &m->nodes[(size_t)fn[1]*3];
+    const double* x2 = &m->nodes[(size_t)fn[2]*3];
+    double v0, v1;
+    if (nb == 3) { v0 = tetraVol(x0, x1, x2, cL); v1 = tetraVol(x0, x1, x2, cR); }
+    else { const double* x3 = &m->nodes[(size_t)fn[3]*3]; v0 = pyramVol(x0, x1, x2, x3, cL); v1 = pyramVol(x0, x1, x2, x3, cR); }
+    if (v0 < 0.0) { cvSign[f] = 1; v0 = std::abs(v0); }
+    if (v1 < 0.0) v1 = std::abs(v1);
+    cvol[f] = v0 + v1;
+  }
+}
+
 void cfb200_mesh_free(cfb200_meshdata* M) { delete M; }
 
 } // extern "C"

@@ -54,6 +54,9 @@ struct MhdPhys {
     dg.V = di.V; dg.A = di.A; dg.p = di.p; dg.B = di.B; dg.phi = di.phi;
     stateFromPhysicalData(c, dg, ghost);
   }
+  static CFB_HD void farFieldGhost(const Cfg&, const double*, const double*, const double* inner, double* ghost) {
+    for (int i = 0; i < Q; ++i) ghost[i] = inner[i];         // FarFieldEuler is rejected for MHD at set_mesh
+  }
   static CFB_HD void physFlux(const Cfg& c, const MhdData& d, const double* n, double* f) {
     const double nx = n[0], ny = n[1], nz = n[2];
     const double rho = d.rho, u = d.v[0], v = d.v[1], w = d.v[2], Bx = d.b[0], By = d.b[1], Bz = d.b[2];

@@ -50,7 +50,7 @@ ABI_SYMBOLS = [
     "get_bsr_values",
     "export_csr", "get_field", "device_ptr", "status", "enable_timing", "last_timings", "stream",
     "nccl_unique_id", "comm_init", "set_halo", "halo_begin", "halo_exchange", "allreduce_sum",
-    "mesh_build", "mesh_sizes", "mesh_get", "mesh_ptr", "mesh_view", "mesh_set_updatable", "mesh_free",
+    "mesh_build", "mesh_sizes", "mesh_get", "mesh_ptr", "mesh_view", "mesh_set_updatable", "mesh_free", "mesh_diamond_volumes",
     "selftest_divsqrt",
 ]
 # symbols the engine part needs (a test-only host build of the kernel functors exports just these)
@@ -116,6 +116,7 @@ def load(path=None, prefix="cfb200_"):
         ns.mesh_view.argtypes = [C.c_void_p, C.POINTER(MeshStruct)]; ns.mesh_view.restype = None
         ns.mesh_set_updatable.argtypes = [C.c_void_p, P_U8]; ns.mesh_set_updatable.restype = None
         ns.mesh_free.argtypes = [C.c_void_p]; ns.mesh_free.restype = None
+        ns.mesh_diamond_volumes.argtypes = [C.POINTER(MeshStruct), P_D, P_U8]; ns.mesh_diamond_volumes.restype = None
         ns.nccl_unique_id.argtypes = [C.c_void_p]
         ns.comm_init.argtypes = [H, C.c_int, C.c_int, C.c_void_p]
         ns.set_halo.argtypes = [H, P_I, P_I, P_I, P_I, C.c_int32]

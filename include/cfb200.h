@@ -44,7 +44,9 @@ enum cfb200_bc_type {
   CFB200_BC_DIRICHLET = 1,         /* ghost[v] = 2*value[v]-inner[v] where mask[v]: SuperInlet.cxx:156-209 (constant Def),
                                       SubInletEulerPvtVT.ci:52-77, SubOutletEulerPvt.ci:36-51, NoSlipWallAdiabaticNSPvt.cxx:109-128 */
   CFB200_BC_MIRROR_VELOCITY = 2,   /* FiniteVolume/MirrorVelocity.cxx:71-111 */
-  CFB200_BC_MIRROR_EULER_CONS = 3  /* FiniteVolumeNavierStokes/MirrorEuler2D.cxx:56-94, MirrorEuler3D */
+  CFB200_BC_MIRROR_EULER_CONS = 3, /* FiniteVolumeNavierStokes/MirrorEuler2D.cxx:56-94, MirrorEuler3D */
+  CFB200_BC_FARFIELD_EULER = 4     /* FiniteVolumeNavierStokes/FarFieldEuler2D.cxx:127-300 (conservative variables),
+                                      FarFieldEuler3D.cxx:62-196 (Cons or Pvt): value = p, u, v, [w,] T at infinity */
 };
 
 enum cfb200_error {
@@ -265,6 +267,9 @@ const void* cfb200_mesh_ptr(const cfb200_meshdata* m, const char* name);
 void cfb200_mesh_view(const cfb200_meshdata* m, cfb200_mesh* out);
 void cfb200_mesh_set_updatable(cfb200_meshdata* m, const uint8_t* updatable);
 void cfb200_mesh_free(cfb200_meshdata* m);
+/* cvol / cvSign of a mesh assembled by the caller (DiamondVolume3DDerivative.cxx:413-563; zeros in 2D); the other
+ * fields of *m must be set */
+void cfb200_mesh_diamond_volumes(const cfb200_mesh* m, double* cvol /* [nFaces] */, uint8_t* cvSign /* [nFaces] */);
 
 #ifdef __cplusplus
 }

@@ -109,6 +109,70 @@ struct Phys {
     stateFromPhysicalDataCons(dg, ghost);
   }
 
+  // FarFieldEuler2D.cxx:127-300 / FarFieldEuler3D.cxx:62-196: the number of imposed quantities follows the normal
+  // Mach number of the inner state; inf = (p, u, v, [w,] T) at infinity (Pressure, Uinf, Vinf, Winf, Temperature).
+  // The 2D command leaves EulerTerm::T of the ghost data unset in two of its branches, so only its conservative form
+  // is a function of its inputs (Euler2DCons::computeStateFromPhysicalData does not read T); the 3D one sets T always.
+  static void farFieldGhost(const Config& cfg, const double* nr, const double* inf, const double* inner, double* ghost) {
+    if (D == 2 && cfg.updateVar != UV_CONS) throw std::runtime_error("FarFieldEuler2D: conservative variables only");
+    double n[3] = {0., 0., 0.};
+    double s2;
+    if (D == 2) s2 = nr[0]*nr[0] + nr[1]*nr[1]; else s2 = nr[0]*nr[0] + nr[1]*nr[1] + nr[2]*nr[2];
+    const double invFaceLength = 1./std::sqrt(s2);
+    for (int i = 0; i < D; ++i) n[i] = nr[i]*invFaceLength;
+    PData di, dg;
+    computePhysicalData(cfg, inner, di);
+    const double gamma = cfg.gamma;
+    const double gammaDivGammaMinus1 = gamma/(gamma - 1.0);
+    const double R = cfg.R;
+    const double pInf = inf[0], TInf = inf[D+1];
+    const double rho = di.rho, pInnerState = di.p;
+    double vn;
+    if (D == 2) vn = di.v[0]*n[0] + di.v[1]*n[1]; else vn = di.v[0]*n[0] + di.v[1]*n[1] + di.v[2]*n[2];
+    const double machInner = vn/di.A;
+    auto speed = [&](const PData& x) {
+      return (D == 2) ? std::sqrt(x.v[0]*x.v[0] + x.v[1]*x.v[1]) : std::sqrt(x.v[0]*x.v[0] + x.v[1]*x.v[1] + x.v[2]*x.v[2]);
+    };
+    auto finish = [&](bool setT) {
+      if (setT) dg.T = dg.p/(dg.rho*R);
+      if (cfg.updateVar == UV_CONS) stateFromPhysicalDataCons(dg, ghost);
+      else { ghost[0] = dg.p; for (int i = 0; i < D; ++i) ghost[1+i] = dg.v[i]; ghost[TID] = dg.T; }   // Euler3DPvt.ci:118-128
+    };
+    dg.v[2] = 0.;
+    if (machInner >= 1.0) {                                  // supersonic outlet
+      for (int i = 0; i < Q; ++i) ghost[i] = inner[i];
+    }
+    if (machInner <= -1.0) {                                 // supersonic inlet
+      const double rhoInf = pInf/(R*TInf);
+      dg.rho = 2.0*rhoInf - rho;
+      for (int i = 0; i < D; ++i) dg.v[i] = 2.0*inf[1+i] - di.v[i];
+      dg.p = 2.0*pInf - pInnerState;
+      dg.A = std::sqrt(gamma*dg.p/dg.rho);
+      dg.V = speed(dg);
+      dg.H = (gammaDivGammaMinus1*dg.p + 0.5*dg.rho*dg.V*dg.V)/dg.rho;
+      finish(D == 3);
+    }
+    if ((machInner < 1.0) && (machInner >= 0.0)) {           // subsonic outlet
+      dg.rho = di.rho;
+      for (int i = 0; i < D; ++i) dg.v[i] = di.v[i];
+      dg.V = di.V;
+      dg.p = 2.0*pInf - pInnerState;
+      dg.H = (gammaDivGammaMinus1*dg.p + 0.5*dg.rho*dg.V*dg.V)/dg.rho;
+      dg.A = std::sqrt(gamma*dg.p/dg.rho);
+      finish(D == 3);
+    }
+    if ((machInner > -1.0) && (machInner < 0.0)) {           // subsonic inlet
+      dg.rho = pInnerState/(R*TInf);
+      for (int i = 0; i < D; ++i) dg.v[i] = 2.0*inf[1+i] - di.v[i];
+      dg.V = speed(dg);
+      dg.p = pInnerState;
+      dg.H = (gammaDivGammaMinus1*dg.p + 0.5*dg.rho*dg.V*dg.V)/dg.rho;
+      dg.A = std::sqrt(gamma*dg.p/dg.rho);
+      dg.T = TInf;
+      finish(D == 3);
+    }
+  }
+
   // Euler2DVarSet.cxx:83-117, Euler3DVarSet.cxx:78-105
   static void convFlux(const PData& d, const double* n, double* f) {
     double un;
@@ -792,6 +856,9 @@ struct MhdPhys {
     const double B = d.B;
     s[7] = d.p/(c.gamma - 1.0) + 0.5*(rho*d.V*d.V + B*B);
     s[8] = d.phi;
+  }
+  static void farFieldGhost(const Config&, const double*, const double*, const double*, double*) {
+    throw std::runtime_error("FarFieldEuler on MHD3DProjection");
   }
   // FiniteVolumeMHD/MirrorMHD3DProjection.cxx:56-96
   static void mirrorGhost(const Config& c, const double* nr, const double* inner, double* ghost) {

@@ -57,6 +57,9 @@ public:
       case BC_MIRROR_EULER_CONS:       // MirrorEuler2D.cxx:56-94 / MirrorMHD3DProjection.cxx:56-96
         P::mirrorGhost(cfg, &mesh.normals[(size_t)f*D], inner, ghost);
         break;
+      case BC_FARFIELD_EULER:          // FarFieldEuler2D.cxx:127-300, FarFieldEuler3D.cxx:62-196
+        P::farFieldGhost(cfg, &mesh.normals[(size_t)f*D], b.value, inner, ghost);
+        break;
       default: throw std::runtime_error("unknown BC type");
     }
   }

@@ -1,4 +1,8 @@
 // See FVMCC_ComputeRHSB200.hh.  Written against the COOLFluiD API of /root/reference; not compiled here.
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <typeinfo>
 #include "FiniteVolumeB200/FiniteVolumeB200.hh"
 #include "FiniteVolumeB200/FVMCC_ComputeRHSB200.hh"
 #include "Framework/MethodCommandProvider.hh"
@@ -9,6 +13,11 @@
 #include "Common/PE.hh"
 #include "Common/BadValueException.hh"
 #include "NavierStokes/EulerTerm.hh"
+#include "Framework/NodalStatesExtrapolator.hh"
+#include "Framework/ConnectivityTable.hh"
+#include "MathTools/MathFunctions.hh"
+#include "Common/DemangledTypeID.hh"
+#include "FiniteVolume/FVMCC_BC.hh"
 
 using namespace std;
 using namespace COOLFluiD::Framework;
@@ -23,6 +32,13 @@ fvmcc_computeRhsJacobB200Provider("B200RhsJacob");
 MethodCommandProvider<FVMCC_ComputeRhsJacobAnalyticB200, CellCenterFVMData, FiniteVolumeB200Module>
 fvmcc_computeRhsJacobAnalyticB200Provider("B200RhsJacobAnalytic");
 
+std::vector<SafePtr<BaseDataSocketSink> > FVMCC_ComputeRHSB200::needsSockets()
+{
+  std::vector<SafePtr<BaseDataSocketSink> > result = FVMCC_ComputeRHS::needsSockets();
+  result.push_back(&socket_stencil);
+  return result;
+}
+
 void FVMCC_ComputeRHSB200::defineConfigOptions(Config::OptionList& options)
 {
   options.addConfigOption< CFint >("Device", "CUDA device ordinal (-1: rank % deviceCount).");
@@ -30,7 +46,7 @@ void FVMCC_ComputeRHSB200::defineConfigOptions(Config::OptionList& options)
 }
 
 FVMCC_ComputeRHSB200::FVMCC_ComputeRHSB200(const std::string& name) :
-  FVMCC_ComputeRHS(name), m_h(CFNULL)
+  FVMCC_ComputeRHS(name), socket_stencil("stencil"), m_h(CFNULL)
 {
   addConfigOptionsTo(this);
   m_device = -1;       setParameter("Device", &m_device);
@@ -108,14 +124,180 @@ void FVMCC_ComputeRHSB200::setup()
   uploadMesh();
 }
 
+// One cfb200_bc per boundary TRS.  Commands without parameters are recognised by their class; FarFieldEuler2D/3D by
+// class + its options.  The Dirichlet-type commands (SuperInlet with a constant Def, SubInletEulerPvtVT,
+// SubOutletEulerPvt, NoSlipWallAdiabaticNSPvt, SuperOutlet, ...) all set ghost = 2*value - inner on a subset of the
+// variables and copy the others, so mask and value are read off the command itself by applying it to a zero inner
+// state on one face of the TRS (ghost = 2*value exactly) and are then verified, bit for bit, against the command on
+// the face's real inner state.  Anything that fails the verification is reported as unsupported (type -1).
+cfb200_bc FVMCC_ComputeRHSB200::translateBC(FVMCC_BC* bc, GeometricEntity* probe, CFuint nEqs)
+{
+  cfb200_bc out;
+  std::memset(&out, 0, sizeof(out));
+  const std::vector<bool>& zg = *bc->getZeroGradientsFlags();
+  for (CFuint i = 0; i < nEqs && i < zg.size(); ++i) out.zeroGrad[i] = zg[i] ? 1 : 0;
+  const std::string cls = Common::demangle(typeid(*bc).name());
+  const auto has = [&](const char* name) { return cls.find(name) != std::string::npos; };
+  const auto opt = [&](const char* name) { return std::strtod(bc->getOption(name)->getValueAsString().c_str(), CFNULL); };
+  if (has("MirrorVelocity")) { out.type = CFB200_BC_MIRROR_VELOCITY; return out; }
+  if (has("MirrorEuler2D") || has("MirrorEuler3D") || has("MirrorMHD3DProjection")) {
+    out.type = CFB200_BC_MIRROR_EULER_CONS; return out;
+  }
+  if (has("FarFieldEuler2D") || has("FarFieldEuler3D")) {
+    // constant far field only (no Def functions, no interpolation file); the option strings carry the values
+    const CFuint dim = PhysicalModelStack::getActive()->getDim();
+    out.type = CFB200_BC_FARFIELD_EULER;
+    out.value[0] = opt("Pressure"); out.value[1] = opt("Uinf"); out.value[2] = opt("Vinf");
+    if (dim == 3) out.value[3] = opt("Winf");
+    out.value[dim + 1] = opt("Temperature");
+    return out;
+  }
+  out.type = -1;
+  if (probe == CFNULL) { out.type = CFB200_BC_SUPER_OUTLET; return out; }    // empty TRS on this rank
+  State& inner = *probe->getState(0);
+  State& ghost = *probe->getState(1);
+  const RealVector innerBkp = inner, ghostBkp = ghost;
+  inner = 0.;
+  bc->setGhostState(probe);
+  bool any = false;
+  for (CFuint i = 0; i < nEqs; ++i) {
+    out.mask[i] = (ghost[i] != 0.) ? 1 : 0;
+    out.value[i] = 0.5*ghost[i];
+    any = any || out.mask[i];
+  }
+  static_cast<RealVector&>(inner) = innerBkp;
+  bc->setGhostState(probe);
+  bool linear = true;
+  for (CFuint i = 0; i < nEqs; ++i) {
+    const CFreal expect = out.mask[i] ? 2.*out.value[i] - inner[i] : inner[i];
+    linear = linear && (ghost[i] == expect);
+  }
+  static_cast<RealVector&>(ghost) = ghostBkp;
+  if (linear) out.type = any ? CFB200_BC_DIRICHLET : CFB200_BC_SUPER_OUTLET;
+  return out;
+}
+
 void FVMCC_ComputeRHSB200::uploadMesh()
 {
-  // Flattens the sockets nodes, states/gstates coordinates, normals, faceAreas, volumes, stencil, the connectivity
-  // tables cellFaces / InnerFaces / boundary TRSs (in the order of FVMCC_ComputeRHS::execute's TRS loop), the nodal
-  // extrapolator's neighbour lists and weights, and State::isParUpdatable() into a cfb200_mesh (include/cfb200.h),
-  // one boundary-condition record per boundary TRS (type + values from the configured BC commands), then
-  //   check(cfb200_set_mesh(m_h, &mesh, nbBCs, bcs), "cfb200_set_mesh");
-  // Field-by-field mapping: INTEGRATION.md §3.
+  // Flattens the sockets and connectivity tables into a cfb200_mesh (include/cfb200.h; field-by-field mapping:
+  // INTEGRATION.md §3).  State-indexed arrays hold the cells first, then the ghost states.
+  const CFuint dim = PhysicalModelStack::getActive()->getDim();
+  DataHandle<State*, GLOBAL> states = socket_states.getDataHandle();
+  DataHandle<State*> gstates = socket_gstates.getDataHandle();
+  DataHandle<Node*, GLOBAL> nodes = socket_nodes.getDataHandle();
+  DataHandle<CFreal> normals = socket_normals.getDataHandle();
+  DataHandle<CFreal> faceAreas = socket_faceAreas.getDataHandle();
+  DataHandle<CFreal> volumes = socket_volumes.getDataHandle();
+  DataHandle<std::vector<State*> > stencil = socket_stencil.getDataHandle();
+  const CFuint nCells = states.size(), nGhosts = gstates.size(), nNodes = nodes.size();
+
+  std::vector<CFreal> xNodes(nNodes*dim), xStates((nCells + nGhosts)*dim), vol(nCells);
+  std::vector<uint8_t> updatable(nCells);
+  for (CFuint i = 0; i < nNodes; ++i)
+    for (CFuint k = 0; k < dim; ++k) xNodes[i*dim + k] = (*nodes[i])[k];
+  for (CFuint i = 0; i < nCells; ++i) {
+    for (CFuint k = 0; k < dim; ++k) xStates[i*dim + k] = states[i]->getCoordinates()[k];
+    vol[i] = volumes[i];
+    updatable[i] = states[i]->isParUpdatable() ? 1 : 0;
+  }
+  for (CFuint i = 0; i < nGhosts; ++i)
+    for (CFuint k = 0; k < dim; ++k) xStates[(nCells + i)*dim + k] = gstates[i]->getCoordinates()[k];
+  // a state pointer -> its index in the state-indexed arrays
+  const auto stateIndex = [&](const State* s) -> CFint {
+    return s->isGhost() ? (CFint)(nCells + s->getLocalID()) : (CFint)s->getLocalID();
+  };
+
+
+  // Faces in the order of the TRS loop of FVMCC_ComputeRHS::execute (FVMCC_ComputeRHS.cxx:148-300): InnerFaces, then
+  // every boundary TRS (FVMCC_MeshDataBuilder.cxx:91-124 creates them in that order).  normals / faceAreas are
+  // indexed by face ID in the sockets and by loop position in cfb200_mesh.
+  const CFuint nEqs = PhysicalModelStack::getActive()->getNbEq();
+  std::vector<CFint> faceL, faceR, faceNodePtr(1, 0), faceNodes, faceBC;
+  std::vector<CFreal> nrm, area;
+  std::map<CFuint, CFint> loopIndexOfFace;
+  std::vector<cfb200_bc> bcs;
+  CFint nInner = -1;
+  SafePtr<GeometricEntityPool<FaceCellTrsGeoBuilder> > geoBuilder = getMethodData().getFaceCellTrsGeoBuilder();
+  FaceCellTrsGeoBuilder::GeoData& geoData = geoBuilder->getDataGE();
+  SafePtr<CFMap<CFuint, FVMCC_BC*> > bcMap = getMethodData().getMapBC();
+  std::vector<SafePtr<TopologicalRegionSet> > trs = MeshDataStack::getActive()->getTrsList();
+  for (CFuint iTRS = 0; iTRS < trs.size(); ++iTRS) {
+    SafePtr<TopologicalRegionSet> currTrs = trs[iTRS];
+    if (currTrs->getName() == "PartitionFaces" || currTrs->getName() == "InnerCells") continue;
+    const bool isBFace = currTrs->hasTag("writable");
+    if (!isBFace && nInner >= 0) throw BadValueException(FromHere(), "B200: more than one interior face TRS");
+    if (isBFace && nInner < 0) throw BadValueException(FromHere(), "B200: a boundary TRS precedes InnerFaces");
+    CFint bcIndex = -1;
+    if (isBFace) {
+      FVMCC_BC* bc = bcMap->find(iTRS);
+      geoData.trs = currTrs; geoData.isBFace = true; geoData.idx = 0;
+      GeometricEntity* probe = (currTrs->getLocalNbGeoEnts() > 0) ? geoBuilder->buildGE() : CFNULL;
+      bcs.push_back(translateBC(bc, probe, nEqs));
+      if (probe != CFNULL) geoBuilder->releaseGE();
+      bcIndex = (CFint)bcs.size() - 1;
+    }
+    geoData.trs = currTrs;
+    geoData.isBFace = isBFace;
+    const CFuint nbTrsFaces = currTrs->getLocalNbGeoEnts();
+    for (CFuint iFace = 0; iFace < nbTrsFaces; ++iFace) {
+      geoData.idx = iFace;
+      GeometricEntity* face = geoBuilder->buildGE();
+      const CFuint faceID = face->getID();
+      loopIndexOfFace[faceID] = (CFint)faceL.size();
+      faceL.push_back(stateIndex(face->getState(0)));
+      faceR.push_back(stateIndex(face->getState(1)));
+      for (CFuint n = 0; n < face->nbNodes(); ++n) faceNodes.push_back((CFint)face->getNode(n)->getLocalID());
+      faceNodePtr.push_back((CFint)faceNodes.size());
+      for (CFuint k = 0; k < dim; ++k) nrm.push_back(normals[faceID*dim + k]);
+      area.push_back(faceAreas[faceID]);
+      faceBC.push_back(bcIndex);
+      geoBuilder->releaseGE();
+    }
+    if (!isBFace) nInner = (CFint)faceL.size();
+  }
+
+
+  // cellFaces (the limiter and the residual gather follow the cell's local face order), reconstruction stencil,
+  // nodal-extrapolation neighbours and weights (DistanceBasedExtrapolator.ci:105-125)
+  SafePtr<ConnectivityTable<CFuint> > cf = MeshDataStack::getActive()->getConnectivity("cellFaces");
+  std::vector<CFint> cellFacePtr(1, 0), cellFaces, stencilPtr(1, 0), stencilIdx, nodeNbrPtr(1, 0), nodeNbr;
+  std::vector<CFreal> nodeW;
+  for (CFuint c = 0; c < nCells; ++c) {
+    for (CFuint k = 0; k < cf->nbCols(c); ++k) cellFaces.push_back(loopIndexOfFace[(*cf)(c, k)]);
+    cellFacePtr.push_back((CFint)cellFaces.size());
+    for (CFuint k = 0; k < stencil[c].size(); ++k) stencilIdx.push_back(stateIndex(stencil[c][k]));
+    stencilPtr.push_back((CFint)stencilIdx.size());
+  }
+  SafePtr<NodalStatesExtrapolator<CellCenterFVMData> > nse = getMethodData().getNodalStatesExtrapolator();
+  for (CFuint n = 0; n < nNodes; ++n) {
+    const std::vector<State*>& nb = nse->getNodalStateNeighbors(n);
+    CFreal sumWeight = 0.0;
+    const size_t first = nodeW.size();
+    for (CFuint k = 0; k < nb.size(); ++k) {
+      nodeNbr.push_back(stateIndex(nb[k]));
+      const CFreal weight = 1./MathTools::MathFunctions::getDistance(nb[k]->getCoordinates(), *nodes[n]);
+      nodeW.push_back(weight);
+      sumWeight += weight;
+    }
+    for (size_t k = first; k < nodeW.size(); ++k) nodeW[k] /= sumWeight;
+    nodeNbrPtr.push_back((CFint)nodeNbr.size());
+  }
+
+  cfb200_mesh mesh;
+  mesh.dim = dim; mesh.nCells = nCells; mesh.nGhosts = nGhosts; mesh.nNodes = nNodes;
+  mesh.nFaces = (CFint)faceL.size(); mesh.nInner = nInner;
+  mesh.nodes = &xNodes[0]; mesh.centres = &xStates[0];
+  mesh.faceL = &faceL[0]; mesh.faceR = &faceR[0]; mesh.faceNodePtr = &faceNodePtr[0]; mesh.faceNodes = &faceNodes[0];
+  mesh.normals = &nrm[0]; mesh.areas = &area[0]; mesh.volumes = &vol[0];
+  mesh.cellFacePtr = &cellFacePtr[0]; mesh.cellFaces = &cellFaces[0];
+  mesh.stencilPtr = &stencilPtr[0]; mesh.stencil = &stencilIdx[0];
+  mesh.nodeNbrPtr = &nodeNbrPtr[0]; mesh.nodeNbr = &nodeNbr[0]; mesh.nodeW = &nodeW[0];
+  mesh.faceBC = &faceBC[0]; mesh.updatable = &updatable[0];
+  std::vector<CFreal> cvol(faceL.size());
+  std::vector<uint8_t> cvSign(faceL.size());
+  mesh.cvol = &cvol[0]; mesh.cvSign = &cvSign[0];
+  cfb200_mesh_diamond_volumes(&mesh, &cvol[0], &cvSign[0]);
+  check(cfb200_set_mesh(m_h, &mesh, (int)bcs.size(), bcs.empty() ? CFNULL : &bcs[0]), "cfb200_set_mesh");
 }
 
 void FVMCC_ComputeRHSB200::execute()

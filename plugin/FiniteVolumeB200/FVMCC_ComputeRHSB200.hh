@@ -24,15 +24,19 @@ public:
   virtual void setup();
   virtual void unsetup();
   virtual void execute();
+  /// FVMCC_ComputeRHS's sockets + the reconstruction stencil (socket "stencil", filled by the setup of LeastSquareP1)
+  virtual std::vector<Common::SafePtr<Framework::BaseDataSocketSink> > needsSockets();
 
 protected:
   /// 0 for "B200Rhs", 1 for "B200RhsJacob" (= NumJacob), 2 for "B200RhsJacobAnalytic" (= NumJacobAnalytic)
   virtual int withJacobian() const { return 0; }
   void fillConfig(cfb200_config& c);
   void uploadMesh();
+  cfb200_bc translateBC(FVMCC_BC* bc, Framework::GeometricEntity* probe, CFuint nEqs);
   void insertJacobian();
   void check(int rc, const char* what);
 
+  Framework::DataSocketSink<std::vector<Framework::State*> > socket_stencil;
   cfb200_handle* m_h;
   CFint m_device;          ///< option Device (-1: rank % device count, as CudaDeviceManager.cu:58)
   bool m_hostJacobian;     ///< option HostJacobian: copy the BSR back and MatSetValuesBlocked (CPU PETSc); else device view

@@ -17,6 +17,10 @@ def init_state(fm, q, pvt, seed=67890):
     n = fm.nCells
     U = np.zeros((n + fm.nGhosts, q))
     s = 1.0 + 0.05*np.sin(2*np.pi*x[:, 0])*np.cos(2*np.pi*x[:, 1]) + 0.01*rng.standard_normal(n)
+    fast = 1.0
+    if pvt in ("cons_fast", "pvt_fast"):       # normal Mach numbers beyond +-1 at the x boundaries (FarFieldEuler branches)
+        fast = 2.0 if pvt == "cons_fast" else 3.5
+        pvt = (pvt == "pvt_fast")
     if pvt == "mhd":
         # rho, rho V, B (dipole-like smooth field + uniform part), rho E, phi
         rho = s
@@ -30,14 +34,14 @@ def init_state(fm, q, pvt, seed=67890):
         U[:n, 8] = 0.01*np.sin(2*np.pi*x[:, 0])*np.sin(2*np.pi*x[:, 1])
     elif pvt:
         U[:n, 0] = s
-        U[:n, 1] = 0.4 + 0.05*np.cos(2*np.pi*x[:, 1])
+        U[:n, 1] = fast*(0.4 + 0.05*np.cos(2*np.pi*x[:, 1]))
         U[:n, 2] = 0.03*np.sin(2*np.pi*x[:, 0])
         if d == 3:
             U[:n, 3] = 0.02*np.sin(2*np.pi*x[:, 2])
         U[:n, q-1] = 1.0 + 0.05*np.cos(2*np.pi*x[:, 0]) + 0.01*rng.standard_normal(n)
     else:
         rho = s
-        u = 0.8 + 0.1*np.cos(2*np.pi*x[:, 1])
+        u = fast*(0.8 + 0.1*np.cos(2*np.pi*x[:, 1]))
         v = 0.05*np.sin(2*np.pi*x[:, 0])
         p = 1.0 + 0.05*np.cos(2*np.pi*x[:, 0])
         U[:n, 0] = rho; U[:n, 1] = rho*u; U[:n, 2] = rho*v
@@ -82,6 +86,14 @@ def bcs_euler2d():
 def bcs_euler3d():
     mir = B.make_bc(B.BC_MIRROR_EULER_CONS)
     return [B.make_bc(B.BC_SUPER_OUTLET)]*2 + [mir]*4
+
+
+def bcs_farfield(dim, pvt):
+    """FarFieldEuler2D / FarFieldEuler3D on every boundary: value = p, u, v, [w,] T at infinity."""
+    R = 1.0 if pvt else B.make_config(dim).R
+    vel = [0.4, 0.0, 0.0][:dim] if pvt else [0.8, 0.0, 0.0][:dim]
+    ff = B.make_bc(B.BC_FARFIELD_EULER, value=[1.0] + vel + [1.0/R])
+    return [ff]*(2*dim)
 
 
 def bcs_mhd3d():
@@ -197,6 +209,20 @@ CASES = {
                                        bcs_ns2d, True),
     "ns3d_single_cell_corrected": (lambda: meshgen.hex_box(1, 1, 1, jitter=0.0), lambda: ns3d_cfg(derivative="corrected"),
                                    bcs_ns3d, True),
+    # a16: FarFieldEuler2D (conservative) / FarFieldEuler3D (Cons, Pvt): subsonic in/outflow and, with the fast initial
+    # field, supersonic inflow at xmin and outflow at xmax
+    "euler2d_farfield_sub": (lambda: meshgen.quad_channel(12, 9),
+                             lambda: B.make_config(2, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, jacobian=True),
+                             lambda: bcs_farfield(2, False), False),
+    "euler2d_farfield_super": (lambda: meshgen.quad_channel(12, 9, triangles=True),
+                               lambda: B.make_config(2, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, jacobian=True),
+                               lambda: bcs_farfield(2, False), "cons_fast"),
+    "euler3d_farfield_cons_tet": (lambda: meshgen.tet_box(3, 3, 3),
+                                  lambda: B.make_config(3, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, jacobian=True),
+                                  lambda: bcs_farfield(3, False), "cons_fast"),
+    "ns3d_farfield_pvt_sub": (lambda: meshgen.hex_box(5, 4, 4), ns3d_cfg, lambda: bcs_farfield(3, True), True),
+    "ns3d_farfield_pvt_super": (lambda: meshgen.hex_box(5, 4, 4), lambda: ns3d_cfg(derivative="corrected"),
+                                lambda: bcs_farfield(3, True), "pvt_fast"),
     # single cell / single row edge cases
     "ns3d_single_cell": (lambda: meshgen.hex_box(1, 1, 1, jitter=0.0), ns3d_cfg, bcs_ns3d, True),
     "euler2d_single_row": (lambda: meshgen.quad_channel(5, 1), lambda: B.make_config(2, poly_rec=B.PR_LINEARLS,
@@ -221,7 +247,8 @@ def run_case(name, oracle, make_engine, updatable=None, limiter_init=None, cfg_m
     U = init_state(fm, q, pvt)
     jac = bool(cfg.computeJacobian)
     uc0 = 0.1*np.arange(fm.nCells, dtype=np.float64)/max(fm.nCells, 1)      # updateCoeff accumulates onto its input
-    r = oracle.compute(cfg, fm, bcs, U.copy(), jacobian=jac, limiter_init=limiter_init, update_coeff_init=uc0)
+    Ug = U.copy()                                  # the oracle fills the ghost states in place
+    r = oracle.compute(cfg, fm, bcs, Ug, jacobian=jac, limiter_init=limiter_init, update_coeff_init=uc0)
     assert r.status == 0
     e = make_engine(cfg)
     out = {}
@@ -238,7 +265,7 @@ def run_case(name, oracle, make_engine, updatable=None, limiter_init=None, cfg_m
             if f == "uZ" and fm.dim == 2:
                 continue
             out[f] = (e.field(f), getattr(r, f).copy())
-        out["gstates"] = (e.field("gstates"), None)
+        out["gstates"] = (e.field("gstates"), Ug[fm.nCells*q:].copy())
         if q == 9:
             out["divB"] = (e.field("divB"), r.divB.copy())      # a22
         if jac:

@@ -51,3 +51,18 @@ def test_bad_input_returns_null(product_lib):
                                cl._pi(em.cell_nodes), cl._pi(em.cell_shape), em.n_trs, cl._pi(em.trs_face_ptr),
                                cl._pi(bad), cl._pi(em.trs_face_node_ptr), cl._pi(em.trs_face_nodes))
     assert not h
+
+
+def test_diamond_volumes_of_a_caller_built_mesh(product_lib):
+    """cfb200_mesh_diamond_volumes (what the COOLFluiD plugin calls after flattening the sockets) reproduces the
+    cvol / cvSign of the mesh builder on hexahedra (pyramids) and tetrahedra, and gives zeros in 2D."""
+    import ctypes as C
+    for em in (meshgen.hex_box(5, 4, 3), meshgen.tet_box(3, 3, 2), meshgen.quad_channel(6, 4)):
+        fm = cl.build_mesh(em, product_lib)
+        ms = cl.mesh_struct(fm)
+        cvol = np.full(fm.nFaces, -1.0)
+        sign = np.full(fm.nFaces, 7, dtype=np.uint8)
+        product_lib.mesh_diamond_volumes(C.byref(ms), cl._pd(cvol), cl._pu8(sign))
+        assert np.array_equal(cvol, fm.cvol) and np.array_equal(sign, fm.cvSign)
+        if em.dim == 3:
+            assert (cvol > 0).all()
