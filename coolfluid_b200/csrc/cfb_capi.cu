@@ -181,11 +181,10 @@ struct CudaBackend {
     };
     // launch shape = resident 128-thread blocks per SM = warps per scheduler (each scheduler owns 16384 registers, so the
     // only register budgets that change occupancy are 255 / 168 / 128 per thread; measured on B200: 2 is fastest)
-    switch (minBlocks) {
-      case 3: go(k_staged<F, 128, 3>, 128); break;      // 12 warps, 168 registers
-      case 4: go(k_staged<F, 128, 4>, 128); break;      // 16 warps, 128 registers
-      default: go(k_staged<F, 128, 2>, 128); break;     //  8 warps, 255 registers
-    }
+    // (3 and 4 resident blocks = 168 / 128 registers were measured 17 % and more slower, DESIGN.md §4.2, and are no longer
+    // compiled: they tripled the build time of the face kernels)
+    (void)minBlocks;
+    go(k_staged<F, 128, 2>, 128);                       //  8 warps per SM, 255 registers
     CFB_CUDA(cudaGetLastError());
     if (ev) CFB_CUDA(cudaEventRecord(ev->b, stream));
   }

@@ -184,7 +184,7 @@ struct CentredBoundaryFaceK {   // idx over boundary faces
       double sLp[Q], sRp[Q];
 #pragma unroll
       for (int v = 0; v < Q; ++v) sLp[v] = (v == iVar) ? orig + eps : sL[v];
-      ghostState<D, PH>(c, bc, nr, sLp, sRp);
+      ghostState<D, PH>(d, g, c, bc, nr, sLp, sRp);
 #pragma unroll
       for (int v = 0; v < Q; ++v) { vL[v] = lin ? sLp[v] + gL[v] : sLp[v]; vR[v] = lin ? sRp[v] + gR[v] : sRp[v]; }
       typename PH::CSide a, b;

@@ -60,6 +60,8 @@ public:
   int nNonUpd = 0;
   bool meshSet = false, statesSet = false;
   int lastStatus = 0;
+  double* bcFaceVal = nullptr; uint8_t* bcFaceFlag = nullptr;      // device copies behind Dev::bcFaceVal / bcFaceFlag
+  std::vector<double> hBcFaceVal; std::vector<uint8_t> hBcFaceFlag; std::vector<int32_t> hGhostBC;
   int faceShape = 2;       // resident 128-thread blocks per SM the interior-face Jacobian kernel is compiled for
                            // (CudaBackend::launchStaged): 2 -> 255 registers, no spills: measured fastest on B200 (profiles/)
   // multi-GPU (cfb_halo.cuh): a state halo exchange may be in flight when computeRhs is called; the first nIndep
@@ -153,6 +155,7 @@ public:
     for (int f = ni; f < nf; ++f)
       if (m.faceBC[f] < 0 || m.faceBC[f] >= nbc) throw std::invalid_argument("boundary face without a boundary condition");
     d.bcs = upload(bcs, (size_t)nbc);
+    hGhostBC.assign(m.faceBC + ni, m.faceBC + nf);      // boundary-condition record of every ghost
 
     // cell -> faces sorted in loop order, R side flagged by bitwise not (gather order = reference face loop order)
     {
@@ -371,6 +374,27 @@ public:
     else if (cfg.dim == 2) bk.launch("timeRhs", TimeRhs<2>{d, cfg, doJac}, d.nCells, 128);
     else bk.launch("timeRhs", TimeRhs<3>{d, cfg, doJac}, d.nCells, 128);
     bk.sync();
+  }
+  // position-dependent Dirichlet data of one boundary-condition record: values[iFace*q + v] for the faces of that
+  // record in face-loop order; nullptr reverts the record to its constant
+  void setBcFaceValues(int bcIndex, const double* values) {
+    const int32_t* hostFaceBC = hGhostBC.data();
+    const int Q = q(), ng = d.nGhosts;
+    if (!bcFaceVal) {
+      bcFaceVal = dalloc<double>((size_t)Q*ng); bcFaceFlag = dalloc<uint8_t>(ng);
+      bk.memset(bcFaceVal, 0, sizeof(double)*Q*ng); bk.memset(bcFaceFlag, 0, ng);
+      hBcFaceVal.assign((size_t)Q*ng, 0.); hBcFaceFlag.assign(ng, 0);
+    }
+    int k = 0;
+    for (int g = 0; g < ng; ++g) {
+      if (hostFaceBC[g] != bcIndex) continue;
+      hBcFaceFlag[g] = values ? 1 : 0;
+      if (values) for (int v = 0; v < Q; ++v) hBcFaceVal[(size_t)v*ng + g] = values[(size_t)k*Q + v];
+      ++k;
+    }
+    bk.h2d(bcFaceVal, hBcFaceVal.data(), sizeof(double)*Q*ng);
+    bk.h2d(bcFaceFlag, hBcFaceFlag.data(), ng);
+    d.bcFaceVal = bcFaceVal; d.bcFaceFlag = bcFaceFlag;
   }
   double updateSolFwdEuler(double cfl, int monitorVar) {
     if (isMhd()) bk.launch("updateSol", UpdateSolFwdEuler<3, MhdPhys>{d, cfl, monitorVar}, d.nCells, 256);

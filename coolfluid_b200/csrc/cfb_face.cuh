@@ -676,7 +676,7 @@ struct BoundaryFaceK {   // idx over boundary faces; DV = 0 DiamondVolume, 1 Cor
       double sLp[Q], sRp[Q];
 #pragma unroll
       for (int v = 0; v < Q; ++v) sLp[v] = (v == iVar) ? orig + eps : sL[v];
-      ghostState<D>(c, bc, nr, sLp, sRp);
+      ghostState<D>(d, g, c, bc, nr, sLp, sRp);
       w.reconstruct(c, sLp, sRp, vL, vR);
       typename P::Side a, b;
       P::side(c, vL, w.n, a);

@@ -32,6 +32,8 @@ struct Dev {
   const int* lsqPtr; const int* lsqNbr;            // per-cell neighbour list in the reference's edge order
   const int* nodeNbrPtr; const int* nodeNbr; const double* nodeW;
   const double* cvol; const uint8_t* cvSign; const int* faceBC;
+  const double* bcFaceVal;    // [q][nGhosts] position-dependent Dirichlet data (cfb200_set_bc_face_values), or null
+  const uint8_t* bcFaceFlag;  // [nGhosts] 1 where bcFaceVal replaces BCond::value
   const int* bndStPtr; const int* bndSt;           // Corrected2D/3D: gradient stencil of each boundary face (CSR over ghosts)
   const uint8_t* updatable;
   const uint8_t* cellActive;  // cell touches at least one face with an updatable side
@@ -84,8 +86,10 @@ struct FaceCentres {   // idx over faces
 
 // ------------------------------------------------------------------------------------------------
 // a16: boundary conditions, FVMCC_BaseBC.ci:144-187 executeOnTrs -> setGhostState(face)
+// g = boundary face (ghost) index: position-dependent Dirichlet data, when set, replaces the constant of the record
+// (SuperInlet.cxx:156-209 evaluates its Def function at the boundary point of every face)
 template <int D, class PH = Phys<D> >
-CFB_HD void ghostState(const Cfg& c, const BCond& b, const double* nr /*area-weighted normal*/,
+CFB_HD void ghostState(const Dev& d, int g, const Cfg& c, const BCond& b, const double* nr /*area-weighted normal*/,
                        const double* inner, double* ghost) {
   constexpr int Q = PH::Q;
   typedef PH P;
@@ -94,7 +98,12 @@ CFB_HD void ghostState(const Cfg& c, const BCond& b, const double* nr /*area-wei
       for (int i = 0; i < Q; ++i) ghost[i] = inner[i];
       break;
     case CFB200_BC_DIRICHLET:
-      for (int i = 0; i < Q; ++i) ghost[i] = b.mask[i] ? (2.*b.value[i] - inner[i]) : inner[i];
+      if (d.bcFaceFlag && d.bcFaceFlag[g]) {
+        for (int i = 0; i < Q; ++i)
+          ghost[i] = b.mask[i] ? (2.*d.bcFaceVal[(size_t)i*d.nGhosts + g] - inner[i]) : inner[i];
+      } else {
+        for (int i = 0; i < Q; ++i) ghost[i] = b.mask[i] ? (2.*b.value[i] - inner[i]) : inner[i];
+      }
       break;
     case CFB200_BC_MIRROR_VELOCITY: {     // MirrorVelocity.cxx:71-111
       double vn = 0., area2 = 0.;
@@ -123,7 +132,7 @@ struct GhostFill {   // idx over boundary faces
     double inner[Q], ghost[Q], nr[D];
     for (int v = 0; v < Q; ++v) inner[v] = d.U[(size_t)v*d.nStates + L];
     for (int k = 0; k < D; ++k) nr[k] = d.normals[(size_t)k*d.nFaces + f];
-    ghostState<D, PH>(c, d.bcs[d.faceBC[f]], nr, inner, ghost);
+    ghostState<D, PH>(d, g, c, d.bcs[d.faceBC[f]], nr, inner, ghost);
     for (int v = 0; v < Q; ++v) d.U[(size_t)v*d.nStates + d.nCells + g] = ghost[v];
   }
 };

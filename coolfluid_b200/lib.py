@@ -45,7 +45,7 @@ class BsrStruct(C.Structure):    # cfb200_bsr
 # every symbol include/cfb200.h declares (tests check that the library exports all of them)
 ABI_SYMBOLS = [
     "abi_version", "device_count", "create", "destroy", "last_error", "set_mesh", "set_step", "set_states",
-    "get_states", "set_past_states", "backup_past_states", "set_limiter", "set_update_coeff", "apply_bc",
+    "get_states", "set_past_states", "set_bc_face_values", "backup_past_states", "set_limiter", "set_update_coeff", "apply_bc",
     "compute_rhs", "time_rhs", "update_sol_fwd_euler", "update_sol_newton", "bsr_view", "bsr_pattern", "bsr_nnzb",
     "get_bsr_values",
     "export_csr", "get_field", "device_ptr", "status", "enable_timing", "last_timings", "stream",
@@ -54,7 +54,7 @@ ABI_SYMBOLS = [
     "selftest_divsqrt",
 ]
 # symbols the engine part needs (a test-only host build of the kernel functors exports just these)
-ENGINE_SYMBOLS = ABI_SYMBOLS[2:29]
+ENGINE_SYMBOLS = ABI_SYMBOLS[2:30]
 
 _libs = {}
 
@@ -88,6 +88,7 @@ def load(path=None, prefix="cfb200_"):
     for f in (ns.set_states, ns.get_states, ns.set_past_states):
         f.argtypes = [H, P_D, C.c_int64]
     ns.backup_past_states.argtypes = [H]
+    ns.set_bc_face_values.argtypes = [H, C.c_int, P_D]
     ns.set_limiter.argtypes = [H, P_D]
     ns.set_update_coeff.argtypes = [H, P_D]
     ns.apply_bc.argtypes = [H]
@@ -233,6 +234,10 @@ class Engine:
     def set_limiter(self, lim):
         lim = np.ascontiguousarray(lim, dtype=np.float64).reshape(-1)
         self._chk(self.L.set_limiter(self.h, _pd(lim)), "set_limiter")
+
+    def set_bc_face_values(self, bc_index, values=None):
+        pv = None if values is None else _pd(np.ascontiguousarray(values, dtype=np.float64))
+        self._chk(self.L.set_bc_face_values(self.h, bc_index, pv), "set_bc_face_values")
 
     def set_update_coeff(self, uc=None):
         if uc is None:

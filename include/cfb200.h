@@ -182,6 +182,12 @@ int cfb200_get_states(cfb200_handle* h, double* U, int64_t nCells);
 /* pastStates socket (NewtonIterator::prepare) for the pseudo-time term */
 int cfb200_set_past_states(cfb200_handle* h, const double* U, int64_t nCells);
 int cfb200_backup_past_states(cfb200_handle* h);   /* device copy states -> pastStates */
+/* Position-dependent Dirichlet data (SuperInlet.cxx:156-209 evaluates its parsed Def function at the boundary point of
+ * every face; a time-dependent Def is re-sent before the evaluation): values[iFace*q + v] for the faces of boundary
+ * condition record bcIndex in face-loop order replace cfb200_bc::value of a CFB200_BC_DIRICHLET record (the mask stays);
+ * NULL reverts the record to its constant.  Call after cfb200_set_mesh. */
+int cfb200_set_bc_face_values(cfb200_handle* h, int bcIndex, const double* values);
+
 /* limiter / updateCoeff sockets are stateful across calls (historical limiter; updateCoeff is zeroed by the updater) */
 int cfb200_set_limiter(cfb200_handle* h, const double* limiter /* AoS [nCells][nEqs] */);
 int cfb200_set_update_coeff(cfb200_handle* h, const double* updateCoeff /* [nCells], NULL = zero */);

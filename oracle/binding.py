@@ -23,7 +23,7 @@ class MeshView(C.Structure):
                 ("faceNodes", P_I), ("normals", P_D), ("areas", P_D), ("volumes", P_D),
                 ("cellFacePtr", P_I), ("cellFaces", P_I), ("stencilPtr", P_I), ("stencil", P_I),
                 ("nodeNbrPtr", P_I), ("nodeNbr", P_I), ("nodeW", P_D), ("cvol", P_D), ("cvSign", P_U8),
-                ("faceBC", P_I), ("updatable", P_U8)]
+                ("faceBC", P_I), ("updatable", P_U8), ("bcFaceVal", P_D), ("bcFaceFlag", P_U8)]
 
 
 class Outputs(C.Structure):
@@ -129,7 +129,9 @@ def mesh_view(fm: FlatMesh) -> MeshView:
     mv = MeshView()
     mv.dim, mv.nCells, mv.nGhosts, mv.nNodes, mv.nFaces, mv.nInner = fm.dim, fm.nCells, fm.nGhosts, fm.nNodes, fm.nFaces, fm.nInner
     for name, _t in MeshView._fields_[6:]:
-        a = getattr(fm, name)
+        a = getattr(fm, name, None)
+        if a is None:                       # optional: bcFaceVal / bcFaceFlag
+            continue
         setattr(mv, name, pd(a) if a.dtype == np.float64 else (pi(a) if a.dtype == np.int32 else pu8(a)))
     return mv
 

@@ -42,9 +42,12 @@ public:
       case BC_SUPER_OUTLET:
         for (int i = 0; i < Q; ++i) ghost[i] = inner[i];
         break;
-      case BC_DIRICHLET:
-        for (int i = 0; i < Q; ++i) ghost[i] = b.mask[i] ? (2.*b.value[i] - inner[i]) : inner[i];
+      case BC_DIRICHLET: {
+        const int g = f - mesh.nInner;
+        const double* value = (mesh.bcFaceFlag && mesh.bcFaceFlag[g]) ? &mesh.bcFaceVal[(size_t)g*Q] : b.value;
+        for (int i = 0; i < Q; ++i) ghost[i] = b.mask[i] ? (2.*value[i] - inner[i]) : inner[i];
         break;
+      }
       case BC_MIRROR_VELOCITY: {       // MirrorVelocity.cxx:71-111 (velocity IDs = 1..D)
         const double* nr = &mesh.normals[(size_t)f*D];
         double vn = 0., area2 = 0.;

@@ -126,6 +126,10 @@ struct MeshView {
   const uint8_t* cvSign;    // [nFaces] _changeNormalSign
   const int32_t* faceBC;    // [nFaces] -1 inner, else index into the BC array
   const uint8_t* updatable; // [nCells] isParUpdatable
+  // position-dependent Dirichlet data (SuperInlet.cxx:156-209 with a parsed Def function evaluated at the boundary
+  // point of each face): when bcFaceFlag[ghost] is set, BC_DIRICHLET reads bcFaceVal[ghost*q + v] instead of BC::value
+  const double* bcFaceVal;    // [nGhosts*q] or NULL
+  const uint8_t* bcFaceFlag;  // [nGhosts] or NULL
 };
 
 } // namespace cfo

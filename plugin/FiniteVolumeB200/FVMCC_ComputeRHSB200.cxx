@@ -216,6 +216,8 @@ void FVMCC_ComputeRHSB200::uploadMesh()
   std::vector<CFreal> nrm, area;
   std::map<CFuint, CFint> loopIndexOfFace;
   std::vector<cfb200_bc> bcs;
+  std::map<CFint, std::vector<CFreal> > faceValues;      // per Dirichlet record: value[iFace*nEqs + v]
+  std::map<CFint, bool> positionDependent;
   CFint nInner = -1;
   SafePtr<GeometricEntityPool<FaceCellTrsGeoBuilder> > geoBuilder = getMethodData().getFaceCellTrsGeoBuilder();
   FaceCellTrsGeoBuilder::GeoData& geoData = geoBuilder->getDataGE();
@@ -251,6 +253,22 @@ void FVMCC_ComputeRHSB200::uploadMesh()
       for (CFuint k = 0; k < dim; ++k) nrm.push_back(normals[faceID*dim + k]);
       area.push_back(faceAreas[faceID]);
       faceBC.push_back(bcIndex);
+      if (isBFace && bcs[bcIndex].type == CFB200_BC_DIRICHLET) {
+        // value of the record at this face (a Def function of the position gives a different one per face):
+        // the command applied to a zero inner state leaves ghost = 2*value
+        State& inner = *face->getState(0);
+        State& ghost = *face->getState(1);
+        const RealVector innerBkp = inner, ghostBkp = ghost;
+        inner = 0.;
+        bcMap->find(iTRS)->setGhostState(face);
+        for (CFuint v = 0; v < nEqs; ++v) {
+          const CFreal value = 0.5*ghost[v];
+          faceValues[bcIndex].push_back(value);
+          if (bcs[bcIndex].mask[v] && value != bcs[bcIndex].value[v]) positionDependent[bcIndex] = true;
+        }
+        static_cast<RealVector&>(inner) = innerBkp;
+        static_cast<RealVector&>(ghost) = ghostBkp;
+      }
       geoBuilder->releaseGE();
     }
     if (!isBFace) nInner = (CFint)faceL.size();
@@ -298,6 +316,8 @@ void FVMCC_ComputeRHSB200::uploadMesh()
   mesh.cvol = &cvol[0]; mesh.cvSign = &cvSign[0];
   cfb200_mesh_diamond_volumes(&mesh, &cvol[0], &cvSign[0]);
   check(cfb200_set_mesh(m_h, &mesh, (int)bcs.size(), bcs.empty() ? CFNULL : &bcs[0]), "cfb200_set_mesh");
+  for (std::map<CFint, bool>::const_iterator it = positionDependent.begin(); it != positionDependent.end(); ++it)
+    if (it->second) check(cfb200_set_bc_face_values(m_h, it->first, &faceValues[it->first][0]), "cfb200_set_bc_face_values");
 }
 
 void FVMCC_ComputeRHSB200::execute()

@@ -323,3 +323,49 @@ def check_newton_update(engine_factory, build_mesh):
     after[upd] += dU.reshape(-1, 5)[upd]
     assert np.array_equal(e.get_states().reshape(-1, 5), after)
     e.close()
+
+
+def check_bc_face_values(oracle, engine_factory):
+    """Position-dependent SuperInlet (Def functions of x, y, z evaluated at the boundary point of every face,
+    SuperInlet.cxx:156-209): per-face Dirichlet data through cfb200_set_bc_face_values against the oracle, with the
+    FD Jacobian (the boundary blocks re-apply the BC on the perturbed inner state)."""
+    fm = oracle.build_mesh(meshgen.hex_box(5, 4, 4))
+    cfg = ns3d_cfg()
+    bcs = bcs_ns3d()
+    q = 5
+    # boundary point of each face of record 0 (the inlet): 0.5*(inner centre + ghost centre)
+    gb = fm.faceBC[fm.nInner:]
+    faces = np.nonzero(gb == 0)[0]
+    x = fm.centres.reshape(-1, 3)
+    xb = 0.5*(x[fm.faceL[fm.nInner + faces]] + x[fm.nCells + faces])
+    vals = np.zeros((len(faces), q))
+    vals[:, 1] = 0.4*(1.0 + 0.3*np.sin(2*np.pi*xb[:, 1])*np.cos(np.pi*xb[:, 2]))
+    vals[:, 2] = 0.02*xb[:, 1]
+    vals[:, 3] = -0.01*xb[:, 2]
+    vals[:, 4] = 1.0 + 0.05*xb[:, 1]*xb[:, 2]
+    fm.bcFaceVal = np.zeros(fm.nGhosts*q)
+    fm.bcFaceFlag = np.zeros(fm.nGhosts, dtype=np.uint8)
+    fm.bcFaceVal.reshape(-1, q)[faces] = vals
+    fm.bcFaceFlag[faces] = 1
+    U = init_state(fm, q, True)
+    Ug = U.copy()
+    r = oracle.compute(cfg, fm, bcs, Ug, jacobian=True)
+    e = engine_factory(cfg)
+    try:
+        e.set_mesh(fm, bcs)
+        e.set_bc_face_values(0, vals.reshape(-1))
+        e.set_states(U[:fm.nCells*q])
+        rhs, uc = e.compute_rhs()
+        assert np.array_equal(e.field("gstates"), Ug[fm.nCells*q:])
+        assert np.array_equal(rhs, r.rhs) and np.array_equal(uc, r.updateCoeff)
+        assert np.array_equal(e.bsr_values(), r.bsrVal)
+        # back to the constant of the record
+        e.set_bc_face_values(0, None)
+        e.set_update_coeff(None)
+        fm.bcFaceFlag[:] = 0
+        Ug2 = U.copy()
+        r2 = oracle.compute(cfg, fm, bcs, Ug2, jacobian=True)
+        rhs2, _ = e.compute_rhs()
+        assert np.array_equal(rhs2, r2.rhs) and not np.array_equal(rhs2, rhs)
+    finally:
+        e.close()

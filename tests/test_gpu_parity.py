@@ -134,6 +134,10 @@ def test_forward_euler_history(oracle, product_lib):
     assert np.abs(np.array(hist) - ref.history).max() <= 1e-10
 
 
+def test_position_dependent_inlet(oracle, product_lib):
+    cases.check_bc_face_values(oracle, _factory(product_lib))
+
+
 def test_newton_update(product_lib):
     cases.check_newton_update(_factory(product_lib), lambda em: cl.build_mesh(em, product_lib))
 

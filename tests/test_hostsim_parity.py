@@ -86,3 +86,7 @@ def test_bad_value_is_reported(oracle, hostsim_lib):
 def test_newton_update(hostsim_lib):
     from oracle import binding as ob
     cases.check_newton_update(_engine_factory(hostsim_lib), ob.build_mesh)
+
+
+def test_position_dependent_inlet(oracle, hostsim_lib):
+    cases.check_bc_face_values(oracle, _engine_factory(hostsim_lib))
