@@ -90,3 +90,16 @@ def test_newton_update(hostsim_lib):
 
 def test_position_dependent_inlet(oracle, hostsim_lib):
     cases.check_bc_face_values(oracle, _engine_factory(hostsim_lib))
+
+
+def test_set_step_cannot_change_the_derivative_strategy(oracle, hostsim_lib):
+    """The boundary gradient stencil of Corrected2D/3D is built at set_mesh: switching afterwards is refused."""
+    from coolfluid_b200 import meshgen
+    fm = oracle.build_mesh(meshgen.hex_box(3, 3, 2))
+    e = cl.Engine(cases.ns3d_cfg(), 0, lib=hostsim_lib)
+    e.set_mesh(fm, cases.bcs_ns3d())
+    with pytest.raises(cl.Cfb200Error) as ei:
+        e.set_step(cases.ns3d_cfg(derivative="corrected"))
+    assert ei.value.code == 2
+    e.set_step(cases.ns3d_cfg(gradient_factor=0.5, res_factor=0.3))       # per-step scalars may change
+    e.close()
