@@ -1,6 +1,7 @@
 // cfb200 — the product library: CUDA backend of cfb::Engine + the extern "C" surface of include/cfb200.h.
 // Compiled for sm_100a only (nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false).  There is no CPU
 // execution path in this library: without a usable CUDA device cfb200_create returns CFB200_ERR_NO_DEVICE.
+#include <type_traits>
 #include <cuda_runtime.h>
 #include <cstdio>
 #include <cstdlib>
@@ -89,6 +90,9 @@ __global__ void __launch_bounds__(256) k_block_sum(const double* __restrict__ x,
   if (threadIdx.x == 0) out[blockIdx.x] = s[0];
 }
 
+template <class F, class = void> struct HasMinB : std::false_type {};
+template <class F> struct HasMinB<F, std::void_t<decltype(F::MINB)> > : std::true_type {};
+
 struct CudaBackend {
   int dev = 0;
   cudaStream_t stream = nullptr;
@@ -152,10 +156,9 @@ struct CudaBackend {
       ev = &evs[nEv++]; ev->name = name;
       CFB_CUDA(cudaEventRecord(ev->a, stream));
     }
-    // bs encodes the launch shape: 256 -> 256 threads; 128 -> 128 threads, >= 2 blocks/SM (<= 255 registers);
-    // 1283 / 1284 -> 128 threads with >= 3 / 4 resident blocks per SM (<= 168 / 128 registers)
-    if (bs == 1283) k_run<F, 128, 3><<<(n + 127)/128, 128, 0, stream>>>(f, n);
-    else if (bs == 1284) k_run<F, 128, 4><<<(n + 127)/128, 128, 0, stream>>>(f, n);
+    // launch shape: a functor that declares `static constexpr int MINB = 4` runs as 128 threads with >= 4 resident
+    // blocks per SM (<= 128 registers); otherwise bs = 256 -> 256 threads, bs = 128 -> 128 threads, >= 2 blocks/SM
+    if constexpr (HasMinB<F>::value) k_run<F, 128, F::MINB><<<(n + 127)/128, 128, 0, stream>>>(f, n);
     else if (bs == 128) k_run<F, 128, 2><<<(n + 127)/128, 128, 0, stream>>>(f, n);
     else k_run<F, 256, 1><<<(n + 255)/256, 256, 0, stream>>>(f, n);
     CFB_CUDA(cudaGetLastError());

@@ -473,6 +473,7 @@ struct ZeroRows {   // idx over (non-updatable cell list) * GS
 // rhs -= (U - U_past) * diag * resFactor in SOLUTION variables, diagonal block += diag * dU/dP (numerical)
 template <int D, class PH = Phys<D> >
 struct TimeRhs {   // idx over cells
+  static constexpr int MINB = 4;   // 126-128 registers without spills: 16 resident warps per SM for a streaming kernel
   Dev d; Cfg c; int doJac;
   CFB_HD void operator()(int cell) const {
     constexpr int Q = PH::Q;
