@@ -250,6 +250,7 @@ struct NodalExtrapolate {
 // loop, so the value is the same).  Venktn2D.cxx:111-260, Venktn3D.cxx:44-190, BarthJesp.cxx:60-155.
 template <int D, class PH = Phys<D> >
 struct LimiterK {   // idx over cells
+  static constexpr int MINB = 6;   // 80 registers: measured 8 % faster than the 96 of the default shape (8 -> 64 registers spills)
   Dev d; Cfg c;
   CFB_HD void operator()(int cell) const {
     constexpr int Q = PH::Q;
