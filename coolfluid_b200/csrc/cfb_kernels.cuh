@@ -474,7 +474,8 @@ struct ZeroRows {   // idx over (non-updatable cell list) * GS
 // rhs -= (U - U_past) * diag * resFactor in SOLUTION variables, diagonal block += diag * dU/dP (numerical)
 template <int D, class PH = Phys<D> >
 struct TimeRhs {   // idx over cells
-  static constexpr int MINB = 4;   // 126-128 registers without spills: 16 resident warps per SM for a streaming kernel
+  // q = 4, 5: 106-126 registers without spills, 16 resident warps per SM; q = 9 is faster at the default shape (measured)
+  static constexpr int MINB = (PH::Q > 5) ? 2 : 4;
   Dev d; Cfg c; int doJac;
   CFB_HD void operator()(int cell) const {
     constexpr int Q = PH::Q;
