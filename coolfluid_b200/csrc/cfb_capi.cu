@@ -215,29 +215,29 @@ struct CudaBackend {
     if (ev) CFB_CUDA(cudaEventRecord(ev->b, stream));
   }
 
-  // sum of x[0..n) with a fixed reduction shape; x must have >= ceil(n/1024) doubles of scratch after position n
+  // sum of x[0..n) with a fixed reduction shape (run-to-run deterministic); the scratch behind x[n) is preallocated by
+  // the engine (Engine::setMesh: nCells + ceil(nCells/1024) + 1024 doubles), so no allocation happens per call
   double sumOrdered(double* x, int n) {
     if (n <= 0) return 0.;
     const int nb = (n + 1023)/1024;
-    double* out = x + n;                      // Engine allocates nCells + 1024 ... see below
+    double* out = x + n;
     std::vector<double> h;
     if (nb > 1024) {
       // two levels: reduce the block sums again
-      double* tmp = nullptr;
-      CFB_CUDA(cudaMalloc((void**)&tmp, sizeof(double)*(nb + (nb + 1023)/1024)));
-      k_block_sum<<<nb, 256, 0, stream>>>(x, tmp, n);
       const int nb2 = (nb + 1023)/1024;
-      k_block_sum<<<nb2, 256, 0, stream>>>(tmp, tmp + nb, nb);
+      double* out2 = out + nb;
+      k_block_sum<<<nb, 256, 0, stream>>>(x, out, n);
+      k_block_sum<<<nb2, 256, 0, stream>>>(out, out2, nb);
+      CFB_CUDA(cudaGetLastError());
       h.resize(nb2);
-      CFB_CUDA(cudaMemcpyAsync(h.data(), tmp + nb, sizeof(double)*nb2, cudaMemcpyDeviceToHost, stream));
-      CFB_CUDA(cudaStreamSynchronize(stream));
-      cudaFree(tmp);
+      CFB_CUDA(cudaMemcpyAsync(h.data(), out2, sizeof(double)*nb2, cudaMemcpyDeviceToHost, stream));
     } else {
       k_block_sum<<<nb, 256, 0, stream>>>(x, out, n);
+      CFB_CUDA(cudaGetLastError());
       h.resize(nb);
       CFB_CUDA(cudaMemcpyAsync(h.data(), out, sizeof(double)*nb, cudaMemcpyDeviceToHost, stream));
-      CFB_CUDA(cudaStreamSynchronize(stream));
     }
+    CFB_CUDA(cudaStreamSynchronize(stream));
     double s = 0.;
     for (double v : h) s += v;
     return s;
@@ -361,8 +361,7 @@ int cfb200_halo_exchange(cfb200_handle* h) {
     cfb::Halo* H = haloOf(h, false);
     if (!H) throw std::runtime_error("comm_init has not been called");
     haloBegin(e, *H);
-    e.haloWait();
-    e.haloPending = false;
+    e.joinHalo();
     e.bk.sync();
     return CFB200_OK;
   });

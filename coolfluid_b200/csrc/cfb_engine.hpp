@@ -14,6 +14,7 @@
 #include <algorithm>
 #include <stdexcept>
 #include <functional>
+#include <cstdlib>
 #include "cfb_kernels.cuh"
 
 namespace cfb {
@@ -62,6 +63,7 @@ public:
   int lastStatus = 0;
   double* bcFaceVal = nullptr; uint8_t* bcFaceFlag = nullptr;      // device copies behind Dev::bcFaceVal / bcFaceFlag
   std::vector<double> hBcFaceVal; std::vector<uint8_t> hBcFaceFlag; std::vector<int32_t> hGhostBC;
+  bool roePipeline = true; // false (CFB200_ROE_PIPELINE=0): the rolled, non-pipelined FD loop of the Roe families (A/B measurements)
   int faceShape = 2;       // resident 128-thread blocks per SM the interior-face Jacobian kernel is compiled for
                            // (CudaBackend::launchStaged): 2 -> 255 registers, no spills: measured fastest on B200 (profiles/)
   // multi-GPU (cfb_halo.cuh): a state halo exchange may be in flight when computeRhs is called; the first nIndep
@@ -69,11 +71,20 @@ public:
   int nIndep = 0;
   bool haloPending = false;
   std::function<void()> haloWait;
+  // every entry point that reads or writes U outside computeRhs joins an exchange that is still in flight first
+  void joinHalo() {
+    if (!haloPending) return;
+    haloPending = false;
+    if (haloWait) haloWait();
+  }
   std::vector<void*> owned;
   int* nonUpdCells = nullptr;
   std::vector<int32_t> hRowPtr, hColInd;
 
-  explicit Engine(const Cfg& c, int device) : cfg(c), bk(device) { std::memset(&d, 0, sizeof(d)); }
+  explicit Engine(const Cfg& c, int device) : cfg(c), bk(device) {
+    std::memset(&d, 0, sizeof(d));
+    if (const char* v = std::getenv("CFB200_ROE_PIPELINE")) roePipeline = (std::atoi(v) != 0);
+  }
   ~Engine() { for (void* p : owned) bk.free(p); }
 
   template <class T> T* dalloc(size_t n) {
@@ -254,7 +265,7 @@ public:
     d.rhs = dalloc<double>((size_t)Q*nc);
     d.updateCoeff = dalloc<double>(nc);
     d.aos = dalloc<double>((size_t)Q*std::max(ns, nn));
-    d.partial = dalloc<double>((size_t)nc + 1024);
+    d.partial = dalloc<double>((size_t)nc + (size_t)(nc + 1023)/1024 + 2048);   // + both levels of sumOrdered's block sums
     d.status = dalloc<int>(1);
     d.bndBlocks = dalloc<double>((size_t)ng*Q*Q);
     d.bsrVal = nullptr;       // allocated on the first Jacobian evaluation
@@ -299,6 +310,14 @@ public:
     if (doJac && cfg.computeJacobian == 2) {
       bk.launchStaged("innerFaceJacAnalytic", AnalyticInnerFaceK<D>{d, cfg}, d.nInner, faceShape);
       bk.launch("boundaryFaceJac", BoundaryFaceK<D, true, 0>{d, cfg}, d.nGhosts, 128);
+    } else if (doJac && (fam == 0 || fam == 3) && roePipeline) {
+      // Roe families: update-variable set fixed at compile time, software-pipelined finite-difference loop
+      const bool cons = (cfg.updateVar == CFB200_UV_CONS);
+      if (fam == 0 && cons) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 0, DV, CFB200_UV_CONS>{d, cfg}, d.nInner, faceShape);
+      else if (fam == 0) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 0, DV, CFB200_UV_PVT>{d, cfg}, d.nInner, faceShape);
+      else if (cons) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 3, DV, CFB200_UV_CONS>{d, cfg}, d.nInner, faceShape);
+      else bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 3, DV, CFB200_UV_PVT>{d, cfg}, d.nInner, faceShape);
+      bk.launch("boundaryFaceJac", BoundaryFaceK<D, true, DV>{d, cfg}, d.nGhosts, 128);
     } else if (doJac) {
       if (fam == 0) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 0, DV>{d, cfg}, d.nInner, faceShape);
       else if (fam == 1) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 1, DV>{d, cfg}, d.nInner, faceShape);
@@ -327,8 +346,7 @@ public:
         g0 = std::min(nIndep, d.nCells);
         bk.launch("gradientsInterior", Gradients<D, PH>{d, 0}, g0, 128);
       }
-      haloWait();                          // the engine's stream now waits for the unpacked overlap states
-      haloPending = false;
+      joinHalo();                          // the engine's stream now waits for the unpacked overlap states
     }
     if (applyBC) applyBC_<D, PH>();
     // initializeComputationRHS (FVMCC_ComputeRHS.cxx:690-705)

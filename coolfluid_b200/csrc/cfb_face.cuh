@@ -413,6 +413,140 @@ struct FaceWork {
     }
   }
 
+  // ---- Roe FD loop, software-pipelined (FS = 0 | 3 with the Jacobian) --------------------------------------------------
+  // One evaluation is a long dependent chain (state -> physical data -> Roe vector -> Roe average: seven divide / square
+  // root sequences) followed by a wide part (eigenvector matrices, the O(q^3) product).  With two resident warps per
+  // scheduler the chain cannot be hidden by other warps, so the loop body is arranged as
+  //     front(it + 1)  ||  back(it)
+  // in ONE basic block: the chain of the next perturbation has no dependence on the product of the current one and the
+  // instruction scheduler interleaves the two.  Same operations, same order inside each evaluation: bit-identical.
+  // What lives across iterations is parked in the thread's shared-memory staging area (entry k at stg[k*stride]):
+  //   [0, 2QQ) blocks | side L: s z f (un a) | side R: s z f (un a) | base flux (diffusive base flux before it = -1) | gL | gR
+  // both unperturbed sides are parked once, the perturbed one is rebuilt per iteration.
+  static constexpr int RP_NSIDE(bool efix) { return 3*Q + (efix ? 2 : 0); }
+  static constexpr int RP_STAGE(bool efix) { return 2*Q*Q + 2*RP_NSIDE(efix) + 3*Q; }
+  struct RoeHand { PData lin; double dU[Q], sumF[Q], eps, lc; bool ok; };   // front -> back
+  template <bool EFIX, int UV>
+  CFB_HD void roeFront(const Dev& d, const Cfg& c, int it, const double* vL, const double* vR, const double* stg,
+                       int stride, RoeHand& h) const {
+    constexpr int NS = RP_NSIDE(EFIX), OFF_SIDES = 2*Q*Q, OFF_G = 2*Q*Q + 2*NS + Q;
+    const int side = (it >= Q) ? 1 : 0;
+    const int iVar = it - side*Q;                  // -1: the base evaluation
+    const int iv = (iVar < 0) ? 0 : iVar;
+    const double orig = d.U[(size_t)iv*d.nStates + (side ? R : L)];
+    const double gp = stg[(size_t)(OFF_G + side*Q + iv)*stride];
+    const double eps = fdEps(c, iv, orig);
+    const double pv = orig + eps;
+    const double pvr = (c.polyRec == CFB200_PR_CONSTANT) ? pv : pv + gp;
+    double vp[Q];
+#pragma unroll
+    for (int v = 0; v < Q; ++v) vp[v] = dsel(v == iVar, pvr, dsel(side != 0, vR[v], vL[v]));
+    typename P::SideLite p;
+    P::template sideLiteT<UV>(c, vp, n, p);
+    const double* fx = stg + (size_t)(OFF_SIDES + (1 - side)*NS)*stride;     // the unperturbed other side
+    {
+      double fz[Q];
+#pragma unroll
+      for (int k = 0; k < Q; ++k) fz[k] = fx[(size_t)(Q + k)*stride];
+      h.ok = P::linearize(c, p.z, fz, h.lin);
+    }
+#pragma unroll
+    for (int k = 0; k < Q; ++k) {
+      const double fsk = fx[(size_t)k*stride];                 // dU = sR - sL: the operands are selected, not the result
+      h.dU[k] = dsel(side == 0, fsk, p.s[k]) - dsel(side == 0, p.s[k], fsk);
+    }
+#pragma unroll
+    for (int i = 0; i < Q; ++i) h.sumF[i] = p.f[i] + fx[(size_t)(2*Q + i)*stride];
+    h.lc = 0.;
+    if constexpr (EFIX) h.lc = P::lambdaCorrOf(p.un, p.A, fx[(size_t)(3*Q)*stride], fx[(size_t)(3*Q + 1)*stride]);
+    h.eps = eps;
+  }
+  template <bool EFIX>
+  CFB_HD void roeBack(const Dev& d, const Cfg& c, int it, const RoeHand& h, bool hasDiff, double* stg, int stride) const {
+    constexpr int NS = RP_NSIDE(EFIX), OFF_FLUX = 2*Q*Q + 2*NS;
+    double Lm[Q*Q];
+    typename P::RCoef rc;
+    if constexpr (EFIX) P::leftScaled(c, h.lin, n, Lm, rc, c.entropyFixID, h.lc); else P::leftScaled(c, h.lin, n, Lm, rc);
+    const double kred = c.diffRedCoeff;
+    double pf[Q];
+#pragma unroll
+    for (int i = 0; i < Q; ++i) {
+      double Ri[Q];
+      P::rightRow(rc, i, Ri);
+      double res = 0.;
+#pragma unroll
+      for (int k = 0; k < Q; ++k) {
+        double m = 0.;
+#pragma unroll
+        for (int mm = 0; mm < Q; ++mm) m += Ri[mm]*Lm[mm*Q+k];
+        res += (kred*m)*h.dU[k];
+      }
+      pf[i] = 0.5*(h.sumF[i] - res);
+    }
+    if (!h.ok) *d.status = CFB200_ERR_BAD_VALUE;
+#pragma unroll
+    for (int v = 0; v < Q; ++v) pf[v] = dsel(h.ok, pf[v], 0.);
+    double* fluxS = stg + (size_t)OFF_FLUX*stride;
+    const int side = (it >= Q) ? 1 : 0;
+    const int iVar = it - side*Q;
+    if (it < 0) {
+#pragma unroll
+      for (int v = 0; v < Q; ++v) {
+        double x = pf[v]*area;                                   // FVMCC_FluxSplitter.hh:79-83
+        const double dfl = fluxS[(size_t)v*stride];              // base diffusive flux, parked here by the caller
+        x = hasDiff ? x - dfl : x;                               // FVMCC_ComputeRHS.cxx:260-276
+        fluxS[(size_t)v*stride] = x;
+        d.faceFlux[(size_t)v*d.nFaces + f] = x;
+      }
+    } else {
+      double* blk = stg + (size_t)(side*Q*Q + iVar)*stride;      // column iVar of block(R,L) (side 0) / block(L,R) (side 1)
+      const double invEps = ddiv(1., h.eps);
+      const double rf = c.resFactor;
+#pragma unroll
+      for (int v = 0; v < Q; ++v) {
+        double x = pf[v]*area;
+        const double dfl = blk[(size_t)v*Q*stride];              // perturbed diffusive flux staged by innerDiffusive
+        x = hasDiff ? x - dfl : x;
+        double fd = (x - fluxS[(size_t)v*stride])*invEps;
+        fd *= rf;                                                // what row L receives (upFactor[0])
+        blk[(size_t)v*Q*stride] = side ? fd : fd*(-1.0);         // block(R,L) is what row R receives: upFactor[1] = -1 times that
+      }
+    }
+  }
+  template <bool EFIX, int UV>
+  CFB_HD void innerConvectiveRoePipelined(const Dev& d, const Cfg& c, const double* vL, const double* vR, bool hasDiff,
+                                          const double* dfluxBase, double* stg, int stride) const {
+    constexpr int NS = RP_NSIDE(EFIX), OFF_SIDES = 2*Q*Q, OFF_FLUX = 2*Q*Q + 2*NS, OFF_G = OFF_FLUX + Q;
+#pragma unroll
+    for (int v = 0; v < Q; ++v) {
+      stg[(size_t)(OFF_FLUX + v)*stride] = dfluxBase[v];
+      stg[(size_t)(OFF_G + v)*stride] = gL[v];
+      stg[(size_t)(OFF_G + Q + v)*stride] = gR[v];
+    }
+#pragma unroll 1
+    for (int sd = 0; sd < 2; ++sd) {
+      double vF[Q];
+#pragma unroll
+      for (int v = 0; v < Q; ++v) vF[v] = sd ? vR[v] : vL[v];
+      typename P::SideLite fixed;
+      P::template sideLiteT<UV>(c, vF, n, fixed);
+      double* fx = stg + (size_t)(OFF_SIDES + sd*NS)*stride;
+#pragma unroll
+      for (int v = 0; v < Q; ++v) { fx[(size_t)v*stride] = fixed.s[v]; fx[(size_t)(Q + v)*stride] = fixed.z[v]; fx[(size_t)(2*Q + v)*stride] = fixed.f[v]; }
+      if constexpr (EFIX) { fx[(size_t)(3*Q)*stride] = fixed.un; fx[(size_t)(3*Q + 1)*stride] = fixed.A; }
+    }
+    RoeHand cur;
+    roeFront<EFIX, UV>(d, c, -1, vL, vR, stg, stride, cur);
+#pragma unroll 1
+    for (int it = -1; it < 2*Q; ++it) {
+      RoeHand nxt;
+      const int itn = (it + 1 < 2*Q) ? it + 1 : it;      // the last iteration has no successor: its front half is recomputed and dropped
+      roeFront<EFIX, UV>(d, c, itn, vL, vR, stg, stride, nxt);
+      roeBack<EFIX>(d, c, it, cur, hasDiff, stg, stride);
+      cur = nxt;
+    }
+  }
+
   // a18 (boundary-kernel helpers, kept per side): FVMCC_ComputeRhsJacob.cxx:126-236,321-365.
   // Done in two passes over the perturbed variables so that the diamond-volume working set (24 normals, 30 control
   // volume values, 15 gradients) and the Roe working set are never live in registers at the same time:
@@ -492,12 +626,16 @@ struct FaceWork {
 // these and are gathered by DiagGather.  One-sided updatable faces (partition overlap) use the same values
 // (FVMCC_ComputeRhsJacob.cxx:184-236: row idx receives (-1)^idx * resFactor * dF/dU); the blocks that land in
 // non-updatable rows are staging for DiagGather and are zeroed afterwards by ZeroRows.
-template <int D, bool JAC, int FS = 0, int DV = 0>
+// UV >= 0 (Roe families with the Jacobian): the update-variable set as a compile-time constant and the software-pipelined
+// finite-difference loop (FaceWork::innerConvectiveRoePipelined).
+template <int D, bool JAC, int FS = 0, int DV = 0, int UV = -1>
 struct InnerFaceK {   // idx over interior faces; FS = 0 Roe, 1 AUSM+ / AUSM+up, 2 LaxFried / HLL; DV = 0 DiamondVolume, 1 Corrected
   static constexpr int Q = D + 2;
   static constexpr int BLK = Q*Q;
   static constexpr int NOUT = 2*Q*Q;    // per-thread staging (shared memory, entry k at stg[k*stride]): block(R,L) | block(L,R)
-  static constexpr int STAGE = NOUT + 4*Q + ((FS == 3) ? 2 : 0);   // ... | fixed side s z f (un a) | base flux (loop-carried state of the FD loop)
+  static constexpr bool PIPE = JAC && (FS == 0 || FS == 3) && UV >= 0;
+  // ... | fixed side s z f (un a) | base flux (loop-carried state of the FD loop); PIPE: FaceWork::RP_STAGE
+  static constexpr int STAGE = PIPE ? FaceWork<D>::RP_STAGE(FS == 3) : NOUT + 4*Q + ((FS == 3) ? 2 : 0);
   Dev d; Cfg c;
   CFB_HD void operator()(int f) const { run(f, nullptr, 0); }
   CFB_HD double* out() const { return d.bsrVal; }
@@ -549,7 +687,8 @@ struct InnerFaceK {   // idx over interior faces; FS = 0 Roe, 1 AUSM+ / AUSM+up,
       }
     }
     d.ucD[f] = ucD;
-    w.template innerConvective<FS>(d, c, sL, sR, vL, vR, hasDiff, dfluxBase, JAC, stg, stride);
+    if constexpr (PIPE) w.template innerConvectiveRoePipelined<FS == 3, UV>(d, c, vL, vR, hasDiff, dfluxBase, stg, stride);
+    else w.template innerConvective<FS>(d, c, sL, sR, vL, vR, hasDiff, dfluxBase, JAC, stg, stride);
   }
 };
 

@@ -77,6 +77,7 @@ struct Halo {
 
   ~Halo() {
     cudaSetDevice(dev);
+    if (cs) cudaStreamSynchronize(cs);      // no NCCL / unpack kernel may still be using the buffers freed below
     if (comm) NcclApi::get().CommDestroy(comm);
     cudaFree(dSend); cudaFree(dRecv); cudaFree(sbuf); cudaFree(rbuf); cudaFree(red);
     if (packed) cudaEventDestroy(packed);

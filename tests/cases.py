@@ -9,6 +9,14 @@ def relerr(a, b):
     return float(np.abs(a - b).max()/(s if s > 0 else 1.0))
 
 
+def relerr_rows(a, b, width):
+    """Largest error relative to the max-abs of its own row (one cell's residual, one Jacobian block): the per-cell /
+    per-entry measure BASELINE.json's 1e-12 is stated in (SURVEY.md 8d parity gates)."""
+    a = np.asarray(a).reshape(-1, width); b = np.asarray(b).reshape(-1, width)
+    scale = np.maximum(np.abs(b).max(axis=1, keepdims=True), 1e-300)
+    return float((np.abs(a - b)/scale).max())
+
+
 def init_state(fm, q, pvt, seed=67890):
     """Smooth field + seeded noise, physically admissible (SURVEY.md §8d synthetic inputs)."""
     d = fm.dim

@@ -32,8 +32,8 @@ def oracle():
 def product_lib():
     """libcfb200.so; built here when nvcc is available, otherwise the prebuilt in-tree file is used."""
     from coolfluid_b200 import lib
-    if not os.path.exists(lib.LIB_PATH):
-        _make(os.path.join(ROOT, "coolfluid_b200", "csrc"))
+    from coolfluid_b200 import build
+    build.ensure()           # rebuilds when the sources changed since the last build: never a stale binary
     return lib.load()
 
 

@@ -25,7 +25,9 @@ import cases  # noqa: E402
 from coolfluid_b200 import meshgen, config as B  # noqa: E402
 from oracle import binding as ob  # noqa: E402
 
-WEDGE = "/root/reference/plugins/NavierStokes/testcases/Wedge/"
+# the reference's mesh of the case (plugins/NavierStokes/testcases/Wedge/wedge.thor, wedge.SP), committed beside this script
+# as a data fixture so that the GPU box (no /root/reference) can run the case
+WEDGE = HERE + "/"
 WEDGE_INLET = [1., 2.366431913, 0.0, 5.3]          # wedgeFVM.CFcase InField.Def / Inlet.Def
 
 

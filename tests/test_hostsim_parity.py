@@ -70,17 +70,18 @@ def test_stop_limiting(oracle, hostsim_lib):
 def test_bad_value_is_reported(oracle, hostsim_lib):
     """a^2 < 0 in the Roe linearisation -> CFB200_ERR_BAD_VALUE (BadValueException in the reference)."""
     from coolfluid_b200 import meshgen, config as B
-    fm = oracle.build_mesh(meshgen.quad_channel(4, 4))
-    cfg = B.make_config(2)
-    U = cases.init_state(fm, 4, False)
-    U[4*5 + 3] = -50.0          # negative total energy in cell 5
-    e = cl.Engine(cfg, 0, lib=hostsim_lib)
-    e.set_mesh(fm, cases.bcs_euler2d())
-    e.set_states(U[:fm.nCells*4])
-    with pytest.raises(cl.Cfb200Error) as ei:
-        e.compute_rhs()
-    assert ei.value.code == 1
-    e.close()
+    for jac in (False, True):       # the pipelined finite-difference loop carries the flag instead of branching
+        fm = oracle.build_mesh(meshgen.quad_channel(4, 4))
+        cfg = B.make_config(2, jacobian=jac)
+        U = cases.init_state(fm, 4, False)
+        U[4*5 + 3] = -50.0          # negative total energy in cell 5
+        e = cl.Engine(cfg, 0, lib=hostsim_lib)
+        e.set_mesh(fm, cases.bcs_euler2d())
+        e.set_states(U[:fm.nCells*4])
+        with pytest.raises(cl.Cfb200Error) as ei:
+            e.compute_rhs()
+        assert ei.value.code == 1
+        e.close()
 
 
 def test_newton_update(hostsim_lib):

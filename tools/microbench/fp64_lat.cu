@@ -43,6 +43,9 @@ int main() {
   run<1, 0>("DFMA", 8, d); run<1, 0>("DFMA", 16, d); run<1, 0>("DFMA", 32, d); run<1, 0>("DFMA", 64, d);
   run<2, 0>("DFMA", 8, d); run<2, 0>("DFMA", 16, d); run<4, 0>("DFMA", 8, d); run<4, 0>("DFMA", 16, d); run<4, 0>("DFMA", 32, d);
   run<8, 0>("DFMA", 8, d); run<8, 0>("DFMA", 16, d);
+  // no-FMA issue peak (the kernels are built with -fmad=false): DADD / DMUL with 8 independent chains, 16 and 32 warps per SM
+  run<8, 1>("DADD", 16, d); run<8, 1>("DADD", 32, d); run<8, 2>("DMUL", 16, d); run<8, 2>("DMUL", 32, d);
+  run<4, 1>("DADD", 8, d); run<4, 2>("DMUL", 8, d); run<2, 1>("DADD", 8, d); run<1, 1>("DADD", 8, d);
   run<1, 3>("DDIV", 4, d); run<1, 3>("DDIV", 8, d); run<1, 3>("DDIV", 16, d); run<4, 3>("DDIV", 8, d); run<4, 3>("DDIV", 16, d);
   return 0;
 }
