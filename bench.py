@@ -66,7 +66,7 @@ def flagship(n, workload="ns3d"):
     `mhd3d` = configs[3]: the same box with MHD3DProjection (q = 9), HLL, LSQ + Venkatakrishnan."""
     import cases
     from coolfluid_b200 import meshgen
-    em = meshgen.hex_box(n, n, n) if not workload.startswith("euler2d") else None
+    em = meshgen.hex_box(n, n, n, nz_total=n) if not workload.startswith("euler2d") else None
     if workload == "mhd3d":
         return em, cases.mhd3d_cfg(), cases.bcs_mhd3d()
     if workload.startswith("euler2d"):
@@ -99,37 +99,112 @@ WORKLOADS = {
 }
 
 
-def slab_partition(n, rank, world, workload):
-    """N > 1: rank r owns a slab of n^3 cells of an n x n x (n*world) box cut along z and carries the two overlap
-    layers of each interior side (LSQ needs 2: LeastSquareP1Setup.cxx:60-63).  The slab is generated locally; its cells
-    are renumbered [own cells that see no overlap cell | own cells next to the overlap | overlap cells] so that the
-    gradients of the first group overlap the state halo exchange; the halo lists pair this slab's two outermost own
-    layers with the neighbour's overlap layers (same (i, j, k) order on both sides).  Returns (ElementMesh, Partition)."""
+def slab_partition(n, rank, world, workload, box=None):
+    """N > 1: ONE global box of n x n x (n*world) cells (jitter = hash of the global node index: every rank generates
+    only its own slab, node for node a piece of that mesh), cut along z.  Rank r owns cell layers [r*n, (r+1)*n) and
+    carries the two overlap layers of each interior side (LSQ needs 2: LeastSquareP1Setup.cxx:60-63).  Local cells keep
+    the global order (so every gather of an updatable cell runs in the single-domain order); the cells whose gradients
+    may overlap the halo exchange are given as a list.  The cut planes appear as the slab's zmin / zmax TRSs: their inner
+    cells are not updatable, so they are never evaluated.  Returns (ElementMesh, Partition).
+    box = (nx, ny, layers per rank) overrides the cube (tests)."""
     from coolfluid_b200 import meshgen, partition
+    nx, ny, nzr = box if box is not None else (n, n, n)
     lo = 2 if rank > 0 else 0
     hi = 2 if rank < world - 1 else 0
-    K = n + lo + hi
-    em = meshgen.hex_box(n, n, K, lengths=(1.0, 1.0, K/float(n)), seed=12345 + rank)
-    nl = n*n
+    K = nzr + lo + hi
+    nzt = nzr*world
+    em = meshgen.hex_box(nx, ny, K, lengths=(1.0, 1.0*ny/nx, 1.0*nzt/nx), k0=rank*nzr - lo, nz_total=nzt)
+    nl = nx*ny
     k_of = np.arange(em.n_cells)//nl
-    own = (k_of >= lo) & (k_of < lo + n)
-    near = own & (((k_of == lo) & (lo > 0)) | ((k_of == lo + n - 1) & (hi > 0)))
-    group = np.where(own & ~near, 0, np.where(near, 1, 2))
-    perm = np.argsort(group, kind="stable").astype(np.int64)        # new -> old
-    inv = np.empty_like(perm); inv[perm] = np.arange(em.n_cells)    # old -> new
-    em.cell_nodes = np.ascontiguousarray(em.cell_nodes.reshape(-1, 8)[perm].reshape(-1))
-    em.trs_face_cell = np.ascontiguousarray(inv[em.trs_face_cell]).astype(em.trs_face_cell.dtype)
+    own = (k_of >= lo) & (k_of < lo + nzr)
+    near = own & (((k_of == lo) & (lo > 0)) | ((k_of == lo + nzr - 1) & (hi > 0)))
     p = partition.Partition()
     p.rank, p.nranks, p.em = rank, world, em
-    p.updatable = (group[perm] < 2).astype(np.uint8)
-    p.n_interior = int((group == 0).sum())
+    p.updatable = own.astype(np.uint8)
+    p.indep = np.nonzero(own & ~near)[0].astype(np.int32)
+    p.n_interior = len(p.indep)
     p.n_updatable = int(own.sum())
-    layer = lambda k0: inv[np.arange(k0*nl, (k0 + 2)*nl)].astype(np.int32)
+    p.cell_l2g = (np.arange(em.n_cells) + (rank*nzr - lo)*nl).astype(np.int64)
+    layer = lambda k0: np.arange(k0*nl, (k0 + 2)*nl).astype(np.int32)
     if lo:
         p.send[rank - 1] = layer(lo); p.recv[rank - 1] = layer(0)
     if hi:
-        p.send[rank + 1] = layer(lo + n - 2); p.recv[rank + 1] = layer(lo + n)
+        p.send[rank + 1] = layer(lo + nzr - 2); p.recv[rank + 1] = layer(lo + nzr)
     return em, p
+
+
+def multi_gpu_parity(rank, world, local_rank, L, dist, torch):
+    """Cross-rank correctness statement carried by every N > 1 bench line (untimed): a global 32 x 32 x (16*N) jittered
+    hex box is partitioned with the general partitioner (recursive coordinate bisection, node-adjacency overlap, order
+    preserving local numbering), each rank evaluates its partition on its GPU (NCCL state halo in flight while the
+    independent gradients run; residual + FD block Jacobian + fused pseudo-steady term), and rank 0 compares every
+    updatable cell's residual, update coefficient and Jacobian block row, bit for bit, with a single-domain evaluation of
+    the same mesh on its own GPU."""
+    import cases
+    from coolfluid_b200 import meshgen, partition, lib as cl, config as B
+    em = meshgen.hex_box(32, 32, 16*world, lengths=(1.0, 1.0, 0.5*world), nz_total=16*world)
+    part = partition.rcb_partition(em, world)
+    p = partition.extract(em, part, rank, world)
+    cfg = cases.ns3d_cfg(fuse_time_rhs=1, cfl=3.0)
+    q = cfg.nEqs
+    bcs = cases.bcs_ns3d()
+    fm_g = cl.build_mesh(em, L)
+    Ug = cases.init_state(fm_g, q, True)[:fm_g.nCells*q].reshape(-1, q)
+    fm = cl.build_mesh(p.em, L)
+    fm.updatable = np.ascontiguousarray(p.updatable)
+    lb = bcs + ([B.make_bc(B.BC_SUPER_OUTLET)] if p.em.trs_names[-1] == "PartitionFaces" else [])
+    e = cl.Engine(cfg, local_rank, lib=L)
+    e.set_mesh(fm, lb)
+    # overlap cells start from garbage: only the halo exchange can make the result right
+    Ul = Ug[p.cell_l2g].copy()
+    Ul[p.updatable == 0] = 1e30
+    e.set_states(Ul.reshape(-1))
+    idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+    if rank == 0:
+        idt.copy_(torch.frombuffer(bytearray(cl.nccl_unique_id(L)), dtype=torch.uint8))
+    dist.broadcast(idt, 0)
+    e.comm_init(rank, world, bytes(idt.cpu().numpy().tobytes()))
+    e.set_halo(p)
+    e.set_past_states(Ug[p.cell_l2g].reshape(-1)*(1 + 1e-3))
+    e.halo_begin()
+    rhs, uc = e.compute_rhs()
+    jac = e.bsr_values().reshape(-1, q*q)
+    rp, ci = e.bsr_pattern()
+    e.close()
+    upd = p.updatable == 1
+    brow = np.repeat(np.arange(fm.nCells), np.diff(rp))
+    keep = upd[brow]
+    mine = dict(gid=p.cell_l2g[upd], rhs=rhs.reshape(-1, q)[upd], uc=uc[upd], jac=jac[keep],
+                jrow=p.cell_l2g[brow[keep]], jcol=p.cell_l2g[ci[keep]])
+    allr = [None]*world
+    dist.gather_object(mine, allr if rank == 0 else None, dst=0)
+    if rank != 0:
+        return None
+    e = cl.Engine(cfg, local_rank, lib=L)
+    e.set_mesh(fm_g, bcs)
+    e.set_states(Ug.reshape(-1))
+    e.set_past_states(Ug.reshape(-1)*(1 + 1e-3))
+    rhs_g, uc_g = e.compute_rhs()
+    jac_g = e.bsr_values().reshape(-1, q*q)
+    rp_g, ci_g = e.bsr_pattern()
+    e.close()
+    rhs_g = rhs_g.reshape(-1, q)
+    key_g = np.repeat(np.arange(fm_g.nCells, dtype=np.int64), np.diff(rp_g))*fm_g.nCells + ci_g
+    order = np.argsort(key_g)
+    ok_r = ok_u = ok_j = True
+    ncell = nblk = 0
+    for z in allr:
+        ok_r &= bool(np.array_equal(z["rhs"], rhs_g[z["gid"]]))
+        ok_u &= bool(np.array_equal(z["uc"], uc_g[z["gid"]]))
+        k = order[np.searchsorted(key_g[order], z["jrow"]*fm_g.nCells + z["jcol"])]
+        ok_j &= bool(np.array_equal(z["jac"], jac_g[k]))
+        ncell += len(z["gid"]); nblk += len(k)
+    complete = (ncell == fm_g.nCells) and (nblk == len(ci_g))
+    return {"ok": bool(ok_r and ok_u and ok_j and complete), "mesh": "32x32x%d jittered hexahedra, RCB into %d partitions, "
+            "2 overlap layers" % (16*world, world), "cells": int(ncell), "jacobian_blocks": int(nblk),
+            "rhs_bitwise_equal_to_single_domain": ok_r, "update_coeff_bitwise_equal": ok_u,
+            "jacobian_rows_bitwise_equal": ok_j, "every_cell_and_block_covered_once": bool(complete),
+            "sum_rhs_sq": float((rhs_g*rhs_g).sum())}
 
 
 class ClockSampler:
@@ -181,58 +256,88 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def cpu_baseline(sample_n, evals, threads):
-    """The oracle (CPU restatement of the reference path, `kind: port`) on `threads` host threads, one independent
-    partition of sample_n^3 hex cells per thread (the MPI path runs one rank per core on its own partition)."""
-    import cases
-    from oracle import binding as ob
-    em, cfg, bcs = flagship(sample_n)
-    fm = ob.build_mesh(em)
-    q = 5
-    U0 = cases.init_state(fm, q, True)
-    ob.lib(True)
-    outs = [ob.alloc_outputs(cfg, fm, True) for _ in range(threads)]
-    Us = [U0.copy() for _ in range(threads)]
-    past = np.concatenate([U0[:fm.nCells*q]*(1 + 1e-3), np.zeros(fm.nGhosts*q)])
+class CpuArm:
+    """The oracle (CPU restatement of the reference path, `kind: port`) on `threads` host threads, the way the MPI path
+    runs: one rank per core, each on its own partition of THE SAME n^3 mesh the GPU arm evaluates (a z-slab of
+    n x n x layers cells plus the two overlap layers per interior side, cut from the global box node for node), full
+    RHS + FD Jacobian + pseudo-steady term per evaluation.  `layers` bounds the sample: every thread gets the first
+    `layers` cell layers of its share n/threads of the box (all of it when the share is not larger)."""
 
-    def work(i):
-        for _ in range(evals):
-            outs[i].updateCoeff[:] = 0.0
-            ob.compute(cfg, fm, bcs, Us[i], jacobian=True, omp=True, out=outs[i])
-            ob.time_rhs(cfg, fm, bcs, Us[i], past, outs[i], omp=True)
-    th = [threading.Thread(target=work, args=(i,)) for i in range(threads)]
-    t0 = time.perf_counter()
-    for t in th:
-        t.start()
-    for t in th:
-        t.join()
-    dt = time.perf_counter() - t0
-    cells = fm.nCells*threads*evals
-    return cells/dt, dt, fm.nCells
+    def __init__(self, n, threads, layers):
+        import cases
+        from coolfluid_b200 import lib as cl, meshgen
+        from oracle import binding as ob
+        self.ob, self.cfg, self.bcs = ob, cases.ns3d_cfg(), cases.bcs_ns3d()
+        self.n, self.threads = n, threads
+        share = max(1, n//threads)
+        self.layers = layers = share if not layers else max(1, min(layers, share))
+        L = cl.load()
+        ob.lib(True)
+        q = 5
+        self.items = []
+        for t in range(threads):
+            k_first = t*share
+            lo = 2 if k_first > 0 else 0
+            hi = 2 if k_first + layers < n else 0
+            em = meshgen.hex_box(n, n, layers + lo + hi, k0=k_first - lo, nz_total=n)
+            fm = cl.build_mesh(em, L)                            # host mesh-data builder (setup, not timed)
+            k_of = np.arange(fm.nCells)//(n*n)
+            fm.updatable = np.ascontiguousarray(((k_of >= lo) & (k_of < lo + layers)).astype(np.uint8))
+            U = cases.init_state(fm, q, True)
+            past = np.concatenate([U[:fm.nCells*q]*(1 + 1e-3), np.zeros(fm.nGhosts*q)])
+            self.items.append((fm, U, past, ob.alloc_outputs(self.cfg, fm, True)))
+        self.cells = n*n*layers*threads
+        self.sample = ("%d host threads, one oracle instance each on its own z-slab (%d of the %d cell layers of its share, "
+                       "+ 2 overlap layers per interior side) of the same %d^3 mesh: %d updatable cells per evaluation"
+                       % (threads, layers, share, n, self.cells))
+
+    def run(self, evals):
+        """-> (updatable cells per second over all threads, seconds)"""
+        ob, cfg, bcs = self.ob, self.cfg, self.bcs
+
+        def work(i):
+            fm, U, past, out = self.items[i]
+            for _ in range(evals):
+                out.updateCoeff[:] = 0.0
+                ob.compute(cfg, fm, bcs, U, jacobian=True, omp=True, out=out)
+                ob.time_rhs(cfg, fm, bcs, U, past, out, omp=True)
+        th = [threading.Thread(target=work, args=(i,)) for i in range(self.threads)]
+        t0 = time.perf_counter()
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        dt = time.perf_counter() - t0
+        return self.cells*evals/dt, dt
+
+
+def workload_text(workload, n, n_upd):
+    return WORKLOADS[workload][0] % (n, n_upd)
 
 
 def run_reference(args, rank):
+    """`--impl reference`: the reference's CPU path for the same workload on the box's host cores.  COOLFluiD itself cannot
+    be built on this image (no Boost / MPI / PETSc: DESIGN.md), so this is the oracle port, one instance per host thread
+    like one MPI rank per core; each step is one evaluation of a bounded sample of the workload (CpuArm)."""
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    n = args.cpu_sample
+    arm = CpuArm(args.n, threads, args.cpu_layers)
     vals = []
     for _ in range(args.warmup):
-        cpu_baseline(n, 1, threads)
+        arm.run(1)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        v, dt, nc = cpu_baseline(n, 1, threads)
+        v, dt = arm.run(1)
         vals.append(v)
     total = time.perf_counter() - t0
-    v = statistics.median(vals)
-    sample = "%d independent partitions of %d^3 hex cells (one per host thread), 1 evaluation per step" % (threads, n)
+    v = statistics.median(vals) if vals else 0.0
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3*total/max(args.steps, 1), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "3D Navier-Stokes hex box, Roe + viscous (DiamondVolume3D), LSQ + Venktn3D, FD Jacobian, "
-                               "pseudo-steady time term; CPU sample %s" % sample},
-        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "config": {"workload": workload_text("ns3d", args.n, args.n**3)},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": arm.sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "the reference itself (Boost/MPI/PETSc) cannot be built on this image; this is the oracle port "
                 "(-O3, no FP contraction), one instance per host thread"}))
@@ -246,8 +351,11 @@ def main():
     ap.add_argument("--impl", default="cfb200")
     ap.add_argument("--n", "--edge", dest="n", type=int, default=220, help="hex box edge per GPU (220^3 = 10.6 M cells, configs[2])")
     ap.add_argument("--workload", default="ns3d", choices=sorted(WORKLOADS), help="ns3d = configs[2] (the metric), euler2d_* = configs[1], mhd3d = configs[3]")
-    ap.add_argument("--cpu-sample", type=int, default=36, help="edge of the per-thread hex box of the CPU baseline")
-    ap.add_argument("--cpu-evals", type=int, default=24, help="evaluations per thread of the cpu_baseline leg (~10-20 s)")
+    ap.add_argument("--cpu-layers", type=int, default=8, help="cell layers (of n x n cells) per host thread of the CPU arm: the "
+                    "bounded sample of each thread's share of the n^3 mesh (0 = the whole share)")
+    ap.add_argument("--cpu-evals", type=int, default=2, help="timed evaluations of the cpu_baseline leg (after one warm-up)")
+    ap.add_argument("--no-fuse", action="store_true", help="pseudo-steady time term as a separate kernel (cfb200_time_rhs)")
+    ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the cross-rank parity mini-problem")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -272,7 +380,11 @@ def main():
 
     wl_desc, wl_pvt, a_rhs, a_jac = WORKLOADS[args.workload]
     t0 = time.perf_counter()
+    parity = None
+    if world > 1 and not args.no_parity:
+        parity = multi_gpu_parity(rank, world, local_rank, L, dist, torch)
     em, cfg, bcs = flagship(args.n if world == 1 else 2, args.workload)
+    cfg.fuseTimeRhs = 0 if args.no_fuse else 1
     q = cfg.nEqs
     part = None
     if world > 1:
@@ -310,7 +422,8 @@ def main():
         if part is not None:
             eng.halo_begin()                 # state halo over NCCL; compute_rhs overlaps it with the interior gradients
         eng.compute_rhs(apply_bc=True, download=False)
-        eng.time_rhs(download=False)
+        if args.no_fuse:
+            eng.time_rhs(download=False)
 
     def step_e2e():
         eng.set_states(hU.numpy())
@@ -318,7 +431,8 @@ def main():
         if part is not None:
             eng.halo_begin()
         eng.compute_rhs(apply_bc=True, download=True, out_rhs=hR.numpy(), out_uc=hC.numpy())
-        eng.time_rhs(download=False)
+        if args.no_fuse:
+            eng.time_rhs(download=False)
 
     def barrier():
         if dist is not None:
@@ -352,7 +466,7 @@ def main():
     def step_resident_timed():
         step_resident()
         tl = eng.last_timings()
-        launches[0] += len(tl) + 1          # + the time-term kernel is in the list; +1 = updateCoeff memset excluded
+        launches[0] += len(tl)              # every kernel of the step is in the list (the updateCoeff memset is not a kernel)
         per = {}
         for name, ms in tl:                   # chunked kernels appear once per chunk: sum them per step
             per[name] = per.get(name, 0.0) + ms
@@ -387,14 +501,16 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": wl_desc % (args.n, n_upd),
+            "config": {"workload": workload_text(args.workload, args.n, n_upd),
                        "cells_per_gpu": nc, "faces_per_gpu": int(fm.nFaces), "bsr_blocks_per_gpu": int(eng.nnzb),
                        "l2": "inputs (%.1f GB BSR + %.2f GB states/gradients) far larger than the 126 MB L2; no flush needed"
                              % (eng.nnzb*q*q*8/1e9, nc*q*8*6/1e9),
                        "partitioning": ("single partition" if part is None else
-                                        "slab per GPU (%d updatable + %d overlap cells on rank 0), state halo exchange over "
-                                        "NCCL every step (%d cells x %d doubles per neighbour), overlapped with the "
-                                        "interior gradients" % (n_upd, nc - n_upd, 2*args.n*args.n, q)),
+                                        "one global %d x %d x %d box cut along z, one slab per GPU (%d updatable + %d overlap "
+                                        "cells on rank 0, order-preserving local numbering), state halo exchange over NCCL "
+                                        "every step (%d cells x %d doubles per neighbour), overlapped with the independent "
+                                        "gradients" % (args.n, args.n, args.n*world, n_upd, nc - n_upd, 2*args.n*args.n, q)),
+                       "time_term": "separate kernel" if args.no_fuse else "fused into the residual / diagonal gathers",
                        "mesh_build_s": round(t_mesh, 2), "device_setup_s": round(t_setup, 2)},
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": int(nc*q*8*world), "d2h_bytes_per_step": int((nc*q*8 + nc*8)*world)},
@@ -408,13 +524,15 @@ def main():
                               "frac_of_hbm_peak": (a_rhs + a_jac)*value/world/1e9/peak},
             "clocks": clocks, "status": int(status),
         }
+        if parity is not None:
+            out["parity"] = parity
         if world == 1 and not args.no_cpu_baseline and args.workload == "ns3d":
             threads = os.cpu_count() or 1
-            v, dt, ncs = cpu_baseline(args.cpu_sample, args.cpu_evals, threads)
+            arm = CpuArm(args.n, threads, args.cpu_layers)
+            arm.run(1)
+            v, dt = arm.run(args.cpu_evals)
             out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
-                                   "sample": "%d independent partitions of %d^3 hex cells (one oracle instance per host "
-                                             "thread), %d evaluations each, %.1f s" % (threads, args.cpu_sample,
-                                                                                       args.cpu_evals, dt)}
+                                   "sample": arm.sample + "; %d evaluations, %.1f s" % (args.cpu_evals, dt)}
         print(json.dumps(out))
     eng.close()
     if dist is not None:

@@ -43,7 +43,9 @@ class ConfigStruct(C.Structure):
         ("ausmBeta", C.c_double), ("ausmAlpha", C.c_double),
         ("ausmKu", C.c_double), ("ausmKp", C.c_double), ("ausmSigma", C.c_double), ("machInf", C.c_double),
         ("physicalModel", C.c_int32), ("entropyFixID", C.c_int32), ("refSpeed", C.c_double), ("coeffSigmoid", C.c_double),
-        ("derivativeStrategy", C.c_int32), ("reserved0", C.c_int32),
+        ("derivativeStrategy", C.c_int32), ("fuseTimeRhs", C.c_int32),
+        ("timeZeroDiag", C.c_int32*MAXEQ), ("timeAnalyticalMatrix", C.c_int32), ("timeUseGlobalDT", C.c_int32),
+        ("reserved1", C.c_int32), ("dt", C.c_double),
     ]
 
 
@@ -132,6 +134,14 @@ def make_config(dim, update_var=UV_CONS, flux=FS_ROE, poly_rec=PR_CONSTANT, limi
     c.ausmKp = kw.get("coeff_kp", 0.25)
     c.ausmSigma = kw.get("sigma", 1.0)
     c.machInf = kw.get("mach_inf", 0.0)
+    # pseudo-steady time term (FVMCC_StdComputeTimeRhs.cxx:42-57, FVMCC_PseudoSteadyTimeRhs.cxx:40-46)
+    c.fuseTimeRhs = int(kw.get("fuse_time_rhs", 0))
+    zd = kw.get("time_zero_diag", None)
+    for i in range(MAXEQ):
+        c.timeZeroDiag[i] = int(zd[i]) if zd is not None and i < len(zd) else 0
+    c.timeAnalyticalMatrix = int(kw.get("time_analytical_matrix", 0))
+    c.timeUseGlobalDT = int(kw.get("time_use_global_dt", 0))
+    c.dt = float(kw.get("dt", 0.0))
     return c
 
 

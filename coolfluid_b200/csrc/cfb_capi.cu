@@ -40,15 +40,27 @@ __global__ void __launch_bounds__(BS, MINB) k_staged(const F f, const int n) {
   double* out = f.out();
   // entry e = lane + 32*it of the warp's 32 x NOUT finished values: face lf = e / NOUT, k = e % NOUT, kept incrementally
   static_assert(F::NOUT >= 32 && F::STAGE >= F::NOUT + 2, "staging layout");
+  // batches of WB entries: all shared-memory reads of a batch are issued before its first global store (one round trip
+  // per batch instead of one per entry: with 8 resident warps per SM nothing else hides the latency)
+  constexpr int WB = (F::NOUT % 10 == 0) ? 10 : 8;
+  static_assert(F::NOUT % WB == 0, "write-out batch");
   int k = lane, lf = 0;
-#pragma unroll 2
-  for (int it = 0; it < F::NOUT; ++it) {
-    const int sel = (k >= F::BLK) ? 1 : 0;
-    const int kk = k - sel*F::BLK;
-    const int slot = __double2loint(sm[(F::NOUT + sel)*STRIDE + warpBase + lf]);
-    if (slot >= 0) out[(size_t)slot*F::BLK + kk] = sm[k*STRIDE + warpBase + lf];
-    k += 32;
-    if (k >= F::NOUT) { k -= F::NOUT; ++lf; }
+#pragma unroll 1
+  for (int it = 0; it < F::NOUT; it += WB) {
+    double x[WB]; size_t dst[WB]; bool on[WB];
+#pragma unroll
+    for (int j = 0; j < WB; ++j) {
+      const int sel = (k >= F::BLK) ? 1 : 0;
+      const int kk = k - sel*F::BLK;
+      const int slot = __double2loint(sm[(F::NOUT + sel)*STRIDE + warpBase + lf]);
+      x[j] = sm[k*STRIDE + warpBase + lf];
+      on[j] = slot >= 0;
+      dst[j] = (size_t)slot*F::BLK + kk;
+      k += 32;
+      if (k >= F::NOUT) { k -= F::NOUT; ++lf; }
+    }
+#pragma unroll
+    for (int j = 0; j < WB; ++j) if (on[j]) out[dst[j]] = x[j];
   }
 }
 
@@ -87,6 +99,21 @@ __global__ void __launch_bounds__(256) k_block_sum(const double* __restrict__ x,
   s[threadIdx.x] = a;
   __syncthreads();
   for (int w = 128; w > 0; w >>= 1) { if (threadIdx.x < w) s[threadIdx.x] += s[threadIdx.x + w]; __syncthreads(); }
+  if (threadIdx.x == 0) out[blockIdx.x] = s[0];
+}
+
+// fixed-shape block minimum (the minimum is exact whatever the order)
+__global__ void __launch_bounds__(256) k_block_min(const double* __restrict__ x, double* __restrict__ out, int n) {
+  __shared__ double s[256];
+  const int base = blockIdx.x*1024;
+  double a = 1.7976931348623157e308;
+  for (int k = 0; k < 4; ++k) { const int i = base + k*256 + threadIdx.x; if (i < n) a = (x[i] < a) ? x[i] : a; }
+  s[threadIdx.x] = a;
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1) {
+    if (threadIdx.x < w) { const double b = s[threadIdx.x + w]; if (b < s[threadIdx.x]) s[threadIdx.x] = b; }
+    __syncthreads();
+  }
   if (threadIdx.x == 0) out[blockIdx.x] = s[0];
 }
 
@@ -242,6 +269,19 @@ struct CudaBackend {
     for (double v : h) s += v;
     return s;
   }
+  double minOrdered(double* x, int n) {
+    if (n <= 0) return 0.;
+    const int nb = (n + 1023)/1024;
+    double* out = x + n;
+    k_block_min<<<nb, 256, 0, stream>>>(x, out, n);
+    CFB_CUDA(cudaGetLastError());
+    std::vector<double> h(nb);
+    CFB_CUDA(cudaMemcpyAsync(h.data(), out, sizeof(double)*nb, cudaMemcpyDeviceToHost, stream));
+    CFB_CUDA(cudaStreamSynchronize(stream));
+    double m = h[0];
+    for (double v : h) m = (v < m) ? v : m;
+    return m;
+  }
 };
 
 } // namespace cfb
@@ -343,6 +383,15 @@ int cfb200_set_halo(cfb200_handle* h, const int32_t* sendPtr, const int32_t* sen
     if (nr) CFB_CUDA(cudaMemcpy(H->dRecv, recvCells, sizeof(int)*nr, cudaMemcpyHostToDevice));
     H->haveLists = true;
     e.nIndep = nIndependent;
+    return CFB200_OK;
+  });
+}
+
+int cfb200_set_independent_cells(cfb200_handle* h, const int32_t* cells, int32_t n) {
+  if (n < 0 || (n > 0 && !cells)) return CFB200_ERR_INVALID_ARG;
+  return guarded(h, [&](cfb::Engine<BackendT>& e) {
+    CFB_NEED_MESH(e);
+    e.setIndependentCells(cells, n);
     return CFB200_OK;
   });
 }

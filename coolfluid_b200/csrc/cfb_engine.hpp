@@ -21,6 +21,7 @@ namespace cfb {
 
 // Roe; AUSM+ and AUSM+up with the perfect-gas interface sound speeds (choiceA12 4/5 are the TCNEQ variants).
 inline bool splitterSupported(const cfb200_config& c) {
+  if (c.fuseTimeRhs && c.timeUseGlobalDT) return false;   // the global minimum needs the complete updateCoeff first
   // "NumJacobAnalytic": the analytic flux Jacobian exists for AUSM+up in conservative variables, inviscid (a19)
   if (c.computeJacobian == 2 && !(c.physicalModel == CFB200_PM_EULER && c.fluxSplitter == CFB200_FS_AUSMPLUSUP &&
                                   c.updateVar == CFB200_UV_CONS && c.diffusive == CFB200_DIFF_NONE && c.machInf > 0.))
@@ -60,6 +61,7 @@ public:
   int64_t nnzb = 0;
   int nNonUpd = 0;
   bool meshSet = false, statesSet = false;
+  bool timeTermApplied = false;     // the last computeRhs applied the pseudo-steady time term itself (cfg.fuseTimeRhs)
   int lastStatus = 0;
   double* bcFaceVal = nullptr; uint8_t* bcFaceFlag = nullptr;      // device copies behind Dev::bcFaceVal / bcFaceFlag
   std::vector<double> hBcFaceVal; std::vector<uint8_t> hBcFaceFlag; std::vector<int32_t> hGhostBC;
@@ -69,6 +71,9 @@ public:
   // multi-GPU (cfb_halo.cuh): a state halo exchange may be in flight when computeRhs is called; the first nIndep
   // cells have no received cell in their reconstruction stencil, so their gradients overlap with the exchange
   int nIndep = 0;
+  // the same set given as a list (cfb200_set_independent_cells): local cell numbering then stays free, e.g. ascending
+  // global ID, which keeps every gather order of the single-domain run; depCells = the complement
+  int* indepCells = nullptr; int* depCells = nullptr; int nIndepList = 0;
   bool haloPending = false;
   std::function<void()> haloWait;
   // every entry point that reads or writes U outside computeRhs joins an exchange that is still in flight first
@@ -206,6 +211,7 @@ public:
         }
       d.lsqPtr = upload(cnt);
       d.lsqNbr = upload(nbr);
+      d.lsqW = dalloc<double>(nbr.size());
     }
     // BSR pattern (FVMCCSparsity.cxx:47-106: diagonal + one block per interior-face neighbour) and face slots
     {
@@ -339,18 +345,25 @@ public:
     bk.resetTimings();
     bk.memset(d.status, 0, sizeof(int));
     int g0 = 0;
+    bool listed = false;
     if (haloPending) {
       // overlap with the halo exchange: ghosts + gradients of the cells that do not see a received state
       if (applyBC) applyBC_<D, PH>();
-      if (cfg.polyRec == CFB200_PR_LINEARLS && nIndep > 0) {
+      if (cfg.polyRec == CFB200_PR_LINEARLS && indepCells && nIndepList > 0) {
+        bk.launch("gradientsInterior", Gradients<D, PH>{d, 0, indepCells}, nIndepList, 128);
+        listed = true;
+      } else if (cfg.polyRec == CFB200_PR_LINEARLS && nIndep > 0) {
         g0 = std::min(nIndep, d.nCells);
-        bk.launch("gradientsInterior", Gradients<D, PH>{d, 0}, g0, 128);
+        bk.launch("gradientsInterior", Gradients<D, PH>{d, 0, nullptr}, g0, 128);
       }
       joinHalo();                          // the engine's stream now waits for the unpacked overlap states
     }
     if (applyBC) applyBC_<D, PH>();
     // initializeComputationRHS (FVMCC_ComputeRHS.cxx:690-705)
-    if (cfg.polyRec == CFB200_PR_LINEARLS) bk.launch("gradients", Gradients<D, PH>{d, g0}, d.nCells - g0, 128);
+    if (cfg.polyRec == CFB200_PR_LINEARLS) {
+      if (listed) bk.launch("gradients", Gradients<D, PH>{d, 0, depCells}, d.nCells - nIndepList, 128);
+      else bk.launch("gradients", Gradients<D, PH>{d, g0, nullptr}, d.nCells - g0, 128);
+    }
     bk.launch("nodalExtrapolate", NodalExtrapolate<D, PH>{d}, d.nNodes, 256);
     if (cfg.polyRec == CFB200_PR_LINEARLS && cfg.limiter != CFB200_LIM_NONE)
       bk.launch("limiter", LimiterK<D, PH>{d, cfg}, d.nCells, 128);
@@ -368,11 +381,16 @@ public:
     }
     bk.launch("cellGather", CellGather<D, PH>{d, cfg}, d.nCells, 256);
     if (doJac) {
-      if ((long long)d.nCells*DiagGather<D, PH>::GS > 2147483647LL)
-        throw std::runtime_error("mesh too large for one device: nCells * q*q exceeds the 32-bit launch index");
-      bk.launch("diagGather", DiagGather<D, PH>{d}, d.nCells*DiagGather<D, PH>::GS, 256);
-      if (nNonUpd) bk.launch("zeroRows", ZeroRows<D, PH>{d, nonUpdCells}, nNonUpd*ZeroRows<D, PH>::GS, 256);
+      // one thread per (cell, block entry): launched in chunks of < 2^31 entries (q = 9: 26.5 M cells per chunk)
+      const long long CH = 1LL << 30;
+      const long long nd = (long long)d.nCells*DiagGather<D, PH>::GS;
+      for (long long b0 = 0; b0 < nd; b0 += CH)
+        bk.launch("diagGather", DiagGather<D, PH>{d, cfg, b0}, (int)std::min(CH, nd - b0), 256);
+      const long long nz = (long long)nNonUpd*ZeroRows<D, PH>::GS;
+      for (long long b0 = 0; b0 < nz; b0 += CH)
+        bk.launch("zeroRows", ZeroRows<D, PH>{d, nonUpdCells, b0}, (int)std::min(CH, nz - b0), 256);
     }
+    timeTermApplied = (cfg.fuseTimeRhs != 0);
     int st = 0;
     bk.d2h(&st, d.status, sizeof(int));   // synchronises
     lastStatus = st;
@@ -386,12 +404,29 @@ public:
     if (isMhd()) computeRhs_<3, MhdPhys>(applyBCFirst);
     else if (cfg.dim == 2) computeRhs_<2, Phys<2> >(applyBCFirst); else computeRhs_<3, Phys<3> >(applyBCFirst);
   }
-  void timeRhs() {
+  template <int D, class PH> void timeRhs_() {
     const int doJac = cfg.computeJacobian && d.bsrVal;
-    if (isMhd()) bk.launch("timeRhs", TimeRhs<3, MhdPhys>{d, cfg, doJac}, d.nCells, 128);
-    else if (cfg.dim == 2) bk.launch("timeRhs", TimeRhs<2>{d, cfg, doJac}, d.nCells, 128);
-    else bk.launch("timeRhs", TimeRhs<3>{d, cfg, doJac}, d.nCells, 128);
+    double minDt = 0.;
+    if (cfg.timeUseGlobalDT) {            // FVMCC_PseudoSteadyTimeRhs.cxx:121-127: minimum over every local state
+      bk.launch("timeLocalDt", TimeLocalDt<D, PH>{d, cfg}, d.nCells, 256);
+      minDt = bk.minOrdered(d.partial, d.nCells);
+    }
+    bk.launch("timeRhs", TimeRhs<D, PH>{d, cfg, doJac, minDt}, d.nCells, 128);
     bk.sync();
+  }
+  void timeRhs() {
+    if (timeTermApplied) throw std::runtime_error("the pseudo-steady time term was already applied by compute_rhs (fuseTimeRhs)");
+    if (isMhd()) timeRhs_<3, MhdPhys>(); else if (cfg.dim == 2) timeRhs_<2, Phys<2> >(); else timeRhs_<3, Phys<3> >();
+  }
+  void setIndependentCells(const int32_t* cells, int n) {
+    std::vector<uint8_t> in(d.nCells, 0);
+    for (int i = 0; i < n; ++i) {
+      if (cells[i] < 0 || cells[i] >= d.nCells || in[cells[i]]) throw std::invalid_argument("set_independent_cells: bad or repeated cell id");
+      in[cells[i]] = 1;
+    }
+    std::vector<int32_t> a(cells, cells + n), b;
+    for (int c = 0; c < d.nCells; ++c) if (!in[c]) b.push_back(c);
+    indepCells = upload(a); depCells = upload(b); nIndepList = n;
   }
   // position-dependent Dirichlet data of one boundary-condition record: values[iFace*q + v] for the faces of that
   // record in face-loop order; nullptr reverts the record to its constant

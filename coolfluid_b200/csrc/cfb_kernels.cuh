@@ -39,6 +39,7 @@ struct Dev {
   const uint8_t* cellActive;  // cell touches at least one face with an updatable side
   const BCond* bcs;
   double* lsqL;               // [6][nCells]  l11 l12 l13 l22 l23 l33
+  double* lsqW;               // [len(lsqNbr)] inverse-distance weight of each gather entry (static geometry: formed once at setup)
   // ---- block Jacobian ----
   const int* bsrRowPtr; const int* bsrColInd;
   const int* slotLR;          // [nInner] block (L,R)
@@ -155,6 +156,17 @@ CFB_HD double edgeWeight(const Dev& d, int c, int nb, double* dx) {
   for (int k = 0; k < D; ++k) dx[k] = w*dx[k];
   return w;
 }
+// the same with the weight read back from the setup pass (LeastSquareP1PolyRec2D::updateWeights keeps them in its
+// `weights` array too, LeastSquareP1PolyRec2D.cxx:266-400): no square root / division per neighbour and evaluation
+template <int D, class PH = Phys<D> >
+CFB_HD double edgeWeightStored(const Dev& d, int c, int nb, int j, double* dx) {
+  const double w = d.lsqW[j];
+  for (int k = 0; k < D; ++k) {
+    const double xc = d.centres[(size_t)k*d.nStates + c], xn = d.centres[(size_t)k*d.nStates + nb];
+    dx[k] = w*(xn - xc);
+  }
+  return w;
+}
 
 template <int D, class PH = Phys<D> >
 struct LsqSetup {   // LeastSquareP1PolyRec{2,3}D::updateWeights; idx over cells
@@ -163,7 +175,7 @@ struct LsqSetup {   // LeastSquareP1PolyRec{2,3}D::updateWeights; idx over cells
     double l[6] = {0., 0., 0., 0., 0., 0.};
     for (int j = d.lsqPtr[c]; j < d.lsqPtr[c+1]; ++j) {
       double dx[3] = {0., 0., 0.};
-      edgeWeight<D>(d, c, d.lsqNbr[j], dx);
+      d.lsqW[j] = edgeWeight<D>(d, c, d.lsqNbr[j], dx);
       if (D == 2) { l[0] += dx[0]*dx[0]; l[1] += dx[0]*dx[1]; l[3] += dx[1]*dx[1]; }
       else {
         l[0] += dx[0]*dx[0]; l[1] += dx[0]*dx[1]; l[2] += dx[0]*dx[2];
@@ -175,18 +187,18 @@ struct LsqSetup {   // LeastSquareP1PolyRec{2,3}D::updateWeights; idx over cells
 };
 
 template <int D, class PH = Phys<D> >
-struct Gradients {   // idx over the cells [c0, c0 + n)
-  Dev d; int c0;
+struct Gradients {   // idx over the cells [c0, c0 + n), or over the cell list `cells` when it is given
+  Dev d; int c0; const int* cells;
   CFB_HD void operator()(int idx) const {
     constexpr int Q = PH::Q;
-    const int c = c0 + idx;
+    const int c = cells ? cells[idx] : c0 + idx;
     double lf[3][Q];
     double u0[Q];
     for (int v = 0; v < Q; ++v) { lf[0][v] = lf[1][v] = lf[2][v] = 0.; u0[v] = d.U[(size_t)v*d.nStates + c]; }
     for (int j = d.lsqPtr[c]; j < d.lsqPtr[c+1]; ++j) {
       const int nb = d.lsqNbr[j];
       double dx[3] = {0., 0., 0.};
-      const double w = edgeWeight<D>(d, c, nb, dx);
+      const double w = edgeWeightStored<D>(d, c, nb, j, dx);
       for (int v = 0; v < Q; ++v) {
         const double du = w*(d.U[(size_t)v*d.nStates + nb] - u0[v]);
         lf[0][v] += dx[0]*du; lf[1][v] += dx[1]*du;
@@ -363,6 +375,81 @@ struct LimiterK {   // idx over cells
 #include "cfb_face.cuh"
 #include "cfb_centred_face.cuh"
 
+// ------------------------------------------------------------------------------------------------
+// a21: FVMCC_PseudoSteadyTimeRhs::execute (FVMCC_PseudoSteadyTimeRhs.cxx:106-330):
+//   diag = V/dt (dt > 0, unsteady) | updateCoeff/CFL (steady) | V/minDt (useGlobalDT, minDt = min_cells V/updateCoeff*CFL)
+//   rhs -= (U - U_past) * diag * resFactor in SOLUTION variables, unless zeroDiagValue[iEq]
+//   diagonal block += diag * resFactor * dU/dP, dU/dP numerical (:197-262) or analytical (:266-310)
+// The same two device functions serve the stand-alone kernel (cfb200_time_rhs) and the fused form (cfg.fuseTimeRhs:
+// CellGather subtracts the rhs part, DiagGather adds the block part), so both give the same bits.
+template <int D, class PH>
+CFB_HD double timeDiagValue(const Dev& d, const Cfg& c, int cell, double updateCoeff, double minDt) {
+  if (c.timeUseGlobalDT) return ddiv(d.volumes[cell], minDt);
+  return (c.dt > 0.0) ? ddiv(d.volumes[cell], c.dt) : ddiv(updateCoeff, c.cfl);
+}
+// dU/dP, analytical: Euler2DPuvtToConsInPuvt.cxx:42-67, Euler3DPvtToConsInPvt.cxx:42-76; identity when update = solution
+template <int D, class PH>
+CFB_HD double timeAnalyticalEntry(const Cfg& c, const double* u, int i, int j) {
+  constexpr int Q = PH::Q;
+  if (PH::CENTRED_ONLY || c.updateVar == CFB200_UV_CONS) return (i == j) ? 1. : 0.;
+  constexpr int TID = D + 1;
+  const double p = u[0] + c.pOffset;
+  const double T = u[TID];
+  const double rho = ddiv(p, c.R*T);
+  const double rhoOvT = ddiv(rho, T);
+  const double invRT = ddiv(1., c.R*T);
+  double V2;
+  if (D == 2) V2 = u[1]*u[1] + u[2]*u[2]; else V2 = u[1]*u[1] + u[2]*u[2] + u[3]*u[3];
+  const double gammaMinus1 = c.gamma - 1.;
+  double r = 0.;
+  if (i == 0) { if (j == 0) r = invRT; else if (j == TID) r = -rhoOvT; }
+  else if (i == TID) {
+    if (j == 0) r = ddiv(1., gammaMinus1) + 0.5*V2*invRT;
+    else if (j == TID) r = -0.5*rhoOvT*V2;
+    else r = rho*pick<Q>(u, j);
+  } else {
+    const double ui = pick<Q>(u, i);
+    if (j == 0) r = ui*invRT; else if (j == i) r = rho; else if (j == TID) r = -rhoOvT*ui;
+  }
+  return r;
+}
+// what the time term adds to entry (v, iVar) of the diagonal block of a cell with update state u
+template <int D, class PH>
+CFB_HD double timeBlockEntry(const Cfg& c, const double* u, int v, int iVar, double diagValue) {
+  constexpr int Q = PH::Q;
+  if (c.timeAnalyticalMatrix) {
+    if (c.timeZeroDiag[iVar]) return 0.;        // (sic) the reference tests the flag of the COLUMN in the analytical variant
+    return timeAnalyticalEntry<D, PH>(c, u, v, iVar)*diagValue*c.resFactor;
+  }
+  double up[Q], tempState[Q], tPert[Q];
+  const double orig = pick<Q>(u, iVar);
+  const double eps = fdEps(c, iVar, orig);
+#pragma unroll
+  for (int k = 0; k < Q; ++k) up[k] = (k == iVar) ? orig + eps : u[k];
+  PH::toCons(c, u, tempState);
+  PH::toCons(c, up, tPert);
+  const double invEps = ddiv(1., eps);
+  double fd = (pick<Q>(tPert, v) - pick<Q>(tempState, v))*invEps;
+  fd *= c.timeZeroDiag[v] ? 0.0 : diagValue*c.resFactor;
+  return fd;
+}
+// rhs part for one cell (AoS rhs row r[] in registers)
+template <int D, class PH>
+CFB_HD void timeRhsRow(const Dev& d, const Cfg& c, int cell, const double* u, double diagValue, double* r) {
+  constexpr int Q = PH::Q;
+  double up[Q], tempState[Q], tPast[Q];
+#pragma unroll
+  for (int v = 0; v < Q; ++v) up[v] = d.pastU[(size_t)v*d.nCells + cell];
+  PH::toCons(c, u, tempState);
+  PH::toCons(c, up, tPast);
+#pragma unroll
+  for (int v = 0; v < Q; ++v) {
+    const double dU = tempState[v] - tPast[v];
+    r[v] -= c.timeZeroDiag[v] ? 0.0 : dU*diagValue*c.resFactor;
+  }
+}
+
+
 // a17: FVMCC_ComputeRHS::updateRHS (FVMCC_ComputeRHS.cxx:455-514) as a gather: for each cell, its faces in
 // ascending loop order; rhs starts from 0, updateCoeff accumulates onto the incoming value
 // (it is zeroed by the updater, UpdateSol.cxx:192).
@@ -389,6 +476,12 @@ struct CellGather {   // idx over cells
       }
       uc += isR ? d.ucR[f] : d.ucL[f];
       if (hasDiff) uc += d.ucD[f];
+    }
+    if (c.fuseTimeRhs && d.updatable[cell]) {     // a21 fused: FVMCC_PseudoSteadyTimeRhs on the finished residual row
+      double u[Q];
+#pragma unroll
+      for (int v = 0; v < Q; ++v) u[v] = d.U[(size_t)v*d.nStates + cell];
+      timeRhsRow<D, PH>(d, c, cell, u, timeDiagValue<D, PH>(d, c, cell, uc, 0.), r);
     }
     for (int v = 0; v < Q; ++v) d.rhs[(size_t)cell*Q + v] = r[v];
     d.updateCoeff[cell] = uc;
@@ -426,10 +519,11 @@ struct DivBGather {   // idx over cells
 template <int D, class PH = Phys<D> >
 struct DiagGather {   // idx over nCells*GS: one thread per (cell, block entry), no idle lanes
   static constexpr int GS = PH::Q*PH::Q;
-  Dev d;
-  CFB_HD void operator()(int idx) const {
+  Dev d; Cfg c; long long base;      // base: first (cell, entry) index of this launch (chunked above 2^31 entries)
+  CFB_HD void operator()(int idx0) const {
     constexpr int Q = PH::Q;
-    const int cell = idx/GS, e = idx - cell*GS;
+    const long long idx = base + idx0;
+    const int cell = (int)(idx/GS), e = (int)(idx - (long long)cell*GS);
     if (e >= Q*Q) return;
     double acc = 0.;
     if (d.updatable[cell]) {
@@ -452,6 +546,13 @@ struct DiagGather {   // idx over nCells*GS: one thread per (cell, block entry),
         for (int k = 0; k < 6; ++k)
           if (j0 + k < je) { if (d.diagSrc[j0 + k] >= 0) acc -= x[k]; else acc += x[k]; }
       }
+      if (c.fuseTimeRhs) {     // a21 fused: the time term lands on the finished face sum (updateCoeff is complete: CellGather ran)
+        double u[Q];
+#pragma unroll
+        for (int v = 0; v < Q; ++v) u[v] = d.U[(size_t)v*d.nStates + cell];
+        const int v = e/Q, iVar = e - v*Q;
+        acc += timeBlockEntry<D, PH>(c, u, v, iVar, timeDiagValue<D, PH>(d, c, cell, d.updateCoeff[cell], 0.));
+      }
     }
     d.bsrVal[(size_t)d.diagSlot[cell]*Q*Q + e] = acc;
   }
@@ -460,52 +561,63 @@ struct DiagGather {   // idx over nCells*GS: one thread per (cell, block entry),
 template <int D, class PH = Phys<D> >
 struct ZeroRows {   // idx over (non-updatable cell list) * GS
   static constexpr int GS = PH::Q*PH::Q;
-  Dev d; const int* cells;
-  CFB_HD void operator()(int idx) const {
+  Dev d; const int* cells; long long base;
+  CFB_HD void operator()(int idx0) const {
     constexpr int Q = PH::Q;
-    const int cell = cells[idx/GS], e = idx - (idx/GS)*GS;
+    const long long idx = base + idx0;
+    const int cell = cells[idx/GS], e = (int)(idx - (idx/GS)*GS);
     if (e >= Q*Q) return;
     for (int k = d.bsrRowPtr[cell]; k < d.bsrRowPtr[cell+1]; ++k) d.bsrVal[(size_t)k*Q*Q + e] = 0.;
   }
 };
 
 // ------------------------------------------------------------------------------------------------
-// a21: FVMCC_PseudoSteadyTimeRhs.cxx:106-262, steady branch (dt == 0): diag = updateCoeff/CFL,
-// rhs -= (U - U_past) * diag * resFactor in SOLUTION variables, diagonal block += diag * dU/dP (numerical)
+// a21 kernels (the device functions are above CellGather)
 template <int D, class PH = Phys<D> >
 struct TimeRhs {   // idx over cells
   // q = 4, 5: 106-126 registers without spills, 16 resident warps per SM; q = 9 is faster at the default shape (measured)
   static constexpr int MINB = (PH::Q > 5) ? 2 : 4;
-  Dev d; Cfg c; int doJac;
+  Dev d; Cfg c; int doJac; double minDt;
   CFB_HD void operator()(int cell) const {
     constexpr int Q = PH::Q;
-    typedef PH P;
     if (!d.updatable[cell]) return;
-    const double diagValue = ddiv(d.updateCoeff[cell], c.cfl);
-    double u[Q], up[Q], tempState[Q], tPast[Q], tPert[Q];
-    for (int v = 0; v < Q; ++v) { u[v] = d.U[(size_t)v*d.nStates + cell]; up[v] = d.pastU[(size_t)v*d.nCells + cell]; }
-    P::toCons(c, u, tempState);
-    P::toCons(c, up, tPast);
-    for (int v = 0; v < Q; ++v) {
-      const double dU = tempState[v] - tPast[v];
-      d.rhs[(size_t)cell*Q + v] -= dU*diagValue*c.resFactor;
-    }
+    const double diagValue = timeDiagValue<D, PH>(d, c, cell, d.updateCoeff[cell], minDt);
+    double u[Q], r[Q];
+#pragma unroll
+    for (int v = 0; v < Q; ++v) { u[v] = d.U[(size_t)v*d.nStates + cell]; r[v] = d.rhs[(size_t)cell*Q + v]; }
+    timeRhsRow<D, PH>(d, c, cell, u, diagValue, r);
+#pragma unroll
+    for (int v = 0; v < Q; ++v) d.rhs[(size_t)cell*Q + v] = r[v];
     if (!doJac) return;
     double* blk = &d.bsrVal[(size_t)d.diagSlot[cell]*Q*Q];
+    if (c.timeAnalyticalMatrix) {
+      for (int iVar = 0; iVar < Q; ++iVar)
+        for (int v = 0; v < Q; ++v) blk[v*Q + iVar] += timeBlockEntry<D, PH>(c, u, v, iVar, diagValue);
+      return;
+    }
+    double tempState[Q], tPert[Q];
+    PH::toCons(c, u, tempState);
     for (int iVar = 0; iVar < Q; ++iVar) {
       const double orig = u[iVar];
       const double eps = fdEps(c, iVar, orig);
       u[iVar] = orig + eps;
-      P::toCons(c, u, tPert);
+      PH::toCons(c, u, tPert);
       const double invEps = ddiv(1., eps);
       for (int v = 0; v < Q; ++v) {
         double fd = (tPert[v] - tempState[v])*invEps;
-        fd *= diagValue*c.resFactor;
+        fd *= c.timeZeroDiag[v] ? 0.0 : diagValue*c.resFactor;
         blk[v*Q + iVar] += fd;
       }
       u[iVar] = orig;
     }
   }
+};
+// useGlobalDT: per-cell V/updateCoeff*CFL (the reference's minimum runs over every local state, :121-127); the minimum of
+// the values is exact whatever the reduction order
+template <int D, class PH = Phys<D> >
+struct TimeLocalDt {   // idx over cells
+  Dev d; Cfg c;
+  CFB_HD void operator()(int cell) const { d.partial[cell] = ddiv(d.volumes[cell], d.updateCoeff[cell])*c.cfl; }
 };
 
 // ------------------------------------------------------------------------------------------------

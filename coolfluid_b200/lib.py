@@ -49,7 +49,7 @@ ABI_SYMBOLS = [
     "compute_rhs", "time_rhs", "update_sol_fwd_euler", "update_sol_newton", "bsr_view", "bsr_pattern", "bsr_nnzb",
     "get_bsr_values",
     "export_csr", "get_field", "device_ptr", "status", "enable_timing", "last_timings", "stream",
-    "nccl_unique_id", "comm_init", "set_halo", "halo_begin", "halo_exchange", "allreduce_sum",
+    "nccl_unique_id", "comm_init", "set_halo", "set_independent_cells", "halo_begin", "halo_exchange", "allreduce_sum",
     "mesh_build", "mesh_sizes", "mesh_get", "mesh_ptr", "mesh_view", "mesh_set_updatable", "mesh_free", "mesh_diamond_volumes",
     "selftest_divsqrt",
 ]
@@ -121,6 +121,7 @@ def load(path=None, prefix="cfb200_"):
         ns.nccl_unique_id.argtypes = [C.c_void_p]
         ns.comm_init.argtypes = [H, C.c_int, C.c_int, C.c_void_p]
         ns.set_halo.argtypes = [H, P_I, P_I, P_I, P_I, C.c_int32]
+        ns.set_independent_cells.argtypes = [H, P_I, C.c_int32]
         ns.halo_begin.argtypes = [H]
         ns.halo_exchange.argtypes = [H]
         ns.allreduce_sum.argtypes = [H, P_D, C.c_int]
@@ -334,7 +335,13 @@ class Engine:
         """part: coolfluid_b200.partition.Partition of this rank"""
         sp, sc, rp, rc = part.halo_csr()
         self._halo_keep = (sp, sc, rp, rc)
-        self._chk(self.L.set_halo(self.h, _pi(sp), _pi(sc), _pi(rp), _pi(rc), int(part.n_interior)), "set_halo")
+        indep = getattr(part, "indep", None)
+        self._chk(self.L.set_halo(self.h, _pi(sp), _pi(sc), _pi(rp), _pi(rc), 0 if indep is not None else int(part.n_interior)),
+                  "set_halo")
+        if indep is not None:
+            indep = np.ascontiguousarray(indep, dtype=np.int32)
+            self._halo_keep += (indep,)
+            self._chk(self.L.set_independent_cells(self.h, _pi(indep), len(indep)), "set_independent_cells")
 
     def halo_begin(self):
         self._chk(self.L.halo_begin(self.h), "halo_begin")

@@ -63,23 +63,46 @@ def _pack_trs(faces_per_trs):
             np.array(nptr, dtype=np.int32), np.concatenate(nodes).astype(np.int32))
 
 
-def hex_box(nx, ny, nz, lengths=(1.0, 1.0, 1.0), jitter=0.15, seed=12345):
+def _hash_uniform(ids, seed, comp):
+    """U(-1, 1) as a pure function of (global node id, component, seed): splitmix64.  Any z-slab of a box can be generated
+    on its own with the node positions of the whole box (bench.py: one slab per GPU / per host thread of ONE mesh)."""
+    with np.errstate(over="ignore"):
+        x = ids.astype(np.uint64)*np.uint64(3) + np.uint64(comp) + np.uint64(seed)*np.uint64(0x9E3779B97F4A7C15)
+        x = x + np.uint64(0x9E3779B97F4A7C15)
+        x = (x ^ (x >> np.uint64(30)))*np.uint64(0xBF58476D1CE4E5B9)
+        x = (x ^ (x >> np.uint64(27)))*np.uint64(0x94D049BB133111EB)
+        x = x ^ (x >> np.uint64(31))
+    return (x >> np.uint64(11)).astype(np.float64)*(2.0/9007199254740992.0) - 1.0
+
+
+def hex_box(nx, ny, nz, lengths=(1.0, 1.0, 1.0), jitter=0.15, seed=12345, k0=0, nz_total=None):
     """Unit-box hexahedral mesh, cells numbered x-fastest, interior nodes jittered by
     ``jitter*h*U(-1,1)`` so that faces are non-planar and the LSQ problem is non-trivial
-    (SURVEY.md §8d config C3).  TRS order: xmin, xmax, ymin, ymax, zmin, zmax."""
+    (SURVEY.md §8d config C3).  TRS order: xmin, xmax, ymin, ymax, zmin, zmax.
+
+    ``nz_total`` given: the mesh is the slab of cell layers [k0, k0 + nz) of the box nx x ny x nz_total of extent
+    ``lengths``; the jitter is then a hash of the GLOBAL node index, so that slabs generated independently are pieces of
+    one mesh (node for node).  Its zmin / zmax TRSs are the cut planes when they are not the box sides."""
     lx, ly, lz = lengths
+    nzt = nz if nz_total is None else int(nz_total)
     xs = np.linspace(0.0, lx, nx + 1)
     ys = np.linspace(0.0, ly, ny + 1)
-    zs = np.linspace(0.0, lz, nz + 1)
+    zs = np.linspace(0.0, lz, nzt + 1)[k0:k0 + nz + 1]
     Z, Y, X = np.meshgrid(zs, ys, xs, indexing="ij")
     nodes = np.stack([X, Y, Z], axis=-1).astype(np.float64)
     if jitter > 0.0:
-        rng = np.random.RandomState(seed)
-        h = np.array([lx/nx, ly/ny, lz/nz])
-        d = jitter*h*(2.0*rng.random_sample(nodes.shape) - 1.0)
-        mask = np.zeros(nodes.shape[:3], dtype=bool)
-        mask[1:-1, 1:-1, 1:-1] = True
-        nodes = nodes + d*mask[..., None]
+        h = np.array([lx/nx, ly/ny, lz/nzt])
+        if nz_total is None:
+            rng = np.random.RandomState(seed)
+            u = 2.0*rng.random_sample(nodes.shape) - 1.0
+            mask = np.zeros(nodes.shape[:3], dtype=bool)
+            mask[1:-1, 1:-1, 1:-1] = True
+        else:
+            KK, JJ, II = np.meshgrid(np.arange(k0, k0 + nz + 1), np.arange(ny + 1), np.arange(nx + 1), indexing="ij")
+            gid = (KK.astype(np.int64)*(ny + 1) + JJ)*(nx + 1) + II
+            u = np.stack([_hash_uniform(gid, seed, c) for c in range(3)], axis=-1)
+            mask = (II > 0) & (II < nx) & (JJ > 0) & (JJ < ny) & (KK > 0) & (KK < nzt)
+        nodes = nodes + jitter*h*u*mask[..., None]
     nodes = nodes.reshape(-1, 3)
 
     def nid(i, j, k):

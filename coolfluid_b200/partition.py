@@ -86,7 +86,8 @@ class Partition:
         self.em = None              # local ElementMesh (TRS: the global ones restricted + "PartitionFaces")
         self.cell_l2g = None        # [nLocal] global cell id
         self.updatable = None       # [nLocal] uint8
-        self.n_interior = 0         # leading cells whose whole node neighbourhood is updatable
+        self.n_interior = 0         # cells whose whole node neighbourhood is updatable (leading range when order = "grouped")
+        self.indep = None           # the same cells as a list of local ids (order = "global")
         self.n_updatable = 0
         self.send = {}              # peer -> local ids (this rank's updatable cells that are overlap cells on peer)
         self.recv = {}              # peer -> local ids of overlap cells owned by peer
@@ -111,8 +112,16 @@ def _face_keys(cell_nodes_2d, shape):
     return -np.sort(-f, axis=2), lf
 
 
-def extract(em: ElementMesh, part: np.ndarray, rank: int, nranks: int | None = None, overlap: int = 2) -> Partition:
-    """Local mesh, maps and halo lists of ``rank`` for the element -> rank map ``part``."""
+def extract(em: ElementMesh, part: np.ndarray, rank: int, nranks: int | None = None, overlap: int = 2,
+            order: str = "global") -> Partition:
+    """Local mesh, maps and halo lists of ``rank`` for the element -> rank map ``part``.
+
+    order = "global" (default): local cells in ascending global ID.  Face creation order, face orientation (L = the
+    lower-ID cell), least-squares edge order and stencil order of every updatable cell are then those of the
+    single-domain mesh restricted to the partition, so the partitioned evaluation is BIT-IDENTICAL to the single-domain
+    one; the cells whose gradients may run while the halo is in flight are given as the list ``indep``.
+    order = "grouped": [interior | next to the overlap | overlap], the interior ones as a leading range
+    (``n_interior``); same values up to the summation order."""
     part = np.asarray(part)
     nranks = int(nranks if nranks is not None else part.max() + 1)
     n2c_ptr, n2c = _node_to_cells(em)
@@ -124,7 +133,10 @@ def extract(em: ElementMesh, part: np.ndarray, rank: int, nranks: int | None = N
     g_int = np.nonzero(own & ~near_other)[0]
     g_bnd = np.nonzero(own & near_other)[0]
     g_ovl = np.nonzero(local & ~own)[0]
-    l2g = np.concatenate([g_int, g_bnd, g_ovl]).astype(np.int64)
+    if order == "global":
+        l2g = np.sort(np.concatenate([g_int, g_bnd, g_ovl])).astype(np.int64)
+    else:
+        l2g = np.concatenate([g_int, g_bnd, g_ovl]).astype(np.int64)
     nl = len(l2g)
     g2l = np.full(em.n_cells, -1, dtype=np.int64)
     g2l[l2g] = np.arange(nl)
@@ -200,8 +212,9 @@ def extract(em: ElementMesh, part: np.ndarray, rank: int, nranks: int | None = N
     p.rank, p.nranks, p.em, p.cell_l2g = int(rank), nranks, lem, l2g
     p.node_l2g = used
     p.n_interior, p.n_updatable = len(g_int), len(g_int) + len(g_bnd)
-    p.updatable = np.zeros(nl, dtype=np.uint8)
-    p.updatable[:p.n_updatable] = 1
+    p.updatable = np.ascontiguousarray(own[l2g].astype(np.uint8))
+    if order == "global":
+        p.indep = g2l[g_int].astype(np.int32)          # ascending
     # halo lists (both sides sort by global id, so the packed orders agree without any handshake)
     for peer in np.unique(part[g_ovl]):
         peer = int(peer)

@@ -23,7 +23,7 @@ extern "C" {
 #endif
 
 #define CFB200_MAXEQ 9
-#define CFB200_ABI_VERSION 1
+#define CFB200_ABI_VERSION 2
 
 /* ---- enums: values are shared with the .CFcase option strings through the plugin ---- */
 enum cfb200_physical_model { CFB200_PM_EULER = 0, CFB200_PM_MHD3D_PROJECTION = 1 };
@@ -114,7 +114,18 @@ typedef struct cfb200_config {
   double refSpeed;          /* MHD3DProjection.ConvTerm.refSpeed */
   double coeffSigmoid;      /* AUSMFlux.ci:64 coeffSigmoid (default 1e-8), analytic Jacobian only */
   int32_t derivativeStrategy; /* cfb200_derivative: CellCenterFVM.Data.DerivativeStrategy (CellCenterFVMData.cxx:298) */
-  int32_t reserved0;
+  /* 1: cfb200_compute_rhs also applies the pseudo-steady time term (what cfb200_time_rhs does) inside its residual and
+   * diagonal gathers: the diagonal blocks and rhs are written once instead of being re-read and re-written by a third
+   * kernel.  Same operations in the same order: the results are bit-identical to compute_rhs followed by time_rhs.
+   * Not available with timeUseGlobalDT (the global minimum needs the complete updateCoeff first). */
+  int32_t fuseTimeRhs;
+  /* FVMCC_StdComputeTimeRhs / FVMCC_PseudoSteadyTimeRhs options (FVMCC_StdComputeTimeRhs.cxx:42-57,
+   * FVMCC_PseudoSteadyTimeRhs.cxx:40-46,150-175) */
+  int32_t timeZeroDiag[CFB200_MAXEQ]; /* zeroDiagValue: equations whose time term is dropped (MHD phi equation) */
+  int32_t timeAnalyticalMatrix;       /* useAnalyticalMatrix: dU/dP from Euler2DPuvtToConsInPuvt / Euler3DPvtToConsInPvt */
+  int32_t timeUseGlobalDT;            /* useGlobalDT: diag = V / min_cells(V/updateCoeff*CFL) */
+  int32_t reserved1;
+  double dt;                          /* SubSystemStatus::getDT(): > 0 (unsteady) -> diag = V/dt, else updateCoeff/CFL */
 } cfb200_config;
 
 /* Flat mesh data = the contents of the reference's sockets and connectivity tables (SURVEY.md §8b "Data ownership").
@@ -249,6 +260,10 @@ int cfb200_comm_init(cfb200_handle* h, int rank, int nRanks, const void* id128);
  * stencil (their gradients are computed while an exchange is in flight); 0 = no overlap of compute and exchange */
 int cfb200_set_halo(cfb200_handle* h, const int32_t* sendPtr, const int32_t* sendCells,
                     const int32_t* recvPtr, const int32_t* recvCells, int32_t nIndependent);
+/* the independent cells as a LIST instead of a leading range (overrides nIndependent): the local numbering is then free.
+ * With local cells in ascending global ID every gather of an updatable cell runs in the order of the single-domain run, so
+ * a partitioned evaluation is bit-identical to it (tests/test_gpu_multi.py, bench.py `parity`). */
+int cfb200_set_independent_cells(cfb200_handle* h, const int32_t* cells, int32_t n);
 /* starts the exchange (pack kernel, NCCL send/recv group and unpack kernel on a communication stream) and returns;
  * the next cfb200_compute_rhs overlaps it with the work that does not depend on received states */
 int cfb200_halo_begin(cfb200_handle* h);

@@ -214,6 +214,34 @@ struct Phys {
     r[TID] = p/(c.gamma - 1.) + 0.5*rho*V2;
   }
 
+  // dU/dP of the update -> solution transformation, row-major Q x Q: Euler2DPuvtToConsInPuvt.cxx:42-67,
+  // Euler3DPvtToConsInPvt.cxx:42-76; identity for conservative update variables (IdentityVarSetMatrixTransformer)
+  static void updateToSolutionMatrix(const Config& c, const double* state, double* M) {
+    for (int i = 0; i < Q*Q; ++i) M[i] = 0.;
+    if (c.updateVar == UV_CONS) { for (int i = 0; i < Q; ++i) M[i*Q + i] = 1.; return; }
+    const double R = c.R;
+    const double p = state[0] + c.pOffset;
+    const double T = state[TID];
+    const double rho = p/(R*T);
+    const double rhoOvT = rho/T;
+    const double invRT = 1./(R*T);
+    double V2;
+    if (D == 2) V2 = state[1]*state[1] + state[2]*state[2];
+    else V2 = state[1]*state[1] + state[2]*state[2] + state[3]*state[3];
+    const double gammaMinus1 = c.gamma - 1.;
+    M[0*Q + 0] = invRT;
+    M[0*Q + TID] = -rhoOvT;
+    for (int i = 0; i < D; ++i) {
+      const double u = state[1+i];
+      M[(1+i)*Q + 0] = u*invRT;
+      M[(1+i)*Q + 1+i] = rho;
+      M[(1+i)*Q + TID] = -rhoOvT*u;
+      M[TID*Q + 1+i] = rho*u;
+    }
+    M[TID*Q + 0] = 1./gammaMinus1 + 0.5*V2*invRT;
+    M[TID*Q + TID] = -0.5*rhoOvT*V2;
+  }
+
   // Euler2DConsToRoe.cxx:41-52, Euler3DConsToRoe.cxx:41-58
   static void consToRoe(const Config& c, const double* s, double* r) {
     const double gamma = c.gamma;
@@ -938,6 +966,10 @@ struct MhdPhys {
     return emax;
   }
   static void toCons(const Config&, const double* s, double* r) { for (int i = 0; i < Q; ++i) r[i] = s[i]; }
+  static void updateToSolutionMatrix(const Config&, const double*, double* M) {      // update = solution = Cons
+    for (int i = 0; i < Q*Q; ++i) M[i] = 0.;
+    for (int i = 0; i < Q; ++i) M[i*Q + i] = 1.;
+  }
 
   // LaxFriedFlux.cxx:79-118 and HLLFlux.cxx:73-133 on the MHD variable set (update = solution = Cons)
   static bool centredFlux(const Config& c, const double* uL, const double* uR, const MhdData& pL, const MhdData& pR,

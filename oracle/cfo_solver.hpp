@@ -816,21 +816,32 @@ public:
     }
   }
 
-  // ---- pseudo-steady time term (a21): FVMCC_PseudoSteadyTimeRhs.cxx:106-262
-  // (steady: dt == 0 -> diag = updateCoeff/CFL; numerical transformation matrix)
+  // ---- pseudo-steady time term (a21): FVMCC_PseudoSteadyTimeRhs::execute (FVMCC_PseudoSteadyTimeRhs.cxx:106-175):
+  //   diag = V/dt when dt > 0 (unsteady), updateCoeff/CFL otherwise; with useGlobalDT: V/min_cells(V/updateCoeff*CFL)
+  //   (the reference takes the minimum over all local states, :121-127); zeroDiagValue drops the term of an equation;
+  //   numerical (:197-262) or analytical (:266-310) transformation matrix dU/dP
   void pseudoSteadyTimeRhs(double* U, const double* pastU, Outputs& o) const {
     const bool doJac = cfg.computeJacobian && o.bsrVal;
+    const double dt = cfg.dt;
+    double minDt = 0.0;
+    if (cfg.timeUseGlobalDT) {
+      minDt = mesh.volumes[0]/o.updateCoeff[0]*cfg.cfl;
+      for (int c = 1; c < mesh.nCells; ++c) minDt = std::min(mesh.volumes[c]/o.updateCoeff[c]*cfg.cfl, minDt);
+    }
     for (int c = 0; c < mesh.nCells; ++c) {
-      const double diagValue = o.updateCoeff[c]/cfg.cfl;
+      double diagValue;
+      if (!cfg.timeUseGlobalDT) diagValue = (dt > 0.0) ? mesh.volumes[c]/dt : o.updateCoeff[c]/cfg.cfl;
+      else diagValue = mesh.volumes[c]/minDt;
       if (!mesh.updatable[c]) continue;
       double tempState[Q], tPast[Q], tPert[Q], fluxDiff[Q];
       P::toCons(cfg, &U[(size_t)c*Q], tempState);
       P::toCons(cfg, &pastU[(size_t)c*Q], tPast);
       for (int iEq = 0; iEq < Q; ++iEq) {
         const double dU = tempState[iEq] - tPast[iEq];
-        o.rhs[(size_t)c*Q + iEq] -= dU*diagValue*cfg.resFactor;
+        o.rhs[(size_t)c*Q + iEq] -= (!cfg.timeZeroDiag[iEq]) ? dU*diagValue*cfg.resFactor : 0.0;
       }
-      if (doJac) {
+      if (!doJac) continue;
+      if (!cfg.timeAnalyticalMatrix) {
         for (int iVar = 0; iVar < Q; ++iVar) {
           double& val = U[(size_t)c*Q + iVar];
           const double orig = val;
@@ -839,9 +850,19 @@ public:
           P::toCons(cfg, &U[(size_t)c*Q], tPert);
           const double invEps = 1./eps;
           for (int i = 0; i < Q; ++i) fluxDiff[i] = (tPert[i] - tempState[i])*invEps;
-          for (int i = 0; i < Q; ++i) fluxDiff[i] *= diagValue*cfg.resFactor;
+          for (int i = 0; i < Q; ++i) fluxDiff[i] *= (!cfg.timeZeroDiag[i]) ? diagValue*cfg.resFactor : 0.0;
           addColumn(o, c, c, iVar, fluxDiff);
           val = orig;
+        }
+      } else {
+        // computeAnalyticalTransMatrix: value = matrix(iVar,jVar)*diag*resFactor added where !zeroDiagValue[jVar] (sic: the
+        // flag is tested on the COLUMN index there)
+        double M[Q*Q];
+        P::updateToSolutionMatrix(cfg, &U[(size_t)c*Q], M);
+        for (int jVar = 0; jVar < Q; ++jVar) {
+          if (cfg.timeZeroDiag[jVar]) continue;
+          for (int iVar = 0; iVar < Q; ++iVar) fluxDiff[iVar] = M[iVar*Q + jVar]*diagValue*cfg.resFactor;
+          addColumn(o, c, c, jVar, fluxDiff);
         }
       }
     }

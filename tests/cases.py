@@ -377,3 +377,61 @@ def check_bc_face_values(oracle, engine_factory):
         assert np.array_equal(rhs2, r2.rhs) and not np.array_equal(rhs2, rhs)
     finally:
         e.close()
+
+
+def check_time_term_variants(oracle, engine_factory):
+    """a21 FVMCC_PseudoSteadyTimeRhs in all its branches (steady updateCoeff/CFL, dt > 0, useGlobalDT, zeroDiagValue,
+    numerical / analytical dU/dP), as a separate call (cfb200_time_rhs) and fused into compute_rhs (cfg.fuseTimeRhs):
+    rhs and the block Jacobian bit-identical to the oracle's compute + time_rhs in every variant."""
+    variants = [
+        ("ns3d_hex", {}),
+        ("ns3d_hex", {"dt": 1e-3}),
+        ("ns3d_hex", {"timeAnalyticalMatrix": 1}),
+        ("ns3d_hex", {"timeAnalyticalMatrix": 1, "zero": [0, 1, 0, 0, 1]}),
+        ("ns3d_hex", {"timeUseGlobalDT": 1}),
+        ("ns2d_quad", {"timeAnalyticalMatrix": 1, "dt": 2e-3}),
+        ("euler2d_2nd_quad", {"zero": [0, 0, 1, 0]}),
+        ("euler2d_2nd_quad", {"timeAnalyticalMatrix": 1}),
+        ("mhd3d_hex_hll", {"zero": [0, 0, 0, 0, 0, 0, 0, 0, 1]}),     # the phi equation of the divergence cleaning
+        ("mhd3d_hex_hll", {"timeAnalyticalMatrix": 1, "zero": [0, 0, 0, 0, 0, 0, 0, 0, 1]}),
+    ]
+    for name, opts in variants:
+        mesh_f, cfg_f, bcs_f, pvt = CASES[name]
+        fm = oracle.build_mesh(mesh_f())
+        bcs = bcs_f()
+
+        def cfg_with(fuse):
+            c = cfg_f()
+            c.cfl = 2.5
+            for k, v in opts.items():
+                if k == "zero":
+                    for i, z in enumerate(v):
+                        c.timeZeroDiag[i] = z
+                else:
+                    setattr(c, k, v)
+            c.fuseTimeRhs = fuse
+            return c
+        q = cfg_f().nEqs
+        U = init_state(fm, q, pvt)
+        past = U[:fm.nCells*q]*(1 + 1e-3)
+        Ug = U.copy()
+        c0 = cfg_with(0)
+        r = oracle.compute(c0, fm, bcs, Ug, jacobian=True)
+        oracle.time_rhs(c0, fm, bcs, Ug, np.concatenate([past, np.zeros(fm.nGhosts*q)]), r)
+        for fuse in (0, 1):
+            if fuse and opts.get("timeUseGlobalDT"):
+                continue
+            e = engine_factory(cfg_with(fuse))
+            try:
+                e.set_mesh(fm, bcs)
+                e.set_states(U[:fm.nCells*q])
+                e.set_past_states(past)
+                rhs, uc = e.compute_rhs()
+                if not fuse:
+                    rhs = e.time_rhs()
+                jac = e.bsr_values()
+            finally:
+                e.close()
+            assert np.array_equal(rhs, r.rhs), (name, opts, fuse, "rhs")
+            assert np.array_equal(uc, r.updateCoeff), (name, opts, fuse, "updateCoeff")
+            assert np.array_equal(jac, r.bsrVal), (name, opts, fuse, "jacobian")

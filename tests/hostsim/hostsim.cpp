@@ -48,6 +48,7 @@ struct HostLoopBackend {
       }
   }
   double sumOrdered(double* x, int n) { double s = 0.; for (int i = 0; i < n; ++i) s += x[i]; return s; }
+  double minOrdered(double* x, int n) { double m = x[0]; for (int i = 1; i < n; ++i) m = (x[i] < m) ? x[i] : m; return m; }
 };
 }
 

@@ -91,8 +91,25 @@ def run(rank, world, mode, name, steps, out_dir, cfl=0.5, overlap_mode=True):
                     e.halo_exchange()
             hist.append(0.5*np.log10(tot) if tot > 0 else -np.inf)
         U = e.get_states().reshape(-1, q)
-        np.savez(os.path.join(out_dir, "rank%d.npz" % rank), U=U[:p.n_updatable], gid=p.cell_l2g[:p.n_updatable],
-                 hist=np.array(hist), Uall=U, gall=p.cell_l2g)
+        # one implicit evaluation on top (overlap states in place): residual + block Jacobian + fused pseudo-steady term
+        jc = cfg_f()
+        jc.fuseTimeRhs = 1
+        jc.cfl = 3.0
+        e.set_step(jc)
+        e.backup_past_states()
+        e.set_update_coeff(None)
+        if mode != "hostsim":
+            e.halo_begin()              # joined inside compute_rhs (overlapped with the independent gradients)
+        rhs, uc = e.compute_rhs()
+        jac = e.bsr_values().reshape(-1, q*q)
+        rp, ci = e.bsr_pattern()
+        upd = p.updatable == 1
+        rows = np.nonzero(upd)[0]
+        blk_row = np.repeat(np.arange(fm.nCells), np.diff(rp))
+        keep = upd[blk_row]
+        np.savez(os.path.join(out_dir, "rank%d.npz" % rank), U=U[upd], gid=p.cell_l2g[upd],
+                 hist=np.array(hist), Uall=U, gall=p.cell_l2g, rhs=rhs.reshape(-1, q)[upd], uc=uc[upd],
+                 jac=jac[keep], jrow=p.cell_l2g[blk_row[keep]], jcol=p.cell_l2g[ci[keep]])
         e.close()
     finally:
         dist.barrier()
@@ -119,8 +136,18 @@ def single_domain(name, steps, lib, cfl=0.5, device=0):
         e.compute_rhs(apply_bc=True, download=False)
         hist.append(e.update_sol_fwd_euler(cfl, 0))
     U = e.get_states().reshape(-1, q)
+    jc = cfg_f()
+    jc.fuseTimeRhs = 1
+    jc.cfl = 3.0
+    e.set_step(jc)
+    e.backup_past_states()
+    e.set_update_coeff(None)
+    rhs, uc = e.compute_rhs()
+    jac = e.bsr_values().reshape(-1, q*q)
+    rp, ci = e.bsr_pattern()
     e.close()
-    return U, np.array(hist)
+    extra = dict(rhs=rhs.reshape(-1, q), uc=uc, jac=jac, rowPtr=rp, colInd=ci)
+    return U, np.array(hist), extra
 
 
 if __name__ == "__main__":

@@ -254,6 +254,10 @@ def test_bad_value_is_reported(product_lib):
         e.close()
 
 
+def test_time_term_variants_separate_and_fused(oracle, product_lib):
+    cases.check_time_term_variants(oracle, _factory(product_lib))
+
+
 def test_position_dependent_inlet(oracle, product_lib):
     cases.check_bc_face_values(oracle, _factory(product_lib))
 

@@ -84,6 +84,10 @@ def test_bad_value_is_reported(oracle, hostsim_lib):
         e.close()
 
 
+def test_time_term_variants_separate_and_fused(oracle, hostsim_lib):
+    cases.check_time_term_variants(oracle, _engine_factory(hostsim_lib))
+
+
 def test_newton_update(hostsim_lib):
     from oracle import binding as ob
     cases.check_newton_update(_engine_factory(hostsim_lib), ob.build_mesh)
