@@ -90,6 +90,49 @@ __global__ void __launch_bounds__(BS, MINB) k_staged2(const F f, const int n) {
   }
 }
 
+// Phased functors (F::begin, F::phase(ph), F::slot(f, ph)): the per-face state lives in registers across the two phases,
+// each phase leaves ONE finished block in the thread's staging area, which the warp writes out (whole rows, coalesced)
+// before the next phase reuses the area.  Warps stay independent (no block-wide barrier).
+template <class F, int BS, int MINB>
+__global__ void __launch_bounds__(BS, MINB) k_phased(const F f, const int n) {
+  extern __shared__ double sm[];
+  constexpr int STRIDE = BS + 1;
+  const int t = threadIdx.x, lane = t & 31, warpBase = t & ~31;
+  const int i = blockIdx.x*BS + t;
+  typename F::State st;
+  const bool valid = i < n;
+  const bool active = valid && f.begin(i, st, sm + t, STRIDE);
+  double* out = f.out();
+  constexpr int WB = (F::BLK % 5 == 0) ? 5 : 4;
+  static_assert(F::BLK % WB == 0 && F::BLK <= 32 && 2*F::BLK >= 32, "write-out batch");
+#pragma unroll 1
+  for (int ph = 0; ph < 2; ++ph) {
+    if (active) f.phase(ph, st, sm + t, STRIDE);
+    sm[F::SLOTROW*STRIDE + t] = __hiloint2double(0, valid ? f.slot(i, ph) : -1);
+    __syncwarp();
+    // entry e = lane + 32*it of the warp's 32 x BLK finished values: face lf = e / BLK, k = e % BLK, kept incrementally
+    int k = lane, lf = 0;
+    if (k >= F::BLK) { k -= F::BLK; ++lf; }
+#pragma unroll 1
+    for (int it = 0; it < F::BLK; it += WB) {
+      double x[WB]; size_t dst[WB]; bool on[WB];
+#pragma unroll
+      for (int j = 0; j < WB; ++j) {
+        const int slot = __double2loint(sm[F::SLOTROW*STRIDE + warpBase + lf]);
+        x[j] = sm[k*STRIDE + warpBase + lf];
+        on[j] = slot >= 0;
+        dst[j] = (size_t)slot*F::BLK + k;
+        k += 32;
+        if (k >= F::BLK) { k -= F::BLK; ++lf; }
+        if (k >= F::BLK) { k -= F::BLK; ++lf; }
+      }
+#pragma unroll
+      for (int j = 0; j < WB; ++j) if (on[j]) out[dst[j]] = x[j];
+    }
+    __syncwarp();
+  }
+}
+
 // fixed-shape block sum (run-to-run deterministic): each block reduces 1024 consecutive entries
 __global__ void __launch_bounds__(256) k_block_sum(const double* __restrict__ x, double* __restrict__ out, int n) {
   __shared__ double s[256];
@@ -123,6 +166,9 @@ template <class F> struct HasMinB<F, std::void_t<decltype(F::MINB)> > : std::tru
 struct CudaBackend {
   int dev = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t copyStream = nullptr;       // device -> host copies that overlap the kernels still to run (d2hOverlapped)
+  cudaEvent_t copyReady = nullptr;
+  bool copiesInFlight = false;
   bool timing = false;
   struct Ev { const char* name; cudaEvent_t a, b; };
   std::vector<Ev> evs;
@@ -137,9 +183,13 @@ struct CudaBackend {
     if (device < 0 || device >= count) throw DeviceError(CFB200_ERR_INVALID_ARG, "device ordinal out of range");
     CFB_CUDA(cudaSetDevice(dev));
     CFB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    CFB_CUDA(cudaStreamCreateWithFlags(&copyStream, cudaStreamNonBlocking));
+    CFB_CUDA(cudaEventCreateWithFlags(&copyReady, cudaEventDisableTiming));
   }
   ~CudaBackend() {
     cudaSetDevice(dev);
+    if (copyStream) { cudaStreamSynchronize(copyStream); cudaStreamDestroy(copyStream); }
+    if (copyReady) cudaEventDestroy(copyReady);
     for (auto& e : evs) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     if (stream) cudaStreamDestroy(stream);
   }
@@ -156,6 +206,21 @@ struct CudaBackend {
   void d2h(void* dst, const void* src, size_t bytes) {
     CFB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, stream));
     CFB_CUDA(cudaStreamSynchronize(stream));
+  }
+  // device -> host copy of data that is final at this point of the stream, on the copy stream: it runs while the kernels
+  // launched afterwards execute (PCIe and the SMs are independent); joinCopies() before the host reads it
+  void d2hOverlapped(void* dst, const void* src, size_t bytes) {
+    if (!copiesInFlight) {
+      CFB_CUDA(cudaEventRecord(copyReady, stream));
+      CFB_CUDA(cudaStreamWaitEvent(copyStream, copyReady, 0));
+      copiesInFlight = true;
+    }
+    CFB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, copyStream));
+  }
+  void joinCopies() {
+    if (!copiesInFlight) return;
+    copiesInFlight = false;
+    CFB_CUDA(cudaStreamSynchronize(copyStream));
   }
   void d2d(void* dst, const void* src, size_t bytes) { CFB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, stream)); }
   void memset(void* p, int v, size_t bytes) { CFB_CUDA(cudaMemsetAsync(p, v, bytes, stream)); }
@@ -218,6 +283,25 @@ struct CudaBackend {
     // compiled: they tripled the build time of the face kernels)
     (void)minBlocks;
     go(k_staged<F, 128, 2>, 128);                       //  8 warps per SM, 255 registers
+    CFB_CUDA(cudaGetLastError());
+    if (ev) CFB_CUDA(cudaEventRecord(ev->b, stream));
+  }
+
+  // three resident 128-thread blocks per SM (168 registers), F::STAGE doubles of staging per thread
+  template <class F> void launchPhased(const char* name, const F& f, int n) {
+    if (n <= 0) return;
+    Ev* ev = nullptr;
+    if (timing) {
+      if (nEv == evs.size()) { Ev e; e.name = name; CFB_CUDA(cudaEventCreate(&e.a)); CFB_CUDA(cudaEventCreate(&e.b)); evs.push_back(e); }
+      ev = &evs[nEv++]; ev->name = name;
+      CFB_CUDA(cudaEventRecord(ev->a, stream));
+    }
+    constexpr int BS = 128;
+    const size_t smem = (size_t)F::STAGE*(BS + 1)*sizeof(double);
+    auto kern = k_phased<F, BS, 3>;
+    CFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    kern<<<(n + BS - 1)/BS, BS, smem, stream>>>(f, n);
     CFB_CUDA(cudaGetLastError());
     if (ev) CFB_CUDA(cudaEventRecord(ev->b, stream));
   }

@@ -65,7 +65,9 @@ public:
   int lastStatus = 0;
   double* bcFaceVal = nullptr; uint8_t* bcFaceFlag = nullptr;      // device copies behind Dev::bcFaceVal / bcFaceFlag
   std::vector<double> hBcFaceVal; std::vector<uint8_t> hBcFaceFlag; std::vector<int32_t> hGhostBC;
-  bool roePipeline = true; // false (CFB200_ROE_PIPELINE=0): the rolled, non-pipelined FD loop of the Roe families (A/B measurements)
+  // FD loop of the Roe families (CFB200_ROE_PIPELINE, for A/B measurements): 0 = rolled loop, 1 = software-pipelined,
+  // 2 = software-pipelined in two phases with three resident blocks per SM (DiamondVolume; Corrected uses 1)
+  int roePipeline = 1;
   int faceShape = 2;       // resident 128-thread blocks per SM the interior-face Jacobian kernel is compiled for
                            // (CudaBackend::launchStaged): 2 -> 255 registers, no spills: measured fastest on B200 (profiles/)
   // multi-GPU (cfb_halo.cuh): a state halo exchange may be in flight when computeRhs is called; the first nIndep
@@ -88,7 +90,10 @@ public:
 
   explicit Engine(const Cfg& c, int device) : cfg(c), bk(device) {
     std::memset(&d, 0, sizeof(d));
-    if (const char* v = std::getenv("CFB200_ROE_PIPELINE")) roePipeline = (std::atoi(v) != 0);
+    if (const char* v = std::getenv("CFB200_ROE_PIPELINE")) roePipeline = std::atoi(v);
+    // faces ahead whose gathers the interior-face Jacobian kernels prefetch into L2: one wave of resident blocks
+    d.prefetchAhead = 2*148*128;
+    if (const char* v = std::getenv("CFB200_PREFETCH_AHEAD")) d.prefetchAhead = std::atoi(v);
   }
   ~Engine() { for (void* p : owned) bk.free(p); }
 
@@ -316,6 +321,14 @@ public:
     if (doJac && cfg.computeJacobian == 2) {
       bk.launchStaged("innerFaceJacAnalytic", AnalyticInnerFaceK<D>{d, cfg}, d.nInner, faceShape);
       bk.launch("boundaryFaceJac", BoundaryFaceK<D, true, 0>{d, cfg}, d.nGhosts, 128);
+    } else if (doJac && (fam == 0 || fam == 3) && roePipeline == 2 && DV == 0) {
+      // Roe families, DiamondVolume: two phases, three resident blocks per SM
+      const bool cons = (cfg.updateVar == CFB200_UV_CONS);
+      if (fam == 0 && cons) bk.launchPhased("innerFaceJac", InnerFacePhased<D, 0, CFB200_UV_CONS>{d, cfg}, d.nInner);
+      else if (fam == 0) bk.launchPhased("innerFaceJac", InnerFacePhased<D, 0, CFB200_UV_PVT>{d, cfg}, d.nInner);
+      else if (cons) bk.launchPhased("innerFaceJac", InnerFacePhased<D, 3, CFB200_UV_CONS>{d, cfg}, d.nInner);
+      else bk.launchPhased("innerFaceJac", InnerFacePhased<D, 3, CFB200_UV_PVT>{d, cfg}, d.nInner);
+      bk.launch("boundaryFaceJac", BoundaryFaceK<D, true, DV>{d, cfg}, d.nGhosts, 128);
     } else if (doJac && (fam == 0 || fam == 3) && roePipeline) {
       // Roe families: update-variable set fixed at compile time, software-pipelined finite-difference loop
       const bool cons = (cfg.updateVar == CFB200_UV_CONS);
@@ -339,7 +352,9 @@ public:
     }
   }
 
-  template <int D, class PH> void computeRhs_(bool applyBC) {
+  // hostRhs / hostUc (optional): host copies of rhs / updateCoeff, started as soon as CellGather has produced them and
+  // overlapped with the diagonal gather (the callers of the reference read them right after ComputeRHS: UpdateSol.cxx:83)
+  template <int D, class PH> void computeRhs_(bool applyBC, double* hostRhs, double* hostUc) {
     const bool doJac = cfg.computeJacobian != 0;
     if (doJac) ensureJacobian();
     bk.resetTimings();
@@ -380,19 +395,20 @@ public:
       else faceKernels_<D, 0>(doJac, faceShape);
     }
     bk.launch("cellGather", CellGather<D, PH>{d, cfg}, d.nCells, 256);
+    if (hostRhs) bk.d2hOverlapped(hostRhs, d.rhs, sizeof(double)*d.nCells*PH::Q);
+    if (hostUc) bk.d2hOverlapped(hostUc, d.updateCoeff, sizeof(double)*d.nCells);
     if (doJac) {
       // one thread per (cell, block entry): launched in chunks of < 2^31 entries (q = 9: 26.5 M cells per chunk)
-      const long long CH = 1LL << 30;
-      const long long nd = (long long)d.nCells*DiagGather<D, PH>::GS;
-      for (long long b0 = 0; b0 < nd; b0 += CH)
-        bk.launch("diagGather", DiagGather<D, PH>{d, cfg, b0}, (int)std::min(CH, nd - b0), 256);
-      const long long nz = (long long)nNonUpd*ZeroRows<D, PH>::GS;
-      for (long long b0 = 0; b0 < nz; b0 += CH)
-        bk.launch("zeroRows", ZeroRows<D, PH>{d, nonUpdCells, b0}, (int)std::min(CH, nz - b0), 256);
+      const int CH = (1 << 30)/DiagGather<D, PH>::GS;          // cells per launch
+      for (int c0 = 0; c0 < d.nCells; c0 += CH)
+        bk.launch("diagGather", DiagGather<D, PH>{d, c0, cfg.fuseTimeRhs}, std::min(CH, d.nCells - c0)*DiagGather<D, PH>::GS, 256);
+      for (int c0 = 0; c0 < nNonUpd; c0 += CH)
+        bk.launch("zeroRows", ZeroRows<D, PH>{d, nonUpdCells, c0}, std::min(CH, nNonUpd - c0)*ZeroRows<D, PH>::GS, 256);
     }
     timeTermApplied = (cfg.fuseTimeRhs != 0);
     int st = 0;
     bk.d2h(&st, d.status, sizeof(int));   // synchronises
+    bk.joinCopies();
     lastStatus = st;
   }
   bool isMhd() const { return cfg.physicalModel == CFB200_PM_MHD3D_PROJECTION; }
@@ -400,9 +416,12 @@ public:
     if (isMhd()) applyBC_<3, MhdPhys>(); else if (cfg.dim == 2) applyBC_<2, Phys<2> >(); else applyBC_<3, Phys<3> >();
     bk.sync();
   }
-  void computeRhs(bool applyBCFirst) {
-    if (isMhd()) computeRhs_<3, MhdPhys>(applyBCFirst);
-    else if (cfg.dim == 2) computeRhs_<2, Phys<2> >(applyBCFirst); else computeRhs_<3, Phys<3> >(applyBCFirst);
+  void computeRhs(bool applyBCFirst, double* hostRhs = nullptr, double* hostUc = nullptr) {
+    try {
+      if (isMhd()) computeRhs_<3, MhdPhys>(applyBCFirst, hostRhs, hostUc);
+      else if (cfg.dim == 2) computeRhs_<2, Phys<2> >(applyBCFirst, hostRhs, hostUc);
+      else computeRhs_<3, Phys<3> >(applyBCFirst, hostRhs, hostUc);
+    } catch (...) { try { bk.joinCopies(); } catch (...) {} throw; }
   }
   template <int D, class PH> void timeRhs_() {
     const int doJac = cfg.computeJacobian && d.bsrVal;

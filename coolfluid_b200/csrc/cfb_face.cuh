@@ -423,17 +423,25 @@ struct FaceWork {
   // What lives across iterations is parked in the thread's shared-memory staging area (entry k at stg[k*stride]):
   //   [0, 2QQ) blocks | side L: s z f (un a) | side R: s z f (un a) | base flux (diffusive base flux before it = -1) | gL | gR
   // both unperturbed sides are parked once, the perturbed one is rebuilt per iteration.
+  // NB = output blocks staged at a time: 2 (both, k_staged) or 1 (one per phase, k_phased: the staging area then fits three
+  // resident blocks per SM)
   static constexpr int RP_NSIDE(bool efix) { return 3*Q + (efix ? 2 : 0); }
-  static constexpr int RP_STAGE(bool efix) { return 2*Q*Q + 2*RP_NSIDE(efix) + 3*Q; }
+  static constexpr int RP_STAGE(bool efix, int nb = 2) { return nb*Q*Q + 2*RP_NSIDE(efix) + 3*Q; }
   struct RoeHand { PData lin; double dU[Q], sumF[Q], eps, lc; bool ok; };   // front -> back
-  template <bool EFIX, int UV>
-  CFB_HD void roeFront(const Dev& d, const Cfg& c, int it, const double* vL, const double* vR, const double* stg,
+  // the cell value perturbed at iteration `it` (the base evaluation reads any): loaded two iterations ahead by the callers
+  CFB_HD double roeOrig(const Dev& d, int it) const {
+    const int side = (it >= Q) ? 1 : 0;
+    const int iVar = it - side*Q;
+    const int iv = (iVar < 0) ? 0 : iVar;
+    return d.U[(size_t)iv*d.nStates + (side ? R : L)];
+  }
+  template <bool EFIX, int UV, int NB = 2>
+  CFB_HD void roeFront(const Dev& d, const Cfg& c, int it, double orig, const double* vL, const double* vR, const double* stg,
                        int stride, RoeHand& h) const {
-    constexpr int NS = RP_NSIDE(EFIX), OFF_SIDES = 2*Q*Q, OFF_G = 2*Q*Q + 2*NS + Q;
+    constexpr int NS = RP_NSIDE(EFIX), OFF_SIDES = NB*Q*Q, OFF_G = NB*Q*Q + 2*NS + Q;
     const int side = (it >= Q) ? 1 : 0;
     const int iVar = it - side*Q;                  // -1: the base evaluation
     const int iv = (iVar < 0) ? 0 : iVar;
-    const double orig = d.U[(size_t)iv*d.nStates + (side ? R : L)];
     const double gp = stg[(size_t)(OFF_G + side*Q + iv)*stride];
     const double eps = fdEps(c, iv, orig);
     const double pv = orig + eps;
@@ -461,9 +469,9 @@ struct FaceWork {
     if constexpr (EFIX) h.lc = P::lambdaCorrOf(p.un, p.A, fx[(size_t)(3*Q)*stride], fx[(size_t)(3*Q + 1)*stride]);
     h.eps = eps;
   }
-  template <bool EFIX>
+  template <bool EFIX, int NB = 2>
   CFB_HD void roeBack(const Dev& d, const Cfg& c, int it, const RoeHand& h, bool hasDiff, double* stg, int stride) const {
-    constexpr int NS = RP_NSIDE(EFIX), OFF_FLUX = 2*Q*Q + 2*NS;
+    constexpr int NS = RP_NSIDE(EFIX), OFF_FLUX = NB*Q*Q + 2*NS;
     double Lm[Q*Q];
     typename P::RCoef rc;
     if constexpr (EFIX) P::leftScaled(c, h.lin, n, Lm, rc, c.entropyFixID, h.lc); else P::leftScaled(c, h.lin, n, Lm, rc);
@@ -476,9 +484,12 @@ struct FaceWork {
       double res = 0.;
 #pragma unroll
       for (int k = 0; k < Q; ++k) {
-        double m = 0.;
+        // m = 0 + R(i,0) L(0,k) + ... in the reference's accumulation; the leading `0 +` is dropped: it only turns a -0
+        // product into +0, a difference that survives to m solely when every term is a zero, and then
+        // res += (k*m)*dU adds a zero of either sign to a sum that starts from +0: the same res, bit for bit
+        double m = Ri[0]*Lm[k];
 #pragma unroll
-        for (int mm = 0; mm < Q; ++mm) m += Ri[mm]*Lm[mm*Q+k];
+        for (int mm = 1; mm < Q; ++mm) m += Ri[mm]*Lm[mm*Q+k];
         res += (kred*m)*h.dU[k];
       }
       pf[i] = 0.5*(h.sumF[i] - res);
@@ -499,7 +510,7 @@ struct FaceWork {
         d.faceFlux[(size_t)v*d.nFaces + f] = x;
       }
     } else {
-      double* blk = stg + (size_t)(side*Q*Q + iVar)*stride;      // column iVar of block(R,L) (side 0) / block(L,R) (side 1)
+      double* blk = stg + (size_t)((NB == 2 ? side*Q*Q : 0) + iVar)*stride;   // column iVar of block(R,L) (side 0) / block(L,R) (side 1)
       const double invEps = ddiv(1., h.eps);
       const double rf = c.resFactor;
 #pragma unroll
@@ -536,14 +547,137 @@ struct FaceWork {
       if constexpr (EFIX) { fx[(size_t)(3*Q)*stride] = fixed.un; fx[(size_t)(3*Q + 1)*stride] = fixed.A; }
     }
     RoeHand cur;
-    roeFront<EFIX, UV>(d, c, -1, vL, vR, stg, stride, cur);
+    roeFront<EFIX, UV>(d, c, -1, roeOrig(d, -1), vL, vR, stg, stride, cur);
+    double origNext = roeOrig(d, 0);
 #pragma unroll 1
     for (int it = -1; it < 2*Q; ++it) {
       RoeHand nxt;
       const int itn = (it + 1 < 2*Q) ? it + 1 : it;      // the last iteration has no successor: its front half is recomputed and dropped
-      roeFront<EFIX, UV>(d, c, itn, vL, vR, stg, stride, nxt);
+      const double origAfter = roeOrig(d, (it + 2 < 2*Q) ? it + 2 : 2*Q - 1);   // consumed by the NEXT iteration's front half
+      roeFront<EFIX, UV>(d, c, itn, origNext, vL, vR, stg, stride, nxt);
       roeBack<EFIX>(d, c, it, cur, hasDiff, stg, stride);
       cur = nxt;
+      origNext = origAfter;
+    }
+  }
+
+  // ---- the same loop, one side per phase (k_phased): staging = one block | both sides | flux | gL gR ---------------------
+  // parks what both phases read: the base diffusive flux slots are written by diffusiveSide(0)
+  template <bool EFIX, int UV>
+  CFB_HD void phasedPark(const Cfg& c, const double* vL, const double* vR, double* stg, int stride) const {
+    constexpr int NS = RP_NSIDE(EFIX), OFF_SIDES = Q*Q, OFF_FLUX = Q*Q + 2*NS, OFF_G = OFF_FLUX + Q;
+#pragma unroll
+    for (int v = 0; v < Q; ++v) {
+      stg[(size_t)(OFF_FLUX + v)*stride] = 0.;
+      stg[(size_t)(OFF_G + v)*stride] = gL[v];
+      stg[(size_t)(OFF_G + Q + v)*stride] = gR[v];
+    }
+#pragma unroll 1
+    for (int sd = 0; sd < 2; ++sd) {
+      double vF[Q];
+#pragma unroll
+      for (int v = 0; v < Q; ++v) vF[v] = dsel(sd != 0, vR[v], vL[v]);
+      typename P::SideLite fixed;
+      P::template sideLiteT<UV>(c, vF, n, fixed);
+      double* fx = stg + (size_t)(OFF_SIDES + sd*NS)*stride;
+#pragma unroll
+      for (int v = 0; v < Q; ++v) { fx[(size_t)v*stride] = fixed.s[v]; fx[(size_t)(Q + v)*stride] = fixed.z[v]; fx[(size_t)(2*Q + v)*stride] = fixed.f[v]; }
+      if constexpr (EFIX) { fx[(size_t)(3*Q)*stride] = fixed.un; fx[(size_t)(3*Q + 1)*stride] = fixed.A; }
+    }
+  }
+  // diffusive part of one phase: the diamond is rebuilt from the mesh (it cannot stay in registers across the convective
+  // loop), phase 0 also forms the base diffusive flux (-> flux slots) and the diffusive update coefficient; then the Q
+  // perturbed diffusive fluxes of side `side` are staged as the columns of the block
+  CFB_HD void diffusiveSide(const Dev& d, const Cfg& c, int side, double* stg, int stride, int offFlux) {
+    {
+      double sL[Q], sR[Q];
+#pragma unroll
+      for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + L]; sR[v] = d.U[(size_t)v*d.nStates + R]; }
+      loadDiamond(d);
+      setCellStates(sL, sR);
+    }
+    allGrads();
+    transport(c);
+    if (side == 0) {
+      double dfluxBase[Q];
+      diffFlux(c, grad, dfluxBase);
+#pragma unroll
+      for (int v = 0; v < Q; ++v) stg[(size_t)(offFlux + v)*stride] = dfluxBase[v];
+      const double nu = ddiv(mu, P::density(c, avState));      // NSFlux.ci:127-152
+      d.ucD[f] = ddiv(nu*area*area, volume);
+    }
+    // The control-volume values of the perturbed variable (face nodes, L cell, R cell) are read back from memory per
+    // perturbation (they hit L1 / L2) instead of keeping all 6 x Q of them in registers next to the 24 normals and 15
+    // gradients; the loads of the next perturbation are issued before the arithmetic of the current one.
+    int node[NMAX];
+    {
+      const int b0 = d.faceNodePtr[f];
+#pragma unroll
+      for (int j = 0; j < NMAX; ++j) node[j] = d.faceNodes[b0 + ((j < nbN) ? j : nbN - 1)];
+    }
+    const int pc = side ? R : L, oc = side ? L : R;
+    double an[6];
+#pragma unroll
+    for (int j = 0; j < NMAX; ++j) an[j] = d.nstates[node[j]];
+    if (NMAX < 4) { an[2] = 0.; an[3] = 0.; }
+    an[4] = d.U[pc]; an[5] = d.U[oc];
+#pragma unroll 1
+    for (int iVar = 0; iVar < Q; ++iVar) {
+      double a[6];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) a[j] = an[j];
+      {
+        const int nv = (iVar + 1 < Q) ? iVar + 1 : iVar;
+#pragma unroll
+        for (int j = 0; j < NMAX; ++j) an[j] = d.nstates[(size_t)nv*d.nNodes + node[j]];
+        an[4] = d.U[(size_t)nv*d.nStates + pc]; an[5] = d.U[(size_t)nv*d.nStates + oc];
+      }
+      const double orig = a[4], other = a[5];
+      const double pv = orig + fdEps(c, iVar, orig);
+      a[4] = dsel(side == 0, pv, other);         // the control volume holds the CELL state, not the reconstructed one
+      a[5] = dsel(side == 0, other, pv);
+      double gr[3];
+      gradRow(a, gr);
+      double g2[Q][3];
+#pragma unroll
+      for (int v = 0; v < Q; ++v)
+#pragma unroll
+        for (int k = 0; k < 3; ++k) g2[v][k] = dsel(v == iVar, gr[k], grad[v][k]);
+      double dflux[Q];
+      diffFlux(c, g2, dflux);
+      double* blk = stg + (size_t)iVar*stride;
+#pragma unroll
+      for (int v = 0; v < Q; ++v) blk[(size_t)v*Q*stride] = dflux[v];
+    }
+  }
+  // convective part of one phase, software-pipelined like innerConvectiveRoePipelined: phase 0 = base evaluation + side L,
+  // phase 1 = side R
+  template <bool EFIX, int UV>
+  CFB_HD void convectiveSide(const Dev& d, const Cfg& c, int side, bool hasDiff, double* stg, int stride) const {
+    // the reconstructed face states are re-formed (cell state + parked increment: the additions of reconstruct()) rather
+    // than kept in registers across the diffusive part
+    constexpr int OFF_G = Q*Q + 2*RP_NSIDE(EFIX) + Q;
+    double vL[Q], vR[Q];
+    const bool constant = (c.polyRec == CFB200_PR_CONSTANT);
+#pragma unroll
+    for (int v = 0; v < Q; ++v) {
+      const double sl = d.U[(size_t)v*d.nStates + L], sr = d.U[(size_t)v*d.nStates + R];
+      vL[v] = dsel(constant, sl, sl + stg[(size_t)(OFF_G + v)*stride]);
+      vR[v] = dsel(constant, sr, sr + stg[(size_t)(OFF_G + Q + v)*stride]);
+    }
+    const int first = side ? Q : -1, last = side ? 2*Q - 1 : Q - 1;
+    RoeHand cur;
+    roeFront<EFIX, UV, 1>(d, c, first, roeOrig(d, first), vL, vR, stg, stride, cur);
+    double origNext = roeOrig(d, (first < last) ? first + 1 : last);
+#pragma unroll 1
+    for (int it = first; it <= last; ++it) {
+      RoeHand nxt;
+      const int itn = (it < last) ? it + 1 : it;       // the last iteration of a phase has no successor: recomputed and dropped
+      const double origAfter = roeOrig(d, (it + 2 < last) ? it + 2 : last);
+      roeFront<EFIX, UV, 1>(d, c, itn, origNext, vL, vR, stg, stride, nxt);
+      roeBack<EFIX, 1>(d, c, it, cur, hasDiff, stg, stride);
+      cur = nxt;
+      origNext = origAfter;
     }
   }
 
@@ -626,6 +760,41 @@ struct FaceWork {
 // these and are gathered by DiagGather.  One-sided updatable faces (partition overlap) use the same values
 // (FVMCC_ComputeRhsJacob.cxx:184-236: row idx receives (-1)^idx * resFactor * dF/dU); the blocks that land in
 // non-updatable rows are staging for DiagGather and are zeroed afterwards by ZeroRows.
+// The gathers of a face miss L2 about two times in three (each cell / node datum is first touched by one of its faces), and
+// with two resident warps per scheduler a DRAM round trip in the prologue is not covered by other warps.  Blocks start in
+// index order, so the face `ahead` = (resident blocks) x (block size) positions further on is picked up when the current
+// wave of blocks retires: its cell- and node-indexed data are requested into L2 now.  Prefetches write no register.
+template <int D>
+CFB_HD void prefetchFaceGathers(const Dev& d, const Cfg& c, int fn, bool diamond) {
+  constexpr int Q = D + 2;
+  if (fn >= d.nInner) return;
+  const int Ln = d.faceL[fn], Rn = d.faceR[fn];
+#pragma unroll
+  for (int v = 0; v < Q; ++v) {
+    prefetchL2(&d.U[(size_t)v*d.nStates + Ln]); prefetchL2(&d.U[(size_t)v*d.nStates + Rn]);
+    if (c.polyRec != CFB200_PR_CONSTANT) {
+      const size_t iL = (size_t)v*d.nCells + Ln, iR = (size_t)v*d.nCells + Rn;
+      prefetchL2(&d.uX[iL]); prefetchL2(&d.uX[iR]); prefetchL2(&d.uY[iL]); prefetchL2(&d.uY[iR]);
+      if (D == 3) { prefetchL2(&d.uZ[iL]); prefetchL2(&d.uZ[iR]); }
+      prefetchL2(&d.lim[iL]); prefetchL2(&d.lim[iR]);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < D; ++k) { prefetchL2(&d.centres[(size_t)k*d.nStates + Ln]); prefetchL2(&d.centres[(size_t)k*d.nStates + Rn]); }
+  if (diamond) {
+    const int b = d.faceNodePtr[fn], nb = d.faceNodePtr[fn + 1] - b;
+    constexpr int NMAX = (D == 2) ? 2 : 4;
+#pragma unroll
+    for (int j = 0; j < NMAX; ++j) {
+      const int node = d.faceNodes[b + ((j < nb) ? j : nb - 1)];
+#pragma unroll
+      for (int k = 0; k < D; ++k) prefetchL2(&d.nodes[(size_t)k*d.nNodes + node]);
+#pragma unroll
+      for (int v = 0; v < Q; ++v) prefetchL2(&d.nstates[(size_t)v*d.nNodes + node]);
+    }
+  }
+}
+
 // UV >= 0 (Roe families with the Jacobian): the update-variable set as a compile-time constant and the software-pipelined
 // finite-difference loop (FaceWork::innerConvectiveRoePipelined).
 template <int D, bool JAC, int FS = 0, int DV = 0, int UV = -1>
@@ -687,8 +856,67 @@ struct InnerFaceK {   // idx over interior faces; FS = 0 Roe, 1 AUSM+ / AUSM+up,
       }
     }
     d.ucD[f] = ucD;
+    if (JAC && d.prefetchAhead > 0) prefetchFaceGathers<D>(d, c, f + d.prefetchAhead, hasDiff && DV == 0);
     if constexpr (PIPE) w.template innerConvectiveRoePipelined<FS == 3, UV>(d, c, vL, vR, hasDiff, dfluxBase, stg, stride);
     else w.template innerConvective<FS>(d, c, sL, sR, vL, vR, hasDiff, dfluxBase, JAC, stg, stride);
+  }
+};
+
+// The Roe finite-difference kernel in two phases (k_phased): phase 0 = base evaluation + the perturbations of the left
+// state -> block(R,L), written out by the warp; phase 1 = the perturbations of the right state -> block(L,R).  Only one
+// block is staged at a time, so the per-thread staging area is 71 doubles instead of 95 and THREE 128-thread blocks are
+// resident per SM (168 registers per thread): the FP64 pipe needs about four independent instruction streams per
+// scheduler to stay busy (tools/microbench/fp64_lat.cu), two resident warps with the software-pipelined loop give ~2.
+// Price: the diamond control volume of the diffusive flux is rebuilt in phase 1 (~5 % more instructions).
+template <int D, int FS, int UV>
+struct InnerFacePhased {   // idx over interior faces; FS = 0 Roe | 3 Roe with the entropy fix; DiamondVolume derivatives
+  static constexpr int Q = D + 2;
+  static constexpr int BLK = Q*Q;
+  static constexpr bool EFIX = (FS == 3);
+  static constexpr int OFF_FLUX = BLK + 2*FaceWork<D>::RP_NSIDE(EFIX);
+  static constexpr int SLOTROW = FaceWork<D>::RP_STAGE(EFIX, 1);      // one more row: the destination slot of the phase
+  static constexpr int STAGE = SLOTROW + 1;
+  Dev d; Cfg c;
+  struct State { FaceWork<D> w; };
+  CFB_HD double* out() const { return d.bsrVal; }
+  CFB_HD int slot(int f, int ph) const { return ph == 0 ? d.slotRL[f] : d.slotLR[f]; }
+  // false: the face has no updatable side (FVMCC_ComputeRHS.cxx:212-213): zero flux, zero blocks
+  CFB_HD bool begin(int f, State& st, double* stg, int stride) const {
+    typedef Phys<D> P;
+    const int L = d.faceL[f], R = d.faceR[f];
+    if (!(d.updatable[L] || d.updatable[R])) {
+#pragma unroll
+      for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = 0.;
+      d.ucL[f] = 0.; d.ucR[f] = 0.; d.ucD[f] = 0.;
+      for (int k = 0; k < BLK; ++k) stg[(size_t)k*stride] = 0.;
+      return false;
+    }
+    FaceWork<D>& w = st.w;
+    w.f = f; w.L = L; w.R = R;
+    double sL[Q], sR[Q], vL[Q], vR[Q];
+#pragma unroll
+    for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + L]; sR[v] = d.U[(size_t)v*d.nStates + R]; }
+    w.load(d, c, f);
+    w.reconstruct(c, sL, sR, vL, vR);
+    {
+      PData pL, pR;
+      P::physicalData(c, vL, pL);
+      P::physicalData(c, vR, pR);
+      const double faceArea = w.area/1;
+      d.ucL[f] = dmax(P::maxEigenValue(pL, w.n), 0.)*faceArea;          // RoeFlux.cxx:165-185
+      double tn[3];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) tn[k] = -1.0*w.n[k];
+      d.ucR[f] = dmax(P::maxEigenValue(pR, tn), 0.)*faceArea;
+    }
+    if (c.diffusive != CFB200_DIFF_NS) d.ucD[f] = 0.;
+    w.template phasedPark<EFIX, UV>(c, vL, vR, stg, stride);
+    return true;
+  }
+  CFB_HD void phase(int ph, State& st, double* stg, int stride) const {
+    const bool hasDiff = (c.diffusive == CFB200_DIFF_NS);
+    if (hasDiff) st.w.diffusiveSide(d, c, ph, stg, stride, OFF_FLUX);
+    st.w.template convectiveSide<EFIX, UV>(d, c, ph, hasDiff, stg, stride);
   }
 };
 

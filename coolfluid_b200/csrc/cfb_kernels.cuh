@@ -60,6 +60,7 @@ struct Dev {
   double* aos;                // staging [max(nStates,nNodes)*q]
   double* partial;            // reduction scratch
   int* status;
+  int prefetchAhead;          // interior-face kernels: faces ahead whose gathers are prefetched into L2 (0 = off)
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -433,6 +434,31 @@ CFB_HD double timeBlockEntry(const Cfg& c, const double* u, int v, int iVar, dou
   fd *= c.timeZeroDiag[v] ? 0.0 : diagValue*c.resFactor;
   return fd;
 }
+// the whole time-term block of one cell, blk[v*Q + iVar] = value (one thread per cell)
+template <int D, class PH>
+CFB_HD void timeBlock(const Cfg& c, double* u, double diagValue, double* blk) {
+  constexpr int Q = PH::Q;
+  if (c.timeAnalyticalMatrix) {
+    for (int iVar = 0; iVar < Q; ++iVar)
+      for (int v = 0; v < Q; ++v) blk[v*Q + iVar] = timeBlockEntry<D, PH>(c, u, v, iVar, diagValue);
+    return;
+  }
+  double tempState[Q], tPert[Q];
+  PH::toCons(c, u, tempState);
+  for (int iVar = 0; iVar < Q; ++iVar) {
+    const double orig = u[iVar];
+    const double eps = fdEps(c, iVar, orig);
+    u[iVar] = orig + eps;
+    PH::toCons(c, u, tPert);
+    const double invEps = ddiv(1., eps);
+    for (int v = 0; v < Q; ++v) {
+      double fd = (tPert[v] - tempState[v])*invEps;
+      fd *= c.timeZeroDiag[v] ? 0.0 : diagValue*c.resFactor;
+      blk[v*Q + iVar] = fd;
+    }
+    u[iVar] = orig;
+  }
+}
 // rhs part for one cell (AoS rhs row r[] in registers)
 template <int D, class PH>
 CFB_HD void timeRhsRow(const Dev& d, const Cfg& c, int cell, const double* u, double diagValue, double* r) {
@@ -481,7 +507,12 @@ struct CellGather {   // idx over cells
       double u[Q];
 #pragma unroll
       for (int v = 0; v < Q; ++v) u[v] = d.U[(size_t)v*d.nStates + cell];
-      timeRhsRow<D, PH>(d, c, cell, u, timeDiagValue<D, PH>(d, c, cell, uc, 0.), r);
+      const double diagValue = timeDiagValue<D, PH>(d, c, cell, uc, 0.);
+      timeRhsRow<D, PH>(d, c, cell, u, diagValue, r);
+      if (c.computeJacobian) {       // block part parked in the (not yet written) diagonal slot: DiagGather adds it to its face sum
+        double* blk = &d.bsrVal[(size_t)d.diagSlot[cell]*Q*Q];
+        timeBlock<D, PH>(c, u, diagValue, blk);
+      }
     }
     for (int v = 0; v < Q; ++v) d.rhs[(size_t)cell*Q + v] = r[v];
     d.updateCoeff[cell] = uc;
@@ -519,11 +550,11 @@ struct DivBGather {   // idx over cells
 template <int D, class PH = Phys<D> >
 struct DiagGather {   // idx over nCells*GS: one thread per (cell, block entry), no idle lanes
   static constexpr int GS = PH::Q*PH::Q;
-  Dev d; Cfg c; long long base;      // base: first (cell, entry) index of this launch (chunked above 2^31 entries)
-  CFB_HD void operator()(int idx0) const {
+  Dev d; int cell0; int fused;      // cell0: first cell of this launch (chunks of < 2^31 entries start at a cell boundary)
+  CFB_HD void operator()(int idx) const {
     constexpr int Q = PH::Q;
-    const long long idx = base + idx0;
-    const int cell = (int)(idx/GS), e = (int)(idx - (long long)cell*GS);
+    const int lc = idx/GS, e = idx - lc*GS;
+    const int cell = cell0 + lc;
     if (e >= Q*Q) return;
     double acc = 0.;
     if (d.updatable[cell]) {
@@ -546,13 +577,9 @@ struct DiagGather {   // idx over nCells*GS: one thread per (cell, block entry),
         for (int k = 0; k < 6; ++k)
           if (j0 + k < je) { if (d.diagSrc[j0 + k] >= 0) acc -= x[k]; else acc += x[k]; }
       }
-      if (c.fuseTimeRhs) {     // a21 fused: the time term lands on the finished face sum (updateCoeff is complete: CellGather ran)
-        double u[Q];
-#pragma unroll
-        for (int v = 0; v < Q; ++v) u[v] = d.U[(size_t)v*d.nStates + cell];
-        const int v = e/Q, iVar = e - v*Q;
-        acc += timeBlockEntry<D, PH>(c, u, v, iVar, timeDiagValue<D, PH>(d, c, cell, d.updateCoeff[cell], 0.));
-      }
+      // a21 fused: CellGather (one thread per cell, updateCoeff complete there) left the time-term block in the diagonal
+      // slot; it lands on the finished face sum, as FVMCC_PseudoSteadyTimeRhs adds it after the face loop
+      if (fused) acc += d.bsrVal[(size_t)d.diagSlot[cell]*Q*Q + e];
     }
     d.bsrVal[(size_t)d.diagSlot[cell]*Q*Q + e] = acc;
   }
@@ -561,11 +588,10 @@ struct DiagGather {   // idx over nCells*GS: one thread per (cell, block entry),
 template <int D, class PH = Phys<D> >
 struct ZeroRows {   // idx over (non-updatable cell list) * GS
   static constexpr int GS = PH::Q*PH::Q;
-  Dev d; const int* cells; long long base;
-  CFB_HD void operator()(int idx0) const {
+  Dev d; const int* cells; int first;      // first: position in the list of the first cell of this launch
+  CFB_HD void operator()(int idx) const {
     constexpr int Q = PH::Q;
-    const long long idx = base + idx0;
-    const int cell = cells[idx/GS], e = (int)(idx - (idx/GS)*GS);
+    const int cell = cells[first + idx/GS], e = idx - (idx/GS)*GS;
     if (e >= Q*Q) return;
     for (int k = d.bsrRowPtr[cell]; k < d.bsrRowPtr[cell+1]; ++k) d.bsrVal[(size_t)k*Q*Q + e] = 0.;
   }

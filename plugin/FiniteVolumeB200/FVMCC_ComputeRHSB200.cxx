@@ -18,6 +18,16 @@
 #include "MathTools/MathFunctions.hh"
 #include "Common/DemangledTypeID.hh"
 #include "FiniteVolume/FVMCC_BC.hh"
+#include "FiniteVolume/FVMCC_PolyRec.hh"
+#include "Framework/Limiter.hh"
+#include "Framework/FluxSplitter.hh"
+#include "Framework/CFL.hh"
+#include "Framework/BlockAccumulator.hh"
+#include "Framework/LinearSystemSolver.hh"
+#include "Config/ConfigOptionException.hh"
+#include "NavierStokes/NSTerm.hh"
+#include "MHD/MHDProjectionTerm.hh"
+#include <sstream>
 
 using namespace std;
 using namespace COOLFluiD::Framework;
@@ -36,6 +46,7 @@ std::vector<SafePtr<BaseDataSocketSink> > FVMCC_ComputeRHSB200::needsSockets()
 {
   std::vector<SafePtr<BaseDataSocketSink> > result = FVMCC_ComputeRHS::needsSockets();
   result.push_back(&socket_stencil);
+  result.push_back(&socket_pastStates);      // not essential: only the fused pseudo-steady term reads it
   return result;
 }
 
@@ -43,14 +54,31 @@ void FVMCC_ComputeRHSB200::defineConfigOptions(Config::OptionList& options)
 {
   options.addConfigOption< CFint >("Device", "CUDA device ordinal (-1: rank % deviceCount).");
   options.addConfigOption< bool >("HostJacobian", "Copy the block Jacobian to the host LSS matrix (CPU PETSc).");
+  options.addConfigOption< CFreal >("ViscRef", "Reference viscosity of the configured viscosity law (NavierStokes.DiffTerm.*.ViscRef).");
+  options.addConfigOption< CFreal >("TRef", "Reference temperature of the configured viscosity law.");
+  options.addConfigOption< CFreal >("SuthConst", "Sutherland constant of the configured viscosity law.");
+  options.addConfigOption< CFreal >("FixedVisc", "Viscosity of a constant viscosity law.");
+  options.addConfigOption< bool >("FuseTimeRhs", "Apply the pseudo-steady time term inside this command (ComputeTimeRHS must then be Null).");
+  options.addConfigOption< bool >("useAnalyticalMatrix", "As PseudoSteadyTimeRhs.useAnalyticalMatrix (fused time term).");
+  options.addConfigOption< bool >("useGlobalDT", "As PseudoSteadyTimeRhs.useGlobalDT.");
+  options.addConfigOption< std::vector<bool> >("zeroDiagValue", "As PseudoSteadyTimeRhs.zeroDiagValue (fused time term).");
 }
 
 FVMCC_ComputeRHSB200::FVMCC_ComputeRHSB200(const std::string& name) :
-  FVMCC_ComputeRHS(name), socket_stencil("stencil"), m_h(CFNULL)
+  FVMCC_ComputeRHS(name), socket_stencil("stencil"), socket_pastStates("pastStates", false), m_h(CFNULL)
 {
   addConfigOptionsTo(this);
   m_device = -1;       setParameter("Device", &m_device);
   m_hostJacobian = true; setParameter("HostJacobian", &m_hostJacobian);
+  m_viscRef = 0.;        setParameter("ViscRef", &m_viscRef);
+  m_viscTRef = 0.;       setParameter("TRef", &m_viscTRef);
+  m_viscSuthConst = 0.;  setParameter("SuthConst", &m_viscSuthConst);
+  m_fixedVisc = 1.;      setParameter("FixedVisc", &m_fixedVisc);
+  m_fuseTimeRhs = false; setParameter("FuseTimeRhs", &m_fuseTimeRhs);
+  m_timeAnalyticalMatrix = false; setParameter("useAnalyticalMatrix", &m_timeAnalyticalMatrix);
+  m_timeUseGlobalDT = false;      setParameter("useGlobalDT", &m_timeUseGlobalDT);
+  m_timeZeroDiag = std::vector<bool>(); setParameter("zeroDiagValue", &m_timeZeroDiag);
+  std::memset(&m_cfg, 0, sizeof(m_cfg));
 }
 
 FVMCC_ComputeRHSB200::~FVMCC_ComputeRHSB200() {}
@@ -64,60 +92,182 @@ void FVMCC_ComputeRHSB200::check(int rc, const char* what)
   throw BadValueException(FromHere(), std::string(what) + ": " + cfb200_last_error(m_h));
 }
 
+// ---- option read-back -------------------------------------------------------------------------------------------------
+// Every strategy is a Config::ConfigObject whose options are linked to its members (ConfigObject.hh:143-175 setParameter),
+// so Option::getValueAsString() (OptionT.hh:52,153) returns the CURRENT value, configured or default, also of members that
+// have no accessor (Venktn2D::_coeffEps, AUSMPlusUpFlux::m_coeffKu, ...).  Vectors come back blank separated, bool as 0/1.
+namespace {
+template <class OBJ> bool hasOpt(OBJ& o, const std::string& name) {
+  try { o.getOption(name); return true; } catch (Config::ConfigOptionException&) { return false; }
+}
+template <class OBJ> std::string optStr(OBJ& o, const std::string& name, const std::string& dflt) {
+  try { return o.getOption(name)->getValueAsString(); } catch (Config::ConfigOptionException&) { return dflt; }
+}
+template <class OBJ> CFreal optReal(OBJ& o, const std::string& name, CFreal dflt) {
+  const std::string v = optStr(o, name, "");
+  return v.empty() ? dflt : std::strtod(v.c_str(), CFNULL);
+}
+template <class OBJ> CFint optInt(OBJ& o, const std::string& name, CFint dflt) {
+  const std::string v = optStr(o, name, "");
+  if (v == "true") return 1;
+  if (v == "false") return 0;
+  return v.empty() ? dflt : (CFint)std::strtol(v.c_str(), CFNULL, 10);
+}
+template <class OBJ> std::vector<CFreal> optVec(OBJ& o, const std::string& name) {
+  std::vector<CFreal> r;
+  std::istringstream is(optStr(o, name, ""));
+  std::string tok;
+  while (is >> tok) r.push_back((tok == "true") ? 1. : (tok == "false") ? 0. : std::strtod(tok.c_str(), CFNULL));
+  return r;
+}
+}
+
+// The static part of cfb200_config: everything the CPU strategies hold after configuration.  Built ONCE in setup() (the
+// strategies are configured by then) and cached in m_cfg; execute() only refreshes the per-call scalars.  Field by field
+// this follows include/cfb200.h; INTEGRATION.md section 4 lists option -> accessor -> field.
 void FVMCC_ComputeRHSB200::fillConfig(cfb200_config& c)
 {
-  // values the CPU strategies hold after configuration: PhysicalModel (gamma, R, refValues), PolyReconstructor
-  // (limitRes, gradientFactor, limitIter, freezeLimiter), Limiter (coeffEps, length, magnitudeValues, useFullStencil),
-  // FluxSplitter (DiffCoeff), NSTerm (coeffTau, coeffQ, cpOverPrandtl, mu/temp/p references), NumericalJacobian tol.
+  CellCenterFVMData& md = getMethodData();
   const CFuint dim = PhysicalModelStack::getActive()->getDim();
   const CFuint nbEqs = PhysicalModelStack::getActive()->getNbEq();
+  SafePtr<PhysicalModelImpl> pm = PhysicalModelStack::getActive()->getImplementor();
   std::memset(&c, 0, sizeof(c));
   c.dim = dim; c.nEqs = nbEqs;
-  const std::string model = PhysicalModelStack::getActive()->getImplementor()->getConvectiveName();
+
+  // ---- physical model: convective term
+  const std::string model = pm->getConvectiveName();
   if (model.find("MHD3DProjection") == 0) {
     // plugins/MHD: MHD3DProjection.ConvTerm.gamma / refSpeed (e.g. Dipole3D/dipole3DFVMMHDProjImpl.CFcase)
-    SafePtr<Physics::MHD::MHDProjectionTerm> mhdTerm = PhysicalModelStack::getActive()->getImplementor()->
-      getConvectiveTerm().d_castTo<Physics::MHD::MHDProjectionTerm>();
+    SafePtr<Physics::MHD::MHDProjectionTerm> mhdTerm = pm->getConvectiveTerm().d_castTo<Physics::MHD::MHDProjectionTerm>();
     c.physicalModel = CFB200_PM_MHD3D_PROJECTION;
     c.gamma = mhdTerm->getGamma(); c.refSpeed = mhdTerm->getRefSpeed(); c.R = 1.0;
   } else {
-    SafePtr<Physics::NavierStokes::EulerTerm> eulerTerm = PhysicalModelStack::getActive()->getImplementor()->
-      getConvectiveTerm().d_castTo<Physics::NavierStokes::EulerTerm>();
+    SafePtr<Physics::NavierStokes::EulerTerm> eulerTerm = pm->getConvectiveTerm().d_castTo<Physics::NavierStokes::EulerTerm>();
     c.physicalModel = CFB200_PM_EULER;
-    c.gamma = eulerTerm->getGamma(); c.R = eulerTerm->getR();
+    c.gamma = eulerTerm->getGamma();                       // EulerTerm.hh:139
+    c.R = eulerTerm->getR();                               // EulerTerm.hh:129 (_RRef)
+    c.pOffset = eulerTerm->getPressureFromState(0.);       // EulerTerm.hh:199-202: _p0Inf/refP
+    c.tempRef = eulerTerm->getTempRef();                   // EulerTerm.hh:174
+    c.pRef = eulerTerm->getPressRef();                     // EulerTerm.hh:179
   }
-  c.updateVar = (getMethodData().getUpdateVarStr() == "Cons") ? CFB200_UV_CONS : CFB200_UV_PVT;
-  // CellCenterFVM.Data.FluxSplitter = Roe | AUSMPlus{2,3}D | AUSMPlusUp{2,3}D | LaxFried | HLL
-  const std::string fs = getMethodData().getFluxSplitter()->getName();
+  c.isAdimensional = pm->isAdimensional() ? 1 : 0;         // PhysicalModelImpl.hh:120
+  c.updateVar = (md.getUpdateVarStr() == "Cons") ? CFB200_UV_CONS : CFB200_UV_PVT;
+  const RealVector& refValues = pm->getRefStateValues();   // PhysicalModelImpl.hh:108 -> NumericalJacobian (RoeFlux.cxx:113-115)
+  for (CFuint i = 0; i < nbEqs; ++i) { c.refValues[i] = refValues[i]; c.magnitudeValues[i] = refValues[i]; }
+  c.fdTol = 10e-7;                                         // NumericalJacobian.cxx:31 (no option, no accessor)
+
+  // ---- flux splitter: CellCenterFVM.Data.FluxSplitter = Roe | RoeEntropyFix | AUSMPlus{2,3}D | AUSMPlusUp{2,3}D | LaxFried | HLL
+  FluxSplitter<CellCenterFVMData>& fsp = *md.getFluxSplitter();
+  const std::string fs = fsp.getName();
   c.fluxSplitter = (fs.find("AUSMPlusUp") == 0) ? CFB200_FS_AUSMPLUSUP : (fs.find("AUSMPlus") == 0) ? CFB200_FS_AUSMPLUS :
-                   (fs == "LaxFried") ? CFB200_FS_LAXFRIED : (fs == "HLL") ? CFB200_FS_HLL : CFB200_FS_ROE;
-  // AUSMFlux.ci:55, AUSMPlusFlux.ci:17-23, AUSMPlusUpFlux.ci:20-33 defaults; the configured values are read from the
-  // splitter's option map (choiceA12, beta, alpha, coeffKu, coeffKp, sigma, machInf), HLLFlux.cxx:48 UseAlpha
-  c.choiceA12 = 1; c.ausmBeta = 1./8.; c.ausmAlpha = 3./16.; c.ausmKu = 0.75; c.ausmKp = 0.25; c.ausmSigma = 1.0;
-  c.machInf = 0.0; c.hllUseAlpha = 0;
-  c.polyRec = (getMethodData().getPolyReconstructor()->getName() == "Constant") ? CFB200_PR_CONSTANT : CFB200_PR_LINEARLS;
-  const std::string lim = getMethodData().getLimiter()->getName();
-  c.limiter = (lim.find("Venktn") == 0) ? CFB200_LIM_VENKTN : (lim == "BarthJesp" ? CFB200_LIM_BARTHJESP : CFB200_LIM_NONE);
-  c.diffusive = getMethodData().getDiffusiveFluxComputer()->isNull() ? CFB200_DIFF_NONE : CFB200_DIFF_NS;
+                   (fs == "LaxFried") ? CFB200_FS_LAXFRIED : (fs == "HLL") ? CFB200_FS_HLL :
+                   (fs == "Roe" || fs == "RoeEntropyFix") ? CFB200_FS_ROE : -1;      // -1: cfb200_create -> UNSUPPORTED
+  c.diffRedCoeff = optReal(fsp, "DiffCoeff", 1.0);         // RoeFlux.cxx:34,62 / LaxFriedFlux.cxx:32
+  c.entropyFixID = (fs == "RoeEntropyFix") ? optInt(fsp, "entropyFixID", 1) : 0;     // RoeEntropyFixFlux.cxx:35,49
+  c.choiceA12 = optInt(fsp, "choiceA12", 1);               // AUSMFlux.ci:55,73
+  c.coeffSigmoid = optReal(fsp, "coeffSigmoid", 1e-8);     // AUSMFlux.ci:64,84
+  c.ausmBeta = optReal(fsp, "beta", 1./8.);                // AUSMPlusFlux.ci:38 / AUSMPlusUpFlux.ci:58
+  c.ausmAlpha = optReal(fsp, "alpha", 3./16.);             // AUSMPlusFlux.ci:41
+  c.ausmKu = optReal(fsp, "coeffKu", 0.75);                // AUSMPlusUpFlux.ci:50
+  c.ausmKp = optReal(fsp, "coeffKp", 0.25);                // AUSMPlusUpFlux.ci:52
+  c.ausmSigma = optReal(fsp, "sigma", 1.0);                // AUSMPlusUpFlux.ci:54
+  c.machInf = optReal(fsp, "machInf", 0.0);                // AUSMPlusUpFlux.ci:56
+  c.hllUseAlpha = optInt(fsp, "UseAlpha", 0);              // HLLFlux.cxx:32,48
+
+  // ---- reconstruction + limiter
+  FVMCC_PolyRec& rec = *md.getPolyReconstructor();
+  c.polyRec = (rec.getName() == "Constant") ? CFB200_PR_CONSTANT : CFB200_PR_LINEARLS;
+  c.limitIter = optInt(rec, "limitIter", 1000000000);      // PolyReconstructor.ci:29,57
+  c.limitRes = optReal(rec, "limitRes", -2.0);             // PolyReconstructor.ci:31,60
+  c.gradientFactor = optReal(rec, "gradientFactor", 1.0);  // PolyReconstructor.ci:33,63 (constant; a Def of the iteration is
+                                                           //  re-evaluated per call by refreshStep())
+  c.freezeLimiter = optInt(rec, "freezeLimiter", 0);       // PolyReconstructor.ci:35,66
+  c.stopLimiting = optInt(rec, "StopLimiting", 0);         // FVMCC_PolyRec.cxx:27,52
+  Limiter<CellCenterFVMData>& limr = *md.getLimiter();
+  const std::string lim = limr.getName();
+  c.limiter = (lim == "Venktn2D" || lim == "Venktn3D") ? CFB200_LIM_VENKTN : (lim == "BarthJesp") ? CFB200_LIM_BARTHJESP :
+              (lim == "Null" || c.polyRec == CFB200_PR_CONSTANT) ? CFB200_LIM_NONE : -1;
+  c.coeffEps = optReal(limr, "coeffEps", 1.0);             // Venktn2D.cxx:34,58
+  c.length = optReal(limr, "length", 1.0);                 // Venktn2D.cxx:36,62
+  c.useFullStencil = optInt(limr, "useFullStencil", 0);    // Limiter.ci:22
+  {
+    const std::vector<CFreal> mv = optVec(limr, "magnitudeValues");              // Venktn2D.cxx:32,96-106: default = refValues
+    if (mv.size() == nbEqs) for (CFuint i = 0; i < nbEqs; ++i) c.magnitudeValues[i] = mv[i];
+  }
+  if (optInt(limr, "isMFMHD", 0)) c.limiter = -1;          // Venktn3D.cxx:125-156 alternative formula: not provided
+
+  // ---- diffusive flux
+  c.diffusive = md.getDiffusiveFluxComputer()->isNull() ? CFB200_DIFF_NONE : CFB200_DIFF_NS;
   // CellCenterFVM.Data.DerivativeStrategy: DiamondVolume2D/3D (CellCenterFVMData.cxx:298 default) or Corrected2D/3D
-  const std::string deriv = getMethodData().getDerivativeComputer()->getName();
+  const std::string deriv = md.getDerivativeComputer()->getName();
   if (deriv == "Corrected2D" || deriv == "Corrected3D") c.derivativeStrategy = CFB200_DV_CORRECTED;
   else if (deriv == "DiamondVolume2D" || deriv == "DiamondVolume3D" || c.diffusive == CFB200_DIFF_NONE)
     c.derivativeStrategy = CFB200_DV_DIAMOND;
   else c.derivativeStrategy = -1;      // CorrectedGG*, StateDiff, ...: cfb200_create answers CFB200_ERR_UNSUPPORTED
-  c.reserved0 = 0;
-  const RealVector& refValues = PhysicalModelStack::getActive()->getImplementor()->getRefStateValues();
-  for (CFuint i = 0; i < nbEqs; ++i) { c.refValues[i] = refValues[i]; c.magnitudeValues[i] = refValues[i]; }
-  c.fdTol = 10e-7;                     // NumericalJacobian.cxx:31
-  c.limitRes = -2.0; c.gradientFactor = 1.0; c.limitIter = 1000000000; c.coeffEps = 1.0; c.length = 1.0;
-  c.diffRedCoeff = 1.0; c.artDiffCoeff = 1.0;
-  // (the remaining option values are read from the configured strategies through their accessor methods)
+  c.coeffTau = 1.0; c.coeffQ = 1.0; c.cpOverPrandtl = 1.0; c.muRef = 1.0; c.artDiffCoeff = 1.0;
+  if (c.diffusive == CFB200_DIFF_NS) {
+    SafePtr<Physics::NavierStokes::NSTerm> ns = pm->getDiffusiveTerm().d_castTo<Physics::NavierStokes::NSTerm>();
+    c.coeffTau = ns->getCoeffTau();                        // NSTerm.hh:190
+    c.coeffQ = ns->getCoeffQ();                            // NSTerm.hh:199
+    c.cpOverPrandtl = ns->getCpOverPrandtl();              // NSTerm.hh:208
+    c.artDiffCoeff = ns->getArtDiffCoeff();                // NSTerm.hh:234
+    c.muRef = ns->getReferencePhysicalData()[Physics::NavierStokes::NSTerm::MU];   // NavierStokesPhysicalModel.ci:69-170
+    // The viscosity law object is private to NSTerm (NSTerm.hh:251, no accessor): its name is NSTerm's "ViscosityLaw" option,
+    // its constants are this command's options ViscRef / TRef / SuthConst / FixedVisc (defaults = the reference's air
+    // values); setup() then VERIFIES the translated law against NSTerm::getDynViscosityDim and refuses to run otherwise.
+    const std::string law = optStr(*ns, "ViscosityLaw", "SimplerSutherland");     // NSTerm.cxx:47-48
+    c.viscLaw = (law == "SimplerSutherland") ? CFB200_VISC_SIMPLER_SUTHERLAND : (law == "Sutherland") ? CFB200_VISC_SUTHERLAND :
+                (law.find("Fixed") == 0 || law.find("Constant") == 0) ? CFB200_VISC_FIXED : -1;
+    c.viscRef = (m_viscRef > 0.) ? m_viscRef : (c.viscLaw == CFB200_VISC_SUTHERLAND ? 18.27e-6 : 0.000001458);
+    c.viscTRef = (m_viscTRef > 0.) ? m_viscTRef : (c.viscLaw == CFB200_VISC_SUTHERLAND ? 291.15 : 110.4);
+    c.viscSuthConst = (m_viscSuthConst > 0.) ? m_viscSuthConst : 120.0;
+    c.fixedVisc = m_fixedVisc;
+    if (c.viscLaw >= 0) {
+      const CFreal Ts[3] = {0.7*c.tempRef, c.tempRef, 2.5*c.tempRef};
+      for (int k = 0; k < 3; ++k) {
+        const CFreal T = Ts[k] > 0. ? Ts[k] : 100.*(k + 1);
+        const CFreal ref = ns->getDynViscosityDim(c.pRef, T);                     // NSTerm.hh:113-119
+        const CFreal mine = (c.viscLaw == CFB200_VISC_SIMPLER_SUTHERLAND) ? c.viscRef*std::pow(T, 1.5)/(c.viscTRef + T) :
+                            (c.viscLaw == CFB200_VISC_SUTHERLAND) ? c.viscRef*(c.viscTRef + c.viscSuthConst)/(T + c.viscSuthConst)*std::pow(T/c.viscTRef, 1.5) :
+                            c.fixedVisc;
+        if (std::abs(mine - ref) > 1e-13*std::abs(ref))
+          throw BadValueException(FromHere(), "B200: the viscosity law constants differ from the configured law: set "
+                                  "ViscRef / TRef / SuthConst / FixedVisc of this command to the values of NavierStokes.DiffTerm");
+      }
+    }
+  }
+  // ---- time integration scalars that the pseudo-steady term reads (FVMCC_PseudoSteadyTimeRhs.cxx:40-46,150-175); the
+  // flags of the configured "PseudoSteadyTimeRhs" command are mirrored by this command's options of the same names
+  c.timeAnalyticalMatrix = m_timeAnalyticalMatrix ? 1 : 0;
+  c.timeUseGlobalDT = m_timeUseGlobalDT ? 1 : 0;
+  for (CFuint i = 0; i < nbEqs && i < m_timeZeroDiag.size(); ++i) c.timeZeroDiag[i] = m_timeZeroDiag[i] ? 1 : 0;
+  c.fuseTimeRhs = m_fuseTimeRhs ? 1 : 0;
+}
+
+// per-call scalars (SURVEY.md section 8b "Scalars crossing per call")
+void FVMCC_ComputeRHSB200::refreshStep(cfb200_config& c)
+{
+  c.resFactor = getResFactor();
+  c.computeJacobian = (getMethodData().doComputeJacobian() && !getMethodData().isSysMatrixFrozen()) ? withJacobian() : 0;
+  c.iter = SubSystemStatusStack::getActive()->getNbIter();
+  c.residual = SubSystemStatusStack::getActive()->getResidual();
+  c.cfl = getMethodData().getCFL()->getCFLValue();        // FVMCC_PseudoSteadyTimeRhs.cxx:119
+  c.dt = SubSystemStatusStack::getActive()->getDT();      // FVMCC_PseudoSteadyTimeRhs.cxx:147
+  // PolyReconstructor options declared DynamicOption (limitIter, limitRes, gradientFactor) and RoeFlux::DiffCoeff may be
+  // changed interactively / be functions of the iteration: re-read them
+  FVMCC_PolyRec& rec = *getMethodData().getPolyReconstructor();
+  c.limitIter = optInt(rec, "limitIter", c.limitIter);
+  c.limitRes = optReal(rec, "limitRes", c.limitRes);
+  c.gradientFactor = optReal(rec, "gradientFactor", c.gradientFactor);
+  c.diffRedCoeff = optReal(*getMethodData().getFluxSplitter(), "DiffCoeff", c.diffRedCoeff);
 }
 
 void FVMCC_ComputeRHSB200::setup()
 {
   FVMCC_ComputeRHS::setup();
-  cfb200_config c; fillConfig(c);
+  fillConfig(m_cfg);                   // string matching and option read-back happen once, here
+  refreshStep(m_cfg);
+  cfb200_config& c = m_cfg;
   int device = m_device;
   if (device < 0) device = PE::GetPE().GetRank("Default") % std::max(1, cfb200_device_count());
   check(cfb200_create(&c, device, &m_h), "cfb200_create");
@@ -325,41 +475,73 @@ void FVMCC_ComputeRHSB200::execute()
   DataHandle<State*, GLOBAL> states = socket_states.getDataHandle();
   DataHandle<CFreal> rhs = socket_rhs.getDataHandle();
   DataHandle<CFreal> updateCoeff = socket_updateCoeff.getDataHandle();
-  cfb200_config c; fillConfig(c);
-  c.resFactor = getResFactor();
-  c.computeJacobian = getMethodData().doComputeJacobian() ? withJacobian() : 0;
-  c.iter = SubSystemStatusStack::getActive()->getNbIter();
-  c.residual = SubSystemStatusStack::getActive()->getResidual();
-  check(cfb200_set_step(m_h, &c), "cfb200_set_step");
+  refreshStep(m_cfg);
+  check(cfb200_set_step(m_h, &m_cfg), "cfb200_set_step");
   // states are contiguous in the global array (FVMCC_ComputeRHSCell.cu:743)
   check(cfb200_set_states(m_h, states.getGlobalArray()->ptr(), states.size()), "cfb200_set_states");
   check(cfb200_set_update_coeff(m_h, &updateCoeff[0]), "cfb200_set_update_coeff");
+  if (m_cfg.fuseTimeRhs) {
+    // pastStates socket of the time integrator (FVMCC_PseudoSteadyTimeRhs.cxx:199-207): contiguous like the states
+    if (!socket_pastStates.isConnected())
+      throw BadValueException(FromHere(), "B200: FuseTimeRhs needs the pastStates socket of an implicit time integrator");
+    DataHandle<State*> pastStates = socket_pastStates.getDataHandle();
+    m_past.resize(states.size()*m_cfg.nEqs);
+    for (CFuint i = 0; i < states.size(); ++i)
+      for (CFint v = 0; v < m_cfg.nEqs; ++v) m_past[i*m_cfg.nEqs + v] = (*pastStates[i])[v];
+    check(cfb200_set_past_states(m_h, &m_past[0], states.size()), "cfb200_set_past_states");
+  }
   // ghost states are rebuilt on the device by the same boundary conditions (applyBC = 1)
   check(cfb200_compute_rhs(m_h, 1, &rhs[0], &updateCoeff[0]), "cfb200_compute_rhs");
-  if (c.computeJacobian) insertJacobian();
+  if (m_cfg.computeJacobian) insertJacobian();
 }
 
+// The block Jacobian -> the LSS matrix, as FVMCC_ComputeRhsJacob does it (FVMCC_ComputeRhsJacob.cxx:126-176: fill a
+// BlockAccumulator, LSSMatrix::addValues(acc), LSSMatrix.hh:156-162).  One accumulator of 1 x n blocks per block ROW of
+// an updatable cell (n = 1 + its interior faces); rows of non-updatable cells are not touched (the reference never adds
+// to them, FVMCC_ComputeRhsJacob.cxx:108-119; FVMCC_ComputeRhsJacobCell.ci:281,296-299 passes row index -1 for them).
+// BlockAccumulator::setValue(i, j, ib, jb, v) addresses entry [ib][jb] of sub-block (i, j) whatever index coefficients
+// the LSS installed (BlockAccumulator.hh:289-296: PETSc row-oriented blocked layout by default) -- the same [ib][jb] the
+// BSR blocks hold.  setRowIndex / setColIndex translate local state IDs through the LSSIdxMapping (:183-207).
+// Device-resident consumers (PETSc MATMPIAIJCUSPARSE, Paralution) take cfb200_bsr_view / cfb200_export_csr_device instead
+// and skip this host copy (HostJacobian = false).
 void FVMCC_ComputeRHSB200::insertJacobian()
 {
-  // CPU PETSc: copy the BSR values once and insert block rows (BlockAccumulator.hh:289-296 layout is the BSR block
-  // layout, so one MatSetValuesBlocked per row); GPU PETSc (MATMPIAIJCUSPARSE) / Paralution: hand over the device
-  // view from cfb200_bsr_view instead (ParalutionMatrix.hh:144 SetDataPtrCSR after cfb200_export_csr).
-  SafePtr<LSSMatrix> jacobMatrix = getMethodData().getLinearSystemSolver()[0]->getMatrix();
+  SafePtr<LinearSystemSolver> lss = getMethodData().getLinearSystemSolver()[0];
+  SafePtr<LSSMatrix> jacobMatrix = lss->getMatrix();
+  const CFuint nbEqs = PhysicalModelStack::getActive()->getNbEq();
+  DataHandle<State*, GLOBAL> states = socket_states.getDataHandle();
+  const CFuint nbCells = states.size();
   if (m_rowPtr.empty()) {
-    const CFuint nbCells = socket_states.getDataHandle().size();
     m_rowPtr.resize(nbCells + 1); m_colInd.resize(cfb200_bsr_nnzb(m_h));
     check(cfb200_bsr_pattern(m_h, &m_rowPtr[0], &m_colInd[0]), "cfb200_bsr_pattern");
-    const CFuint nbEqs = PhysicalModelStack::getActive()->getNbEq();
     m_bsr.resize(m_colInd.size()*nbEqs*nbEqs);
   }
-  check(cfb200_get_bsr_values(m_h, &m_bsr[0]), "cfb200_get_bsr_values");
+  // FVMCC_ComputeRhsJacob::initializeComputationRHS resets the matrix itself (FVMCC_ComputeRhsJacob.cxx:413-416); this
+  // command stands in its place
   jacobMatrix->resetToZeroEntries();
-  // for each updatable row: jacobMatrix->addValues(row accumulator built over m_colInd[rowPtr[i]..rowPtr[i+1]))
+  if (!m_hostJacobian) return;          // the device view is consumed by a device-side LSS
+  check(cfb200_get_bsr_values(m_h, &m_bsr[0]), "cfb200_get_bsr_values");
+  for (CFuint iCell = 0; iCell < nbCells; ++iCell) {
+    if (!states[iCell]->isParUpdatable()) continue;
+    const CFint first = m_rowPtr[iCell], nCols = m_rowPtr[iCell + 1] - first;
+    BlockAccumulator*& acc = m_rowAcc[nCols];
+    if (acc == CFNULL) acc = lss->createBlockAccumulator(1, nCols, nbEqs);     // LinearSystemSolver.hh:70
+    acc->setRowIndex(0, (CFint)iCell);
+    for (CFint j = 0; j < nCols; ++j) {
+      acc->setColIndex(j, m_colInd[first + j]);
+      const CFreal* blk = &m_bsr[(size_t)(first + j)*nbEqs*nbEqs];
+      for (CFuint ib = 0; ib < nbEqs; ++ib)
+        for (CFuint jb = 0; jb < nbEqs; ++jb) acc->setValue(0, j, ib, jb, blk[ib*nbEqs + jb]);
+    }
+    jacobMatrix->addValues(*acc);
+  }
 }
 
 void FVMCC_ComputeRHSB200::unsetup()
 {
   if (m_h != CFNULL) { cfb200_destroy(m_h); m_h = CFNULL; }
+  for (std::map<CFint, BlockAccumulator*>::iterator it = m_rowAcc.begin(); it != m_rowAcc.end(); ++it) delete it->second;
+  m_rowAcc.clear();
   FVMCC_ComputeRHS::unsetup();
 }
 

@@ -9,6 +9,7 @@
 #ifndef COOLFluiD_Numerics_FiniteVolume_FVMCC_ComputeRHSB200_hh
 #define COOLFluiD_Numerics_FiniteVolume_FVMCC_ComputeRHSB200_hh
 
+#include <map>
 #include "FiniteVolume/FVMCC_ComputeRHS.hh"
 #include "Framework/BlockAccumulator.hh"
 #include "cfb200.h"
@@ -30,18 +31,25 @@ public:
 protected:
   /// 0 for "B200Rhs", 1 for "B200RhsJacob" (= NumJacob), 2 for "B200RhsJacobAnalytic" (= NumJacobAnalytic)
   virtual int withJacobian() const { return 0; }
-  void fillConfig(cfb200_config& c);
+  void fillConfig(cfb200_config& c);        ///< static part, once in setup()
+  void refreshStep(cfb200_config& c);       ///< per-call scalars (resFactor, iteration, residual, CFL, DT, dynamic options)
   void uploadMesh();
   cfb200_bc translateBC(FVMCC_BC* bc, Framework::GeometricEntity* probe, CFuint nEqs);
   void insertJacobian();
   void check(int rc, const char* what);
 
   Framework::DataSocketSink<std::vector<Framework::State*> > socket_stencil;
+  Framework::DataSocketSink<Framework::State*> socket_pastStates;   ///< non-essential (FVMCC_PseudoSteadyTimeRhs.cxx:55)
   cfb200_handle* m_h;
   CFint m_device;          ///< option Device (-1: rank % device count, as CudaDeviceManager.cu:58)
-  bool m_hostJacobian;     ///< option HostJacobian: copy the BSR back and MatSetValuesBlocked (CPU PETSc); else device view
-  std::vector<CFreal> m_gstates, m_bsr;
+  bool m_hostJacobian;     ///< option HostJacobian: copy the BSR back and LSSMatrix::addValues (CPU PETSc); else device view
+  CFreal m_viscRef, m_viscTRef, m_viscSuthConst, m_fixedVisc;   ///< constants of the viscosity law (verified in setup())
+  bool m_fuseTimeRhs, m_timeAnalyticalMatrix, m_timeUseGlobalDT;
+  std::vector<bool> m_timeZeroDiag;
+  cfb200_config m_cfg;     ///< translated once in setup(), per-call scalars refreshed in execute()
+  std::vector<CFreal> m_bsr, m_past;
   std::vector<CFint> m_rowPtr, m_colInd;
+  std::map<CFint, Framework::BlockAccumulator*> m_rowAcc;       ///< one 1 x n accumulator per block-row length
 };
 
 class FVMCC_ComputeRhsJacobB200 : public FVMCC_ComputeRHSB200 {

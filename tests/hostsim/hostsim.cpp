@@ -20,6 +20,8 @@ struct HostLoopBackend {
   void h2d(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
   void d2h(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
   void d2d(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
+  void d2hOverlapped(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
+  void joinCopies() {}
   void memset(void* p, int v, size_t n) { std::memset(p, v, n); }
   void sync() {}
   void* streamPtr() { return nullptr; }
@@ -35,6 +37,18 @@ struct HostLoopBackend {
       for (int k = 0; k < F::NOUT; ++k) {                   // the warp's block write-out
         const int slot = (k/F::BLK) ? s1 : s0;
         if (slot >= 0) f.out()[(size_t)slot*F::BLK + k%F::BLK] = stg[k];
+      }
+    }
+  }
+  template <class F> void launchPhased(const char*, const F& f, int n) {
+    double stg[F::STAGE];
+    for (int i = 0; i < n; ++i) {
+      typename F::State st;
+      const bool active = f.begin(i, st, stg, 1);
+      for (int ph = 0; ph < 2; ++ph) {
+        if (active) f.phase(ph, st, stg, 1);
+        const int slot = f.slot(i, ph);
+        if (slot >= 0) for (int k = 0; k < F::BLK; ++k) f.out()[(size_t)slot*F::BLK + k] = stg[k];
       }
     }
   }
