@@ -349,6 +349,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cfb200")
+    # (--edge is the spelling to use under torchrun, whose own parser takes a bare --n for an abbreviation of --nnodes)
     ap.add_argument("--n", "--edge", dest="n", type=int, default=220, help="hex box edge per GPU (220^3 = 10.6 M cells, configs[2])")
     ap.add_argument("--workload", default="ns3d", choices=sorted(WORKLOADS), help="ns3d = configs[2] (the metric), euler2d_* = configs[1], mhd3d = configs[3]")
     ap.add_argument("--cpu-layers", type=int, default=8, help="cell layers (of n x n cells) per host thread of the CPU arm: the "

@@ -133,6 +133,31 @@ __global__ void __launch_bounds__(BS, MINB) k_phased(const F f, const int n) {
   }
 }
 
+// One cell per thread with F::BLK doubles of staging per thread (entry k of thread t at sm[k*(BS+1) + t]); after the cells
+// are evaluated the BLOCK writes the BS finished q x q blocks to their slots, whole rows at a time (coalesced).
+template <class F, int BS>
+__global__ void __launch_bounds__(BS) k_cell_staged(const F f, const int n) {
+  extern __shared__ double sm[];
+  constexpr int STRIDE = BS + 1;
+  __shared__ int slots[BS];
+  const int t = threadIdx.x;
+  const int i = blockIdx.x*BS + t;
+  int s = -1;
+  if (i < n) { f.run(i, sm + t, STRIDE); s = f.slot(i); }
+  slots[t] = s;
+  __syncthreads();
+  double* out = f.out();
+  int k = t, lc = 0;
+  while (k >= F::BLK) { k -= F::BLK; ++lc; }
+#pragma unroll 1
+  for (int it = 0; it < F::BLK; ++it) {      // entry e = t + BS*it of the block's BS x BLK values: cell lc = e / BLK, k = e % BLK
+    const int slot = slots[lc];
+    if (slot >= 0) out[(size_t)slot*F::BLK + k] = sm[k*STRIDE + lc];
+    k += BS;
+    while (k >= F::BLK) { k -= F::BLK; ++lc; }
+  }
+}
+
 // fixed-shape block sum (run-to-run deterministic): each block reduces 1024 consecutive entries
 __global__ void __launch_bounds__(256) k_block_sum(const double* __restrict__ x, double* __restrict__ out, int n) {
   __shared__ double s[256];
@@ -287,6 +312,23 @@ struct CudaBackend {
     if (ev) CFB_CUDA(cudaEventRecord(ev->b, stream));
   }
 
+  template <class F> void launchCellStaged(const char* name, const F& f, int n) {
+    if (n <= 0) return;
+    Ev* ev = nullptr;
+    if (timing) {
+      if (nEv == evs.size()) { Ev e; e.name = name; CFB_CUDA(cudaEventCreate(&e.a)); CFB_CUDA(cudaEventCreate(&e.b)); evs.push_back(e); }
+      ev = &evs[nEv++]; ev->name = name;
+      CFB_CUDA(cudaEventRecord(ev->a, stream));
+    }
+    constexpr int BS = 128;
+    const size_t smem = (size_t)F::BLK*(BS + 1)*sizeof(double);
+    auto kern = k_cell_staged<F, BS>;
+    CFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(n + BS - 1)/BS, BS, smem, stream>>>(f, n);
+    CFB_CUDA(cudaGetLastError());
+    if (ev) CFB_CUDA(cudaEventRecord(ev->b, stream));
+  }
+
   // three resident 128-thread blocks per SM (168 registers), F::STAGE doubles of staging per thread
   template <class F> void launchPhased(const char* name, const F& f, int n) {
     if (n <= 0) return;
@@ -374,6 +416,7 @@ typedef cfb::CudaBackend BackendT;
 #define CFB_FN(x) cfb200_##x
 #include "cfb_capi.inc"
 #include "cfb_halo.cuh"
+#include "cfb_solver.cuh"
 
 // ---- multi-GPU entry points (include/cfb200.h) -----------------------------------------------------------------
 namespace {
@@ -509,6 +552,157 @@ int cfb200_allreduce_sum(cfb200_handle* h, double* v, int n) {
     CFB_NCCL(cfb::NcclApi::get().AllReduce(H->red, H->red, (size_t)n, ncclDouble, ncclSum, H->comm, e.bk.stream));
     CFB_CUDA(cudaMemcpyAsync(v, H->red, sizeof(double)*n, cudaMemcpyDeviceToHost, e.bk.stream));
     e.bk.sync();
+    return CFB200_OK;
+  });
+}
+
+} // extern "C"
+
+// ---- device-side consumers of the block Jacobian (cfb_solver.cuh) ------------------------------
+namespace {
+struct SolverWork {      // scratch of cfb200_solve_gmres / cfb200_export_csr_device, owned by the handle's engine
+  int* blockRow = nullptr;
+  double* V = nullptr; double* w = nullptr; double* z = nullptr; double* x = nullptr; double* b = nullptr;
+  double* tmp = nullptr; double* dinv = nullptr;
+  int restart = 0; size_t n = 0;
+};
+const int* blockRows(cfb::Engine<BackendT>& e, SolverWork& W) {
+  if (!W.blockRow) {
+    std::vector<int32_t> br((size_t)e.nnzb);
+    for (int c = 0; c < e.d.nCells; ++c)
+      for (int k = e.hRowPtr[c]; k < e.hRowPtr[c+1]; ++k) br[k] = c;
+    W.blockRow = e.upload(br);
+  }
+  return W.blockRow;
+}
+SolverWork& solverWork(cfb::Engine<BackendT>& e) {
+  if (!e.solverExt) { e.solverExt = new SolverWork(); e.solverExtFree = [](void* p) { delete static_cast<SolverWork*>(p); }; }
+  return *static_cast<SolverWork*>(e.solverExt);
+}
+template <class F> void launchN(cfb::Engine<BackendT>& e, const char* name, const F& f, long long n) {
+  if (n > 2147483647LL) throw std::invalid_argument("vector too long for one launch");
+  e.bk.launch(name, f, (int)n, 256);
+}
+}
+
+extern "C" {
+
+// scalar CSR written on the device into caller-provided DEVICE arrays (rowOff [nCells*q + 1], col / val [nnzb*q*q]); any
+// of them may be NULL.  index64 != 0: 64-bit offsets and columns (needed above 2^31 scalar entries, e.g. 220^3 NS)
+int cfb200_export_csr_device(cfb200_handle* h, void* rowOff, void* col, double* val, int index64) {
+  return guarded(h, [&](cfb::Engine<BackendT>& e) {
+    CFB_NEED_MESH(e);
+    if (!e.d.bsrVal) throw std::runtime_error("no Jacobian has been computed");
+    const int q = e.q();
+    const long long total = e.nnzb*q*q;
+    if (!index64 && (total > 2147483647LL || (long long)e.d.nCells*q > 2147483647LL))
+      throw std::invalid_argument("export_csr_device: scalar nnz exceeds 32-bit offsets: pass index64 = 1");
+    const int* br = blockRows(e, solverWork(e));
+    const long long CH = 1LL << 30;
+    for (long long b0 = 0; b0 < total; b0 += CH) {
+      const int n = (int)std::min(CH, total - b0);
+      if (index64) e.bk.launch("bsrToCsr", cfb::BsrToCsr<long long>{e.d.bsrRowPtr, e.d.bsrColInd, br, e.d.bsrVal, q, b0,
+                                   (long long*)rowOff, (long long*)col, val}, n, 256);
+      else e.bk.launch("bsrToCsr", cfb::BsrToCsr<int>{e.d.bsrRowPtr, e.d.bsrColInd, br, e.d.bsrVal, q, b0,
+                                   (int*)rowOff, (int*)col, val}, n, 256);
+    }
+    if (rowOff) {      // the closing offset
+      if (index64) { const long long t = total; CFB_CUDA(cudaMemcpyAsync((long long*)rowOff + (size_t)e.d.nCells*q, &t, 8, cudaMemcpyHostToDevice, e.bk.stream)); }
+      else { const int t = (int)total; CFB_CUDA(cudaMemcpyAsync((int*)rowOff + (size_t)e.d.nCells*q, &t, 4, cudaMemcpyHostToDevice, e.bk.stream)); }
+    }
+    e.bk.sync();
+    return CFB200_OK;
+  });
+}
+
+// J x = rhs on the device: restarted GMRES, right-preconditioned with the inverted diagonal blocks (precond = 1) or not
+// (0).  The right-hand side is the device rhs buffer (what compute_rhs [+ the time term] left there), the solution
+// overwrites it, so cfb200_update_sol_newton(h, NULL, ...) follows directly.  Rows of non-updatable cells are excluded.
+int cfb200_solve_gmres(cfb200_handle* h, const cfb200_gmres_params* prm, int32_t* iterations, double* relResidual) {
+  if (!prm || prm->restart < 1 || prm->restart > 200 || prm->maxIter < 1) return CFB200_ERR_INVALID_ARG;
+  return guarded(h, [&](cfb::Engine<BackendT>& e) {
+    CFB_NEED_MESH(e);
+    if (!e.d.bsrVal) throw std::runtime_error("no Jacobian has been computed");
+    e.joinHalo();
+    const int q = e.q(), m = prm->restart;
+    const long long n = (long long)e.d.nCells*q;
+    SolverWork& W = solverWork(e);
+    if (W.restart < m || W.n != (size_t)n) {
+      if (W.V) throw std::runtime_error("solve_gmres: the restart length cannot grow after the first solve");
+      W.V = e.template dalloc<double>((size_t)n*(m + 1));
+      W.w = e.template dalloc<double>(n); W.z = e.template dalloc<double>(n); W.x = e.template dalloc<double>(n);
+      W.b = e.template dalloc<double>(n);
+      W.tmp = e.template dalloc<double>((size_t)n + n/1024 + 4096);
+      W.dinv = e.template dalloc<double>((size_t)e.d.nCells*q*q);
+      W.restart = m; W.n = (size_t)n;
+    }
+    auto& bk = e.bk;
+    auto dot = [&](const double* a, const double* b) {
+      launchN(e, "gmresDot", cfb::VecMul{a, b, W.tmp}, n);
+      return bk.sumOrdered(W.tmp, (int)n);
+    };
+    auto spmv = [&](const double* x, double* y) { launchN(e, "gmresSpmv", cfb::BsrSpmv{e.d.bsrRowPtr, e.d.bsrColInd, e.d.bsrVal, x, y, q}, n); };
+    auto prec = [&](const double* x, double* y) { launchN(e, "gmresPrec", cfb::ApplyDiagInv{W.dinv, x, y, q, prm->precond}, n); };
+    if (prm->precond) bk.launch("gmresInvDiag", cfb::InvertDiag{e.d.diagSlot, e.d.updatable, e.d.bsrVal, W.dinv, q}, e.d.nCells, 128);
+    bk.d2d(W.b, e.d.rhs, sizeof(double)*n);
+    launchN(e, "gmresMask", cfb::VecZeroMasked{e.d.updatable, W.b, q}, n);
+    bk.memset(W.x, 0, sizeof(double)*n);
+    bk.d2d(W.w, W.b, sizeof(double)*n);                 // r0 = b (x0 = 0)
+    double beta = std::sqrt(dot(W.w, W.w));
+    const double beta0 = beta;
+    const double tol = std::max(prm->relTol*beta0, prm->absTol);
+    int it = 0;
+    std::vector<double> H((size_t)(m + 1)*m), cs(m), sn(m), g(m + 1), y(m);
+    bool done = (beta0 == 0.0);
+    while (!done) {
+      launchN(e, "gmresScale", cfb::VecScaleTo{1.0/beta, W.w, W.V}, n);
+      std::fill(g.begin(), g.end(), 0.); g[0] = beta;
+      int j = 0;
+      for (; j < m; ++j) {
+        double* vj = W.V + (size_t)j*n;
+        prec(vj, W.z);
+        spmv(W.z, W.w);
+        for (int i = 0; i <= j; ++i) {                  // modified Gram-Schmidt
+          const double hij = dot(W.w, W.V + (size_t)i*n);
+          H[(size_t)i*m + j] = hij;
+          launchN(e, "gmresAxpy", cfb::VecAxpy{-hij, W.V + (size_t)i*n, W.w}, n);
+        }
+        const double hn = std::sqrt(dot(W.w, W.w));
+        H[(size_t)(j + 1)*m + j] = hn;
+        if (hn > 0.) launchN(e, "gmresScale", cfb::VecScaleTo{1.0/hn, W.w, W.V + (size_t)(j + 1)*n}, n);
+        for (int i = 0; i < j; ++i) {                   // earlier rotations on the new column
+          const double t = cs[i]*H[(size_t)i*m + j] + sn[i]*H[(size_t)(i + 1)*m + j];
+          H[(size_t)(i + 1)*m + j] = -sn[i]*H[(size_t)i*m + j] + cs[i]*H[(size_t)(i + 1)*m + j];
+          H[(size_t)i*m + j] = t;
+        }
+        const double a = H[(size_t)j*m + j], b2 = H[(size_t)(j + 1)*m + j], rr = std::sqrt(a*a + b2*b2);
+        cs[j] = (rr > 0.) ? a/rr : 1.; sn[j] = (rr > 0.) ? b2/rr : 0.;
+        H[(size_t)j*m + j] = rr; H[(size_t)(j + 1)*m + j] = 0.;
+        g[j + 1] = -sn[j]*g[j]; g[j] = cs[j]*g[j];
+        ++it;
+        if (std::abs(g[j + 1]) <= tol || it >= prm->maxIter || hn == 0.) { ++j; break; }
+      }
+      const int k = j;                                   // columns used
+      for (int i = k - 1; i >= 0; --i) {                 // back substitution
+        double sum = g[i];
+        for (int l = i + 1; l < k; ++l) sum -= H[(size_t)i*m + l]*y[l];
+        y[i] = sum/H[(size_t)i*m + i];
+      }
+      bk.memset(W.w, 0, sizeof(double)*n);
+      for (int i = 0; i < k; ++i) launchN(e, "gmresAxpy", cfb::VecAxpy{y[i], W.V + (size_t)i*n, W.w}, n);
+      prec(W.w, W.z);
+      launchN(e, "gmresAxpy", cfb::VecAxpy{1.0, W.z, W.x}, n);
+      // true residual for the restart / the report
+      spmv(W.x, W.w);
+      launchN(e, "gmresScale", cfb::VecScaleTo{-1.0, W.w, W.w}, n);
+      launchN(e, "gmresAxpy", cfb::VecAxpy{1.0, W.b, W.w}, n);
+      beta = std::sqrt(dot(W.w, W.w));
+      done = (beta <= tol) || it >= prm->maxIter;
+    }
+    bk.d2d(e.d.rhs, W.x, sizeof(double)*n);
+    bk.sync();
+    if (iterations) *iterations = it;
+    if (relResidual) *relResidual = (beta0 > 0.) ? beta/beta0 : 0.;
     return CFB200_OK;
   });
 }

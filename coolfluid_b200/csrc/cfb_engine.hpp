@@ -85,17 +85,15 @@ public:
     if (haloWait) haloWait();
   }
   std::vector<void*> owned;
+  void* solverExt = nullptr; void (*solverExtFree)(void*) = nullptr;     // scratch of the device linear solver (cfb_capi.cu)
   int* nonUpdCells = nullptr;
   std::vector<int32_t> hRowPtr, hColInd;
 
   explicit Engine(const Cfg& c, int device) : cfg(c), bk(device) {
     std::memset(&d, 0, sizeof(d));
     if (const char* v = std::getenv("CFB200_ROE_PIPELINE")) roePipeline = std::atoi(v);
-    // faces ahead whose gathers the interior-face Jacobian kernels prefetch into L2: one wave of resident blocks
-    d.prefetchAhead = 2*148*128;
-    if (const char* v = std::getenv("CFB200_PREFETCH_AHEAD")) d.prefetchAhead = std::atoi(v);
   }
-  ~Engine() { for (void* p : owned) bk.free(p); }
+  ~Engine() { if (solverExt && solverExtFree) solverExtFree(solverExt); for (void* p : owned) bk.free(p); }
 
   template <class T> T* dalloc(size_t n) {
     T* p = (T*)bk.alloc(std::max<size_t>(n, 1)*sizeof(T));
@@ -394,18 +392,23 @@ public:
       if (cfg.derivativeStrategy == CFB200_DV_CORRECTED && cfg.diffusive == CFB200_DIFF_NS) faceKernels_<D, 1>(doJac, faceShape);
       else faceKernels_<D, 0>(doJac, faceShape);
     }
-    bk.launch("cellGather", CellGather<D, PH>{d, cfg}, d.nCells, 256);
+    const bool fused = (cfg.fuseTimeRhs != 0);
+    if (fused) bk.launchCellStaged("cellGather", CellGather<D, PH, true>{d, cfg}, d.nCells);
+    else bk.launch("cellGather", CellGather<D, PH, false>{d, cfg}, d.nCells, 256);
     if (hostRhs) bk.d2hOverlapped(hostRhs, d.rhs, sizeof(double)*d.nCells*PH::Q);
     if (hostUc) bk.d2hOverlapped(hostUc, d.updateCoeff, sizeof(double)*d.nCells);
     if (doJac) {
       // one thread per (cell, block entry): launched in chunks of < 2^31 entries (q = 9: 26.5 M cells per chunk)
       const int CH = (1 << 30)/DiagGather<D, PH>::GS;          // cells per launch
-      for (int c0 = 0; c0 < d.nCells; c0 += CH)
-        bk.launch("diagGather", DiagGather<D, PH>{d, c0, cfg.fuseTimeRhs}, std::min(CH, d.nCells - c0)*DiagGather<D, PH>::GS, 256);
+      for (int c0 = 0; c0 < d.nCells; c0 += CH) {
+        const int ne = std::min(CH, d.nCells - c0)*DiagGather<D, PH>::GS;
+        if (fused) bk.launch("diagGather", DiagGather<D, PH, true>{d, c0}, ne, 256);
+        else bk.launch("diagGather", DiagGather<D, PH, false>{d, c0}, ne, 256);
+      }
       for (int c0 = 0; c0 < nNonUpd; c0 += CH)
         bk.launch("zeroRows", ZeroRows<D, PH>{d, nonUpdCells, c0}, std::min(CH, nNonUpd - c0)*ZeroRows<D, PH>::GS, 256);
     }
-    timeTermApplied = (cfg.fuseTimeRhs != 0);
+    timeTermApplied = fused;
     int st = 0;
     bk.d2h(&st, d.status, sizeof(int));   // synchronises
     bk.joinCopies();

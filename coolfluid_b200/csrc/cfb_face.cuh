@@ -760,41 +760,6 @@ struct FaceWork {
 // these and are gathered by DiagGather.  One-sided updatable faces (partition overlap) use the same values
 // (FVMCC_ComputeRhsJacob.cxx:184-236: row idx receives (-1)^idx * resFactor * dF/dU); the blocks that land in
 // non-updatable rows are staging for DiagGather and are zeroed afterwards by ZeroRows.
-// The gathers of a face miss L2 about two times in three (each cell / node datum is first touched by one of its faces), and
-// with two resident warps per scheduler a DRAM round trip in the prologue is not covered by other warps.  Blocks start in
-// index order, so the face `ahead` = (resident blocks) x (block size) positions further on is picked up when the current
-// wave of blocks retires: its cell- and node-indexed data are requested into L2 now.  Prefetches write no register.
-template <int D>
-CFB_HD void prefetchFaceGathers(const Dev& d, const Cfg& c, int fn, bool diamond) {
-  constexpr int Q = D + 2;
-  if (fn >= d.nInner) return;
-  const int Ln = d.faceL[fn], Rn = d.faceR[fn];
-#pragma unroll
-  for (int v = 0; v < Q; ++v) {
-    prefetchL2(&d.U[(size_t)v*d.nStates + Ln]); prefetchL2(&d.U[(size_t)v*d.nStates + Rn]);
-    if (c.polyRec != CFB200_PR_CONSTANT) {
-      const size_t iL = (size_t)v*d.nCells + Ln, iR = (size_t)v*d.nCells + Rn;
-      prefetchL2(&d.uX[iL]); prefetchL2(&d.uX[iR]); prefetchL2(&d.uY[iL]); prefetchL2(&d.uY[iR]);
-      if (D == 3) { prefetchL2(&d.uZ[iL]); prefetchL2(&d.uZ[iR]); }
-      prefetchL2(&d.lim[iL]); prefetchL2(&d.lim[iR]);
-    }
-  }
-#pragma unroll
-  for (int k = 0; k < D; ++k) { prefetchL2(&d.centres[(size_t)k*d.nStates + Ln]); prefetchL2(&d.centres[(size_t)k*d.nStates + Rn]); }
-  if (diamond) {
-    const int b = d.faceNodePtr[fn], nb = d.faceNodePtr[fn + 1] - b;
-    constexpr int NMAX = (D == 2) ? 2 : 4;
-#pragma unroll
-    for (int j = 0; j < NMAX; ++j) {
-      const int node = d.faceNodes[b + ((j < nb) ? j : nb - 1)];
-#pragma unroll
-      for (int k = 0; k < D; ++k) prefetchL2(&d.nodes[(size_t)k*d.nNodes + node]);
-#pragma unroll
-      for (int v = 0; v < Q; ++v) prefetchL2(&d.nstates[(size_t)v*d.nNodes + node]);
-    }
-  }
-}
-
 // UV >= 0 (Roe families with the Jacobian): the update-variable set as a compile-time constant and the software-pipelined
 // finite-difference loop (FaceWork::innerConvectiveRoePipelined).
 template <int D, bool JAC, int FS = 0, int DV = 0, int UV = -1>
@@ -856,7 +821,6 @@ struct InnerFaceK {   // idx over interior faces; FS = 0 Roe, 1 AUSM+ / AUSM+up,
       }
     }
     d.ucD[f] = ucD;
-    if (JAC && d.prefetchAhead > 0) prefetchFaceGathers<D>(d, c, f + d.prefetchAhead, hasDiff && DV == 0);
     if constexpr (PIPE) w.template innerConvectiveRoePipelined<FS == 3, UV>(d, c, vL, vR, hasDiff, dfluxBase, stg, stride);
     else w.template innerConvective<FS>(d, c, sL, sR, vL, vR, hasDiff, dfluxBase, JAC, stg, stride);
   }

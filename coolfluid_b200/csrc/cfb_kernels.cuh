@@ -60,7 +60,6 @@ struct Dev {
   double* aos;                // staging [max(nStates,nNodes)*q]
   double* partial;            // reduction scratch
   int* status;
-  int prefetchAhead;          // interior-face kernels: faces ahead whose gathers are prefetched into L2 (0 = off)
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -196,6 +195,7 @@ struct Gradients {   // idx over the cells [c0, c0 + n), or over the cell list `
     double lf[3][Q];
     double u0[Q];
     for (int v = 0; v < Q; ++v) { lf[0][v] = lf[1][v] = lf[2][v] = 0.; u0[v] = d.U[(size_t)v*d.nStates + c]; }
+    // (batching the gathers of several neighbours was measured: 142 registers, 2.07 instead of 1.97 ms at 10.6 M cells)
     for (int j = d.lsqPtr[c]; j < d.lsqPtr[c+1]; ++j) {
       const int nb = d.lsqNbr[j];
       double dx[3] = {0., 0., 0.};
@@ -263,7 +263,9 @@ struct NodalExtrapolate {
 // loop, so the value is the same).  Venktn2D.cxx:111-260, Venktn3D.cxx:44-190, BarthJesp.cxx:60-155.
 template <int D, class PH = Phys<D> >
 struct LimiterK {   // idx over cells
-  static constexpr int MINB = 6;   // 80 registers: measured 8 % faster than the 96 of the default shape (8 -> 64 registers spills)
+  // 80 registers: measured 8 % faster than the 96 of the default shape; unrolling the loop over the variables at 4 resident
+  // blocks (102 registers, all gathers in flight together) was measured 50 % slower (2.88 vs 1.94 ms at 10.6 M cells)
+  static constexpr int MINB = 6;
   Dev d; Cfg c;
   CFB_HD void operator()(int cell) const {
     constexpr int Q = PH::Q;
@@ -436,11 +438,11 @@ CFB_HD double timeBlockEntry(const Cfg& c, const double* u, int v, int iVar, dou
 }
 // the whole time-term block of one cell, blk[v*Q + iVar] = value (one thread per cell)
 template <int D, class PH>
-CFB_HD void timeBlock(const Cfg& c, double* u, double diagValue, double* blk) {
+CFB_HD void timeBlock(const Cfg& c, double* u, double diagValue, double* blk, int stride) {
   constexpr int Q = PH::Q;
   if (c.timeAnalyticalMatrix) {
     for (int iVar = 0; iVar < Q; ++iVar)
-      for (int v = 0; v < Q; ++v) blk[v*Q + iVar] = timeBlockEntry<D, PH>(c, u, v, iVar, diagValue);
+      for (int v = 0; v < Q; ++v) blk[(size_t)(v*Q + iVar)*stride] = timeBlockEntry<D, PH>(c, u, v, iVar, diagValue);
     return;
   }
   double tempState[Q], tPert[Q];
@@ -454,7 +456,7 @@ CFB_HD void timeBlock(const Cfg& c, double* u, double diagValue, double* blk) {
     for (int v = 0; v < Q; ++v) {
       double fd = (tPert[v] - tempState[v])*invEps;
       fd *= c.timeZeroDiag[v] ? 0.0 : diagValue*c.resFactor;
-      blk[v*Q + iVar] = fd;
+      blk[(size_t)(v*Q + iVar)*stride] = fd;
     }
     u[iVar] = orig;
   }
@@ -479,10 +481,18 @@ CFB_HD void timeRhsRow(const Dev& d, const Cfg& c, int cell, const double* u, do
 // a17: FVMCC_ComputeRHS::updateRHS (FVMCC_ComputeRHS.cxx:455-514) as a gather: for each cell, its faces in
 // ascending loop order; rhs starts from 0, updateCoeff accumulates onto the incoming value
 // (it is zeroed by the updater, UpdateSol.cxx:192).
-template <int D, class PH = Phys<D> >
+// FUSED: also applies the pseudo-steady time term (cfg.fuseTimeRhs); a template parameter so that the plain gather
+// keeps its register count (56 -> occupancy) when the term runs as its own kernel
+template <int D, class PH = Phys<D>, bool FUSED = false>
 struct CellGather {   // idx over cells
+  static constexpr int BLK = PH::Q*PH::Q;      // FUSED: doubles of per-thread staging (the time-term block of the cell)
   Dev d; Cfg c;
-  CFB_HD void operator()(int cell) const {
+  CFB_HD double* out() const { return d.bsrVal; }
+  CFB_HD int slot(int cell) const { return (c.computeJacobian && d.updatable[cell]) ? d.diagSlot[cell] : -1; }
+  CFB_HD void operator()(int cell) const { run(cell, nullptr, 0); }
+  // stg (entry k at stg[k*stride]): where the FUSED variant leaves the time-term block of the cell for the block-wide
+  // coalesced write-out of k_cell_staged (cfb_capi.cu) into the cell's diagonal slot
+  CFB_HD void run(int cell, double* stg, int stride) const {
     constexpr int Q = PH::Q;
     double r[Q];
     for (int v = 0; v < Q; ++v) r[v] = 0.;
@@ -503,16 +513,14 @@ struct CellGather {   // idx over cells
       uc += isR ? d.ucR[f] : d.ucL[f];
       if (hasDiff) uc += d.ucD[f];
     }
-    if (c.fuseTimeRhs && d.updatable[cell]) {     // a21 fused: FVMCC_PseudoSteadyTimeRhs on the finished residual row
+    if (FUSED && d.updatable[cell]) {     // a21 fused: FVMCC_PseudoSteadyTimeRhs on the finished residual row
       double u[Q];
 #pragma unroll
       for (int v = 0; v < Q; ++v) u[v] = d.U[(size_t)v*d.nStates + cell];
       const double diagValue = timeDiagValue<D, PH>(d, c, cell, uc, 0.);
       timeRhsRow<D, PH>(d, c, cell, u, diagValue, r);
-      if (c.computeJacobian) {       // block part parked in the (not yet written) diagonal slot: DiagGather adds it to its face sum
-        double* blk = &d.bsrVal[(size_t)d.diagSlot[cell]*Q*Q];
-        timeBlock<D, PH>(c, u, diagValue, blk);
-      }
+      // block part -> staging area -> (coalesced) the not yet written diagonal slot: DiagGather adds it to its face sum
+      if (c.computeJacobian) timeBlock<D, PH>(c, u, diagValue, stg, stride);
     }
     for (int v = 0; v < Q; ++v) d.rhs[(size_t)cell*Q + v] = r[v];
     d.updateCoeff[cell] = uc;
@@ -547,10 +555,10 @@ struct DivBGather {   // idx over cells
 // Diagonal blocks: one thread per (cell, block entry).  diag(c) = sum over the cell's faces in loop order of
 //   inner face, c == L:  -block(R,c)      inner face, c == R:  -block(L,c)      boundary face: +bnd block
 // Rows of non-updatable cells are staging only and are zeroed by ZeroRows afterwards.
-template <int D, class PH = Phys<D> >
+template <int D, class PH = Phys<D>, bool FUSED = false>
 struct DiagGather {   // idx over nCells*GS: one thread per (cell, block entry), no idle lanes
   static constexpr int GS = PH::Q*PH::Q;
-  Dev d; int cell0; int fused;      // cell0: first cell of this launch (chunks of < 2^31 entries start at a cell boundary)
+  Dev d; int cell0;      // cell0: first cell of this launch (chunks of < 2^31 entries start at a cell boundary)
   CFB_HD void operator()(int idx) const {
     constexpr int Q = PH::Q;
     const int lc = idx/GS, e = idx - lc*GS;
@@ -579,7 +587,7 @@ struct DiagGather {   // idx over nCells*GS: one thread per (cell, block entry),
       }
       // a21 fused: CellGather (one thread per cell, updateCoeff complete there) left the time-term block in the diagonal
       // slot; it lands on the finished face sum, as FVMCC_PseudoSteadyTimeRhs adds it after the face loop
-      if (fused) acc += d.bsrVal[(size_t)d.diagSlot[cell]*Q*Q + e];
+      if (FUSED) acc += d.bsrVal[(size_t)d.diagSlot[cell]*Q*Q + e];
     }
     d.bsrVal[(size_t)d.diagSlot[cell]*Q*Q + e] = acc;
   }

@@ -37,6 +37,11 @@ class MeshStruct(C.Structure):   # cfb200_mesh
                 ("faceBC", P_I), ("updatable", P_U8)]
 
 
+class GmresParams(C.Structure):  # cfb200_gmres_params
+    _fields_ = [("restart", C.c_int32), ("maxIter", C.c_int32), ("precond", C.c_int32), ("reserved", C.c_int32),
+                ("relTol", C.c_double), ("absTol", C.c_double)]
+
+
 class BsrStruct(C.Structure):    # cfb200_bsr
     _fields_ = [("nRows", C.c_int32), ("nnzb", C.c_int32), ("blockSize", C.c_int32),
                 ("rowPtr", C.c_void_p), ("colInd", C.c_void_p), ("val", C.c_void_p)]
@@ -51,7 +56,7 @@ ABI_SYMBOLS = [
     "export_csr", "get_field", "device_ptr", "status", "enable_timing", "last_timings", "stream",
     "nccl_unique_id", "comm_init", "set_halo", "set_independent_cells", "halo_begin", "halo_exchange", "allreduce_sum",
     "mesh_build", "mesh_sizes", "mesh_get", "mesh_ptr", "mesh_view", "mesh_set_updatable", "mesh_free", "mesh_diamond_volumes",
-    "selftest_divsqrt",
+    "selftest_divsqrt", "export_csr_device", "solve_gmres",
 ]
 # symbols the engine part needs (a test-only host build of the kernel functors exports just these)
 ENGINE_SYMBOLS = ABI_SYMBOLS[2:30]
@@ -118,6 +123,8 @@ def load(path=None, prefix="cfb200_"):
         ns.mesh_set_updatable.argtypes = [C.c_void_p, P_U8]; ns.mesh_set_updatable.restype = None
         ns.mesh_free.argtypes = [C.c_void_p]; ns.mesh_free.restype = None
         ns.mesh_diamond_volumes.argtypes = [C.POINTER(MeshStruct), P_D, P_U8]; ns.mesh_diamond_volumes.restype = None
+        ns.export_csr_device.argtypes = [H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        ns.solve_gmres.argtypes = [H, C.POINTER(GmresParams), C.POINTER(C.c_int32), P_D]
         ns.nccl_unique_id.argtypes = [C.c_void_p]
         ns.comm_init.argtypes = [H, C.c_int, C.c_int, C.c_void_p]
         ns.set_halo.argtypes = [H, P_I, P_I, P_I, P_I, C.c_int32]
@@ -303,6 +310,18 @@ class Engine:
         val = np.empty(self.nnzb*self.q*self.q)
         self._chk(self.L.export_csr(self.h, _pi(ro), _pi(col), _pd(val)), "export_csr")
         return ro, col, val
+
+    def solve_gmres(self, restart=30, max_iter=50, rel_tol=1e-5, abs_tol=1e-30, precond=1):
+        """J x = rhs on the device (block-Jacobi GMRES); the solution replaces the device rhs buffer.
+        Returns (iterations, final relative residual)."""
+        p = GmresParams(restart, max_iter, precond, 0, rel_tol, abs_tol)
+        it = C.c_int32()
+        rr = C.c_double()
+        self._chk(self.L.solve_gmres(self.h, C.byref(p), C.byref(it), C.byref(rr)), "solve_gmres")
+        return it.value, rr.value
+
+    def export_csr_device(self, row_off_ptr, col_ptr, val_ptr, index64=False):
+        self._chk(self.L.export_csr_device(self.h, row_off_ptr, col_ptr, val_ptr, int(index64)), "export_csr_device")
 
     def field(self, name):
         fm, q = self.fm, self.q

@@ -235,6 +235,22 @@ int64_t cfb200_bsr_nnzb(cfb200_handle* h);
 int cfb200_get_bsr_values(cfb200_handle* h, double* val /* [nnzb*q*q] */);
 /* scalar CSR view for Paralution (ParalutionMatrix.hh:144 SetDataPtrCSR): rows of a cell one after the other */
 int cfb200_export_csr(cfb200_handle* h, int32_t* rowOff, int32_t* col, double* val);
+/* the same scalar CSR written by a kernel into caller-provided DEVICE arrays (no download of the values; any array may be
+ * NULL): rowOff [nCells*q + 1], col / val [nnzb*q*q]; index64 != 0 -> 64-bit rowOff / col (above 2^31 scalar entries).
+ * replaces: the host assembly behind ParalutionMatrix::createSeqBAIJ / SetDataPtrCSR (plugins/Paralution/ParalutionMatrix.cu:48-105) */
+int cfb200_export_csr_device(cfb200_handle* h, void* rowOff, void* col, double* val, int index64);
+/* replaces: LinearSystemSolver::solveSys with KSPGMRES + block-Jacobi (plugins/Petsc/StdParSolveSys.cxx, PetscLSSData.cxx:60-100:
+ * NbKrylovSpaces 30, MaxIter 50, RelativeTolerance 1e-5) for a single partition, entirely on the device: J x = rhs with the
+ * right-hand side taken from the device rhs buffer and the solution written back into it (where StdUpdateSol reads dU:
+ * cfb200_update_sol_newton(h, NULL, ...)).  Deterministic (ordered sums, no atomics). */
+typedef struct cfb200_gmres_params {
+  int32_t restart;     /* Krylov vectors per cycle (PETSc NbKrylovSpaces) */
+  int32_t maxIter;     /* total iterations */
+  int32_t precond;     /* 0 none, 1 block Jacobi (inverted diagonal q x q blocks), right preconditioning */
+  int32_t reserved;
+  double relTol, absTol;
+} cfb200_gmres_params;
+int cfb200_solve_gmres(cfb200_handle* h, const cfb200_gmres_params* p, int32_t* iterations, double* relResidual);
 /* named fields, reference (AoS, reference IDs) layout: "rhs","updateCoeff","uX","uY","uZ","limiter","nstates","gstates";
  * "divB" [nCells] (MHD3DProjection only): the divergence diagnostic of FVMCC_ComputeRHSMHD.ci:160-203, formed from the
  * face fluxes of the last evaluation */

@@ -40,6 +40,14 @@ struct HostLoopBackend {
       }
     }
   }
+  template <class F> void launchCellStaged(const char*, const F& f, int n) {
+    double stg[F::BLK];
+    for (int i = 0; i < n; ++i) {
+      f.run(i, stg, 1);
+      const int slot = f.slot(i);
+      if (slot >= 0) for (int k = 0; k < F::BLK; ++k) f.out()[(size_t)slot*F::BLK + k] = stg[k];
+    }
+  }
   template <class F> void launchPhased(const char*, const F& f, int n) {
     double stg[F::STAGE];
     for (int i = 0; i < n; ++i) {
