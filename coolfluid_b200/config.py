@@ -17,7 +17,7 @@ DV_DIAMOND, DV_CORRECTED = 0, 1
 UV_CONS, UV_PVT = 0, 1
 FS_ROE, FS_AUSMPLUS, FS_AUSMPLUSUP, FS_LAXFRIED, FS_HLL = 0, 1, 2, 3, 4
 PR_CONSTANT, PR_LINEARLS = 0, 1
-LIM_NONE, LIM_VENKTN, LIM_BARTHJESP = 0, 1, 2
+LIM_NONE, LIM_VENKTN, LIM_BARTHJESP, LIM_VENKTN_STRICT = 0, 1, 2, 3
 DIFF_NONE, DIFF_NS = 0, 1
 VISC_SIMPLER_SUTHERLAND, VISC_SUTHERLAND, VISC_FIXED = 0, 1, 2
 BC_SUPER_OUTLET, BC_DIRICHLET, BC_MIRROR_VELOCITY, BC_MIRROR_EULER_CONS, BC_FARFIELD_EULER = 0, 1, 2, 3, 4
@@ -45,7 +45,8 @@ class ConfigStruct(C.Structure):
         ("physicalModel", C.c_int32), ("entropyFixID", C.c_int32), ("refSpeed", C.c_double), ("coeffSigmoid", C.c_double),
         ("derivativeStrategy", C.c_int32), ("fuseTimeRhs", C.c_int32),
         ("timeZeroDiag", C.c_int32*MAXEQ), ("timeAnalyticalMatrix", C.c_int32), ("timeUseGlobalDT", C.c_int32),
-        ("reserved1", C.c_int32), ("dt", C.c_double),
+        ("renumber", C.c_int32), ("dt", C.c_double),
+        ("venktnIsMFMHD", C.c_int32), ("psiMinEqual1", C.c_int32), ("strictCoeff", C.c_double),
     ]
 
 
@@ -142,6 +143,10 @@ def make_config(dim, update_var=UV_CONS, flux=FS_ROE, poly_rec=PR_CONSTANT, limi
     c.timeAnalyticalMatrix = int(kw.get("time_analytical_matrix", 0))
     c.timeUseGlobalDT = int(kw.get("time_use_global_dt", 0))
     c.dt = float(kw.get("dt", 0.0))
+    c.renumber = int(kw.get("renumber", 0))
+    c.venktnIsMFMHD = int(kw.get("is_mfmhd", 1 if limiter == LIM_VENKTN_STRICT else 0))
+    c.psiMinEqual1 = int(kw.get("psi_min_equal_1", 0))
+    c.strictCoeff = float(kw.get("strict_coeff", 1.0))
     return c
 
 

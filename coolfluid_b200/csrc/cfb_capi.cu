@@ -506,8 +506,11 @@ int cfb200_set_halo(cfb200_handle* h, const int32_t* sendPtr, const int32_t* sen
     CFB_CUDA(cudaMalloc((void**)&H->dRecv, sizeof(int)*std::max(nr, 1)));
     CFB_CUDA(cudaMalloc((void**)&H->sbuf, sizeof(double)*std::max(ns, 1)*q));
     CFB_CUDA(cudaMalloc((void**)&H->rbuf, sizeof(double)*std::max(nr, 1)*q));
-    if (ns) CFB_CUDA(cudaMemcpy(H->dSend, sendCells, sizeof(int)*ns, cudaMemcpyHostToDevice));
-    if (nr) CFB_CUDA(cudaMemcpy(H->dRecv, recvCells, sizeof(int)*nr, cudaMemcpyHostToDevice));
+    std::vector<int32_t> sc(ns), rc(nr);                 // the caller's cell IDs -> storage IDs (cfg.renumber)
+    for (int i = 0; i < ns; ++i) sc[i] = e.cinv(sendCells[i]);
+    for (int i = 0; i < nr; ++i) rc[i] = e.cinv(recvCells[i]);
+    if (ns) CFB_CUDA(cudaMemcpy(H->dSend, sc.data(), sizeof(int)*ns, cudaMemcpyHostToDevice));
+    if (nr) CFB_CUDA(cudaMemcpy(H->dRecv, rc.data(), sizeof(int)*nr, cudaMemcpyHostToDevice));
     H->haveLists = true;
     e.nIndep = nIndependent;
     return CFB200_OK;
@@ -643,9 +646,9 @@ int cfb200_solve_gmres(cfb200_handle* h, const cfb200_gmres_params* prm, int32_t
     };
     auto spmv = [&](const double* x, double* y) { launchN(e, "gmresSpmv", cfb::BsrSpmv{e.d.bsrRowPtr, e.d.bsrColInd, e.d.bsrVal, x, y, q}, n); };
     auto prec = [&](const double* x, double* y) { launchN(e, "gmresPrec", cfb::ApplyDiagInv{W.dinv, x, y, q, prm->precond}, n); };
-    if (prm->precond) bk.launch("gmresInvDiag", cfb::InvertDiag{e.d.diagSlot, e.d.updatable, e.d.bsrVal, W.dinv, q}, e.d.nCells, 128);
+    if (prm->precond) bk.launch("gmresInvDiag", cfb::InvertDiag{e.d.bsrRowPtr, e.d.bsrColInd, e.dUpdatableByRow, e.d.bsrVal, W.dinv, q}, e.d.nCells, 128);
     bk.d2d(W.b, e.d.rhs, sizeof(double)*n);
-    launchN(e, "gmresMask", cfb::VecZeroMasked{e.d.updatable, W.b, q}, n);
+    launchN(e, "gmresMask", cfb::VecZeroMasked{e.dUpdatableByRow, W.b, q}, n);
     bk.memset(W.x, 0, sizeof(double)*n);
     bk.d2d(W.w, W.b, sizeof(double)*n);                 // r0 = b (x0 = 0)
     double beta = std::sqrt(dot(W.w, W.w));

@@ -118,9 +118,97 @@ public:
 
   int q() const { return cfg.nEqs; }
 
+  // ---- storage permutation (cfg.renumber) -----------------------------------------------------------
+  // Cells along the Morton curve of their centres, interior faces by (lower, higher) storage cell; boundary faces, ghosts
+  // and nodes keep their places.  The permuted copy of the caller's mesh keeps every LIST ORDER of the original (a cell's
+  // faces, its stencil, a node's neighbours): only the IDs inside change.  cellRef / faceRef give the caller's IDs back.
+  struct Permuted {
+    std::vector<double> centres, normals, areas, volumes, cvol;
+    std::vector<int32_t> faceL, faceR, faceNodePtr, faceNodes, cellFacePtr, cellFaces, stencilPtr, stencil, nodeNbr, faceBC;
+    std::vector<uint8_t> cvSign, updatable;
+    cfb200_mesh view;
+  };
+  std::vector<int32_t> hCellRef, hCellInv, hFaceRef;     // storage -> caller, caller -> storage, storage face -> caller face
+  int* dStateRef = nullptr; int* dFaceRef = nullptr;     // device: [nStates] (ghosts map to themselves), [nFaces]
+  uint8_t* dUpdatableByRow = nullptr;                    // updatable flag by BSR row (= caller's cell ID)
+  static uint64_t spread3(uint64_t x) {                  // 21 bits -> every third bit
+    x &= 0x1fffff; x = (x | x << 32) & 0x1f00000000ffffULL; x = (x | x << 16) & 0x1f0000ff0000ffULL;
+    x = (x | x << 8) & 0x100f00f00f00f00fULL; x = (x | x << 4) & 0x10c30c30c30c30c3ULL; x = (x | x << 2) & 0x1249249249249249ULL;
+    return x;
+  }
+  void buildPermutation(const cfb200_mesh& m, Permuted& P) {
+    const int D = m.dim, nc = m.nCells, ng = m.nGhosts, nf = m.nFaces, ni = m.nInner, nn = m.nNodes;
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    for (int c = 0; c < nc; ++c) for (int k = 0; k < D; ++k) { lo[k] = std::min(lo[k], m.centres[(size_t)c*D + k]); hi[k] = std::max(hi[k], m.centres[(size_t)c*D + k]); }
+    std::vector<std::pair<uint64_t, int32_t> > key(nc);
+    for (int c = 0; c < nc; ++c) {
+      uint64_t code = 0;
+      for (int k = 0; k < D; ++k) {
+        const double t = (hi[k] > lo[k]) ? (m.centres[(size_t)c*D + k] - lo[k])/(hi[k] - lo[k]) : 0.;
+        code |= spread3((uint64_t)(t*2097151.0)) << k;
+      }
+      key[c] = std::make_pair(code, (int32_t)c);
+    }
+    std::sort(key.begin(), key.end());
+    hCellRef.resize(nc); hCellInv.resize(nc);
+    for (int i = 0; i < nc; ++i) { hCellRef[i] = key[i].second; hCellInv[key[i].second] = i; }
+    auto st = [&](int s) { return s < nc ? hCellInv[s] : s; };      // state id: cells move, ghosts stay
+    // interior faces by their storage cells
+    std::vector<std::pair<std::pair<int32_t, int32_t>, int32_t> > fk(ni);
+    for (int f = 0; f < ni; ++f) {
+      const int a = hCellInv[m.faceL[f]], b = hCellInv[m.faceR[f]];
+      fk[f] = std::make_pair(std::make_pair(std::min(a, b), std::max(a, b)), (int32_t)f);
+    }
+    std::sort(fk.begin(), fk.end());
+    hFaceRef.resize(nf);
+    std::vector<int32_t> finv(nf);
+    for (int f = 0; f < ni; ++f) hFaceRef[f] = fk[f].second;
+    for (int f = ni; f < nf; ++f) hFaceRef[f] = f;
+    for (int f = 0; f < nf; ++f) finv[hFaceRef[f]] = f;
+    const int ns = nc + ng;
+    P.centres.resize((size_t)ns*D);
+    for (int i = 0; i < ns; ++i) { const int o = i < nc ? hCellRef[i] : i; for (int k = 0; k < D; ++k) P.centres[(size_t)i*D + k] = m.centres[(size_t)o*D + k]; }
+    P.volumes.resize(nc); P.updatable.resize(nc);
+    for (int i = 0; i < nc; ++i) { P.volumes[i] = m.volumes[hCellRef[i]]; P.updatable[i] = m.updatable[hCellRef[i]]; }
+    P.faceL.resize(nf); P.faceR.resize(nf); P.normals.resize((size_t)nf*D); P.areas.resize(nf); P.cvol.resize(nf);
+    P.cvSign.resize(nf); P.faceBC.resize(nf); P.faceNodePtr.assign(1, 0);
+    for (int f = 0; f < nf; ++f) {
+      const int o = hFaceRef[f];
+      P.faceL[f] = st(m.faceL[o]); P.faceR[f] = st(m.faceR[o]);       // the orientation (which cell is L) is the caller's
+      for (int k = 0; k < D; ++k) P.normals[(size_t)f*D + k] = m.normals[(size_t)o*D + k];
+      P.areas[f] = m.areas[o]; P.cvol[f] = m.cvol[o]; P.cvSign[f] = m.cvSign[o]; P.faceBC[f] = m.faceBC[o];
+      P.faceNodes.insert(P.faceNodes.end(), m.faceNodes + m.faceNodePtr[o], m.faceNodes + m.faceNodePtr[o+1]);
+      P.faceNodePtr.push_back((int32_t)P.faceNodes.size());
+    }
+    P.cellFacePtr.assign(1, 0); P.stencilPtr.assign(1, 0);
+    for (int i = 0; i < nc; ++i) {
+      const int o = hCellRef[i];
+      for (int k = m.cellFacePtr[o]; k < m.cellFacePtr[o+1]; ++k) P.cellFaces.push_back(finv[m.cellFaces[k]]);
+      P.cellFacePtr.push_back((int32_t)P.cellFaces.size());
+      for (int k = m.stencilPtr[o]; k < m.stencilPtr[o+1]; ++k) P.stencil.push_back(st(m.stencil[k]));
+      P.stencilPtr.push_back((int32_t)P.stencil.size());
+    }
+    P.nodeNbr.resize((size_t)m.nodeNbrPtr[nn]);
+    for (size_t k = 0; k < P.nodeNbr.size(); ++k) P.nodeNbr[k] = st(m.nodeNbr[k]);
+    P.view = m;
+    P.view.centres = P.centres.data(); P.view.faceL = P.faceL.data(); P.view.faceR = P.faceR.data();
+    P.view.faceNodePtr = P.faceNodePtr.data(); P.view.faceNodes = P.faceNodes.data(); P.view.normals = P.normals.data();
+    P.view.areas = P.areas.data(); P.view.volumes = P.volumes.data(); P.view.cellFacePtr = P.cellFacePtr.data();
+    P.view.cellFaces = P.cellFaces.data(); P.view.stencilPtr = P.stencilPtr.data(); P.view.stencil = P.stencil.data();
+    P.view.nodeNbr = P.nodeNbr.data(); P.view.cvol = P.cvol.data(); P.view.cvSign = P.cvSign.data();
+    P.view.faceBC = P.faceBC.data(); P.view.updatable = P.updatable.data();
+  }
+  // the caller's ID of a storage cell / face (the identity without renumbering): what defines every summation order
+  int cref(int c) const { return hCellRef.empty() ? c : hCellRef[c]; }
+  int fref(int f) const { return hFaceRef.empty() ? f : hFaceRef[f]; }
+  int cinv(int c) const { return hCellInv.empty() ? c : hCellInv[c]; }
+
   // ---- setup: static data + gather tables --------------------------------------------------------
-  void setMesh(const cfb200_mesh& m, int nbc, const cfb200_bc* bcs) {
-    if (m.dim != cfg.dim) throw std::invalid_argument("mesh dimension differs from the configuration");
+  void setMesh(const cfb200_mesh& mIn, int nbc, const cfb200_bc* bcs) {
+    if (mIn.dim != cfg.dim) throw std::invalid_argument("mesh dimension differs from the configuration");
+    Permuted perm;
+    if (cfg.renumber) buildPermutation(mIn, perm);
+    const cfb200_mesh& m = cfg.renumber ? perm.view : mIn;
     const int D = m.dim, nc = m.nCells, ng = m.nGhosts, nf = m.nFaces, nn = m.nNodes, ni = m.nInner;
     const int ns = nc + ng;
     const int Q = q();
@@ -183,7 +271,7 @@ public:
       std::vector<int32_t> tmp;
       for (int c = 0; c < nc; ++c) {
         tmp.assign(m.cellFaces + m.cellFacePtr[c], m.cellFaces + m.cellFacePtr[c+1]);
-        std::sort(tmp.begin(), tmp.end());
+        std::sort(tmp.begin(), tmp.end(), [&](int a, int b) { return fref(a) < fref(b); });     // the caller's loop order
         for (size_t k = 0; k < tmp.size(); ++k) {
           const int f = tmp[k];
           const bool isR = (m.faceL[f] != c);
@@ -199,19 +287,24 @@ public:
     // LSQ gather list: replay the reference's edge loop (LeastSquareP1PolyRec2D.cxx:100-134): cell i visits
     // stencil entries that are ghosts or have a higher ID; the edge contributes to i and (if not ghost) to `last`.
     {
+      // (cells are visited in the CALLER's order and compared by the caller's IDs: r = reference ID, i = storage ID)
       std::vector<int32_t> cnt(nc + 1, 0);
-      for (int i = 0; i < nc; ++i)
+      for (int r = 0; r < nc; ++r) {
+        const int i = cinv(r);
         for (int k = m.stencilPtr[i]; k < m.stencilPtr[i+1]; ++k) {
           const int last = m.stencil[k];
-          if (last >= nc || last > i) { cnt[i+1]++; if (last < nc) cnt[last+1]++; }
+          if (last >= nc || cref(last) > r) { cnt[i+1]++; if (last < nc) cnt[last+1]++; }
         }
+      }
       for (int i = 0; i < nc; ++i) cnt[i+1] += cnt[i];
       std::vector<int32_t> pos(cnt.begin(), cnt.end() - 1), nbr(cnt[nc]);
-      for (int i = 0; i < nc; ++i)
+      for (int r = 0; r < nc; ++r) {
+        const int i = cinv(r);
         for (int k = m.stencilPtr[i]; k < m.stencilPtr[i+1]; ++k) {
           const int last = m.stencil[k];
-          if (last >= nc || last > i) { nbr[pos[i]++] = last; if (last < nc) nbr[pos[last]++] = i; }
+          if (last >= nc || cref(last) > r) { nbr[pos[i]++] = last; if (last < nc) nbr[pos[last]++] = i; }
         }
+      }
       d.lsqPtr = upload(cnt);
       d.lsqNbr = upload(nbr);
       d.lsqW = dalloc<double>(nbr.size());
@@ -221,19 +314,22 @@ public:
       hRowPtr.assign(1, 0);
       hColInd.clear();
       hColInd.reserve(ncf + nc);
+      // rows and columns are the CALLER's cell IDs (the matrix is the consumer's): row r = storage cell cinv(r)
       std::vector<int32_t> cols;
-      for (int c = 0; c < nc; ++c) {
-        cols.assign(1, c);
+      for (int r = 0; r < nc; ++r) {
+        const int c = cinv(r);
+        cols.assign(1, r);
         for (int k = m.cellFacePtr[c]; k < m.cellFacePtr[c+1]; ++k) {
           const int f = m.cellFaces[k];
-          if (f < ni) cols.push_back(m.faceL[f] == c ? m.faceR[f] : m.faceL[f]);
+          if (f < ni) cols.push_back(cref(m.faceL[f] == c ? m.faceR[f] : m.faceL[f]));
         }
         std::sort(cols.begin(), cols.end());
         hColInd.insert(hColInd.end(), cols.begin(), cols.end());
         hRowPtr.push_back((int32_t)hColInd.size());
       }
       nnzb = (int64_t)hColInd.size();
-      auto slot = [&](int r, int cidx) {
+      auto slot = [&](int cRow, int cCol) {        // storage cell ids in, slot of block (row, column) out
+        const int r = cref(cRow), cidx = cref(cCol);
         const int32_t* b = &hColInd[hRowPtr[r]]; const int32_t* e = &hColInd[hRowPtr[r+1]];
         const int32_t* it = std::lower_bound(b, e, cidx);
         if (it == e || *it != cidx) throw std::runtime_error("BSR slot not found");
@@ -249,7 +345,7 @@ public:
       std::vector<int32_t> dsrc(ncf);
       for (int c = 0; c < nc; ++c) {
         std::vector<int32_t> fs(m.cellFaces + m.cellFacePtr[c], m.cellFaces + m.cellFacePtr[c+1]);
-        std::sort(fs.begin(), fs.end());
+        std::sort(fs.begin(), fs.end(), [&](int a, int b) { return fref(a) < fref(b); });
         for (size_t k = 0; k < fs.size(); ++k) {
           const int f = fs[k];
           dsrc[m.cellFacePtr[c] + k] = (f >= ni) ? ~(f - ni) : ((m.faceL[f] == c) ? sRL[f] : sLR[f]);
@@ -288,6 +384,19 @@ public:
       std::vector<double> ones((size_t)Q*nc, 1.0);   // limiter socket starts at 1 (LeastSquareP1Setup.cxx:127-129)
       bk.h2d(d.lim, ones.data(), ones.size()*sizeof(double));
     }
+    d.cellRef = nullptr;
+    {
+      std::vector<uint8_t> byRow(nc);
+      for (int c = 0; c < nc; ++c) byRow[cref(c)] = m.updatable[c];
+      dUpdatableByRow = upload(byRow);
+    }
+    if (cfg.renumber) {
+      std::vector<int32_t> sref(ns);
+      for (int i = 0; i < ns; ++i) sref[i] = i < nc ? hCellRef[i] : i;
+      dStateRef = upload(sref);
+      dFaceRef = upload(hFaceRef);
+      d.cellRef = dStateRef;
+    }
     bk.launch("faceCentres", FaceCentres{d}, nf, 256);
     if (D == 2) bk.launch("lsqSetup", LsqSetup<2>{d}, nc, 256); else bk.launch("lsqSetup", LsqSetup<3>{d}, nc, 256);
     bk.sync();
@@ -299,13 +408,14 @@ public:
   }
 
   // ---- AoS <-> SoA transfers ---------------------------------------------------------------------
-  void putAoS(double* dstSoA, int ld, const double* hostAoS, int n, int k) {
+  // ref: storage -> caller index of the items (dStateRef for cell / state arrays, dFaceRef for face arrays) or null
+  void putAoS(double* dstSoA, int ld, const double* hostAoS, int n, int k, const int* ref = nullptr) {
     bk.h2d(d.aos, hostAoS, (size_t)n*k*sizeof(double));
-    bk.launch("aosToSoa", AosToSoa{d.aos, dstSoA, n, k, ld}, n*k, 256);
+    bk.launch("aosToSoa", AosToSoa{d.aos, dstSoA, n, k, ld, ref}, n*k, 256);
     bk.sync();
   }
-  void getAoS(const double* srcSoA, int ld, double* hostAoS, int n, int k) {
-    bk.launch("soaToAos", SoaToAos{srcSoA, d.aos, n, k, ld}, n*k, 256);
+  void getAoS(const double* srcSoA, int ld, double* hostAoS, int n, int k, const int* ref = nullptr) {
+    bk.launch("soaToAos", SoaToAos{srcSoA, d.aos, n, k, ld, ref}, n*k, 256);
     bk.d2h(hostAoS, d.aos, (size_t)n*k*sizeof(double));
   }
 
@@ -446,8 +556,11 @@ public:
       if (cells[i] < 0 || cells[i] >= d.nCells || in[cells[i]]) throw std::invalid_argument("set_independent_cells: bad or repeated cell id");
       in[cells[i]] = 1;
     }
-    std::vector<int32_t> a(cells, cells + n), b;
-    for (int c = 0; c < d.nCells; ++c) if (!in[c]) b.push_back(c);
+    std::vector<int32_t> a(n), b;
+    for (int i = 0; i < n; ++i) a[i] = cinv(cells[i]);
+    std::sort(a.begin(), a.end());
+    for (int r = 0; r < d.nCells; ++r) if (!in[r]) b.push_back(cinv(r));
+    std::sort(b.begin(), b.end());
     indepCells = upload(a); depCells = upload(b); nIndepList = n;
   }
   // position-dependent Dirichlet data of one boundary-condition record: values[iFace*q + v] for the faces of that

@@ -38,6 +38,9 @@ struct Dev {
   const uint8_t* updatable;
   const uint8_t* cellActive;  // cell touches at least one face with an updatable side
   const BCond* bcs;
+  // storage permutation (cfg.renumber): reference (caller) ID of internal cell i; null = the identity.  rhs, updateCoeff,
+  // the norm partials and the BSR rows are indexed by REFERENCE id (they are the consumer's), everything else by storage id
+  const int* cellRef;
   double* lsqL;               // [6][nCells]  l11 l12 l13 l22 l23 l33
   double* lsqW;               // [len(lsqNbr)] inverse-distance weight of each gather entry (static geometry: formed once at setup)
   // ---- block Jacobian ----
@@ -62,15 +65,24 @@ struct Dev {
   int* status;
 };
 
+CFB_HD int refId(const Dev& d, int cell) { return d.cellRef ? d.cellRef[cell] : cell; }
+
 // ------------------------------------------------------------------------------------------------
-// layout conversion between the reference's AoS sockets and the device SoA
+// layout conversion between the reference's AoS sockets and the device SoA; ref (optional): storage item i is the
+// caller's item ref[i] (cells / faces renumbered inside the engine)
 struct AosToSoa {   // idx over n*q
-  const double* src; double* dst; int n, q, ld;
-  CFB_HD void operator()(int idx) const { const int i = idx/q, v = idx - i*q; dst[(size_t)v*ld + i] = src[idx]; }
+  const double* src; double* dst; int n, q, ld; const int* ref;
+  CFB_HD void operator()(int idx) const {
+    const int i = idx/q, v = idx - i*q;
+    dst[(size_t)v*ld + i] = src[ref ? (size_t)ref[i]*q + v : (size_t)idx];
+  }
 };
 struct SoaToAos {
-  const double* src; double* dst; int n, q, ld;
-  CFB_HD void operator()(int idx) const { const int i = idx/q, v = idx - i*q; dst[idx] = src[(size_t)v*ld + i]; }
+  const double* src; double* dst; int n, q, ld; const int* ref;
+  CFB_HD void operator()(int idx) const {
+    const int i = idx/q, v = idx - i*q;
+    dst[ref ? (size_t)ref[i]*q + v : (size_t)idx] = src[(size_t)v*ld + i];
+  }
 };
 struct FaceCentres {   // idx over faces
   Dev d;
@@ -310,6 +322,7 @@ struct LimiterK {   // idx over cells
       }
       avgDistance /= nbFaces;
     }
+    double weight = 0.0;      // Venktn3DStrict.cxx:87,150-151: from the density (v == 0), kept for the other variables
     for (int v = 0; v < Q; ++v) {
       const double u0 = d.U[(size_t)v*d.nStates + cell];
       double min0 = u0, max0 = u0;
@@ -335,7 +348,35 @@ struct LimiterK {   // idx over cells
       double psimin = 1.1;
       const double ux = d.uX[(size_t)v*d.nCells + cell], uy = d.uY[(size_t)v*d.nCells + cell];
       const double uz = (D == 3) ? d.uZ[(size_t)v*d.nCells + cell] : 0.;
-      if (c.limiter == CFB200_LIM_VENKTN) {
+      const bool strict = (c.limiter == CFB200_LIM_VENKTN_STRICT);
+      if (strict && v == 0) weight = c.strictCoeff*fabs(ddiv(min0 + 1e-10, max0 + 1e-10)) + (1.0 - c.strictCoeff);
+      if ((c.limiter == CFB200_LIM_VENKTN && c.venktnIsMFMHD) || strict) {
+        // "implementation from the Venkatakrishnan paper": Venktn3D.cxx:125-156 / Venktn3DStrict.cxx:166-203
+        if (!(strict && !c.venktnIsMFMHD)) {
+          const double mag = c.magnitudeValues[v];
+          const Recip rmag = recipOf(mag);
+          const double epsilon2 = pow3(ddiv(c.coeffEps*avgDistance, c.length));
+#pragma unroll
+          for (int j = 0; j < 6; ++j) if (j < nbFaces) {
+            double deltaMin;
+            if (D == 2) deltaMin = ux*dxq[j][0] + uy*dxq[j][1];
+            else deltaMin = ux*dxq[j][0] + uy*dxq[j][1] + uz*dxq[j][2];
+            const bool pos = deltaMin > 0.0;
+            const double dMinStar = ((deltaMin < 0.0) ? -1.0 : 1.0)*(divBy(fabs(deltaMin), rmag) + 1e-24);
+            const double dPlus = divBy(pos ? deltaPlusMax : deltaPlusMin, rmag);
+            const double dPlus2 = dPlus*dPlus;
+            const double dPlusMin = dPlus*dMinStar;
+            const double Num = (dPlus2 + epsilon2)*dMinStar + ((2*dMinStar)*dMinStar)*dPlus;
+            const double Den = ((dPlus2 + (2*dMinStar)*dMinStar) + dPlusMin) + epsilon2;
+            const double cand = ddiv(1., dMinStar)*ddiv(Num, Den);
+            if (deltaMin > 0.0 || deltaMin < 0.0) psi = cand;        // psi is kept when deltaMin == 0
+            if (strict) {
+              if (v < 4 || v == 7) psimin = dmin(psi*weight, psimin);
+              else psimin = (!c.psiMinEqual1) ? dmin(psi, psimin) : 1.0;
+            } else psimin = dmin(psi, psimin);
+          }
+        }
+      } else if (c.limiter == CFB200_LIM_VENKTN) {
         const double epsilon = c.coeffEps*c.magnitudeValues[v]*c.magnitudeValues[v]*pow3(ddiv(avgDistance, c.length));
 #pragma unroll
         for (int j = 0; j < 6; ++j) if (j < nbFaces) {
@@ -496,7 +537,8 @@ struct CellGather {   // idx over cells
     constexpr int Q = PH::Q;
     double r[Q];
     for (int v = 0; v < Q; ++v) r[v] = 0.;
-    double uc = d.updateCoeff[cell];
+    const int rc = refId(d, cell);
+    double uc = d.updateCoeff[rc];
     const double coeff = c.resFactor*1.0;
     const bool hasDiff = (c.diffusive == CFB200_DIFF_NS);
     for (int j = d.cellFacePtr[cell]; j < d.cellFacePtr[cell+1]; ++j) {
@@ -522,8 +564,8 @@ struct CellGather {   // idx over cells
       // block part -> staging area -> (coalesced) the not yet written diagonal slot: DiagGather adds it to its face sum
       if (c.computeJacobian) timeBlock<D, PH>(c, u, diagValue, stg, stride);
     }
-    for (int v = 0; v < Q; ++v) d.rhs[(size_t)cell*Q + v] = r[v];
-    d.updateCoeff[cell] = uc;
+    for (int v = 0; v < Q; ++v) d.rhs[(size_t)rc*Q + v] = r[v];
+    d.updateCoeff[rc] = uc;
   }
 };
 
@@ -548,7 +590,7 @@ struct DivBGather {   // idx over cells
       const double t = divBy(d.faceFlux[(size_t)(Q-1)*d.nFaces + f], rd);
       if (isR) acc -= t; else acc += t;
     }
-    out[cell] = acc;
+    out[refId(d, cell)] = acc;
   }
 };
 
@@ -599,9 +641,9 @@ struct ZeroRows {   // idx over (non-updatable cell list) * GS
   Dev d; const int* cells; int first;      // first: position in the list of the first cell of this launch
   CFB_HD void operator()(int idx) const {
     constexpr int Q = PH::Q;
-    const int cell = cells[first + idx/GS], e = idx - (idx/GS)*GS;
+    const int row = refId(d, cells[first + idx/GS]), e = idx - (idx/GS)*GS;
     if (e >= Q*Q) return;
-    for (int k = d.bsrRowPtr[cell]; k < d.bsrRowPtr[cell+1]; ++k) d.bsrVal[(size_t)k*Q*Q + e] = 0.;
+    for (int k = d.bsrRowPtr[row]; k < d.bsrRowPtr[row+1]; ++k) d.bsrVal[(size_t)k*Q*Q + e] = 0.;
   }
 };
 
@@ -615,13 +657,14 @@ struct TimeRhs {   // idx over cells
   CFB_HD void operator()(int cell) const {
     constexpr int Q = PH::Q;
     if (!d.updatable[cell]) return;
-    const double diagValue = timeDiagValue<D, PH>(d, c, cell, d.updateCoeff[cell], minDt);
+    const int rc = refId(d, cell);
+    const double diagValue = timeDiagValue<D, PH>(d, c, cell, d.updateCoeff[rc], minDt);
     double u[Q], r[Q];
 #pragma unroll
-    for (int v = 0; v < Q; ++v) { u[v] = d.U[(size_t)v*d.nStates + cell]; r[v] = d.rhs[(size_t)cell*Q + v]; }
+    for (int v = 0; v < Q; ++v) { u[v] = d.U[(size_t)v*d.nStates + cell]; r[v] = d.rhs[(size_t)rc*Q + v]; }
     timeRhsRow<D, PH>(d, c, cell, u, diagValue, r);
 #pragma unroll
-    for (int v = 0; v < Q; ++v) d.rhs[(size_t)cell*Q + v] = r[v];
+    for (int v = 0; v < Q; ++v) d.rhs[(size_t)rc*Q + v] = r[v];
     if (!doJac) return;
     double* blk = &d.bsrVal[(size_t)d.diagSlot[cell]*Q*Q];
     if (c.timeAnalyticalMatrix) {
@@ -651,7 +694,7 @@ struct TimeRhs {   // idx over cells
 template <int D, class PH = Phys<D> >
 struct TimeLocalDt {   // idx over cells
   Dev d; Cfg c;
-  CFB_HD void operator()(int cell) const { d.partial[cell] = ddiv(d.volumes[cell], d.updateCoeff[cell])*c.cfl; }
+  CFB_HD void operator()(int cell) const { d.partial[cell] = ddiv(d.volumes[cell], d.updateCoeff[refId(d, cell)])*c.cfl; }
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -663,21 +706,22 @@ struct UpdateSolFwdEuler {   // idx over cells
   CFB_HD void operator()(int cell) const {
     constexpr int Q = PH::Q;
     double sq = 0.;
+    const int rc = refId(d, cell);
     if (!d.updatable[cell]) {
-      for (int v = 0; v < Q; ++v) d.rhs[(size_t)cell*Q + v] = 0.;
+      for (int v = 0; v < Q; ++v) d.rhs[(size_t)rc*Q + v] = 0.;
     } else {
-      const double uc = d.updateCoeff[cell];
+      const double uc = d.updateCoeff[rc];
       const bool isZero = fabs(uc) <= 2.2250738585072014e-308;
       const double dt = isZero ? 0. : cfl/uc;
       for (int v = 0; v < Q; ++v) {
-        double rhsState = d.rhs[(size_t)cell*Q + v];     // a copy: the rhs socket itself is NOT scaled (UpdateSol.cxx:176-177)
+        double rhsState = d.rhs[(size_t)rc*Q + v];     // a copy: the rhs socket itself is NOT scaled (UpdateSol.cxx:176-177)
         d.U[(size_t)v*d.nStates + cell] += rhsState *= dt;
       }
-      const double t = d.rhs[(size_t)cell*Q + monitorVar]; // ComputeL2Norm.cxx:111-125 on the rhs socket
+      const double t = d.rhs[(size_t)rc*Q + monitorVar]; // ComputeL2Norm.cxx:111-125 on the rhs socket
       sq = t*t;
     }
-    d.updateCoeff[cell] = 0.0;
-    d.partial[cell] = sq;
+    d.updateCoeff[rc] = 0.0;
+    d.partial[rc] = sq;              // the ordered norm sum runs in reference order
   }
 };
 
@@ -690,18 +734,19 @@ struct UpdateSolNewton {   // idx over cells
   CFB_HD void operator()(int cell) const {
     constexpr int Q = PH::Q;
     double sq = 0.;
+    const int rc = refId(d, cell);
     if (!d.updatable[cell]) {
-      for (int v = 0; v < Q; ++v) d.rhs[(size_t)cell*Q + v] = 0.;
+      for (int v = 0; v < Q; ++v) d.rhs[(size_t)rc*Q + v] = 0.;
     } else {
 #pragma unroll
       for (int v = 0; v < Q; ++v) {
-        const double dU = d.rhs[(size_t)cell*Q + v];
+        const double dU = d.rhs[(size_t)rc*Q + v];
         d.U[(size_t)v*d.nStates + cell] += alpha[v]*dU;
         if (v == monitorVar) sq = dU*dU;
       }
     }
-    d.updateCoeff[cell] = 0.0;
-    d.partial[cell] = sq;
+    d.updateCoeff[rc] = 0.0;
+    d.partial[rc] = sq;
   }
 };
 

@@ -49,12 +49,14 @@ struct BsrSpmv {
 };
 // inverse of every diagonal block: Gauss-Jordan without pivoting (the pseudo-time term makes the diagonal blocks strongly
 // diagonally dominant); rows of non-updatable cells get the identity.  One thread per cell, q <= 9.
-struct InvertDiag {
-  const int* diagSlot; const uint8_t* updatable; const double* bsr; double* inv; int q;
+struct InvertDiag {      // idx over block rows (the matrix's own numbering)
+  const int* rowPtr; const int* colInd; const uint8_t* updatable; const double* bsr; double* inv; int q;
   __device__ void operator()(int c) const {
     double a[81], b[81];
     const int qq = q*q;
-    const double* blk = bsr + (size_t)diagSlot[c]*qq;
+    int ds = rowPtr[c];
+    while (colInd[ds] != c) ++ds;                       // columns ascending, the diagonal block is always present
+    const double* blk = bsr + (size_t)ds*qq;
     for (int i = 0; i < qq; ++i) { a[i] = blk[i]; b[i] = 0.; }
     for (int i = 0; i < q; ++i) b[i*q + i] = 1.;
     if (updatable[c]) {

@@ -126,6 +126,21 @@ def hex_box(nx, ny, nz, lengths=(1.0, 1.0, 1.0), jitter=0.15, seed=12345, k0=0, 
                        np.full(nc, SH_HEXA), ["xmin", "xmax", "ymin", "ymax", "zmin", "zmax"], ptr, fc, fnp, fn)
 
 
+def shuffle_cells(em, seed=4321):
+    """The same mesh with its cells renumbered at random (nodes keep their IDs): what a mesh generator without any
+    locality in its numbering hands over.  Returns (mesh, new -> old cell map)."""
+    rng = np.random.RandomState(seed)
+    perm = rng.permutation(em.n_cells)                         # new -> old
+    inv = np.empty_like(perm); inv[perm] = np.arange(em.n_cells)
+    npc = np.diff(em.cell_node_ptr).astype(np.int64)
+    lnpc = npc[perm]
+    ptr = np.concatenate([[0], np.cumsum(lnpc)])
+    src = np.repeat(em.cell_node_ptr[perm].astype(np.int64), lnpc) + (np.arange(ptr[-1]) - np.repeat(ptr[:-1], lnpc))
+    out = ElementMesh(em.dim, em.nodes, ptr.astype(np.int32), em.cell_nodes[src], em.cell_shape[perm], em.trs_names,
+                      em.trs_face_ptr, inv[em.trs_face_cell].astype(np.int32), em.trs_face_node_ptr, em.trs_face_nodes)
+    return out, perm
+
+
 # Kuhn split of the reference hexahedron (local hex nodes) into 6 positively oriented tetrahedra
 _KUHN = np.array([[0, 1, 2, 6], [0, 2, 3, 6], [0, 3, 7, 6], [0, 7, 4, 6], [0, 4, 5, 6], [0, 5, 1, 6]])
 

@@ -36,7 +36,7 @@ enum cfb200_flux_splitter { CFB200_FS_ROE = 0 /* "Roe" plugins/FiniteVolume/RoeF
 enum cfb200_poly_rec { CFB200_PR_CONSTANT = 0 /* "Constant" ConstantPolyRec.cxx */,
                        CFB200_PR_LINEARLS = 1 /* "LinearLS2D"/"LinearLS3D" LeastSquareP1PolyRec{2,3}D.cxx */ };
 enum cfb200_limiter { CFB200_LIM_NONE = 0, CFB200_LIM_VENKTN = 1 /* "Venktn2D"/"Venktn3D" */,
-                      CFB200_LIM_BARTHJESP = 2 /* "BarthJesp" */ };
+                      CFB200_LIM_BARTHJESP = 2 /* "BarthJesp" */, CFB200_LIM_VENKTN_STRICT = 3 /* "Venktn3DStrict" */ };
 enum cfb200_diffusive { CFB200_DIFF_NONE = 0, CFB200_DIFF_NS = 1 /* "NavierStokes" NSFlux.ci + DiamondVolume{2,3}D */ };
 enum cfb200_visc_law { CFB200_VISC_SIMPLER_SUTHERLAND = 0, CFB200_VISC_SUTHERLAND = 1, CFB200_VISC_FIXED = 2 };
 enum cfb200_bc_type {
@@ -124,8 +124,20 @@ typedef struct cfb200_config {
   int32_t timeZeroDiag[CFB200_MAXEQ]; /* zeroDiagValue: equations whose time term is dropped (MHD phi equation) */
   int32_t timeAnalyticalMatrix;       /* useAnalyticalMatrix: dU/dP from Euler2DPuvtToConsInPuvt / Euler3DPvtToConsInPvt */
   int32_t timeUseGlobalDT;            /* useGlobalDT: diag = V / min_cells(V/updateCoeff*CFL) */
-  int32_t reserved1;
+  /* 1: cfb200_set_mesh renumbers the cells along a space-filling curve (Morton order of the centres) and sorts the
+   * interior faces by their cells, as a pure permutation INSIDE the engine: storage and kernel access order change, every
+   * sum keeps the order the reference's numbering defines (FVMCC_MeshDataBuilder.cxx:129-365 IDs stay the parity key) and
+   * everything crossing this ABI (states, rhs, updateCoeff, fields, BSR rows / columns, halo lists) stays in the caller's
+   * numbering.  For meshes whose numbering has no locality (the gathers then miss L2). */
+  int32_t renumber;
   double dt;                          /* SubSystemStatus::getDT(): > 0 (unsteady) -> diag = V/dt, else updateCoeff/CFL */
+  /* Venkatakrishnan variants: isMFMHD = the "implementation from the Venkatakrishnan paper" branch (Venktn2D.cxx /
+   * Venktn3D.cxx:125-156, normalised by magnitudeValues); CFB200_LIM_VENKTN_STRICT = "Venktn3DStrict"
+   * (plugins/FiniteVolumeMHD/Venktn3DStrict.cxx:70-260: that branch with the density-ratio weight strictCoeff on variables
+   * 0-3 and 7 and the optional psiMinEqual1 on the others; it has no other branch, so isMFMHD must be set with it) */
+  int32_t venktnIsMFMHD;
+  int32_t psiMinEqual1;
+  double strictCoeff;
 } cfb200_config;
 
 /* Flat mesh data = the contents of the reference's sockets and connectivity tables (SURVEY.md §8b "Data ownership").

@@ -199,6 +199,7 @@ public:
     const double* xc = &mesh.centres[(size_t)c*D];
     double xq[6][3];
     for (int k = 0; k < nbFaces; ++k) faceMidPoint(mesh.cellFaces[fb+k], xq[k]);
+    double weight = 0.0;        // Venktn3DStrict.cxx:87: set at iVar == 0, kept for the other variables
     for (int iVar = 0; iVar < Q; ++iVar) {
       const double u0 = U[(size_t)c*Q + iVar];
       double min0 = u0, max0 = u0, avgDistance = 0.0;
@@ -230,7 +231,34 @@ public:
       double psimin = 1.1;
       const double ux = o.uX[(size_t)c*Q + iVar], uy = o.uY[(size_t)c*Q + iVar];
       const double uz = (D == 3) ? o.uZ[(size_t)c*Q + iVar] : 0.;
-      if (cfg.limiter == LIM_VENKTN) {
+      if (cfg.limiter == LIM_VENKTN_STRICT && iVar == 0)      // Venktn3DStrict.cxx:150-151 (pow(x, 1.0) == x)
+        weight = cfg.strictCoeff*std::abs((min0 + 1e-10)/(max0 + 1e-10)) + (1.0 - cfg.strictCoeff);
+      if ((cfg.limiter == LIM_VENKTN && cfg.venktnIsMFMHD) || cfg.limiter == LIM_VENKTN_STRICT) {
+        // "implementation from the Venkatakrishnan paper": Venktn3D.cxx:125-156, Venktn3DStrict.cxx:166-203 (the strict
+        // limiter has only this branch: without isMFMHD it returns 1.1 and complains)
+        if (cfg.limiter == LIM_VENKTN_STRICT && !cfg.venktnIsMFMHD) { lim[iVar] = psimin; continue; }
+        const double mag = cfg.magnitudeValues[iVar];
+        const double epsilon2 = cr_pow3(cfg.coeffEps*avgDistance/cfg.length);
+        for (int k = 0; k < nbFaces; ++k) {
+          double deltaMin;
+          if (D == 2) deltaMin = ux*(xq[k][0] - xc[0]) + uy*(xq[k][1] - xc[1]);
+          else deltaMin = ux*(xq[k][0] - xc[0]) + uy*(xq[k][1] - xc[1]) + uz*(xq[k][2] - xc[2]);
+          for (int sgn = 0; sgn < 2; ++sgn) {
+            if (sgn == 0 ? !(deltaMin > 0.0) : !(deltaMin < 0.0)) continue;
+            const double dMinStar = ((deltaMin < 0.0) ? -1.0 : 1.0)*(std::abs(deltaMin)/mag + 1e-24);
+            const double dPlus = (sgn == 0 ? deltaPlusMax : deltaPlusMin)/mag;
+            const double dPlus2 = dPlus*dPlus;
+            const double dPlusMin = dPlus*dMinStar;
+            const double Num = (dPlus2 + epsilon2)*dMinStar + 2*dMinStar*dMinStar*dPlus;
+            const double Den = (dPlus2 + 2*dMinStar*dMinStar + dPlusMin + epsilon2);
+            psi = 1./dMinStar*(Num/Den);
+          }
+          if (cfg.limiter == LIM_VENKTN_STRICT) {
+            if (iVar < 4 || iVar == 7) psimin = std::min(psi*weight, psimin);
+            else psimin = (!cfg.psiMinEqual1) ? std::min(psi, psimin) : 1.0;
+          } else psimin = std::min(psi, psimin);
+        }
+      } else if (cfg.limiter == LIM_VENKTN) {
         const double epsilon = cfg.coeffEps*cfg.magnitudeValues[iVar]*cfg.magnitudeValues[iVar]*
           cr_pow3(avgDistance/cfg.length);
         for (int k = 0; k < nbFaces; ++k) {

@@ -34,7 +34,7 @@ enum PhysicalModel { PM_EULER = 0, PM_MHD3D_PROJECTION = 1 };
 enum UpdateVar { UV_CONS = 0, UV_PVT = 1 };            // Euler{2,3}DCons / Euler2DPuvt, Euler3DPvt
 enum FluxSplitter { FS_ROE = 0, FS_AUSMPLUS = 1, FS_AUSMPLUSUP = 2, FS_LAXFRIED = 3, FS_HLL = 4 };
 enum PolyRec { PR_CONSTANT = 0, PR_LINEARLS = 1 };
-enum Limiter { LIM_NONE = 0, LIM_VENKTN = 1, LIM_BARTHJESP = 2 };
+enum Limiter { LIM_NONE = 0, LIM_VENKTN = 1, LIM_BARTHJESP = 2, LIM_VENKTN_STRICT = 3 };
 enum Diffusive { DIFF_NONE = 0, DIFF_NS = 1 };
 enum ViscLaw { VISC_SIMPLER_SUTHERLAND = 0, VISC_SUTHERLAND = 1, VISC_FIXED = 2 };
 enum BCType {
@@ -106,8 +106,11 @@ struct Config {
   int32_t timeZeroDiag[MAXEQ];
   int32_t timeAnalyticalMatrix;
   int32_t timeUseGlobalDT;
-  int32_t reserved1;
+  int32_t renumber;            // product-side storage permutation (no meaning for the oracle)
   double dt;                   // SubSystemStatus::getDT()
+  int32_t venktnIsMFMHD;       // Venktn2D/3D option isMFMHD (Venktn3D.cxx:125-156)
+  int32_t psiMinEqual1;        // Venktn3DStrict.cxx:33,47
+  double strictCoeff;          // Venktn3DStrict.cxx:31,44
 };
 
 struct MeshView {

@@ -206,6 +206,19 @@ CASES = {
     "mhd3d_hex_laxfried_barth": (lambda: meshgen.hex_box(4, 4, 3),
                                  lambda: mhd3d_cfg(flux=B.FS_LAXFRIED, limiter=B.LIM_BARTHJESP, res_factor=0.5),
                                  bcs_mhd3d, "mhd"),
+    # a7 variants: the "Venkatakrishnan paper" branch (isMFMHD) of Venktn2D/3D and Venktn3DStrict (what the reference's MHD
+    # dipole case selects, plugins/MHD/testcases/COCONUT/Dipole/map_TEST.CFcase:73)
+    "ns3d_hex_venktn_mfmhd": (lambda: meshgen.hex_box(6, 5, 4), lambda: ns3d_cfg(is_mfmhd=1, coeff_eps=0.7), bcs_ns3d, True),
+    "euler2d_tri_venktn_mfmhd": (lambda: meshgen.quad_channel(12, 9, triangles=True),
+                                 lambda: B.make_config(2, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, jacobian=True,
+                                                       is_mfmhd=1, magnitude_values=[1.0, 0.9, 0.2, 2.5]), bcs_euler2d, False),
+    "mhd3d_hex_venktn_strict": (lambda: meshgen.hex_box(5, 4, 4),
+                                lambda: mhd3d_cfg(limiter=B.LIM_VENKTN_STRICT, strict_coeff=0.6,
+                                                  magnitude_values=[1.0, 0.8, 0.8, 0.8, 0.3, 0.3, 0.3, 20.0, 0.1]),
+                                bcs_mhd3d, "mhd"),
+    "mhd3d_tet_venktn_strict_psimin1": (lambda: meshgen.tet_box(3, 3, 2),
+                                        lambda: mhd3d_cfg(limiter=B.LIM_VENKTN_STRICT, psi_min_equal_1=1, use_full_stencil=True),
+                                        bcs_mhd3d, "mhd"),
     # a15: the Corrected2D / Corrected3D derivative computer (what most reference test cases select) on every face type
     "ns3d_hex_corrected": (lambda: meshgen.hex_box(6, 5, 4), lambda: ns3d_cfg(derivative="corrected"), bcs_ns3d, True),
     "ns3d_tet_corrected_ausmplusup": (lambda: meshgen.tet_box(3, 3, 3),
@@ -240,10 +253,13 @@ CASES = {
 FIELDS = ("uX", "uY", "uZ", "limiter", "nstates")
 
 
-def run_case(name, oracle, make_engine, updatable=None, limiter_init=None, cfg_mut=None):
-    """Runs the oracle and an engine on one case; returns {quantity: (engine array, oracle array)}."""
+def run_case(name, oracle, make_engine, updatable=None, limiter_init=None, cfg_mut=None, shuffle=False):
+    """Runs the oracle and an engine on one case; returns {quantity: (engine array, oracle array)}.
+    shuffle: the cells of the mesh are renumbered at random first (the oracle then takes THAT numbering as the reference's)."""
     mesh_f, cfg_f, bcs_f, pvt = CASES[name]
     em = mesh_f()
+    if shuffle:
+        em, _ = meshgen.shuffle_cells(em)
     fm = oracle.build_mesh(em)
     cfg = cfg_f()
     if cfg_mut:
@@ -435,3 +451,38 @@ def check_time_term_variants(oracle, engine_factory):
             assert np.array_equal(rhs, r.rhs), (name, opts, fuse, "rhs")
             assert np.array_equal(uc, r.updateCoeff), (name, opts, fuse, "updateCoeff")
             assert np.array_equal(jac, r.bsrVal), (name, opts, fuse, "jacobian")
+
+
+def check_renumbering_layer(oracle, engine_factory, names=("ns3d_hex", "ns3d_tet", "euler2d_2nd_tri_fullstencil", "ns2d_quad_corrected",
+                                                            "mhd3d_hex_hll", "euler2d_ausmplusup_analytic", "ns3d_hex_roe_efix2")):
+    """cfg.renumber: the engine stores cells along a space-filling curve and faces by their cells, yet everything it returns
+    is in the caller's numbering and bit-identical to the oracle on the caller's (here: randomly shuffled) numbering --
+    ghost states, gradients, limiter, nodal states, residual, update coefficient, divB, the BSR pattern and every block,
+    the pseudo-steady term; then a ForwardEuler update and its ordered residual norm."""
+    for name in names:
+        def mut(cfg):
+            cfg.renumber = 1
+        out = run_case(name, oracle, engine_factory, cfg_mut=mut, shuffle=True)
+        for k, ab in out.items():
+            if k.startswith("_") or ab[1] is None:
+                continue
+            assert np.array_equal(ab[0], ab[1]), (name, k)
+    # update + norm: renumbered vs plain storage on the same shuffled mesh
+    mesh_f, cfg_f, bcs_f, pvt = CASES["euler2d_2nd_tri_fullstencil"]
+    em, _ = meshgen.shuffle_cells(mesh_f())
+    fm = oracle.build_mesh(em)
+    res = []
+    for ren in (0, 1):
+        cfg = cfg_f()
+        cfg.computeJacobian = 0
+        cfg.renumber = ren
+        e = engine_factory(cfg)
+        e.set_mesh(fm, bcs_f())
+        e.set_states(init_state(fm, 4, pvt)[:fm.nCells*4])
+        h = []
+        for _ in range(4):
+            e.compute_rhs(apply_bc=True, download=False)
+            h.append(e.update_sol_fwd_euler(0.5, 0))
+        res.append((h, e.get_states()))
+        e.close()
+    assert res[0][0] == res[1][0] and np.array_equal(res[0][1], res[1][1])

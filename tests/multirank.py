@@ -31,6 +31,8 @@ def run(rank, world, mode, name, steps, out_dir, cfl=0.5, overlap_mode=True):
         p = partition.extract(em, part, rank, world)
         cfg = cfg_f()
         cfg.computeJacobian = 0
+        renumber = int(os.environ.get("CFB_TEST_RENUMBER", "0"))     # storage renumbering inside every rank's engine
+        cfg.renumber = renumber
         q = cfg.nEqs
         if mode == "hostsim":
             L = cl.load(os.path.join(ROOT, "tests", "hostsim", "libhostsim.so"), "hostsim_")
@@ -95,6 +97,7 @@ def run(rank, world, mode, name, steps, out_dir, cfl=0.5, overlap_mode=True):
         jc = cfg_f()
         jc.fuseTimeRhs = 1
         jc.cfl = 3.0
+        jc.renumber = renumber
         e.set_step(jc)
         e.backup_past_states()
         e.set_update_coeff(None)

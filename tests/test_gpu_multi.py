@@ -13,10 +13,11 @@ def _ngpu(product_lib):
     return product_lib.device_count()
 
 
-@pytest.mark.parametrize("name,world", [("ns3d_hex", 2), ("euler2d_2nd_tri_fullstencil", 2), ("ns3d_tet", 4)])
-def test_forward_euler_with_halo_nccl(name, world, tmp_path, product_lib, oracle):
+@pytest.mark.parametrize("name,world,renumber", [("ns3d_hex", 2, 0), ("euler2d_2nd_tri_fullstencil", 2, 0), ("ns3d_tet", 4, 0),
+                                                 ("ns3d_hex", 2, 1)])
+def test_forward_euler_with_halo_nccl(name, world, renumber, tmp_path, product_lib, oracle):
     if _ngpu(product_lib) < world:
         pytest.skip("needs %d GPUs" % world)
     steps = 6
-    launch(world, "cuda", name, steps, tmp_path)
+    launch(world, "cuda", name, steps, tmp_path, renumber=renumber)
     check_against_single_domain(world, name, steps, tmp_path, product_lib)

@@ -258,6 +258,30 @@ def test_time_term_variants_separate_and_fused(oracle, product_lib):
     cases.check_time_term_variants(oracle, _factory(product_lib))
 
 
+def test_renumbering_layer_is_a_pure_permutation(oracle, product_lib):
+    cases.check_renumbering_layer(oracle, _factory(product_lib))
+
+
+def test_renumbering_layer_at_size(product_lib):
+    """96^3 hexahedra numbered at random: the renumbering engine returns, in the caller's numbering, exactly what the plain
+    engine returns on the same mesh (which is bit-exact against the oracle: test_large_hex_ns_2M_cells)."""
+    em, _ = meshgen.shuffle_cells(meshgen.hex_box(96, 96, 96))
+    fm = cl.build_mesh(em, product_lib)
+    U = cases.init_state(fm, 5, True)[:fm.nCells*5]
+    got = []
+    for ren in (0, 1):
+        e = cl.Engine(cases.ns3d_cfg(renumber=ren, fuse_time_rhs=1, cfl=5.0), 0, lib=product_lib)
+        e.set_mesh(fm, cases.bcs_ns3d())
+        e.set_states(U)
+        e.set_past_states(U*(1 + 1e-3))
+        rhs, uc = e.compute_rhs()
+        got.append((rhs, uc, e.bsr_values(), e.field("limiter"), e.bsr_pattern()))
+        e.close()
+    for a, b in zip(got[0][:4], got[1][:4]):
+        assert np.array_equal(a, b)
+    assert np.array_equal(got[0][4][0], got[1][4][0]) and np.array_equal(got[0][4][1], got[1][4][1])
+
+
 def test_position_dependent_inlet(oracle, product_lib):
     cases.check_bc_face_values(oracle, _factory(product_lib))
 

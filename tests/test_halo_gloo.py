@@ -22,12 +22,12 @@ def free_port():
     return port
 
 
-def launch(world, mode, name, steps, out_dir, timeout=600):
+def launch(world, mode, name, steps, out_dir, timeout=600, renumber=0):
     port = free_port()
     procs = []
     for r in range(world):
         env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port),
-                   LOCAL_RANK=str(r))
+                   LOCAL_RANK=str(r), CFB_TEST_RENUMBER=str(renumber))
         procs.append(subprocess.Popen([sys.executable, os.path.join(ROOT, "tests", "multirank.py"), mode, name, str(steps),
                                        str(out_dir)], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
     outs = []
@@ -73,8 +73,8 @@ def check_against_single_domain(world, name, steps, out_dir, lib, device=0):
     assert nblocks == len(ci)          # every block of the global matrix was produced by exactly one rank
 
 
-@pytest.mark.parametrize("name,world", [("ns3d_hex", 2), ("euler2d_2nd_tri_fullstencil", 3)])
-def test_forward_euler_with_halo_gloo(name, world, tmp_path, hostsim_lib, oracle):
+@pytest.mark.parametrize("name,world,renumber", [("ns3d_hex", 2, 0), ("euler2d_2nd_tri_fullstencil", 3, 0), ("ns3d_tet", 2, 1)])
+def test_forward_euler_with_halo_gloo(name, world, renumber, tmp_path, hostsim_lib, oracle):
     steps = 5
-    launch(world, "hostsim", name, steps, tmp_path)
+    launch(world, "hostsim", name, steps, tmp_path, renumber=renumber)
     check_against_single_domain(world, name, steps, tmp_path, hostsim_lib)

@@ -88,6 +88,10 @@ def test_time_term_variants_separate_and_fused(oracle, hostsim_lib):
     cases.check_time_term_variants(oracle, _engine_factory(hostsim_lib))
 
 
+def test_renumbering_layer_is_a_pure_permutation(oracle, hostsim_lib):
+    cases.check_renumbering_layer(oracle, _engine_factory(hostsim_lib))
+
+
 def test_newton_update(hostsim_lib):
     from oracle import binding as ob
     cases.check_newton_update(_engine_factory(hostsim_lib), ob.build_mesh)
