@@ -354,7 +354,6 @@ struct LimiterK {   // idx over cells
         // "implementation from the Venkatakrishnan paper": Venktn3D.cxx:125-156 / Venktn3DStrict.cxx:166-203
         if (!(strict && !c.venktnIsMFMHD)) {
           const double mag = c.magnitudeValues[v];
-          const Recip rmag = recipOf(mag);
           const double epsilon2 = pow3(ddiv(c.coeffEps*avgDistance, c.length));
 #pragma unroll
           for (int j = 0; j < 6; ++j) if (j < nbFaces) {
@@ -362,8 +361,11 @@ struct LimiterK {   // idx over cells
             if (D == 2) deltaMin = ux*dxq[j][0] + uy*dxq[j][1];
             else deltaMin = ux*dxq[j][0] + uy*dxq[j][1] + uz*dxq[j][2];
             const bool pos = deltaMin > 0.0;
-            const double dMinStar = ((deltaMin < 0.0) ? -1.0 : 1.0)*(divBy(fabs(deltaMin), rmag) + 1e-24);
-            const double dPlus = divBy(pos ? deltaPlusMax : deltaPlusMin, rmag);
+            // (each quotient with its own reciprocal: sharing one Recip of `mag` across the six unrolled faces gave wrong
+            // limiter values on B200 at this launch shape (80 registers, spills) although the expression itself is
+            // bit-exact in isolation -- tools/dbg/lim.cu -- and the kernel is right at 2 resident blocks: kept simple)
+            const double dMinStar = ((deltaMin < 0.0) ? -1.0 : 1.0)*(ddiv(fabs(deltaMin), mag) + 1e-24);
+            const double dPlus = ddiv(pos ? deltaPlusMax : deltaPlusMin, mag);
             const double dPlus2 = dPlus*dPlus;
             const double dPlusMin = dPlus*dMinStar;
             const double Num = (dPlus2 + epsilon2)*dMinStar + ((2*dMinStar)*dMinStar)*dPlus;
