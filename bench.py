@@ -77,6 +77,8 @@ def flagship(n, workload="ns3d"):
                                  mach_inf=2.0, choice_a12=1), cases.bcs_euler2d()
     if workload == "ns3d_corrected":
         return em, cases.ns3d_cfg(derivative="corrected"), cases.bcs_ns3d()
+    if workload == "ns3d_tet":
+        return meshgen.tet_box(n, n, n), cases.ns3d_cfg(), cases.bcs_ns3d()
     return em, cases.ns3d_cfg(), cases.bcs_ns3d()
 
 
@@ -93,6 +95,9 @@ WORKLOADS = {
                          "term", False, 368, 640),
     "euler2d_numjac": ("configs[1] with the finite-difference Jacobian instead: 2D Euler, %d^2 = %d quadrilaterals per GPU, "
                        "AUSM+up, LinearLS2D + Venktn2D, NumJacob, pseudo-steady time term", False, 368, 640),
+    "ns3d_tet": ("configs[2] on tetrahedra: 3D Navier-Stokes, %d^3 boxes split into 6 tetrahedra each (Kuhn), %d cells "
+                 "per GPU, Pvt variables, Roe + viscous (DiamondVolume3D) flux, LinearLS3D + Venktn3D (stencils of ~60 vertex "
+                 "neighbours), NumJacob into device BSR, pseudo-steady time term", True, 763, 1000),
     "mhd3d": ("configs[3]: 3D ideal MHD (MHD3DProjection, q = 9), %d^3 = %d jittered hex cells per GPU, Cons variables, "
               "HLL flux, LinearLS3D + Venktn3D, finite-difference 9x9 block Jacobian into device BSR, pseudo-steady "
               "time term", "mhd", 960, 4536),
@@ -358,6 +363,7 @@ def main():
     ap.add_argument("--no-fuse", action="store_true", help="pseudo-steady time term as a separate kernel (cfb200_time_rhs) "
                     "instead of inside the residual / diagonal gathers (measured equal on B200: 6.31 vs 6.33 ms at 220^3)")
     ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the cross-rank parity mini-problem")
+    ap.add_argument("--rhs-only", action="store_true", help="explicit configuration: ComputeRHS without the Jacobian (C5 sweep)")
     ap.add_argument("--shuffle", action="store_true", help="renumber the cells of the mesh at random first (no locality)")
     ap.add_argument("--renumber", action="store_true", help="cfg.renumber: space-filling-curve storage order inside the engine")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -390,6 +396,10 @@ def main():
     em, cfg, bcs = flagship(args.n if world == 1 else 2, args.workload)
     cfg.fuseTimeRhs = 0 if args.no_fuse else 1
     cfg.renumber = 1 if args.renumber else 0
+    if args.rhs_only:
+        cfg.computeJacobian = 0
+        cfg.fuseTimeRhs = 0
+        a_jac = 0
     if args.shuffle and world == 1:
         from coolfluid_b200 import meshgen as _mg
         em, _ = _mg.shuffle_cells(em)
@@ -430,7 +440,7 @@ def main():
         if part is not None:
             eng.halo_begin()                 # state halo over NCCL; compute_rhs overlaps it with the interior gradients
         eng.compute_rhs(apply_bc=True, download=False)
-        if args.no_fuse:
+        if args.no_fuse and not args.rhs_only:
             eng.time_rhs(download=False)
 
     def step_e2e():
@@ -439,7 +449,7 @@ def main():
         if part is not None:
             eng.halo_begin()
         eng.compute_rhs(apply_bc=True, download=True, out_rhs=hR.numpy(), out_uc=hC.numpy())
-        if args.no_fuse:
+        if args.no_fuse and not args.rhs_only:
             eng.time_rhs(download=False)
 
     def barrier():
@@ -509,7 +519,8 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": workload_text(args.workload, args.n, n_upd),
+            "config": {"workload": workload_text(args.workload, args.n, n_upd) + (" -- RHS ONLY (explicit: no Jacobian, no time "
+                                   "term)" if args.rhs_only else ""),
                        "cells_per_gpu": nc, "faces_per_gpu": int(fm.nFaces), "bsr_blocks_per_gpu": int(eng.nnzb),
                        "l2": "inputs (%.1f GB BSR + %.2f GB states/gradients) far larger than the 126 MB L2; no flush needed"
                              % (eng.nnzb*q*q*8/1e9, nc*q*8*6/1e9),
