@@ -15,6 +15,7 @@
 #include <stdexcept>
 #include <functional>
 #include <cstdlib>
+#include <cmath>
 #include "cfb_kernels.cuh"
 
 namespace cfb {
@@ -256,6 +257,35 @@ public:
         sp.push_back((int32_t)st.size());
       }
       d.bndStPtr = upload(sp); d.bndSt = upload(st);
+    }
+    d.bcWallRatio = nullptr;
+    {
+      bool any = false;
+      for (int i = 0; i < nbc; ++i) any = any || (bcs[i].type == CFB200_BC_NOSLIP_ISOTHERMAL);
+      if (any) {
+        // FVMCC_BaseBC::computeGhostPosition (FVMCC_BaseBC.ci:271-350) per boundary face: the inner node mirrored through
+        // the face plane (normal through the face mid point), the wall point half way, then |x_I x_G| / |x_I x_W|
+        std::vector<double> ratio(ng, 2.0);
+        for (int g = 0; g < ng; ++g) {
+          const int f = ni + g;
+          const double* n = m.normals + (size_t)f*D;
+          const double* xI = m.centres + (size_t)m.faceL[f]*D;
+          double mid[3] = {0., 0., 0.};
+          const int b = m.faceNodePtr[f], e = m.faceNodePtr[f+1];
+          for (int j = b; j < e; ++j) for (int k = 0; k < D; ++k) mid[k] += m.nodes[(size_t)m.faceNodes[j]*D + k];
+          for (int k = 0; k < D; ++k) mid[k] /= (double)(e - b);
+          double nm = 0., n2 = 0., nx = 0.;
+          for (int k = 0; k < D; ++k) { nm += n[k]*mid[k]; n2 += n[k]*n[k]; nx += n[k]*xI[k]; }
+          const double t = (nx + (-nm))/n2;
+          double dw = 0., dg = 0.;
+          for (int k = 0; k < D; ++k) {
+            const double xG = xI[k] - 2.*t*n[k], xM = 0.5*(xI[k] + xG);
+            dw += (xI[k] - xM)*(xI[k] - xM); dg += (xI[k] - xG)*(xI[k] - xG);
+          }
+          ratio[g] = std::sqrt(dg)/std::sqrt(dw);
+        }
+        d.bcWallRatio = upload(ratio);
+      }
     }
     d.faceBC = upload(m.faceBC, nf);
     d.updatable = upload(m.updatable, nc);

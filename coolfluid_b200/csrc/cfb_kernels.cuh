@@ -34,6 +34,7 @@ struct Dev {
   const double* cvol; const uint8_t* cvSign; const int* faceBC;
   const double* bcFaceVal;    // [q][nGhosts] position-dependent Dirichlet data (cfb200_set_bc_face_values), or null
   const uint8_t* bcFaceFlag;  // [nGhosts] 1 where bcFaceVal replaces BCond::value
+  const double* bcWallRatio;  // [nGhosts] (inner-ghost)/(inner-wall) distance ratio of FVMCC_BaseBC::computeGhostPosition, or null
   const int* bndStPtr; const int* bndSt;           // Corrected2D/3D: gradient stencil of each boundary face (CSR over ghosts)
   const uint8_t* updatable;
   const uint8_t* cellActive;  // cell touches at least one face with an updatable side
@@ -129,6 +130,18 @@ CFB_HD void ghostState(const Dev& d, int g, const Cfg& c, const BCond& b, const 
     case CFB200_BC_FARFIELD_EULER:        // FarFieldEuler2D.cxx:127-300, FarFieldEuler3D.cxx:62-196
       P::farFieldGhost(c, nr, b.value, inner, ghost);
       break;
+    case CFB200_BC_NOSLIP_ISOTHERMAL: {   // NoSlipWallIsothermalNSvt.ci:178-243: linear extrapolation through the wall values
+      constexpr int TID = Q - 1;
+      const double ratio = d.bcWallRatio[g];                     // m_drXiXg/m_drXiXw (static geometry: formed at set_mesh)
+      const double ghostT = 2.*b.value[TID] - inner[TID];        // repositionNode: ghostValue = 2 bValue - innerValue
+      if (!(ghostT >= b.value[0])) *d.status = CFB200_ERR_GHOST_REPOSITION;      // the reference would move the ghost node
+      for (int i = 0; i < Q; ++i) {
+        if (i >= 1 && i <= D) ghost[i] = inner[i] - (inner[i] - b.value[i])*ratio;
+        else if (i != TID) ghost[i] = inner[i];
+        else ghost[i] = ghostT;
+      }
+      break;
+    }
     default:                              // CFB200_BC_MIRROR_EULER_CONS: MirrorEuler2D.cxx:56-94 / MirrorMHD3DProjection.cxx:56-96
       P::mirrorGhost(c, nr, inner, ghost);
       break;

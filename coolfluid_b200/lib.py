@@ -18,7 +18,8 @@ P_D = C.POINTER(C.c_double)
 P_I = C.POINTER(C.c_int32)
 P_U8 = C.POINTER(C.c_uint8)
 
-ERRORS = {1: "BAD_VALUE", 2: "INVALID_ARG", 3: "NO_DEVICE", 4: "CUDA", 5: "STATE", 6: "UNSUPPORTED", 7: "NCCL"}
+ERRORS = {1: "BAD_VALUE", 2: "INVALID_ARG", 3: "NO_DEVICE", 4: "CUDA", 5: "STATE", 6: "UNSUPPORTED", 7: "NCCL",
+          8: "GHOST_REPOSITION"}
 
 
 class Cfb200Error(RuntimeError):

@@ -45,8 +45,14 @@ enum cfb200_bc_type {
                                       SubInletEulerPvtVT.ci:52-77, SubOutletEulerPvt.ci:36-51, NoSlipWallAdiabaticNSPvt.cxx:109-128 */
   CFB200_BC_MIRROR_VELOCITY = 2,   /* FiniteVolume/MirrorVelocity.cxx:71-111 */
   CFB200_BC_MIRROR_EULER_CONS = 3, /* FiniteVolumeNavierStokes/MirrorEuler2D.cxx:56-94, MirrorEuler3D */
-  CFB200_BC_FARFIELD_EULER = 4     /* FiniteVolumeNavierStokes/FarFieldEuler2D.cxx:127-300 (conservative variables),
+  CFB200_BC_FARFIELD_EULER = 4,    /* FiniteVolumeNavierStokes/FarFieldEuler2D.cxx:127-300 (conservative variables),
                                       FarFieldEuler3D.cxx:62-196 (Cons or Pvt): value = p, u, v, [w,] T at infinity */
+  CFB200_BC_NOSLIP_ISOTHERMAL = 5  /* FiniteVolumeNavierStokes/NoSlipWallIsothermalNSvt.ci:178-243 (Puvt / Pvt variables): velocity and
+                                      temperature linearly extrapolated through the wall values over the inner-wall / inner-ghost
+                                      distances of FVMCC_BaseBC.ci:271-350, the other variables copied.  value[1..dim] = uWall,
+                                      value[dim+1] = TWall / tempRef, value[0] = TGhostMin / tempRef.  When the ghost temperature
+                                      2 TWall - T_inner falls below TGhostMin the reference MOVES the ghost node (repositionNode,
+                                      FVMCC_BaseBC.hh:290-340): not done here, the evaluation reports CFB200_ERR_GHOST_REPOSITION */
 };
 
 enum cfb200_error {
@@ -57,7 +63,8 @@ enum cfb200_error {
   CFB200_ERR_CUDA = 4,
   CFB200_ERR_STATE = 5,       /* call order (mesh/states not set) */
   CFB200_ERR_UNSUPPORTED = 6,
-  CFB200_ERR_NCCL = 7
+  CFB200_ERR_NCCL = 7,
+  CFB200_ERR_GHOST_REPOSITION = 8  /* an isothermal wall would reposition a ghost node (see CFB200_BC_NOSLIP_ISOTHERMAL) */
 };
 
 /* One boundary condition per boundary TRS (FVMCC_BaseBC.ci:144-187 executeOnTrs -> setGhostState). */

@@ -63,6 +63,37 @@ public:
       case BC_FARFIELD_EULER:          // FarFieldEuler2D.cxx:127-300, FarFieldEuler3D.cxx:62-196
         P::farFieldGhost(cfg, &mesh.normals[(size_t)f*D], b.value, inner, ghost);
         break;
+      case BC_NOSLIP_ISOTHERMAL: {     // NoSlipWallIsothermalNSvt.ci:178-243 (not adiabatic, FixTWallInGhost = false)
+        // computeGhostPosition (FVMCC_BaseBC.ci:271-350): mirror of the inner node through the face plane, the wall
+        // point half way, the two distances
+        const double* n = &mesh.normals[(size_t)f*D];
+        const int L = mesh.faceL[f];
+        const double* xI = &mesh.centres[(size_t)L*D];
+        double mid[3] = {0., 0., 0.};
+        const int nb = mesh.faceNodePtr[f+1] - mesh.faceNodePtr[f];
+        for (int j = mesh.faceNodePtr[f]; j < mesh.faceNodePtr[f+1]; ++j)
+          for (int k = 0; k < D; ++k) mid[k] += mesh.nodes[(size_t)mesh.faceNodes[j]*D + k];
+        for (int k = 0; k < D; ++k) mid[k] /= (double)nb;
+        double nm = 0., n2 = 0., nx = 0.;
+        for (int k = 0; k < D; ++k) { nm += n[k]*mid[k]; n2 += n[k]*n[k]; nx += n[k]*xI[k]; }
+        const double kk = -nm;
+        const double t = (nx + kk)/n2;
+        double xG[3], xM[3];
+        for (int k = 0; k < D; ++k) { xG[k] = xI[k] - 2.*t*n[k]; xM[k] = 0.5*(xI[k] + xG[k]); }
+        const double drXiXw = getDistance<D>(xI, xM);
+        const double drXiXg = getDistance<D>(xI, xG);
+        // repositionNode (FVMCC_BaseBC.hh:290-340): ghostValue = 2 bValue - innerValue; the loop that moves the ghost
+        // node when it is below minValue is NOT restated: status 8
+        const int TID = Q - 1;
+        const double ghostT = 2.*b.value[TID] - inner[TID];
+        if (!(ghostT >= b.value[0])) throw std::runtime_error("ghost reposition");
+        for (int i = 0; i < Q; ++i) {
+          if (i >= 1 && i <= D) ghost[i] = inner[i] - (inner[i] - b.value[i])*(drXiXg/drXiXw);     // linearInterpolate
+          else if (i != TID) ghost[i] = inner[i];
+          else ghost[i] = ghostT;
+        }
+        break;
+      }
       default: throw std::runtime_error("unknown BC type");
     }
   }

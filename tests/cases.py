@@ -78,6 +78,19 @@ def bcs_ns3d():
     return [inlet, outlet, wall, mirror, mirror, B.make_bc(B.BC_SUPER_OUTLET)]
 
 
+def bcs_ns3d_isothermal(t_wall=1.1, t_ghost_min=0.1):
+    """bcs_ns3d with the adiabatic wall replaced by NoSlipWallIsothermalNSvt (a moving wall to exercise uWall)."""
+    b = bcs_ns3d()
+    b[2] = B.make_bc(B.BC_NOSLIP_ISOTHERMAL, value=[t_ghost_min, 0.02, -0.01, 0.0, t_wall])
+    return b
+
+
+def bcs_ns2d_isothermal():
+    b = bcs_ns2d()
+    b[2] = B.make_bc(B.BC_NOSLIP_ISOTHERMAL, value=[0.1, 0.0, 0.0, 0.9])
+    return b
+
+
 def bcs_ns2d():
     wall = B.make_bc(B.BC_DIRICHLET, mask=[0, 1, 1, 0], value=[0, 0, 0, 0])
     inlet = B.make_bc(B.BC_DIRICHLET, mask=[0, 1, 1, 1], value=[0, 0.4, 0, 1.0])
@@ -219,6 +232,11 @@ CASES = {
     "mhd3d_tet_venktn_strict_psimin1": (lambda: meshgen.tet_box(3, 3, 2),
                                         lambda: mhd3d_cfg(limiter=B.LIM_VENKTN_STRICT, psi_min_equal_1=1, use_full_stencil=True),
                                         bcs_mhd3d, "mhd"),
+    # a16: NoSlipWallIsothermalNSvt (FiniteVolumeNavierStokes/NoSlipWallIsothermalNSvt.ci:178-243), hot and cold wall
+    "ns3d_hex_isothermal_wall": (lambda: meshgen.hex_box(6, 5, 4), ns3d_cfg, bcs_ns3d_isothermal, True),
+    "ns3d_tet_isothermal_wall_corrected": (lambda: meshgen.tet_box(3, 3, 3), lambda: ns3d_cfg(derivative="corrected"),
+                                           bcs_ns3d_isothermal, True),
+    "ns2d_quad_isothermal_wall": (lambda: meshgen.quad_channel(10, 8), ns2d_cfg, bcs_ns2d_isothermal, True),
     # a15: the Corrected2D / Corrected3D derivative computer (what most reference test cases select) on every face type
     "ns3d_hex_corrected": (lambda: meshgen.hex_box(6, 5, 4), lambda: ns3d_cfg(derivative="corrected"), bcs_ns3d, True),
     "ns3d_tet_corrected_ausmplusup": (lambda: meshgen.tet_box(3, 3, 3),
@@ -486,3 +504,19 @@ def check_renumbering_layer(oracle, engine_factory, names=("ns3d_hex", "ns3d_tet
         res.append((h, e.get_states()))
         e.close()
     assert res[0][0] == res[1][0] and np.array_equal(res[0][1], res[1][1])
+
+
+def check_ghost_reposition_is_reported(oracle, engine_factory):
+    from coolfluid_b200 import lib as cl
+    fm = oracle.build_mesh(meshgen.hex_box(4, 4, 3))
+    e = engine_factory(ns3d_cfg())
+    try:
+        e.set_mesh(fm, bcs_ns3d_isothermal(t_wall=0.3, t_ghost_min=0.5))      # 2*0.3 - ~1.0 < 0.5
+        e.set_states(init_state(fm, 5, True)[:fm.nCells*5])
+        try:
+            e.compute_rhs()
+            raise AssertionError("no error reported")
+        except cl.Cfb200Error as err:
+            assert err.code == 8
+    finally:
+        e.close()

@@ -282,6 +282,10 @@ def test_renumbering_layer_at_size(product_lib):
     assert np.array_equal(got[0][4][0], got[1][4][0]) and np.array_equal(got[0][4][1], got[1][4][1])
 
 
+def test_isothermal_wall_reports_ghost_reposition(oracle, product_lib):
+    cases.check_ghost_reposition_is_reported(oracle, _factory(product_lib))
+
+
 def test_position_dependent_inlet(oracle, product_lib):
     cases.check_bc_face_values(oracle, _factory(product_lib))
 

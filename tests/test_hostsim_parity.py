@@ -92,6 +92,12 @@ def test_renumbering_layer_is_a_pure_permutation(oracle, hostsim_lib):
     cases.check_renumbering_layer(oracle, _engine_factory(hostsim_lib))
 
 
+def test_isothermal_wall_reports_ghost_reposition(oracle, hostsim_lib):
+    """ghost T = 2 TWall - T_inner below TGhostMin: the reference moves the ghost node (repositionNode); the engine
+    reports CFB200_ERR_GHOST_REPOSITION instead of returning something else."""
+    cases.check_ghost_reposition_is_reported(oracle, _engine_factory(hostsim_lib))
+
+
 def test_newton_update(hostsim_lib):
     from oracle import binding as ob
     cases.check_newton_update(_engine_factory(hostsim_lib), ob.build_mesh)
