@@ -271,3 +271,102 @@ def read_thor(thor_path, sp_path):
     ptr, fc, fnp, fn = _pack_trs(trs)
     return ElementMesh(dim, coords, np.array(cell_ptr), np.concatenate(cell_nodes), np.array(cell_shape),
                        names, ptr, fc, fnp, fn)
+
+
+_CFMESH_SHAPES = {"Triag": (SH_TRIAG, 3), "Quad": (SH_QUAD, 4), "Tetra": (SH_TETRA, 4), "Hexa": (SH_HEXA, 8)}
+
+
+def read_cfmesh(path):
+    """Reader for the reference's native ASCII mesh format (what CFmeshFileReader consumes,
+    /root/reference/src/Framework/CFmeshFileReader.ci:60-100 keyword table, :902-951 readGeomEntList), restricted to what the
+    cell-centred FV path reads: P1 geometry, P0 solution (one state per element), Triag / Quad / Tetra / Hexa elements.
+    Elements keep the file order (type after type), the TRSs the file order, each the concatenation of its TRs; a boundary
+    face is `nbNodes nbStates nodes... states...` and its state ID names the cell it belongs to.
+    Returns (ElementMesh, states or None): states [nCells, nEq] when the file carries a solution (!LIST_STATE 1)."""
+    tok = open(path).read().split()
+    p = 0
+    n = len(tok)
+    dim = neq = nb_nodes = nb_states = 0
+    coords = states = None
+    types, per_type, nodes_per_type, states_per_type = [], [], [], []
+    elem_nodes, elem_ptr, elem_shape, state_of_elem = [], [0], [], []
+    names, trs = [], []
+    geo_order = sol_order = None
+    while p < n:
+        key = tok[p]; p += 1
+        if key == "!END":
+            break
+        if key == "!NB_DIM":
+            dim = int(tok[p]); p += 1
+        elif key == "!NB_EQ":
+            neq = int(tok[p]); p += 1
+        elif key == "!NB_NODES":
+            nb_nodes = int(tok[p]); p += 2                      # updatable, non-updatable
+        elif key == "!LIST_NODE":
+            coords = np.array(tok[p:p + dim*nb_nodes], dtype=np.float64).reshape(nb_nodes, dim); p += dim*nb_nodes
+        elif key == "!NB_STATES":
+            nb_states = int(tok[p]); p += 2
+        elif key == "!LIST_STATE":
+            flag = int(tok[p]); p += 1
+            if flag:
+                states = np.array(tok[p:p + neq*nb_states], dtype=np.float64).reshape(nb_states, neq); p += neq*nb_states
+        elif key == "!NB_ELEM":
+            p += 1
+        elif key == "!NB_ELEM_TYPES":
+            ntypes = int(tok[p]); p += 1
+        elif key == "!GEOM_POLYORDER":
+            geo_order = int(tok[p]); p += 1
+        elif key == "!SOL_POLYORDER":
+            sol_order = int(tok[p]); p += 1
+        elif key == "!ELEM_TYPES":
+            types = tok[p:p + ntypes]; p += ntypes
+        elif key == "!NB_ELEM_PER_TYPE":
+            per_type = [int(x) for x in tok[p:p + ntypes]]; p += ntypes
+        elif key == "!NB_NODES_PER_TYPE":
+            nodes_per_type = [int(x) for x in tok[p:p + ntypes]]; p += ntypes
+        elif key == "!NB_STATES_PER_TYPE":
+            states_per_type = [int(x) for x in tok[p:p + ntypes]]; p += ntypes
+        elif key == "!LIST_ELEM":
+            if geo_order != 1 or sol_order != 0:
+                raise ValueError("read_cfmesh: only P1 geometry with a P0 (cell-centred) solution is supported")
+            for t, ne, nn, ns in zip(types, per_type, nodes_per_type, states_per_type):
+                if t not in _CFMESH_SHAPES or _CFMESH_SHAPES[t][1] != nn or ns != 1:
+                    raise ValueError("read_cfmesh: unsupported element type %s" % t)
+                a = np.array(tok[p:p + ne*(nn + 1)], dtype=np.int64).reshape(ne, nn + 1); p += ne*(nn + 1)
+                elem_nodes.append(a[:, :nn].reshape(-1))
+                state_of_elem.append(a[:, nn])
+                elem_ptr.extend((elem_ptr[-1] + nn*(np.arange(ne) + 1)).tolist())
+                elem_shape.extend([_CFMESH_SHAPES[t][0]]*ne)
+        elif key == "!NB_TRSs":
+            p += 1
+        elif key == "!TRS_NAME":
+            names.append(tok[p]); p += 1
+        elif key == "!NB_TRs":
+            ntr = int(tok[p]); p += 1
+        elif key == "!NB_GEOM_ENTS":
+            counts = [int(x) for x in tok[p:p + ntr]]; p += ntr
+        elif key == "!GEOM_TYPE":
+            p += 1
+        elif key == "!LIST_GEOM_ENT":
+            cells, fnodes = [], []
+            for _ in range(sum(counts)):
+                nn, ns = int(tok[p]), int(tok[p + 1]); p += 2
+                fnodes.append([int(x) for x in tok[p:p + nn]]); p += nn
+                cells.append(int(tok[p])); p += ns
+            trs.append((cells, fnodes))
+        elif key.startswith("!"):
+            # keywords without meaning for this path (e.g. !COOLFLUID_VERSION, !CFMESH_FORMAT_VERSION, !NB_EXTRA_*): skip their values
+            while p < n and not tok[p].startswith("!"):
+                p += 1
+    soe = np.concatenate(state_of_elem)
+    cell_of_state = np.empty(len(soe), dtype=np.int64); cell_of_state[soe] = np.arange(len(soe))
+    # one TRS may mix face shapes only in 3D hybrid meshes, which the element types above already exclude per mesh
+    packed = []
+    for cells, fnodes in trs:
+        k = len(fnodes[0]) if fnodes else 2
+        packed.append((cell_of_state[np.array(cells, dtype=np.int64)] if cells else [], np.array(fnodes, dtype=np.int64).reshape(len(cells), k)))
+    ptr, fc, fnp, fn = _pack_trs(packed)
+    em = ElementMesh(dim, coords, np.array(elem_ptr), np.concatenate(elem_nodes), np.array(elem_shape), names, ptr, fc, fnp, fn)
+    if states is not None:
+        states = states[soe]
+    return em, states
