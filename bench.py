@@ -363,6 +363,8 @@ def main():
     ap.add_argument("--no-fuse", action="store_true", help="pseudo-steady time term as a separate kernel (cfb200_time_rhs) "
                     "instead of inside the residual / diagonal gathers (measured equal on B200: 6.31 vs 6.33 ms at 220^3)")
     ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the cross-rank parity mini-problem")
+    ap.add_argument("--strong", action="store_true", help="N > 1: strong scaling, ONE n^3 box cut into N slabs of n/N layers "
+                    "(n must be a multiple of N) instead of one n^3 slab per GPU")
     ap.add_argument("--rhs-only", action="store_true", help="explicit configuration: ComputeRHS without the Jacobian (C5 sweep)")
     ap.add_argument("--shuffle", action="store_true", help="renumber the cells of the mesh at random first (no locality)")
     ap.add_argument("--renumber", action="store_true", help="cfg.renumber: space-filling-curve storage order inside the engine")
@@ -406,7 +408,12 @@ def main():
     q = cfg.nEqs
     part = None
     if world > 1:
-        em, part = slab_partition(args.n, rank, world, args.workload)
+        if args.strong:
+            if args.n % world:
+                raise SystemExit("--strong needs an edge that is a multiple of the number of GPUs")
+            em, part = slab_partition(args.n, rank, world, args.workload, box=(args.n, args.n, args.n//world))
+        else:
+            em, part = slab_partition(args.n, rank, world, args.workload)
     fm = cl.build_mesh(em, L)
     if part is not None:
         fm.updatable = np.ascontiguousarray(part.updatable)
@@ -517,7 +524,7 @@ def main():
                                 if args.workload == "ns3d" else (None, None))
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if (args.strong and world > 1) else "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
             "config": {"workload": workload_text(args.workload, args.n, n_upd) + (" -- RHS ONLY (explicit: no Jacobian, no time "
                                    "term)" if args.rhs_only else ""),
@@ -525,10 +532,11 @@ def main():
                        "l2": "inputs (%.1f GB BSR + %.2f GB states/gradients) far larger than the 126 MB L2; no flush needed"
                              % (eng.nnzb*q*q*8/1e9, nc*q*8*6/1e9),
                        "partitioning": ("single partition" if part is None else
+                                        ("STRONG scaling: " if args.strong else "") +
                                         "one global %d x %d x %d box cut along z, one slab per GPU (%d updatable + %d overlap "
                                         "cells on rank 0, order-preserving local numbering), state halo exchange over NCCL "
                                         "every step (%d cells x %d doubles per neighbour), overlapped with the independent "
-                                        "gradients" % (args.n, args.n, args.n*world, n_upd, nc - n_upd, 2*args.n*args.n, q)),
+                                        "gradients" % (args.n, args.n, args.n if args.strong else args.n*world, n_upd, nc - n_upd, 2*args.n*args.n, q)),
                        "time_term": "separate kernel" if args.no_fuse else "fused into the residual / diagonal gathers",
                        "numbering": ("cells renumbered at random" if args.shuffle else "generator order (x fastest)") +
                                     (", Morton storage order inside the engine (cfg.renumber)" if args.renumber else ""),
