@@ -79,6 +79,9 @@ def flagship(n, workload="ns3d"):
         return em, cases.ns3d_cfg(derivative="corrected"), cases.bcs_ns3d()
     if workload == "ns3d_tet":
         return meshgen.tet_box(n, n, n), cases.ns3d_cfg(), cases.bcs_ns3d()
+    if workload == "ns3d_ausm_analytic":
+        from coolfluid_b200 import config as B
+        return em, cases.ns3d_cfg(flux=B.FS_AUSMPLUSUP, jacobian="analytic", mach_inf=0.35), cases.bcs_ns3d()
     return em, cases.ns3d_cfg(), cases.bcs_ns3d()
 
 
@@ -95,6 +98,10 @@ WORKLOADS = {
                          "term", False, 368, 640),
     "euler2d_numjac": ("configs[1] with the finite-difference Jacobian instead: 2D Euler, %d^2 = %d quadrilaterals per GPU, "
                        "AUSM+up, LinearLS2D + Venktn2D, NumJacob, pseudo-steady time term", False, 368, 640),
+    "ns3d_ausm_analytic": ("configs[2] with the analytic Jacobians of a19 (NumJacobAnalytic: AUSM+up ComputedFluxdPvt + "
+                           "NSFluxAndJacob): 3D Navier-Stokes, %d^3 = %d jittered hex cells per GPU, Pvt variables, AUSM+up "
+                           "(machInf 0.35) + viscous (DiamondVolume3D) flux, LinearLS3D + Venktn3D, block Jacobian into device "
+                           "BSR, pseudo-steady time term", True, 744, 1400),
     "ns3d_tet": ("configs[2] on tetrahedra: 3D Navier-Stokes, %d^3 boxes split into 6 tetrahedra each (Kuhn), %d cells "
                  "per GPU, Pvt variables, Roe + viscous (DiamondVolume3D) flux, LinearLS3D + Venktn3D (stencils of ~60 vertex "
                  "neighbours), NumJacob into device BSR, pseudo-steady time term", True, 763, 1000),

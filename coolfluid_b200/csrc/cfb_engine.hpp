@@ -23,10 +23,14 @@ namespace cfb {
 // Roe; AUSM+ and AUSM+up with the perfect-gas interface sound speeds (choiceA12 4/5 are the TCNEQ variants).
 inline bool splitterSupported(const cfb200_config& c) {
   if (c.fuseTimeRhs && c.timeUseGlobalDT) return false;   // the global minimum needs the complete updateCoeff first
-  // "NumJacobAnalytic": the analytic flux Jacobian exists for AUSM+up in conservative variables, inviscid (a19)
-  if (c.computeJacobian == 2 && !(c.physicalModel == CFB200_PM_EULER && c.fluxSplitter == CFB200_FS_AUSMPLUSUP &&
-                                  c.updateVar == CFB200_UV_CONS && c.diffusive == CFB200_DIFF_NONE && c.machInf > 0.))
-    return false;
+  // "NumJacobAnalytic" (a19): the analytic flux Jacobian exists for AUSM+up, in conservative variables (inviscid) and in
+  // Puvt / Pvt; the analytic diffusive Jacobian (NSFluxAndJacob) exists for the Puvt / Pvt variable sets with the
+  // DiamondVolume computers and Corrected2D (CorrectedDerivative3D has no getGradientsJacob)
+  if (c.computeJacobian == 2) {
+    if (!(c.physicalModel == CFB200_PM_EULER && c.fluxSplitter == CFB200_FS_AUSMPLUSUP && c.machInf > 0.)) return false;
+    if (c.diffusive != CFB200_DIFF_NONE && c.updateVar != CFB200_UV_PVT) return false;
+    if (c.diffusive != CFB200_DIFF_NONE && c.derivativeStrategy == CFB200_DV_CORRECTED && c.dim != 2) return false;
+  }
   // Corrected2D/3D reads the cell gradients (uX uY uZ sockets), which only the linear reconstruction computes
   if (c.diffusive == CFB200_DIFF_NS && c.derivativeStrategy != CFB200_DV_DIAMOND &&
       !(c.derivativeStrategy == CFB200_DV_CORRECTED && c.polyRec != CFB200_PR_CONSTANT))
@@ -457,8 +461,8 @@ public:
   void faceKernels_(bool doJac, int faceShape) {
     const int fam = splitterFamily(cfg);
     if (doJac && cfg.computeJacobian == 2) {
-      bk.launchStaged("innerFaceJacAnalytic", AnalyticInnerFaceK<D>{d, cfg}, d.nInner, faceShape);
-      bk.launch("boundaryFaceJac", BoundaryFaceK<D, true, 0>{d, cfg}, d.nGhosts, 128);
+      bk.launchStaged("innerFaceJacAnalytic", AnalyticInnerFaceK<D, DV>{d, cfg}, d.nInner, faceShape);
+      bk.launch("boundaryFaceJac", BoundaryFaceK<D, true, DV>{d, cfg}, d.nGhosts, 128);
     } else if (doJac && (fam == 0 || fam == 3) && roePipeline == 2 && DV == 0) {
       // Roe families, DiamondVolume: two phases, three resident blocks per SM
       const bool cons = (cfg.updateVar == CFB200_UV_CONS);

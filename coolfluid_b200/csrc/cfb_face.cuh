@@ -890,7 +890,7 @@ struct InnerFacePhased {   // idx over interior faces; FS = 0 Roe | 3 Roe with t
 //   block(R,L) = -(resFactor * area * dF/dU_L)       block(L,R) = resFactor * area * dF/dU_R
 // (the diagonal contributions are their negatives, gathered by DiagGather like the finite-difference ones; the same values
 // serve the one-sided updatable faces).  Boundary faces keep the finite-difference term (FVMCC_FluxSplitter.cxx:117-124).
-template <int D>
+template <int D, int DV = 0>
 struct AnalyticInnerFaceK {   // idx over interior faces; staged like InnerFaceK (the warp writes whole blocks)
   static constexpr int Q = D + 2;
   static constexpr int BLK = Q*Q;
@@ -909,6 +909,7 @@ struct AnalyticInnerFaceK {   // idx over interior faces; staged like InnerFaceK
       for (int k = 0; k < NOUT; ++k) stg[(size_t)k*stride] = 0.;
       return;
     }
+    const bool hasDiff = (c.diffusive == CFB200_DIFF_NS);
     FaceWork<D> w;
     w.f = f; w.L = L; w.R = R;
     double sL[Q], sR[Q], vL[Q], vR[Q];
@@ -916,35 +917,106 @@ struct AnalyticInnerFaceK {   // idx over interior faces; staged like InnerFaceK
     for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + L]; sR[v] = d.U[(size_t)v*d.nStates + R]; }
     w.load(d, c, f);
     w.reconstruct(c, sL, sR, vL, vR);
+    PData pL, pR;
+    P::physicalData(c, vL, pL);
+    P::physicalData(c, vR, pR);
+    double flux[Q];
     {
-      PData pL, pR;
-      P::physicalData(c, vL, pL);
-      P::physicalData(c, vR, pR);
       const double faceArea = w.area/1;
       d.ucL[f] = dmax(P::maxEigenValue(pL, w.n), 0.)*faceArea;         // AUSMFlux.ci:410-440
       double tn[3];
 #pragma unroll
       for (int k = 0; k < 3; ++k) tn[k] = -1.0*w.n[k];
       d.ucR[f] = dmax(P::maxEigenValue(pR, tn), 0.)*faceArea;
-      d.ucD[f] = 0.;
       typename P::ASide a, b;
       P::aside(pL, a); P::aside(pR, b);
-      double flux[Q];
       P::ausm(c, a, b, w.n, flux);
 #pragma unroll
-      for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = flux[v]*w.area;
+      for (int v = 0; v < Q; ++v) flux[v] *= w.area;
     }
-    typename P::JSide jl, jr;
-    P::jside(c, vL, jl);
-    P::jside(c, vR, jr);
+    // NSFluxAndJacob::computeFlux (NSFluxAndJacob.cxx:54-118): the diffusive flux, its update coefficient and
+    // d grad / d state of the two cells (DerivativeComputer::getGradientsJacob)
+    double gj[2][3] = {{0., 0., 0.}, {0., 0., 0.}}, avS[Q], mu = 0., lambda = 0., ucD = 0.;
+#pragma unroll
+    for (int v = 0; v < Q; ++v) avS[v] = 0.;
+    if (hasDiff) {
+      double dflux[Q];
+      if constexpr (DV == 1) {
+        CorrectedWork<D> cw;
+        cw.setup(d, c, f, L, R, false, w.n, w.area);
+        cw.innerDiffusive(d, c, R, sL, sR, false, dflux, ucD, stg, stride);
+        const double ovDr = ddiv(1., cw.dr);                    // CorrectedDerivative2D.cxx:461-469
+#pragma unroll
+        for (int k = 0; k < D; ++k) { gj[0][k] = (-ovDr)*cw.eN[k]; gj[1][k] = ovDr*cw.eN[k]; }
+#pragma unroll
+        for (int v = 0; v < Q; ++v) avS[v] = cw.avState[v];
+        mu = cw.mu; lambda = cw.lambda;
+      } else {
+        w.loadDiamond(d);
+        w.setCellStates(sL, sR);
+        w.allGrads();
+        w.transport(c);
+        w.diffFlux(c, w.grad, dflux);
+        const double nu = ddiv(w.mu, P::density(c, w.avState));
+        ucD = ddiv(nu*w.area*w.area, w.volume);
+        if constexpr (D == 2) {                                 // DiamondVolume2DDerivative.cxx:153-159
+          const double iv = ddiv(0.5, w.volume);
+#pragma unroll
+          for (int k = 0; k < 2; ++k) { gj[0][k] = iv*(w.cvn[0][k] + w.cvn[1][k]); gj[1][k] = iv*(w.cvn[3][k] + w.cvn[2][k]); }
+        } else {                                                // DiamondVolume3DDerivative.cxx:607-625
+          const double iv = ddiv(1./3., w.volume);
+          if (w.nbN == 3) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+              gj[0][k] = iv*(w.cvn[0][k] + w.cvn[1][k] + w.cvn[2][k]);
+              gj[1][k] = iv*(w.cvn[3][k] + w.cvn[4][k] + w.cvn[5][k]);
+            }
+          } else {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+              gj[0][k] = iv*(w.cvn[0][k] + w.cvn[1][k] + w.cvn[2][k] + w.cvn[3][k]);
+              gj[1][k] = iv*(w.cvn[4][k] + w.cvn[5][k] + w.cvn[6][k] + w.cvn[7][k]);
+            }
+          }
+        }
+#pragma unroll
+        for (int v = 0; v < Q; ++v) avS[v] = w.avState[v];
+        mu = w.mu; lambda = w.lambda;
+      }
+#pragma unroll
+      for (int v = 0; v < Q; ++v) flux[v] -= dflux[v];          // FVMCC_ComputeRHS.cxx:260-276
+    }
+    d.ucD[f] = ucD;
+#pragma unroll
+    for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = flux[v];
     const double rf = c.resFactor;
-    double J[Q*Q];
-    P::ausmUpJacobCons(c, jl, jr, w.n, 0, J);
+    typename P::JSide jl, jr;
+    typename P::JPvt kp;
+    const bool pvt = (c.updateVar == CFB200_UV_PVT);            // AUSMPlusUpFlux.ci:1238-1273
+    if (pvt) P::jprePvt(c, pL, pR, w.n, kp);
+    else { P::jside(c, vL, jl); P::jside(c, vR, jr); }
+#pragma unroll 1
+    for (int side = 0; side < 2; ++side) {
+      double J[Q*Q];
+      if (pvt) P::ausmUpJacobPvt(c, kp, pL, pR, w.n, side, J);
+      else P::ausmUpJacobCons(c, jl, jr, w.n, side, J);
 #pragma unroll
-    for (int k = 0; k < Q*Q; ++k) stg[(size_t)k*stride] = ((J[k]*w.area)*rf)*(-1.);
-    P::ausmUpJacobCons(c, jl, jr, w.n, 1, J);
+      for (int k = 0; k < Q*Q; ++k) J[k] *= w.area;             // FVMCC_FluxSplitter.hh:88-96
+      if (hasDiff) {
+        // "note the opposite sign of the diffusive jacob compared to convective jacob", FVMCC_ComputeRhsJacobAnalytic.cxx:83-91
+        double DJ[Q*Q];
+        P::nsFluxJacobian(c, avS, gj[side], w.n, mu, lambda, DJ);
 #pragma unroll
-    for (int k = 0; k < Q*Q; ++k) stg[(size_t)(Q*Q + k)*stride] = (J[k]*w.area)*rf;
+        for (int k = 0; k < Q*Q; ++k) J[k] -= DJ[k]*w.area;
+      }
+      if (side == 0) {
+#pragma unroll
+        for (int k = 0; k < Q*Q; ++k) stg[(size_t)k*stride] = (J[k]*rf)*(-1.);
+      } else {
+#pragma unroll
+        for (int k = 0; k < Q*Q; ++k) stg[(size_t)(Q*Q + k)*stride] = J[k]*rf;
+      }
+    }
   }
 };
 

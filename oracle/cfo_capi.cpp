@@ -72,8 +72,11 @@ int cfo_compute(const Config* c, const MeshView* m, const BC* bcs, double* U, Cf
           c->diffusive != DIFF_NONE) { co->status = 2; return 2; }
       Solver<3, MhdPhys> s(*c, *m, bcs); s.execute(U, o);
     }
-    else if (c->computeJacobian == 2 && !(c->fluxSplitter == FS_AUSMPLUSUP && c->updateVar == UV_CONS &&
-                                          c->diffusive == DIFF_NONE)) { co->status = 2; return 2; }
+    else if (c->computeJacobian == 2 && (c->fluxSplitter != FS_AUSMPLUSUP ||
+                                         (c->diffusive != DIFF_NONE && c->updateVar != UV_PVT) ||
+                                         (c->diffusive != DIFF_NONE && c->derivativeStrategy == 1 && c->dim != 2))) {
+      co->status = 2; return 2;
+    }
     else if (c->dim == 2) { Solver<2> s(*c, *m, bcs); s.execute(U, o); }
     else { Solver<3> s(*c, *m, bcs); s.execute(U, o); }
   } catch (const std::exception&) { co->status = 2; return 2; }
@@ -98,6 +101,21 @@ int cfo_ausm_jacob_cons(const Config* c, const double* uL, const double* uR, con
                      Phys<2>::ausmPlusUpJacobCons(*c, a, b, n, side, J); }
   else { Phys<3>::Data a, b; Phys<3>::computePhysicalData(*c, uL, a); Phys<3>::computePhysicalData(*c, uR, b);
          Phys<3>::ausmPlusUpJacobCons(*c, a, b, n, side, J); }
+  return 0;
+}
+// Same in Puvt / Pvt variables (c->updateVar == UV_PVT): the two face states in UPDATE variables.
+int cfo_ausm_jacob_pvt(const Config* c, const double* uL, const double* uR, const double* n, int side, double* J) {
+  if (c->dim == 2) { Phys<2>::Data a, b; Phys<2>::computePhysicalData(*c, uL, a); Phys<2>::computePhysicalData(*c, uR, b);
+                     Phys<2>::ausmPlusUpJacobPvt(*c, a, b, n, side, J); }
+  else { Phys<3>::Data a, b; Phys<3>::computePhysicalData(*c, uL, a); Phys<3>::computePhysicalData(*c, uR, b);
+         Phys<3>::ausmPlusUpJacobPvt(*c, a, b, n, side, J); }
+  return 0;
+}
+// Test hook: analytic diffusive flux Jacobian of one side from the average state, d grad / d state, mu and lambda.
+int cfo_ns_flux_jacob(const Config* c, const double* avState, const double* gj, const double* n, double mu, double tc,
+                      double* J) {
+  if (c->dim == 2) Phys<2>::nsFluxJacobian(*c, avState, gj, n, mu, tc, J);
+  else Phys<3>::nsFluxJacobian(*c, avState, gj, n, mu, tc, J);
   return 0;
 }
 int cfo_ausm_flux(const Config* c, const double* uL, const double* uR, const double* n, double* F) {

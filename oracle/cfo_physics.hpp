@@ -516,6 +516,179 @@ struct Phys {
   // MathFunctions.hh:58-61
   static double sigmoidF(double x, double y, double K) { return 0.5*(1.0 - (1.0 + K)*(x - y)/(-std::abs(x - y) - K)); }
 
+  // ---- a19: analytic Jacobian of the AUSM+up flux in Puvt / Pvt variables -------------------------------------------
+  // AUSMPlusUpFlux<UPDATEVAR>::ComputedFluxdPvt (AUSMPlusUpFlux.ci:160-668), column by column: p (:320-391), u v w
+  // (:394-597, one form), T (:599-664).  Its quirks are kept: d rho / d p and d rho / d T use the dimensional constants of
+  // air (Mmass, Rgas :183-184) whatever the model's R; the T column leaves the d rho12 term out of d mP (:633-635) and sums
+  // d mdot12 in another order than the p column (:641 vs :363); the p column has no mdot12 dH term in the energy row (:390).
+  static void ausmPlusUpJacobPvt(const Config& c, const PData& L, const PData& R, const double* n, int side, double* J) {
+    const bool LEFT = (side == 0);
+    const double rhoL = L.rho, rhoR = R.rho, HL = L.H, HR = R.H, TL = L.T, TR = R.T;
+    const double gammaL = c.gamma, gammaR = c.gamma, pL = L.p, pR = R.p;
+    const double UL = L.v[0], UR = R.v[0], VL = L.v[1], VR = R.v[1], WL = L.v[2], WR = R.v[2];
+    const double Mmass = 28.965338E-3, Rgas = 8.3145;
+    const double beta = c.ausmBeta, Ksig = c.coeffSigmoid, sigma = c.ausmSigma;
+    double qnL = 0.0, qnR = 0.0;
+    for (int i = 0; i < D; ++i) { qnL += L.v[i]*n[i]; qnR += R.v[i]*n[i]; }
+    // computeSoundSpeedForJacobian (AUSMFlux.ci:795-822)
+    const double aCritL = std::sqrt(2.0*(gammaL - 1.0)/(gammaL + 1.0)*HL);
+    const double aCritR = std::sqrt(2.0*(gammaR - 1.0)/(gammaR + 1.0)*HR);
+    const double aCritLsig = sigmoidF(aCritL, qnL, Ksig);
+    const double OneaCritLsig = (1.0 - aCritLsig);
+    const double aCritRsig = sigmoidF(aCritR, -qnR, Ksig);
+    const double OneaCritRsig = -(1.0 - aCritRsig);
+    const double asigL = aCritLsig*aCritL + (1.0 - aCritLsig)*qnL;
+    const double asigR = aCritRsig*aCritR - (1.0 - aCritRsig)*qnR;
+    const double ahatL = aCritL*aCritL/std::max(aCritL, qnL);
+    const double ahatR = aCritR*aCritR/std::max(aCritR, -qnR);
+    const double a12 = (1.0 - sigmoidF(ahatL, ahatR, Ksig))*aCritL*aCritL/asigL + sigmoidF(ahatL, ahatR, Ksig)*aCritR*aCritR/asigR;
+
+    const double rho12 = 0.5*(rhoL + rhoR);
+    const double ML = qnL/a12, MR = qnR/a12;
+    const double mInf = c.machInf;
+    const double MBarSq = 0.5*(ML*ML + MR*MR);
+    const double MinfSq = mInf*mInf;
+    const double sigMbarsqMinfsq = sigmoidF(MBarSq, MinfSq, Ksig);
+    const double sig2 = sigMbarsqMinfsq*MBarSq + (1.0 - sigMbarsqMinfsq)*MinfSq;
+    const double MZeroSig = sigmoidF(1.0, sig2, Ksig);
+    const double mZero = std::sqrt((1 - MZeroSig)*1.0 + MZeroSig*sig2);
+    const double fa = mZero*(2.0 - mZero);
+    const double sigmaMBarSq = 1.0 - sigma*MBarSq;
+    const double mPSig = sigmoidF(sigmaMBarSq, 0.0, Ksig);
+    const double dMpCon = -(c.ausmKp)*mPSig;
+    const double M4Plus = (std::abs(ML) >= 1.0) ? mach1Plus(ML) : mach2Plus(ML)*(1.0 - 16.*beta*mach2Min(ML));
+    const double M4Minus = (std::abs(MR) >= 1.0) ? mach1Min(MR) : mach2Min(MR)*(1.0 + 16.*beta*mach2Plus(MR));
+    const double mP = -(c.ausmKp)*mPSig*sigmaMBarSq*(pR - pL)/(fa*rho12*a12*a12);
+    const double M12 = M4Plus + M4Minus + mP;
+    const double sigrho = sigmoidF(M12, 0.0, Ksig);
+    const double Onesigrho = (1.0 - sigrho);
+    const double rhostar = sigrho*rhoL + Onesigrho*rhoR;
+    const double mdot12 = M12*a12*rhostar;
+    const double sigm = sigmoidF(mdot12, 0.0, Ksig);
+    const double Onesigm = (1.0 - sigm);
+    const double alpha = (3.0/16.0)*(-4.0 + 5.0*fa*fa);
+    const double P5Plus = (std::abs(ML) >= 1.0) ? mach1Plus(ML)/ML : mach2Plus(ML)*((2.0 - ML) - 16.*alpha*ML*mach2Min(ML));
+    const double P5Minus = (std::abs(MR) >= 1.0) ? mach1Min(MR)/MR : mach2Min(MR)*((-2.0 - MR) + 16.*alpha*MR*mach2Plus(MR));
+    // global constants (:283-317)
+    const double rhoa2 = fa*rho12*a12*a12;
+    const double prho2a2 = -(pR - pL)/(fa*rho12*rho12*a12*a12);
+    const double prhoa3 = -2.0*(pR - pL)/(fa*rho12*a12*a12*a12);
+    const double prhoa2fa = -(pR - pL)/(fa*fa*rho12*a12*a12);
+    const double daCritLconst = std::sqrt((gammaL - 1.0)/(2.0*(gammaL + 1.0)*HL));
+    const double daCritRconst = std::sqrt((gammaR - 1.0)/(2.0*(gammaR + 1.0)*HR));
+    const double dahatCon1L = 2.0*aCritL/asigL, dahatCon1R = 2.0*aCritR/asigR;
+    const double dahatCon2L = -aCritL*aCritL/(asigL*asigL), dahatCon2R = -aCritR*aCritR/(asigR*asigR);
+    const double dahatSig = sigmoidF(ahatL, ahatR, Ksig);
+    const double OnedahatSig = (1.0 - dahatSig);
+    const double dMCon = 1.0/a12;
+    const double dMConL = -qnL/(a12*a12), dMConR = -qnR/(a12*a12);
+    const double dmZeroCon = 0.5/mZero*sigMbarsqMinfsq*MZeroSig*sigmaMBarSq;
+    const double dfaCon = 2.0*(1.0 - mZero);
+    const double dM4Lsign = (ML < 0.0) ? -1.0 : 1.0, dM4Rsign = (MR < 0.0) ? -1.0 : 1.0;
+    const double OnedM4Lsign = 0.5*(1. + dM4Lsign), OnedM4Rsign = 0.5*(1. - dM4Rsign);
+    const double dM4Lsuper = (0.5*(ML + 1.) + 4.*beta*ML*(ML*ML - 1.));
+    const double dM4Rsuper = -(0.5*(MR - 1.) + 4.*beta*MR*(MR*MR - 1.));
+    const double a12rhostar = a12*rhostar, M12a12 = M12*a12, M12rhostar = M12*rhostar;
+    const double dalphaCon = 15.0/8.0*fa;
+    const double dP5Lconst1 = 0.5*(10.0*alpha*ML*ML*ML*ML - (1.5 + 12.0*alpha)*ML*ML + 1.5 + 2.0*alpha);
+    const double dP5Rconst1 = -0.5*(10.0*alpha*MR*MR*MR*MR - (1.5 + 12.0*alpha)*MR*MR + 1.5 + 2.0*alpha);
+    const double dP5Lconst2 = ML*(ML*ML - 1)*(ML*ML - 1);
+    const double dP5Rconst2 = -MR*(MR*MR - 1)*(MR*MR - 1);
+    const double pudP5Plus = P5Minus*rho12*fa*a12*(qnR - qnL);
+    const double pudP5Minus = P5Plus*rho12*fa*a12*(qnR - qnL);
+    const double pudrho12 = P5Plus*P5Minus*fa*a12*(qnR - qnL);
+    const double pudfa = P5Plus*P5Minus*rho12*a12*(qnR - qnL);
+    const double puda12 = P5Plus*P5Minus*rho12*fa*(qnR - qnL);
+    const double pudqn = P5Plus*P5Minus*rho12*fa;
+    const double dpuCon = 0.5*c.ausmKu;
+    const double Usig = sigm*UL + Onesigm*UR, Vsig = sigm*VL + Onesigm*VR, Wsig = sigm*WL + Onesigm*WR;
+    const double Hsig = sigm*HL + Onesigm*HR;
+    const bool supL = std::abs(ML) >= 1.0, supR = std::abs(MR) >= 1.0;
+    for (int k = 0; k < Q*Q; ++k) J[k] = 0.;
+    const double vs[3] = {Usig, Vsig, Wsig};
+
+    // kind 0: p column, 1: a velocity column, 2: T column
+    struct Col { double dmdot, dp12; };
+    auto column = [&](int kind, double dqnL, double dqnR, double dhL, double dhR, double dpL, double dpR,
+                      double drhoLd, double drhoRd) -> Col {
+      const double drho12d = 0.5*(drhoLd + drhoRd);
+      const double drhostard = sigrho*drhoLd + Onesigrho*drhoRd;
+      const double daCritLd = daCritLconst*dhL, daCritRd = daCritRconst*dhR;
+      const double dasigLd = (kind == 1) ? aCritLsig*daCritLd + OneaCritLsig*dqnL : aCritLsig*daCritLd;
+      const double dasigRd = (kind == 1) ? aCritRsig*daCritRd + OneaCritRsig*dqnR : aCritRsig*daCritRd;
+      const double dahatLd = (dahatCon1L*daCritLd + dahatCon2L*dasigLd);
+      const double dahatRd = (dahatCon1R*daCritRd + dahatCon2R*dasigRd);
+      const double da12d = OnedahatSig*dahatLd + dahatSig*dahatRd;
+      const double dMLd = (kind == 1) ? dMCon*dqnL + dMConL*da12d : dMConL*da12d;
+      const double dMRd = (kind == 1) ? dMCon*dqnR + dMConR*da12d : dMConR*da12d;
+      const double dMBarSqd = ML*dMLd + MR*dMRd;
+      const double dmZerod = dmZeroCon*dMBarSqd;
+      const double dfad = dfaCon*dmZerod;
+      const double dM4Plusd = supL ? OnedM4Lsign*dMLd : dM4Lsuper*dMLd;
+      const double dM4Minusd = supR ? OnedM4Rsign*dMRd : dM4Rsuper*dMRd;
+      const double dMpdda = prhoa3*da12d;
+      const double dMpddfa = prhoa2fa*dfad;
+      double dMpd;
+      if (kind == 0) {
+        const double dMpddp = (dpR - dpL)/rhoa2;
+        const double dMpddrho = prho2a2*drho12d;
+        dMpd = dMpCon*(dMpddp + dMpddrho + dMpdda + dMpddfa);
+      } else dMpd = dMpCon*(dMpdda + dMpddfa);
+      const double dM12d = dM4Plusd + dM4Minusd + dMpd;
+      double dmdotd;
+      if (kind == 0) dmdotd = dM12d*a12rhostar + M12a12*drhostard + M12rhostar*da12d;
+      else if (kind == 1) dmdotd = dM12d*a12rhostar + M12rhostar*da12d;
+      else dmdotd = dM12d*a12rhostar + M12rhostar*da12d + M12a12*drhostard;
+      const double dalphad = dalphaCon*dfad;
+      const double dP5Plusd = supL ? 0. : dP5Lconst1*dMLd + dP5Lconst2*dalphad;
+      const double dP5Minusd = supR ? 0. : dP5Rconst1*dMRd + dP5Rconst2*dalphad;
+      const double t1 = pudP5Plus*dP5Plusd, t2 = pudP5Minus*dP5Minusd, tfa = pudfa*dfad, tda = puda12*da12d;
+      const double trho = (kind == 1) ? 0.0 : pudrho12*drho12d;
+      const double tqn = (kind == 1) ? pudqn*da12d*(dqnR - dqnL) : 0.0;
+      const double dpud = dpuCon*(t1 + t2 + trho + tfa + tda + tqn);
+      Col o;
+      o.dmdot = dmdotd;
+      if (kind == 0) o.dp12 = dP5Plusd*pL + P5Plus*dpL + dP5Minusd*pR + P5Minus*dpR + dpud;
+      else o.dp12 = dP5Plusd*pL + dP5Minusd*pR + dpud;
+      return o;
+    };
+    // dFdp
+    {
+      const double drhoLd = LEFT ? Mmass/(Rgas*TL) : 0., drhoRd = LEFT ? 0. : Mmass/(Rgas*TR);
+      const double dhL = LEFT ? -gammaL*pL/((gammaL - 1)*rhoL*rhoL) : 0.;
+      const double dhR = LEFT ? 0. : -gammaR*pR/((gammaR - 1)*rhoR*rhoR);
+      const Col k = column(0, 0., 0., dhL, dhR, LEFT ? 1. : 0., LEFT ? 0. : 1., drhoLd, drhoRd);
+      J[0*Q + 0] = k.dmdot;
+      for (int r = 0; r < D; ++r) J[(1+r)*Q + 0] = k.dmdot*vs[r] + k.dp12*n[r];
+      J[(Q-1)*Q + 0] = k.dmdot*Hsig;
+    }
+    // dFdu, dFdv, dFdw
+    for (int m = 0; m < D; ++m) {
+      const double dqnLd = LEFT ? n[m] : 0., dqnRd = LEFT ? 0. : n[m];
+      const double dhL = LEFT ? L.v[m] : 0., dhR = LEFT ? 0. : R.v[m];
+      const double dvelL = LEFT ? 1. : 0., dvelR = LEFT ? 0. : 1.;
+      const Col k = column(1, dqnLd, dqnRd, dhL, dhR, 0., 0., 0., 0.);
+      const int col = 1 + m;
+      J[0*Q + col] = k.dmdot;
+      for (int r = 0; r < D; ++r) {
+        if (r == m) J[(1+r)*Q + col] = k.dmdot*vs[r] + mdot12*(sigm*dvelL + Onesigm*dvelR) + k.dp12*n[r];
+        else J[(1+r)*Q + col] = k.dmdot*vs[r] + k.dp12*n[r];
+      }
+      J[(Q-1)*Q + col] = k.dmdot*Hsig + mdot12*(sigm*dhL + Onesigm*dhR);
+    }
+    // dFdT
+    {
+      const double drhoLd = LEFT ? -Mmass*pL/(Rgas*TL*TL) : 0., drhoRd = LEFT ? 0. : -Mmass*pR/(Rgas*TR*TR);
+      const double dhL = LEFT ? gammaL/(rhoL*(gammaL - 1)) : 0., dhR = LEFT ? 0. : gammaR/(rhoR*(gammaR - 1));
+      const Col k = column(2, 0., 0., dhL, dhR, 0., 0., drhoLd, drhoRd);
+      const int col = Q - 1;
+      J[0*Q + col] = k.dmdot;
+      for (int r = 0; r < D; ++r) J[(1+r)*Q + col] = k.dmdot*vs[r] + k.dp12*n[r];
+      J[(Q-1)*Q + col] = k.dmdot*Hsig + mdot12*(sigm*dhL + Onesigm*dhR);
+    }
+  }
+
+
   // AUSMPlusUpFlux<UPDATEVAR>::ComputedFluxdCons (AUSMPlusUpFlux.ci:675-1203) with
   // AUSMFlux::computeSoundSpeedForJacobian (AUSMFlux.ci:795-822).  side 0 = LEFT, 1 = RIGHT;
   // J is row-major Q x Q: J[i*Q + j] = d F_i / d U_j (per unit area).  The columns follow the reference one by
@@ -822,6 +995,75 @@ struct Phys {
                (tau[0][1]*avState[1] + tau[1][1]*avState[2])*n[1] - qFlux;
     }
   }
+
+  // a19: analytic Jacobian of the diffusive flux with respect to the state of one side, given d grad / d state of that
+  // side (gj, from DerivativeComputer::getGradientsJacob): NavierStokes2DPuvt::computeFluxJacobian
+  // (NavierStokes2DPuvt.cxx:126-161) / NavierStokes3DPvt::computeFluxJacobian (NavierStokes3DPvt.cxx:129-193).
+  // Only the velocity / temperature entries are written, the rest of J stays zero (the matrices are sized once and never
+  // touched elsewhere, DiffusiveVarSet / ComputeDiffusiveFlux::setup).  The 4/3 and 2/3 of the reference are kept as they
+  // are (they are swapped with respect to the stress tensor of getFlux).
+  static void nsFluxJacobian(const Config& c, const double* avState, const double* gj, const double* n,
+                             double mu, double tc, double* J) {
+    for (int k = 0; k < Q*Q; ++k) J[k] = 0.;
+    const double fourThird = 4./3.;
+    const double twoThird = 2./3.;
+    const double nx = n[0], ny = n[1];
+    const double coeffTau = c.coeffTau, coeffQ = c.coeffQ;
+    if (D == 2) {
+      const double tauxx_uL = twoThird*mu*gj[0];
+      const double tauxx_vL = -fourThird*mu*gj[1];
+      const double tauxy_uL = mu*gj[1];
+      const double tauxy_vL = mu*gj[0];
+      const double tauyy_uL = -fourThird*mu*gj[0];
+      const double tauyy_vL = twoThird*mu*gj[1];
+      const double qx_T = -tc*gj[0];
+      const double qy_T = -tc*gj[1];
+      const double avU = avState[1], avV = avState[2];
+      J[1*Q+1] = coeffTau*(tauxx_uL*nx + tauxy_uL*ny);
+      J[1*Q+2] = coeffTau*(tauxx_vL*nx + tauxy_vL*ny);
+      J[2*Q+1] = coeffTau*(tauxy_uL*nx + tauyy_uL*ny);
+      J[2*Q+2] = coeffTau*(tauxy_vL*nx + tauyy_vL*ny);
+      J[3*Q+1] = J[1*Q+1]*avU + J[2*Q+1]*avV;
+      J[3*Q+2] = J[1*Q+2]*avU + J[2*Q+2]*avV;
+      J[3*Q+3] = -coeffQ*(qx_T*nx + qy_T*ny);
+    } else {
+      const double nz = n[D-1];
+      const double gz = gj[D-1];
+      const double tauxx_uL = twoThird*mu*gj[0];
+      const double tauxx_vL = -fourThird*mu*gj[1];
+      const double tauxx_wL = -fourThird*mu*gz;
+      const double tauyy_uL = -fourThird*mu*gj[0];
+      const double tauyy_vL = twoThird*mu*gj[1];
+      const double tauyy_wL = -fourThird*mu*gz;
+      const double tauzz_uL = -fourThird*mu*gj[0];
+      const double tauzz_vL = -fourThird*mu*gj[1];
+      const double tauzz_wL = twoThird*mu*gz;
+      const double tauxy_uL = mu*gj[1];
+      const double tauxy_vL = mu*gj[0];
+      const double tauxz_uL = mu*gz;
+      const double tauxz_wL = mu*gj[0];
+      const double tauyz_vL = mu*gz;
+      const double tauyz_wL = mu*gj[1];
+      const double qx_T = -tc*gj[0];
+      const double qy_T = -tc*gj[1];
+      const double qz_T = -tc*gz;
+      const double avU = avState[1], avV = avState[2], avW = avState[D];
+      const int q4 = Q - 1;
+      J[1*Q+1] = coeffTau*(tauxx_uL*nx + tauxy_uL*ny + tauxz_uL*nz);
+      J[1*Q+2] = coeffTau*(tauxx_vL*nx + tauxy_vL*ny);
+      J[1*Q+3] = coeffTau*(tauxx_wL*nx + tauxz_wL*nz);
+      J[2*Q+1] = coeffTau*(tauxy_uL*nx + tauyy_uL*ny);
+      J[2*Q+2] = coeffTau*(tauxy_vL*nx + tauyy_vL*ny + tauyz_vL*nz);
+      J[2*Q+3] = coeffTau*(tauyy_wL*ny + tauyz_wL*nz);
+      J[3*Q+1] = coeffTau*(tauxz_uL*nx + tauzz_uL*nz);
+      J[3*Q+2] = coeffTau*(tauyz_vL*ny + tauzz_vL*nz);
+      J[3*Q+3] = coeffTau*(tauxz_wL*nx + tauyz_wL*ny + tauzz_wL*nz);
+      J[q4*Q+1] = J[1*Q+1]*avU + J[2*Q+1]*avV + J[3*Q+1]*avW;
+      J[q4*Q+2] = J[1*Q+2]*avU + J[2*Q+2]*avV + J[3*Q+2]*avW;
+      J[q4*Q+3] = J[1*Q+3]*avU + J[2*Q+3]*avV + J[3*Q+3]*avW;
+      J[q4*Q+q4] = -coeffQ*(qx_T*nx + qy_T*ny + qz_T*nz);
+    }
+  }
 };
 
 // MathFunctions.hh:167-179
@@ -1009,11 +1251,14 @@ struct MhdPhys {
   static bool roeFlux(const Config&, const double*, const double*, const MhdData&, const MhdData&, const double*, double*) { return false; }
   static bool ausmFlux(const Config&, const MhdData&, const MhdData&, const double*, double*) { return false; }
   static void ausmPlusUpJacobCons(const Config&, const MhdData&, const MhdData&, const double*, int, double*) {}
+  static void ausmPlusUpJacobPvt(const Config&, const MhdData&, const MhdData&, const double*, int, double*) {}
   static double dynViscosity(const Config&, const double*) { return 0.; }
   static double thermConductivity(const Config&, double) { return 0.; }
   static double nsDensity(const Config&, const double*) { return 1.; }
   static void nsFluxUnit(const Config&, const double*, const double (*)[3], const double*, double, double, double* f) {
     for (int i = 0; i < Q; ++i) f[i] = 0.;
+  }  static void nsFluxJacobian(const Config&, const double*, const double*, const double*, double, double, double* J) {
+    for (int k = 0; k < Q*Q; ++k) J[k] = 0.;
   }
 };
 

@@ -360,6 +360,9 @@ public:
     // Corrected{2,3}D derivative (CorrectedDerivative2D.hh:150-190)
     double dr, eRLdotNN[3], oEminusNN[3][3];
     int nCorr, corrStencil[128];   // _stencil of a boundary face (state indices)
+    // a19: d grad / d state of the left / right cell (DerivativeComputer::getGradientsJacob) and the average state of
+    // the unperturbed evaluation, what NSFluxAndJacob::computeFlux (NSFluxAndJacob.cxx:106-118) differentiates
+    double gradJacob[2][3], avState[Q];
   };
 
   double gradCoeff(int stateID, int iVar, const double* xq, const double* xs, const Outputs& o) const {
@@ -487,6 +490,9 @@ public:
         for (int b = 0; b < D; ++b)
           x.oEminusNN[a][b] = (a == b) ? 1.0 - x.n[a]*x.n[a] : -(x.n[std::min(a, b)]*x.n[std::max(a, b)]);
       x.volume = x.isB ? mesh.volumes[x.L] : 0.5*(mesh.volumes[x.L] + mesh.volumes[x.R]);
+      // getGradientsJacob, CorrectedDerivative2D.cxx:461-469 (CorrectedDerivative3D has none: rejected at set_config)
+      const double ovDr = 1./x.dr;
+      for (int k = 0; k < D; ++k) { x.gradJacob[0][k] = (-ovDr)*x.eRLdotNN[k]; x.gradJacob[1][k] = ovDr*x.eRLdotNN[k]; }
     }
     // setGradientVars: values(i,j) = (*states[j])[i]; states = L, R, face nodes, boundary stencil
     const double* sL = &U[(size_t)x.L*Q];
@@ -573,6 +579,7 @@ public:
     P::nsFluxUnit(cfg, avState, grad, x.n, mu, lambda, dflux);
     for (int i = 0; i < Q; ++i) dflux[i] *= x.area;
     if (!isPerturb) {
+      for (int i = 0; i < Q; ++i) x.avState[i] = avState[i];
       const double nu = mu/P::nsDensity(cfg, avState);
       const double diffUpdateCoeff = nu*x.area*x.area/x.volume;
       o.updateCoeff[x.L] += diffUpdateCoeff;
@@ -601,6 +608,11 @@ public:
         const double det = (node2[0] - node0[0])*(node3[1] - node1[1]) - (node3[0] - node1[0])*(node2[1] - node0[1]);
         if (det < 0.0) for (int k = 0; k < 4; ++k) { x.n2d[k][0] *= -1.; x.n2d[k][1] *= -1.; }
         x.volume = 0.5*std::abs(det);
+        // getGradientsJacob, DiamondVolume2DDerivative.cxx:153-159
+        for (int k = 0; k < 2; ++k) {
+          x.gradJacob[0][k] = (0.5/x.volume)*(x.n2d[0][k] + x.n2d[1][k]);
+          x.gradJacob[1][k] = (0.5/x.volume)*(x.n2d[3][k] + x.n2d[2][k]);
+        }
       } else if (nb == 3) {
         x.nbCV = 5;
         for (int k = 0; k < 3; ++k) x.cvState[k] = &o.nstates[(size_t)fn[k]*Q];
@@ -622,6 +634,12 @@ public:
         factor *= -1.;
         for (int r = 1; r < 5; ++r) for (int d = 0; d < 3; ++d) x.pn2[r][d] *= factor;
         x.volume = mesh.cvol[x.f];
+        // getGradientsJacob, DiamondVolume3DDerivative.cxx:607-625
+        const double invVolume = (1./3.)/x.volume;
+        for (int ix = 0; ix < 3; ++ix) {
+          x.gradJacob[0][ix] = invVolume*(x.pn1[1][ix] + x.pn1[2][ix] + x.pn1[3][ix] + x.pn1[4][ix]);
+          x.gradJacob[1][ix] = invVolume*(x.pn2[1][ix] + x.pn2[2][ix] + x.pn2[3][ix] + x.pn2[4][ix]);
+        }
       }
     }
     // setGradientVars (NavierStokes3DPvt.cxx:52-63): values(i,j) = (*states[j])[i]
@@ -660,6 +678,11 @@ public:
       nrm(node4, node1, node2, node1, factor, n142);
       nrm(node2, node0, node4, node0, factor, n024);
       const double invVolume = (1./3.)/x.volume;
+      if (!isPerturb)    // getGradientsJacob, DiamondVolume3DDerivative.cxx:611-614 (the normals of the last evaluation)
+        for (int ix = 0; ix < 3; ++ix) {
+          x.gradJacob[0][ix] = invVolume*(n031[ix] + n132[ix] + n023[ix]);
+          x.gradJacob[1][ix] = invVolume*(n041[ix] + n142[ix] + n024[ix]);
+        }
       for (int i = 0; i < Q; ++i) {
         const double v031 = values[i][0] + values[i][3] + values[i][1];
         const double v132 = values[i][1] + values[i][3] + values[i][2];
@@ -706,6 +729,7 @@ public:
     P::nsFluxUnit(cfg, avState, grad, x.n, mu, lambda, dflux);
     for (int i = 0; i < Q; ++i) dflux[i] *= x.area;
     if (!isPerturb) {
+      for (int i = 0; i < Q; ++i) x.avState[i] = avState[i];
       const double nu = mu/P::nsDensity(cfg, avState);
       const double diffUpdateCoeff = nu*x.area*x.area/x.volume;
       o.updateCoeff[x.L] += diffUpdateCoeff;
@@ -787,9 +811,22 @@ public:
         // a19: FVMCC_ComputeRhsJacobAnalytic.cxx:68-246 (non axisymmetric, no diffusive term, no source term) with the
         // flux Jacobians integrated over the face by FVMCC_FluxSplitter::integrateFluxAndJacob (FVMCC_FluxSplitter.hh:88-96)
         double JL[Q*Q], JR[Q*Q], colv[Q];
-        P::ausmPlusUpJacobCons(cfg, x.pL, x.pR, x.n, 0, JL);
-        P::ausmPlusUpJacobCons(cfg, x.pL, x.pR, x.n, 1, JR);
+        if (cfg.updateVar == UV_PVT) {          // AUSMPlusUpFlux.ci:1238-1273
+          P::ausmPlusUpJacobPvt(cfg, x.pL, x.pR, x.n, 0, JL);
+          P::ausmPlusUpJacobPvt(cfg, x.pL, x.pR, x.n, 1, JR);
+        } else {
+          P::ausmPlusUpJacobCons(cfg, x.pL, x.pR, x.n, 0, JL);
+          P::ausmPlusUpJacobCons(cfg, x.pL, x.pR, x.n, 1, JR);
+        }
         for (int k = 0; k < Q*Q; ++k) { JL[k] *= x.area; JR[k] *= x.area; }
+        if (cfg.diffusive != DIFF_NONE) {
+          // NSFluxAndJacob.cxx:106-118, then "note the opposite sign" FVMCC_ComputeRhsJacobAnalytic.cxx:83-91
+          double DL[Q*Q], DR[Q*Q];
+          P::nsFluxJacobian(cfg, x.avState, x.gradJacob[0], x.n, x.muBkp, x.lambdaBkp, DL);
+          P::nsFluxJacobian(cfg, x.avState, x.gradJacob[1], x.n, x.muBkp, x.lambdaBkp, DR);
+          for (int k = 0; k < Q*Q; ++k) { DL[k] *= x.area; DR[k] *= x.area; }
+          for (int k = 0; k < Q*Q; ++k) { JL[k] -= DL[k]; JR[k] -= DR[k]; }
+        }
         auto addBlock = [&](int rowCell, int colCell, const double* Jm) {
           for (int j = 0; j < Q; ++j) {
             for (int i = 0; i < Q; ++i) colv[i] = Jm[i*Q + j];

@@ -196,6 +196,26 @@ CASES = {
                                     lambda: B.make_config(3, flux=B.FS_AUSMPLUSUP, poly_rec=B.PR_LINEARLS,
                                                           limiter=B.LIM_VENKTN, jacobian="analytic", mach_inf=0.8,
                                                           res_factor=0.5), bcs_euler3d, False),
+    # a19 in Puvt / Pvt variables (ComputedFluxdPvt) and with the analytic diffusive Jacobian (NSFluxAndJacob), all three
+    # DiamondVolume control volumes + Corrected2D
+    "euler2d_pvt_ausmplusup_analytic": (lambda: meshgen.quad_channel(12, 9, triangles=True),
+                                        lambda: B.make_config(2, update_var=B.UV_PVT, flux=B.FS_AUSMPLUSUP,
+                                                              poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN,
+                                                              jacobian="analytic", mach_inf=0.5, **ns_kwargs()),
+                                        bcs_ns2d, True),
+    "ns2d_quad_ausmplusup_analytic": (lambda: meshgen.quad_channel(10, 8),
+                                      lambda: ns2d_cfg(flux=B.FS_AUSMPLUSUP, jacobian="analytic", mach_inf=0.35),
+                                      bcs_ns2d, True),
+    "ns2d_tri_ausmplusup_analytic_corrected": (lambda: meshgen.quad_channel(10, 8, triangles=True),
+                                               lambda: ns2d_cfg(flux=B.FS_AUSMPLUSUP, jacobian="analytic", mach_inf=0.35,
+                                                                derivative="corrected", res_factor=0.5),
+                                               bcs_ns2d, True),
+    "ns3d_hex_ausmplusup_analytic": (lambda: meshgen.hex_box(6, 5, 4),
+                                     lambda: ns3d_cfg(flux=B.FS_AUSMPLUSUP, jacobian="analytic", mach_inf=0.35),
+                                     bcs_ns3d, True),
+    "ns3d_tet_ausmplusup_analytic": (lambda: meshgen.tet_box(3, 3, 3),
+                                     lambda: ns3d_cfg(flux=B.FS_AUSMPLUSUP, jacobian="analytic", mach_inf=0.35,
+                                                      choice_a12=1), bcs_ns3d, True),
     # "RoeEntropyFix" (RoeEntropyFixFlux.cxx), both correction types
     "euler2d_roe_efix1": (lambda: meshgen.quad_channel(12, 9, triangles=True),
                           lambda: B.make_config(2, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, jacobian=True,
