@@ -15,7 +15,7 @@ MAXEQ = 9
 PM_EULER, PM_MHD3D_PROJECTION = 0, 1
 DV_DIAMOND, DV_CORRECTED = 0, 1
 UV_CONS, UV_PVT = 0, 1
-FS_ROE, FS_AUSMPLUS, FS_AUSMPLUSUP, FS_LAXFRIED, FS_HLL = 0, 1, 2, 3, 4
+FS_ROE, FS_AUSMPLUS, FS_AUSMPLUSUP, FS_LAXFRIED, FS_HLL, FS_ROESA = 0, 1, 2, 3, 4, 5
 PR_CONSTANT, PR_LINEARLS = 0, 1
 LIM_NONE, LIM_VENKTN, LIM_BARTHJESP, LIM_VENKTN_STRICT = 0, 1, 2, 3
 DIFF_NONE, DIFF_NS = 0, 1
@@ -47,6 +47,7 @@ class ConfigStruct(C.Structure):
         ("timeZeroDiag", C.c_int32*MAXEQ), ("timeAnalyticalMatrix", C.c_int32), ("timeUseGlobalDT", C.c_int32),
         ("renumber", C.c_int32), ("dt", C.c_double),
         ("venktnIsMFMHD", C.c_int32), ("psiMinEqual1", C.c_int32), ("strictCoeff", C.c_double),
+        ("roeSaOldStencil", C.c_int32), ("reservedPad", C.c_int32),
     ]
 
 
@@ -147,6 +148,7 @@ def make_config(dim, update_var=UV_CONS, flux=FS_ROE, poly_rec=PR_CONSTANT, limi
     c.venktnIsMFMHD = int(kw.get("is_mfmhd", 1 if limiter == LIM_VENKTN_STRICT else 0))
     c.psiMinEqual1 = int(kw.get("psi_min_equal_1", 0))
     c.strictCoeff = float(kw.get("strict_coeff", 1.0))
+    c.roeSaOldStencil = int(kw.get("roe_sa_old_stencil", 0))
     return c
 
 

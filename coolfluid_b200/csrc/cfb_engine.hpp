@@ -39,14 +39,16 @@ inline bool splitterSupported(const cfb200_config& c) {
     return (c.fluxSplitter == CFB200_FS_LAXFRIED || c.fluxSplitter == CFB200_FS_HLL) && c.updateVar == CFB200_UV_CONS &&
            c.diffusive == CFB200_DIFF_NONE;
   if (c.fluxSplitter == CFB200_FS_ROE) return c.entropyFixID >= 0 && c.entropyFixID <= 2;
+  if (c.fluxSplitter == CFB200_FS_ROESA) return c.entropyFixID >= 0 && c.entropyFixID <= 3;
   if (c.fluxSplitter == CFB200_FS_AUSMPLUS || c.fluxSplitter == CFB200_FS_AUSMPLUSUP)
     return c.choiceA12 >= 1 && c.choiceA12 <= 3 && (c.fluxSplitter == CFB200_FS_AUSMPLUS || c.machInf > 0.);
   if (c.fluxSplitter == CFB200_FS_LAXFRIED || c.fluxSplitter == CFB200_FS_HLL) return true;
   return false;
 }
-// kernel family of the splitter: 0 Roe, 1 AUSM+ / AUSM+up, 2 Lax-Friedrichs / HLL, 3 Roe with the entropy fix
+// kernel family of the splitter: 0 Roe, 1 AUSM+ / AUSM+up, 2 Lax-Friedrichs / HLL, 3 Roe with the entropy fix, 4 RoeSA
 inline int splitterFamily(const cfb200_config& c) {
   if (c.fluxSplitter == CFB200_FS_ROE) return (c.entropyFixID != 0) ? 3 : 0;
+  if (c.fluxSplitter == CFB200_FS_ROESA) return 4;
   return (c.fluxSplitter == CFB200_FS_LAXFRIED || c.fluxSplitter == CFB200_FS_HLL) ? 2 : 1;
 }
 
@@ -261,6 +263,35 @@ public:
         sp.push_back((int32_t)st.size());
       }
       d.bndStPtr = upload(sp); d.bndSt = upload(st);
+    }
+    d.saFace = nullptr;
+    if (cfg.fluxSplitter == CFB200_FS_ROESA) {
+      // RoeSAFlux::updateEtaPA (RoeSAFlux.cxx:146-190): per face and side, the faces of that cell which share a node with
+      // the face (every face of the cell with oldStencil); the face itself first.  Partition faces do not exist here: the
+      // two overlap layers keep them away from every face that has an updatable side.
+      constexpr int W = CFB_SA_WIDTH;
+      std::vector<int32_t> sa((size_t)2*W*nf, -1);
+      for (int f = 0; f < nf; ++f) {
+        const int32_t* fnB = m.faceNodes + m.faceNodePtr[f];
+        const int32_t* fnE = m.faceNodes + m.faceNodePtr[f+1];
+        for (int side = 0; side < 2; ++side) {
+          const int cell = side ? m.faceR[f] : m.faceL[f];
+          if (cell >= nc) continue;                         // ghost: RoeSAFlux.cxx:92-94
+          int n = 0;
+          sa[(size_t)(side*W + n++)*nf + f] = f;
+          for (int k = m.cellFacePtr[cell]; k < m.cellFacePtr[cell+1]; ++k) {
+            const int g = m.cellFaces[k];
+            if (g == f) continue;
+            bool take = cfg.roeSaOldStencil != 0;
+            for (const int32_t* a = m.faceNodes + m.faceNodePtr[g]; a != m.faceNodes + m.faceNodePtr[g+1] && !take; ++a)
+              take = std::find(fnB, fnE, *a) != fnE;
+            if (!take) continue;
+            if (n >= W) throw std::invalid_argument("RoeSA: a cell with more than 6 faces");
+            sa[(size_t)(side*W + n++)*nf + f] = g;
+          }
+        }
+      }
+      d.saFace = upload(sa);
     }
     d.bcWallRatio = nullptr;
     {
@@ -483,12 +514,14 @@ public:
       if (fam == 0) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 0, DV>{d, cfg}, d.nInner, faceShape);
       else if (fam == 1) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 1, DV>{d, cfg}, d.nInner, faceShape);
       else if (fam == 2) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 2, DV>{d, cfg}, d.nInner, faceShape);
+      else if (fam == 4) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 4, DV>{d, cfg}, d.nInner, faceShape);
       else bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 3, DV>{d, cfg}, d.nInner, faceShape);
       bk.launch("boundaryFaceJac", BoundaryFaceK<D, true, DV>{d, cfg}, d.nGhosts, 128);
     } else {
       if (fam == 0) bk.launch("innerFace", InnerFaceK<D, false, 0, DV>{d, cfg}, d.nInner, 128);
       else if (fam == 1) bk.launch("innerFace", InnerFaceK<D, false, 1, DV>{d, cfg}, d.nInner, 128);
       else if (fam == 2) bk.launch("innerFace", InnerFaceK<D, false, 2, DV>{d, cfg}, d.nInner, 128);
+      else if (fam == 4) bk.launch("innerFace", InnerFaceK<D, false, 4, DV>{d, cfg}, d.nInner, 128);
       else bk.launch("innerFace", InnerFaceK<D, false, 3, DV>{d, cfg}, d.nInner, 128);
       bk.launch("boundaryFace", BoundaryFaceK<D, false, DV>{d, cfg}, d.nGhosts, 128);
     }

@@ -16,6 +16,64 @@ template <int N> CFB_HD double pick(const double* a, int i) {
 }
 
 // Per-face working set shared by the flux and the Jacobian part.
+// "RoeSA" (RoeSAFlux.cxx:66-197): Sanders' H-correction.  etaSA = half the largest jump between the eigenvalues
+// (un, .., un + a, un - a) of the reconstructed L (R) state and those of the CELL (or ghost) state across every face of the
+// L (R) cell that shares a node with the face (all its faces with "oldStencil"), each taken with that face's own stored
+// normal.  Dev::saFace lists those faces per face and side (host-built at set_mesh; entry 0 is the face itself, whose
+// "state across" is the other cell of the face: the one entry a finite-difference perturbation of that cell changes,
+// because the reference perturbs the State object in place, FVMCC_ComputeRhsJacob.cxx:321-365).  Boundary faces use
+// the left cell only (RoeSAFlux.cxx:92-94).  The triples live in local memory (dynamic index).
+template <int D>
+struct SaWork {
+  static constexpr int Q = D + 2;
+  static constexpr int W = CFB_SA_WIDTH;
+  typedef Phys<D> P;
+  double ev[2][W][3];
+  int cnt[2];
+  static CFB_HD void triple(const Cfg& c, const double* u, const double* nrm, double* t) {
+    PData pd;
+    P::physicalData(c, u, pd);                       // updateVarSet->computePhysicalData(*rs, _dataRightState)
+    const double un = P::vn(pd, nrm);                // Euler{2,3}DVarSet::computeEigenValues
+    t[0] = un; t[1] = un + pd.A; t[2] = un - pd.A;
+  }
+  CFB_HD void load(const Dev& d, const Cfg& c, int f, int L, int R, bool isB) {
+    cnt[0] = 0; cnt[1] = 0;
+    const int nSides = isB ? 1 : 2;
+    for (int side = 0; side < nSides; ++side) {
+      const int cell = side ? R : L;
+      for (int k = 0; k < W; ++k) {
+        const int nf = d.saFace[(size_t)(side*W + k)*d.nFaces + f];
+        if (nf < 0) break;
+        const int l = d.faceL[nf];
+        const int rs = (l == cell) ? d.faceR[nf] : l;
+        const double invArea = ddiv(1., d.areas[nf]);
+        double nrm[3] = {0., 0., 0.}, u[Q];
+#pragma unroll
+        for (int i = 0; i < D; ++i) nrm[i] = d.normals[(size_t)i*d.nFaces + nf]*invArea;
+#pragma unroll
+        for (int v = 0; v < Q; ++v) u[v] = d.U[(size_t)v*d.nStates + rs];
+        triple(c, u, nrm, ev[side][k]);
+        cnt[side] = k + 1;
+      }
+    }
+  }
+  // the state across the face itself as seen from the cell of `side` (a perturbed cell / ghost state)
+  CFB_HD void setAcross(const Cfg& c, int side, const double* u, const double* n) { triple(c, u, n, ev[side][0]); }
+  CFB_HD double eta(double unL, double aL, double unR, double aR) const {
+    double m = 0.0;
+    for (int side = 0; side < 2; ++side) {
+      const double un = side ? unR : unL, a = side ? aR : aL;
+      const double e1 = un + a, e2 = un - a;
+      for (int k = 0; k < cnt[side]; ++k) {
+        m = dmax(m, fabs(ev[side][k][0] - un));
+        m = dmax(m, fabs(ev[side][k][1] - e1));
+        m = dmax(m, fabs(ev[side][k][2] - e2));
+      }
+    }
+    return m*0.5;
+  }
+};
+
 template <int D>
 struct FaceWork {
   static constexpr int Q = D + 2;
@@ -225,8 +283,9 @@ struct FaceWork {
   // Base (unperturbed) evaluation: a11/a14/a17.  Returns the face-integrated flux (convective - diffusive) and the
   // update coefficients (RoeFlux.cxx:165-185, NSFlux.ci:127-152).
   CFB_HD void baseFlux(const Dev& d, const Cfg& c, const double* sL, const double* sR, const typename P::Side& a,
-                       const typename P::Side& b, bool hasDiff, double* flux, double& ucL, double& ucR, double& ucD) {
-    if (!P::numFlux(c, a, b, n, flux)) {
+                       const typename P::Side& b, bool hasDiff, double* flux, double& ucL, double& ucR, double& ucD,
+                       double etaSA = 0.) {
+    if (!P::numFlux(c, a, b, n, flux, etaSA)) {
       *d.status = CFB200_ERR_BAD_VALUE;
 #pragma unroll
       for (int v = 0; v < Q; ++v) flux[v] = 0.;
@@ -310,7 +369,9 @@ struct FaceWork {
     const double rf = c.resFactor;
     // loop-carried state parked in the staging area (shared memory) instead of registers: the unperturbed other side
     // (s z f) and the base flux; without a staging area (RHS-only kernel: one evaluation) they live in locals
-    constexpr int NFX = (FS == 3) ? 3*Q + 2 : 3*Q;       // doubles of the parked fixed side
+    constexpr int NFX = (FS == 3 || FS == 4) ? 3*Q + 2 : 3*Q;       // doubles of the parked fixed side
+    SaWork<D> sa;                                        // FS == 4 ("RoeSA") only
+    if constexpr (FS == 4) sa.load(d, c, f, L, R, false);
     double local[NFX + Q];
     double* fx = jac ? stg + (size_t)2*Q*Q*stride : local;
     const int fs = jac ? stride : 1;
@@ -324,12 +385,13 @@ struct FaceWork {
         double vF[Q];
 #pragma unroll
         for (int v = 0; v < Q; ++v) vF[v] = side ? vL[v] : vR[v];
-        if constexpr (FS == 0 || FS == 3) {
+        if constexpr (FS == 0 || FS == 3 || FS == 4) {
           typename P::SideLite fixed;
           P::sideLite(c, vF, n, fixed);              // the unperturbed other side
 #pragma unroll
           for (int v = 0; v < Q; ++v) { fx[(size_t)v*fs] = fixed.s[v]; fx[(size_t)(Q + v)*fs] = fixed.z[v]; fx[(size_t)(2*Q + v)*fs] = fixed.f[v]; }
-          if constexpr (FS == 3) { fx[(size_t)(3*Q)*fs] = fixed.un; fx[(size_t)(3*Q + 1)*fs] = fixed.A; }
+          if constexpr (FS == 3 || FS == 4) { fx[(size_t)(3*Q)*fs] = fixed.un; fx[(size_t)(3*Q + 1)*fs] = fixed.A; }
+          if constexpr (FS == 4) { if (it == Q) sa.setAcross(c, 1, sL, n); }   // the L cell is back to its own value
         } else if constexpr (FS == 2) {
           typename P::CSide fixed;
           P::cside(c, vF, n, fixed);
@@ -357,10 +419,23 @@ struct FaceWork {
 #pragma unroll
       for (int v = 0; v < Q; ++v) { const double base = side ? vR[v] : vL[v]; vp[v] = (v == iVar) ? pvr : base; }
       double pf[Q];
-      if constexpr (FS == 0 || FS == 3) {
+      if constexpr (FS == 0 || FS == 3 || FS == 4) {
         typename P::SideLite pert;
         P::sideLite(c, vp, n, pert);
-        if (!P::template roeOriented<FS == 3>(c, pert, fx, fs, side == 0, n, pf)) {
+        double etaSA = 0.;
+        if constexpr (FS == 4) {
+          if (iVar >= 0) {
+            // the perturbed CELL state is what the other cell sees across this face
+            double sp[Q];
+#pragma unroll
+            for (int v = 0; v < Q; ++v) { const double base = side ? sR[v] : sL[v]; sp[v] = (v == iVar) ? pv : base; }
+            sa.setAcross(c, 1 - side, sp, n);
+          }
+          const double fun = fx[(size_t)(3*Q)*fs], fa = fx[(size_t)(3*Q + 1)*fs];
+          etaSA = side ? sa.eta(fun, fa, pert.un, pert.A) : sa.eta(pert.un, pert.A, fun, fa);
+          if (!(fabs(etaSA) > 0.)) *d.status = CFB200_ERR_BAD_VALUE;      // assert(std::abs(etaSA) > 0.), RoeSAFlux.cxx:97
+        }
+        if (!P::template roeOriented<(FS == 3) ? 1 : ((FS == 4) ? 2 : 0)>(c, pert, fx, fs, side == 0, n, pf, etaSA)) {
           *d.status = CFB200_ERR_BAD_VALUE;
 #pragma unroll
           for (int v = 0; v < Q; ++v) pf[v] = 0.;
@@ -769,7 +844,7 @@ struct InnerFaceK {   // idx over interior faces; FS = 0 Roe, 1 AUSM+ / AUSM+up,
   static constexpr int NOUT = 2*Q*Q;    // per-thread staging (shared memory, entry k at stg[k*stride]): block(R,L) | block(L,R)
   static constexpr bool PIPE = JAC && (FS == 0 || FS == 3) && UV >= 0;
   // ... | fixed side s z f (un a) | base flux (loop-carried state of the FD loop); PIPE: FaceWork::RP_STAGE
-  static constexpr int STAGE = PIPE ? FaceWork<D>::RP_STAGE(FS == 3) : NOUT + 4*Q + ((FS == 3) ? 2 : 0);
+  static constexpr int STAGE = PIPE ? FaceWork<D>::RP_STAGE(FS == 3) : NOUT + 4*Q + ((FS == 3 || FS == 4) ? 2 : 0);
   Dev d; Cfg c;
   CFB_HD void operator()(int f) const { run(f, nullptr, 0); }
   CFB_HD double* out() const { return d.bsrVal; }
@@ -1046,12 +1121,19 @@ struct BoundaryFaceK {   // idx over boundary faces; DV = 0 DiamondVolume, 1 Cor
 #pragma unroll
     for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + L]; sR[v] = d.U[(size_t)v*d.nStates + R]; }
     w.reconstruct(c, sL, sR, vL, vR);
+    const bool roeSA = (c.fluxSplitter == CFB200_FS_ROESA);
+    SaWork<D> sa;
+    if (roeSA) sa.load(d, c, f, L, R, true);
     {
       typename P::Side a, b;
       P::side(c, vL, w.n, a);
       P::side(c, vR, w.n, b);
-      double ucL, ucR, ucD;
-      w.baseFlux(d, c, sL, sR, a, b, hasDiff && DV == 0, flux, ucL, ucR, ucD);
+      double ucL, ucR, ucD, etaSA = 0.;
+      if (roeSA) {
+        etaSA = sa.eta(P::vn(a.pd, w.n), a.pd.A, 0., 0.);
+        if (!(fabs(etaSA) > 0.)) *d.status = CFB200_ERR_BAD_VALUE;
+      }
+      w.baseFlux(d, c, sL, sR, a, b, hasDiff && DV == 0, flux, ucL, ucR, ucD, etaSA);
       d.ucL[f] = ucL; d.ucR[f] = ucR; d.ucD[f] = ucD;
     }
     CorrectedWork<D> cw;
@@ -1084,8 +1166,13 @@ struct BoundaryFaceK {   // idx over boundary faces; DV = 0 DiamondVolume, 1 Cor
       typename P::Side a, b;
       P::side(c, vL, w.n, a);
       P::side(c, vR, w.n, b);
-      double pf[Q];
-      if (!P::numFlux(c, a, b, w.n, pf)) {
+      double pf[Q], etaSA = 0.;
+      if (roeSA) {
+        sa.setAcross(c, 0, sRp, w.n);             // the ghost state rebuilt from the perturbed inner state
+        etaSA = sa.eta(P::vn(a.pd, w.n), a.pd.A, 0., 0.);
+        if (!(fabs(etaSA) > 0.)) *d.status = CFB200_ERR_BAD_VALUE;
+      }
+      if (!P::numFlux(c, a, b, w.n, pf, etaSA)) {
         *d.status = CFB200_ERR_BAD_VALUE;
 #pragma unroll
         for (int v = 0; v < Q; ++v) pf[v] = 0.;

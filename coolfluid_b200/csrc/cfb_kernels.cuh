@@ -11,6 +11,7 @@
 //     gathered in face order (FVMCC_ComputeRhsJacob.cxx:347-365: row R receives -1 x what row L receives);
 //   * all reals FP64, SoA by component so that one-thread-per-item accesses coalesce.
 #pragma once
+#define CFB_SA_WIDTH 6     /* faces per cell listed for RoeSA: hexahedra, prisms, pyramids, tetrahedra, quads, triangles */
 #include "cfb_math.cuh"
 
 namespace cfb {
@@ -36,6 +37,7 @@ struct Dev {
   const uint8_t* bcFaceFlag;  // [nGhosts] 1 where bcFaceVal replaces BCond::value
   const double* bcWallRatio;  // [nGhosts] (inner-ghost)/(inner-wall) distance ratio of FVMCC_BaseBC::computeGhostPosition, or null
   const int* bndStPtr; const int* bndSt;           // Corrected2D/3D: gradient stencil of each boundary face (CSR over ghosts)
+  const int* saFace;          // "RoeSA": [2*CFB_SA_WIDTH][nFaces] faces of the L / R cell entering etaSA (-1 = none), or null
   const uint8_t* updatable;
   const uint8_t* cellActive;  // cell touches at least one face with an updatable side
   const BCond* bcs;

@@ -32,7 +32,10 @@ enum cfb200_flux_splitter { CFB200_FS_ROE = 0 /* "Roe" plugins/FiniteVolume/RoeF
                             CFB200_FS_AUSMPLUS = 1 /* "AUSMPlus2D/3D" FiniteVolumeNavierStokes/AUSMPlusFlux.ci */,
                             CFB200_FS_AUSMPLUSUP = 2 /* "AUSMPlusUp2D/3D" AUSMPlusUpFlux.ci:50-135 */,
                             CFB200_FS_LAXFRIED = 3 /* "LaxFried" plugins/FiniteVolume/LaxFriedFlux.cxx:79-190 */,
-                            CFB200_FS_HLL = 4 /* "HLL" plugins/FiniteVolume/HLLFlux.cxx:73-150 */ };
+                            CFB200_FS_HLL = 4 /* "HLL" plugins/FiniteVolume/HLLFlux.cxx:73-150 */,
+                            CFB200_FS_ROESA = 5 /* "RoeSA" plugins/FiniteVolume/RoeSAFlux.cxx:66-197: Roe with Sanders'
+                                                   H-correction; entropyFixID then is RoeSA's own option (0 | 3: |ev| + eta,
+                                                   1: Harten-like with eta, 2: max(|ev|, eta)) */ };
 enum cfb200_poly_rec { CFB200_PR_CONSTANT = 0 /* "Constant" ConstantPolyRec.cxx */,
                        CFB200_PR_LINEARLS = 1 /* "LinearLS2D"/"LinearLS3D" LeastSquareP1PolyRec{2,3}D.cxx */ };
 enum cfb200_limiter { CFB200_LIM_NONE = 0, CFB200_LIM_VENKTN = 1 /* "Venktn2D"/"Venktn3D" */,
@@ -145,6 +148,9 @@ typedef struct cfb200_config {
   int32_t venktnIsMFMHD;
   int32_t psiMinEqual1;
   double strictCoeff;
+  int32_t roeSaOldStencil;            /* RoeSA option "oldStencil" (RoeSAFlux.cxx:44-45,171): every face of the two cells,
+                                       * not only those sharing a node with the face */
+  int32_t reservedPad;
 } cfb200_config;
 
 /* Flat mesh data = the contents of the reference's sockets and connectivity tables (SURVEY.md §8b "Data ownership").

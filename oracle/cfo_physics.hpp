@@ -393,8 +393,9 @@ struct Phys {
   // is evaluated lazily by MatExprT.hh:255-390 / ExprT.hh as
   //   result_i = 0.5*(sumFlux_i - sum_k [ (k * sum_m R(i,m)*(|ev_m|*L(m,k))) * (sR_k - sL_k) ])
   // (pinned against the reference headers by oracle/ref_mathtools.cpp).
+  // etaSA: RoeSA only (RoeSAFlux.cxx:66-120), the H-correction the solver gathered from the neighbouring faces
   static bool roeFlux(const Config& c, const double* uL, const double* uR,
-                      const PData& pL, const PData& pR, const double* n, double* result) {
+                      const PData& pL, const PData& pR, const double* n, double* result, double etaSA = 0.) {
     double sL[Q], sR[Q], zL[Q], zR[Q];
     toCons(c, uL, sL); toCons(c, uR, sR);
     consToRoe(c, sL, zL); consToRoe(c, sR, zR);
@@ -403,7 +404,18 @@ struct Phys {
     double Rm[Q*Q], Lm[Q*Q], ev[Q], aev[Q];
     eigen(c, lin, n, Rm, Lm, ev);
     for (int i = 0; i < Q; ++i) aev[i] = std::abs(ev[i]);     // RoeFlux.cxx:200-203
-    if (c.entropyFixID != 0) {
+    if (c.fluxSplitter == FS_ROESA) {
+      // RoeSAFlux::setAbsEigenValues, RoeSAFlux.cxx:100-119
+      for (int i = 0; i < Q; ++i) {
+        const double absEv = std::abs(ev[i]);
+        switch (c.entropyFixID) {
+        case 1: aev[i] = (absEv >= 2.*etaSA) ? absEv : 0.25*absEv*absEv/etaSA + etaSA; break;
+        case 2: aev[i] = std::max(absEv, etaSA); break;
+        case 3: aev[i] = absEv + etaSA; break;
+        default: aev[i] = absEv + etaSA; break;
+        }
+      }
+    } else if (c.entropyFixID != 0) {
       // RoeEntropyFixFlux::setAbsEigenValues (RoeEntropyFixFlux.cxx:57-90) + computeLambdaCorr (RoeEntropyFixFlux.hh:49-56)
       double evL[Q], evR[Q];
       eigenValues(pL, n, evL);
@@ -1248,7 +1260,8 @@ struct MhdPhys {
     return true;
   }
   // not available for this model (the configuration is rejected before the solver runs)
-  static bool roeFlux(const Config&, const double*, const double*, const MhdData&, const MhdData&, const double*, double*) { return false; }
+  static bool roeFlux(const Config&, const double*, const double*, const MhdData&, const MhdData&, const double*, double*, double = 0.) { return false; }
+  static void eigenValues(const MhdData&, const double*, double*) {}     // RoeSA is not offered on MHD3DProjection
   static bool ausmFlux(const Config&, const MhdData&, const MhdData&, const double*, double*) { return false; }
   static void ausmPlusUpJacobCons(const Config&, const MhdData&, const MhdData&, const double*, int, double*) {}
   static void ausmPlusUpJacobPvt(const Config&, const MhdData&, const MhdData&, const double*, int, double*) {}

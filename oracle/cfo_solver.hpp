@@ -344,6 +344,7 @@ public:
   // ---- reconstruction (a8) -------------------------------------------------
   struct FaceCtx {
     int f, L, R; bool isB;
+    const double* U;      // the state array of the evaluation (RoeSA reads the neighbours' states)
     double xq[3];
     double n[3];          // unit normal (FVMCC_ComputeRHS.cxx:518-534)
     double area;
@@ -415,6 +416,35 @@ public:
     v[iVar] = U[(size_t)st*Q + iVar] + lValue*gc;
   }
 
+  // RoeSAFlux::updateEtaPA (RoeSAFlux.cxx:146-190).  No partition faces in a single domain (`_isPartitionFace` all false).
+  template <class PD>
+  void updateEtaPAImpl(const FaceCtx& x, int cell, const double* eValues, double& etaSA, PD*) {
+    const int nbC = mesh.faceNodePtr[x.f+1] - mesh.faceNodePtr[x.f];
+    const int32_t* fnC = &mesh.faceNodes[mesh.faceNodePtr[x.f]];
+    for (int k = mesh.cellFacePtr[cell]; k < mesh.cellFacePtr[cell+1]; ++k) {
+      const int nf = mesh.cellFaces[k];
+      bool shares = false;                                 // GeometricEntity::sharesNodesWith
+      const int32_t* fnN = &mesh.faceNodes[mesh.faceNodePtr[nf]];
+      const int nbN = mesh.faceNodePtr[nf+1] - mesh.faceNodePtr[nf];
+      for (int a = 0; a < nbN && !shares; ++a)
+        for (int b = 0; b < nbC; ++b) if (fnN[a] == fnC[b]) { shares = true; break; }
+      if ((shares && !cfg.roeSaOldStencil) || cfg.roeSaOldStencil) {
+        const int rs = (mesh.faceL[nf] == cell) ? mesh.faceR[nf] : mesh.faceL[nf];
+        const double invArea = 1./mesh.areas[nf];
+        double nrm[3] = {0., 0., 0.};
+        for (int i = 0; i < D; ++i) nrm[i] = mesh.normals[(size_t)nf*D + i]*invArea;
+        PD dataR;
+        P::computePhysicalData(cfg, &x.U[(size_t)rs*Q], dataR);
+        double tmpEv[Q];
+        P::eigenValues(dataR, nrm, tmpEv);
+        for (int i = 0; i < Q; ++i) etaSA = std::max(etaSA, std::abs(tmpEv[i] - eValues[i]));
+      }
+    }
+  }
+  void updateEtaPA(const FaceCtx& x, int cell, const double* eValues, double& etaSA) {
+    updateEtaPAImpl(x, cell, eValues, etaSA, (PData*)nullptr);
+  }
+
   // ---- convective flux incl. face integration (FVMCC_FluxSplitter.hh:79-83) and, when
   // !isPerturb, the update coefficient (RoeFlux.cxx:165-185)
   bool convectiveFlux(FaceCtx& x, bool isPerturb, Outputs& o, double* flux) {
@@ -423,6 +453,19 @@ public:
     for (int i = 0; i < Q; ++i) flux[i] = 0.;
     if (cfg.fluxSplitter == FS_ROE) {
       if (!P::roeFlux(cfg, x.vL, x.vR, x.pL, x.pR, x.n, flux)) { o.status = 1; return false; }
+    } else if (cfg.fluxSplitter == FS_ROESA) {
+      // RoeSAFlux::setAbsEigenValues (RoeSAFlux.cxx:66-98): eigenvalues of the two reconstructed states against those of
+      // the states across the faces of the left and of the right cell; the states are read where they live (x.U: a
+      // perturbed cell state is seen through the current face's own entry, as in the reference)
+      double evL[Q], evR[Q];
+      P::eigenValues(x.pL, x.n, evL);
+      P::eigenValues(x.pR, x.n, evR);
+      double etaSA = 0.0;
+      updateEtaPA(x, x.L, evL, etaSA);
+      if (!x.isB) updateEtaPA(x, x.R, evR, etaSA);
+      etaSA *= 0.5;
+      if (!(std::abs(etaSA) > 0.)) { o.status = 1; return false; }     // assert(std::abs(etaSA) > 0.), :97
+      if (!P::roeFlux(cfg, x.vL, x.vR, x.pL, x.pR, x.n, flux, etaSA)) { o.status = 1; return false; }
     } else if (cfg.fluxSplitter == FS_LAXFRIED || cfg.fluxSplitter == FS_HLL) {
       // update coefficient (LaxFriedFlux.cxx:120-188, HLLFlux.cxx:135-150): _leftEv.max() == un + a, as Roe's
       P::centredFlux(cfg, x.vL, x.vR, x.pL, x.pR, x.n, flux);
@@ -774,7 +817,7 @@ public:
     FaceCtx x;
     double flux[Q], dFlux[Q], pertFlux[Q], fluxDiff[Q];
     for (int f = 0; f < mesh.nFaces; ++f) {
-      x.f = f; x.L = mesh.faceL[f]; x.R = mesh.faceR[f]; x.isB = (x.R >= nc);
+      x.f = f; x.L = mesh.faceL[f]; x.R = mesh.faceR[f]; x.isB = (x.R >= nc); x.U = U;
       const bool upL = mesh.updatable[x.L];
       const bool upR = (!x.isB) && mesh.updatable[x.R];
       if (!(upL || upR)) continue;                     // FVMCC_ComputeRHS.cxx:212-213

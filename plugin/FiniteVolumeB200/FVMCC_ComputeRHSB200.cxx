@@ -156,14 +156,17 @@ void FVMCC_ComputeRHSB200::fillConfig(cfb200_config& c)
   for (CFuint i = 0; i < nbEqs; ++i) { c.refValues[i] = refValues[i]; c.magnitudeValues[i] = refValues[i]; }
   c.fdTol = 10e-7;                                         // NumericalJacobian.cxx:31 (no option, no accessor)
 
-  // ---- flux splitter: CellCenterFVM.Data.FluxSplitter = Roe | RoeEntropyFix | AUSMPlus{2,3}D | AUSMPlusUp{2,3}D | LaxFried | HLL
+  // ---- flux splitter: CellCenterFVM.Data.FluxSplitter = Roe | RoeEntropyFix | RoeSA | AUSMPlus{2,3}D | AUSMPlusUp{2,3}D | LaxFried | HLL
   FluxSplitter<CellCenterFVMData>& fsp = *md.getFluxSplitter();
   const std::string fs = fsp.getName();
   c.fluxSplitter = (fs.find("AUSMPlusUp") == 0) ? CFB200_FS_AUSMPLUSUP : (fs.find("AUSMPlus") == 0) ? CFB200_FS_AUSMPLUS :
                    (fs == "LaxFried") ? CFB200_FS_LAXFRIED : (fs == "HLL") ? CFB200_FS_HLL :
-                   (fs == "Roe" || fs == "RoeEntropyFix") ? CFB200_FS_ROE : -1;      // -1: cfb200_create -> UNSUPPORTED
+                   (fs == "Roe" || fs == "RoeEntropyFix") ? CFB200_FS_ROE : (fs == "RoeSA") ? CFB200_FS_ROESA :
+                   -1;                                                               // -1: cfb200_create -> UNSUPPORTED
   c.diffRedCoeff = optReal(fsp, "DiffCoeff", 1.0);         // RoeFlux.cxx:34,62 / LaxFriedFlux.cxx:32
-  c.entropyFixID = (fs == "RoeEntropyFix") ? optInt(fsp, "entropyFixID", 1) : 0;     // RoeEntropyFixFlux.cxx:35,49
+  c.entropyFixID = (fs == "RoeEntropyFix") ? optInt(fsp, "entropyFixID", 1) :        // RoeEntropyFixFlux.cxx:35,49
+                   (fs == "RoeSA") ? optInt(fsp, "entropyFixID", 0) : 0;             // RoeSAFlux.cxx:41-42
+  c.roeSaOldStencil = (fs == "RoeSA") ? optInt(fsp, "oldStencil", 0) : 0;            // RoeSAFlux.cxx:44-45
   c.choiceA12 = optInt(fsp, "choiceA12", 1);               // AUSMFlux.ci:55,73
   c.coeffSigmoid = optReal(fsp, "coeffSigmoid", 1e-8);     // AUSMFlux.ci:64,84
   c.ausmBeta = optReal(fsp, "beta", 1./8.);                // AUSMPlusFlux.ci:38 / AUSMPlusUpFlux.ci:58
@@ -186,6 +189,7 @@ void FVMCC_ComputeRHSB200::fillConfig(cfb200_config& c)
   Limiter<CellCenterFVMData>& limr = *md.getLimiter();
   const std::string lim = limr.getName();
   c.limiter = (lim == "Venktn2D" || lim == "Venktn3D") ? CFB200_LIM_VENKTN : (lim == "BarthJesp") ? CFB200_LIM_BARTHJESP :
+              (lim == "Venktn3DStrict") ? CFB200_LIM_VENKTN_STRICT :
               (lim == "Null" || c.polyRec == CFB200_PR_CONSTANT) ? CFB200_LIM_NONE : -1;
   c.coeffEps = optReal(limr, "coeffEps", 1.0);             // Venktn2D.cxx:34,58
   c.length = optReal(limr, "length", 1.0);                 // Venktn2D.cxx:36,62
@@ -194,7 +198,9 @@ void FVMCC_ComputeRHSB200::fillConfig(cfb200_config& c)
     const std::vector<CFreal> mv = optVec(limr, "magnitudeValues");              // Venktn2D.cxx:32,96-106: default = refValues
     if (mv.size() == nbEqs) for (CFuint i = 0; i < nbEqs; ++i) c.magnitudeValues[i] = mv[i];
   }
-  if (optInt(limr, "isMFMHD", 0)) c.limiter = -1;          // Venktn3D.cxx:125-156 alternative formula: not provided
+  c.venktnIsMFMHD = (c.limiter == CFB200_LIM_VENKTN_STRICT) ? 1 : optInt(limr, "isMFMHD", 0);   // Venktn3D.cxx:125-156
+  c.strictCoeff = optReal(limr, "strictCoeff", 1.0);       // Venktn3DStrict.cxx:31,44
+  c.psiMinEqual1 = optInt(limr, "psiMinEqual1", 0);        // Venktn3DStrict.cxx:33,47
 
   // ---- diffusive flux
   c.diffusive = md.getDiffusiveFluxComputer()->isNull() ? CFB200_DIFF_NONE : CFB200_DIFF_NS;

@@ -221,6 +221,20 @@ CASES = {
                           lambda: B.make_config(2, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, jacobian=True,
                                                 entropy_fix_id=1), bcs_euler2d, False),
     "ns3d_hex_roe_efix2": (lambda: meshgen.hex_box(5, 4, 4), lambda: ns3d_cfg(entropy_fix_id=2), bcs_ns3d, True),
+    # "RoeSA" (RoeSAFlux.cxx): Sanders' H-correction over the faces of the two cells, all four entropyFixID forms, both
+    # stencils; the cylinder case of the reference (cyl_Pg_M15_FVM_1st2nd.CFcase:104) is Euler2D Puvt + RoeSA
+    "euler2d_puvt_roesa_quad": (lambda: meshgen.quad_channel(12, 9),
+                                lambda: B.make_config(2, update_var=B.UV_PVT, flux=B.FS_ROESA, poly_rec=B.PR_LINEARLS,
+                                                      limiter=B.LIM_VENKTN, jacobian=True, **ns_kwargs()), bcs_ns2d, True),
+    "euler2d_roesa_tri_fix1": (lambda: meshgen.quad_channel(12, 9, triangles=True),
+                               lambda: B.make_config(2, flux=B.FS_ROESA, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN,
+                                                     jacobian=True, entropy_fix_id=1), bcs_euler2d, False),
+    "euler2d_roesa_1st_oldstencil": (lambda: meshgen.quad_channel(12, 9),
+                                     lambda: B.make_config(2, flux=B.FS_ROESA, jacobian=True, entropy_fix_id=3,
+                                                           roe_sa_old_stencil=1), bcs_euler2d, False),
+    "ns3d_hex_roesa_fix2": (lambda: meshgen.hex_box(5, 4, 4), lambda: ns3d_cfg(flux=B.FS_ROESA, entropy_fix_id=2),
+                            bcs_ns3d, True),
+    "ns3d_tet_roesa": (lambda: meshgen.tet_box(3, 3, 3), lambda: ns3d_cfg(flux=B.FS_ROESA), bcs_ns3d, True),
     # a13 (Euler part): Lax-Friedrichs and HLL
     "euler2d_laxfried_1st": (lambda: meshgen.quad_channel(12, 9),
                              lambda: B.make_config(2, flux=B.FS_LAXFRIED, jacobian=True), bcs_euler2d, False),

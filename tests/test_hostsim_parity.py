@@ -34,7 +34,8 @@ def test_partition_overlap_rows(oracle, hostsim_lib):
     def upd(fm):
         x = fm.centres.reshape(-1, fm.dim)[:fm.nCells, 0]
         return (x < 0.6).astype(np.uint8)
-    for name in ("ns3d_hex", "euler2d_2nd_tri_fullstencil", "euler2d_ausmplusup_analytic", "mhd3d_hex_hll"):
+    for name in ("ns3d_hex", "euler2d_2nd_tri_fullstencil", "euler2d_ausmplusup_analytic", "mhd3d_hex_hll",
+                 "ns3d_hex_roesa_fix2", "ns2d_quad_ausmplusup_analytic"):
         out = cases.run_case(name, oracle, _engine_factory(hostsim_lib), updatable=upd)
         _check(out)
         fm = out["_fm"]
