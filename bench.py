@@ -79,6 +79,9 @@ def flagship(n, workload="ns3d"):
         return em, cases.ns3d_cfg(derivative="corrected"), cases.bcs_ns3d()
     if workload == "ns3d_tet":
         return meshgen.tet_box(n, n, n), cases.ns3d_cfg(), cases.bcs_ns3d()
+    if workload == "ns3d_roesa":
+        from coolfluid_b200 import config as B
+        return em, cases.ns3d_cfg(flux=B.FS_ROESA), cases.bcs_ns3d()
     if workload == "ns3d_ausm_analytic":
         from coolfluid_b200 import config as B
         return em, cases.ns3d_cfg(flux=B.FS_AUSMPLUSUP, jacobian="analytic", mach_inf=0.35), cases.bcs_ns3d()
@@ -102,6 +105,10 @@ WORKLOADS = {
                            "NSFluxAndJacob): 3D Navier-Stokes, %d^3 = %d jittered hex cells per GPU, Pvt variables, AUSM+up "
                            "(machInf 0.35) + viscous (DiamondVolume3D) flux, LinearLS3D + Venktn3D, block Jacobian into device "
                            "BSR, pseudo-steady time term", True, 744, 1400),
+    "ns3d_roesa": ("configs[2] with FluxSplitter = RoeSA (Sanders' H-correction over the faces of the two cells, the "
+                   "splitter of the reference's cylinder case): 3D Navier-Stokes, %d^3 = %d jittered hex cells per GPU, Pvt "
+                   "variables, RoeSA + viscous (DiamondVolume3D) flux, LinearLS3D + Venktn3D, NumJacob into device BSR, "
+                   "pseudo-steady time term", True, 744, 1400),
     "ns3d_tet": ("configs[2] on tetrahedra: 3D Navier-Stokes, %d^3 boxes split into 6 tetrahedra each (Kuhn), %d cells "
                  "per GPU, Pvt variables, Roe + viscous (DiamondVolume3D) flux, LinearLS3D + Venktn3D (stencils of ~60 vertex "
                  "neighbours), NumJacob into device BSR, pseudo-steady time term", True, 763, 1000),
