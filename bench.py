@@ -41,6 +41,15 @@ A_RHS, A_JAC = 744, 1400
 INNER_FACE_JAC_BYTES = 104 + 75 + 21 + 400 + 40 + 24
 
 
+# FP64 roofline of the dominant kernel: thread-level FP64 instructions per interior face of the
+# finite-difference Jacobian kernel from the committed ncu source-page capture
+# (profiles/r02_ncu_innerface_pipe1_source_lines.md: DMUL 966 M + DADD 739 M + DFMA 282 M warp instructions per launch
+# at 6.24 M faces), and the measured no-FMA FP64 issue peak of tools/microbench/fp64_lat.cu
+# (profiles/r02_fp64_microbench.txt: DADD 567.7 G warp-instr/s over 148 SMs)
+INNER_FACE_JAC_FP64_PER_FACE = 10190.0
+FP64_PEAK_WARP_INSTR = 567.7e9
+
+
 def measured_traffic(kernel, items):
     """dram__bytes_read.sum + dram__bytes_write.sum of one launch from the committed `ncu --set full` capture
     (profiles/traffic.json: bytes per item measured at the capture's size), scaled to this launch's item count."""
@@ -581,6 +590,15 @@ def main():
                          "frac": achieved/peak, "traffic": traffic, "traffic_source": traffic_src,
                          "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": int(algo), "avg_launch_ms": kavg[top]},
+            # the same kernel against the pipe that actually bounds it: FP64 instructions per launch / time / measured peak
+            **({"roofline_fp64": {
+                "kernel": top, "bound": "fp64 issue (no FMA: reference operation order)",
+                "achieved": fm.nInner*INNER_FACE_JAC_FP64_PER_FACE/32./(kavg[top]*1e-3)/1e9,
+                "peak": FP64_PEAK_WARP_INSTR/1e9, "unit": "G warp-instr/s",
+                "frac": fm.nInner*INNER_FACE_JAC_FP64_PER_FACE/32./(kavg[top]*1e-3)/FP64_PEAK_WARP_INSTR,
+                "instr_source": "profiles/r02_ncu_innerface_pipe1_source_lines.md",
+                "peak_source": "profiles/r02_fp64_microbench.txt"}}
+               if (top == "innerFaceJac" and args.workload == "ns3d") else {}),
             "step_roofline": {"bytes_per_cell": a_rhs + a_jac, "achieved_gbs": (a_rhs + a_jac)*value/world/1e9,
                               "frac_of_hbm_peak": (a_rhs + a_jac)*value/world/1e9/peak},
             "clocks": clocks, "status": int(status),

@@ -47,7 +47,8 @@ class ConfigStruct(C.Structure):
         ("timeZeroDiag", C.c_int32*MAXEQ), ("timeAnalyticalMatrix", C.c_int32), ("timeUseGlobalDT", C.c_int32),
         ("renumber", C.c_int32), ("dt", C.c_double),
         ("venktnIsMFMHD", C.c_int32), ("psiMinEqual1", C.c_int32), ("strictCoeff", C.c_double),
-        ("roeSaOldStencil", C.c_int32), ("reservedPad", C.c_int32),
+        ("roeSaOldStencil", C.c_int32), ("mhdPotentialBType", C.c_int32),
+        ("mhdDipole", C.c_double*3),
     ]
 
 
@@ -149,6 +150,10 @@ def make_config(dim, update_var=UV_CONS, flux=FS_ROE, poly_rec=PR_CONSTANT, limi
     c.psiMinEqual1 = int(kw.get("psi_min_equal_1", 0))
     c.strictCoeff = float(kw.get("strict_coeff", 1.0))
     c.roeSaOldStencil = int(kw.get("roe_sa_old_stencil", 0))
+    dip = kw.get("mhd_dipole")                       # (mX, mY, mZ): potentialBType = Dipole
+    c.mhdPotentialBType = 1 if dip is not None else 0
+    for i in range(3):
+        c.mhdDipole[i] = float(dip[i]) if dip is not None else 0.0
     return c
 
 

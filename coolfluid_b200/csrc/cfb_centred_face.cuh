@@ -53,6 +53,15 @@ CFB_HD void faceRecon(const Dev& d, const Cfg& c, int f, int L, int R, double* n
   for (int k = 0; k < D; ++k) n[k] = nr[k]*invArea;
 }
 
+// B0 at the quadrature point of face f (both extrapolated states sit there: FVMCC_PolyRec.cxx:170-185)
+template <class PH>
+CFB_HD void faceBackgroundB(const Dev& d, const Cfg& c, int f, double* B0) {
+  double xq[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) xq[k] = (c.mhdPotentialBType != 0) ? d.faceCentres[(size_t)k*d.nFaces + f] : 1.0;
+  PH::backgroundB(c, xq, B0);
+}
+
 template <class PH, bool JAC>
 struct CentredInnerFaceK {   // idx over interior faces
   static constexpr int D = PH::DIM, Q = PH::Q;
@@ -80,12 +89,14 @@ struct CentredInnerFaceK {   // idx over interior faces
 #pragma unroll
     for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + L]; sR[v] = d.U[(size_t)v*d.nStates + R]; }
     faceRecon<D, Q>(d, c, f, L, R, n, area, gL, gR);
+    double b0[3];
+    faceBackgroundB<PH>(d, c, f, b0);
     const bool lin = (c.polyRec != CFB200_PR_CONSTANT);
 #pragma unroll
     for (int v = 0; v < Q; ++v) { vL[v] = lin ? sL[v] + gL[v] : sL[v]; vR[v] = lin ? sR[v] + gR[v] : sR[v]; }
     typename PH::CSide a, b;
-    PH::cside(c, vL, n, a);
-    PH::cside(c, vR, n, b);
+    PH::cside(c, vL, n, a, b0);
+    PH::cside(c, vR, n, b, b0);
     double flux[Q];
     PH::centred(c, a, b, flux);
 #pragma unroll
@@ -100,6 +111,7 @@ struct CentredInnerFaceK {   // idx over interior faces
       for (int k = 0; k < 3; ++k) tn[k] = -1.0*n[k];
       typename PH::Data pR;
       PH::physicalData(c, vR, pR);
+      pR.b0[0] = b0[0]; pR.b0[1] = b0[1]; pR.b0[2] = b0[2];
       d.ucR[f] = dmax(PH::maxEigenValue(c, pR, tn), 0.)*faceArea;
       d.ucD[f] = 0.;
 #pragma unroll
@@ -124,7 +136,7 @@ struct CentredInnerFaceK {   // idx over interior faces
 #pragma unroll
       for (int v = 0; v < Q; ++v) { const double base = side ? vR[v] : vL[v]; vp[v] = (v == iVar) ? pvr : base; }
       typename PH::CSide pert;
-      PH::cside(c, vp, n, pert);
+      PH::cside(c, vp, n, pert, b0);
       double pf[Q];
       if (side == 0) PH::centred(c, pert, b, pf); else PH::centred(c, a, pert, pf);
       const double invEps = ddiv(1., eps);
@@ -156,14 +168,16 @@ struct CentredBoundaryFaceK {   // idx over boundary faces
 #pragma unroll
     for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + L]; sR[v] = d.U[(size_t)v*d.nStates + R]; }
     faceRecon<D, Q>(d, c, f, L, R, n, area, gL, gR);
+    double b0[3];
+    faceBackgroundB<PH>(d, c, f, b0);
     const bool lin = (c.polyRec != CFB200_PR_CONSTANT);
 #pragma unroll
     for (int v = 0; v < Q; ++v) { vL[v] = lin ? sL[v] + gL[v] : sL[v]; vR[v] = lin ? sR[v] + gR[v] : sR[v]; }
     double flux[Q];
     {
       typename PH::CSide a, b;
-      PH::cside(c, vL, n, a);
-      PH::cside(c, vR, n, b);
+      PH::cside(c, vL, n, a, b0);
+      PH::cside(c, vR, n, b, b0);
       PH::centred(c, a, b, flux);
       d.ucL[f] = dmax(a.evVecMax, 0.)*(area/1);
       d.ucR[f] = 0.; d.ucD[f] = 0.;               // the ghost side has no cell (FVMCC_ComputeRHS.cxx:455-514)
@@ -188,8 +202,8 @@ struct CentredBoundaryFaceK {   // idx over boundary faces
 #pragma unroll
       for (int v = 0; v < Q; ++v) { vL[v] = lin ? sLp[v] + gL[v] : sLp[v]; vR[v] = lin ? sRp[v] + gR[v] : sRp[v]; }
       typename PH::CSide a, b;
-      PH::cside(c, vL, n, a);
-      PH::cside(c, vR, n, b);
+      PH::cside(c, vL, n, a, b0);
+      PH::cside(c, vR, n, b, b0);
       double pf[Q];
       PH::centred(c, a, b, pf);
       const double invEps = ddiv(1., eps);

@@ -35,6 +35,8 @@ inline bool splitterSupported(const cfb200_config& c) {
   if (c.diffusive == CFB200_DIFF_NS && c.derivativeStrategy != CFB200_DV_DIAMOND &&
       !(c.derivativeStrategy == CFB200_DV_CORRECTED && c.polyRec != CFB200_PR_CONSTANT))
     return false;
+  // background potential field: none or Dipole, MHD3DProjection only ("PFSS" needs the reference's harmonics data)
+  if (c.mhdPotentialBType != 0 && !(c.mhdPotentialBType == 1 && c.physicalModel == CFB200_PM_MHD3D_PROJECTION)) return false;
   if (c.physicalModel == CFB200_PM_MHD3D_PROJECTION)      // MHD: centred splitters, conservative variables, inviscid
     return (c.fluxSplitter == CFB200_FS_LAXFRIED || c.fluxSplitter == CFB200_FS_HLL) && c.updateVar == CFB200_UV_CONS &&
            c.diffusive == CFB200_DIFF_NONE;

@@ -4,10 +4,11 @@
 //   MHD3DProjectionCons.cxx:540-574   computePhysicalData          :1132-1148 computeStateFromPhysicalData
 //   MHD3DProjectionVarSet.cxx:42-78   computeFlux   :398-436 getMaxEigenValue   :499-548 computeEigenValues
 //   FiniteVolumeMHD/MirrorMHD3DProjection.cxx:56-96
-// No background potential field (potentialBType unset, B0 = 0).
+// Background potential field B0: none or "Dipole" (computeMagneticDipole :479-495), evaluated at the face quadrature point;
+// it enters the wave speeds only (computeFlux has no B0 term).
 #pragma once
 
-struct MhdData { double rho, p, A, V, B, phi, v[3], b[3]; };
+struct MhdData { double rho, p, A, V, B, phi, v[3], b[3], b0[3]; };   // b0: background field at the point of the data
 
 struct MhdPhys {
   static constexpr int DIM = 3;
@@ -31,6 +32,23 @@ struct MhdPhys {
     d.p = (c.gamma - 1.)*(s[7] - 0.5*(rho*V2 + B2));
     d.phi = s[8];
     d.A = dsqrt(divBy(c.gamma*d.p, rr));
+    d.b0[0] = 0.0; d.b0[1] = 0.0; d.b0[2] = 0.0;
+  }
+  // MHD3DProjectionVarSet::computeMagneticDipole (MHD3DProjectionVarSet.cxx:479-495) at x; zero without potentialBType
+  static CFB_HD void backgroundB(const Cfg& c, const double* x, double* B0) {
+    B0[0] = 0.0; B0[1] = 0.0; B0[2] = 0.0;
+    if (c.mhdPotentialBType == 1) {
+      const double mX = c.mhdDipole[0], mY = c.mhdDipole[1], mZ = c.mhdDipole[2];
+      const double xCoord = x[0], yCoord = x[1], zCoord = x[2];
+      const double r = dsqrt(xCoord*xCoord + yCoord*yCoord + zCoord*zCoord);
+      const double rCubeInv = ddiv(1.0, r*r*r);
+      const double rSqInv = ddiv(1.0, r*r);
+      const double mDotr = mX*xCoord + mY*yCoord + mZ*zCoord;
+      const double coeff = 3.0*rSqInv*mDotr;
+      B0[0] = rCubeInv*(coeff*xCoord - mX);
+      B0[1] = rCubeInv*(coeff*yCoord - mY);
+      B0[2] = rCubeInv*(coeff*zCoord - mZ);
+    }
   }
   static CFB_HD void stateFromPhysicalData(const Cfg& c, const MhdData& d, double* s) {
     const double rho = d.rho;
@@ -80,7 +98,7 @@ struct MhdPhys {
   // The wave speeds the eigenvalue vector is made of (computeEigenValues): Vn, cf, cs, ca.
   struct Waves { double Vn, cf, cs, ca; };
   static CFB_HD void waves(const Cfg& c, const MhdData& d, const double* n, Waves& w) {
-    const double Bx = d.b[0] + 0.0, By = d.b[1] + 0.0, Bz = d.b[2] + 0.0;      // B1 + B0 with B0 = 0
+    const double Bx = d.b[0] + d.b0[0], By = d.b[1] + d.b0[1], Bz = d.b[2] + d.b0[2];      // B1 + B0
     const Recip rr = recipOf(d.rho);
     const double invRho = divBy(1., rr);
     const double sqB = Bx*Bx + By*By + Bz*Bz;
@@ -112,9 +130,10 @@ struct MhdPhys {
   // that LaxFriedFlux.cxx:96-102 / HLLFlux.cxx:93-107 form (each starting from 0.0), plus RealVector::max() of it
   // (ArrayT.hh:61-66) for the left update coefficient.
   struct CSide { double f[Q], s[Q], evMax0, evMin0, evAbs0, evVecMax; };
-  static CFB_HD void cside(const Cfg& c, const double* u, const double* n, CSide& o) {
+  static CFB_HD void cside(const Cfg& c, const double* u, const double* n, CSide& o, const double* b0) {
     MhdData pd;
     physicalData(c, u, pd);
+    pd.b0[0] = b0[0]; pd.b0[1] = b0[1]; pd.b0[2] = b0[2];
     physFlux(c, pd, n, o.f);
 #pragma unroll
     for (int i = 0; i < Q; ++i) o.s[i] = u[i];

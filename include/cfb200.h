@@ -150,7 +150,13 @@ typedef struct cfb200_config {
   double strictCoeff;
   int32_t roeSaOldStencil;            /* RoeSA option "oldStencil" (RoeSAFlux.cxx:44-45,171): every face of the two cells,
                                        * not only those sharing a node with the face */
-  int32_t reservedPad;
+  /* MHD3DProjection background potential field B0 (MHDTerm option potentialBType, MHDTerm.cxx:25,38-40): 0 = none,
+   * 1 = "Dipole" at the origin with moment (mX, mY, mZ) (MHD3DProjectionVarSet.cxx:479-495).  B0 enters the wave speeds of
+   * the centred splitters and the update coefficient (computeEigenValues :499-548, getMaxEigenValue :398-436), evaluated at
+   * the face quadrature point (FVMCC_PolyRec.cxx:170-185); the flux itself has no B0 term (computeFlux :42-78).
+   * "PFSS" needs the reference's own spherical-harmonics data and is not provided. */
+  int32_t mhdPotentialBType;
+  double mhdDipole[3];
 } cfb200_config;
 
 /* Flat mesh data = the contents of the reference's sockets and connectivity tables (SURVEY.md §8b "Data ownership").

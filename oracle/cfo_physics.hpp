@@ -35,6 +35,7 @@ struct Phys {
   typedef PData Data;
 
   // Euler2DCons.cxx:441-465, Euler3DCons.cxx:538-562, Euler2DPuvt.cxx:78-108, Euler3DPvt.ci:76-116
+  static void setCoordinates(PData&, const double*) {}      // the Euler physical data hold no coordinates
   static void computePhysicalData(const Config& c, const double* s, PData& d) {
     if (c.updateVar == UV_CONS) {
       const double rho = s[0];
@@ -1107,7 +1108,7 @@ namespace cfo {
 // plugins/MHD/MHD3DProjectionCons.cxx:540-574 (computePhysicalData), :1132-1148 (computeStateFromPhysicalData),
 // plugins/MHD/MHD3DProjectionVarSet.cxx:42-78 (computeFlux), :398-436 (getMaxEigenValue), :499-548 (computeEigenValues);
 // no background potential field (potentialBType unset: B0 = 0).  Only the centred splitters (LaxFried, HLL) apply.
-struct MhdData { double rho, p, A, V, B, phi, v[3], b[3]; };
+struct MhdData { double rho, p, A, V, B, phi, v[3], b[3], x[3]; };   // x: data[XP YP ZP], the point the data belong to
 
 struct MhdPhys {
   static constexpr int D = 3;
@@ -1129,6 +1130,7 @@ struct MhdPhys {
     d.p = (c.gamma - 1.)*(s[7] - 0.5*(rho*V2 + B2));
     d.phi = s[8];
     d.A = std::sqrt(c.gamma*d.p/rho);
+    d.x[0] = 0.; d.x[1] = 0.; d.x[2] = 0.;   // data[XP YP ZP] = state.getCoordinates() (:570-573): set by the caller
   }
   static void stateFromPhysicalData(const Config& c, const MhdData& d, double* s) {
     const double rho = d.rho;
@@ -1178,8 +1180,27 @@ struct MhdPhys {
     f[7] = Vn*(E + P) - Bn*VdotB;
     f[8] = refSpeedSq*Bn;
   }
+  // MHD3DProjectionVarSet::computeMagneticDipole (MHD3DProjectionVarSet.cxx:479-495); B0 = 0 without potentialBType
+  static void backgroundB(const Config& c, const double* x, double* B0) {
+    B0[0] = 0.0; B0[1] = 0.0; B0[2] = 0.0;
+    if (c.mhdPotentialBType == 1) {
+      const double mX = c.mhdDipole[0], mY = c.mhdDipole[1], mZ = c.mhdDipole[2];
+      const double xCoord = x[0], yCoord = x[1], zCoord = x[2];
+      const double r = std::sqrt(xCoord*xCoord + yCoord*yCoord + zCoord*zCoord);
+      const double rCubeInv = 1.0/(r*r*r);
+      const double rSqInv = 1.0/(r*r);
+      const double mDotr = mX*xCoord + mY*yCoord + mZ*zCoord;
+      const double coeff = 3.0*rSqInv*mDotr;
+      B0[0] = rCubeInv*(coeff*xCoord - mX);
+      B0[1] = rCubeInv*(coeff*yCoord - mY);
+      B0[2] = rCubeInv*(coeff*zCoord - mZ);
+    }
+  }
+  static void setCoordinates(MhdData& d, const double* x) { d.x[0] = x[0]; d.x[1] = x[1]; d.x[2] = x[2]; }
   static void eigenValues(const Config& c, const MhdData& d, const double* n, double* ev) {
-    const double Bx = d.b[0] + 0.0, By = d.b[1] + 0.0, Bz = d.b[2] + 0.0;    // B1 + B0, B0 = 0
+    double B0[3];
+    backgroundB(c, d.x, B0);
+    const double Bx = d.b[0] + B0[0], By = d.b[1] + B0[1], Bz = d.b[2] + B0[2];    // B1 + B0
     const double invRho = 1./d.rho;
     const double sqB = Bx*Bx + By*By + Bz*Bz;
     const double p = d.p;
@@ -1200,7 +1221,9 @@ struct MhdPhys {
   // MHD3DProjectionVarSet.cxx:398-436 (what the RIGHT side of the update coefficient uses; the left side uses
   // _leftEv.max(): LaxFriedFlux.cxx:131, HLLFlux.cxx:141)
   static double maxEigenValue(const Config& c, const MhdData& d, const double* n) {
-    const double Bx = d.b[0] + 0.0, By = d.b[1] + 0.0, Bz = d.b[2] + 0.0;
+    double B0[3];
+    backgroundB(c, d.x, B0);
+    const double Bx = d.b[0] + B0[0], By = d.b[1] + B0[1], Bz = d.b[2] + B0[2];
     const double invRho = 1./d.rho;
     const double sqB = Bx*Bx + By*By + Bz*Bz;
     const double p = d.p;

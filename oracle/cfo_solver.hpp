@@ -450,6 +450,8 @@ public:
   bool convectiveFlux(FaceCtx& x, bool isPerturb, Outputs& o, double* flux) {
     P::computePhysicalData(cfg, x.vL, x.pL);   // computeStatesData, FVMCC_ComputeRHS.hh:112-118
     P::computePhysicalData(cfg, x.vR, x.pR);
+    // both extrapolated states sit at the face quadrature point (FVMCC_PolyRec::baseExtrapolateImpl, FVMCC_PolyRec.cxx:170-185)
+    P::setCoordinates(x.pL, x.xq); P::setCoordinates(x.pR, x.xq);
     for (int i = 0; i < Q; ++i) flux[i] = 0.;
     if (cfg.fluxSplitter == FS_ROE) {
       if (!P::roeFlux(cfg, x.vL, x.vR, x.pL, x.pR, x.n, flux)) { o.status = 1; return false; }

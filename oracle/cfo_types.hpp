@@ -113,7 +113,8 @@ struct Config {
   int32_t psiMinEqual1;        // Venktn3DStrict.cxx:33,47
   double strictCoeff;          // Venktn3DStrict.cxx:31,44
   int32_t roeSaOldStencil;     // RoeSAFlux.cxx:44-45
-  int32_t reservedPad;
+  int32_t mhdPotentialBType;   // MHDTerm.cxx:25: 0 none, 1 "Dipole"
+  double mhdDipole[3];         // MHDTerm.cxx:38-40 mX mY mZ
 };
 
 struct MeshView {

@@ -141,6 +141,10 @@ void FVMCC_ComputeRHSB200::fillConfig(cfb200_config& c)
     SafePtr<Physics::MHD::MHDProjectionTerm> mhdTerm = pm->getConvectiveTerm().d_castTo<Physics::MHD::MHDProjectionTerm>();
     c.physicalModel = CFB200_PM_MHD3D_PROJECTION;
     c.gamma = mhdTerm->getGamma(); c.refSpeed = mhdTerm->getRefSpeed(); c.R = 1.0;
+    // background potential field (MHDTerm.hh:203-232): "Dipole" is evaluated by the engine, anything else but "" is refused
+    const std::string pb = mhdTerm->getPotentialBType();
+    c.mhdPotentialBType = (pb == "Dipole") ? 1 : (pb.empty() ? 0 : -1);
+    c.mhdDipole[0] = mhdTerm->getMX(); c.mhdDipole[1] = mhdTerm->getMY(); c.mhdDipole[2] = mhdTerm->getMZ();
   } else {
     SafePtr<Physics::NavierStokes::EulerTerm> eulerTerm = pm->getConvectiveTerm().d_castTo<Physics::NavierStokes::EulerTerm>();
     c.physicalModel = CFB200_PM_EULER;

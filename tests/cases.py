@@ -247,6 +247,12 @@ CASES = {
                            bcs_ns2d, True),
     # BASELINE config 4: 3D ideal MHD with hyperbolic divergence cleaning (q = 9), HLL / Lax-Friedrichs
     "mhd3d_hex_hll": (lambda: meshgen.hex_box(5, 4, 4), mhd3d_cfg, bcs_mhd3d, "mhd"),
+    # background potential field B0 = "Dipole" (MHDTerm potentialBType): enters the wave speeds and the update coefficient
+    "mhd3d_hex_hll_dipole": (lambda: meshgen.hex_box(5, 4, 4), lambda: mhd3d_cfg(mhd_dipole=(0.002, 0.001, 0.004)),
+                             bcs_mhd3d, "mhd"),
+    "mhd3d_tet_laxfried_1st_dipole": (lambda: meshgen.tet_box(3, 3, 2),
+                                      lambda: mhd3d_cfg(flux=B.FS_LAXFRIED, poly_rec=B.PR_CONSTANT, limiter=B.LIM_NONE,
+                                                        mhd_dipole=(0.0, 0.0, 0.005)), bcs_mhd3d, "mhd"),
     "mhd3d_tet_laxfried_1st": (lambda: meshgen.tet_box(3, 3, 2),
                                lambda: mhd3d_cfg(flux=B.FS_LAXFRIED, poly_rec=B.PR_CONSTANT, limiter=B.LIM_NONE),
                                bcs_mhd3d, "mhd"),
