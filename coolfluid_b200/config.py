@@ -13,7 +13,7 @@ MAXEQ = 9
 
 # enums (must match include/cfb200.h and oracle/cfo_types.hpp)
 PM_EULER, PM_MHD3D_PROJECTION = 0, 1
-DV_DIAMOND, DV_CORRECTED = 0, 1
+DV_DIAMOND, DV_CORRECTED, DV_STATEDIFF = 0, 1, 2
 UV_CONS, UV_PVT = 0, 1
 FS_ROE, FS_AUSMPLUS, FS_AUSMPLUSUP, FS_LAXFRIED, FS_HLL, FS_ROESA = 0, 1, 2, 3, 4, 5
 PR_CONSTANT, PR_LINEARLS = 0, 1
@@ -95,7 +95,7 @@ def make_config(dim, update_var=UV_CONS, flux=FS_ROE, poly_rec=PR_CONSTANT, limi
     c.viscLaw = kw.get("visc_law", VISC_SIMPLER_SUTHERLAND)
     c.computeJacobian = (2 if jacobian == "analytic" else 1) if jacobian else 0
     c.coeffSigmoid = kw.get("coeff_sigmoid", 1e-8)
-    c.derivativeStrategy = {"diamond": DV_DIAMOND, "corrected": DV_CORRECTED}[kw.get("derivative", "diamond")]
+    c.derivativeStrategy = {"diamond": DV_DIAMOND, "corrected": DV_CORRECTED, "statediff": DV_STATEDIFF}[kw.get("derivative", "diamond")]
     c.useFullStencil = 1 if use_full_stencil else 0
     c.freezeLimiter = int(kw.get("freeze_limiter", 0))
     c.stopLimiting = int(kw.get("stop_limiting", 0))

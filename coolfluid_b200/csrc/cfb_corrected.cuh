@@ -17,6 +17,8 @@ struct CorrectedWork {
   double n[3], area;
   double dr, eN[3], oe[3][3], volume, mu, lambda;
   double xR[3];
+  bool stateDiff;         // "StateDiff" (StateDiffDerivative.cxx:56-131): grad = dv * (xR - xL)/|xR - xL|, no tangential part,
+                          // average state = mean of the nodal states of the first two face nodes, no boundary stencil
   double avState[Q];
   double gradL[Q][3];     // the left cell's gradient
   double tang[Q][3];      // (I - n n) 0.5 (gradL + gradR)
@@ -25,6 +27,7 @@ struct CorrectedWork {
   // computeControlVolume + computeAverageValues + the transport coefficients of the (never perturbed) nodal average
   CFB_HD void setup(const Dev& d, const Cfg& c, int f, int L, int R, bool isB, const double* unitNormal, double faceArea) {
     area = faceArea;
+    stateDiff = (c.derivativeStrategy == CFB200_DV_STATEDIFF);
     double xL[3] = {0., 0., 0.};
 #pragma unroll
     for (int k = 0; k < 3; ++k) { n[k] = unitNormal[k]; xR[k] = 0.; }
@@ -43,6 +46,7 @@ struct CorrectedWork {
 #pragma unroll
     for (int v = 0; v < Q; ++v) {
       const size_t iL = (size_t)v*d.nCells + L;
+      if (stateDiff) { gradL[v][0] = 0.; gradL[v][1] = 0.; gradL[v][2] = 0.; continue; }   // no cell gradients (constant rec.)
       gradL[v][0] = d.uX[iL]; gradL[v][1] = d.uY[iL]; gradL[v][2] = (D == 3) ? d.uZ[iL] : 0.;
     }
     const double volL = d.volumes[L];
@@ -57,6 +61,10 @@ struct CorrectedWork {
     for (int k = 0; k < D; ++k) eDotN += divBy(xR[k] - xL[k], rd)*n[k];
 #pragma unroll
     for (int k = 0; k < 3; ++k) eN[k] = (k < D) ? eDotN*n[k] : 0.;
+    if (stateDiff) {                                  // _vectorLR, StateDiffDerivative.cxx:89-94
+#pragma unroll
+      for (int k = 0; k < D; ++k) eN[k] = divBy(xR[k] - xL[k], rd);
+    }
 #pragma unroll
     for (int a = 0; a < 3; ++a)
 #pragma unroll
@@ -68,7 +76,7 @@ struct CorrectedWork {
       double a = 0.0;
 #pragma unroll
       for (int j = 0; j < NMAX; ++j) if (j < nbN) a += invNbNodes*nv[v][j];
-      avState[v] = a;
+      avState[v] = stateDiff ? 0.5*(nv[v][0] + nv[v][1]) : a;       // StateDiffDerivative.cxx:121-128
     }
     mu = P::dynViscosity(c, avState)*c.artDiffCoeff;
     lambda = P::thermConductivity(c, mu);
@@ -86,7 +94,7 @@ struct CorrectedWork {
   }
   CFB_HD void gradOf(double dv, const double* t, double* g) const {
 #pragma unroll
-    for (int a = 0; a < 3; ++a) g[a] = (a < D) ? dv*eN[a] + t[a] : 0.;
+    for (int a = 0; a < 3; ++a) g[a] = (a < D) ? (stateDiff ? dv*eN[a] : dv*eN[a] + t[a]) : 0.;
   }
   CFB_HD void diffFlux(const Cfg& c, const double (*g)[3], double* dflux) const {
     P::nsFlux(c, avState, g, n, mu, lambda, dflux);
@@ -100,6 +108,11 @@ struct CorrectedWork {
 
   // ---- interior faces -----------------------------------------------------------------------------------------
   CFB_HD void innerTang(const Dev& d, int R) {
+    if (stateDiff) {
+#pragma unroll
+      for (int v = 0; v < Q; ++v) { tang[v][0] = 0.; tang[v][1] = 0.; tang[v][2] = 0.; }
+      return;
+    }
 #pragma unroll
     for (int v = 0; v < Q; ++v) {
       const size_t iR = (size_t)v*d.nCells + R;
@@ -155,6 +168,13 @@ struct CorrectedWork {
   // g = boundary face index; sLs / sRs = the (possibly perturbed) left cell state and the ghost state rebuilt from it.
   // Stencil member 0 is the left cell itself; the other members are read from the state array.
   CFB_HD void boundaryGrads(const Dev& d, int g, const double* sLs, const double* sRs) {
+    if (stateDiff) {                                  // the same two-point difference with the ghost state
+      const Recip rd0 = recipOf(dr);
+      const double t0[3] = {0., 0., 0.};
+#pragma unroll
+      for (int v = 0; v < Q; ++v) gradOf(divBy(sRs[v] - sLs[v], rd0), t0, grad[v]);
+      return;
+    }
     double l11 = 0.0, l12 = 0.0, l13 = 0.0, l22 = 0.0, l23 = 0.0, l33 = 0.0;
     double lf1[Q], lf2[Q], lf3[Q];
 #pragma unroll

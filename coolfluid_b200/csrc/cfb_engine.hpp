@@ -30,9 +30,11 @@ inline bool splitterSupported(const cfb200_config& c) {
     if (!(c.physicalModel == CFB200_PM_EULER && c.fluxSplitter == CFB200_FS_AUSMPLUSUP && c.machInf > 0.)) return false;
     if (c.diffusive != CFB200_DIFF_NONE && c.updateVar != CFB200_UV_PVT) return false;
     if (c.diffusive != CFB200_DIFF_NONE && c.derivativeStrategy == CFB200_DV_CORRECTED && c.dim != 2) return false;
+    if (c.diffusive != CFB200_DIFF_NONE && c.derivativeStrategy == CFB200_DV_STATEDIFF) return false;   // its getGradientsJacob is a stub
   }
   // Corrected2D/3D reads the cell gradients (uX uY uZ sockets), which only the linear reconstruction computes
   if (c.diffusive == CFB200_DIFF_NS && c.derivativeStrategy != CFB200_DV_DIAMOND &&
+      c.derivativeStrategy != CFB200_DV_STATEDIFF &&
       !(c.derivativeStrategy == CFB200_DV_CORRECTED && c.polyRec != CFB200_PR_CONSTANT))
     return false;
   // background potential field: none or Dipole, MHD3DProjection only ("PFSS" needs the reference's harmonics data)
@@ -568,7 +570,7 @@ public:
         bk.launch("boundaryFace", CentredBoundaryFaceK<PH, false>{d, cfg}, d.nGhosts, 128);
       }
     } else {
-      if (cfg.derivativeStrategy == CFB200_DV_CORRECTED && cfg.diffusive == CFB200_DIFF_NS) faceKernels_<D, 1>(doJac, faceShape);
+      if (cfg.derivativeStrategy != CFB200_DV_DIAMOND && cfg.diffusive == CFB200_DIFF_NS) faceKernels_<D, 1>(doJac, faceShape);   // Corrected / StateDiff: CorrectedWork
       else faceKernels_<D, 0>(doJac, faceShape);
     }
     const bool fused = (cfg.fuseTimeRhs != 0);

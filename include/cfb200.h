@@ -80,7 +80,8 @@ typedef struct cfb200_bc {
 
 /* DerivativeComputer of the diffusive flux: DiamondVolume2D/3D (DiamondVolume{2,3}DDerivative.cxx, the default) or
  * Corrected2D/3D (CorrectedDerivative2D.cxx:91-430, CorrectedDerivative3D.cxx:54-176) */
-enum cfb200_derivative { CFB200_DV_DIAMOND = 0, CFB200_DV_CORRECTED = 1 };
+enum cfb200_derivative { CFB200_DV_DIAMOND = 0, CFB200_DV_CORRECTED = 1,
+                         CFB200_DV_STATEDIFF = 2 /* "StateDiff" plugins/FiniteVolume/StateDiffDerivative.cxx:56-131 */ };
 
 /* Everything ComputeRHS reads from the .CFcase and from SubSystemStatus (SURVEY.md §8b "Scalars crossing per call").
  * The per-call scalars (iter, residual, resFactor, cfl, computeJacobian) may be changed between calls with

@@ -74,7 +74,8 @@ int cfo_compute(const Config* c, const MeshView* m, const BC* bcs, double* U, Cf
     }
     else if (c->computeJacobian == 2 && (c->fluxSplitter != FS_AUSMPLUSUP ||
                                          (c->diffusive != DIFF_NONE && c->updateVar != UV_PVT) ||
-                                         (c->diffusive != DIFF_NONE && c->derivativeStrategy == 1 && c->dim != 2))) {
+                                         (c->diffusive != DIFF_NONE && c->derivativeStrategy == 1 && c->dim != 2) ||
+                                         (c->diffusive != DIFF_NONE && c->derivativeStrategy == 2))) {
       co->status = 2; return 2;
     }
     else if (c->dim == 2) { Solver<2> s(*c, *m, bcs); s.execute(U, o); }

@@ -632,8 +632,53 @@ public:
     }
   }
 
+  // ---- a15, third DerivativeComputer: "StateDiff" (StateDiffDerivative.cxx:56-131) inside NSFlux.ci:59-156: the
+  // two-point difference along the line of centres, grad = (vR - vL)/|xR - xL| * (xR - xL)/|xR - xL|; the average state is
+  // the mean of the nodal states of the first two face nodes (also in 3D); volume = mean of the cell volumes.  The flat
+  // mesh orients every face from its L state (isOutward == L), so `_vectorLR` is never flipped (:98-102).
+  void diffusiveFluxStateDiff(FaceCtx& x, const double* U, bool isPerturb, int iPerturbVar, Outputs& o, double* dflux) {
+    const int32_t* fn = &mesh.faceNodes[mesh.faceNodePtr[x.f]];
+    const double* cL = &mesh.centres[(size_t)x.L*D];
+    const double* cR = &mesh.centres[(size_t)x.R*D];
+    if (!isPerturb) {
+      x.dr = getDistance<D>(cL, cR);
+      for (int k = 0; k < D; ++k) x.eRLdotNN[k] = cR[k] - cL[k];       // _vectorLR
+      for (int k = 0; k < D; ++k) x.eRLdotNN[k] /= x.dr;
+      x.volume = x.isB ? mesh.volumes[x.L] : 0.5*(mesh.volumes[x.L] + mesh.volumes[x.R]);
+    }
+    const double* sL = &U[(size_t)x.L*Q];
+    const double* sR = &U[(size_t)x.R*Q];
+    double grad[Q][3];
+    for (int i = 0; i < Q; ++i) {
+      const double dv = (sR[i] - sL[i])/x.dr;
+      for (int ix = 0; ix < D; ++ix) grad[i][ix] = dv*x.eRLdotNN[ix];
+      if (D == 2) grad[i][2] = 0.;
+    }
+    double avState[Q];
+    for (int i = 0; i < Q; ++i) avState[i] = 0.5*(o.nstates[(size_t)fn[0]*Q + i] + o.nstates[(size_t)fn[1]*Q + i]);
+    bool useBackUp = false, setBackUp = false;
+    if (isPerturb && iPerturbVar != P::TID) useBackUp = true;
+    else if (!isPerturb) setBackUp = true;
+    double mu, lambda;
+    if (useBackUp || freezeCoeff) { mu = x.muBkp; lambda = x.lambdaBkp; }
+    else {
+      mu = P::dynViscosity(cfg, avState)*cfg.artDiffCoeff;
+      lambda = P::thermConductivity(cfg, mu);
+      if (setBackUp) { x.muBkp = mu; x.lambdaBkp = lambda; }
+    }
+    P::nsFluxUnit(cfg, avState, grad, x.n, mu, lambda, dflux);
+    for (int i = 0; i < Q; ++i) dflux[i] *= x.area;
+    if (!isPerturb) {
+      const double nu = mu/P::nsDensity(cfg, avState);
+      const double diffUpdateCoeff = nu*x.area*x.area/x.volume;
+      o.updateCoeff[x.L] += diffUpdateCoeff;
+      if (!x.isB) o.updateCoeff[x.R] += diffUpdateCoeff;
+    }
+  }
+
   void diffusiveFlux(FaceCtx& x, const double* U, bool isPerturb, int iPerturbVar, Outputs& o, double* dflux) {
     if (cfg.derivativeStrategy == 1) { diffusiveFluxCorrected(x, U, isPerturb, iPerturbVar, o, dflux); return; }
+    if (cfg.derivativeStrategy == 2) { diffusiveFluxStateDiff(x, U, isPerturb, iPerturbVar, o, dflux); return; }
     const int nb = mesh.faceNodePtr[x.f+1] - mesh.faceNodePtr[x.f];
     const int32_t* fn = &mesh.faceNodes[mesh.faceNodePtr[x.f]];
     const double* cL = &mesh.centres[(size_t)x.L*D];

@@ -101,7 +101,7 @@ struct Config {
   int32_t entropyFixID;   // RoeEntropyFixFlux.cxx:35 (0 = plain RoeFlux, 1 | 2 = "RoeEntropyFix")
   double refSpeed;        // MHDProjectionTerm refSpeed (hyperbolic divergence cleaning speed)
   double coeffSigmoid;    // AUSMFlux.ci:64 coeffSigmoid (1e-8): blending of the sigmoid switches of the analytic Jacobian
-  int32_t derivativeStrategy;  // 0 DiamondVolume{2,3}D (CellCenterFVMData.cxx:298 default), 1 Corrected{2,3}D
+  int32_t derivativeStrategy;  // 0 DiamondVolume{2,3}D (CellCenterFVMData.cxx:298 default), 1 Corrected{2,3}D, 2 StateDiff
   int32_t fuseTimeRhs;         // product-side scheduling flag (no meaning for the oracle)
   // FVMCC_StdComputeTimeRhs.cxx:42-57 zeroDiagValue; FVMCC_PseudoSteadyTimeRhs.cxx:40-46 useAnalyticalMatrix, useGlobalDT
   int32_t timeZeroDiag[MAXEQ];

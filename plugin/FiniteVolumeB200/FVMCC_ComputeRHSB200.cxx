@@ -208,12 +208,13 @@ void FVMCC_ComputeRHSB200::fillConfig(cfb200_config& c)
 
   // ---- diffusive flux
   c.diffusive = md.getDiffusiveFluxComputer()->isNull() ? CFB200_DIFF_NONE : CFB200_DIFF_NS;
-  // CellCenterFVM.Data.DerivativeStrategy: DiamondVolume2D/3D (CellCenterFVMData.cxx:298 default) or Corrected2D/3D
+  // CellCenterFVM.Data.DerivativeStrategy: DiamondVolume2D/3D (CellCenterFVMData.cxx:298 default), Corrected2D/3D or StateDiff
   const std::string deriv = md.getDerivativeComputer()->getName();
   if (deriv == "Corrected2D" || deriv == "Corrected3D") c.derivativeStrategy = CFB200_DV_CORRECTED;
+  else if (deriv == "StateDiff") c.derivativeStrategy = CFB200_DV_STATEDIFF;
   else if (deriv == "DiamondVolume2D" || deriv == "DiamondVolume3D" || c.diffusive == CFB200_DIFF_NONE)
     c.derivativeStrategy = CFB200_DV_DIAMOND;
-  else c.derivativeStrategy = -1;      // CorrectedGG*, StateDiff, ...: cfb200_create answers CFB200_ERR_UNSUPPORTED
+  else c.derivativeStrategy = -1;      // CorrectedGG*, ...: cfb200_create answers CFB200_ERR_UNSUPPORTED
   c.coeffTau = 1.0; c.coeffQ = 1.0; c.cpOverPrandtl = 1.0; c.muRef = 1.0; c.artDiffCoeff = 1.0;
   if (c.diffusive == CFB200_DIFF_NS) {
     SafePtr<Physics::NavierStokes::NSTerm> ns = pm->getDiffusiveTerm().d_castTo<Physics::NavierStokes::NSTerm>();

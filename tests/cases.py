@@ -286,6 +286,13 @@ CASES = {
     "ns2d_tri_corrected_fullstencil": (lambda: meshgen.quad_channel(10, 8, triangles=True),
                                        lambda: ns2d_cfg(derivative="corrected", use_full_stencil=True, res_factor=0.5),
                                        bcs_ns2d, True),
+    # a15, third derivative computer: "StateDiff" (two-point difference along the line of centres)
+    "ns2d_quad_statediff": (lambda: meshgen.quad_channel(10, 8), lambda: ns2d_cfg(derivative="statediff"), bcs_ns2d, True),
+    "ns3d_tet_statediff_1st": (lambda: meshgen.tet_box(3, 3, 3),
+                               lambda: ns3d_cfg(derivative="statediff", poly_rec=B.PR_CONSTANT, limiter=B.LIM_NONE,
+                                                flux=B.FS_AUSMPLUS), bcs_ns3d, True),
+    "ns3d_hex_statediff": (lambda: meshgen.hex_box(5, 4, 4), lambda: ns3d_cfg(derivative="statediff", res_factor=0.5),
+                           bcs_ns3d, True),
     "ns3d_single_cell_corrected": (lambda: meshgen.hex_box(1, 1, 1, jitter=0.0), lambda: ns3d_cfg(derivative="corrected"),
                                    bcs_ns3d, True),
     # a16: FarFieldEuler2D (conservative) / FarFieldEuler3D (Cons, Pvt): subsonic in/outflow and, with the fast initial
