@@ -1,6 +1,7 @@
 // See FVMCC_ComputeRHSB200.hh.  Written against the COOLFluiD API of /root/reference; not compiled here.
 #include <cstdlib>
 #include <cstring>
+#include <sstream>
 #include <map>
 #include <typeinfo>
 #include "FiniteVolumeB200/FiniteVolumeB200.hh"
@@ -311,6 +312,20 @@ cfb200_bc FVMCC_ComputeRHSB200::translateBC(FVMCC_BC* bc, GeometricEntity* probe
     out.value[0] = opt("Pressure"); out.value[1] = opt("Uinf"); out.value[2] = opt("Vinf");
     if (dim == 3) out.value[3] = opt("Winf");
     out.value[dim + 1] = opt("Temperature");
+    return out;
+  }
+  if (has("NoSlipWallIsothermalNSvt")) {
+    // NoSlipWallIsothermalNSvt.ci:22-83: TWall (dimensional), uWall, TGhostMin; the radiative-equilibrium wall, the
+    // fixed-ghost-temperature variant and the "Adiabatic" switch are other commands in disguise: not translated
+    const auto flag = [&](const char* name) { return bc->getOption(name)->getValueAsString() == "true"; };
+    if (flag("RadEquilibrium") || flag("FixTWallInGhost") || flag("Adiabatic")) { out.type = -1; return out; }
+    const CFuint dim = PhysicalModelStack::getActive()->getDim();
+    const CFreal tempRef = m_cfg.tempRef;                 // EulerTerm::getTempRef(), read by fillConfig()
+    out.type = CFB200_BC_NOSLIP_ISOTHERMAL;
+    out.value[0] = opt("TGhostMin")/tempRef;
+    std::istringstream uw(bc->getOption("uWall")->getValueAsString());     // "u v [w]", default: all zero
+    for (CFuint k = 0; k < dim; ++k) { CFreal v = 0.; uw >> v; out.value[1 + k] = v; }
+    out.value[dim + 1] = opt("TWall")/tempRef;
     return out;
   }
   out.type = -1;
