@@ -8,6 +8,7 @@
 #include <cmath>
 #include <string>
 #include <vector>
+#include <mutex>
 #include "cfb_engine.hpp"
 
 namespace cfb {
@@ -747,6 +748,118 @@ __global__ void k_selftest_divsqrt(unsigned long long seed, long long n, int spa
   if (__double_as_longlong(s0) != __double_as_longlong(s1)) ++nbad;
   if (nbad) atomicAdd(bad, nbad);
 }
+}
+
+// ---- allocation-free residual norm (cfb200_l2_norm_noalloc) ----------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops).  The block partial sums that Engine::sumOrdered keeps behind its
+// cudaMalloc'ed `partial` array live here in a file-scope device array instead; the reduction shape is the same
+// (1024 consecutive cells per block, 4 strided loads per thread, shared-memory tree, partials summed in index order), so
+// the sum of squares equals the one cfb200_update_sol_newton forms, bit for bit.
+#define CFB_NOALLOC_L1 16384                      /* level-1 partials: CFB200_NOALLOC_MAX_CELLS / 1024 */
+#define CFB_NOALLOC_L2 16                         /* level-2 partials: CFB_NOALLOC_L1 / 1024 */
+static_assert((long long)CFB_NOALLOC_L1*1024 == CFB200_NOALLOC_MAX_CELLS, "scratch size and the documented maximum differ");
+static __device__ __align__(256) double g_noallocScratch[CFB_NOALLOC_L1 + CFB_NOALLOC_L2];   // 131 200 B per GPU, until exit
+
+namespace cfb {
+
+// squares of one equation's increment, reduced like k_block_sum reduces Dev::partial (UpdateSolNewton: sq = dU*dU for
+// updatable cells, 0 for the others)
+__global__ void __launch_bounds__(256) k_block_sumsq(const double* __restrict__ dU, const uint8_t* __restrict__ updatable,
+                                                     double* __restrict__ out, int n, int q, int var) {
+  __shared__ double s[256];
+  const int base = blockIdx.x*1024;
+  double a = 0.;
+  for (int k = 0; k < 4; ++k) {
+    const int i = base + k*256 + threadIdx.x;
+    if (i < n) {
+      double sq = 0.;
+      if (!updatable || updatable[i]) { const double v = dU[(size_t)i*q + var]; sq = v*v; }
+      a += sq;
+    }
+  }
+  s[threadIdx.x] = a;
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1) { if (threadIdx.x < w) s[threadIdx.x] += s[threadIdx.x + w]; __syncthreads(); }
+  if (threadIdx.x == 0) out[blockIdx.x] = s[0];
+}
+// the host loop of Engine::sumOrdered (partials added in index order) and the log10 of cfb200_update_sol_newton
+__global__ void k_noalloc_final(const double* __restrict__ partials, int m, double* __restrict__ out) {
+  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  double sum = 0.;
+  for (int i = 0; i < m; ++i) sum += partials[i];
+  out[0] = sum;
+  out[1] = (sum > 0.) ? log10(sqrt(sum)) : -1.7976931348623157e308;
+}
+
+// device address of g_noallocScratch per device: in host code the array's name is only a stand-in for the symbol, the
+// address a kernel can use comes from cudaGetSymbolAddress, asked once per device with that device current
+static std::mutex g_noallocMutex;
+static double* g_noallocAddr[64] = {};
+
+static int noallocFail(char* err, int cap, int code, const std::string& what) {
+  if (err && cap > 0) { std::snprintf(err, (size_t)cap, "%s", what.c_str()); }
+  return code;
+}
+
+} // namespace cfb
+
+extern "C" int cfb200_l2_norm_noalloc(int device, const double* d_dU, const uint8_t* d_updatable, int64_t nCells,
+                                      int32_t nEqs, int32_t monitorVar, void* cudaStream, double* d_out,
+                                      char* err, int32_t errCap) {
+  using namespace cfb;
+  if (err && errCap > 0) err[0] = 0;
+  if (nCells < 0) return noallocFail(err, errCap, CFB200_ERR_INVALID_ARG, "cfb200_l2_norm_noalloc: nCells < 0");
+  if (nCells > (int64_t)CFB200_NOALLOC_MAX_CELLS)
+    return noallocFail(err, errCap, CFB200_ERR_INVALID_ARG,
+                       "cfb200_l2_norm_noalloc: nCells = " + std::to_string((long long)nCells) + " exceeds the fixed scratch of "
+                       "CFB200_NOALLOC_MAX_CELLS = " + std::to_string((long long)CFB200_NOALLOC_MAX_CELLS) +
+                       " cells (use cfb200_update_sol_newton, whose scratch is sized with the mesh)");
+  if (nEqs < 1 || nEqs > 1024 || monitorVar < 0 || monitorVar >= nEqs)
+    return noallocFail(err, errCap, CFB200_ERR_INVALID_ARG, "cfb200_l2_norm_noalloc: nEqs / monitorVar out of range");
+  if (device < 0 || device >= 64) return noallocFail(err, errCap, CFB200_ERR_INVALID_ARG, "cfb200_l2_norm_noalloc: device out of range");
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) {
+    cudaGetLastError();
+    return noallocFail(err, errCap, CFB200_ERR_NO_DEVICE, "cfb200_l2_norm_noalloc: no usable CUDA device");
+  }
+  if (device >= count || cudaSetDevice(device) != cudaSuccess) {
+    cudaGetLastError();
+    return noallocFail(err, errCap, CFB200_ERR_INVALID_ARG, "cfb200_l2_norm_noalloc: cannot select the device");
+  }
+  double* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_noallocMutex);
+    if (!g_noallocAddr[device]) {
+      double* p = nullptr;
+      const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noallocScratch);
+      if (e != cudaSuccess || !p) {
+        cudaGetLastError();
+        return noallocFail(err, errCap, CFB200_ERR_CUDA,
+                           std::string("cfb200_l2_norm_noalloc: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+      }
+      g_noallocAddr[device] = p;
+    }
+    scratch = g_noallocAddr[device];
+  }
+  if (nCells == 0) return CFB200_OK;                 // set-up call: the address is resolved, nothing is launched
+  if (!d_dU || !d_out) return noallocFail(err, errCap, CFB200_ERR_INVALID_ARG, "cfb200_l2_norm_noalloc: null input / output pointer");
+  cudaStream_t st = (cudaStream_t)cudaStream;
+  const int n = (int)nCells;
+  const int nb = (n + 1023)/1024;
+  // every partial the final kernel reads is written by this call: nothing has to start at zero
+  k_block_sumsq<<<nb, 256, 0, st>>>(d_dU, d_updatable, scratch, n, (int)nEqs, (int)monitorVar);
+  if (nb > 1024) {
+    const int nb2 = (nb + 1023)/1024;
+    k_block_sum<<<nb2, 256, 0, st>>>(scratch, scratch + CFB_NOALLOC_L1, nb);
+    k_noalloc_final<<<1, 32, 0, st>>>(scratch + CFB_NOALLOC_L1, nb2, d_out);
+  } else {
+    k_noalloc_final<<<1, 32, 0, st>>>(scratch, nb, d_out);
+  }
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess)
+    return noallocFail(err, errCap, CFB200_ERR_CUDA, std::string("cfb200_l2_norm_noalloc: launch: ") + cudaGetErrorString(e));
+  return CFB200_OK;
 }
 
 extern "C" {

@@ -57,7 +57,7 @@ ABI_SYMBOLS = [
     "export_csr", "get_field", "device_ptr", "status", "enable_timing", "last_timings", "stream",
     "nccl_unique_id", "comm_init", "set_halo", "set_independent_cells", "halo_begin", "halo_exchange", "allreduce_sum",
     "mesh_build", "mesh_sizes", "mesh_get", "mesh_ptr", "mesh_view", "mesh_set_updatable", "mesh_free", "mesh_diamond_volumes",
-    "selftest_divsqrt", "export_csr_device", "solve_gmres",
+    "selftest_divsqrt", "export_csr_device", "solve_gmres", "l2_norm_noalloc",
 ]
 # symbols the engine part needs (a test-only host build of the kernel functors exports just these)
 ENGINE_SYMBOLS = ABI_SYMBOLS[2:30]
@@ -83,6 +83,9 @@ def load(path=None, prefix="cfb200_"):
         except AttributeError:
             if prefix == "cfb200_" or name in ENGINE_SYMBOLS:
                 raise
+    if hasattr(ns, "l2_norm_noalloc"):
+        ns.l2_norm_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
+                                       C.c_void_p, C.c_char_p, C.c_int32]
     if hasattr(ns, "selftest_divsqrt"):
         ns.selftest_divsqrt.argtypes = [C.c_int, C.c_int64, C.c_uint64, C.c_int, C.POINTER(C.c_int64)]
     H = C.c_void_p

@@ -320,6 +320,25 @@ int cfb200_halo_exchange(cfb200_handle* h);
 /* sum over ranks of n <= 64 host doubles (residual norms; replaces the MPI_Allreduce of ComputeL2Norm.cxx:127-137) */
 int cfb200_allreduce_sum(cfb200_handle* h, double* v, int n);
 
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The residual norm of
+ * cfb200_update_sol_newton / ComputeL2Norm without a handle and WITHOUT ANY ALLOCATION (no cudaMalloc / cudaFree, no
+ * allocating library call): d_out[0] = sum over the updatable cells of dU[cell*nEqs + monitorVar]^2, formed with the
+ * reduction shape of cfb200_update_sol_newton (same bits); d_out[1] = log10(sqrt(d_out[0])) (-DBL_MAX for a zero sum).
+ *   d_dU        device, [nCells*nEqs] increments in the rhs socket layout;   d_updatable  device, [nCells] or NULL = all
+ *   d_out       device, 2 doubles, written by the last kernel;   cudaStream  cudaStream_t the kernels are launched on
+ *               (NULL = default stream); the call does not synchronise
+ *   err/errCap  optional buffer for the error text
+ * The block partial sums live in a file-scope device array of the library (131 200 bytes on every GPU that loads it, held
+ * until exit), which fixes the limit: nCells <= CFB200_NOALLOC_MAX_CELLS, beyond it the call returns
+ * CFB200_ERR_INVALID_ARG with a message.  Every call on a device shares that array and it keeps the last call's
+ * contents (each call overwrites every entry it reads, nothing needs clearing): two calls that overlap on the GPU (different
+ * streams, no ordering) race; order them.  nCells = 0 is a set-up call: it resolves the array's device address for
+ * `device` (done once per device, on the first call) and launches nothing - make it before a graph capture. */
+#define CFB200_NOALLOC_MAX_CELLS 16777216
+int cfb200_l2_norm_noalloc(int device, const double* d_dU, const uint8_t* d_updatable, int64_t nCells, int32_t nEqs,
+                           int32_t monitorVar, void* cudaStream, double* d_out, char* err, int32_t errCap);
+
 /* ---- host-side mesh-data construction (replaces FVMCC_MeshDataBuilder.cxx:91-499, ComputeFaceNormals*P1,
  * FVMCCGeoDataComputer.ci:61-89, ComputeDummyStates.cxx, ComputeFaceVertexNeighborsPlusGhost.cxx,
  * NodalStatesExtrapolator.ci:134-237, DistanceBasedExtrapolator.ci:60-125, DiamondVolume3DDerivative.cxx:413-563,
