@@ -79,13 +79,23 @@ __global__ void __launch_bounds__(BS, MINB) k_staged2(const F f, const int n) {
     if (i < n) { f.run(i, phase, sm + t, STRIDE); s = f.slot(i, phase); }
     sm[F::BLK*STRIDE + t] = __hiloint2double(0, s);
     __syncwarp();
+    // batches of WB entries, as in k_staged: the shared-memory reads of a batch are issued before its first global store
+    constexpr int WB = (F::BLK % 9 == 0) ? 9 : ((F::BLK % 5 == 0) ? 5 : 1);
     int k = lane, lf = 0;
-#pragma unroll 2
-    for (int it = 0; it < F::BLK; ++it) {
-      const int slot = __double2loint(sm[F::BLK*STRIDE + warpBase + lf]);
-      if (slot >= 0) out[(size_t)slot*F::BLK + k] = sm[k*STRIDE + warpBase + lf];
-      k += 32;
-      if (k >= F::BLK) { k -= F::BLK; ++lf; }
+#pragma unroll 1
+    for (int it = 0; it < F::BLK; it += WB) {
+      double x[WB]; size_t dst[WB]; bool on[WB];
+#pragma unroll
+      for (int j = 0; j < WB; ++j) {
+        const int slot = __double2loint(sm[F::BLK*STRIDE + warpBase + lf]);
+        x[j] = sm[k*STRIDE + warpBase + lf];
+        on[j] = slot >= 0;
+        dst[j] = (size_t)slot*F::BLK + k;
+        k += 32;
+        if (k >= F::BLK) { k -= F::BLK; ++lf; }
+      }
+#pragma unroll
+      for (int j = 0; j < WB; ++j) if (on[j]) out[dst[j]] = x[j];
     }
     __syncwarp();
   }

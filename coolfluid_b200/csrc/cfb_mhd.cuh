@@ -139,15 +139,23 @@ struct MhdPhys {
     for (int i = 0; i < Q; ++i) o.s[i] = u[i];
     Waves w;
     waves(c, pd, n, w);
-    double ev[Q];
-    eigenValues(c, w, ev);
-    double a = 0.0, b = 0.0, m = 0.0, vm = ev[0];
-#pragma unroll
-    for (int i = 0; i < Q; ++i) {
-      a = dmax(a, ev[i]); b = dmin(b, ev[i]); m = dmax(m, fabs(ev[i]));
-      if (i > 0) vm = dmax(vm, ev[i]);
+    // The folds over ev = (Vn-cf, Vn-ca, Vn-cs, Vn, c, -c, Vn+cs, Vn+ca, Vn+cf) (eigenValues()) without the entries that can
+    // never decide them.  In floating point cf >= cs >= 0 and ca >= 0 (square roots / a quotient of non-negative numbers,
+    // 0.5*(a2 + ab) >= 0.5*(a2 - ab) for ab >= 0) and x + y is monotone in y, so Vn-cs, Vn, Vn+cs lie in [Vn-cf, Vn+cf],
+    // Vn-ca <= Vn+cf and Vn+ca >= Vn-cf: those entries are never the strict maximum, minimum or largest magnitude, and
+    // max / min / abs do not round, so the values equal the 9-entry loops of LaxFriedFlux.cxx:96-102 / HLLFlux.cxx:93-107
+    // (which start from 0.0) and RealVector::max() (which starts from ev[0]).  Only the folds the configured splitter
+    // reads are formed (warp-uniform branch); a fold nobody reads at a call site is dead code there.
+    const double e0 = w.Vn - w.cf, e1 = w.Vn - w.ca, e7 = w.Vn + w.ca, e8 = w.Vn + w.cf;
+    const double cp = c.refSpeed, cm = -c.refSpeed;
+    o.evMax0 = 0.0; o.evMin0 = 0.0; o.evAbs0 = 0.0;
+    if (c.fluxSplitter == CFB200_FS_LAXFRIED) {
+      o.evAbs0 = dmax(dmax(dmax(dmax(dmax(dmax(0.0, fabs(e0)), fabs(e1)), fabs(cp)), fabs(cm)), fabs(e7)), fabs(e8));
+    } else {
+      o.evMax0 = dmax(dmax(dmax(dmax(0.0, cp), cm), e7), e8);
+      o.evMin0 = dmin(dmin(dmin(dmin(0.0, e0), e1), cp), cm);
     }
-    o.evMax0 = a; o.evMin0 = b; o.evAbs0 = m; o.evVecMax = vm;
+    o.evVecMax = dmax(dmax(dmax(dmax(e0, cp), cm), e7), e8);
   }
   // LaxFriedFlux.cxx:79-118:  0.5*(fR + fL - a*k*(sR - sL));  HLLFlux.cxx:73-133
   static CFB_HD void centred(const Cfg& c, const CSide& l, const CSide& r, double* result) {
