@@ -74,9 +74,10 @@ __global__ void __launch_bounds__(BS, MINB) k_staged2(const F f, const int n) {
   const int t = threadIdx.x, lane = t & 31, warpBase = t & ~31;
   const int i = blockIdx.x*BS + t;
   double* out = f.out();
+  typename F::State st;            // what phase 1 keeps of phase 0, in registers across the write-out
   for (int phase = 0; phase < 2; ++phase) {
     int s = -1;
-    if (i < n) { f.run(i, phase, sm + t, STRIDE); s = f.slot(i, phase); }
+    if (i < n) { f.run(i, phase, st, sm + t, STRIDE); s = f.slot(i, phase); }
     sm[F::BLK*STRIDE + t] = __hiloint2double(0, s);
     __syncwarp();
     // batches of WB entries, as in k_staged: the shared-memory reads of a batch are issued before its first global store

@@ -66,87 +66,95 @@ template <class PH, bool JAC>
 struct CentredInnerFaceK {   // idx over interior faces
   static constexpr int D = PH::DIM, Q = PH::Q;
   // JAC: launched in two phases through k_staged2 (cfb_capi.cu): phase 0 evaluates the face and perturbs the L state ->
-  // block(R,L); phase 1 re-evaluates the two unperturbed sides and perturbs the R state -> block(L,R).  One q x q block is
-  // staged in shared memory per thread and written out by the warp in whole rows (a 9 x 9 block is 648 B: staging both at
-  // once would leave one resident block per SM).
+  // block(R,L); phase 1 perturbs the R state -> block(L,R).  One q x q block is staged in shared memory per thread and
+  // written out by the warp in whole rows (a 9 x 9 block is 648 B: staging both at once would leave one resident block
+  // per SM).  What phase 1 needs of phase 0 (normal, the R cell state and its reconstruction increment, the unperturbed
+  // left side, the base flux) stays in registers across the write-out (State): no second gather, no second base evaluation.
   static constexpr int BLK = Q*Q;
   static constexpr int STAGE = BLK + 1;
+  struct State { double n[3], area, b0[3], sR[Q], gR[Q], flux[Q]; typename PH::CSide a; bool active; };
   Dev d; Cfg c;
   CFB_HD double* out() const { return d.bsrVal; }
   CFB_HD int slot(int f, int phase) const { return phase ? d.slotLR[f] : d.slotRL[f]; }
-  CFB_HD void operator()(int f) const { run(f, 0, nullptr, 0); }        // RHS only
-  CFB_HD void run(int f, int phase, double* stg, int stride) const {
-    const int L = d.faceL[f], R = d.faceR[f];
-    if (!(d.updatable[L] || d.updatable[R])) {             // FVMCC_ComputeRHS.cxx:212-213
-      if (phase == 0) {
-        for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = 0.;
-        d.ucL[f] = 0.; d.ucR[f] = 0.; d.ucD[f] = 0.;
-      }
-      if (JAC) for (int k = 0; k < BLK; ++k) stg[(size_t)k*stride] = 0.;
-      return;
-    }
-    double n[3], area, gL[Q], gR[Q], sL[Q], sR[Q], vL[Q], vR[Q];
-#pragma unroll
-    for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + L]; sR[v] = d.U[(size_t)v*d.nStates + R]; }
-    faceRecon<D, Q>(d, c, f, L, R, n, area, gL, gR);
-    double b0[3];
-    faceBackgroundB<PH>(d, c, f, b0);
-    const bool lin = (c.polyRec != CFB200_PR_CONSTANT);
-#pragma unroll
-    for (int v = 0; v < Q; ++v) { vL[v] = lin ? sL[v] + gL[v] : sL[v]; vR[v] = lin ? sR[v] + gR[v] : sR[v]; }
-    typename PH::CSide a, b;
-    PH::cside(c, vL, n, a, b0);
-    PH::cside(c, vR, n, b, b0);
-    double flux[Q];
-    PH::centred(c, a, b, flux);
-#pragma unroll
-    for (int v = 0; v < Q; ++v) flux[v] *= area;
-    if (phase == 0) {
-      // update coefficients: LaxFriedFlux.cxx:120-188 / HLLFlux.cxx:135-150 (left: _leftEv.max(); right: getMaxEigenValue
-      // with the reversed normal)
-      const double faceArea = area/1;
-      d.ucL[f] = dmax(a.evVecMax, 0.)*faceArea;
-      double tn[3];
-#pragma unroll
-      for (int k = 0; k < 3; ++k) tn[k] = -1.0*n[k];
-      typename PH::Data pR;
-      PH::physicalData(c, vR, pR);
-      pR.b0[0] = b0[0]; pR.b0[1] = b0[1]; pR.b0[2] = b0[2];
-      d.ucR[f] = dmax(PH::maxEigenValue(c, pR, tn), 0.)*faceArea;
-      d.ucD[f] = 0.;
-#pragma unroll
-      for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = flux[v];
-    }
-    if (!JAC) return;
-    // FVMCC_ComputeRhsJacob.cxx:126-236,321-365 with the frozen gradient / limiter (LeastSquareP1PolyRec3D.cxx:272-318)
+  CFB_HD void operator()(int f) const { State st; run(f, 0, st, nullptr, 0); }        // RHS only
+  // the finite-difference columns of one side: `fixed` is the unperturbed other side, sP / gP / vBase the cell state, the
+  // reconstruction increment and the reconstructed state of the perturbed side
+  // (FVMCC_ComputeRhsJacob.cxx:126-236,321-365 with the frozen gradient / limiter, LeastSquareP1PolyRec3D.cxx:272-318)
+  template <int SIDE>
+  CFB_HD void fdColumns(const State& st, const typename PH::CSide& fixed, const double* sP, const double* gP,
+                        const double* vBase, bool lin, double* stg, int stride) const {
     const double rf = c.resFactor;
-    const int side = phase;
 #pragma unroll 1
     for (int iVar = 0; iVar < Q; ++iVar) {
-      double orig = 0., gp = 0.;
-#pragma unroll
-      for (int v = 0; v < Q; ++v) {
-        if (side == 0 && iVar == v) { orig = sL[v]; gp = gL[v]; }
-        if (side == 1 && iVar == v) { orig = sR[v]; gp = gR[v]; }
-      }
+      const double orig = pick<Q>(sP, iVar), gp = pick<Q>(gP, iVar);
       const double eps = fdEps(c, iVar, orig);
       const double pv = orig + eps;
       const double pvr = lin ? pv + gp : pv;
       double vp[Q];
 #pragma unroll
-      for (int v = 0; v < Q; ++v) { const double base = side ? vR[v] : vL[v]; vp[v] = (v == iVar) ? pvr : base; }
+      for (int v = 0; v < Q; ++v) vp[v] = (v == iVar) ? pvr : vBase[v];
       typename PH::CSide pert;
-      PH::cside(c, vp, n, pert, b0);
+      PH::cside(c, vp, st.n, pert, st.b0);
       double pf[Q];
-      if (side == 0) PH::centred(c, pert, b, pf); else PH::centred(c, a, pert, pf);
+      if (SIDE == 0) PH::centred(c, pert, fixed, pf); else PH::centred(c, fixed, pert, pf);
       const double invEps = ddiv(1., eps);
 #pragma unroll
       for (int v = 0; v < Q; ++v) {
-        double fd = (pf[v]*area - flux[v])*invEps;
+        double fd = (pf[v]*st.area - st.flux[v])*invEps;
         fd *= rf;                                                    // what row L receives (upFactor[0])
-        stg[(size_t)(v*Q + iVar)*stride] = side ? fd : fd*(-1.0);    // row R receives upFactor[1] = -1 times that
+        stg[(size_t)(v*Q + iVar)*stride] = SIDE ? fd : fd*(-1.0);    // row R receives upFactor[1] = -1 times that
       }
     }
+  }
+  CFB_HD void run(int f, int phase, State& st, double* stg, int stride) const {
+    const bool lin = (c.polyRec != CFB200_PR_CONSTANT);
+    if (phase == 1) {
+      if (!st.active) { for (int k = 0; k < BLK; ++k) stg[(size_t)k*stride] = 0.; return; }
+      double vR[Q];
+#pragma unroll
+      for (int v = 0; v < Q; ++v) vR[v] = lin ? st.sR[v] + st.gR[v] : st.sR[v];
+      fdColumns<1>(st, st.a, st.sR, st.gR, vR, lin, stg, stride);
+      return;
+    }
+    const int L = d.faceL[f], R = d.faceR[f];
+    st.active = d.updatable[L] || d.updatable[R];
+    if (!st.active) {             // FVMCC_ComputeRHS.cxx:212-213
+      for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = 0.;
+      d.ucL[f] = 0.; d.ucR[f] = 0.; d.ucD[f] = 0.;
+      if (JAC) for (int k = 0; k < BLK; ++k) stg[(size_t)k*stride] = 0.;
+      return;
+    }
+    double gL[Q], sL[Q], vL[Q], vR[Q];
+#pragma unroll
+    for (int v = 0; v < Q; ++v) { sL[v] = d.U[(size_t)v*d.nStates + L]; st.sR[v] = d.U[(size_t)v*d.nStates + R]; }
+    faceRecon<D, Q>(d, c, f, L, R, st.n, st.area, gL, st.gR);
+    faceBackgroundB<PH>(d, c, f, st.b0);
+#pragma unroll
+    for (int v = 0; v < Q; ++v) { vL[v] = lin ? sL[v] + gL[v] : sL[v]; vR[v] = lin ? st.sR[v] + st.gR[v] : st.sR[v]; }
+    typename PH::CSide b;
+    PH::cside(c, vL, st.n, st.a, st.b0);
+    PH::cside(c, vR, st.n, b, st.b0);
+    PH::centred(c, st.a, b, st.flux);
+#pragma unroll
+    for (int v = 0; v < Q; ++v) st.flux[v] *= st.area;
+    {
+      // update coefficients: LaxFriedFlux.cxx:120-188 / HLLFlux.cxx:135-150 (left: _leftEv.max(); right: getMaxEigenValue
+      // with the reversed normal)
+      const double faceArea = st.area/1;
+      d.ucL[f] = dmax(st.a.evVecMax, 0.)*faceArea;
+      double tn[3];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) tn[k] = -1.0*st.n[k];
+      typename PH::Data pR;
+      PH::physicalData(c, vR, pR);
+      pR.b0[0] = st.b0[0]; pR.b0[1] = st.b0[1]; pR.b0[2] = st.b0[2];
+      d.ucR[f] = dmax(PH::maxEigenValue(c, pR, tn), 0.)*faceArea;
+      d.ucD[f] = 0.;
+#pragma unroll
+      for (int v = 0; v < Q; ++v) d.faceFlux[(size_t)v*d.nFaces + f] = st.flux[v];
+    }
+    if (!JAC) return;
+    fdColumns<0>(st, b, sL, gL, vL, lin, stg, stride);
   }
 };
 

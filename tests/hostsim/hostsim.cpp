@@ -62,12 +62,14 @@ struct HostLoopBackend {
   }
   template <class F> void launchStaged2(const char*, const F& f, int n) {
     double stg[F::STAGE];
-    for (int i = 0; i < n; ++i)
+    for (int i = 0; i < n; ++i) {
+      typename F::State st;
       for (int phase = 0; phase < 2; ++phase) {
-        f.run(i, phase, stg, 1);
+        f.run(i, phase, st, stg, 1);
         const int slot = f.slot(i, phase);
         if (slot >= 0) for (int k = 0; k < F::BLK; ++k) f.out()[(size_t)slot*F::BLK + k] = stg[k];
       }
+    }
   }
   double sumOrdered(double* x, int n) { double s = 0.; for (int i = 0; i < n; ++i) s += x[i]; return s; }
   double minOrdered(double* x, int n) { double m = x[0]; for (int i = 1; i < n; ++i) m = (x[i] < m) ? x[i] : m; return m; }
