@@ -48,7 +48,7 @@ class ConfigStruct(C.Structure):
         ("renumber", C.c_int32), ("dt", C.c_double),
         ("venktnIsMFMHD", C.c_int32), ("psiMinEqual1", C.c_int32), ("strictCoeff", C.c_double),
         ("roeSaOldStencil", C.c_int32), ("mhdPotentialBType", C.c_int32),
-        ("mhdDipole", C.c_double*3),
+        ("mhdDipole", C.c_double*3), ("noLimiterVar", C.c_int32*MAXEQ), ("reservedTail", C.c_int32),
     ]
 
 
@@ -150,6 +150,8 @@ def make_config(dim, update_var=UV_CONS, flux=FS_ROE, poly_rec=PR_CONSTANT, limi
     c.psiMinEqual1 = int(kw.get("psi_min_equal_1", 0))
     c.strictCoeff = float(kw.get("strict_coeff", 1.0))
     c.roeSaOldStencil = int(kw.get("roe_sa_old_stencil", 0))
+    for i in kw.get("no_limiter_id", ()):            # Venktn2D "2DNoLimiterID"
+        c.noLimiterVar[int(i)] = 1
     dip = kw.get("mhd_dipole")                       # (mX, mY, mZ): potentialBType = Dipole
     c.mhdPotentialBType = 1 if dip is not None else 0
     for i in range(3):

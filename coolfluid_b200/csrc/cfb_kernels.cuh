@@ -428,6 +428,8 @@ struct LimiterK {   // idx over cells
         }
       }
       double* out = &d.lim[(size_t)v*d.nCells + cell];
+      // Venktn2D option "2DNoLimiterID" (Venktn2D.cxx:253-258): the limiter of the listed variables is cancelled
+      if (D == 2 && c.limiter == CFB200_LIM_VENKTN && c.noLimiterVar[v]) psimin = 1.0;
       *out = fresh ? psimin : dmin(psimin, *out);
     }
   }

@@ -158,6 +158,9 @@ typedef struct cfb200_config {
    * "PFSS" needs the reference's own spherical-harmonics data and is not provided. */
   int32_t mhdPotentialBType;
   double mhdDipole[3];
+  int32_t noLimiterVar[CFB200_MAXEQ]; /* Venktn2D option "2DNoLimiterID" (Venktn2D.cxx:40-41,253-258): 1 = the limiter of this
+                                       * variable is forced to 1 */
+  int32_t reservedTail;
 } cfb200_config;
 
 /* Flat mesh data = the contents of the reference's sockets and connectivity tables (SURVEY.md §8b "Data ownership").

@@ -320,6 +320,9 @@ public:
       }
       lim[iVar] = psimin;
     }
+    // Venktn2D option "2DNoLimiterID" (Venktn2D.cxx:253-258): cancels the limiter of the listed variables
+    if (D == 2 && cfg.limiter == LIM_VENKTN)
+      for (int iVar = 0; iVar < Q; ++iVar) if (cfg.noLimiterVar[iVar]) lim[iVar] = 1.0;
   }
 
   // FVMCC_PolyRec.cxx:120-167 computeFaceLimiter (first touch per cell through cellFlag)

@@ -115,6 +115,8 @@ struct Config {
   int32_t roeSaOldStencil;     // RoeSAFlux.cxx:44-45
   int32_t mhdPotentialBType;   // MHDTerm.cxx:25: 0 none, 1 "Dipole"
   double mhdDipole[3];         // MHDTerm.cxx:38-40 mX mY mZ
+  int32_t noLimiterVar[MAXEQ]; // Venktn2D.cxx:40-41,253-258 "2DNoLimiterID" as a per-variable flag
+  int32_t reservedTail;
 };
 
 struct MeshView {

@@ -193,7 +193,8 @@ void FVMCC_ComputeRHSB200::fillConfig(cfb200_config& c)
   c.stopLimiting = optInt(rec, "StopLimiting", 0);         // FVMCC_PolyRec.cxx:27,52
   Limiter<CellCenterFVMData>& limr = *md.getLimiter();
   const std::string lim = limr.getName();
-  c.limiter = (lim == "Venktn2D" || lim == "Venktn3D") ? CFB200_LIM_VENKTN : (lim == "BarthJesp") ? CFB200_LIM_BARTHJESP :
+  c.limiter = (lim == "Venktn2D" || lim == "Venktn3D") ? CFB200_LIM_VENKTN : (lim.find("BarthJesp") == 0) ? CFB200_LIM_BARTHJESP :    // BarthJesp | BarthJesp2D | BarthJesp3D: one class (BarthJesp.cxx:26-34)
+             
               (lim == "Venktn3DStrict") ? CFB200_LIM_VENKTN_STRICT :
               (lim == "Null" || c.polyRec == CFB200_PR_CONSTANT) ? CFB200_LIM_NONE : -1;
   c.coeffEps = optReal(limr, "coeffEps", 1.0);             // Venktn2D.cxx:34,58
@@ -202,6 +203,11 @@ void FVMCC_ComputeRHSB200::fillConfig(cfb200_config& c)
   {
     const std::vector<CFreal> mv = optVec(limr, "magnitudeValues");              // Venktn2D.cxx:32,96-106: default = refValues
     if (mv.size() == nbEqs) for (CFuint i = 0; i < nbEqs; ++i) c.magnitudeValues[i] = mv[i];
+  }
+  {
+    const std::vector<CFreal> nl = (lim == "Venktn2D") ? optVec(limr, "2DNoLimiterID") : std::vector<CFreal>();   // Venktn2D.cxx:40-41
+    for (CFuint i = 0; i < CFB200_MAXEQ; ++i) c.noLimiterVar[i] = 0;
+    for (CFuint i = 0; i < nl.size(); ++i) if (nl[i] >= 0 && nl[i] < nbEqs) c.noLimiterVar[(CFuint)nl[i]] = 1;
   }
   c.venktnIsMFMHD = (c.limiter == CFB200_LIM_VENKTN_STRICT) ? 1 : optInt(limr, "isMFMHD", 0);   // Venktn3D.cxx:125-156
   c.strictCoeff = optReal(limr, "strictCoeff", 1.0);       // Venktn3DStrict.cxx:31,44

@@ -262,6 +262,9 @@ CASES = {
     # a7 variants: the "Venkatakrishnan paper" branch (isMFMHD) of Venktn2D/3D and Venktn3DStrict (what the reference's MHD
     # dipole case selects, plugins/MHD/testcases/COCONUT/Dipole/map_TEST.CFcase:73)
     "ns3d_hex_venktn_mfmhd": (lambda: meshgen.hex_box(6, 5, 4), lambda: ns3d_cfg(is_mfmhd=1, coeff_eps=0.7), bcs_ns3d, True),
+    "euler2d_quad_venktn_nolimiterid": (lambda: meshgen.quad_channel(12, 9),
+                                        lambda: B.make_config(2, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, jacobian=True,
+                                                              no_limiter_id=[0, 3]), bcs_euler2d, False),
     "euler2d_tri_venktn_mfmhd": (lambda: meshgen.quad_channel(12, 9, triangles=True),
                                  lambda: B.make_config(2, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, jacobian=True,
                                                        is_mfmhd=1, magnitude_values=[1.0, 0.9, 0.2, 2.5]), bcs_euler2d, False),
