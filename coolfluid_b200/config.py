@@ -13,7 +13,7 @@ MAXEQ = 9
 
 # enums (must match include/cfb200.h and oracle/cfo_types.hpp)
 PM_EULER, PM_MHD3D_PROJECTION = 0, 1
-DV_DIAMOND, DV_CORRECTED, DV_STATEDIFF = 0, 1, 2
+DV_DIAMOND, DV_CORRECTED, DV_STATEDIFF, DV_CORRECTED_GG = 0, 1, 2, 3
 UV_CONS, UV_PVT = 0, 1
 FS_ROE, FS_AUSMPLUS, FS_AUSMPLUSUP, FS_LAXFRIED, FS_HLL, FS_ROESA = 0, 1, 2, 3, 4, 5
 PR_CONSTANT, PR_LINEARLS = 0, 1
@@ -48,7 +48,7 @@ class ConfigStruct(C.Structure):
         ("renumber", C.c_int32), ("dt", C.c_double),
         ("venktnIsMFMHD", C.c_int32), ("psiMinEqual1", C.c_int32), ("strictCoeff", C.c_double),
         ("roeSaOldStencil", C.c_int32), ("mhdPotentialBType", C.c_int32),
-        ("mhdDipole", C.c_double*3), ("noLimiterVar", C.c_int32*MAXEQ), ("reservedTail", C.c_int32),
+        ("mhdDipole", C.c_double*3), ("noLimiterVar", C.c_int32*MAXEQ), ("correctedGGUseWeights", C.c_int32),
     ]
 
 
@@ -95,7 +95,8 @@ def make_config(dim, update_var=UV_CONS, flux=FS_ROE, poly_rec=PR_CONSTANT, limi
     c.viscLaw = kw.get("visc_law", VISC_SIMPLER_SUTHERLAND)
     c.computeJacobian = (2 if jacobian == "analytic" else 1) if jacobian else 0
     c.coeffSigmoid = kw.get("coeff_sigmoid", 1e-8)
-    c.derivativeStrategy = {"diamond": DV_DIAMOND, "corrected": DV_CORRECTED, "statediff": DV_STATEDIFF}[kw.get("derivative", "diamond")]
+    c.derivativeStrategy = {"diamond": DV_DIAMOND, "corrected": DV_CORRECTED, "statediff": DV_STATEDIFF,
+                            "correctedgg": DV_CORRECTED_GG}[kw.get("derivative", "diamond")]
     c.useFullStencil = 1 if use_full_stencil else 0
     c.freezeLimiter = int(kw.get("freeze_limiter", 0))
     c.stopLimiting = int(kw.get("stop_limiting", 0))
@@ -150,6 +151,7 @@ def make_config(dim, update_var=UV_CONS, flux=FS_ROE, poly_rec=PR_CONSTANT, limi
     c.psiMinEqual1 = int(kw.get("psi_min_equal_1", 0))
     c.strictCoeff = float(kw.get("strict_coeff", 1.0))
     c.roeSaOldStencil = int(kw.get("roe_sa_old_stencil", 0))
+    c.correctedGGUseWeights = int(kw.get("gg_use_weights", 0))
     for i in kw.get("no_limiter_id", ()):            # Venktn2D "2DNoLimiterID"
         c.noLimiterVar[int(i)] = 1
     dip = kw.get("mhd_dipole")                       # (mX, mY, mZ): potentialBType = Dipole

@@ -17,6 +17,11 @@ struct CorrectedWork {
   double n[3], area;
   double dr, eN[3], oe[3][3], volume, mu, lambda;
   double xR[3];
+  bool gg;                // "CorrectedGG2D/3D" (CorrectedDerivativeGG2D.cxx, CorrectedDerivativeGG3D.cxx): the cell gradients
+                          // are Green-Gauss sums over the nodal states, the boundary least squares runs over the states
+                          // across the L cell's faces that touch the face (unweighted unless useWeights), and the
+                          // "average state" reads the shifted control-volume entries of Dev::ggAv (see the oracle)
+  bool ggWeights;
   bool stateDiff;         // "StateDiff" (StateDiffDerivative.cxx:56-131): grad = dv * (xR - xL)/|xR - xL|, no tangential part,
                           // average state = mean of the nodal states of the first two face nodes, no boundary stencil
   double avState[Q];
@@ -24,10 +29,43 @@ struct CorrectedWork {
   double tang[Q][3];      // (I - n n) 0.5 (gradL + gradR)
   double grad[Q][3];
 
+  // computeGradientsGG (CorrectedDerivativeGG2D.cxx:437-476): g[var][dim] = (1/V) sum over the cell's faces (local order) and
+  // their nodes (cell-local table order) of nstate/nbNodesInFace * outward area normal
+  static CFB_HD void ggGrad(const Dev& d, int cell, double (*g)[3]) {
+#pragma unroll
+    for (int v = 0; v < Q; ++v) { g[v][0] = 0.0; g[v][1] = 0.0; g[v][2] = 0.0; }
+    int p = d.ggPtr[cell];
+    for (int k = d.cellFacePtr[cell]; k < d.cellFacePtr[cell+1]; ++k) {
+      const int cf = d.cellFaces[k];
+      const int nbN = d.faceNodePtr[cf+1] - d.faceNodePtr[cf];
+      const bool flip = (d.faceL[cf] != cell);               // isOutward[faceID] != state->getLocalID()
+      double fnr[3] = {0., 0., 0.};
+#pragma unroll
+      for (int a = 0; a < D; ++a) { const double x = d.normals[(size_t)a*d.nFaces + cf]; fnr[a] = flip ? x*(-1.) : x; }
+      const double inv = ddiv(1., (double)nbN);
+      for (int j = 0; j < nbN; ++j) {
+        const int node = d.ggNode[p++];
+#pragma unroll
+        for (int v = 0; v < Q; ++v) {
+          const double vOvN = d.nstates[(size_t)v*d.nNodes + node]*inv;
+#pragma unroll
+          for (int a = 0; a < D; ++a) g[v][a] += vOvN*fnr[a];
+        }
+      }
+    }
+    const Recip rv = recipOf(d.volumes[cell]);
+#pragma unroll
+    for (int v = 0; v < Q; ++v)
+#pragma unroll
+      for (int a = 0; a < D; ++a) g[v][a] = divBy(g[v][a], rv);
+  }
+
   // computeControlVolume + computeAverageValues + the transport coefficients of the (never perturbed) nodal average
   CFB_HD void setup(const Dev& d, const Cfg& c, int f, int L, int R, bool isB, const double* unitNormal, double faceArea) {
     area = faceArea;
     stateDiff = (c.derivativeStrategy == CFB200_DV_STATEDIFF);
+    gg = (c.derivativeStrategy == CFB200_DV_CORRECTED_GG);
+    ggWeights = (c.correctedGGUseWeights != 0);
     double xL[3] = {0., 0., 0.};
 #pragma unroll
     for (int k = 0; k < 3; ++k) { n[k] = unitNormal[k]; xR[k] = 0.; }
@@ -46,7 +84,7 @@ struct CorrectedWork {
 #pragma unroll
     for (int v = 0; v < Q; ++v) {
       const size_t iL = (size_t)v*d.nCells + L;
-      if (stateDiff) { gradL[v][0] = 0.; gradL[v][1] = 0.; gradL[v][2] = 0.; continue; }   // no cell gradients (constant rec.)
+      if (stateDiff || gg) { gradL[v][0] = 0.; gradL[v][1] = 0.; gradL[v][2] = 0.; continue; }   // no LSQ cell gradients read
       gradL[v][0] = d.uX[iL]; gradL[v][1] = d.uY[iL]; gradL[v][2] = (D == 3) ? d.uZ[iL] : 0.;
     }
     const double volL = d.volumes[L];
@@ -77,6 +115,23 @@ struct CorrectedWork {
 #pragma unroll
       for (int j = 0; j < NMAX; ++j) if (j < nbN) a += invNbNodes*nv[v][j];
       avState[v] = stateDiff ? 0.5*(nv[v][0] + nv[v][1]) : a;       // StateDiffDerivative.cxx:121-128
+    }
+    if (gg) {
+      ggGrad(d, L, gradL);
+      // computeAverageValues (CorrectedDerivativeGG2D.cxx:265-285): sum of the listed entries, then * 1/nbNodesInFace
+      int code[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) code[j] = d.ggAv[(size_t)j*d.nFaces + f];
+#pragma unroll
+      for (int v = 0; v < Q; ++v) {
+        double a = 0.0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (code[j] == INT32_MIN) continue;
+          a += (code[j] >= 0) ? d.nstates[(size_t)v*d.nNodes + code[j]] : d.U[(size_t)v*d.nStates + (~code[j])];
+        }
+        avState[v] = a*invNbNodes;
+      }
     }
     mu = P::dynViscosity(c, avState)*c.artDiffCoeff;
     lambda = P::thermConductivity(c, mu);
@@ -111,6 +166,18 @@ struct CorrectedWork {
     if (stateDiff) {
 #pragma unroll
       for (int v = 0; v < Q; ++v) { tang[v][0] = 0.; tang[v][1] = 0.; tang[v][2] = 0.; }
+      return;
+    }
+    if (gg) {
+      double gR[Q][3];
+      ggGrad(d, R, gR);
+#pragma unroll
+      for (int v = 0; v < Q; ++v) {
+        double gl[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) gl[a] = (a < D) ? 0.5*(gradL[v][a] + gR[v][a]) : 0.;
+        tangOf(gl, tang[v]);
+      }
       return;
     }
 #pragma unroll
@@ -187,14 +254,14 @@ struct CorrectedWork {
       for (int k = 0; k < D; ++k) xs[k] = d.centres[(size_t)k*d.nStates + s];
 #pragma unroll
       for (int v = 0; v < Q; ++v) sv[v] = d.U[(size_t)v*d.nStates + s];
-      if (in == b) {
+      if (in == b && !gg) {                 // Corrected: member 0 is the (possibly perturbed) left cell itself
 #pragma unroll
         for (int v = 0; v < Q; ++v) sv[v] = sLs[v];
       }
       double dist = 0.;
 #pragma unroll
       for (int k = 0; k < D; ++k) { const double diff = xR[k] - xs[k]; dist += diff*diff; }
-      const double weight = ddiv(1.0, dsqrt(dist));
+      const double weight = (gg && !ggWeights) ? 1.0 : ddiv(1.0, dsqrt(dist));
       const double dx = weight*(xs[0] - xR[0]);
       const double dy = weight*(xs[1] - xR[1]);
       const double dz = (D == 3) ? weight*(xs[2] - xR[2]) : 0.;

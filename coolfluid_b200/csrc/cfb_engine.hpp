@@ -30,11 +30,12 @@ inline bool splitterSupported(const cfb200_config& c) {
     if (!(c.physicalModel == CFB200_PM_EULER && c.fluxSplitter == CFB200_FS_AUSMPLUSUP && c.machInf > 0.)) return false;
     if (c.diffusive != CFB200_DIFF_NONE && c.updateVar != CFB200_UV_PVT) return false;
     if (c.diffusive != CFB200_DIFF_NONE && c.derivativeStrategy == CFB200_DV_CORRECTED && c.dim != 2) return false;
-    if (c.diffusive != CFB200_DIFF_NONE && c.derivativeStrategy == CFB200_DV_STATEDIFF) return false;   // its getGradientsJacob is a stub
+    if (c.diffusive != CFB200_DIFF_NONE && (c.derivativeStrategy == CFB200_DV_STATEDIFF ||
+                                            c.derivativeStrategy == CFB200_DV_CORRECTED_GG)) return false;   // getGradientsJacob: stubs
   }
   // Corrected2D/3D reads the cell gradients (uX uY uZ sockets), which only the linear reconstruction computes
   if (c.diffusive == CFB200_DIFF_NS && c.derivativeStrategy != CFB200_DV_DIAMOND &&
-      c.derivativeStrategy != CFB200_DV_STATEDIFF &&
+      c.derivativeStrategy != CFB200_DV_STATEDIFF && c.derivativeStrategy != CFB200_DV_CORRECTED_GG &&
       !(c.derivativeStrategy == CFB200_DV_CORRECTED && c.polyRec != CFB200_PR_CONSTANT))
     return false;
   // background potential field: none or Dipole, MHD3DProjection only ("PFSS" needs the reference's harmonics data)
@@ -136,6 +137,7 @@ public:
   struct Permuted {
     std::vector<double> centres, normals, areas, volumes, cvol;
     std::vector<int32_t> faceL, faceR, faceNodePtr, faceNodes, cellFacePtr, cellFaces, stencilPtr, stencil, nodeNbr, faceBC;
+    std::vector<int32_t> cellNodePtr, cellNodes;
     std::vector<uint8_t> cvSign, updatable;
     cfb200_mesh view;
   };
@@ -202,6 +204,15 @@ public:
     P.nodeNbr.resize((size_t)m.nodeNbrPtr[nn]);
     for (size_t k = 0; k < P.nodeNbr.size(); ++k) P.nodeNbr[k] = st(m.nodeNbr[k]);
     P.view = m;
+    if (m.cellNodePtr && m.cellNodes) {
+      P.cellNodePtr.assign(1, 0);
+      for (int i = 0; i < nc; ++i) {
+        const int o = hCellRef[i];
+        P.cellNodes.insert(P.cellNodes.end(), m.cellNodes + m.cellNodePtr[o], m.cellNodes + m.cellNodePtr[o+1]);
+        P.cellNodePtr.push_back((int32_t)P.cellNodes.size());
+      }
+      P.view.cellNodePtr = P.cellNodePtr.data(); P.view.cellNodes = P.cellNodes.data();
+    }
     P.view.centres = P.centres.data(); P.view.faceL = P.faceL.data(); P.view.faceR = P.faceR.data();
     P.view.faceNodePtr = P.faceNodePtr.data(); P.view.faceNodes = P.faceNodes.data(); P.view.normals = P.normals.data();
     P.view.areas = P.areas.data(); P.view.volumes = P.volumes.data(); P.view.cellFacePtr = P.cellFacePtr.data();
@@ -267,6 +278,75 @@ public:
         sp.push_back((int32_t)st.size());
       }
       d.bndStPtr = upload(sp); d.bndSt = upload(st);
+    }
+    d.ggPtr = nullptr; d.ggNode = nullptr; d.ggAv = nullptr;
+    if (cfg.derivativeStrategy == CFB200_DV_CORRECTED_GG && cfg.diffusive == CFB200_DIFF_NS) {
+      // CorrectedGG2D/3D (CorrectedDerivativeGG2D.cxx:300-397,437-476): (i) per cell the nodes of its faces in the order of
+      // computeGradientsGG (local face by local face, the cell-local face-node table); (ii) per face the entries of the
+      // control-volume list its "average state" reads: the one FOLLOWING each face node of the L cell (see the oracle);
+      // (iii) per boundary face the states across the other faces of the L cell that share a node with it.
+      if (!m.cellNodePtr || !m.cellNodes) throw std::invalid_argument("CorrectedGG needs cfb200_mesh::cellNodePtr / cellNodes");
+      static const int tri[3][2] = {{0,1},{1,2},{2,0}};
+      static const int quad[4][2] = {{0,1},{1,2},{2,3},{3,0}};
+      static const int tet[4][3] = {{0,1,2},{0,3,1},{1,3,2},{0,2,3}};
+      static const int hex[6][4] = {{0,3,2,1},{4,5,6,7},{0,1,5,4},{1,2,6,5},{2,3,7,6},{0,4,7,3}};
+      std::vector<int32_t> gp(1, 0), gn;
+      for (int c = 0; c < nc; ++c) {
+        const int32_t* cn = m.cellNodes + m.cellNodePtr[c];
+        const int ncn = m.cellNodePtr[c+1] - m.cellNodePtr[c];
+        const int nfc = m.cellFacePtr[c+1] - m.cellFacePtr[c];
+        const bool ok = (D == 2) ? ((ncn == 3 && nfc == 3) || (ncn == 4 && nfc == 4)) : ((ncn == 4 && nfc == 4) || (ncn == 8 && nfc == 6));
+        if (!ok) throw std::invalid_argument("CorrectedGG: triangles, quadrilaterals, tetrahedra and hexahedra only");
+        for (int iFace = 0; iFace < nfc; ++iFace) {
+          const int nbN = (D == 2) ? 2 : (ncn == 4 ? 3 : 4);
+          const int* dof = (D == 2) ? (ncn == 3 ? tri[iFace] : quad[iFace]) : (ncn == 4 ? tet[iFace] : hex[iFace]);
+          for (int j = 0; j < nbN; ++j) gn.push_back(cn[dof[j]]);
+        }
+        gp.push_back((int32_t)gn.size());
+      }
+      d.ggPtr = upload(gp); d.ggNode = upload(gn);
+      std::vector<int32_t> sp(1, 0), st;
+      std::vector<int32_t> av((size_t)4*nf, INT32_MIN);
+      for (int f = 0; f < nf; ++f) {
+        const int L = m.faceL[f], R = m.faceR[f];
+        const bool isB = f >= ni;
+        const int32_t* fnB = m.faceNodes + m.faceNodePtr[f];
+        const int32_t* fnE = m.faceNodes + m.faceNodePtr[f+1];
+        const size_t st0 = st.size();
+        if (isB) {
+          for (int k = m.cellFacePtr[L]; k < m.cellFacePtr[L+1]; ++k) {
+            const int cf = m.cellFaces[k];
+            if (cf == f) continue;
+            bool shares = false;
+            for (const int32_t* a = m.faceNodes + m.faceNodePtr[cf]; a != m.faceNodes + m.faceNodePtr[cf+1] && !shares; ++a)
+              shares = std::find(fnB, fnE, *a) != fnE;
+            if (shares) st.push_back(m.faceL[cf] != L ? m.faceL[cf] : m.faceR[cf]);
+          }
+          sp.push_back((int32_t)st.size());
+        }
+        const int32_t* cnL = m.cellNodes + m.cellNodePtr[L];
+        const int nL = m.cellNodePtr[L+1] - m.cellNodePtr[L];
+        int cnt = 0;
+        for (int iNode = 0; iNode < nL; ++iNode) {
+          if (std::find(fnB, fnE, cnL[iNode]) == fnE) continue;
+          const int j = iNode + 1;                      // the entry after this node in [L nodes | R nodes or stencil]
+          int32_t code;
+          if (j < nL) code = cnL[j];
+          else if (!isB) {
+            const int k = j - nL, nR = m.cellNodePtr[R+1] - m.cellNodePtr[R];
+            if (k >= nR) throw std::invalid_argument("CorrectedGG: average state reads past the control volume");
+            code = m.cellNodes[m.cellNodePtr[R] + k];
+          } else {
+            const size_t k = (size_t)(j - nL);
+            if (st0 + k >= st.size()) throw std::invalid_argument("CorrectedGG: average state reads past the control volume");
+            code = ~st[st0 + k];
+          }
+          if (cnt >= 4) throw std::invalid_argument("CorrectedGG: face with more than 4 nodes");
+          av[(size_t)cnt*nf + f] = code; ++cnt;
+        }
+      }
+      d.bndStPtr = upload(sp); d.bndSt = upload(st);
+      d.ggAv = upload(av);
     }
     d.saFace = nullptr;
     if (cfg.fluxSplitter == CFB200_FS_ROESA) {

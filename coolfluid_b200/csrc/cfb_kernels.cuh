@@ -37,6 +37,8 @@ struct Dev {
   const uint8_t* bcFaceFlag;  // [nGhosts] 1 where bcFaceVal replaces BCond::value
   const double* bcWallRatio;  // [nGhosts] (inner-ghost)/(inner-wall) distance ratio of FVMCC_BaseBC::computeGhostPosition, or null
   const int* bndStPtr; const int* bndSt;           // Corrected2D/3D: gradient stencil of each boundary face (CSR over ghosts)
+  const int* ggPtr; const int* ggNode;   // CorrectedGG: per cell, the nodes of its faces in computeGradientsGG order (CSR over cells)
+  const int* ggAv;            // CorrectedGG: [4][nFaces] entries of the "average state": node id >= 0, ~state id < 0, INT32_MIN none
   const int* saFace;          // "RoeSA": [2*CFB_SA_WIDTH][nFaces] faces of the L / R cell entering etaSA (-1 = none), or null
   const uint8_t* updatable;
   const uint8_t* cellActive;  // cell touches at least one face with an updatable side

@@ -115,6 +115,7 @@ struct cfb200_meshdata {
   std::vector<double> nodes, centres, normals, areas, volumes, nodeW, cvol, faceCentres;
   std::vector<int32_t> faceL, faceR, faceNodePtr, faceNodes, faceGeoID, faceBC, cellFacePtr, cellFaces;
   std::vector<int32_t> stencilPtr, stencil, nodeNbrPtr, nodeNbr, trsPtr, bsrRowPtr, bsrColInd;
+  std::vector<int32_t> cellNodePtr, cellNodes;     // the caller's connectivity, kept for CorrectedGG (cfb200_mesh::cellNodes)
   std::vector<uint8_t> cvSign, updatable;
 };
 
@@ -127,6 +128,8 @@ void build(cfb200_meshdata& M, int dim, int nNodes, const double* nodes, int nCe
   M.dim = dim; M.nCells = nCells; M.nNodes = nNodes; M.nTRS = nTRS;
   M.nodes.assign(nodes, nodes + (size_t)nNodes*D);
   M.updatable.assign(nCells, 1);
+  M.cellNodePtr.assign(cnPtr, cnPtr + nCells + 1);
+  M.cellNodes.assign(cn, cn + cnPtr[nCells]);
   for (int e = 0; e < nCells; ++e)
     if (shape[e] < 0 || shape[e] > 3 || cnPtr[e+1] - cnPtr[e] != (shape[e] == SH_TRIAG ? 3 : shape[e] == SH_HEXA ? 8 : 4))
       throw std::invalid_argument("unsupported element");
@@ -556,6 +559,7 @@ void cfb200_mesh_view(const cfb200_meshdata* M, cfb200_mesh* o) {
   o->cellFaces = M->cellFaces.data(); o->stencilPtr = M->stencilPtr.data(); o->stencil = M->stencil.data();
   o->nodeNbrPtr = M->nodeNbrPtr.data(); o->nodeNbr = M->nodeNbr.data(); o->nodeW = M->nodeW.data();
   o->cvol = M->cvol.data(); o->cvSign = M->cvSign.data(); o->faceBC = M->faceBC.data(); o->updatable = M->updatable.data();
+  o->cellNodePtr = M->cellNodePtr.data(); o->cellNodes = M->cellNodes.data();
 }
 
 void cfb200_mesh_set_updatable(cfb200_meshdata* M, const uint8_t* updatable) {

@@ -35,7 +35,7 @@ class MeshStruct(C.Structure):   # cfb200_mesh
                 ("faceNodes", P_I), ("normals", P_D), ("areas", P_D), ("volumes", P_D),
                 ("cellFacePtr", P_I), ("cellFaces", P_I), ("stencilPtr", P_I), ("stencil", P_I),
                 ("nodeNbrPtr", P_I), ("nodeNbr", P_I), ("nodeW", P_D), ("cvol", P_D), ("cvSign", P_U8),
-                ("faceBC", P_I), ("updatable", P_U8)]
+                ("faceBC", P_I), ("updatable", P_U8), ("cellNodePtr", P_I), ("cellNodes", P_I)]
 
 
 class GmresParams(C.Structure):  # cfb200_gmres_params

@@ -81,7 +81,10 @@ typedef struct cfb200_bc {
 /* DerivativeComputer of the diffusive flux: DiamondVolume2D/3D (DiamondVolume{2,3}DDerivative.cxx, the default) or
  * Corrected2D/3D (CorrectedDerivative2D.cxx:91-430, CorrectedDerivative3D.cxx:54-176) */
 enum cfb200_derivative { CFB200_DV_DIAMOND = 0, CFB200_DV_CORRECTED = 1,
-                         CFB200_DV_STATEDIFF = 2 /* "StateDiff" plugins/FiniteVolume/StateDiffDerivative.cxx:56-131 */ };
+                         CFB200_DV_STATEDIFF = 2 /* "StateDiff" plugins/FiniteVolume/StateDiffDerivative.cxx:56-131 */,
+                         CFB200_DV_CORRECTED_GG = 3 /* "CorrectedGG2D/3D" plugins/FiniteVolume/CorrectedDerivativeGG2D.cxx,
+                                                       CorrectedDerivativeGG3D.cxx: the Corrected face gradient with Green-Gauss
+                                                       cell gradients over the nodal states; needs cfb200_mesh::cellNodes */ };
 
 /* Everything ComputeRHS reads from the .CFcase and from SubSystemStatus (SURVEY.md §8b "Scalars crossing per call").
  * The per-call scalars (iter, residual, resFactor, cfl, computeJacobian) may be changed between calls with
@@ -160,7 +163,8 @@ typedef struct cfb200_config {
   double mhdDipole[3];
   int32_t noLimiterVar[CFB200_MAXEQ]; /* Venktn2D option "2DNoLimiterID" (Venktn2D.cxx:40-41,253-258): 1 = the limiter of this
                                        * variable is forced to 1 */
-  int32_t reservedTail;
+  int32_t correctedGGUseWeights;      /* CorrectedGG2D/3D option "useWeights" (CorrectedDerivativeGG2D.cxx:60-61,72-75): inverse
+                                       * distance weights in the least squares of the boundary faces (default: none) */
 } cfb200_config;
 
 /* Flat mesh data = the contents of the reference's sockets and connectivity tables (SURVEY.md §8b "Data ownership").
@@ -188,6 +192,8 @@ typedef struct cfb200_mesh {
   const uint8_t* cvSign;       /* [nFaces]      _changeNormalSign */
   const int32_t* faceBC;       /* [nFaces]      -1 inner, else boundary-condition index */
   const uint8_t* updatable;    /* [nCells]      State::isParUpdatable() */
+  const int32_t* cellNodePtr;  /* [nCells+1]    connectivity "cellNodes_InnerCells" (cell-local node order); optional (NULL) */
+  const int32_t* cellNodes;    /*               unless derivativeStrategy = CFB200_DV_CORRECTED_GG */
 } cfb200_mesh;
 
 /* Device view of the block Jacobian (LSSMatrix replacement; BlockAccumulator.hh:289-296 sub-block layout [ib][jb]). */

@@ -23,7 +23,8 @@ class MeshView(C.Structure):
                 ("faceNodes", P_I), ("normals", P_D), ("areas", P_D), ("volumes", P_D),
                 ("cellFacePtr", P_I), ("cellFaces", P_I), ("stencilPtr", P_I), ("stencil", P_I),
                 ("nodeNbrPtr", P_I), ("nodeNbr", P_I), ("nodeW", P_D), ("cvol", P_D), ("cvSign", P_U8),
-                ("faceBC", P_I), ("updatable", P_U8), ("bcFaceVal", P_D), ("bcFaceFlag", P_U8)]
+                ("faceBC", P_I), ("updatable", P_U8), ("cellNodePtr", P_I), ("cellNodes", P_I),
+                ("bcFaceVal", P_D), ("bcFaceFlag", P_U8)]
 
 
 class Outputs(C.Structure):

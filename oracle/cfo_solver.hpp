@@ -679,8 +679,191 @@ public:
     }
   }
 
+  // ---- a15, fourth DerivativeComputer: "CorrectedGG2D" / "CorrectedGG3D" (CorrectedDerivativeGG2D.cxx:108-487,
+  // CorrectedDerivativeGG3D.cxx:56-150) inside NSFlux.ci:59-156.  The Corrected face gradient
+  //   grad = (vR - vL)/|xR - xL| * (e.n) n + (I - n n) 0.5 (gradL + gradR)
+  // with gradL / gradR the Green-Gauss gradients of the two cells over the NODAL states (sum over the cell's faces of
+  // the face-averaged nodal state times the outward area normal, divided by the cell volume).  On a boundary face gradR is
+  // a least-squares gradient at the ghost centre over the states across the other faces of the left cell that share a node
+  // with the face, unweighted unless "useWeights".
+  // The control-volume list is states = [L, R, nodal states of the L cell (cell-local order), nodal states of the R cell |
+  // boundary stencil].  _currFaceNodeIDs collects `counter` AFTER `states[counter++] = ...` (:317-321), so the "average
+  // state of the face nodes" of computeAverageValues (:277-296) reads the entry FOLLOWING each face node of the L cell: the
+  // next L-cell node, or the first R-cell node / stencil state after the last one.  Restated as it is.
+  static const int* ggFaceDof(int nbCellNodes, int iFace, int& nb) {     // LocalConnectionDataBuilder (as cfo_mesh.hpp faceDof)
+    static const int tri[3][2] = {{0,1},{1,2},{2,0}};
+    static const int quad[4][2] = {{0,1},{1,2},{2,3},{3,0}};
+    static const int tet[4][3] = {{0,1,2},{0,3,1},{1,3,2},{0,2,3}};
+    static const int hex[6][4] = {{0,3,2,1},{4,5,6,7},{0,1,5,4},{1,2,6,5},{2,3,7,6},{0,4,7,3}};
+    if (D == 2) { nb = 2; return (nbCellNodes == 3) ? tri[iFace] : quad[iFace]; }
+    if (nbCellNodes == 4) { nb = 3; return tet[iFace]; }
+    if (nbCellNodes == 8) { nb = 4; return hex[iFace]; }
+    throw std::runtime_error("CorrectedGG: prisms and pyramids are not provided");
+  }
+  // computeGradientsGG (CorrectedDerivativeGG2D.cxx:437-476): ux[iDim][iVar]
+  void gradientsGG(int cell, const Outputs& o, double ux[3][Q]) const {
+    if (!mesh.cellNodePtr) throw std::runtime_error("CorrectedGG needs the cellNodes connectivity");
+    const int32_t* cn = &mesh.cellNodes[mesh.cellNodePtr[cell]];
+    const int nbCellNodes = mesh.cellNodePtr[cell+1] - mesh.cellNodePtr[cell];
+    for (int a = 0; a < 3; ++a) for (int i = 0; i < Q; ++i) ux[a][i] = 0.0;
+    const int fb = mesh.cellFacePtr[cell], fe = mesh.cellFacePtr[cell+1];
+    for (int iFace = 0; iFace < fe - fb; ++iFace) {
+      const int faceID = mesh.cellFaces[fb + iFace];
+      double fnormal[3] = {0., 0., 0.};
+      for (int iDim = 0; iDim < D; ++iDim) {
+        fnormal[iDim] = mesh.normals[(size_t)faceID*D + iDim];
+        if (mesh.faceL[faceID] != cell) fnormal[iDim] *= -1.;      // isOutward[faceID] != state->getLocalID()
+      }
+      int nbNodesInFace;
+      const int* dof = ggFaceDof(nbCellNodes, iFace, nbNodesInFace);
+      const double invNodesInFace = 1./nbNodesInFace;
+      for (int i = 0; i < Q; ++i)
+        for (int iNode = 0; iNode < nbNodesInFace; ++iNode) {
+          const double vOvN = o.nstates[(size_t)cn[dof[iNode]]*Q + i]*invNodesInFace;
+          for (int iDim = 0; iDim < D; ++iDim) ux[iDim][i] += vOvN*fnormal[iDim];
+        }
+    }
+    for (int a = 0; a < D; ++a) for (int i = 0; i < Q; ++i) ux[a][i] /= mesh.volumes[cell];
+  }
+  void diffusiveFluxCorrectedGG(FaceCtx& x, const double* U, bool isPerturb, int iPerturbVar, Outputs& o, double* dflux) {
+    const int nb = mesh.faceNodePtr[x.f+1] - mesh.faceNodePtr[x.f];
+    const int32_t* fn = &mesh.faceNodes[mesh.faceNodePtr[x.f]];
+    const double* cL = &mesh.centres[(size_t)x.L*D];
+    const double* cR = &mesh.centres[(size_t)x.R*D];
+    if (!mesh.cellNodePtr) throw std::runtime_error("CorrectedGG needs the cellNodes connectivity");
+    const int32_t* cnL = &mesh.cellNodes[mesh.cellNodePtr[x.L]];
+    const int nL = mesh.cellNodePtr[x.L+1] - mesh.cellNodePtr[x.L];
+    if (!isPerturb) {
+      // setControlVolumeStates (:300-397): the boundary stencil
+      x.nCorr = 0;
+      if (x.isB) {
+        for (int k = mesh.cellFacePtr[x.L]; k < mesh.cellFacePtr[x.L+1]; ++k) {
+          const int cf = mesh.cellFaces[k];
+          if (cf == x.f) continue;
+          bool sharesNode = false;
+          const int32_t* cfn = &mesh.faceNodes[mesh.faceNodePtr[cf]];
+          const int cnb = mesh.faceNodePtr[cf+1] - mesh.faceNodePtr[cf];
+          for (int j = 0; j < nb && !sharesNode; ++j)
+            for (int m = 0; m < cnb; ++m) if (cfn[m] == fn[j]) { sharesNode = true; break; }
+          if (sharesNode) x.corrStencil[x.nCorr++] = (mesh.faceL[cf] != x.L) ? mesh.faceL[cf] : mesh.faceR[cf];
+        }
+      }
+      // computeControlVolume (:222-263)
+      x.dr = getDistance<D>(cL, cR);
+      double eRL[3] = {0., 0., 0.};
+      for (int k = 0; k < D; ++k) eRL[k] = cR[k] - cL[k];
+      for (int k = 0; k < D; ++k) eRL[k] /= x.dr;
+      double eDotN = 0.0;
+      for (int k = 0; k < D; ++k) eDotN += eRL[k]*x.n[k];
+      for (int k = 0; k < D; ++k) x.eRLdotNN[k] = eDotN*x.n[k];
+      for (int a = 0; a < D; ++a)
+        for (int b = 0; b < D; ++b)
+          x.oEminusNN[a][b] = (a == b) ? 1.0 - x.n[a]*x.n[a] : -(x.n[std::min(a, b)]*x.n[std::max(a, b)]);
+      x.volume = x.isB ? mesh.volumes[x.L] : 0.5*(mesh.volumes[x.L] + mesh.volumes[x.R]);
+    }
+    const double* sL = &U[(size_t)x.L*Q];
+    const double* sR = &U[(size_t)x.R*Q];
+    double uxL[3][Q], uxR[3][Q];
+    gradientsGG(x.L, o, uxL);
+    if (!x.isB) gradientsGG(x.R, o, uxR);
+    else {
+      // computeBoundaryGradients (2D :146-217, 3D :56-150)
+      double l11 = 0.0, l12 = 0.0, l13 = 0.0, l22 = 0.0, l23 = 0.0, l33 = 0.0;
+      double lf1[Q], lf2[Q], lf3[Q];
+      for (int i = 0; i < Q; ++i) { lf1[i] = 0.0; lf2[i] = 0.0; lf3[i] = 0.0; }
+      for (int in = 0; in < x.nCorr; ++in) {
+        const double* nodeLast = &mesh.centres[(size_t)x.corrStencil[in]*D];
+        const double weight = (!cfg.correctedGGUseWeights) ? 1.0 : 1.0/getDistance<D>(cR, nodeLast);
+        const double dx = weight*(nodeLast[0] - cR[0]);
+        const double dy = weight*(nodeLast[1] - cR[1]);
+        const double dz = (D == 3) ? weight*(nodeLast[D-1] - cR[D-1]) : 0.0;
+        l11 += dx*dx; l12 += dx*dy; l22 += dy*dy;
+        if (D == 3) { l13 += dx*dz; l23 += dy*dz; l33 += dz*dz; }
+        const double* sv = &U[(size_t)x.corrStencil[in]*Q];
+        for (int i = 0; i < Q; ++i) {
+          const double du = weight*(sv[i] - sR[i]);
+          lf1[i] += dx*du; lf2[i] += dy*du;
+          if (D == 3) lf3[i] += dz*du;
+        }
+      }
+      if (D == 2) {
+        const double invDet = 1./(l11*l22 - l12*l12);
+        for (int i = 0; i < Q; ++i) {
+          uxR[0][i] = (l22*lf1[i] - l12*lf2[i])*invDet;
+          uxR[1][i] = (l11*lf2[i] - l12*lf1[i])*invDet;
+          uxR[2][i] = 0.;
+        }
+      } else {
+        const double invDet = 1./(l11*l22*l33 - l11*l23*l23 - l12*l12*l33 + l12*l13*l23 + l13*l12*l23 - l13*l13*l22);
+        const double linv11 = l22*l33 - l23*l23, linv22 = l11*l33 - l13*l13, linv33 = l11*l22 - l12*l12;
+        const double linv12 = -(l12*l33 - l13*l23), linv13 = l12*l23 - l13*l22, linv23 = -(l11*l23 - l13*l12);
+        for (int i = 0; i < Q; ++i) {
+          uxR[0][i] = (linv11*lf1[i] + linv12*lf2[i] + linv13*lf3[i])*invDet;
+          uxR[1][i] = (linv12*lf1[i] + linv22*lf2[i] + linv23*lf3[i])*invDet;
+          uxR[2][i] = (linv13*lf1[i] + linv23*lf2[i] + linv33*lf3[i])*invDet;
+        }
+      }
+    }
+    double grad[Q][3];
+    for (int i = 0; i < Q; ++i) {
+      const double dv = (sR[i] - sL[i])/x.dr;
+      double gradLR[3] = {0., 0., 0.};
+      for (int a = 0; a < D; ++a) gradLR[a] = 0.5*(uxL[a][i] + uxR[a][i]);
+      for (int a = 0; a < D; ++a) {
+        double res = 0.0;
+        for (int k = 0; k < D; ++k) res += x.oEminusNN[a][k]*gradLR[k];
+        grad[i][a] = dv*x.eRLdotNN[a] + res;
+      }
+      if (D == 2) grad[i][2] = 0.;
+    }
+    // computeAverageValues (:277-296) with the shifted ids (see above): entry j of the control-volume list
+    auto cvEntry = [&](int j) -> const double* {
+      if (j == 0) return sL;
+      if (j == 1) return sR;
+      if (j < 2 + nL) return &o.nstates[(size_t)cnL[j - 2]*Q];
+      const int k = j - 2 - nL;
+      if (!x.isB) {
+        const int nR = mesh.cellNodePtr[x.R+1] - mesh.cellNodePtr[x.R];
+        if (k >= nR) throw std::runtime_error("CorrectedGG: average state reads past the control volume");
+        return &o.nstates[(size_t)mesh.cellNodes[mesh.cellNodePtr[x.R] + k]*Q];
+      }
+      if (k >= x.nCorr) throw std::runtime_error("CorrectedGG: average state reads past the control volume");
+      return &U[(size_t)x.corrStencil[k]*Q];
+    };
+    double avState[Q];
+    const double invNbNodes = 1./static_cast<double>(nb);
+    for (int i = 0; i < Q; ++i) {
+      avState[i] = 0.0;
+      for (int iNode = 0; iNode < nL; ++iNode) {
+        bool inFace = false;
+        for (int j = 0; j < nb; ++j) if (fn[j] == cnL[iNode]) inFace = true;    // face->containNode(nodesL[iNode])
+        if (inFace) avState[i] += cvEntry(2 + iNode + 1)[i];
+      }
+      avState[i] *= invNbNodes;
+    }
+    bool useBackUp = false, setBackUp = false;
+    if (isPerturb && iPerturbVar != P::TID) useBackUp = true;
+    else if (!isPerturb) setBackUp = true;
+    double mu, lambda;
+    if (useBackUp || freezeCoeff) { mu = x.muBkp; lambda = x.lambdaBkp; }
+    else {
+      mu = P::dynViscosity(cfg, avState)*cfg.artDiffCoeff;
+      lambda = P::thermConductivity(cfg, mu);
+      if (setBackUp) { x.muBkp = mu; x.lambdaBkp = lambda; }
+    }
+    P::nsFluxUnit(cfg, avState, grad, x.n, mu, lambda, dflux);
+    for (int i = 0; i < Q; ++i) dflux[i] *= x.area;
+    if (!isPerturb) {
+      const double nu = mu/P::nsDensity(cfg, avState);
+      const double diffUpdateCoeff = nu*x.area*x.area/x.volume;
+      o.updateCoeff[x.L] += diffUpdateCoeff;
+      if (!x.isB) o.updateCoeff[x.R] += diffUpdateCoeff;
+    }
+  }
+
   void diffusiveFlux(FaceCtx& x, const double* U, bool isPerturb, int iPerturbVar, Outputs& o, double* dflux) {
     if (cfg.derivativeStrategy == 1) { diffusiveFluxCorrected(x, U, isPerturb, iPerturbVar, o, dflux); return; }
+    if (cfg.derivativeStrategy == 3) { diffusiveFluxCorrectedGG(x, U, isPerturb, iPerturbVar, o, dflux); return; }
     if (cfg.derivativeStrategy == 2) { diffusiveFluxStateDiff(x, U, isPerturb, iPerturbVar, o, dflux); return; }
     const int nb = mesh.faceNodePtr[x.f+1] - mesh.faceNodePtr[x.f];
     const int32_t* fn = &mesh.faceNodes[mesh.faceNodePtr[x.f]];

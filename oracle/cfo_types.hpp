@@ -101,7 +101,7 @@ struct Config {
   int32_t entropyFixID;   // RoeEntropyFixFlux.cxx:35 (0 = plain RoeFlux, 1 | 2 = "RoeEntropyFix")
   double refSpeed;        // MHDProjectionTerm refSpeed (hyperbolic divergence cleaning speed)
   double coeffSigmoid;    // AUSMFlux.ci:64 coeffSigmoid (1e-8): blending of the sigmoid switches of the analytic Jacobian
-  int32_t derivativeStrategy;  // 0 DiamondVolume{2,3}D (CellCenterFVMData.cxx:298 default), 1 Corrected{2,3}D, 2 StateDiff
+  int32_t derivativeStrategy;  // 0 DiamondVolume{2,3}D (CellCenterFVMData.cxx:298 default), 1 Corrected{2,3}D, 2 StateDiff, 3 CorrectedGG{2,3}D
   int32_t fuseTimeRhs;         // product-side scheduling flag (no meaning for the oracle)
   // FVMCC_StdComputeTimeRhs.cxx:42-57 zeroDiagValue; FVMCC_PseudoSteadyTimeRhs.cxx:40-46 useAnalyticalMatrix, useGlobalDT
   int32_t timeZeroDiag[MAXEQ];
@@ -116,7 +116,7 @@ struct Config {
   int32_t mhdPotentialBType;   // MHDTerm.cxx:25: 0 none, 1 "Dipole"
   double mhdDipole[3];         // MHDTerm.cxx:38-40 mX mY mZ
   int32_t noLimiterVar[MAXEQ]; // Venktn2D.cxx:40-41,253-258 "2DNoLimiterID" as a per-variable flag
-  int32_t reservedTail;
+  int32_t correctedGGUseWeights; // CorrectedDerivativeGG2D.cxx:60-61
 };
 
 struct MeshView {
@@ -141,6 +141,8 @@ struct MeshView {
   const uint8_t* cvSign;    // [nFaces] _changeNormalSign
   const int32_t* faceBC;    // [nFaces] -1 inner, else index into the BC array
   const uint8_t* updatable; // [nCells] isParUpdatable
+  const int32_t* cellNodePtr; // [nCells+1] cell -> nodes in the cell-local order (CorrectedGG only; may be NULL otherwise)
+  const int32_t* cellNodes;
   // position-dependent Dirichlet data (SuperInlet.cxx:156-209 with a parsed Def function evaluated at the boundary
   // point of each face): when bcFaceFlag[ghost] is set, BC_DIRICHLET reads bcFaceVal[ghost*q + v] instead of BC::value
   const double* bcFaceVal;    // [nGhosts*q] or NULL

@@ -215,13 +215,17 @@ void FVMCC_ComputeRHSB200::fillConfig(cfb200_config& c)
 
   // ---- diffusive flux
   c.diffusive = md.getDiffusiveFluxComputer()->isNull() ? CFB200_DIFF_NONE : CFB200_DIFF_NS;
-  // CellCenterFVM.Data.DerivativeStrategy: DiamondVolume2D/3D (CellCenterFVMData.cxx:298 default), Corrected2D/3D or StateDiff
+  // CellCenterFVM.Data.DerivativeStrategy: DiamondVolume2D/3D (CellCenterFVMData.cxx:298 default), Corrected2D/3D, CorrectedGG2D/3D or StateDiff
   const std::string deriv = md.getDerivativeComputer()->getName();
   if (deriv == "Corrected2D" || deriv == "Corrected3D") c.derivativeStrategy = CFB200_DV_CORRECTED;
   else if (deriv == "StateDiff") c.derivativeStrategy = CFB200_DV_STATEDIFF;
+  else if (deriv == "CorrectedGG2D" || deriv == "CorrectedGG3D") {
+    c.derivativeStrategy = CFB200_DV_CORRECTED_GG;
+    c.correctedGGUseWeights = optInt(*md.getDerivativeComputer(), "useWeights", 0);    // CorrectedDerivativeGG2D.cxx:60-61,72-75
+  }
   else if (deriv == "DiamondVolume2D" || deriv == "DiamondVolume3D" || c.diffusive == CFB200_DIFF_NONE)
     c.derivativeStrategy = CFB200_DV_DIAMOND;
-  else c.derivativeStrategy = -1;      // CorrectedGG*, ...: cfb200_create answers CFB200_ERR_UNSUPPORTED
+  else c.derivativeStrategy = -1;      // anything else: cfb200_create answers CFB200_ERR_UNSUPPORTED
   c.coeffTau = 1.0; c.coeffQ = 1.0; c.cpOverPrandtl = 1.0; c.muRef = 1.0; c.artDiffCoeff = 1.0;
   if (c.diffusive == CFB200_DIFF_NS) {
     SafePtr<Physics::NavierStokes::NSTerm> ns = pm->getDiffusiveTerm().d_castTo<Physics::NavierStokes::NSTerm>();
@@ -493,6 +497,17 @@ void FVMCC_ComputeRHSB200::uploadMesh()
   mesh.stencilPtr = &stencilPtr[0]; mesh.stencil = &stencilIdx[0];
   mesh.nodeNbrPtr = &nodeNbrPtr[0]; mesh.nodeNbr = &nodeNbr[0]; mesh.nodeW = &nodeW[0];
   mesh.faceBC = &faceBC[0]; mesh.updatable = &updatable[0];
+  // cell -> nodes in the cell-local order (CorrectedGG2D/3D builds each cell with CellTrsGeoBuilder: the order of the
+  // "cellNodes_InnerCells" connectivity, CorrectedDerivativeGG2D.cxx:306-322)
+  std::vector<CFint> cellNodePtr(1, 0), cellNodesIdx;
+  {
+    SafePtr<ConnectivityTable<CFuint> > cn = MeshDataStack::getActive()->getConnectivity("cellNodes_InnerCells");
+    for (CFuint c = 0; c < nCells; ++c) {
+      for (CFuint k = 0; k < cn->nbCols(c); ++k) cellNodesIdx.push_back((CFint)(*cn)(c, k));
+      cellNodePtr.push_back((CFint)cellNodesIdx.size());
+    }
+  }
+  mesh.cellNodePtr = &cellNodePtr[0]; mesh.cellNodes = &cellNodesIdx[0];
   std::vector<CFreal> cvol(faceL.size());
   std::vector<uint8_t> cvSign(faceL.size());
   mesh.cvol = &cvol[0]; mesh.cvSign = &cvSign[0];

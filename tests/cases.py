@@ -296,6 +296,16 @@ CASES = {
                                                 flux=B.FS_AUSMPLUS), bcs_ns3d, True),
     "ns3d_hex_statediff": (lambda: meshgen.hex_box(5, 4, 4), lambda: ns3d_cfg(derivative="statediff", res_factor=0.5),
                            bcs_ns3d, True),
+    # a15, fourth derivative computer: "CorrectedGG2D/3D" (Green-Gauss cell gradients over the nodal states; boundary least
+    # squares over the face neighbours; the shifted "average state" of the reference)
+    "ns2d_quad_correctedgg": (lambda: meshgen.quad_channel(10, 8), lambda: ns2d_cfg(derivative="correctedgg"), bcs_ns2d, True),
+    "ns2d_tri_correctedgg_weights": (lambda: meshgen.quad_channel(10, 8, triangles=True),
+                                     lambda: ns2d_cfg(derivative="correctedgg", gg_use_weights=1, res_factor=0.5),
+                                     bcs_ns2d, True),
+    "ns3d_hex_correctedgg": (lambda: meshgen.hex_box(5, 4, 4), lambda: ns3d_cfg(derivative="correctedgg"), bcs_ns3d, True),
+    "ns3d_tet_correctedgg_ausmplus": (lambda: meshgen.tet_box(3, 3, 3),
+                                      lambda: ns3d_cfg(derivative="correctedgg", flux=B.FS_AUSMPLUS, gg_use_weights=1),
+                                      bcs_ns3d, True),
     "ns3d_single_cell_corrected": (lambda: meshgen.hex_box(1, 1, 1, jitter=0.0), lambda: ns3d_cfg(derivative="corrected"),
                                    bcs_ns3d, True),
     # a16: FarFieldEuler2D (conservative) / FarFieldEuler3D (Cons, Pvt): subsonic in/outflow and, with the fast initial
