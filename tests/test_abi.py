@@ -63,6 +63,9 @@ def test_invalid_arguments(product_lib):
     cfg = B.make_config(2, diffusive=B.DIFF_NS, update_var=B.UV_PVT, derivative="corrected")   # needs the LSQ gradients
     assert product_lib.create(C.byref(cfg), 0, C.byref(h)) == 6
     cfg = B.make_config(2, diffusive=B.DIFF_NS, update_var=B.UV_PVT, poly_rec=B.PR_LINEARLS)
-    cfg.derivativeStrategy = 3                                    # CorrectedGG / StateDiff: not implemented
+    cfg.derivativeStrategy = 4                                    # not a derivative computer
+    assert product_lib.create(C.byref(cfg), 0, C.byref(h)) == 6
+    cfg = B.make_config(2, flux=B.FS_AUSMPLUSUP, mach_inf=0.3, diffusive=B.DIFF_NS, update_var=B.UV_PVT,
+                        jacobian="analytic", derivative="correctedgg")      # getGradientsJacob of CorrectedGG is a stub
     assert product_lib.create(C.byref(cfg), 0, C.byref(h)) == 6
     assert product_lib.compute_rhs(None, 1, None, None) == 2
