@@ -197,6 +197,10 @@ __global__ void __launch_bounds__(256) k_block_min(const double* __restrict__ x,
   if (threadIdx.x == 0) out[blockIdx.x] = s[0];
 }
 
+// resident 128-thread blocks per SM a staged face functor asks for (F::STAGED_MINB), 2 unless it says otherwise
+template <class F, class = void> struct StagedMinB { static constexpr int value = 2; };
+template <class F> struct StagedMinB<F, std::void_t<decltype(F::STAGED_MINB)> > { static constexpr int value = F::STAGED_MINB; };
+
 template <class F, class = void> struct HasMinB : std::false_type {};
 template <class F> struct HasMinB<F, std::void_t<decltype(F::MINB)> > : std::true_type {};
 
@@ -309,7 +313,7 @@ struct CudaBackend {
       // without this the driver sizes the shared-memory carve-out for ONE block and the intended number of resident
       // blocks does not fit.  Ask for just what two resident blocks need (+ 1 KB each of system use): the rest of the
       // 256 KB stays L1 for the gathers of the prologue (measured 31.45 -> 30.56 ms against the maximum carve-out)
-      int pct = (int)((2*(smem + 1024)*100 + 228*1024 - 1)/(228*1024)) + 3;
+      int pct = (int)((StagedMinB<F>::value*(smem + 1024)*100 + 228*1024 - 1)/(228*1024)) + 3;
       if (pct > 100) pct = 100;
       CFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
       kern<<<(n + BS - 1)/BS, BS, smem, stream>>>(f, n);
@@ -319,7 +323,7 @@ struct CudaBackend {
     // (3 and 4 resident blocks = 168 / 128 registers were measured 17 % and more slower, DESIGN.md §4.2, and are no longer
     // compiled: they tripled the build time of the face kernels)
     (void)minBlocks;
-    go(k_staged<F, 128, 2>, 128);                       //  8 warps per SM, 255 registers
+    go(k_staged<F, 128, StagedMinB<F>::value>, 128);    //  2: 8 warps per SM, 255 registers (the FD kernels)
     CFB_CUDA(cudaGetLastError());
     if (ev) CFB_CUDA(cudaEventRecord(ev->b, stream));
   }

@@ -971,6 +971,11 @@ struct AnalyticInnerFaceK {   // idx over interior faces; staged like InnerFaceK
   static constexpr int BLK = Q*Q;
   static constexpr int NOUT = 2*Q*Q;
   static constexpr int STAGE = NOUT + 2;
+  // one straight evaluation per face, no finite-difference loop to amortise the prologue gathers over: latency-bound at
+  // 8 warps per SM (profile: 12 % occupancy, 42 % FP64 pipe), so three resident blocks (168 registers) instead of two:
+  // 14.7 -> 12.2 ms for configs[2] at 220^3, 8.0 -> 7.8 ms for configs[1] at 4096^2; four (128 registers, 900 B of stack)
+  // were measured at 17.6 / 9.2 ms
+  static constexpr int STAGED_MINB = 3;
   Dev d; Cfg c;
   CFB_HD double* out() const { return d.bsrVal; }
   CFB_HD void slots(int f, int& s0, int& s1) const { s0 = d.slotRL[f]; s1 = d.slotLR[f]; }
@@ -1067,14 +1072,15 @@ struct AnalyticInnerFaceK {   // idx over interior faces; staged like InnerFaceK
     const double rf = c.resFactor;
     typename P::JSide jl, jr;
     typename P::JPvt kp;
+    typename P::JPre kc;
     const bool pvt = (c.updateVar == CFB200_UV_PVT);            // AUSMPlusUpFlux.ci:1238-1273
     if (pvt) P::jprePvt(c, pL, pR, w.n, kp);
-    else { P::jside(c, vL, jl); P::jside(c, vR, jr); }
+    else { P::jside(c, vL, jl); P::jside(c, vR, jr); P::jpre(c, jl, jr, w.n, kc); }   // once for both sides
 #pragma unroll 1
     for (int side = 0; side < 2; ++side) {
       double J[Q*Q];
       if (pvt) P::ausmUpJacobPvt(c, kp, pL, pR, w.n, side, J);
-      else P::ausmUpJacobCons(c, jl, jr, w.n, side, J);
+      else P::ausmUpJacobCons(c, kc, jl, jr, w.n, side, J);
 #pragma unroll
       for (int k = 0; k < Q*Q; ++k) J[k] *= w.area;             // FVMCC_FluxSplitter.hh:88-96
       if (hasDiff) {
