@@ -843,6 +843,10 @@ struct InnerFaceK {   // idx over interior faces; FS = 0 Roe, 1 AUSM+ / AUSM+up,
   static constexpr int BLK = Q*Q;
   static constexpr int NOUT = 2*Q*Q;    // per-thread staging (shared memory, entry k at stg[k*stride]): block(R,L) | block(L,R)
   static constexpr bool PIPE = JAC && (FS == 0 || FS == 3) && UV >= 0;
+  // RHS-only launches (one evaluation per face, k_run): three resident 128-thread blocks per SM (168 registers), as for
+  // the analytic kernel (6.10 ms at 220^3 against 6.3 with two blocks and 6.99 with four); the Jacobian variants go
+  // through launchStaged, which does not read this
+  static constexpr int MINB = 3;
   // ... | fixed side s z f (un a) | base flux (loop-carried state of the FD loop); PIPE: FaceWork::RP_STAGE
   static constexpr int STAGE = PIPE ? FaceWork<D>::RP_STAGE(FS == 3) : NOUT + 4*Q + ((FS == 3 || FS == 4) ? 2 : 0);
   Dev d; Cfg c;
