@@ -57,6 +57,10 @@ def test_partition_structure():
 @pytest.mark.parametrize("name,nparts,order", [("ns3d_hex", 2, "global"), ("euler2d_2nd_tri_fullstencil", 3, "global"),
                                                ("ns3d_tet", 2, "global"), ("ns2d_quad", 2, "global"),
                                                ("mhd3d_hex_hll", 2, "global"), ("ns3d_hex_corrected", 3, "global"),
+                                               ("ns3d_hex_roesa_fix2", 2, "global"), ("ns3d_tet_roesa", 3, "global"),
+                                               ("ns3d_hex_correctedgg", 2, "global"), ("ns2d_quad_statediff", 2, "global"),
+                                               ("ns3d_hex_ausmplusup_analytic", 2, "global"),
+                                               ("mhd3d_hex_hll_dipole", 2, "global"),
                                                ("ns3d_hex", 2, "grouped"), ("ns3d_tet", 2, "grouped")])
 def test_partition_matches_single_domain(name, nparts, order, oracle, hostsim_lib):
     mesh_f, cfg_f, bcs_f, pvt = cases.CASES[name]
