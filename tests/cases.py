@@ -532,7 +532,7 @@ def check_time_term_variants(oracle, engine_factory):
 
 
 def check_renumbering_layer(oracle, engine_factory, names=("ns3d_hex", "ns3d_tet", "euler2d_2nd_tri_fullstencil", "ns2d_quad_corrected",
-                                                            "mhd3d_hex_hll", "euler2d_ausmplusup_analytic", "ns3d_hex_roe_efix2")):
+                                                            "mhd3d_hex_hll", "euler2d_ausmplusup_analytic", "ns3d_hex_roe_efix2", "ns3d_hex_roesa_fix2", "ns3d_hex_correctedgg", "ns2d_tri_correctedgg_weights")):
     """cfg.renumber: the engine stores cells along a space-filling curve and faces by their cells, yet everything it returns
     is in the caller's numbering and bit-identical to the oracle on the caller's (here: randomly shuffled) numbering --
     ghost states, gradients, limiter, nodal states, residual, update coefficient, divB, the BSR pattern and every block,
