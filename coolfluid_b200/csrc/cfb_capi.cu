@@ -17,8 +17,8 @@ namespace cfb {
   throw cfb::DeviceError(CFB200_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
 
 template <class F, int BS, int MINB>
-__global__ void __launch_bounds__(BS, MINB) k_run(const F f, const int n) {
-  const int i = blockIdx.x*BS + threadIdx.x;
+__global__ void __launch_bounds__(BS, MINB) k_run(const F f, const int n, const int first) {
+  const int i = first + blockIdx.x*BS + threadIdx.x;     // items [first, n): the launch window (CudaBackend::window)
   if (i < n) f(i);
 }
 
@@ -27,11 +27,11 @@ __global__ void __launch_bounds__(BS, MINB) k_run(const F f, const int n) {
 // writes its 32 x 2 finished blocks to their BSR slots, F::BLK contiguous doubles at a time (coalesced), instead of 8-byte
 // scattered stores.  No block-wide barrier: warps stay independent.
 template <class F, int BS, int MINB>
-__global__ void __launch_bounds__(BS, MINB) k_staged(const F f, const int n) {
+__global__ void __launch_bounds__(BS, MINB) k_staged(const F f, const int n, const int first) {
   extern __shared__ double sm[];
   constexpr int STRIDE = BS + 1;
   const int t = threadIdx.x, lane = t & 31, warpBase = t & ~31;
-  const int i = blockIdx.x*BS + t;
+  const int i = first + blockIdx.x*BS + t;
   int s0 = -1, s1 = -1;
   if (i < n) { f.run(i, sm + t, STRIDE); f.slots(i, s0, s1); }
   // the two destination slots of every face of the warp go to the (now free) loop-state rows of the staging area
@@ -67,12 +67,12 @@ __global__ void __launch_bounds__(BS, MINB) k_staged(const F f, const int n) {
 
 // Two-phase variant for functors that stage ONE block per phase (f.run(i, phase, ...), f.slot(i, phase)): q = 9 blocks.
 template <class F, int BS, int MINB>
-__global__ void __launch_bounds__(BS, MINB) k_staged2(const F f, const int n) {
+__global__ void __launch_bounds__(BS, MINB) k_staged2(const F f, const int n, const int first) {
   extern __shared__ double sm[];
   constexpr int STRIDE = BS + 1;
   static_assert(F::BLK >= 32 && F::STAGE >= F::BLK + 1, "staging layout");
   const int t = threadIdx.x, lane = t & 31, warpBase = t & ~31;
-  const int i = blockIdx.x*BS + t;
+  const int i = first + blockIdx.x*BS + t;
   double* out = f.out();
   typename F::State st;            // what phase 1 keeps of phase 0, in registers across the write-out
   for (int phase = 0; phase < 2; ++phase) {
@@ -106,11 +106,11 @@ __global__ void __launch_bounds__(BS, MINB) k_staged2(const F f, const int n) {
 // each phase leaves ONE finished block in the thread's staging area, which the warp writes out (whole rows, coalesced)
 // before the next phase reuses the area.  Warps stay independent (no block-wide barrier).
 template <class F, int BS, int MINB>
-__global__ void __launch_bounds__(BS, MINB) k_phased(const F f, const int n) {
+__global__ void __launch_bounds__(BS, MINB) k_phased(const F f, const int n, const int first) {
   extern __shared__ double sm[];
   constexpr int STRIDE = BS + 1;
   const int t = threadIdx.x, lane = t & 31, warpBase = t & ~31;
-  const int i = blockIdx.x*BS + t;
+  const int i = first + blockIdx.x*BS + t;
   typename F::State st;
   const bool valid = i < n;
   const bool active = valid && f.begin(i, st, sm + t, STRIDE);
@@ -148,12 +148,12 @@ __global__ void __launch_bounds__(BS, MINB) k_phased(const F f, const int n) {
 // One cell per thread with F::BLK doubles of staging per thread (entry k of thread t at sm[k*(BS+1) + t]); after the cells
 // are evaluated the BLOCK writes the BS finished q x q blocks to their slots, whole rows at a time (coalesced).
 template <class F, int BS>
-__global__ void __launch_bounds__(BS) k_cell_staged(const F f, const int n) {
+__global__ void __launch_bounds__(BS) k_cell_staged(const F f, const int n, const int first) {
   extern __shared__ double sm[];
   constexpr int STRIDE = BS + 1;
   __shared__ int slots[BS];
   const int t = threadIdx.x;
-  const int i = blockIdx.x*BS + t;
+  const int i = first + blockIdx.x*BS + t;
   int s = -1;
   if (i < n) { f.run(i, sm + t, STRIDE); s = f.slot(i); }
   slots[t] = s;
@@ -210,6 +210,17 @@ struct CudaBackend {
   cudaStream_t copyStream = nullptr;       // device -> host copies that overlap the kernels still to run (d2hOverlapped)
   cudaEvent_t copyReady = nullptr;
   bool copiesInFlight = false;
+  // launch window: the NEXT launch covers the items [first, end) of its index range instead of all of them (Engine uses it
+  // to run the face kernel and the residual gather in two parts so that the host copy of the first part's rhs overlaps
+  // the second part)
+  int winFirst = 0, winEnd = -1;
+  void window(int first, int end) { winFirst = first; winEnd = end; }
+  int takeWindow(int& n) {
+    int w0 = 0;
+    if (winEnd >= 0) { w0 = winFirst; if (winEnd < n) n = winEnd; }
+    winFirst = 0; winEnd = -1;
+    return w0;
+  }
   bool timing = false;
   struct Ev { const char* name; cudaEvent_t a, b; };
   std::vector<Ev> evs;
@@ -251,11 +262,10 @@ struct CudaBackend {
   // device -> host copy of data that is final at this point of the stream, on the copy stream: it runs while the kernels
   // launched afterwards execute (PCIe and the SMs are independent); joinCopies() before the host reads it
   void d2hOverlapped(void* dst, const void* src, size_t bytes) {
-    if (!copiesInFlight) {
-      CFB_CUDA(cudaEventRecord(copyReady, stream));
-      CFB_CUDA(cudaStreamWaitEvent(copyStream, copyReady, 0));
-      copiesInFlight = true;
-    }
+    // every copy waits for what is queued on the engine's stream at this point (a re-recorded event keeps earlier waits)
+    CFB_CUDA(cudaEventRecord(copyReady, stream));
+    CFB_CUDA(cudaStreamWaitEvent(copyStream, copyReady, 0));
+    copiesInFlight = true;
     CFB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, copyStream));
   }
   void joinCopies() {
@@ -282,7 +292,8 @@ struct CudaBackend {
   }
 
   template <class F> void launch(const char* name, const F& f, int n, int bs) {
-    if (n <= 0) return;
+    const int w0 = takeWindow(n), m = n - w0;            // items [w0, n) of the launch window, else all
+    if (m <= 0) return;
     Ev* ev = nullptr;
     if (timing) {
       if (nEv == evs.size()) { Ev e; e.name = name; CFB_CUDA(cudaEventCreate(&e.a)); CFB_CUDA(cudaEventCreate(&e.b)); evs.push_back(e); }
@@ -291,16 +302,17 @@ struct CudaBackend {
     }
     // launch shape: a functor that declares `static constexpr int MINB = 4` runs as 128 threads with >= 4 resident
     // blocks per SM (<= 128 registers); otherwise bs = 256 -> 256 threads, bs = 128 -> 128 threads, >= 2 blocks/SM
-    if constexpr (HasMinB<F>::value) k_run<F, 128, F::MINB><<<(n + 127)/128, 128, 0, stream>>>(f, n);
-    else if (bs == 128) k_run<F, 128, 2><<<(n + 127)/128, 128, 0, stream>>>(f, n);
-    else k_run<F, 256, 1><<<(n + 255)/256, 256, 0, stream>>>(f, n);
+    if constexpr (HasMinB<F>::value) k_run<F, 128, F::MINB><<<(m + 127)/128, 128, 0, stream>>>(f, n, w0);
+    else if (bs == 128) k_run<F, 128, 2><<<(m + 127)/128, 128, 0, stream>>>(f, n, w0);
+    else k_run<F, 256, 1><<<(m + 255)/256, 256, 0, stream>>>(f, n, w0);
     CFB_CUDA(cudaGetLastError());
     if (ev) CFB_CUDA(cudaEventRecord(ev->b, stream));
   }
 
   // 128-thread blocks with F::STAGE doubles of shared-memory staging per thread; minBlocks = resident blocks per SM
   template <class F> void launchStaged(const char* name, const F& f, int n, int minBlocks) {
-    if (n <= 0) return;
+    const int w0 = takeWindow(n);       // consumed even when nothing is launched
+    if (n - w0 <= 0) return;
     Ev* ev = nullptr;
     if (timing) {
       if (nEv == evs.size()) { Ev e; e.name = name; CFB_CUDA(cudaEventCreate(&e.a)); CFB_CUDA(cudaEventCreate(&e.b)); evs.push_back(e); }
@@ -316,7 +328,7 @@ struct CudaBackend {
       int pct = (int)((StagedMinB<F>::value*(smem + 1024)*100 + 228*1024 - 1)/(228*1024)) + 3;
       if (pct > 100) pct = 100;
       CFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
-      kern<<<(n + BS - 1)/BS, BS, smem, stream>>>(f, n);
+      kern<<<(n - w0 + BS - 1)/BS, BS, smem, stream>>>(f, n, w0);
     };
     // launch shape = resident 128-thread blocks per SM = warps per scheduler (each scheduler owns 16384 registers, so the
     // only register budgets that change occupancy are 255 / 168 / 128 per thread; measured on B200: 2 is fastest)
@@ -329,7 +341,8 @@ struct CudaBackend {
   }
 
   template <class F> void launchCellStaged(const char* name, const F& f, int n) {
-    if (n <= 0) return;
+    const int w0 = takeWindow(n);       // consumed even when nothing is launched
+    if (n - w0 <= 0) return;
     Ev* ev = nullptr;
     if (timing) {
       if (nEv == evs.size()) { Ev e; e.name = name; CFB_CUDA(cudaEventCreate(&e.a)); CFB_CUDA(cudaEventCreate(&e.b)); evs.push_back(e); }
@@ -340,14 +353,15 @@ struct CudaBackend {
     const size_t smem = (size_t)F::BLK*(BS + 1)*sizeof(double);
     auto kern = k_cell_staged<F, BS>;
     CFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<(n + BS - 1)/BS, BS, smem, stream>>>(f, n);
+    kern<<<(n - w0 + BS - 1)/BS, BS, smem, stream>>>(f, n, w0);
     CFB_CUDA(cudaGetLastError());
     if (ev) CFB_CUDA(cudaEventRecord(ev->b, stream));
   }
 
   // three resident 128-thread blocks per SM (168 registers), F::STAGE doubles of staging per thread
   template <class F> void launchPhased(const char* name, const F& f, int n) {
-    if (n <= 0) return;
+    const int w0 = takeWindow(n);       // consumed even when nothing is launched
+    if (n - w0 <= 0) return;
     Ev* ev = nullptr;
     if (timing) {
       if (nEv == evs.size()) { Ev e; e.name = name; CFB_CUDA(cudaEventCreate(&e.a)); CFB_CUDA(cudaEventCreate(&e.b)); evs.push_back(e); }
@@ -359,13 +373,14 @@ struct CudaBackend {
     auto kern = k_phased<F, BS, 3>;
     CFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-    kern<<<(n + BS - 1)/BS, BS, smem, stream>>>(f, n);
+    kern<<<(n - w0 + BS - 1)/BS, BS, smem, stream>>>(f, n, w0);
     CFB_CUDA(cudaGetLastError());
     if (ev) CFB_CUDA(cudaEventRecord(ev->b, stream));
   }
 
   template <class F> void launchStaged2(const char* name, const F& f, int n) {
-    if (n <= 0) return;
+    const int w0 = takeWindow(n);       // consumed even when nothing is launched
+    if (n - w0 <= 0) return;
     Ev* ev = nullptr;
     if (timing) {
       if (nEv == evs.size()) { Ev e; e.name = name; CFB_CUDA(cudaEventCreate(&e.a)); CFB_CUDA(cudaEventCreate(&e.b)); evs.push_back(e); }
@@ -379,7 +394,7 @@ struct CudaBackend {
     int pct = (int)((2*(smem + 1024)*100 + 228*1024 - 1)/(228*1024)) + 3;      // as in launchStaged
     if (pct > 100) pct = 100;
     CFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
-    kern<<<(n + BS - 1)/BS, BS, smem, stream>>>(f, n);
+    kern<<<(n - w0 + BS - 1)/BS, BS, smem, stream>>>(f, n, w0);
     CFB_CUDA(cudaGetLastError());
     if (ev) CFB_CUDA(cudaEventRecord(ev->b, stream));
   }
@@ -461,7 +476,7 @@ void haloBegin(cfb::Engine<BackendT>& e, cfb::Halo& H) {
   CFB_NCCL(N.GroupEnd());
   if (nRecv) {
     const int n = nRecv*q;
-    cfb::k_run<cfb::HaloUnpack, 256, 1><<<(n + 255)/256, 256, 0, H.cs>>>(cfb::HaloUnpack{e.d.U, e.d.nStates, q, H.dRecv, H.rbuf}, n);
+    cfb::k_run<cfb::HaloUnpack, 256, 1><<<(n + 255)/256, 256, 0, H.cs>>>(cfb::HaloUnpack{e.d.U, e.d.nStates, q, H.dRecv, H.rbuf}, n, 0);
     CFB_CUDA(cudaGetLastError());
   }
   CFB_CUDA(cudaEventRecord(H.done, H.cs));

@@ -80,6 +80,8 @@ public:
   // FD loop of the Roe families (CFB200_ROE_PIPELINE, for A/B measurements): 0 = rolled loop, 1 = software-pipelined,
   // 2 = software-pipelined in two phases with three resident blocks per SM (DiamondVolume; Corrected uses 1)
   int roePipeline = 1;
+  int splitD2H = 1;         // host copies requested: face kernel + residual gather in two parts (CFB200_SPLIT_D2H=0: one)
+  int splitFace = 0, splitCells = 0;   // interior faces [0, splitFace) complete the cells [0, splitCells)
   int faceShape = 2;       // resident 128-thread blocks per SM the interior-face Jacobian kernel is compiled for
                            // (CudaBackend::launchStaged): 2 -> 255 registers, no spills: measured fastest on B200 (profiles/)
   // multi-GPU (cfb_halo.cuh): a state halo exchange may be in flight when computeRhs is called; the first nIndep
@@ -104,6 +106,7 @@ public:
   explicit Engine(const Cfg& c, int device) : cfg(c), bk(device) {
     std::memset(&d, 0, sizeof(d));
     if (const char* v = std::getenv("CFB200_ROE_PIPELINE")) roePipeline = std::atoi(v);
+    if (const char* v = std::getenv("CFB200_SPLIT_D2H")) splitD2H = std::atoi(v);
   }
   ~Engine() { if (solverExt && solverExtFree) solverExtFree(solverExt); for (void* p : owned) bk.free(p); }
 
@@ -546,6 +549,19 @@ public:
       dFaceRef = upload(hFaceRef);
       d.cellRef = dStateRef;
     }
+    // split point of the two-part evaluation (computeRhs_ with host copies): the longest prefix of cells whose interior
+    // faces all lie in the first half of the interior faces
+    splitFace = 0; splitCells = 0;
+    if (ni >= 2) {
+      const int S = ni/2;
+      int n = 0;
+      for (; n < nc; ++n) {
+        bool ready = true;
+        for (int k = m.cellFacePtr[n]; k < m.cellFacePtr[n+1] && ready; ++k) { const int f = m.cellFaces[k]; ready = (f >= ni) || (f < S); }
+        if (!ready) break;
+      }
+      if (n >= nc/4) { splitFace = S; splitCells = n; }
+    }
     bk.launch("faceCentres", FaceCentres{d}, nf, 256);
     if (D == 2) bk.launch("lsqSetup", LsqSetup<2>{d}, nc, 256); else bk.launch("lsqSetup", LsqSetup<3>{d}, nc, 256);
     bk.sync();
@@ -572,12 +588,15 @@ public:
   template <int D, class PH> void applyBC_() { if (d.nGhosts) bk.launch("applyBC", GhostFill<D, PH>{d, cfg}, d.nGhosts, 128); }
 
   // the face kernels of the Euler / Navier-Stokes families; DV = derivative computer of the diffusive flux
+  // part 0: all faces; part 1: the interior faces [0, splitFace) + the boundary faces; part 2: the interior faces
+  // [splitFace, nInner) (the interior kernel is the first launch of every branch: it takes the launch window)
   template <int D, int DV>
-  void faceKernels_(bool doJac, int faceShape) {
+  void faceKernels_(bool doJac, int faceShape, int part = 0) {
     const int fam = splitterFamily(cfg);
+    if (part == 1) bk.window(0, splitFace); else if (part == 2) bk.window(splitFace, d.nInner);
     if (doJac && cfg.computeJacobian == 2) {
       bk.launchStaged("innerFaceJacAnalytic", AnalyticInnerFaceK<D, DV>{d, cfg}, d.nInner, faceShape);
-      bk.launch("boundaryFaceJac", BoundaryFaceK<D, true, DV>{d, cfg}, d.nGhosts, 128);
+      if (part != 2) bk.launch("boundaryFaceJac", BoundaryFaceK<D, true, DV>{d, cfg}, d.nGhosts, 128);
     } else if (doJac && (fam == 0 || fam == 3) && roePipeline == 2 && DV == 0) {
       // Roe families, DiamondVolume: two phases, three resident blocks per SM
       const bool cons = (cfg.updateVar == CFB200_UV_CONS);
@@ -585,7 +604,7 @@ public:
       else if (fam == 0) bk.launchPhased("innerFaceJac", InnerFacePhased<D, 0, CFB200_UV_PVT>{d, cfg}, d.nInner);
       else if (cons) bk.launchPhased("innerFaceJac", InnerFacePhased<D, 3, CFB200_UV_CONS>{d, cfg}, d.nInner);
       else bk.launchPhased("innerFaceJac", InnerFacePhased<D, 3, CFB200_UV_PVT>{d, cfg}, d.nInner);
-      bk.launch("boundaryFaceJac", BoundaryFaceK<D, true, DV>{d, cfg}, d.nGhosts, 128);
+      if (part != 2) bk.launch("boundaryFaceJac", BoundaryFaceK<D, true, DV>{d, cfg}, d.nGhosts, 128);
     } else if (doJac && (fam == 0 || fam == 3) && roePipeline) {
       // Roe families: update-variable set fixed at compile time, software-pipelined finite-difference loop
       const bool cons = (cfg.updateVar == CFB200_UV_CONS);
@@ -593,21 +612,21 @@ public:
       else if (fam == 0) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 0, DV, CFB200_UV_PVT>{d, cfg}, d.nInner, faceShape);
       else if (cons) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 3, DV, CFB200_UV_CONS>{d, cfg}, d.nInner, faceShape);
       else bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 3, DV, CFB200_UV_PVT>{d, cfg}, d.nInner, faceShape);
-      bk.launch("boundaryFaceJac", BoundaryFaceK<D, true, DV>{d, cfg}, d.nGhosts, 128);
+      if (part != 2) bk.launch("boundaryFaceJac", BoundaryFaceK<D, true, DV>{d, cfg}, d.nGhosts, 128);
     } else if (doJac) {
       if (fam == 0) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 0, DV>{d, cfg}, d.nInner, faceShape);
       else if (fam == 1) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 1, DV>{d, cfg}, d.nInner, faceShape);
       else if (fam == 2) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 2, DV>{d, cfg}, d.nInner, faceShape);
       else if (fam == 4) bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 4, DV>{d, cfg}, d.nInner, faceShape);
       else bk.launchStaged("innerFaceJac", InnerFaceK<D, true, 3, DV>{d, cfg}, d.nInner, faceShape);
-      bk.launch("boundaryFaceJac", BoundaryFaceK<D, true, DV>{d, cfg}, d.nGhosts, 128);
+      if (part != 2) bk.launch("boundaryFaceJac", BoundaryFaceK<D, true, DV>{d, cfg}, d.nGhosts, 128);
     } else {
       if (fam == 0) bk.launch("innerFace", InnerFaceK<D, false, 0, DV>{d, cfg}, d.nInner, 128);
       else if (fam == 1) bk.launch("innerFace", InnerFaceK<D, false, 1, DV>{d, cfg}, d.nInner, 128);
       else if (fam == 2) bk.launch("innerFace", InnerFaceK<D, false, 2, DV>{d, cfg}, d.nInner, 128);
       else if (fam == 4) bk.launch("innerFace", InnerFaceK<D, false, 4, DV>{d, cfg}, d.nInner, 128);
       else bk.launch("innerFace", InnerFaceK<D, false, 3, DV>{d, cfg}, d.nInner, 128);
-      bk.launch("boundaryFace", BoundaryFaceK<D, false, DV>{d, cfg}, d.nGhosts, 128);
+      if (part != 2) bk.launch("boundaryFace", BoundaryFaceK<D, false, DV>{d, cfg}, d.nGhosts, 128);
     }
   }
 
@@ -641,23 +660,40 @@ public:
     bk.launch("nodalExtrapolate", NodalExtrapolate<D, PH>{d}, d.nNodes, 256);
     if (cfg.polyRec == CFB200_PR_LINEARLS && cfg.limiter != CFB200_LIM_NONE)
       bk.launch("limiter", LimiterK<D, PH>{d, cfg}, d.nCells, 128);
+    const bool fused = (cfg.fuseTimeRhs != 0);
+    // With host copies requested the face kernel and the residual gather run in two parts: the cells [0, splitCells) have
+    // all their faces among the first splitFace interior faces (+ boundary faces), so their rhs / updateCoeff are final
+    // after part 1 and travel to the host while part 2 computes; the rest of the copy runs under the diagonal gather.
+    const bool split = splitD2H && splitFace > 0 && (hostRhs || hostUc) && !cfg.renumber;
+    auto faces = [&](int part) {
     if constexpr (PH::CENTRED_ONLY) {
+      if (part == 1) bk.window(0, splitFace); else if (part == 2) bk.window(splitFace, d.nInner);
       if (doJac) {
         bk.launchStaged2("innerFaceJac", CentredInnerFaceK<PH, true>{d, cfg}, d.nInner);
-        bk.launch("boundaryFaceJac", CentredBoundaryFaceK<PH, true>{d, cfg}, d.nGhosts, 128);
+        if (part != 2) bk.launch("boundaryFaceJac", CentredBoundaryFaceK<PH, true>{d, cfg}, d.nGhosts, 128);
       } else {
         bk.launch("innerFace", CentredInnerFaceK<PH, false>{d, cfg}, d.nInner, 128);
-        bk.launch("boundaryFace", CentredBoundaryFaceK<PH, false>{d, cfg}, d.nGhosts, 128);
+        if (part != 2) bk.launch("boundaryFace", CentredBoundaryFaceK<PH, false>{d, cfg}, d.nGhosts, 128);
       }
     } else {
-      if (cfg.derivativeStrategy != CFB200_DV_DIAMOND && cfg.diffusive == CFB200_DIFF_NS) faceKernels_<D, 1>(doJac, faceShape);   // Corrected / StateDiff: CorrectedWork
-      else faceKernels_<D, 0>(doJac, faceShape);
+      if (cfg.derivativeStrategy != CFB200_DV_DIAMOND && cfg.diffusive == CFB200_DIFF_NS) faceKernels_<D, 1>(doJac, faceShape, part);   // Corrected / StateDiff / CorrectedGG: CorrectedWork
+      else faceKernels_<D, 0>(doJac, faceShape, part);
     }
-    const bool fused = (cfg.fuseTimeRhs != 0);
-    if (fused) bk.launchCellStaged("cellGather", CellGather<D, PH, true>{d, cfg}, d.nCells);
-    else bk.launch("cellGather", CellGather<D, PH, false>{d, cfg}, d.nCells, 256);
-    if (hostRhs) bk.d2hOverlapped(hostRhs, d.rhs, sizeof(double)*d.nCells*PH::Q);
-    if (hostUc) bk.d2hOverlapped(hostUc, d.updateCoeff, sizeof(double)*d.nCells);
+    };
+    auto gather = [&](int c0, int c1) {      // residual gather + host copies of the cells [c0, c1)
+      if (c1 <= c0) return;
+      if (c0 > 0 || c1 < d.nCells) bk.window(c0, c1);
+      if (fused) bk.launchCellStaged("cellGather", CellGather<D, PH, true>{d, cfg}, d.nCells);
+      else bk.launch("cellGather", CellGather<D, PH, false>{d, cfg}, d.nCells, 256);
+      if (hostRhs) bk.d2hOverlapped(hostRhs + (size_t)c0*PH::Q, d.rhs + (size_t)c0*PH::Q, sizeof(double)*(size_t)(c1 - c0)*PH::Q);
+      if (hostUc) bk.d2hOverlapped(hostUc + c0, d.updateCoeff + c0, sizeof(double)*(size_t)(c1 - c0));
+    };
+    if (split) {
+      faces(1); gather(0, splitCells);
+      faces(2); gather(splitCells, d.nCells);
+    } else {
+      faces(0); gather(0, d.nCells);
+    }
     if (doJac) {
       // one thread per (cell, block entry): launched in chunks of < 2^31 entries (q = 9: 26.5 M cells per chunk)
       const int CH = (1 << 30)/DiagGather<D, PH>::GS;          // cells per launch

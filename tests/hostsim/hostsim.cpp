@@ -22,16 +22,20 @@ struct HostLoopBackend {
   void d2d(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
   void d2hOverlapped(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
   void joinCopies() {}
+  int winFirst = 0, winEnd = -1;
+  void window(int first, int end) { winFirst = first; winEnd = end; }
+  int takeWindow(int& n) { int w0 = 0; if (winEnd >= 0) { w0 = winFirst; if (winEnd < n) n = winEnd; } winFirst = 0; winEnd = -1; return w0; }
   void memset(void* p, int v, size_t n) { std::memset(p, v, n); }
   void sync() {}
   void* streamPtr() { return nullptr; }
   void enableTiming(bool) {}
   void resetTimings() {}
   int timings(const char**, float*, int) { return 0; }
-  template <class F> void launch(const char*, const F& f, int n, int) { for (int i = 0; i < n; ++i) f(i); }
+  template <class F> void launch(const char*, const F& f, int n, int) { const int w0 = takeWindow(n); for (int i = w0; i < n; ++i) f(i); }
   template <class F> void launchStaged(const char*, const F& f, int n, int) {
     double stg[F::STAGE];
-    for (int i = 0; i < n; ++i) {
+    const int w0 = takeWindow(n);
+    for (int i = w0; i < n; ++i) {
       int s0 = -1, s1 = -1;
       f.run(i, stg, 1); f.slots(i, s0, s1);
       for (int k = 0; k < F::NOUT; ++k) {                   // the warp's block write-out
@@ -42,7 +46,8 @@ struct HostLoopBackend {
   }
   template <class F> void launchCellStaged(const char*, const F& f, int n) {
     double stg[F::BLK];
-    for (int i = 0; i < n; ++i) {
+    const int w0 = takeWindow(n);
+    for (int i = w0; i < n; ++i) {
       f.run(i, stg, 1);
       const int slot = f.slot(i);
       if (slot >= 0) for (int k = 0; k < F::BLK; ++k) f.out()[(size_t)slot*F::BLK + k] = stg[k];
@@ -50,7 +55,8 @@ struct HostLoopBackend {
   }
   template <class F> void launchPhased(const char*, const F& f, int n) {
     double stg[F::STAGE];
-    for (int i = 0; i < n; ++i) {
+    const int w0 = takeWindow(n);
+    for (int i = w0; i < n; ++i) {
       typename F::State st;
       const bool active = f.begin(i, st, stg, 1);
       for (int ph = 0; ph < 2; ++ph) {
@@ -62,7 +68,8 @@ struct HostLoopBackend {
   }
   template <class F> void launchStaged2(const char*, const F& f, int n) {
     double stg[F::STAGE];
-    for (int i = 0; i < n; ++i) {
+    const int w0 = takeWindow(n);
+    for (int i = w0; i < n; ++i) {
       typename F::State st;
       for (int phase = 0; phase < 2; ++phase) {
         f.run(i, phase, st, stg, 1);
