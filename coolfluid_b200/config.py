@@ -15,7 +15,7 @@ MAXEQ = 9
 PM_EULER, PM_MHD3D_PROJECTION = 0, 1
 DV_DIAMOND, DV_CORRECTED, DV_STATEDIFF, DV_CORRECTED_GG = 0, 1, 2, 3
 UV_CONS, UV_PVT = 0, 1
-FS_ROE, FS_AUSMPLUS, FS_AUSMPLUSUP, FS_LAXFRIED, FS_HLL, FS_ROESA = 0, 1, 2, 3, 4, 5
+FS_ROE, FS_AUSMPLUS, FS_AUSMPLUSUP, FS_LAXFRIED, FS_HLL, FS_ROESA, FS_CENTRED = 0, 1, 2, 3, 4, 5, 6
 PR_CONSTANT, PR_LINEARLS = 0, 1
 LIM_NONE, LIM_VENKTN, LIM_BARTHJESP, LIM_VENKTN_STRICT = 0, 1, 2, 3
 DIFF_NONE, DIFF_NS = 0, 1

@@ -41,20 +41,21 @@ inline bool splitterSupported(const cfb200_config& c) {
   // background potential field: none or Dipole, MHD3DProjection only ("PFSS" needs the reference's harmonics data)
   if (c.mhdPotentialBType != 0 && !(c.mhdPotentialBType == 1 && c.physicalModel == CFB200_PM_MHD3D_PROJECTION)) return false;
   if (c.physicalModel == CFB200_PM_MHD3D_PROJECTION)      // MHD: centred splitters, conservative variables, inviscid
-    return (c.fluxSplitter == CFB200_FS_LAXFRIED || c.fluxSplitter == CFB200_FS_HLL) && c.updateVar == CFB200_UV_CONS &&
+    return (c.fluxSplitter == CFB200_FS_LAXFRIED || c.fluxSplitter == CFB200_FS_HLL || c.fluxSplitter == CFB200_FS_CENTRED) &&
+           c.updateVar == CFB200_UV_CONS &&
            c.diffusive == CFB200_DIFF_NONE;
   if (c.fluxSplitter == CFB200_FS_ROE) return c.entropyFixID >= 0 && c.entropyFixID <= 2;
   if (c.fluxSplitter == CFB200_FS_ROESA) return c.entropyFixID >= 0 && c.entropyFixID <= 3;
   if (c.fluxSplitter == CFB200_FS_AUSMPLUS || c.fluxSplitter == CFB200_FS_AUSMPLUSUP)
     return c.choiceA12 >= 1 && c.choiceA12 <= 3 && (c.fluxSplitter == CFB200_FS_AUSMPLUS || c.machInf > 0.);
-  if (c.fluxSplitter == CFB200_FS_LAXFRIED || c.fluxSplitter == CFB200_FS_HLL) return true;
+  if (c.fluxSplitter == CFB200_FS_LAXFRIED || c.fluxSplitter == CFB200_FS_HLL || c.fluxSplitter == CFB200_FS_CENTRED) return true;
   return false;
 }
 // kernel family of the splitter: 0 Roe, 1 AUSM+ / AUSM+up, 2 Lax-Friedrichs / HLL, 3 Roe with the entropy fix, 4 RoeSA
 inline int splitterFamily(const cfb200_config& c) {
   if (c.fluxSplitter == CFB200_FS_ROE) return (c.entropyFixID != 0) ? 3 : 0;
   if (c.fluxSplitter == CFB200_FS_ROESA) return 4;
-  return (c.fluxSplitter == CFB200_FS_LAXFRIED || c.fluxSplitter == CFB200_FS_HLL) ? 2 : 1;
+  return (c.fluxSplitter == CFB200_FS_LAXFRIED || c.fluxSplitter == CFB200_FS_HLL || c.fluxSplitter == CFB200_FS_CENTRED) ? 2 : 1;
 }
 
 struct DeviceError : std::runtime_error {

@@ -149,6 +149,12 @@ struct MhdPhys {
     const double e0 = w.Vn - w.cf, e1 = w.Vn - w.ca, e7 = w.Vn + w.ca, e8 = w.Vn + w.cf;
     const double cp = c.refSpeed, cm = -c.refSpeed;
     o.evMax0 = 0.0; o.evMin0 = 0.0; o.evAbs0 = 0.0;
+    if (c.fluxSplitter == CFB200_FS_CENTRED) {
+      // no fold is read by the flux; the left update coefficient is getMaxEigenValue (CentredFlux.cxx:75-77), whose value
+      // max(refSpeed, Vn + cf) is what evVecMax carries for it
+      o.evVecMax = dmax(c.refSpeed, e8);
+      return;
+    }
     if (c.fluxSplitter == CFB200_FS_LAXFRIED) {
       o.evAbs0 = dmax(dmax(dmax(dmax(dmax(dmax(0.0, fabs(e0)), fabs(e1)), fabs(cp)), fabs(cm)), fabs(e7)), fabs(e8));
     } else {
@@ -159,6 +165,11 @@ struct MhdPhys {
   }
   // LaxFriedFlux.cxx:79-118:  0.5*(fR + fL - a*k*(sR - sL));  HLLFlux.cxx:73-133
   static CFB_HD void centred(const Cfg& c, const CSide& l, const CSide& r, double* result) {
+    if (c.fluxSplitter == CFB200_FS_CENTRED) {    // CentredFlux.cxx:62-64
+#pragma unroll
+      for (int i = 0; i < Q; ++i) result[i] = 0.5*(r.f[i] + l.f[i]);
+      return;
+    }
     if (c.fluxSplitter == CFB200_FS_LAXFRIED) {
       const double aDiff = dmax(r.evAbs0, l.evAbs0)*c.diffRedCoeff;
 #pragma unroll

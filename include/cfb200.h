@@ -35,7 +35,9 @@ enum cfb200_flux_splitter { CFB200_FS_ROE = 0 /* "Roe" plugins/FiniteVolume/RoeF
                             CFB200_FS_HLL = 4 /* "HLL" plugins/FiniteVolume/HLLFlux.cxx:73-150 */,
                             CFB200_FS_ROESA = 5 /* "RoeSA" plugins/FiniteVolume/RoeSAFlux.cxx:66-197: Roe with Sanders'
                                                    H-correction; entropyFixID then is RoeSA's own option (0 | 3: |ev| + eta,
-                                                   1: Harten-like with eta, 2: max(|ev|, eta)) */ };
+                                                   1: Harten-like with eta, 2: max(|ev|, eta)) */,
+                            CFB200_FS_CENTRED = 6 /* "Centred" plugins/FiniteVolume/CentredFlux.cxx:55-90: 0.5*(fR + fL), no
+                                                     dissipation (Euler variable sets and MHD3DProjection) */ };
 enum cfb200_poly_rec { CFB200_PR_CONSTANT = 0 /* "Constant" ConstantPolyRec.cxx */,
                        CFB200_PR_LINEARLS = 1 /* "LinearLS2D"/"LinearLS3D" LeastSquareP1PolyRec{2,3}D.cxx */ };
 enum cfb200_limiter { CFB200_LIM_NONE = 0, CFB200_LIM_VENKTN = 1 /* "Venktn2D"/"Venktn3D" */,

@@ -68,7 +68,7 @@ int cfo_compute(const Config* c, const MeshView* m, const BC* bcs, double* U, Cf
             co->bsrRowPtr, co->bsrColInd, co->bsrVal, 0, co->divB};
   try {
     if (c->physicalModel == PM_MHD3D_PROJECTION) {
-      if (c->dim != 3 || c->nEqs != 9 || !(c->fluxSplitter == FS_LAXFRIED || c->fluxSplitter == FS_HLL) ||
+      if (c->dim != 3 || c->nEqs != 9 || !(c->fluxSplitter == FS_LAXFRIED || c->fluxSplitter == FS_HLL || c->fluxSplitter == FS_CENTRED) ||
           c->diffusive != DIFF_NONE) { co->status = 2; return 2; }
       Solver<3, MhdPhys> s(*c, *m, bcs); s.execute(U, o);
     }

@@ -914,6 +914,10 @@ struct Phys {
     convFlux(pR, n, fR); convFlux(pL, n, fL);
     eigenValues(pR, n, evR); eigenValues(pL, n, evL);
     toCons(c, uL, sL); toCons(c, uR, sR);
+    if (c.fluxSplitter == FS_CENTRED) {          // CentredFlux.cxx:62-64: _sumFlux = fR; _sumFlux += fL; result = 0.5*_sumFlux
+      for (int i = 0; i < Q; ++i) { const double sumFlux = fR[i] + fL[i]; result[i] = 0.5*sumFlux; }
+      return true;
+    }
     if (c.fluxSplitter == FS_LAXFRIED) {
       double aR = 0.0, aL = 0.0;
       for (int i = 0; i < Q; ++i) { aR = std::max(aR, std::abs(evR[i])); aL = std::max(aL, std::abs(evL[i])); }
@@ -1254,6 +1258,10 @@ struct MhdPhys {
     double fL[Q], fR[Q], evL[Q], evR[Q];
     convFlux(c, pR, n, fR); convFlux(c, pL, n, fL);
     eigenValues(c, pR, n, evR); eigenValues(c, pL, n, evL);
+    if (c.fluxSplitter == FS_CENTRED) {          // CentredFlux.cxx:62-64
+      for (int i = 0; i < Q; ++i) { const double sumFlux = fR[i] + fL[i]; result[i] = 0.5*sumFlux; }
+      return true;
+    }
     if (c.fluxSplitter == FS_LAXFRIED) {
       double aR = 0.0, aL = 0.0;
       for (int i = 0; i < Q; ++i) { aR = std::max(aR, std::abs(evR[i])); aL = std::max(aL, std::abs(evL[i])); }

@@ -471,7 +471,7 @@ public:
       etaSA *= 0.5;
       if (!(std::abs(etaSA) > 0.)) { o.status = 1; return false; }     // assert(std::abs(etaSA) > 0.), :97
       if (!P::roeFlux(cfg, x.vL, x.vR, x.pL, x.pR, x.n, flux, etaSA)) { o.status = 1; return false; }
-    } else if (cfg.fluxSplitter == FS_LAXFRIED || cfg.fluxSplitter == FS_HLL) {
+    } else if (cfg.fluxSplitter == FS_LAXFRIED || cfg.fluxSplitter == FS_HLL || cfg.fluxSplitter == FS_CENTRED) {
       // update coefficient (LaxFriedFlux.cxx:120-188, HLLFlux.cxx:135-150): _leftEv.max() == un + a, as Roe's
       P::centredFlux(cfg, x.vL, x.vR, x.pL, x.pR, x.n, flux);
     } else {
@@ -480,7 +480,7 @@ public:
     if (!isPerturb) {
       const double faceArea = x.area/1;       // polyRec->nbQPoints() == 1
       // left side: getMaxEigenValue (Roe, AUSM) or _leftEv.max() (LaxFriedFlux.cxx:131, HLLFlux.cxx:141); right side:
-      // getMaxEigenValue with the reversed normal in all splitters
+      // getMaxEigenValue with the reversed normal in all splitters; Centred: getMaxEigenValue on both sides (CentredFlux.cxx:75-87)
       const bool centred = (cfg.fluxSplitter == FS_LAXFRIED || cfg.fluxSplitter == FS_HLL);
       double maxEV = centred ? P::evMaxOfVector(cfg, x.pL, x.n) : P::maxEigenValue(cfg, x.pL, x.n);
       o.updateCoeff[x.L] += std::max(maxEV, 0.)*faceArea;

@@ -32,7 +32,7 @@ constexpr int MAXDIM = 3;
 // ---- enums shared (by value) with the product's include/cfb200.h -------------
 enum PhysicalModel { PM_EULER = 0, PM_MHD3D_PROJECTION = 1 };
 enum UpdateVar { UV_CONS = 0, UV_PVT = 1 };            // Euler{2,3}DCons / Euler2DPuvt, Euler3DPvt
-enum FluxSplitter { FS_ROE = 0, FS_AUSMPLUS = 1, FS_AUSMPLUSUP = 2, FS_LAXFRIED = 3, FS_HLL = 4, FS_ROESA = 5 };
+enum FluxSplitter { FS_ROE = 0, FS_AUSMPLUS = 1, FS_AUSMPLUSUP = 2, FS_LAXFRIED = 3, FS_HLL = 4, FS_ROESA = 5, FS_CENTRED = 6 };
 enum PolyRec { PR_CONSTANT = 0, PR_LINEARLS = 1 };
 enum Limiter { LIM_NONE = 0, LIM_VENKTN = 1, LIM_BARTHJESP = 2, LIM_VENKTN_STRICT = 3 };
 enum Diffusive { DIFF_NONE = 0, DIFF_NS = 1 };

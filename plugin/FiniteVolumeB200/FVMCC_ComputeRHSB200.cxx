@@ -165,7 +165,7 @@ void FVMCC_ComputeRHSB200::fillConfig(cfb200_config& c)
   FluxSplitter<CellCenterFVMData>& fsp = *md.getFluxSplitter();
   const std::string fs = fsp.getName();
   c.fluxSplitter = (fs.find("AUSMPlusUp") == 0) ? CFB200_FS_AUSMPLUSUP : (fs.find("AUSMPlus") == 0) ? CFB200_FS_AUSMPLUS :
-                   (fs == "LaxFried") ? CFB200_FS_LAXFRIED : (fs == "HLL") ? CFB200_FS_HLL :
+                   (fs == "LaxFried") ? CFB200_FS_LAXFRIED : (fs == "HLL") ? CFB200_FS_HLL : (fs == "Centred") ? CFB200_FS_CENTRED :
                    (fs == "Roe" || fs == "RoeEntropyFix") ? CFB200_FS_ROE : (fs == "RoeSA") ? CFB200_FS_ROESA :
                    -1;                                                               // -1: cfb200_create -> UNSUPPORTED
   c.diffRedCoeff = optReal(fsp, "DiffCoeff", 1.0);         // RoeFlux.cxx:34,62 / LaxFriedFlux.cxx:32

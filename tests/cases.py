@@ -245,6 +245,12 @@ CASES = {
                            bcs_ns3d, True),
     "ns2d_quad_laxfried": (lambda: meshgen.quad_channel(10, 8), lambda: ns2d_cfg(flux=B.FS_LAXFRIED, diff_red_coeff=0.8),
                            bcs_ns2d, True),
+    # "Centred" (CentredFlux.cxx): 0.5*(fR + fL), on the Euler variable sets and on MHD3DProjection
+    "euler2d_centred_2nd_tri": (lambda: meshgen.quad_channel(12, 9, triangles=True),
+                                lambda: B.make_config(2, flux=B.FS_CENTRED, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN,
+                                                      jacobian=True), bcs_euler2d, False),
+    "ns3d_hex_centred": (lambda: meshgen.hex_box(5, 4, 4), lambda: ns3d_cfg(flux=B.FS_CENTRED), bcs_ns3d, True),
+    "mhd3d_hex_centred": (lambda: meshgen.hex_box(4, 4, 3), lambda: mhd3d_cfg(flux=B.FS_CENTRED), bcs_mhd3d, "mhd"),
     # BASELINE config 4: 3D ideal MHD with hyperbolic divergence cleaning (q = 9), HLL / Lax-Friedrichs
     "mhd3d_hex_hll": (lambda: meshgen.hex_box(5, 4, 4), mhd3d_cfg, bcs_mhd3d, "mhd"),
     # background potential field B0 = "Dipole" (MHDTerm potentialBType): enters the wave speeds and the update coefficient
