@@ -507,6 +507,66 @@ void build(cfb200_meshdata& M, int dim, int nNodes, const double* nodes, int nCe
   }
 }
 
+// ---- the other stencils of `Setup1.stencil` (a3): 1 "FaceVertex" (ComputeFaceVertexNeighbors.cxx:45-129: the cells around
+// the cell's nodes, no ghosts), 2 "FaceEdge" (ComputeFaceEdgeNeighbors.cxx:44-150: cells of higher ID sharing >= 2 nodes),
+// 3 "Face" (ComputeFaceNeighbors.cxx:46-108: interior-face neighbours of higher ID in cellFaces order).  1 and 2 in
+// ascending ID (the reference iterates a set of State pointers).  A cell that shares k nodes with the cell shows up k
+// times among the cells gathered around its nodes (the nodes of an element are distinct): after one sort, run lengths
+// give the FaceEdge test without comparing node lists.
+int rebuildStencil(cfb200_meshdata& M, int kind) {
+  if (kind < 1 || kind > 3) return 1;
+  const int nCells = M.nCells, nNodes = M.nNodes, nInner = M.nInner;
+  const int32_t* cnPtr = M.cellNodePtr.data();
+  const int32_t* cn = M.cellNodes.data();
+  std::vector<int32_t> ncPtr, ncList;
+  if (kind != 3) {
+    ncPtr.assign(nNodes + 1, 0);
+    for (int e = 0; e < nCells; ++e) for (int k = cnPtr[e]; k < cnPtr[e+1]; ++k) ncPtr[cn[k]+1]++;
+    for (int n = 0; n < nNodes; ++n) ncPtr[n+1] += ncPtr[n];
+    ncList.resize(ncPtr[nNodes]);
+    std::vector<int32_t> pos(ncPtr.begin(), ncPtr.end() - 1);
+    for (int e = 0; e < nCells; ++e) for (int k = cnPtr[e]; k < cnPtr[e+1]; ++k) ncList[pos[cn[k]]++] = e;
+  }
+  unsigned nt = std::thread::hardware_concurrency(); if (nt == 0) nt = 1; if (nt > 32) nt = 32;
+  std::vector<std::vector<int32_t> > lists(nt);
+  std::vector<int32_t> counts(nCells);
+  std::vector<int> chunkB(nt, 0), chunkE(nt, 0);
+  parallelFor(nCells, [&](int t, int b, int e2) {
+    chunkB[t] = b; chunkE[t] = e2;
+    std::vector<int32_t>& out = lists[t];
+    std::vector<int32_t> around;
+    for (int e = b; e < e2; ++e) {
+      const size_t start = out.size();
+      if (kind == 3) {
+        for (int k = M.cellFacePtr[e]; k < M.cellFacePtr[e+1]; ++k) {
+          const int f = M.cellFaces[k];
+          if (f < nInner && M.faceL[f] == e) out.push_back(M.faceR[f]);     // L < R by construction (a1)
+        }
+      } else {
+        around.clear();
+        for (int k = cnPtr[e]; k < cnPtr[e+1]; ++k)
+          for (int j = ncPtr[cn[k]]; j < ncPtr[cn[k]+1]; ++j) around.push_back(ncList[j]);
+        std::sort(around.begin(), around.end());
+        for (size_t i = 0; i < around.size();) {
+          size_t j = i;
+          while (j < around.size() && around[j] == around[i]) ++j;
+          const int32_t s = around[i];
+          if (kind == 1 ? (s != e) : (s > e && j - i >= 2)) out.push_back(s);
+          i = j;
+        }
+      }
+      counts[e] = (int32_t)(out.size() - start);
+    }
+  });
+  M.stencilPtr.assign(nCells + 1, 0);
+  for (int e = 0; e < nCells; ++e) M.stencilPtr[e+1] = M.stencilPtr[e] + counts[e];
+  M.stencil.assign(M.stencilPtr[nCells], 0);
+  for (unsigned t = 0; t < nt; ++t)
+    if (chunkE[t] > chunkB[t] && !lists[t].empty())
+      std::memcpy(&M.stencil[M.stencilPtr[chunkB[t]]], lists[t].data(), lists[t].size()*sizeof(int32_t));
+  return 0;
+}
+
 template <class T> const void* vptr(const std::vector<T>& v) { return v.data(); }
 
 } // namespace
@@ -560,6 +620,12 @@ void cfb200_mesh_view(const cfb200_meshdata* M, cfb200_mesh* o) {
   o->nodeNbrPtr = M->nodeNbrPtr.data(); o->nodeNbr = M->nodeNbr.data(); o->nodeW = M->nodeW.data();
   o->cvol = M->cvol.data(); o->cvSign = M->cvSign.data(); o->faceBC = M->faceBC.data(); o->updatable = M->updatable.data();
   o->cellNodePtr = M->cellNodePtr.data(); o->cellNodes = M->cellNodes.data();
+}
+
+int cfb200_mesh_set_stencil(cfb200_meshdata* M, int kind) {
+  if (!M) return CFB200_ERR_INVALID_ARG;
+  if (kind == CFB200_STENCIL_FACE_VERTEX_PLUS_GHOST) return CFB200_ERR_INVALID_ARG;   // what cfb200_mesh_build leaves; not rebuilt
+  try { return rebuildStencil(*M, kind) ? CFB200_ERR_INVALID_ARG : CFB200_OK; } catch (const std::exception&) { return CFB200_ERR_INVALID_ARG; }
 }
 
 void cfb200_mesh_set_updatable(cfb200_meshdata* M, const uint8_t* updatable) {

@@ -56,7 +56,7 @@ ABI_SYMBOLS = [
     "get_bsr_values",
     "export_csr", "get_field", "device_ptr", "status", "enable_timing", "last_timings", "stream",
     "nccl_unique_id", "comm_init", "set_halo", "set_independent_cells", "halo_begin", "halo_exchange", "allreduce_sum",
-    "mesh_build", "mesh_sizes", "mesh_get", "mesh_ptr", "mesh_view", "mesh_set_updatable", "mesh_free", "mesh_diamond_volumes",
+    "mesh_build", "mesh_sizes", "mesh_get", "mesh_ptr", "mesh_view", "mesh_set_updatable", "mesh_set_stencil", "mesh_free", "mesh_diamond_volumes",
     "selftest_divsqrt", "export_csr_device", "solve_gmres", "l2_norm_noalloc",
 ]
 # symbols the engine part needs (a test-only host build of the kernel functors exports just these)
@@ -125,6 +125,7 @@ def load(path=None, prefix="cfb200_"):
         ns.mesh_ptr.argtypes = [C.c_void_p, C.c_char_p]; ns.mesh_ptr.restype = C.c_void_p
         ns.mesh_view.argtypes = [C.c_void_p, C.POINTER(MeshStruct)]; ns.mesh_view.restype = None
         ns.mesh_set_updatable.argtypes = [C.c_void_p, P_U8]; ns.mesh_set_updatable.restype = None
+        ns.mesh_set_stencil.argtypes = [C.c_void_p, C.c_int]; ns.mesh_set_stencil.restype = C.c_int
         ns.mesh_free.argtypes = [C.c_void_p]; ns.mesh_free.restype = None
         ns.mesh_diamond_volumes.argtypes = [C.POINTER(MeshStruct), P_D, P_U8]; ns.mesh_diamond_volumes.restype = None
         ns.export_csr_device.argtypes = [H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
@@ -152,7 +153,10 @@ def _pu8(a):
     return a.ctypes.data_as(P_U8)
 
 
-def build_mesh(em, lib=None) -> FlatMesh:
+STENCIL_KINDS = {"FaceVertexPlusGhost": 0, "FaceVertex": 1, "FaceEdge": 2, "Face": 3}     # Setup1.stencil
+
+
+def build_mesh(em, lib=None, stencil="FaceVertexPlusGhost") -> FlatMesh:
     """Host mesh-data construction (cfb200_mesh_build): element description -> the flat arrays of the FVMCC sockets."""
     L = lib or load()
     h = L.mesh_build(em.dim, em.n_nodes, _pd(em.nodes), em.n_cells, _pi(em.cell_node_ptr), _pi(em.cell_nodes),
@@ -161,6 +165,8 @@ def build_mesh(em, lib=None) -> FlatMesh:
     if not h:
         raise Cfb200Error(2, "mesh build failed")
     try:
+        if STENCIL_KINDS[stencil] and L.mesh_set_stencil(h, STENCIL_KINDS[stencil]):
+            raise Cfb200Error(2, "stencil rebuild failed")
         sz = (C.c_int64*8)()
         L.mesh_sizes(h, sz)
         fm = FlatMesh(em.dim, em.nodes, em.cell_node_ptr, em.cell_nodes, em.cell_shape, em.trs_names)

@@ -365,6 +365,14 @@ int cfb200_mesh_get(const cfb200_meshdata* m, const char* name, void* dst);
 const void* cfb200_mesh_ptr(const cfb200_meshdata* m, const char* name);
 void cfb200_mesh_view(const cfb200_meshdata* m, cfb200_mesh* out);
 void cfb200_mesh_set_updatable(cfb200_meshdata* m, const uint8_t* updatable);
+/* replaces: the ComputeStencil strategy named by `Setup1.stencil` (LeastSquareP1Setup.cxx; providers "FaceVertex"
+ * ComputeFaceVertexNeighbors.cxx:45-129, "FaceEdge" ComputeFaceEdgeNeighbors.cxx:44-150, "Face" ComputeFaceNeighbors.cxx:46-108).
+ * cfb200_mesh_build leaves "FaceVertexPlusGhost" (ComputeFaceVertexNeighborsPlusGhost.cxx:46-230); this call replaces
+ * stencilPtr / stencil of *m by one of the others (FaceVertex / FaceEdge in ascending cell ID, Face in cellFaces order; FaceEdge
+ * and Face list each edge once, at its lower cell, as the reference does).  Returns CFB200_ERR_INVALID_ARG for any other kind.
+ * Under COOLFluiD the plugin reads whatever stencil the configured strategy left in socket "stencil". */
+enum { CFB200_STENCIL_FACE_VERTEX_PLUS_GHOST = 0, CFB200_STENCIL_FACE_VERTEX = 1, CFB200_STENCIL_FACE_EDGE = 2, CFB200_STENCIL_FACE = 3 };
+int cfb200_mesh_set_stencil(cfb200_meshdata* m, int kind);
 void cfb200_mesh_free(cfb200_meshdata* m);
 /* cvol / cvSign of a mesh assembled by the caller (DiamondVolume3DDerivative.cxx:413-563; zeros in 2D); the other
  * fields of *m must be set */

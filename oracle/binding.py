@@ -53,6 +53,8 @@ def lib(omp=False):
         L.cfo_mesh_sizes.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
         L.cfo_mesh_get.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p]
         L.cfo_mesh_free.argtypes = [C.c_void_p]
+        L.cfo_mesh_set_stencil.restype = C.c_int
+        L.cfo_mesh_set_stencil.argtypes = [C.c_void_p, C.c_int]
         L.cfo_apply_bc.argtypes = [C.POINTER(ConfigStruct), C.POINTER(MeshView), C.POINTER(BCStruct), P_D]
         L.cfo_compute.argtypes = [C.POINTER(ConfigStruct), C.POINTER(MeshView), C.POINTER(BCStruct), P_D, C.POINTER(Outputs)]
         L.cfo_time_rhs.argtypes = [C.POINTER(ConfigStruct), C.POINTER(MeshView), C.POINTER(BCStruct), P_D, P_D, C.POINTER(Outputs)]
@@ -102,7 +104,10 @@ def pu8(a):
     return a.ctypes.data_as(P_U8)
 
 
-def build_mesh(em) -> FlatMesh:
+STENCIL_KINDS = {"FaceVertexPlusGhost": 0, "FaceVertex": 1, "FaceEdge": 2, "Face": 3}     # Setup1.stencil
+
+
+def build_mesh(em, stencil="FaceVertexPlusGhost") -> FlatMesh:
     """Literal (slow) reference algorithm: FVMCC_MeshDataBuilder + geometry + stencils (oracle/cfo_mesh.hpp)."""
     L = lib()
     h = L.cfo_mesh_build(em.dim, em.n_nodes, pd(em.nodes), em.n_cells, pi(em.cell_node_ptr), pi(em.cell_nodes),
@@ -110,6 +115,8 @@ def build_mesh(em) -> FlatMesh:
                          pi(em.trs_face_node_ptr), pi(em.trs_face_nodes))
     if not h:
         raise RuntimeError("oracle mesh build failed")
+    if STENCIL_KINDS[stencil] and L.cfo_mesh_set_stencil(h, STENCIL_KINDS[stencil]):
+        raise RuntimeError("oracle stencil rebuild failed")
     sz = (C.c_int64*8)()
     L.cfo_mesh_sizes(h, sz)
     fm = FlatMesh(em.dim, em.nodes, em.cell_node_ptr, em.cell_nodes, em.cell_shape, em.trs_names)

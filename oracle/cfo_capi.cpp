@@ -52,6 +52,9 @@ int cfo_mesh_get(void* h, const char* name, void* dst) {
   return 1;
 }
 
+// Setup1.stencil = FaceVertex (1) | FaceEdge (2) | Face (3); the build leaves FaceVertexPlusGhost
+int cfo_mesh_set_stencil(void* h, int kind) { return rebuildStencil(*(MeshData*)h, kind); }
+
 void cfo_mesh_free(void* h) { delete (MeshData*)h; }
 
 int cfo_apply_bc(const Config* c, const MeshView* m, const BC* bcs, double* U) {

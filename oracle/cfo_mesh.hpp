@@ -6,6 +6,8 @@
 // linearly) so that the product's fast host builder can be checked against it bit for bit.
 #pragma once
 #include "cfo_physics.hpp"
+#include <map>
+#include <set>
 
 namespace cfo {
 
@@ -446,6 +448,56 @@ inline void buildMesh(int dim, int nNodes, const double* nodes, int nCells, cons
     M.bsrColInd.insert(M.bsrColInd.end(), cols.begin(), cols.end());
     M.bsrRowPtr.push_back((int)M.bsrColInd.size());
   }
+}
+
+// ---- the other ComputeStencil strategies selected by `Setup1.stencil` (a3).  kind: 1 "FaceVertex"
+// (ComputeFaceVertexNeighbors.cxx:45-129: every cell sharing a node, no ghosts), 2 "FaceEdge"
+// (ComputeFaceEdgeNeighbors.cxx:44-150: cells of HIGHER ID with at least two nodes in common), 3 "Face"
+// (ComputeFaceNeighbors.cxx:46-108: interior-face neighbours of higher ID, in cellFaces order).
+// CANONICAL ORDER for 1 and 2: the reference walks a std::set<State*> (pointer order of separately allocated
+// states, i.e. implementation-defined; allocation order in practice) - here ascending cell ID.
+// The one-directional lists of 2 and 3 are what the reference stores: its least-squares loop adds every edge to both
+// of its cells (LeastSquareP1PolyRec2D.cxx:100-134), so each edge is listed once.
+inline int rebuildStencil(MeshData& M, int kind) {
+  if (kind < 1 || kind > 3) return 1;
+  const int nCells = M.nCells, nInner = M.nInner;
+  std::multimap<int, int> mapNodeState;                       // key = node, value = cell (sorted by key)
+  for (int e = 0; e < nCells; ++e)
+    for (int k = M.cellNodePtr[e]; k < M.cellNodePtr[e+1]; ++k) mapNodeState.insert(std::make_pair(M.cellNodes[k], e));
+  M.stencilPtr.assign(1, 0);
+  M.stencil.clear();
+  for (int e = 0; e < nCells; ++e) {
+    if (kind == 3) {
+      for (int k = M.cellFacePtr[e]; k < M.cellFacePtr[e+1]; ++k) {
+        const int lf = M.cellFaces[k];
+        if (lf >= nInner) continue;                            // "neglect the neighbor state if it is a ghost one"
+        const int neighbor = M.faceR[lf];      // state 1 of the face on both branches (:76-88): the cell itself when it is the R cell
+        if (neighbor > e) M.stencil.push_back(neighbor);
+      }
+    } else {
+      std::set<int> neighborList;
+      const int nbNodesInCell = M.cellNodePtr[e+1] - M.cellNodePtr[e];
+      for (int iNode = 0; iNode < nbNodesInCell; ++iNode) {
+        const int nodeID = M.cellNodes[M.cellNodePtr[e] + iNode];
+        auto range = mapNodeState.equal_range(nodeID);
+        for (auto it = range.first; it != range.second; ++it) {
+          const int s = it->second;
+          if (s == e) continue;
+          if (kind == 1) { neighborList.insert(s); continue; }
+          if (!(s > e)) continue;
+          const int nbNeighborNodes = M.cellNodePtr[s+1] - M.cellNodePtr[s];
+          int matchingNodes = 0;
+          for (int in = 0; in < nbNodesInCell; ++in)
+            for (int ik = 0; ik < nbNeighborNodes; ++ik)
+              if (M.cellNodes[M.cellNodePtr[s] + ik] == M.cellNodes[M.cellNodePtr[e] + in]) { ++matchingNodes; break; }
+          if (matchingNodes >= 2) neighborList.insert(s);
+        }
+      }
+      M.stencil.insert(M.stencil.end(), neighborList.begin(), neighborList.end());
+    }
+    M.stencilPtr.push_back((int)M.stencil.size());
+  }
+  return 0;
 }
 
 } // namespace cfo

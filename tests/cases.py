@@ -132,6 +132,12 @@ def mhd3d_cfg(**over):
     return B.make_config(3, **kw)
 
 
+def with_stencil(em, kind):
+    """The element mesh with the reconstruction stencil of `Setup1.stencil = kind` (a3; the default is FaceVertexPlusGhost)."""
+    em.stencil_kind = kind
+    return em
+
+
 def ns3d_cfg(**over):
     kw = dict(update_var=B.UV_PVT, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, diffusive=B.DIFF_NS, jacobian=True)
     kw.update(ns_kwargs())
@@ -328,6 +334,15 @@ CASES = {
     "ns3d_farfield_pvt_sub": (lambda: meshgen.hex_box(5, 4, 4), ns3d_cfg, lambda: bcs_farfield(3, True), True),
     "ns3d_farfield_pvt_super": (lambda: meshgen.hex_box(5, 4, 4), lambda: ns3d_cfg(derivative="corrected"),
                                 lambda: bcs_farfield(3, True), "pvt_fast"),
+    # a3: the other ComputeStencil strategies (Setup1.stencil = FaceVertex: 59 of the reference's cases; FaceEdge; Face)
+    "euler2d_2nd_quad_facevertex": (lambda: with_stencil(meshgen.quad_channel(12, 9), "FaceVertex"),
+                                    lambda: B.make_config(2, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, jacobian=True,
+                                                          use_full_stencil=True), bcs_euler2d, False),
+    "ns3d_hex_facevertex": (lambda: with_stencil(meshgen.hex_box(6, 5, 4), "FaceVertex"), ns3d_cfg, bcs_ns3d, True),
+    "ns3d_tet_faceedge": (lambda: with_stencil(meshgen.tet_box(3, 3, 3), "FaceEdge"), ns3d_cfg, bcs_ns3d, True),
+    "euler2d_2nd_quad_face": (lambda: with_stencil(meshgen.quad_channel(10, 8), "Face"),
+                              lambda: B.make_config(2, poly_rec=B.PR_LINEARLS, limiter=B.LIM_BARTHJESP, jacobian=True,
+                                                    use_full_stencil=True), bcs_euler2d, False),
     # single cell / single row edge cases
     "ns3d_single_cell": (lambda: meshgen.hex_box(1, 1, 1, jitter=0.0), ns3d_cfg, bcs_ns3d, True),
     "euler2d_single_row": (lambda: meshgen.quad_channel(5, 1), lambda: B.make_config(2, poly_rec=B.PR_LINEARLS,
@@ -342,9 +357,10 @@ def run_case(name, oracle, make_engine, updatable=None, limiter_init=None, cfg_m
     shuffle: the cells of the mesh are renumbered at random first (the oracle then takes THAT numbering as the reference's)."""
     mesh_f, cfg_f, bcs_f, pvt = CASES[name]
     em = mesh_f()
+    stencil = getattr(em, "stencil_kind", "FaceVertexPlusGhost")
     if shuffle:
         em, _ = meshgen.shuffle_cells(em)
-    fm = oracle.build_mesh(em)
+    fm = oracle.build_mesh(em, stencil=stencil)
     cfg = cfg_f()
     if cfg_mut:
         cfg_mut(cfg)

@@ -26,6 +26,38 @@ def test_mesh_data_identical(name, oracle, product_lib):
     assert a.equal_to(b) == []
 
 
+@pytest.mark.parametrize("kind", ["FaceVertex", "FaceEdge", "Face"])
+@pytest.mark.parametrize("name", ["hex", "tet", "quad", "tri", "one_hex"])
+def test_stencil_variants_identical(name, kind, oracle, product_lib):
+    """Setup1.stencil = FaceVertex | FaceEdge | Face (cfb200_mesh_set_stencil: sort + run lengths over the cells around
+    the nodes) against the oracle's literal restatement of ComputeFaceVertexNeighbors / ComputeFaceEdgeNeighbors /
+    ComputeFaceNeighbors; everything but the stencil stays what the build left."""
+    em = MESHES[name]()
+    a = oracle.build_mesh(em, stencil=kind)
+    b = cl.build_mesh(em, product_lib, stencil=kind)
+    assert a.equal_to(b) == []
+    base = cl.build_mesh(em, product_lib)
+    assert b.stencil.max(initial=-1) < b.nCells                      # no ghost states in these
+    if kind == "FaceVertex":                                         # = FaceVertexPlusGhost without the ghosts
+        for e in range(b.nCells):
+            full = base.stencil[base.stencilPtr[e]:base.stencilPtr[e+1]]
+            assert sorted(full[full < b.nCells]) == list(b.stencil[b.stencilPtr[e]:b.stencilPtr[e+1]])
+    if kind == "Face":                                               # one entry per interior face
+        assert len(b.stencil) == b.nInner
+
+
+def test_stencil_kind_is_validated(product_lib):
+    em = meshgen.quad_channel(3, 3)
+    h = product_lib.mesh_build(em.dim, em.n_nodes, cl._pd(em.nodes), em.n_cells, cl._pi(em.cell_node_ptr),
+                               cl._pi(em.cell_nodes), cl._pi(em.cell_shape), em.n_trs, cl._pi(em.trs_face_ptr),
+                               cl._pi(em.trs_face_cell), cl._pi(em.trs_face_node_ptr), cl._pi(em.trs_face_nodes))
+    try:
+        assert product_lib.mesh_set_stencil(h, 7) == 2 and product_lib.mesh_set_stencil(h, 0) == 2
+        assert product_lib.mesh_set_stencil(h, 1) == 0
+    finally:
+        product_lib.mesh_free(h)
+
+
 def test_face_orientation_and_closure(product_lib):
     """Size-independent properties: L < R on inner faces (L is the first cell that creates the face,
     FVMCC_MeshDataBuilder.cxx:369-499), and the outward normals of every cell sum to zero."""
