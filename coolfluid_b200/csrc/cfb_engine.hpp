@@ -76,6 +76,7 @@ public:
   bool meshSet = false, statesSet = false;
   bool timeTermApplied = false;     // the last computeRhs applied the pseudo-steady time term itself (cfg.fuseTimeRhs)
   int lastStatus = 0;
+  uint8_t* nodePresc = nullptr; int* nodePrescIdx = nullptr; double* nodePrescVal = nullptr;   // behind Dev::nodePresc*
   double* bcFaceVal = nullptr; uint8_t* bcFaceFlag = nullptr;      // device copies behind Dev::bcFaceVal / bcFaceFlag
   std::vector<double> hBcFaceVal; std::vector<uint8_t> hBcFaceFlag; std::vector<int32_t> hGhostBC;
   // FD loop of the Roe families (CFB200_ROE_PIPELINE, for A/B measurements): 0 = rolled loop, 1 = software-pipelined,
@@ -771,6 +772,20 @@ public:
     bk.h2d(bcFaceVal, hBcFaceVal.data(), sizeof(double)*Q*ng);
     bk.h2d(bcFaceFlag, hBcFaceFlag.data(), ng);
     d.bcFaceVal = bcFaceVal; d.bcFaceFlag = bcFaceFlag;
+  }
+  // "DistanceBasedGMove": nodeFlag[nNodes] marks the nodes of the TRSs named by `TRSName` (the ones that belong to them,
+  // DistanceBasedExtrapolatorGMove.cxx:92-118), idx / values = `ValuesIdx` / `Values`; nodeFlag = nullptr or n = 0 reverts to
+  // the plain distance-based extrapolation.  Nodes keep the caller's numbering under cfg.renumber.
+  void setNodalPrescribed(const uint8_t* nodeFlag, int n, const int32_t* idx, const double* values) {
+    if (!nodeFlag || n == 0) { d.nodePresc = nullptr; d.nNodePresc = 0; return; }
+    for (int i = 0; i < n; ++i) if (idx[i] < 0 || idx[i] >= q()) throw std::invalid_argument("prescribed nodal value index out of range");
+    if (!nodePresc) nodePresc = dalloc<uint8_t>(d.nNodes);
+    if (!nodePrescIdx) { nodePrescIdx = dalloc<int>(CFB200_MAXEQ); nodePrescVal = dalloc<double>(CFB200_MAXEQ); }
+    if (n > CFB200_MAXEQ) throw std::invalid_argument("more prescribed nodal values than equations");
+    bk.h2d(nodePresc, nodeFlag, d.nNodes);
+    bk.h2d(nodePrescIdx, idx, sizeof(int)*n);
+    bk.h2d(nodePrescVal, values, sizeof(double)*n);
+    d.nodePresc = nodePresc; d.nodePrescIdx = nodePrescIdx; d.nodePrescVal = nodePrescVal; d.nNodePresc = n;
   }
   double updateSolFwdEuler(double cfl, int monitorVar) {
     if (isMhd()) bk.launch("updateSol", UpdateSolFwdEuler<3, MhdPhys>{d, cfl, monitorVar}, d.nCells, 256);

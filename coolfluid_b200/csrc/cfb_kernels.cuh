@@ -35,6 +35,9 @@ struct Dev {
   const double* cvol; const uint8_t* cvSign; const int* faceBC;
   const double* bcFaceVal;    // [q][nGhosts] position-dependent Dirichlet data (cfb200_set_bc_face_values), or null
   const uint8_t* bcFaceFlag;  // [nGhosts] 1 where bcFaceVal replaces BCond::value
+  // "DistanceBasedGMove" (DistanceBasedExtrapolatorGMove.cxx:167-173): nodes whose extrapolated values nodePrescIdx[i] are
+  // overwritten by nodePrescVal[i] (cfb200_set_nodal_prescribed); null = plain "DistanceBased"
+  const uint8_t* nodePresc; const int* nodePrescIdx; const double* nodePrescVal; int nNodePresc;
   const double* bcWallRatio;  // [nGhosts] (inner-ghost)/(inner-wall) distance ratio of FVMCC_BaseBC::computeGhostPosition, or null
   const int* bndStPtr; const int* bndSt;           // Corrected2D/3D: gradient stencil of each boundary face (CSR over ghosts)
   const int* ggPtr; const int* ggNode;   // CorrectedGG: per cell, the nodes of its faces in computeGradientsGG order (CSR over cells)
@@ -281,6 +284,13 @@ struct NodalExtrapolate {
       const double w = d.nodeW[k];
       const int s = d.nodeNbr[k];
       for (int v = 0; v < Q; ++v) ns[v] += d.U[(size_t)v*d.nStates + s]*w;
+    }
+    if (d.nodePresc && d.nodePresc[n]) {            // applyBC() after applyInner(), DistanceBasedExtrapolatorGMove.cxx:140-173
+      for (int i = 0; i < d.nNodePresc; ++i) {
+        const int idx = d.nodePrescIdx[i];
+        const double val = d.nodePrescVal[i];
+        for (int v = 0; v < Q; ++v) ns[v] = (v == idx) ? val : ns[v];
+      }
     }
     for (int v = 0; v < Q; ++v) d.nstates[(size_t)v*d.nNodes + n] = ns[v];
   }

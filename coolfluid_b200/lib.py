@@ -51,7 +51,7 @@ class BsrStruct(C.Structure):    # cfb200_bsr
 # every symbol include/cfb200.h declares (tests check that the library exports all of them)
 ABI_SYMBOLS = [
     "abi_version", "device_count", "create", "destroy", "last_error", "set_mesh", "set_step", "set_states",
-    "get_states", "set_past_states", "set_bc_face_values", "backup_past_states", "set_limiter", "set_update_coeff", "apply_bc",
+    "get_states", "set_past_states", "set_bc_face_values", "set_nodal_prescribed", "backup_past_states", "set_limiter", "set_update_coeff", "apply_bc",
     "compute_rhs", "time_rhs", "update_sol_fwd_euler", "update_sol_newton", "bsr_view", "bsr_pattern", "bsr_nnzb",
     "get_bsr_values",
     "export_csr", "get_field", "device_ptr", "status", "enable_timing", "last_timings", "stream",
@@ -98,6 +98,7 @@ def load(path=None, prefix="cfb200_"):
         f.argtypes = [H, P_D, C.c_int64]
     ns.backup_past_states.argtypes = [H]
     ns.set_bc_face_values.argtypes = [H, C.c_int, P_D]
+    ns.set_nodal_prescribed.argtypes = [H, P_U8, C.c_int32, P_I, P_D]
     ns.set_limiter.argtypes = [H, P_D]
     ns.set_update_coeff.argtypes = [H, P_D]
     ns.apply_bc.argtypes = [H]
@@ -256,6 +257,16 @@ class Engine:
     def set_bc_face_values(self, bc_index, values=None):
         pv = None if values is None else _pd(np.ascontiguousarray(values, dtype=np.float64))
         self._chk(self.L.set_bc_face_values(self.h, bc_index, pv), "set_bc_face_values")
+
+    def set_nodal_prescribed(self, node_flag=None, idx=(), values=()):
+        """NodalExtrapolation = DistanceBasedGMove: ValuesIdx / Values imposed on the flagged nodes (None reverts)."""
+        if node_flag is None:
+            self._chk(self.L.set_nodal_prescribed(self.h, None, 0, None, None), "set_nodal_prescribed")
+            return
+        fl = np.ascontiguousarray(node_flag, dtype=np.uint8)
+        ix = np.ascontiguousarray(idx, dtype=np.int32)
+        vv = np.ascontiguousarray(values, dtype=np.float64)
+        self._chk(self.L.set_nodal_prescribed(self.h, _pu8(fl), len(ix), _pi(ix), _pd(vv)), "set_nodal_prescribed")
 
     def set_update_coeff(self, uc=None):
         if uc is None:

@@ -241,6 +241,13 @@ int cfb200_backup_past_states(cfb200_handle* h);   /* device copy states -> past
  * condition record bcIndex in face-loop order replace cfb200_bc::value of a CFB200_BC_DIRICHLET record (the mask stays);
  * NULL reverts the record to its constant.  Call after cfb200_set_mesh. */
 int cfb200_set_bc_face_values(cfb200_handle* h, int bcIndex, const double* values);
+/* replaces: NodalExtrapolation = DistanceBasedGMove (plugins/FiniteVolume/DistanceBasedExtrapolatorGMove.cxx:92-118 setup,
+ * :140-173 applyBC / extrapolate): after the distance-weighted sum, the nodal values idx[i] (option `ValuesIdx`) of the
+ * flagged nodes are overwritten by values[i] (option `Values`).  nodeFlag[nNodes] = 1 for the nodes that belong to the TRSs
+ * named by option `TRSName` (a node belongs to the first TRS of the priority list that holds it: socket `trsID`).  n <= nEqs.
+ * nodeFlag = NULL or n = 0 reverts to the plain "DistanceBased" extrapolation.  Not provided: `RadEquilibrium`, nodal values
+ * interpolated from a file (`NodalValuesIDFlags`), `NbIterAdiabatic`.  Call after cfb200_set_mesh. */
+int cfb200_set_nodal_prescribed(cfb200_handle* h, const uint8_t* nodeFlag, int32_t n, const int32_t* idx, const double* values);
 
 /* limiter / updateCoeff sockets are stateful across calls (historical limiter; updateCoeff is zeroed by the updater) */
 int cfb200_set_limiter(cfb200_handle* h, const double* limiter /* AoS [nCells][nEqs] */);

@@ -24,7 +24,8 @@ class MeshView(C.Structure):
                 ("cellFacePtr", P_I), ("cellFaces", P_I), ("stencilPtr", P_I), ("stencil", P_I),
                 ("nodeNbrPtr", P_I), ("nodeNbr", P_I), ("nodeW", P_D), ("cvol", P_D), ("cvSign", P_U8),
                 ("faceBC", P_I), ("updatable", P_U8), ("cellNodePtr", P_I), ("cellNodes", P_I),
-                ("bcFaceVal", P_D), ("bcFaceFlag", P_U8)]
+                ("bcFaceVal", P_D), ("bcFaceFlag", P_U8),
+                ("nodePresc", P_U8), ("nodePrescIdx", P_I), ("nodePrescVal", P_D), ("nNodePresc", C.c_int32)]
 
 
 class Outputs(C.Structure):
@@ -138,7 +139,10 @@ def mesh_view(fm: FlatMesh) -> MeshView:
     mv.dim, mv.nCells, mv.nGhosts, mv.nNodes, mv.nFaces, mv.nInner = fm.dim, fm.nCells, fm.nGhosts, fm.nNodes, fm.nFaces, fm.nInner
     for name, _t in MeshView._fields_[6:]:
         a = getattr(fm, name, None)
-        if a is None:                       # optional: bcFaceVal / bcFaceFlag
+        if name == "nNodePresc":
+            mv.nNodePresc = len(getattr(fm, "nodePrescIdx", ()))
+            continue
+        if a is None:                       # optional: bcFaceVal / bcFaceFlag / nodePresc*
             continue
         setattr(mv, name, pd(a) if a.dtype == np.float64 else (pi(a) if a.dtype == np.int32 else pu8(a)))
     return mv

@@ -207,6 +207,10 @@ public:
         const double* s = &U[(size_t)mesh.nodeNbr[k]*Q];
         for (int i = 0; i < Q; ++i) ns[i] += s[i]*w;
       }
+      // DistanceBasedExtrapolatorGMove.cxx:162-173 extrapolate(): applyInner(), then applyBC() on the prescribed nodes;
+      // :140-160 applyBC() with constant Values (idx < _radTID = 10000000 always; no file-interpolated nodal values)
+      if (mesh.nodePresc && mesh.nodePresc[n])
+        for (int i = 0; i < mesh.nNodePresc; ++i) ns[mesh.nodePrescIdx[i]] = mesh.nodePrescVal[i];
     }
   }
 

@@ -147,6 +147,11 @@ struct MeshView {
   // point of each face): when bcFaceFlag[ghost] is set, BC_DIRICHLET reads bcFaceVal[ghost*q + v] instead of BC::value
   const double* bcFaceVal;    // [nGhosts*q] or NULL
   const uint8_t* bcFaceFlag;  // [nGhosts] or NULL
+  // NodalExtrapolation = DistanceBasedGMove (DistanceBasedExtrapolatorGMove.cxx): _isNodeToPrescribe, ValuesIdx, Values
+  const uint8_t* nodePresc;   // [nNodes] or NULL
+  const int32_t* nodePrescIdx;  // [nNodePresc]
+  const double* nodePrescVal;   // [nNodePresc]
+  int32_t nNodePresc;
 };
 
 } // namespace cfo

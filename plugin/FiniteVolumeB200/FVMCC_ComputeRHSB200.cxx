@@ -3,6 +3,7 @@
 #include <cstring>
 #include <sstream>
 #include <map>
+#include <algorithm>
 #include <typeinfo>
 #include "FiniteVolumeB200/FiniteVolumeB200.hh"
 #include "FiniteVolumeB200/FVMCC_ComputeRHSB200.hh"
@@ -13,6 +14,8 @@
 #include "Framework/LSSMatrix.hh"
 #include "Common/PE.hh"
 #include "Common/BadValueException.hh"
+#include "Common/NotImplementedException.hh"
+#include "Common/NoSuchStorageException.hh"
 #include "NavierStokes/EulerTerm.hh"
 #include "Framework/NodalStatesExtrapolator.hh"
 #include "Framework/ConnectivityTable.hh"
@@ -48,6 +51,7 @@ std::vector<SafePtr<BaseDataSocketSink> > FVMCC_ComputeRHSB200::needsSockets()
   std::vector<SafePtr<BaseDataSocketSink> > result = FVMCC_ComputeRHS::needsSockets();
   result.push_back(&socket_stencil);
   result.push_back(&socket_pastStates);      // not essential: only the fused pseudo-steady term reads it
+  result.push_back(&socket_trsID);           // not essential: only NodalExtrapolation = DistanceBasedGMove reads it
   return result;
 }
 
@@ -66,7 +70,8 @@ void FVMCC_ComputeRHSB200::defineConfigOptions(Config::OptionList& options)
 }
 
 FVMCC_ComputeRHSB200::FVMCC_ComputeRHSB200(const std::string& name) :
-  FVMCC_ComputeRHS(name), socket_stencil("stencil"), socket_pastStates("pastStates", false), m_h(CFNULL)
+  FVMCC_ComputeRHS(name), socket_stencil("stencil"), socket_pastStates("pastStates", false), socket_trsID("trsID", false),
+  m_h(CFNULL)
 {
   addConfigOptionsTo(this);
   m_device = -1;       setParameter("Device", &m_device);
@@ -515,6 +520,37 @@ void FVMCC_ComputeRHSB200::uploadMesh()
   check(cfb200_set_mesh(m_h, &mesh, (int)bcs.size(), bcs.empty() ? CFNULL : &bcs[0]), "cfb200_set_mesh");
   for (std::map<CFint, bool>::const_iterator it = positionDependent.begin(); it != positionDependent.end(); ++it)
     if (it->second) check(cfb200_set_bc_face_values(m_h, it->first, &faceValues[it->first][0]), "cfb200_set_bc_face_values");
+
+  // NodalExtrapolation = DistanceBasedGMove (DistanceBasedExtrapolatorGMove.cxx:92-118,140-173): the nodes of the TRSs named by
+  // `TRSName` that belong to them (socket trsID holds the position of the node's TRS in the extrapolator's ordered list:
+  // `TrsPriorityList`, else every boundary TRS in mesh order) get `Values` at `ValuesIdx` after the weighted sum
+  if (hasOpt(*nse, "ValuesIdx") && !optStr(*nse, "ValuesIdx", "").empty()) {
+    if (optStr(*nse, "RadEquilibrium", "0") == "1" || optStr(*nse, "RadEquilibrium", "false") == "true" ||
+        !optStr(*nse, "FileNameTw", "").empty() || optInt(*nse, "NbIterAdiabatic", 0) > 0)
+      throw Common::NotImplementedException(FromHere(), "B200: DistanceBasedGMove with RadEquilibrium / file-interpolated nodal values / NbIterAdiabatic");
+    if (!socket_trsID.isConnected()) throw Common::NoSuchStorageException(FromHere(), "B200: socket trsID is needed by DistanceBasedGMove");
+    DataHandle<CFint> trsID = socket_trsID.getDataHandle();
+    std::vector<std::string> ordered, wanted;
+    { std::istringstream in(optStr(*nse, "TrsPriorityList", "")); std::string w; while (in >> w) ordered.push_back(w); }
+    if (ordered.empty()) {
+      std::vector<SafePtr<TopologicalRegionSet> > trsList = MeshDataStack::getActive()->getTrsList();
+      for (CFuint i = 0; i < trsList.size(); ++i) {
+        const std::string nm = trsList[i]->getName();
+        if (nm != "InnerCells" && nm != "InnerFaces" && nm != "PartitionFaces") ordered.push_back(nm);
+      }
+    }
+    { std::istringstream in(optStr(*nse, "TRSName", "")); std::string w; while (in >> w) wanted.push_back(w); }
+    std::vector<uint8_t> nodeFlag(nNodes, 0);
+    for (CFuint n = 0; n < nNodes; ++n) {
+      const CFint id = trsID[n];
+      if (id >= 0 && (size_t)id < ordered.size() && std::find(wanted.begin(), wanted.end(), ordered[id]) != wanted.end()) nodeFlag[n] = 1;
+    }
+    std::vector<CFint> idx; std::vector<CFreal> val;
+    { std::istringstream in(optStr(*nse, "ValuesIdx", "")); CFint v; while (in >> v) idx.push_back(v); }
+    { std::istringstream in(optStr(*nse, "Values", "")); CFreal v; while (in >> v) val.push_back(v); }
+    if (idx.size() != val.size()) throw Common::BadValueException(FromHere(), "B200: DistanceBasedGMove ValuesIdx / Values sizes differ");
+    check(cfb200_set_nodal_prescribed(m_h, &nodeFlag[0], (CFint)idx.size(), &idx[0], &val[0]), "cfb200_set_nodal_prescribed");
+  }
 }
 
 void FVMCC_ComputeRHSB200::execute()

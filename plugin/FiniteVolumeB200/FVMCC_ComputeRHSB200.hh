@@ -40,6 +40,7 @@ protected:
 
   Framework::DataSocketSink<std::vector<Framework::State*> > socket_stencil;
   Framework::DataSocketSink<Framework::State*> socket_pastStates;   ///< non-essential (FVMCC_PseudoSteadyTimeRhs.cxx:55)
+  Framework::DataSocketSink<CFint> socket_trsID;   ///< non-essential: TRS of each boundary node (NodalStatesExtrapolator.ci:71,485), read for DistanceBasedGMove
   cfb200_handle* m_h;
   CFint m_device;          ///< option Device (-1: rank % device count, as CudaDeviceManager.cu:58)
   bool m_hostJacobian;     ///< option HostJacobian: copy the BSR back and LSSMatrix::addValues (CPU PETSc); else device view

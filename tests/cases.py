@@ -495,6 +495,53 @@ def check_bc_face_values(oracle, engine_factory):
         e.close()
 
 
+def check_nodal_prescribed(oracle, engine_factory):
+    """NodalExtrapolation = DistanceBasedGMove (DistanceBasedExtrapolatorGMove.cxx): velocity and temperature imposed on
+    the nodes that belong to the wall TRS (`TRSName = Wall`, `ValuesIdx = 1 2 3 4`, `Values = 0 0 0 Tw`, the options of
+    the reference's blunt-body cases): nodal states, viscous flux (rhs) and FD Jacobian against the oracle, on hexahedra
+    (DiamondVolume3D) and triangles (Corrected2D), then back to the plain extrapolation."""
+    for em, cfg, bcs, idx, vals in (
+            (meshgen.hex_box(5, 4, 4), ns3d_cfg(), bcs_ns3d(), [1, 2, 3, 4], [0., 0., 0., 1.1]),
+            (meshgen.quad_channel(8, 6, triangles=True), ns2d_cfg(derivative="corrected"), bcs_ns2d(), [3, 1], [0.9, 0.05])):
+        fm = oracle.build_mesh(em)
+        q = cfg.nEqs
+        wall = 2                                                    # record index of the no-slip wall in bcs_ns*()
+        # socket trsID: a boundary node belongs to the first TRS that lists it (NodalStatesExtrapolator.ci:529-560)
+        trs_id = np.full(fm.nNodes, -1)
+        for f in range(fm.nInner, fm.nFaces):
+            for n in fm.faceNodes[fm.faceNodePtr[f]:fm.faceNodePtr[f+1]]:
+                if trs_id[n] == -1:
+                    trs_id[n] = fm.faceBC[f]
+        flag = (trs_id == wall).astype(np.uint8)
+        assert flag.any() and not flag.all()
+        U = init_state(fm, q, True)
+        base = oracle.compute(cfg, fm, bcs, U.copy(), jacobian=True)
+        fm.nodePresc = flag
+        fm.nodePrescIdx = np.asarray(idx, dtype=np.int32)
+        fm.nodePrescVal = np.asarray(vals, dtype=np.float64)
+        r = oracle.compute(cfg, fm, bcs, U.copy(), jacobian=True)
+        assert r.status == 0
+        ns = r.nstates.reshape(-1, q)
+        assert all((ns[flag == 1, i] == v).all() for i, v in zip(idx, vals))
+        assert not np.array_equal(r.rhs, base.rhs)                  # the wall nodes feed the viscous flux
+        e = engine_factory(cfg)
+        try:
+            e.set_mesh(fm, bcs)
+            e.set_nodal_prescribed(flag, idx, vals)
+            e.set_states(U[:fm.nCells*q])
+            rhs, uc = e.compute_rhs()
+            assert np.array_equal(e.field("nstates"), r.nstates)
+            assert np.array_equal(rhs, r.rhs) and np.array_equal(uc, r.updateCoeff)
+            assert np.array_equal(e.bsr_values(), r.bsrVal)
+            e.set_nodal_prescribed(None)
+            e.set_update_coeff()
+            rhs, uc = e.compute_rhs()
+            assert np.array_equal(e.field("nstates"), base.nstates)
+            assert np.array_equal(rhs, base.rhs) and np.array_equal(e.bsr_values(), base.bsrVal)
+        finally:
+            e.close()
+
+
 def check_time_term_variants(oracle, engine_factory):
     """a21 FVMCC_PseudoSteadyTimeRhs in all its branches (steady updateCoeff/CFL, dt > 0, useGlobalDT, zeroDiagValue,
     numerical / analytical dU/dP), as a separate call (cfb200_time_rhs) and fused into compute_rhs (cfg.fuseTimeRhs):

@@ -26,9 +26,10 @@ def test_struct_layouts_match_the_oracle(oracle):
     L = oracle.lib()
     assert L.cfo_sizeof_config() == C.sizeof(B.ConfigStruct)
     assert L.cfo_sizeof_bc() == C.sizeof(B.BCStruct)
-    # the oracle's view = cfb200_mesh + two trailing optional pointers (per-face Dirichlet data, which the product
-    # receives through cfb200_set_bc_face_values instead)
-    assert L.cfo_sizeof_meshview() == C.sizeof(cl.MeshStruct) + 2*C.sizeof(C.c_void_p)
+    # the oracle's view = cfb200_mesh + trailing optional entries: per-face Dirichlet data (two pointers; the product
+    # receives them through cfb200_set_bc_face_values) and the prescribed nodal values of DistanceBasedGMove (three
+    # pointers and a count, padded; the product: cfb200_set_nodal_prescribed)
+    assert L.cfo_sizeof_meshview() == C.sizeof(cl.MeshStruct) + 6*C.sizeof(C.c_void_p)
 
 
 def test_product_does_not_link_the_oracle():

@@ -290,6 +290,11 @@ def test_position_dependent_inlet(oracle, product_lib):
     cases.check_bc_face_values(oracle, _factory(product_lib))
 
 
+@pytest.mark.gpu
+def test_nodal_values_prescribed_on_wall_nodes(oracle, product_lib):
+    cases.check_nodal_prescribed(oracle, _factory(product_lib))
+
+
 def test_newton_update(product_lib):
     cases.check_newton_update(_factory(product_lib), lambda em: cl.build_mesh(em, product_lib))
 

@@ -108,6 +108,10 @@ def test_position_dependent_inlet(oracle, hostsim_lib):
     cases.check_bc_face_values(oracle, _engine_factory(hostsim_lib))
 
 
+def test_nodal_values_prescribed_on_wall_nodes(oracle, hostsim_lib):
+    cases.check_nodal_prescribed(oracle, _engine_factory(hostsim_lib))
+
+
 def test_set_step_cannot_change_the_derivative_strategy(oracle, hostsim_lib):
     """The boundary gradient stencil of Corrected2D/3D is built at set_mesh: switching afterwards is refused."""
     from coolfluid_b200 import meshgen
