@@ -13,6 +13,7 @@ MAXEQ = 9
 
 # enums (must match include/cfb200.h and oracle/cfo_types.hpp)
 PM_EULER, PM_MHD3D_PROJECTION = 0, 1
+ST_NONE, ST_MHD_CONS_ACA = 0, 1      # Data.SourceTerm: none, MHDConsACAST (phi damping)
 DV_DIAMOND, DV_CORRECTED, DV_STATEDIFF, DV_CORRECTED_GG = 0, 1, 2, 3
 UV_CONS, UV_PVT = 0, 1
 FS_ROE, FS_AUSMPLUS, FS_AUSMPLUSUP, FS_LAXFRIED, FS_HLL, FS_ROESA, FS_CENTRED = 0, 1, 2, 3, 4, 5, 6
@@ -49,6 +50,7 @@ class ConfigStruct(C.Structure):
         ("venktnIsMFMHD", C.c_int32), ("psiMinEqual1", C.c_int32), ("strictCoeff", C.c_double),
         ("roeSaOldStencil", C.c_int32), ("mhdPotentialBType", C.c_int32),
         ("mhdDipole", C.c_double*3), ("noLimiterVar", C.c_int32*MAXEQ), ("correctedGGUseWeights", C.c_int32),
+        ("sourceTerm", C.c_int32), ("mhdDissipCoeff", C.c_double),
     ]
 
 
@@ -154,6 +156,8 @@ def make_config(dim, update_var=UV_CONS, flux=FS_ROE, poly_rec=PR_CONSTANT, limi
     c.correctedGGUseWeights = int(kw.get("gg_use_weights", 0))
     for i in kw.get("no_limiter_id", ()):            # Venktn2D "2DNoLimiterID"
         c.noLimiterVar[int(i)] = 1
+    c.sourceTerm = int(kw.get("source_term", 0))      # ST_MHD_CONS_ACA: MHDConsACAST
+    c.mhdDissipCoeff = float(kw.get("mhd_dissip_coeff", 0.0))
     dip = kw.get("mhd_dipole")                       # (mX, mY, mZ): potentialBType = Dipole
     c.mhdPotentialBType = 1 if dip is not None else 0
     for i in range(3):

@@ -38,6 +38,10 @@ inline bool splitterSupported(const cfb200_config& c) {
       c.derivativeStrategy != CFB200_DV_STATEDIFF && c.derivativeStrategy != CFB200_DV_CORRECTED_GG &&
       !(c.derivativeStrategy == CFB200_DV_CORRECTED && c.polyRec != CFB200_PR_CONSTANT))
     return false;
+  // Data.SourceTerm: none, or MHDConsACAST (its phi damping term) on MHD3DProjection, FD Jacobian (useAnalyticalJacob is off there)
+  if (c.sourceTerm != CFB200_ST_NONE &&
+      !(c.sourceTerm == CFB200_ST_MHD_CONS_ACA && c.physicalModel == CFB200_PM_MHD3D_PROJECTION && c.computeJacobian != 2 &&
+        !(c.mhdDissipCoeff < 0.))) return false;
   // background potential field: none or Dipole, MHD3DProjection only ("PFSS" needs the reference's harmonics data)
   if (c.mhdPotentialBType != 0 && !(c.mhdPotentialBType == 1 && c.physicalModel == CFB200_PM_MHD3D_PROJECTION)) return false;
   if (c.physicalModel == CFB200_PM_MHD3D_PROJECTION)      // MHD: centred splitters, conservative variables, inviscid
@@ -685,7 +689,16 @@ public:
     auto gather = [&](int c0, int c1) {      // residual gather + host copies of the cells [c0, c1)
       if (c1 <= c0) return;
       if (c0 > 0 || c1 < d.nCells) bk.window(c0, c1);
-      if (fused) bk.launchCellStaged("cellGather", CellGather<D, PH, true>{d, cfg}, d.nCells);
+      bool srcDone = false;
+      if constexpr (PH::Q == 9) {          // Data.SourceTerm (MHD3DProjection only): the variant that adds it at the cell's first face
+        if (cfg.sourceTerm != CFB200_ST_NONE) {
+          if (fused) bk.launchCellStaged("cellGather", CellGather<D, PH, true, true>{d, cfg}, d.nCells);
+          else bk.launch("cellGather", CellGather<D, PH, false, true>{d, cfg}, d.nCells, 256);
+          srcDone = true;
+        }
+      }
+      if (srcDone) {}
+      else if (fused) bk.launchCellStaged("cellGather", CellGather<D, PH, true>{d, cfg}, d.nCells);
       else bk.launch("cellGather", CellGather<D, PH, false>{d, cfg}, d.nCells, 256);
       if (hostRhs) bk.d2hOverlapped(hostRhs + (size_t)c0*PH::Q, d.rhs + (size_t)c0*PH::Q, sizeof(double)*(size_t)(c1 - c0)*PH::Q);
       if (hostUc) bk.d2hOverlapped(hostUc + c0, d.updateCoeff + c0, sizeof(double)*(size_t)(c1 - c0));
@@ -701,8 +714,17 @@ public:
       const int CH = (1 << 30)/DiagGather<D, PH>::GS;          // cells per launch
       for (int c0 = 0; c0 < d.nCells; c0 += CH) {
         const int ne = std::min(CH, d.nCells - c0)*DiagGather<D, PH>::GS;
-        if (fused) bk.launch("diagGather", DiagGather<D, PH, true>{d, c0}, ne, 256);
-        else bk.launch("diagGather", DiagGather<D, PH, false>{d, c0}, ne, 256);
+        bool srcDone = false;
+        if constexpr (PH::Q == 9) {
+          if (cfg.sourceTerm != CFB200_ST_NONE) {
+            if (fused) bk.launch("diagGather", DiagGather<D, PH, true, true>{d, c0, cfg}, ne, 256);
+            else bk.launch("diagGather", DiagGather<D, PH, false, true>{d, c0, cfg}, ne, 256);
+            srcDone = true;
+          }
+        }
+        if (srcDone) {}
+        else if (fused) bk.launch("diagGather", DiagGather<D, PH, true>{d, c0, cfg}, ne, 256);
+        else bk.launch("diagGather", DiagGather<D, PH, false>{d, c0, cfg}, ne, 256);
       }
       for (int c0 = 0; c0 < nNonUpd; c0 += CH)
         bk.launch("zeroRows", ZeroRows<D, PH>{d, nonUpdCells, c0}, std::min(CH, nNonUpd - c0)*ZeroRows<D, PH>::GS, 256);

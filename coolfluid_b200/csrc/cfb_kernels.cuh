@@ -550,12 +550,48 @@ CFB_HD void timeRhsRow(const Dev& d, const Cfg& c, int cell, const double* u, do
 }
 
 
+// Data.SourceTerm = MHDConsACAST (FiniteVolumeMHD/MHDConsACASourceTerm.cxx:164-211, solar terms off): the damping term of the
+// divergence-cleaning potential, from the CELL state u; correctionType "Hyperbolic" is mhdDissipCoeff = 0
+template <int D, class PH>
+CFB_HD void sourceTerm(const Dev& d, const Cfg& c, int cell, const double* u, double* S) {
+  constexpr int Q = PH::Q;
+  for (int v = 0; v < Q - 1; ++v) S[v] = 0.;
+  double last = 0.;
+  if (c.mhdDissipCoeff != 0.0) {
+    const double refSpeedSq = c.refSpeed*c.refSpeed;
+    const double dissipCoeffSq = c.mhdDissipCoeff*c.mhdDissipCoeff;
+    last = (-ddiv(refSpeedSq, dissipCoeffSq))*u[Q-1]*d.volumes[cell];
+  }
+  S[Q-1] = last;
+}
+// entry (row, col) of the finite-difference Jacobian of the source on the diagonal block (FVMCC_ComputeRhsJacob.cxx:359-364
+// with addSourceTermNumJacob, .hh:96-105; _upStFactor = -resFactor, FVMCC_ComputeRHS.hh:143)
+template <int D, class PH>
+CFB_HD double sourceJacobEntry(const Dev& d, const Cfg& c, int cell, int row, int col) {
+  constexpr int Q = PH::Q;
+  double u[Q], S[Q], Sp[Q];
+  for (int v = 0; v < Q; ++v) u[v] = d.U[(size_t)v*d.nStates + cell];
+  sourceTerm<D, PH>(d, c, cell, u, S);
+  double orig = 0.;
+  for (int v = 0; v < Q; ++v) orig = (v == col) ? u[v] : orig;
+  const double eps = fdEps(c, col, orig);
+  for (int v = 0; v < Q; ++v) u[v] = (v == col) ? u[v] + eps : u[v];
+  sourceTerm<D, PH>(d, c, cell, u, Sp);
+  const double invEps = ddiv(1., eps);
+  double sb = 0., sp = 0.;
+  for (int v = 0; v < Q; ++v) { sb = (v == row) ? S[v] : sb; sp = (v == row) ? Sp[v] : sp; }
+  double sum = 0.;
+  sum += (sp - sb)*invEps;
+  return sum*(-c.resFactor);
+}
+
 // a17: FVMCC_ComputeRHS::updateRHS (FVMCC_ComputeRHS.cxx:455-514) as a gather: for each cell, its faces in
 // ascending loop order; rhs starts from 0, updateCoeff accumulates onto the incoming value
 // (it is zeroed by the updater, UpdateSol.cxx:192).
 // FUSED: also applies the pseudo-steady time term (cfg.fuseTimeRhs); a template parameter so that the plain gather
 // keeps its register count (56 -> occupancy) when the term runs as its own kernel
-template <int D, class PH = Phys<D>, bool FUSED = false>
+// SRC: Data.SourceTerm, added (times resFactor) when the face loop first touches the cell (FVMCC_ComputeRHS.cxx:538-600)
+template <int D, class PH = Phys<D>, bool FUSED = false, bool SRC = false>
 struct CellGather {   // idx over cells
   static constexpr int BLK = PH::Q*PH::Q;      // FUSED: doubles of per-thread staging (the time-term block of the cell)
   Dev d; Cfg c;
@@ -572,6 +608,7 @@ struct CellGather {   // idx over cells
     double uc = d.updateCoeff[rc];
     const double coeff = c.resFactor*1.0;
     const bool hasDiff = (c.diffusive == CFB200_DIFF_NS);
+    bool first = true; (void)first;
     for (int j = d.cellFacePtr[cell]; j < d.cellFacePtr[cell+1]; ++j) {
       const int e = d.cellFaceSorted[j];
       const bool isR = e < 0;
@@ -579,6 +616,15 @@ struct CellGather {   // idx over cells
       const int oL = d.faceL[f];
       const bool skip = !(d.updatable[oL] || (f < d.nInner && d.updatable[d.faceR[f]]));
       if (skip) continue;
+      if constexpr (SRC) {
+        if (first) {
+          first = false;
+          double u[Q], S[Q];
+          for (int v = 0; v < Q; ++v) u[v] = d.U[(size_t)v*d.nStates + cell];
+          sourceTerm<D, PH>(d, c, cell, u, S);
+          for (int v = 0; v < Q; ++v) r[v] += (c.resFactor*S[v])*1.0;
+        }
+      }
       for (int v = 0; v < Q; ++v) {
         const double rFlux = coeff*d.faceFlux[(size_t)v*d.nFaces + f];
         if (isR) r[v] += rFlux*1.0; else r[v] -= rFlux*1.0;
@@ -628,10 +674,12 @@ struct DivBGather {   // idx over cells
 // Diagonal blocks: one thread per (cell, block entry).  diag(c) = sum over the cell's faces in loop order of
 //   inner face, c == L:  -block(R,c)      inner face, c == R:  -block(L,c)      boundary face: +bnd block
 // Rows of non-updatable cells are staging only and are zeroed by ZeroRows afterwards.
-template <int D, class PH = Phys<D>, bool FUSED = false>
+// SRC: the finite-difference Jacobian of Data.SourceTerm lands on the block right after the cell's first face
+template <int D, class PH = Phys<D>, bool FUSED = false, bool SRC = false>
 struct DiagGather {   // idx over nCells*GS: one thread per (cell, block entry), no idle lanes
   static constexpr int GS = PH::Q*PH::Q;
   Dev d; int cell0;      // cell0: first cell of this launch (chunks of < 2^31 entries start at a cell boundary)
+  Cfg c;                 // read by the SRC variant only
   CFB_HD void operator()(int idx) const {
     constexpr int Q = PH::Q;
     const int lc = idx/GS, e = idx - lc*GS;
@@ -656,7 +704,10 @@ struct DiagGather {   // idx over nCells*GS: one thread per (cell, block entry),
         }
 #pragma unroll
         for (int k = 0; k < 6; ++k)
-          if (j0 + k < je) { if (d.diagSrc[j0 + k] >= 0) acc -= x[k]; else acc += x[k]; }
+          if (j0 + k < je) {
+            if (d.diagSrc[j0 + k] >= 0) acc -= x[k]; else acc += x[k];
+            if constexpr (SRC) { if (j0 + k == jb) acc += sourceJacobEntry<D, PH>(d, c, cell, e/Q, e - (e/Q)*Q); }
+          }
       }
       // a21 fused: CellGather (one thread per cell, updateCoeff complete there) left the time-term block in the diagonal
       // slot; it lands on the finished face sum, as FVMCC_PseudoSteadyTimeRhs adds it after the face loop

@@ -23,9 +23,10 @@ extern "C" {
 #endif
 
 #define CFB200_MAXEQ 9
-#define CFB200_ABI_VERSION 2
+#define CFB200_ABI_VERSION 3
 
 /* ---- enums: values are shared with the .CFcase option strings through the plugin ---- */
+enum cfb200_source_term { CFB200_ST_NONE = 0, CFB200_ST_MHD_CONS_ACA = 1 };
 enum cfb200_physical_model { CFB200_PM_EULER = 0, CFB200_PM_MHD3D_PROJECTION = 1 };
 enum cfb200_update_var { CFB200_UV_CONS = 0 /* Euler2DCons, Euler3DCons */, CFB200_UV_PVT = 1 /* Euler2DPuvt, Euler3DPvt */ };
 enum cfb200_flux_splitter { CFB200_FS_ROE = 0 /* "Roe" plugins/FiniteVolume/RoeFlux.cxx */,
@@ -167,6 +168,15 @@ typedef struct cfb200_config {
                                        * variable is forced to 1 */
   int32_t correctedGGUseWeights;      /* CorrectedGG2D/3D option "useWeights" (CorrectedDerivativeGG2D.cxx:60-61,72-75): inverse
                                        * distance weights in the least squares of the boundary faces (default: none) */
+  /* Data.SourceTerm (FVMCC_ComputeRHS::computeSourceTerm, FVMCC_ComputeRHS.cxx:538-600: added to the rhs of a cell, times
+   * resFactor, when the face loop first touches the cell; FD Jacobian of the source on the diagonal block,
+   * FVMCC_ComputeRhsJacob.cxx:347-365,391-404, .hh:96-105).  CFB200_ST_MHD_CONS_ACA = "MHDConsACAST"
+   * (FiniteVolumeMHD/MHDConsACASourceTerm.cxx:164-211) with its solar terms off (gravity = Manchester = RadiativeLossTerm = 0,
+   * the defaults: 26 of the reference's 30 cases that name it): the damping term of the divergence-cleaning potential,
+   * S[phi] = -(refSpeed^2 / dissipCoeff^2) phi V for MHDTerm correctionType "Mixed" (mhdDissipCoeff = the model's
+   * dissipCoeff), zero for "Hyperbolic" (mhdDissipCoeff = 0).  MHD3DProjection only. */
+  int32_t sourceTerm;
+  double mhdDissipCoeff;
 } cfb200_config;
 
 /* Flat mesh data = the contents of the reference's sockets and connectivity tables (SURVEY.md §8b "Data ownership").

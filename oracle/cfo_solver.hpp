@@ -1033,6 +1033,30 @@ public:
     for (int ib = 0; ib < Q; ++ib) blk[ib*Q + jb] += v[ib];
   }
 
+  // ---- source term (Data.SourceTerm = MHDConsACAST): MHDConsACASourceTerm.cxx:164-211, the part that runs when
+  // gravity = Manchester = RadiativeLossTerm = 0 (:211 returns before the solar terms).  Reads the CELL state.
+  void computeSource(int cell, const double* U, double* source) const {
+    for (int i = 0; i < Q - 1; ++i) source[i] = 0.0;
+    const double refSpeedSq = cfg.refSpeed*cfg.refSpeed;
+    if (cfg.mhdDissipCoeff != 0.0) {                       // correctionType == "Mixed"
+      const double dissipCoeffSq = cfg.mhdDissipCoeff*cfg.mhdDissipCoeff;
+      source[Q-1] = -(refSpeedSq/dissipCoeffSq)*U[(size_t)cell*Q + Q - 1]*mesh.volumes[cell];
+    } else {
+      source[Q-1] = 0.0;                                    // "Hyperbolic"
+    }
+  }
+  // FVMCC_ComputeRhsJacob.cxx:359-364 / :400-405 with addSourceTermNumJacob (.hh:96-105): the state of `cell` is perturbed
+  // in place by the caller; _upStFactor = -resFactor (FVMCC_ComputeRHS.hh:143)
+  void addSourceJacobColumn(Outputs& o, int cell, const double* U, const double* source, int iVar, double eps) const {
+    double pertSource[Q], sourceDiffSum[Q];
+    computeSource(cell, U, pertSource);
+    const double invEps = 1./eps;
+    for (int i = 0; i < Q; ++i) sourceDiffSum[i] = 0.0;
+    for (int i = 0; i < Q; ++i) sourceDiffSum[i] += (pertSource[i] - source[i])*invEps;
+    for (int i = 0; i < Q; ++i) sourceDiffSum[i] *= -cfg.resFactor;
+    addColumn(o, cell, cell, iVar, sourceDiffSum);
+  }
+
   // ---- the command (a17, a18): FVMCC_ComputeRHS.cxx:139-325, FVMCC_ComputeRhsJacob.cxx:126-443
   // U holds cell states followed by ghost states ([nCells+nGhosts][q]); ghost states must already
   // be set (CellCenterFVM.cxx:464 applyBC before execute); U is perturbed and restored in place.
@@ -1075,6 +1099,21 @@ public:
         const double refSpeedSq = cfg.refSpeed*cfg.refSpeed;
         o.divB[x.L] += flux[Q-1]/(refSpeedSq*mesh.volumes[x.L]);
         if (!x.isB) o.divB[x.R] -= flux[Q-1]/(refSpeedSq*mesh.volumes[x.R]);
+      }
+      // computeSourceTerm (FVMCC_ComputeRHS.cxx:538-600): at the first face that touches the cell (cellFlag), before this
+      // face's flux is added; invR = 1 (non axisymmetric)
+      bool sourceJacobOnCell[2] = {false, false};
+      double source[2][Q];
+      if (cfg.sourceTerm) {
+        for (int iCell = 0; iCell < 2; ++iCell) {
+          if (iCell == 1 && x.isB) continue;
+          const int cellID = (iCell == 0) ? x.L : x.R;
+          if (cellFlag[cellID]) continue;
+          computeSource(cellID, U, source[iCell]);
+          for (int iEq = 0; iEq < Q; ++iEq) o.rhs[(size_t)cellID*Q + iEq] += cfg.resFactor*source[iCell][iEq]*1.0;
+          cellFlag[cellID] = 1;
+          sourceJacobOnCell[iCell] = true;
+        }
       }
       // updateRHS (FVMCC_ComputeRHS.cxx:455-514), non axisymmetric: _rMid = _invr = 1
       {
@@ -1156,10 +1195,12 @@ public:
               addColumn(o, x.L, st, iVar, fluxDiff);
               for (int i = 0; i < Q; ++i) fluxDiff[i] *= upFactor[1];
               addColumn(o, x.R, st, iVar, fluxDiff);
+              if (sourceJacobOnCell[iCell]) addSourceJacobColumn(o, st, U, source[iCell], iVar, eps);
             } else {
               const int idx = upL ? 0 : 1;
               for (int i = 0; i < Q; ++i) fluxDiff[i] *= upFactor[idx];
               addColumn(o, idx == 0 ? x.L : x.R, st, iVar, fluxDiff);
+              if (idx == iCell && sourceJacobOnCell[idx]) addSourceJacobColumn(o, st, U, source[iCell], iVar, eps);
             }
             val = orig;
             (iCell == 0 ? x.vL : x.vR)[iVar] = (iCell == 0 ? x.bL : x.bR)[iVar];   // restoreValues
@@ -1185,6 +1226,7 @@ public:
           for (int i = 0; i < Q; ++i) fluxDiff[i] = (pertFlux[i] - flux[i])*invEps;
           for (int i = 0; i < Q; ++i) fluxDiff[i] *= cfg.resFactor;
           addColumn(o, x.L, x.L, iVar, fluxDiff);
+          if (sourceJacobOnCell[0]) addSourceJacobColumn(o, x.L, U, source[0], iVar, eps);
           val = orig;
           for (int i = 0; i < Q; ++i) U[(size_t)x.R*Q + i] = origGhost[i];
         }

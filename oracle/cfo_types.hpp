@@ -117,6 +117,8 @@ struct Config {
   double mhdDipole[3];         // MHDTerm.cxx:38-40 mX mY mZ
   int32_t noLimiterVar[MAXEQ]; // Venktn2D.cxx:40-41,253-258 "2DNoLimiterID" as a per-variable flag
   int32_t correctedGGUseWeights; // CorrectedDerivativeGG2D.cxx:60-61
+  int32_t sourceTerm;          // Data.SourceTerm: 0 none, 1 "MHDConsACAST" (solar terms off)
+  double mhdDissipCoeff;       // MHDTerm dissipCoeff when correctionType == "Mixed", 0 for "Hyperbolic"
 };
 
 struct MeshView {

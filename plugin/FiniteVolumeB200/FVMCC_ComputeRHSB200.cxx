@@ -25,6 +25,7 @@
 #include "FiniteVolume/FVMCC_PolyRec.hh"
 #include "Framework/Limiter.hh"
 #include "Framework/FluxSplitter.hh"
+#include "Framework/ComputeSourceTerm.hh"
 #include "Framework/CFL.hh"
 #include "Framework/BlockAccumulator.hh"
 #include "Framework/LinearSystemSolver.hh"
@@ -151,6 +152,18 @@ void FVMCC_ComputeRHSB200::fillConfig(cfb200_config& c)
     const std::string pb = mhdTerm->getPotentialBType();
     c.mhdPotentialBType = (pb == "Dipole") ? 1 : (pb.empty() ? 0 : -1);
     c.mhdDipole[0] = mhdTerm->getMX(); c.mhdDipole[1] = mhdTerm->getMY(); c.mhdDipole[2] = mhdTerm->getMZ();
+    // Data.SourceTerm = MHDConsACAST (MHDConsACASourceTerm.cxx:164-211): the phi damping of correctionType "Mixed"
+    // (MHDTerm.hh:197,238); its solar terms (gravity, Manchester, RadiativeLossTerm, :211) are not provided
+    const std::vector<std::string> stNames = md.getSourceTermComputerNames();
+    if (stNames.size() > 1 || (stNames.size() == 1 && stNames[0] != "MHDConsACAST" && stNames[0] != "Null"))
+      throw Common::NotImplementedException(FromHere(), "B200: Data.SourceTerm other than MHDConsACAST");
+    if (stNames.size() == 1 && stNames[0] == "MHDConsACAST") {
+      SafePtr<ComputeSourceTerm<CellCenterFVMData> > st = (*md.getSourceTermComputer())[0];
+      if (optInt(*st, "gravity", 0) != 0 || optInt(*st, "Manchester", 0) != 0 || optInt(*st, "RadiativeLossTerm", 0) != 0)
+        throw Common::NotImplementedException(FromHere(), "B200: MHDConsACAST with gravity / Manchester / RadiativeLossTerm");
+      c.sourceTerm = CFB200_ST_MHD_CONS_ACA;
+      c.mhdDissipCoeff = (mhdTerm->getCorrectionType() == "Mixed") ? mhdTerm->getDissipationCoefficient() : 0.;
+    }
   } else {
     SafePtr<Physics::NavierStokes::EulerTerm> eulerTerm = pm->getConvectiveTerm().d_castTo<Physics::NavierStokes::EulerTerm>();
     c.physicalModel = CFB200_PM_EULER;

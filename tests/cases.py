@@ -260,6 +260,13 @@ CASES = {
     # BASELINE config 4: 3D ideal MHD with hyperbolic divergence cleaning (q = 9), HLL / Lax-Friedrichs
     "mhd3d_hex_hll": (lambda: meshgen.hex_box(5, 4, 4), mhd3d_cfg, bcs_mhd3d, "mhd"),
     # background potential field B0 = "Dipole" (MHDTerm potentialBType): enters the wave speeds and the update coefficient
+    # Data.SourceTerm = MHDConsACAST (26 of the reference's MHD cases, solar terms off): phi damping of the "Mixed" correction
+    # in rhs (first touch) and its FD Jacobian on the diagonal blocks; "Hyperbolic": the term and its Jacobian are zero
+    "mhd3d_hex_hll_aca_mixed": (lambda: meshgen.hex_box(5, 4, 4),
+                                lambda: mhd3d_cfg(source_term=B.ST_MHD_CONS_ACA, mhd_dissip_coeff=0.35, res_factor=0.8),
+                                bcs_mhd3d, "mhd"),
+    "mhd3d_tet_laxfried_aca_hyperbolic": (lambda: meshgen.tet_box(3, 3, 2),
+                                          lambda: mhd3d_cfg(flux=B.FS_LAXFRIED, source_term=B.ST_MHD_CONS_ACA), bcs_mhd3d, "mhd"),
     "mhd3d_hex_hll_dipole": (lambda: meshgen.hex_box(5, 4, 4), lambda: mhd3d_cfg(mhd_dipole=(0.002, 0.001, 0.004)),
                              bcs_mhd3d, "mhd"),
     "mhd3d_tet_laxfried_1st_dipole": (lambda: meshgen.tet_box(3, 3, 2),

@@ -18,7 +18,7 @@ def test_header_symbols_exported(product_lib):
     missing = [s for s in declared if not hasattr(dll, s)]
     assert missing == []
     assert sorted("cfb200_" + s for s in cl.ABI_SYMBOLS) == declared
-    assert dll.cfb200_abi_version() == 2
+    assert dll.cfb200_abi_version() == 3
 
 
 def test_struct_layouts_match_the_oracle(oracle):
