@@ -157,8 +157,9 @@ def _pu8(a):
 STENCIL_KINDS = {"FaceVertexPlusGhost": 0, "FaceVertex": 1, "FaceEdge": 2, "Face": 3}     # Setup1.stencil
 
 
-def build_mesh(em, lib=None, stencil="FaceVertexPlusGhost") -> FlatMesh:
+def build_mesh(em, lib=None, stencil=None) -> FlatMesh:
     """Host mesh-data construction (cfb200_mesh_build): element description -> the flat arrays of the FVMCC sockets."""
+    stencil = stencil or getattr(em, "stencil_kind", "FaceVertexPlusGhost")   # Setup1.stencil of the case (tests/cases.with_stencil)
     L = lib or load()
     h = L.mesh_build(em.dim, em.n_nodes, _pd(em.nodes), em.n_cells, _pi(em.cell_node_ptr), _pi(em.cell_nodes),
                      _pi(em.cell_shape), em.n_trs, _pi(em.trs_face_ptr), _pi(em.trs_face_cell),

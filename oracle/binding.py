@@ -108,8 +108,9 @@ def pu8(a):
 STENCIL_KINDS = {"FaceVertexPlusGhost": 0, "FaceVertex": 1, "FaceEdge": 2, "Face": 3}     # Setup1.stencil
 
 
-def build_mesh(em, stencil="FaceVertexPlusGhost") -> FlatMesh:
+def build_mesh(em, stencil=None) -> FlatMesh:
     """Literal (slow) reference algorithm: FVMCC_MeshDataBuilder + geometry + stencils (oracle/cfo_mesh.hpp)."""
+    stencil = stencil or getattr(em, "stencil_kind", "FaceVertexPlusGhost")   # Setup1.stencil of the case (tests/cases.with_stencil)
     L = lib()
     h = L.cfo_mesh_build(em.dim, em.n_nodes, pd(em.nodes), em.n_cells, pi(em.cell_node_ptr), pi(em.cell_nodes),
                          pi(em.cell_shape), em.n_trs, pi(em.trs_face_ptr), pi(em.trs_face_cell),
