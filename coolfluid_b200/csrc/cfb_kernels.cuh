@@ -149,6 +149,19 @@ CFB_HD void ghostState(const Dev& d, int g, const Cfg& c, const BCond& b, const 
       }
       break;
     }
+    case CFB200_BC_SUPER_OUTLET_MHD:      // SuperOutletMHD3DProjection.cxx:76-239: reads the inner and ghost state coordinates
+      if constexpr (Q == 9) {
+        const int L = d.faceL[d.nInner + g];
+        double xi[3], xg[3];
+        for (int k = 0; k < 3; ++k) {
+          xi[k] = d.centres[(size_t)k*d.nStates + L];
+          xg[k] = d.centres[(size_t)k*d.nStates + d.nCells + g];
+        }
+        P::superOutletGhost(c, b.mask[0] != 0, b.value[0], xi, xg, inner, ghost);
+      } else {
+        for (int i = 0; i < Q; ++i) ghost[i] = inner[i];       // rejected at set_mesh for the Euler models
+      }
+      break;
     default:                              // CFB200_BC_MIRROR_EULER_CONS: MirrorEuler2D.cxx:56-94 / MirrorMHD3DProjection.cxx:56-96
       P::mirrorGhost(c, nr, inner, ghost);
       break;

@@ -72,6 +72,57 @@ struct MhdPhys {
     dg.V = di.V; dg.A = di.A; dg.p = di.p; dg.B = di.B; dg.phi = di.phi;
     stateFromPhysicalData(c, dg, ghost);
   }
+  // SuperOutletMHD3DProjection.cxx:76-239.  coronal (option coronalBC, the default): r^2 Br, Btheta, r Bphi, r^3 rho,
+  // r^2 rho Vr, rho Vtheta, r Vphi and r^3 p continuous across the face, phi mirrored, on the state entries as they are;
+  // else the inner state rebuilt from its physical data with phi = refPhi.  Every quotient a/b of the reference is one
+  // correctly rounded division here too (divBy with the reciprocal of b shared between the quotients over the same b).
+  static CFB_HD void superOutletGhost(const Cfg& c, bool coronal, double refPhi, const double* xi, const double* xg,
+                                      const double* inner, double* ghost) {
+    if (!coronal) {
+      MhdData dg;
+      physicalData(c, inner, dg);
+      dg.phi = refPhi;
+      stateFromPhysicalData(c, dg, ghost);
+      return;
+    }
+    const double rI = dsqrt(xi[0]*xi[0] + xi[1]*xi[1] + xi[2]*xi[2]), rhoI = dsqrt(xi[0]*xi[0] + xi[1]*xi[1]);
+    const double rG = dsqrt(xg[0]*xg[0] + xg[1]*xg[1] + xg[2]*xg[2]), rhoG = dsqrt(xg[0]*xg[0] + xg[1]*xg[1]);
+    const Recip qrI = recipOf(rI), qrhoI = recipOf(rhoI), qrrI = recipOf(rhoI*rI);
+    const Recip qrG = recipOf(rG), qrhoG = recipOf(rhoG), qrrG = recipOf(rhoG*rG);
+    // spherical components of a Cartesian vector at the inner point
+    const double er[3] = {divBy(xi[0], qrI), divBy(xi[1], qrI), divBy(xi[2], qrI)};
+    const double et[3] = {divBy(xi[0]*xi[2], qrrI), divBy(xi[1]*xi[2], qrrI), divBy(rhoI, qrI)};
+    const double ep[2] = {divBy(-xi[1], qrhoI), divBy(xi[0], qrhoI)};
+    const double* V = inner + 1; const double* Bv = inner + 4;
+    const double BrI = er[0]*Bv[0] + er[1]*Bv[1] + er[2]*Bv[2];
+    const double BtI = et[0]*Bv[0] + et[1]*Bv[1] - et[2]*Bv[2];
+    const double BpI = ep[0]*Bv[0] + ep[1]*Bv[1];
+    const double VrI = er[0]*V[0] + er[1]*V[1] + er[2]*V[2];
+    const double VtI = et[0]*V[0] + et[1]*V[1] - et[2]*V[2];
+    const double VpI = ep[0]*V[0] + ep[1]*V[1];
+    const double rI2 = rI*rI, rG2 = rG*rG, rG3 = rG2*rG;
+    const Recip qrG3 = recipOf(rG3);
+    const double ratio = divBy(rI, qrG);
+    const double BrG = divBy(rI2, recipOf(rG2))*BrI, BtG = BtI, BpG = ratio*BpI;
+    const double rhoGst = divBy(rI2*rI*inner[0], qrG3);
+    const Recip qRhoG = recipOf(rhoGst);
+    const double VrG = ddiv(rI2*VrI*inner[0], rG2*rhoGst);
+    const double VtG = divBy(inner[0]*VtI, qRhoG);
+    const double VpG = ratio*VpI;
+    // back to Cartesian components at the ghost point
+    const double gr[3] = {divBy(xg[0], qrG), divBy(xg[1], qrG), divBy(xg[2], qrG)};
+    const double gt[3] = {divBy(xg[0]*xg[2], qrrG), divBy(xg[1]*xg[2], qrrG), divBy(rhoG, qrG)};
+    const double gp[2] = {divBy(xg[1], qrhoG), divBy(xg[0], qrhoG)};
+    ghost[0] = rhoGst;
+    ghost[1] = gr[0]*VrG + gt[0]*VtG - gp[0]*VpG;
+    ghost[2] = gr[1]*VrG + gt[1]*VtG + gp[1]*VpG;
+    ghost[3] = gr[2]*VrG - gt[2]*VtG;
+    ghost[4] = gr[0]*BrG + gt[0]*BtG - gp[0]*BpG;
+    ghost[5] = gr[1]*BrG + gt[1]*BtG + gp[1]*BpG;
+    ghost[6] = gr[2]*BrG - gt[2]*BtG;
+    ghost[7] = divBy(inner[7]*rI*rI*rI, qrG3);
+    ghost[8] = -inner[8];
+  }
   static CFB_HD void farFieldGhost(const Cfg&, const double*, const double*, const double* inner, double* ghost) {
     for (int i = 0; i < Q; ++i) ghost[i] = inner[i];         // FarFieldEuler is rejected for MHD at set_mesh
   }

@@ -53,6 +53,10 @@ enum cfb200_bc_type {
   CFB200_BC_MIRROR_EULER_CONS = 3, /* FiniteVolumeNavierStokes/MirrorEuler2D.cxx:56-94, MirrorEuler3D */
   CFB200_BC_FARFIELD_EULER = 4,    /* FiniteVolumeNavierStokes/FarFieldEuler2D.cxx:127-300 (conservative variables),
                                       FarFieldEuler3D.cxx:62-196 (Cons or Pvt): value = p, u, v, [w,] T at infinity */
+  CFB200_BC_SUPER_OUTLET_MHD = 6,  /* FiniteVolumeMHD/SuperOutletMHD3DProjection.cxx:76-239 (MHD3DProjection only; 16 of the reference's
+                                      cases): mask[0] = option coronalBC (default true: r^2 Br, Btheta, r Bphi, r^3 rho, r^2 rho Vr,
+                                      rho Vtheta, r Vphi, r^3 p continuous over the inner / ghost state positions, phi mirrored),
+                                      else the inner physical data with phi = value[0] (option refPhi) */
   CFB200_BC_NOSLIP_ISOTHERMAL = 5  /* FiniteVolumeNavierStokes/NoSlipWallIsothermalNSvt.ci:178-243 (Puvt / Pvt variables): velocity and
                                       temperature linearly extrapolated through the wall values over the inner-wall / inner-ghost
                                       distances of FVMCC_BaseBC.ci:271-350, the other variables copied.  value[1..dim] = uWall,

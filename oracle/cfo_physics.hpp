@@ -114,6 +114,9 @@ struct Phys {
   // Mach number of the inner state; inf = (p, u, v, [w,] T) at infinity (Pressure, Uinf, Vinf, Winf, Temperature).
   // The 2D command leaves EulerTerm::T of the ghost data unset in two of its branches, so only its conservative form
   // is a function of its inputs (Euler2DCons::computeStateFromPhysicalData does not read T); the 3D one sets T always.
+  static void superOutletGhost(const Config&, bool, double, const double*, const double*, const double*, double*) {
+    throw std::runtime_error("SuperOutletMHD3DProjection is a command of the MHD3DProjection model");
+  }
   static void farFieldGhost(const Config& cfg, const double* nr, const double* inf, const double* inner, double* ghost) {
     if (D == 2 && cfg.updateVar != UV_CONS) throw std::runtime_error("FarFieldEuler2D: conservative variables only");
     double n[3] = {0., 0., 0.};
@@ -1162,6 +1165,54 @@ struct MhdPhys {
     dg.b[0] = di.b[0] - 2.0*bn*nx; dg.b[1] = di.b[1] - 2.0*bn*ny; dg.b[2] = di.b[2] - 2.0*bn*nz;
     dg.V = di.V; dg.A = di.A; dg.p = di.p; dg.B = di.B; dg.phi = di.phi;
     stateFromPhysicalData(c, dg, ghost);
+  }
+  // FiniteVolumeMHD/SuperOutletMHD3DProjection.cxx:76-239.  coronalBC (the default, :45): the "_dimless" lines :99-226, the
+  // state entries read as (rho, V, B, p, phi) whatever the update variables are; otherwise the inner physical data with
+  // phi = refPhi through computeStateFromPhysicalData (:228-238).  xI / xG: inner and ghost state coordinates.
+  static void superOutletGhost(const Config& c, bool coronalBC, double refPhi, const double* xIc, const double* xGc,
+                               const double* inner, double* ghost) {
+    if (!coronalBC) {
+      MhdData dg;
+      computePhysicalData(c, inner, dg);
+      dg.phi = refPhi;
+      stateFromPhysicalData(c, dg, ghost);
+      return;
+    }
+    const double xI = xIc[0], yI = xIc[1], zI = xIc[2];
+    double sq = 0.; sq += xI*xI; sq += yI*yI; sq += zI*zI;            // RealVector::norm2 (ArrayT.hh:93-124)
+    const double rI = std::sqrt(sq);
+    const double rhoI = std::sqrt(xI*xI + yI*yI);
+    const double xG = xGc[0], yG = xGc[1], zG = xGc[2];
+    sq = 0.; sq += xG*xG; sq += yG*yG; sq += zG*zG;
+    const double rG = std::sqrt(sq);
+    const double rhoG = std::sqrt(xG*xG + yG*yG);
+    const double densityI = inner[0];
+    const double VxI = inner[1], VyI = inner[2], VzI = inner[3];
+    const double BxI = inner[4], ByI = inner[5], BzI = inner[6];
+    const double BrI = xI/rI*BxI + yI/rI*ByI + zI/rI*BzI;
+    const double BthetaI = xI*zI/(rhoI*rI)*BxI + yI*zI/(rhoI*rI)*ByI - rhoI/rI*BzI;
+    const double BphiI = -yI/rhoI*BxI + xI/rhoI*ByI;
+    const double VrI = xI/rI*VxI + yI/rI*VyI + zI/rI*VzI;
+    const double VthetaI = xI*zI/(rhoI*rI)*VxI + yI*zI/(rhoI*rI)*VyI - rhoI/rI*VzI;
+    const double VphiI = -yI/rhoI*VxI + xI/rhoI*VyI;
+    const double BrG = rI*rI/(rG*rG)*BrI;
+    const double BthetaG = BthetaI;
+    const double BphiG = (rI/rG)*BphiI;
+    const double densityG = rI*rI*rI*densityI/(rG*rG*rG);
+    ghost[0] = densityG;
+    const double VrG = rI*rI*VrI*densityI/(rG*rG*densityG);
+    const double VthetaG = densityI*VthetaI/densityG;
+    const double VphiG = (rI/rG)*VphiI;
+    const double BxG = xG/rG*BrG + xG*zG/(rhoG*rG)*BthetaG - yG/rhoG*BphiG;
+    const double ByG = yG/rG*BrG + yG*zG/(rhoG*rG)*BthetaG + xG/rhoG*BphiG;
+    const double BzG = zG/rG*BrG - rhoG/rG*BthetaG;
+    const double VxG = xG/rG*VrG + xG*zG/(rhoG*rG)*VthetaG - yG/rhoG*VphiG;
+    const double VyG = yG/rG*VrG + yG*zG/(rhoG*rG)*VthetaG + xG/rhoG*VphiG;
+    const double VzG = zG/rG*VrG - rhoG/rG*VthetaG;
+    ghost[4] = BxG; ghost[5] = ByG; ghost[6] = BzG;
+    ghost[1] = VxG; ghost[2] = VyG; ghost[3] = VzG;
+    ghost[7] = inner[7]*rI*rI*rI/(rG*rG*rG);
+    ghost[8] = -inner[8];
   }
   static void convFlux(const Config& c, const MhdData& d, const double* n, double* f) {
     const double nx = n[0], ny = n[1], nz = n[2];

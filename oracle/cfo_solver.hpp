@@ -94,6 +94,10 @@ public:
         }
         break;
       }
+      case BC_SUPER_OUTLET_MHD:        // SuperOutletMHD3DProjection.cxx:76-239 (inner / ghost state coordinates)
+        P::superOutletGhost(cfg, b.mask[0] != 0, b.value[0], &mesh.centres[(size_t)mesh.faceL[f]*D],
+                            &mesh.centres[(size_t)mesh.faceR[f]*D], inner, ghost);
+        break;
       default: throw std::runtime_error("unknown BC type");
     }
   }

@@ -329,6 +329,13 @@ cfb200_bc FVMCC_ComputeRHSB200::translateBC(FVMCC_BC* bc, GeometricEntity* probe
   const std::string cls = Common::demangle(typeid(*bc).name());
   const auto has = [&](const char* name) { return cls.find(name) != std::string::npos; };
   const auto opt = [&](const char* name) { return std::strtod(bc->getOption(name)->getValueAsString().c_str(), CFNULL); };
+  if (has("SuperOutletMHD3DProjection") && !has("Heating")) {       // SuperOutletMHD3DProjection.cxx:34-48: refPhi, coronalBC
+    out.type = CFB200_BC_SUPER_OUTLET_MHD;
+    const std::string cor = bc->getOption("coronalBC")->getValueAsString();
+    out.mask[0] = (cor == "true" || cor == "1") ? 1 : 0;
+    out.value[0] = std::strtod(bc->getOption("refPhi")->getValueAsString().c_str(), CFNULL);
+    return out;
+  }
   if (has("MirrorVelocity")) { out.type = CFB200_BC_MIRROR_VELOCITY; return out; }
   if (has("MirrorEuler2D") || has("MirrorEuler3D") || has("MirrorMHD3DProjection")) {
     out.type = CFB200_BC_MIRROR_EULER_CONS; return out;

@@ -124,6 +124,15 @@ def bcs_mhd3d():
     return [inl, B.make_bc(B.BC_SUPER_OUTLET), mir, mir, mir, mir]
 
 
+def bcs_mhd3d_outlet(coronal, ref_phi=0.0):
+    """bcs_mhd3d with SuperOutletMHD3DProjection (coronalBC or refPhi form) at xmax and on one side."""
+    b = bcs_mhd3d()
+    out = B.make_bc(B.BC_SUPER_OUTLET_MHD, mask=[1 if coronal else 0] + [0]*8, value=[ref_phi] + [0.]*8)
+    b[1] = out
+    b[3] = out
+    return b
+
+
 def mhd3d_cfg(**over):
     """BASELINE config 4: MHD3DProjection, q = 9, gamma 1.05, refSpeed 1."""
     kw = dict(physical_model=B.PM_MHD3D_PROJECTION, flux=B.FS_HLL, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN,
@@ -267,6 +276,13 @@ CASES = {
                                 bcs_mhd3d, "mhd"),
     "mhd3d_tet_laxfried_aca_hyperbolic": (lambda: meshgen.tet_box(3, 3, 2),
                                           lambda: mhd3d_cfg(flux=B.FS_LAXFRIED, source_term=B.ST_MHD_CONS_ACA), bcs_mhd3d, "mhd"),
+    # SuperOutletMHD3DProjection (16 of the reference's cases): the coronal form (default) and the refPhi form, with the FD
+    # Jacobian of the boundary faces (the BC is re-applied on the perturbed inner state)
+    "mhd3d_hex_hll_outlet_coronal": (lambda: meshgen.hex_box(5, 4, 4),
+                                     lambda: mhd3d_cfg(source_term=B.ST_MHD_CONS_ACA, mhd_dissip_coeff=0.5),
+                                     lambda: bcs_mhd3d_outlet(True), "mhd"),
+    "mhd3d_tet_laxfried_outlet_refphi": (lambda: meshgen.tet_box(3, 3, 2), lambda: mhd3d_cfg(flux=B.FS_LAXFRIED),
+                                         lambda: bcs_mhd3d_outlet(False, 0.02), "mhd"),
     "mhd3d_hex_hll_dipole": (lambda: meshgen.hex_box(5, 4, 4), lambda: mhd3d_cfg(mhd_dipole=(0.002, 0.001, 0.004)),
                              bcs_mhd3d, "mhd"),
     "mhd3d_tet_laxfried_1st_dipole": (lambda: meshgen.tet_box(3, 3, 2),
