@@ -21,7 +21,7 @@ PR_CONSTANT, PR_LINEARLS = 0, 1
 LIM_NONE, LIM_VENKTN, LIM_BARTHJESP, LIM_VENKTN_STRICT = 0, 1, 2, 3
 DIFF_NONE, DIFF_NS = 0, 1
 VISC_SIMPLER_SUTHERLAND, VISC_SUTHERLAND, VISC_FIXED = 0, 1, 2
-BC_SUPER_OUTLET, BC_DIRICHLET, BC_MIRROR_VELOCITY, BC_MIRROR_EULER_CONS, BC_FARFIELD_EULER, BC_NOSLIP_ISOTHERMAL, BC_SUPER_OUTLET_MHD = 0, 1, 2, 3, 4, 5, 6
+BC_SUPER_OUTLET, BC_DIRICHLET, BC_MIRROR_VELOCITY, BC_MIRROR_EULER_CONS, BC_FARFIELD_EULER, BC_NOSLIP_ISOTHERMAL, BC_SUPER_OUTLET_MHD, BC_FARFIELD_EULER_CHAR = 0, 1, 2, 3, 4, 5, 6, 7
 
 
 class ConfigStruct(C.Structure):

@@ -149,6 +149,10 @@ CFB_HD void ghostState(const Dev& d, int g, const Cfg& c, const BCond& b, const 
       }
       break;
     }
+    case CFB200_BC_FARFIELD_EULER_CHAR:   // FarFieldEulerChar2D.cxx:36-254, FarFieldEulerChar3D.cxx:40-200
+      if constexpr (Q != 9) P::farFieldCharGhost(c, nr, b.value, inner, ghost);
+      else { for (int i = 0; i < Q; ++i) ghost[i] = inner[i]; }      // rejected at set_mesh for MHD
+      break;
     case CFB200_BC_SUPER_OUTLET_MHD:      // SuperOutletMHD3DProjection.cxx:76-239: reads the inner and ghost state coordinates
       if constexpr (Q == 9) {
         const int L = d.faceL[d.nInner + g];

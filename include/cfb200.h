@@ -53,6 +53,9 @@ enum cfb200_bc_type {
   CFB200_BC_MIRROR_EULER_CONS = 3, /* FiniteVolumeNavierStokes/MirrorEuler2D.cxx:56-94, MirrorEuler3D */
   CFB200_BC_FARFIELD_EULER = 4,    /* FiniteVolumeNavierStokes/FarFieldEuler2D.cxx:127-300 (conservative variables),
                                       FarFieldEuler3D.cxx:62-196 (Cons or Pvt): value = p, u, v, [w,] T at infinity */
+  CFB200_BC_FARFIELD_EULER_CHAR = 7, /* FiniteVolumeNavierStokes/FarFieldEulerChar2D.cxx:36-254, FarFieldEulerChar3D.cxx:40-200 (Cons, Puvt,
+                                      Pvt; no StateInterpolator): value as CFB200_BC_FARFIELD_EULER; the subsonic branches follow
+                                      the mean of the two Riemann invariants */
   CFB200_BC_SUPER_OUTLET_MHD = 6,  /* FiniteVolumeMHD/SuperOutletMHD3DProjection.cxx:76-239 (MHD3DProjection only; 16 of the reference's
                                       cases): mask[0] = option coronalBC (default true: r^2 Br, Btheta, r Bphi, r^3 rho, r^2 rho Vr,
                                       rho Vtheta, r Vphi, r^3 p continuous over the inner / ghost state positions, phi mirrored),

@@ -177,6 +177,66 @@ struct Phys {
     }
   }
 
+  // FarFieldEulerChar2D.cxx:36-254 / FarFieldEulerChar3D.cxx:40-200 (no StateInterpolator): far field through the Riemann
+  // invariants R+ = vn + 2a/(gamma-1) of the inner state and R- = vn_inf - 2a_inf/(gamma-1).  Supersonic branches as in
+  // FarFieldEuler; subsonic: outflow when (R+ + R-)/2 > 0 (inner rho and p, normal velocity corrected), inflow otherwise
+  // (rho, p from infinity).  Every branch sets T, so all variable sets are served.  2D takes `<= 0` for the inflow
+  // branch, 3D `< 0` (an exactly zero mean then leaves the ghost state as it was: restated here as inflow).
+  static void farFieldCharGhost(const Config& cfg, const double* nr, const double* inf, const double* inner, double* ghost) {
+    double n[3] = {0., 0., 0.};
+    double s2;
+    if (D == 2) s2 = nr[0]*nr[0] + nr[1]*nr[1]; else s2 = nr[0]*nr[0] + nr[1]*nr[1] + nr[2]*nr[2];
+    const double invFaceLength = 1./std::sqrt(s2);
+    for (int i = 0; i < D; ++i) n[i] = nr[i]*invFaceLength;
+    PData di, dg;
+    computePhysicalData(cfg, inner, di);
+    const double gamma = cfg.gamma, gammaMinus1 = gamma - 1.0;
+    const double gammaDivGammaMinus1 = gamma/(gamma - 1.0);
+    const double R = cfg.R;
+    const double pInf = inf[0], TInf = inf[D+1];
+    const double rho = di.rho, pInnerState = di.p, aInnerState = di.A;
+    double vn, vnInf;
+    if (D == 2) { vn = di.v[0]*n[0] + di.v[1]*n[1]; vnInf = inf[1]*n[0] + inf[2]*n[1]; }
+    else { vn = di.v[0]*n[0] + di.v[1]*n[1] + di.v[2]*n[2]; vnInf = inf[1]*n[0] + inf[2]*n[1] + inf[3]*n[2]; }
+    const double machInner = vn/aInnerState;
+    const double rhoInf = pInf/(R*TInf);
+    const double aInf = std::sqrt(gamma*pInf/rhoInf);
+    const double RPlus_n = vn + (2.*aInnerState)/(gammaMinus1);
+    const double RMin_n = vnInf - (2.*aInf)/(gammaMinus1);
+    const double RMinRmax = (RPlus_n + RMin_n)*0.5;
+    auto finish = [&]() {
+      if (D == 2) dg.V = std::sqrt(dg.v[0]*dg.v[0] + dg.v[1]*dg.v[1]);
+      else dg.V = std::sqrt(dg.v[0]*dg.v[0] + dg.v[1]*dg.v[1] + dg.v[2]*dg.v[2]);
+      dg.H = (gammaDivGammaMinus1*dg.p + 0.5*dg.rho*dg.V*dg.V)/dg.rho;
+      dg.A = std::sqrt(gamma*dg.p/dg.rho);
+      dg.T = dg.p/(dg.rho*R);
+      if (cfg.updateVar == UV_CONS) stateFromPhysicalDataCons(dg, ghost);
+      else { ghost[0] = dg.p; for (int i = 0; i < D; ++i) ghost[1+i] = dg.v[i]; ghost[TID] = dg.T; }
+    };
+    dg.v[2] = 0.;
+    if (machInner >= 1.0) for (int i = 0; i < Q; ++i) ghost[i] = inner[i];
+    if (machInner <= -1.0) {
+      dg.rho = 2.0*rhoInf - rho;
+      for (int i = 0; i < D; ++i) dg.v[i] = 2.0*inf[1+i] - di.v[i];
+      dg.p = 2.0*pInf - pInnerState;
+      finish();
+    }
+    if (std::fabs(machInner) < 1.0) {
+      if (RMinRmax > 0.) {
+        const double vnInner = vn;
+        dg.rho = di.rho;
+        for (int i = 0; i < D; ++i) { const double bound = di.v[i] + (RMinRmax - vnInner)*n[i]; dg.v[i] = 2.0*bound - di.v[i]; }
+        dg.p = di.p;
+        finish();
+      } else {
+        dg.rho = pInf/(R*TInf);
+        for (int i = 0; i < D; ++i) { const double bound = inf[1+i] + (RMinRmax - vnInf)*n[i]; dg.v[i] = 2.0*bound - di.v[i]; }
+        dg.p = pInf;
+        finish();
+      }
+    }
+  }
+
   // Euler2DVarSet.cxx:83-117, Euler3DVarSet.cxx:78-105
   static void convFlux(const PData& d, const double* n, double* f) {
     double un;
@@ -1150,6 +1210,9 @@ struct MhdPhys {
   }
   static void farFieldGhost(const Config&, const double*, const double*, const double*, double*) {
     throw std::runtime_error("FarFieldEuler on MHD3DProjection");
+  }
+  static void farFieldCharGhost(const Config&, const double*, const double*, const double*, double*) {
+    throw std::runtime_error("FarFieldEulerChar on MHD3DProjection");
   }
   // FiniteVolumeMHD/MirrorMHD3DProjection.cxx:56-96
   static void mirrorGhost(const Config& c, const double* nr, const double* inner, double* ghost) {

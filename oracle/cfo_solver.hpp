@@ -94,6 +94,9 @@ public:
         }
         break;
       }
+      case BC_FARFIELD_EULER_CHAR:     // FarFieldEulerChar2D.cxx:36-254, FarFieldEulerChar3D.cxx:40-200
+        P::farFieldCharGhost(cfg, &mesh.normals[(size_t)f*D], b.value, inner, ghost);
+        break;
       case BC_SUPER_OUTLET_MHD:        // SuperOutletMHD3DProjection.cxx:76-239 (inner / ghost state coordinates)
         P::superOutletGhost(cfg, b.mask[0] != 0, b.value[0], &mesh.centres[(size_t)mesh.faceL[f]*D],
                             &mesh.centres[(size_t)mesh.faceR[f]*D], inner, ghost);

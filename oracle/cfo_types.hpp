@@ -45,6 +45,7 @@ enum BCType {
   BC_MIRROR_VELOCITY = 2,  // FiniteVolume/MirrorVelocity.cxx:71-111
   BC_MIRROR_EULER_CONS = 3, // FiniteVolumeNavierStokes/MirrorEuler2D.cxx:56-94 (+3D analogue)
   BC_FARFIELD_EULER = 4,   // FiniteVolumeNavierStokes/FarFieldEuler2D.cxx:127-300, FarFieldEuler3D.cxx:62-196; value = p u v [w] T at infinity
+  BC_FARFIELD_EULER_CHAR = 7, // FiniteVolumeNavierStokes/FarFieldEulerChar2D.cxx:36-254, FarFieldEulerChar3D.cxx:40-200; value as BC_FARFIELD_EULER
   BC_SUPER_OUTLET_MHD = 6, // FiniteVolumeMHD/SuperOutletMHD3DProjection.cxx:76-239; mask[0] = coronalBC, value[0] = refPhi
   BC_NOSLIP_ISOTHERMAL = 5 // FiniteVolumeNavierStokes/NoSlipWallIsothermalNSvt.ci:178-243; value = TGhostMin, uWall[D], TWall (adimensional)
 };

@@ -340,10 +340,11 @@ cfb200_bc FVMCC_ComputeRHSB200::translateBC(FVMCC_BC* bc, GeometricEntity* probe
   if (has("MirrorEuler2D") || has("MirrorEuler3D") || has("MirrorMHD3DProjection")) {
     out.type = CFB200_BC_MIRROR_EULER_CONS; return out;
   }
-  if (has("FarFieldEuler2D") || has("FarFieldEuler3D")) {
+  if (has("FarFieldEuler2D") || has("FarFieldEuler3D") || has("FarFieldEulerChar2D") || has("FarFieldEulerChar3D")) {
     // constant far field only (no Def functions, no interpolation file); the option strings carry the values
+    // (FarFieldEulerChar2D / 3D derive FarFieldEuler2D / 3D and read the same options)
     const CFuint dim = PhysicalModelStack::getActive()->getDim();
-    out.type = CFB200_BC_FARFIELD_EULER;
+    out.type = has("FarFieldEulerChar") ? CFB200_BC_FARFIELD_EULER_CHAR : CFB200_BC_FARFIELD_EULER;
     out.value[0] = opt("Pressure"); out.value[1] = opt("Uinf"); out.value[2] = opt("Vinf");
     if (dim == 3) out.value[3] = opt("Winf");
     out.value[dim + 1] = opt("Temperature");

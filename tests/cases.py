@@ -117,6 +117,14 @@ def bcs_farfield(dim, pvt):
     return [ff]*(2*dim)
 
 
+def bcs_farfield_char(dim, pvt):
+    """FarFieldEulerChar2D / 3D on every boundary (value = p, u, v, [w,] T at infinity)."""
+    b = bcs_farfield(dim, pvt)
+    for x in b:
+        x.type = B.BC_FARFIELD_EULER_CHAR
+    return b
+
+
 def bcs_mhd3d():
     """SuperInlet (constant Def) / SuperOutlet / MirrorMHD3DProjection."""
     inl = B.make_bc(B.BC_DIRICHLET, mask=[1]*9, value=[1.0, 0.8, 0.0, 0.0, 0.3, 0.1, 0.05, 2.5, 0.0])
@@ -366,6 +374,13 @@ CASES = {
     "euler2d_2nd_quad_face": (lambda: with_stencil(meshgen.quad_channel(10, 8), "Face"),
                               lambda: B.make_config(2, poly_rec=B.PR_LINEARLS, limiter=B.LIM_BARTHJESP, jacobian=True,
                                                     use_full_stencil=True), bcs_euler2d, False),
+    # FarFieldEulerChar2D / 3D: subsonic in / out by the mean Riemann invariant (2D Puvt, 3D Pvt), supersonic in / out (Cons)
+    "ns2d_farfield_char_sub": (lambda: meshgen.quad_channel(10, 8), ns2d_cfg, lambda: bcs_farfield_char(2, True), True),
+    "ns3d_farfield_char_sub": (lambda: meshgen.hex_box(5, 4, 4), ns3d_cfg, lambda: bcs_farfield_char(3, True), True),
+    "ns3d_farfield_char_super": (lambda: meshgen.tet_box(3, 3, 2), ns3d_cfg, lambda: bcs_farfield_char(3, True), "pvt_fast"),
+    "euler2d_farfield_char_super": (lambda: meshgen.quad_channel(12, 9, triangles=True),
+                                    lambda: B.make_config(2, poly_rec=B.PR_LINEARLS, limiter=B.LIM_VENKTN, jacobian=True),
+                                    lambda: bcs_farfield_char(2, False), "cons_fast"),
     # single cell / single row edge cases
     "ns3d_single_cell": (lambda: meshgen.hex_box(1, 1, 1, jitter=0.0), ns3d_cfg, bcs_ns3d, True),
     "euler2d_single_row": (lambda: meshgen.quad_channel(5, 1), lambda: B.make_config(2, poly_rec=B.PR_LINEARLS,
