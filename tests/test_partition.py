@@ -61,6 +61,8 @@ def test_partition_structure():
                                                ("ns3d_hex_correctedgg", 2, "global"), ("ns2d_quad_statediff", 2, "global"),
                                                ("ns3d_hex_ausmplusup_analytic", 2, "global"),
                                                ("mhd3d_hex_hll_dipole", 2, "global"),
+                                               ("mhd3d_hex_hll_outlet_coronal", 2, "global"),      # + MHDConsACAST source term
+                                               ("ns3d_farfield_char_sub", 2, "global"),
                                                ("ns3d_hex", 2, "grouped"), ("ns3d_tet", 2, "grouped")])
 def test_partition_matches_single_domain(name, nparts, order, oracle, hostsim_lib):
     mesh_f, cfg_f, bcs_f, pvt = cases.CASES[name]
