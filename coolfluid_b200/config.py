@@ -12,6 +12,7 @@ import math
 MAXEQ = 9
 
 # enums (must match include/cfb200.h and oracle/cfo_types.hpp)
+ABI_VERSION = 3                      # CFB200_ABI_VERSION of include/cfb200.h (the struct mirrors below follow it)
 PM_EULER, PM_MHD3D_PROJECTION = 0, 1
 ST_NONE, ST_MHD_CONS_ACA = 0, 1      # Data.SourceTerm: none, MHDConsACAST (phi damping)
 DV_DIAMOND, DV_CORRECTED, DV_STATEDIFF, DV_CORRECTED_GG = 0, 1, 2, 3

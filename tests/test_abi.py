@@ -18,7 +18,7 @@ def test_header_symbols_exported(product_lib):
     missing = [s for s in declared if not hasattr(dll, s)]
     assert missing == []
     assert sorted("cfb200_" + s for s in cl.ABI_SYMBOLS) == declared
-    assert dll.cfb200_abi_version() == 3
+    assert dll.cfb200_abi_version() == B.ABI_VERSION == 3
 
 
 def test_struct_layouts_match_the_oracle(oracle):
@@ -70,3 +70,13 @@ def test_invalid_arguments(product_lib):
                         jacobian="analytic", derivative="correctedgg")      # getGradientsJacob of CorrectedGG is a stub
     assert product_lib.create(C.byref(cfg), 0, C.byref(h)) == 6
     assert product_lib.compute_rhs(None, 1, None, None) == 2
+
+
+def test_graft_entry_build_passes(product_lib):
+    """__graft_entry__.build() is what the driver runs first: its own consistency checks (ABI version of the built library
+    against the Python mirrors) must hold for the tree as it is."""
+    import importlib
+    import sys
+    sys.path.insert(0, ROOT)
+    ge = importlib.import_module("__graft_entry__")
+    ge.build()
