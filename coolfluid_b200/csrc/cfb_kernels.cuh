@@ -35,9 +35,6 @@ struct Dev {
   const double* cvol; const uint8_t* cvSign; const int* faceBC;
   const double* bcFaceVal;    // [q][nGhosts] position-dependent Dirichlet data (cfb200_set_bc_face_values), or null
   const uint8_t* bcFaceFlag;  // [nGhosts] 1 where bcFaceVal replaces BCond::value
-  // "DistanceBasedGMove" (DistanceBasedExtrapolatorGMove.cxx:167-173): nodes whose extrapolated values nodePrescIdx[i] are
-  // overwritten by nodePrescVal[i] (cfb200_set_nodal_prescribed); null = plain "DistanceBased"
-  const uint8_t* nodePresc; const int* nodePrescIdx; const double* nodePrescVal; int nNodePresc;
   const double* bcWallRatio;  // [nGhosts] (inner-ghost)/(inner-wall) distance ratio of FVMCC_BaseBC::computeGhostPosition, or null
   const int* bndStPtr; const int* bndSt;           // Corrected2D/3D: gradient stencil of each boundary face (CSR over ghosts)
   const int* ggPtr; const int* ggNode;   // CorrectedGG: per cell, the nodes of its faces in computeGradientsGG order (CSR over cells)
@@ -71,6 +68,11 @@ struct Dev {
   double* aos;                // staging [max(nStates,nNodes)*q]
   double* partial;            // reduction scratch
   int* status;
+  // "DistanceBasedGMove" (DistanceBasedExtrapolatorGMove.cxx:167-173): nodes whose extrapolated values nodePrescIdx[i] are
+  // overwritten by nodePrescVal[i] (cfb200_set_nodal_prescribed); null = plain "DistanceBased".  Kept at the END of the
+  // struct: the kernel-parameter offsets of everything above are those of the binaries profiled in round 2 (the face kernel's
+  // register allocation moved from 252 to 238 registers, 27.4 -> 28.3 ms, when these sat in the middle)
+  const uint8_t* nodePresc; const int* nodePrescIdx; const double* nodePrescVal; int nNodePresc;
 };
 
 CFB_HD int refId(const Dev& d, int cell) { return d.cellRef ? d.cellRef[cell] : cell; }
@@ -695,6 +697,9 @@ struct DivBGather {   // idx over cells
 template <int D, class PH = Phys<D>, bool FUSED = false, bool SRC = false>
 struct DiagGather {   // idx over nCells*GS: one thread per (cell, block entry), no idle lanes
   static constexpr int GS = PH::Q*PH::Q;
+  // 16 resident 128-thread blocks = 2048 threads per SM = 32 registers: measured 4.15 ms at 90 % occupancy against 4.95 ms
+  // at the 36 registers (67 %) the unconstrained allocation sometimes picks (220^3, fused time term)
+  static constexpr int MINB = 16;
   Dev d; int cell0;      // cell0: first cell of this launch (chunks of < 2^31 entries start at a cell boundary)
   Cfg c;                 // read by the SRC variant only
   CFB_HD void operator()(int idx) const {
