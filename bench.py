@@ -395,7 +395,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cfb200")
     # (--edge is the spelling to use under torchrun, whose own parser takes a bare --n for an abbreviation of --nnodes)
-    ap.add_argument("--n", "--edge", dest="n", type=int, default=220, help="hex box edge per GPU (220^3 = 10.6 M cells, configs[2])")
+    ap.add_argument("--n", "--edge", dest="n", type=int, default=None, help="hex box edge per GPU (default 220: 220^3 = 10.6 M cells, "
+                    "configs[2]; ns3d_tet: 100, i.e. 6 M tetrahedra, whose ~60-entry stencils keep the 32-bit tables in range)")
     ap.add_argument("--workload", default="ns3d", choices=sorted(WORKLOADS), help="ns3d = configs[2] (the metric), euler2d_* = configs[1], mhd3d = configs[3]")
     ap.add_argument("--cpu-layers", type=int, default=8, help="cell layers (of n x n cells) per host thread of the CPU arm: the "
                     "bounded sample of each thread's share of the n^3 mesh (0 = the whole share)")
@@ -410,6 +411,8 @@ def main():
     ap.add_argument("--renumber", action="store_true", help="cfg.renumber: space-filling-curve storage order inside the engine")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    if args.n is None:
+        args.n = 100 if args.workload == "ns3d_tet" else 220
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

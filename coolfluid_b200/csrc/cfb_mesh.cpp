@@ -47,6 +47,14 @@ template <class F> void parallelFor(int n, F f) {
   for (auto& x : th) x.join();
 }
 
+// the flat mesh of the C ABI indexes its CSR tables with 32-bit offsets (cfb200_mesh): a table that does not fit is an error
+// of the caller's mesh size, reported (cfb200_mesh_build returns NULL) instead of wrapping around
+inline void checkCsrTotal(const std::vector<int32_t>& counts, const char* what) {
+  int64_t total = 0;
+  for (int32_t c : counts) total += c;
+  if (total > (int64_t)INT32_MAX) throw std::length_error(std::string(what) + " table exceeds 2^31 entries");
+}
+
 inline void cross(const double* a, const double* b, double* r) {
   r[0] =  a[1]*b[2] - a[2]*b[1];
   r[1] = -a[0]*b[2] + a[2]*b[0];
@@ -388,6 +396,7 @@ void build(cfb200_meshdata& M, int dim, int nNodes, const double* nodes, int nCe
       }
     });
     M.stencilPtr.assign(nCells + 1, 0);
+    checkCsrTotal(counts, "stencil");
     for (int e = 0; e < nCells; ++e) M.stencilPtr[e+1] = M.stencilPtr[e] + counts[e];
     M.stencil.resize(M.stencilPtr[nCells]);
     for (unsigned t = 0; t < nt; ++t)
@@ -559,6 +568,7 @@ int rebuildStencil(cfb200_meshdata& M, int kind) {
     }
   });
   M.stencilPtr.assign(nCells + 1, 0);
+  checkCsrTotal(counts, "stencil");
   for (int e = 0; e < nCells; ++e) M.stencilPtr[e+1] = M.stencilPtr[e] + counts[e];
   M.stencil.assign(M.stencilPtr[nCells], 0);
   for (unsigned t = 0; t < nt; ++t)
