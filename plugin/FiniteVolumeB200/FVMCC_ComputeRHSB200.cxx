@@ -64,6 +64,7 @@ void FVMCC_ComputeRHSB200::defineConfigOptions(Config::OptionList& options)
   options.addConfigOption< CFreal >("TRef", "Reference temperature of the configured viscosity law.");
   options.addConfigOption< CFreal >("SuthConst", "Sutherland constant of the configured viscosity law.");
   options.addConfigOption< CFreal >("FixedVisc", "Viscosity of a constant viscosity law.");
+  options.addConfigOption< bool >("RefreshInletValues", "Re-evaluate the Dirichlet-type boundary commands (SuperInlet ...) on every face before each evaluation: for Def functions of time or iteration.");
   options.addConfigOption< bool >("FuseTimeRhs", "Apply the pseudo-steady time term inside this command (ComputeTimeRHS must then be Null).");
   options.addConfigOption< bool >("useAnalyticalMatrix", "As PseudoSteadyTimeRhs.useAnalyticalMatrix (fused time term).");
   options.addConfigOption< bool >("useGlobalDT", "As PseudoSteadyTimeRhs.useGlobalDT.");
@@ -81,6 +82,7 @@ FVMCC_ComputeRHSB200::FVMCC_ComputeRHSB200(const std::string& name) :
   m_viscTRef = 0.;       setParameter("TRef", &m_viscTRef);
   m_viscSuthConst = 0.;  setParameter("SuthConst", &m_viscSuthConst);
   m_fixedVisc = 1.;      setParameter("FixedVisc", &m_fixedVisc);
+  m_refreshInletValues = false; setParameter("RefreshInletValues", &m_refreshInletValues);
   m_fuseTimeRhs = false; setParameter("FuseTimeRhs", &m_fuseTimeRhs);
   m_timeAnalyticalMatrix = false; setParameter("useAnalyticalMatrix", &m_timeAnalyticalMatrix);
   m_timeUseGlobalDT = false;      setParameter("useGlobalDT", &m_timeUseGlobalDT);
@@ -449,6 +451,7 @@ void FVMCC_ComputeRHSB200::uploadMesh()
       bcs.push_back(translateBC(bc, probe, nEqs));
       if (probe != CFNULL) geoBuilder->releaseGE();
       bcIndex = (CFint)bcs.size() - 1;
+      if (bcs[bcIndex].type == CFB200_BC_DIRICHLET) m_dirichletTrs.push_back(std::make_pair(iTRS, bcIndex));
     }
     geoData.trs = currTrs;
     geoData.isBFace = isBFace;
@@ -574,6 +577,41 @@ void FVMCC_ComputeRHSB200::uploadMesh()
   }
 }
 
+// A SuperInlet whose Def depends on time or on the iteration number (SuperInlet.cxx:156-209 evaluates it inside every
+// setGhostState) changes its values between evaluations: with RefreshInletValues the command is applied again to a zero
+// inner state on every face of its TRS (ghost = 2*value) and the values are re-sent (cfb200_set_bc_face_values).
+void FVMCC_ComputeRHSB200::refreshDirichletValues()
+{
+  const CFuint nEqs = PhysicalModelStack::getActive()->getNbEq();
+  std::vector<SafePtr<TopologicalRegionSet> > trsList = MeshDataStack::getActive()->getTrsList();
+  SafePtr<GeometricEntityPool<FaceCellTrsGeoBuilder> > geoBuilder = getMethodData().getFaceCellTrsGeoBuilder();
+  FaceCellTrsGeoBuilder::GeoData& geoData = geoBuilder->getDataGE();
+  SafePtr<CFMap<CFuint, FVMCC_BC*> > bcMap = getMethodData().getMapBC();
+  std::vector<CFreal> values;
+  for (CFuint k = 0; k < m_dirichletTrs.size(); ++k) {
+    const CFuint iTRS = m_dirichletTrs[k].first;
+    SafePtr<TopologicalRegionSet> currTrs = trsList[iTRS];
+    geoData.trs = currTrs; geoData.isBFace = true;
+    const CFuint nbTrsFaces = currTrs->getLocalNbGeoEnts();
+    if (nbTrsFaces == 0) continue;
+    values.assign((size_t)nbTrsFaces*nEqs, 0.);
+    for (CFuint iFace = 0; iFace < nbTrsFaces; ++iFace) {
+      geoData.idx = iFace;
+      GeometricEntity* face = geoBuilder->buildGE();
+      State& inner = *face->getState(0);
+      State& ghost = *face->getState(1);
+      const RealVector innerBkp = inner, ghostBkp = ghost;
+      inner = 0.;
+      bcMap->find(iTRS)->setGhostState(face);
+      for (CFuint v = 0; v < nEqs; ++v) values[(size_t)iFace*nEqs + v] = 0.5*ghost[v];
+      static_cast<RealVector&>(inner) = innerBkp;
+      static_cast<RealVector&>(ghost) = ghostBkp;
+      geoBuilder->releaseGE();
+    }
+    check(cfb200_set_bc_face_values(m_h, m_dirichletTrs[k].second, &values[0]), "cfb200_set_bc_face_values");
+  }
+}
+
 void FVMCC_ComputeRHSB200::execute()
 {
   DataHandle<State*, GLOBAL> states = socket_states.getDataHandle();
@@ -581,6 +619,7 @@ void FVMCC_ComputeRHSB200::execute()
   DataHandle<CFreal> updateCoeff = socket_updateCoeff.getDataHandle();
   refreshStep(m_cfg);
   check(cfb200_set_step(m_h, &m_cfg), "cfb200_set_step");
+  if (m_refreshInletValues) refreshDirichletValues();
   // states are contiguous in the global array (FVMCC_ComputeRHSCell.cu:743)
   check(cfb200_set_states(m_h, states.getGlobalArray()->ptr(), states.size()), "cfb200_set_states");
   check(cfb200_set_update_coeff(m_h, &updateCoeff[0]), "cfb200_set_update_coeff");

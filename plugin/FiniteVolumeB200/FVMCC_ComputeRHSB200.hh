@@ -34,6 +34,7 @@ protected:
   void fillConfig(cfb200_config& c);        ///< static part, once in setup()
   void refreshStep(cfb200_config& c);       ///< per-call scalars (resFactor, iteration, residual, CFL, DT, dynamic options)
   void uploadMesh();
+  void refreshDirichletValues();            ///< option RefreshInletValues: re-probe the Dirichlet-type commands (Def functions of time / iteration)
   cfb200_bc translateBC(FVMCC_BC* bc, Framework::GeometricEntity* probe, CFuint nEqs);
   void insertJacobian();
   void check(int rc, const char* what);
@@ -46,6 +47,8 @@ protected:
   bool m_hostJacobian;     ///< option HostJacobian: copy the BSR back and LSSMatrix::addValues (CPU PETSc); else device view
   CFreal m_viscRef, m_viscTRef, m_viscSuthConst, m_fixedVisc;   ///< constants of the viscosity law (verified in setup())
   bool m_fuseTimeRhs, m_timeAnalyticalMatrix, m_timeUseGlobalDT;
+  bool m_refreshInletValues;                ///< option RefreshInletValues
+  std::vector<std::pair<CFuint, CFint> > m_dirichletTrs;   ///< (TRS index in the TRS list, cfb200_bc record) of the Dirichlet-type commands
   std::vector<bool> m_timeZeroDiag;
   cfb200_config m_cfg;     ///< translated once in setup(), per-call scalars refreshed in execute()
   std::vector<CFreal> m_bsr, m_past;
