@@ -138,6 +138,8 @@ def shuffle_cells(em, seed=4321):
     src = np.repeat(em.cell_node_ptr[perm].astype(np.int64), lnpc) + (np.arange(ptr[-1]) - np.repeat(ptr[:-1], lnpc))
     out = ElementMesh(em.dim, em.nodes, ptr.astype(np.int32), em.cell_nodes[src], em.cell_shape[perm], em.trs_names,
                       em.trs_face_ptr, inv[em.trs_face_cell].astype(np.int32), em.trs_face_node_ptr, em.trs_face_nodes)
+    if hasattr(em, "stencil_kind"):
+        out.stencil_kind = em.stencil_kind
     return out, perm
 
 

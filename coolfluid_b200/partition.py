@@ -207,6 +207,8 @@ def extract(em: ElementMesh, part: np.ndarray, rank: int, nranks: int | None = N
     ptr, fc, fnp, fn = _pack_trs([(c, n) if len(c) else (np.zeros(0, dtype=np.int64), np.zeros((0, 1), dtype=np.int64))
                                   for c, n in trs])
     lem = ElementMesh(em.dim, em.nodes[used], lptr.astype(np.int32), lnodes.astype(np.int32), shape, names, ptr, fc, fnp, fn)
+    if hasattr(em, "stencil_kind"):          # Setup1.stencil of the global mesh (lib.build_mesh reads it)
+        lem.stencil_kind = em.stencil_kind
 
     p = Partition()
     p.rank, p.nranks, p.em, p.cell_l2g = int(rank), nranks, lem, l2g

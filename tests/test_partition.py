@@ -63,6 +63,9 @@ def test_partition_structure():
                                                ("mhd3d_hex_hll_dipole", 2, "global"),
                                                ("mhd3d_hex_hll_outlet_coronal", 2, "global"),      # + MHDConsACAST source term
                                                ("ns3d_farfield_char_sub", 2, "global"),
+                                               ("ns3d_hex_facevertex", 2, "global"),               # Setup1.stencil = FaceVertex
+                                               ("euler2d_2nd_quad_facevertex", 3, "global"),
+                                               ("ns3d_tet_faceedge", 2, "global"), ("euler2d_2nd_quad_face", 2, "global"),
                                                ("ns3d_hex", 2, "grouped"), ("ns3d_tet", 2, "grouped")])
 def test_partition_matches_single_domain(name, nparts, order, oracle, hostsim_lib):
     mesh_f, cfg_f, bcs_f, pvt = cases.CASES[name]
