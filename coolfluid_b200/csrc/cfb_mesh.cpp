@@ -581,19 +581,27 @@ template <class T> const void* vptr(const std::vector<T>& v) { return v.data(); 
 
 } // namespace
 
+namespace { thread_local std::string g_meshError; }     // why the last cfb200_mesh_build of this thread returned NULL
+
 extern "C" {
 
 cfb200_meshdata* cfb200_mesh_build(int dim, int nNodes, const double* nodes, int nCells, const int32_t* cellNodePtr,
                                    const int32_t* cellNodes, const int32_t* cellShape, int nTRS, const int32_t* trsFacePtr,
                                    const int32_t* trsFaceCell, const int32_t* trsFaceNodePtr, const int32_t* trsFaceNodes) {
-  if (!(dim == 2 || dim == 3) || !nodes || !cellNodePtr || !cellNodes || !cellShape || !trsFacePtr) return nullptr;
+  if (!(dim == 2 || dim == 3) || !nodes || !cellNodePtr || !cellNodes || !cellShape || !trsFacePtr) {
+    g_meshError = "cfb200_mesh_build: dim must be 2 or 3 and the element / TRS tables must not be null";
+    return nullptr;
+  }
   cfb200_meshdata* M = new cfb200_meshdata();
   try {
     build(*M, dim, nNodes, nodes, nCells, cellNodePtr, cellNodes, cellShape, nTRS, trsFacePtr, trsFaceCell,
           trsFaceNodePtr, trsFaceNodes);
-  } catch (const std::exception&) { delete M; return nullptr; }
+  } catch (const std::exception& e) { g_meshError = e.what(); delete M; return nullptr; }
+  g_meshError.clear();
   return M;
 }
+
+const char* cfb200_mesh_build_error(void) { return g_meshError.c_str(); }
 
 void cfb200_mesh_sizes(const cfb200_meshdata* M, int64_t* out) {
   out[0] = M->nFaces; out[1] = M->nInner; out[2] = M->nGhosts; out[3] = (int64_t)M->faceNodes.size();

@@ -56,7 +56,7 @@ ABI_SYMBOLS = [
     "get_bsr_values",
     "export_csr", "get_field", "device_ptr", "status", "enable_timing", "last_timings", "stream",
     "nccl_unique_id", "comm_init", "set_halo", "set_independent_cells", "halo_begin", "halo_exchange", "allreduce_sum",
-    "mesh_build", "mesh_sizes", "mesh_get", "mesh_ptr", "mesh_view", "mesh_set_updatable", "mesh_set_stencil", "mesh_free", "mesh_diamond_volumes",
+    "mesh_build", "mesh_build_error", "mesh_sizes", "mesh_get", "mesh_ptr", "mesh_view", "mesh_set_updatable", "mesh_set_stencil", "mesh_free", "mesh_diamond_volumes",
     "selftest_divsqrt", "export_csr_device", "solve_gmres", "l2_norm_noalloc",
 ]
 # symbols the engine part needs (a test-only host build of the kernel functors exports just these)
@@ -121,6 +121,7 @@ def load(path=None, prefix="cfb200_"):
         ns.device_count.restype = C.c_int
         ns.mesh_build.restype = C.c_void_p
         ns.mesh_build.argtypes = [C.c_int, C.c_int, P_D, C.c_int, P_I, P_I, P_I, C.c_int, P_I, P_I, P_I, P_I]
+        ns.mesh_build_error.argtypes = []; ns.mesh_build_error.restype = C.c_char_p
         ns.mesh_sizes.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]; ns.mesh_sizes.restype = None
         ns.mesh_get.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p]
         ns.mesh_ptr.argtypes = [C.c_void_p, C.c_char_p]; ns.mesh_ptr.restype = C.c_void_p
@@ -165,7 +166,7 @@ def build_mesh(em, lib=None, stencil=None) -> FlatMesh:
                      _pi(em.cell_shape), em.n_trs, _pi(em.trs_face_ptr), _pi(em.trs_face_cell),
                      _pi(em.trs_face_node_ptr), _pi(em.trs_face_nodes))
     if not h:
-        raise Cfb200Error(2, "mesh build failed")
+        raise Cfb200Error(2, "mesh build failed: " + (L.mesh_build_error() or b"").decode())
     try:
         if STENCIL_KINDS[stencil] and L.mesh_set_stencil(h, STENCIL_KINDS[stencil]):
             raise Cfb200Error(2, "stencil rebuild failed")

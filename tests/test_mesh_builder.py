@@ -83,6 +83,10 @@ def test_bad_input_returns_null(product_lib):
                                cl._pi(em.cell_nodes), cl._pi(em.cell_shape), em.n_trs, cl._pi(em.trs_face_ptr),
                                cl._pi(bad), cl._pi(em.trs_face_node_ptr), cl._pi(em.trs_face_nodes))
     assert not h
+    msg = product_lib.mesh_build_error().decode()
+    assert msg and "face" in msg.lower()                 # the reason is reported, not only the NULL
+    ok = cl.build_mesh(em, product_lib)
+    assert ok.nFaces > 0 and product_lib.mesh_build_error() == b""
 
 
 def test_diamond_volumes_of_a_caller_built_mesh(product_lib):
