@@ -384,7 +384,7 @@ cfb200_meshdata* cfb200_mesh_build(int dim, int nNodes, const double* nodes, int
                                    int nTRS, const int32_t* trsFacePtr, const int32_t* trsFaceCell,
                                    const int32_t* trsFaceNodePtr, const int32_t* trsFaceNodes);
 /* why the calling thread's last cfb200_mesh_build returned NULL ("" after a success): unsupported element, a boundary face
- * that matches no cell face, a table beyond the 32-bit offsets of cfb200_mesh (e.g. the stencil of > 35 M tetrahedra), ... */
+ * that matches no cell face, a table beyond the 32-bit offsets of the flat mesh struct: the stencil of more than about 35 M tetrahedra, ... */
 const char* cfb200_mesh_build_error(void);
 /* sizes: nFaces, nInner, nGhosts, len(faceNodes), len(cellFaces), len(stencil), len(nodeNbr), nnzb */
 void cfb200_mesh_sizes(const cfb200_meshdata* m, int64_t* out8);
